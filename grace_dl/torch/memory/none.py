@@ -1,0 +1,1 @@
+from grace_b200.memory import NoneMemory  # noqa: F401
