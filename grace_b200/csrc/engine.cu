@@ -1,0 +1,223 @@
+// Communicator, peer arena, flags, status word, event handles.
+//
+// B200-native stand-in for what the reference gets from Horovod's C++ core and c10d/NCCL
+// (patch_files/horovod/torch/mpi_ops.py:28-88,420-439): every rank owns one
+// cudaMalloc'ed arena, exports it with CUDA IPC, and maps all peers' arenas.  Over NVSwitch
+// every peer is one hop away at full bandwidth, so kernels simply store to / load from the
+// mapped pointers; completion is signalled by epoch-numbered flags written with
+// st.release.sys and polled with ld.acquire.sys.  No negotiation thread is needed because
+// every rank issues the same plans in the same order.
+#include "engine.cuh"
+
+#include <stdarg.h>
+
+#include <mutex>
+#include <unordered_map>
+
+static thread_local char g_err[512] = "";
+
+void gb_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char* gb_last_error(void) { return g_err; }
+extern "C" int gb_version(void) { return 100; }
+
+extern "C" int gb_set_device(int device) {
+  GB_CUDA(cudaSetDevice(device));
+  return 0;
+}
+
+static int comm_init_common(gb_comm* c, size_t arena_bytes) {
+  c->bytes = (arena_bytes + 255) & ~size_t(255);
+  GB_CHECK(c->bytes > GB_FLAG_BYTES, "arena of %zu bytes is smaller than the flag region", arena_bytes);
+  GB_CUDA(cudaGetDevice(&c->device));
+  GB_CUDA(cudaMalloc((void**)&c->base, c->bytes));
+  GB_CUDA(cudaMemset(c->base, 0, c->bytes));
+  GB_CUDA(cudaHostAlloc((void**)&c->status_host, 64, cudaHostAllocMapped));
+  memset(c->status_host, 0, 64);
+  GB_CUDA(cudaHostGetDevicePointer((void**)&c->status_dev, c->status_host, 0));
+  c->cursor = GB_FLAG_BYTES;
+  c->next_channel = 1;  // channel 0 is the barrier
+  c->timeout_ns = 20ull * 1000 * 1000 * 1000;
+  c->barrier_epoch = 0;
+  for (int i = 0; i < GB_MAX_WORLD; ++i) { c->peer[i] = nullptr; c->opened[i] = false; }
+  c->peer[c->rank] = c->base;
+  GB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+extern "C" int gb_comm_create(int rank, int world, size_t arena_bytes, gb_comm** out) {
+  GB_CHECK(world >= 1 && world <= GB_MAX_WORLD, "world size %d not in [1, %d]", world, GB_MAX_WORLD);
+  GB_CHECK(rank >= 0 && rank < world, "rank %d out of range", rank);
+  gb_comm* c = new gb_comm();
+  c->rank = rank;
+  c->world = world;
+  c->local_group = false;
+  if (comm_init_common(c, arena_bytes)) { delete c; return -1; }
+  *out = c;
+  return 0;
+}
+
+extern "C" int gb_comm_ipc_handle(gb_comm* c, void* out64) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+  cudaIpcMemHandle_t h;
+  GB_CUDA(cudaIpcGetMemHandle(&h, c->base));
+  memcpy(out64, &h, 64);
+  return 0;
+}
+
+extern "C" int gb_comm_open_peers(gb_comm* c, const void* handles) {
+  for (int r = 0; r < c->world; ++r) {
+    if (r == c->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)handles + 64 * r, 64);
+    void* p = nullptr;
+    GB_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->peer[r] = (char*)p;
+    c->opened[r] = true;
+  }
+  return 0;
+}
+
+extern "C" int gb_comm_create_local(int world, size_t arena_bytes, gb_comm** out) {
+  GB_CHECK(world >= 1 && world <= GB_MAX_WORLD, "world size %d not in [1, %d]", world, GB_MAX_WORLD);
+  for (int r = 0; r < world; ++r) {
+    gb_comm* c = new gb_comm();
+    c->rank = r;
+    c->world = world;
+    c->local_group = true;
+    if (comm_init_common(c, arena_bytes)) return -1;
+    out[r] = c;
+  }
+  for (int r = 0; r < world; ++r)
+    for (int q = 0; q < world; ++q) out[r]->peer[q] = out[q]->base;
+  return 0;
+}
+
+extern "C" int gb_comm_destroy(gb_comm* c) {
+  if (!c) return 0;
+  cudaDeviceSynchronize();
+  for (int r = 0; r < c->world; ++r)
+    if (c->opened[r]) cudaIpcCloseMemHandle(c->peer[r]);
+  cudaFree(c->base);
+  cudaFreeHost(c->status_host);
+  delete c;
+  return 0;
+}
+
+extern "C" int gb_comm_status(gb_comm* c, uint32_t* out) {
+  *out = *(volatile uint32_t*)c->status_host;
+  return 0;
+}
+extern "C" int gb_comm_clear_status(gb_comm* c) {
+  *(volatile uint32_t*)c->status_host = 0;
+  return 0;
+}
+extern "C" int gb_comm_set_timeout_ms(gb_comm* c, uint64_t ms) {
+  c->timeout_ns = ms * 1000000ull;
+  return 0;
+}
+extern "C" int gb_comm_rank(gb_comm* c) { return c->rank; }
+extern "C" int gb_comm_world(gb_comm* c) { return c->world; }
+extern "C" size_t gb_comm_arena_free(gb_comm* c) { return c->bytes - c->cursor; }
+
+int gb_comm_alloc_channel(gb_comm* c, size_t slot_bytes, int* channel, size_t* offset) {
+  size_t need = ((slot_bytes + 255) & ~size_t(255)) * 2 * (size_t)c->world;
+  GB_CHECK(c->next_channel < GB_MAX_CHANNELS, "out of flag channels (%d)", GB_MAX_CHANNELS);
+  GB_CHECK(c->cursor + need <= c->bytes,
+           "peer arena exhausted: need %zu more bytes, %zu free (create the communicator with a larger arena)", need,
+           c->bytes - c->cursor);
+  *channel = c->next_channel++;
+  *offset = c->cursor;
+  c->cursor += need;
+  return 0;
+}
+
+PeerPtrs gb_comm_peers(const gb_comm* c) {
+  PeerPtrs p;
+  for (int i = 0; i < GB_MAX_WORLD; ++i) p.base[i] = i < c->world ? c->peer[i] : nullptr;
+  p.world = c->world;
+  p.rank = c->rank;
+  return p;
+}
+
+// ---------------------------------------------------------------- flag barrier
+__global__ void barrier_kernel(PeerPtrs peers, uint32_t epoch, uint32_t* status, uint64_t timeout_ns) {
+  int r = threadIdx.x;
+  if (r < peers.world) {
+    __threadfence_system();
+    st_release_sys(gb_flag(peers.base[r], 0, epoch & 1, peers.rank), epoch);
+    wait_flag(gb_flag(peers.base[peers.rank], 0, epoch & 1, r), epoch, status, timeout_ns);
+  }
+}
+
+extern "C" int gb_comm_barrier(gb_comm* c, void* stream) {
+  c->barrier_epoch++;
+  barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(gb_comm_peers(c), c->barrier_epoch, c->status_dev, c->timeout_ns);
+  GB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------- event handles
+static std::mutex g_hmu;
+static std::unordered_map<int64_t, cudaEvent_t> g_handles;
+static int64_t g_next_handle = 1;
+
+extern "C" int gb_handle_record(void* stream, int64_t* out_handle) {
+  cudaEvent_t ev;
+  GB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  GB_CUDA(cudaEventRecord(ev, (cudaStream_t)stream));
+  std::lock_guard<std::mutex> lk(g_hmu);
+  *out_handle = g_next_handle++;
+  g_handles[*out_handle] = ev;
+  return 0;
+}
+
+static bool find_handle(int64_t h, cudaEvent_t* ev) {
+  std::lock_guard<std::mutex> lk(g_hmu);
+  auto it = g_handles.find(h);
+  if (it == g_handles.end()) return false;
+  *ev = it->second;
+  return true;
+}
+
+extern "C" int gb_handle_poll(int64_t handle) {
+  cudaEvent_t ev;
+  GB_CHECK(find_handle(handle, &ev), "unknown handle %lld", (long long)handle);
+  cudaError_t e = cudaEventQuery(ev);
+  if (e == cudaSuccess) return 1;
+  if (e == cudaErrorNotReady) return 0;
+  gb_set_error("cudaEventQuery: %s", cudaGetErrorString(e));
+  return -1;
+}
+
+extern "C" int gb_handle_release(int64_t handle) {
+  cudaEvent_t ev;
+  {
+    std::lock_guard<std::mutex> lk(g_hmu);
+    auto it = g_handles.find(handle);
+    if (it == g_handles.end()) return 0;
+    ev = it->second;
+    g_handles.erase(it);
+  }
+  cudaEventDestroy(ev);
+  return 0;
+}
+
+extern "C" int gb_handle_wait(int64_t handle) {
+  cudaEvent_t ev;
+  GB_CHECK(find_handle(handle, &ev), "unknown handle %lld", (long long)handle);
+  GB_CUDA(cudaEventSynchronize(ev));
+  return gb_handle_release(handle);
+}
+
+extern "C" int gb_handle_stream_wait(int64_t handle, void* stream) {
+  cudaEvent_t ev;
+  GB_CHECK(find_handle(handle, &ev), "unknown handle %lld", (long long)handle);
+  GB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, ev, 0));
+  return 0;
+}

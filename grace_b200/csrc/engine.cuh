@@ -1,0 +1,69 @@
+// Internal structures shared by the translation units of libgrace_b200.
+#pragma once
+#include "../../include/grace_b200.h"
+#include "common.cuh"
+
+#include <vector>
+
+#define GB_MAX_CHANNELS 512
+// flags[channel][parity][src_rank] : uint32 epochs, at the start of every arena
+#define GB_FLAG_BYTES (GB_MAX_CHANNELS * 2 * GB_MAX_WORLD * 4)
+
+__host__ __device__ __forceinline__ uint32_t* gb_flag(char* arena, int channel, int parity, int src) {
+  return (uint32_t*)arena + ((size_t)channel * 2 + parity) * GB_MAX_WORLD + src;
+}
+
+struct gb_comm {
+  int rank, world, device;
+  bool local_group;          // all ranks live in this process on one device (emulation)
+  char* base;                // local arena
+  size_t bytes;
+  char* peer[GB_MAX_WORLD];  // mapped arenas, peer[rank] == base
+  bool opened[GB_MAX_WORLD];
+  size_t cursor;             // symmetric bump allocator (same call sequence on every rank)
+  int next_channel;
+  uint32_t* status_host;     // pinned + mapped: kernels report timeouts/overflow here
+  uint32_t* status_dev;
+  uint64_t timeout_ns;
+  uint32_t barrier_epoch;
+};
+
+int gb_comm_alloc_channel(gb_comm* c, size_t slot_bytes, int* channel, size_t* offset);
+PeerPtrs gb_comm_peers(const gb_comm* c);
+
+// Slot r of parity q of a channel inside one arena.
+__host__ __device__ __forceinline__ char* gb_slot(char* arena, size_t chan_off, size_t slot_bytes, int world, int parity,
+                                                   int src) {
+  return arena + chan_off + ((size_t)parity * world + src) * slot_bytes;
+}
+
+struct gb_plan {
+  gb_comm* comm;
+  gb_codec_params prm;
+  int nseg, ntiles;
+  int64_t padded, ktotal;
+  // host copies of the geometry
+  std::vector<int64_t> h_off, h_kbase;
+  std::vector<int32_t> h_numel, h_k, h_tile0;
+  // device geometry
+  SegTable tab;
+  void* d_tables;
+  // persistent state (padded floats, zero-initialised)
+  float* d_state0;  // residual (ResidualMemory) or DGC accumulated gradient v
+  float* d_state1;  // Signum momentum or DGC velocity u
+  // scratch
+  uint32_t* d_hist;      // [nseg][2048]
+  uint32_t* d_sel;       // [nseg][4]: prefix, k_remaining, threshold bits, ties to take
+  int32_t* d_tilecnt;    // [ntiles][2] then scanned in place
+  float* d_tilestats;    // [ntiles][4]
+  float* d_segstats;     // [nseg][4]
+  uint32_t* d_done;      // last-block-done counters
+  // wire
+  int channel;
+  size_t chan_off, slot_bytes;
+  size_t hdr_bytes;      // per-slot header (counts / stats)
+  int bits;              // quantiser bits per element
+  uint32_t epoch;        // exchanges completed (flag value of the next send = epoch + 1)
+  uint32_t step;         // codec call counter (Philox counter word 1)
+  int64_t launches;
+};

@@ -1,0 +1,783 @@
+// K1 -- sparsifier family: TopK, Threshold, RandomK, DGC.
+//
+// Replaces, per bucket instead of per tensor, the reference op chains
+//   memory/residual.py:10-20 (compensate / update), compressor/topk.py:6-18 (abs, topk,
+//   gather, zeros + scatter_), compressor/threshold.py:17-18 (where), compressor/randomk.py:6-12
+//   (randperm, index), communicator/allgather.py:8-45 (all_gather, W x scatter, sum, div)
+// by (SURVEY §2.9-B, rows TopK/Threshold/RandomK):
+//   send:  pass1  compensate (written in place into the residual buffer) + radix histogram
+//          select exact per-segment threshold by 3 histogram rounds (11+10+10 bits of |x|)
+//          count / scan / emit: index-ORDERED compaction; (value, index32) pairs are stored
+//          straight into every peer's slot (P2P st.global over NVLink); selected positions
+//          are zeroed in place, which leaves the new residual; last CTA releases the flags.
+//   recv:  acquire W flags; each CTA owns one output tile, adds the W ranks' entries for that
+//          tile in rank order in shared memory and writes the tile once (no zero-fill pass, no
+//          atomics, bit-identical on every rank).
+// Ties at the threshold magnitude are broken towards the lowest index (the reference leaves
+// the order unspecified: torch.topk(sorted=False)).
+#include "kernels.cuh"
+
+struct SparseOut {
+  float* vals[GB_MAX_WORLD];
+  int32_t* idx[GB_MAX_WORLD];
+  int2* hdr[GB_MAX_WORLD];
+  int n;
+};
+
+__device__ __forceinline__ float4 load4(const float* p, int e0, int len) {
+  if (e0 + 4 <= len) return *reinterpret_cast<const float4*>(p + e0);
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (e0 < len) v.x = p[e0];
+  if (e0 + 1 < len) v.y = p[e0 + 1];
+  if (e0 + 2 < len) v.z = p[e0 + 2];
+  if (e0 + 3 < len) v.w = p[e0 + 3];
+  return v;
+}
+__device__ __forceinline__ void store4(float* p, int e0, int len, float4 v) {
+  if (e0 + 4 <= len) { *reinterpret_cast<float4*>(p + e0) = v; return; }
+  if (e0 < len) p[e0] = v.x;
+  if (e0 + 1 < len) p[e0 + 1] = v.y;
+  if (e0 + 2 < len) p[e0 + 2] = v.z;
+  if (e0 + 3 < len) p[e0 + 3] = v.w;
+}
+__device__ __forceinline__ float compensate1(float beta, float r, float gamma, float g) {
+  // two roundings like torch's  beta * e + gamma * g  (no fma contraction)
+  return __fadd_rn(__fmul_rn(beta, r), __fmul_rn(gamma, g));
+}
+__device__ __forceinline__ uint32_t absbits(float v) { return __float_as_uint(v) & 0x7FFFFFFFu; }
+
+__device__ __forceinline__ void flush_hist(uint32_t* sh, uint32_t* dst, int nbins) {
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x) {
+    uint32_t c = sh[b];
+    if (c) atomicAdd(dst + b, c);
+    sh[b] = 0;
+  }
+}
+
+// ROUND 0: compensate (+ write) and histogram bits[30:20].  ROUND 1/2: histogram the next 10
+// bits of the elements whose leading bits equal the prefix chosen so far.
+template <int ROUND, bool WRITE>
+__global__ void __launch_bounds__(GB_THREADS) k1_hist(SegTable t, const float* __restrict__ grad, float* work, float beta,
+                                                      float gamma, uint32_t* hist, const uint32_t* __restrict__ sel) {
+  constexpr int NB = ROUND == 0 ? 2048 : 1024;
+  __shared__ uint32_t sh[NB];
+  const int per = (t.ntiles + gridDim.x - 1) / gridDim.x;
+  const int t0 = blockIdx.x * per;
+  const int t1 = min(t0 + per, t.ntiles);
+  if (t0 >= t1) return;
+  for (int b = threadIdx.x; b < NB; b += blockDim.x) sh[b] = 0;
+  __syncthreads();
+  int cur = t.tile_seg[t0];
+  uint32_t prefix = ROUND == 0 ? 0u : sel[cur * 4];
+  for (int tile = t0; tile < t1; ++tile) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    if (seg != cur) {
+      __syncthreads();
+      flush_hist(sh, hist + (size_t)cur * 2048, NB);
+      __syncthreads();
+      cur = seg;
+      if (ROUND != 0) prefix = sel[cur * 4];
+    }
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      float4 v;
+      if (ROUND == 0) {
+        v = load4(grad + base, e0, len);
+        if (WRITE) {
+          float4 r = load4(work + base, e0, len);
+          v.x = compensate1(beta, r.x, gamma, v.x);
+          v.y = compensate1(beta, r.y, gamma, v.y);
+          v.z = compensate1(beta, r.z, gamma, v.z);
+          v.w = compensate1(beta, r.w, gamma, v.w);
+          store4(work + base, e0, len, v);
+        }
+      } else {
+        v = load4(work + base, e0, len);
+      }
+      const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (e0 + q >= len) break;
+        const uint32_t b = absbits(vv[q]);
+        if (ROUND == 0) atomicAdd(&sh[b >> 20], 1u);
+        else if (ROUND == 1) { if ((b >> 20) == prefix) atomicAdd(&sh[(b >> 10) & 1023u], 1u); }
+        else { if ((b >> 10) == prefix) atomicAdd(&sh[b & 1023u], 1u); }
+      }
+    }
+  }
+  __syncthreads();
+  flush_hist(sh, hist + (size_t)cur * 2048, NB);
+}
+
+// One CTA per segment: walk the histogram from the top bin down to the bin holding the
+// k-th largest magnitude; extend the prefix, update k_remaining, re-zero the histogram.
+__global__ void __launch_bounds__(GB_THREADS) k1_select(SegTable t, uint32_t* hist, uint32_t* sel, int round) {
+  __shared__ uint32_t part[GB_THREADS];
+  const int seg = blockIdx.x;
+  const int nb = round == 0 ? 2048 : 1024;
+  const int per = nb / GB_THREADS;
+  uint32_t* h = hist + (size_t)seg * 2048;
+  const uint32_t k_rem = round == 0 ? (uint32_t)t.seg_k[seg] : sel[seg * 4 + 1];
+  const uint32_t prefix = round == 0 ? 0u : sel[seg * 4];
+  const int hi = nb - 1 - threadIdx.x * per;       // this thread's bins: hi, hi-1, ..., hi-per+1
+  uint32_t c[8];
+  uint32_t mine = 0;
+  for (int i = 0; i < per; ++i) { c[i] = h[hi - i]; mine += c[i]; h[hi - i] = 0; }
+  part[threadIdx.x] = mine;
+  __syncthreads();
+  for (int o = 1; o < GB_THREADS; o <<= 1) {           // inclusive Hillis-Steele scan
+    uint32_t add = threadIdx.x >= o ? part[threadIdx.x - o] : 0u;
+    __syncthreads();
+    part[threadIdx.x] += add;
+    __syncthreads();
+  }
+  uint32_t running = part[threadIdx.x] - mine;      // elements in strictly higher bins
+  for (int i = 0; i < per; ++i) {
+    if (running < k_rem && running + c[i] >= k_rem) {
+      const uint32_t bin = (uint32_t)(hi - i);
+      sel[seg * 4] = round == 0 ? bin : ((prefix << 10) | bin);
+      sel[seg * 4 + 1] = k_rem - running;           // still to take inside this bin
+    }
+    running += c[i];
+  }
+}
+
+__device__ __forceinline__ int block_sum_i(int v, int* sh) {
+  v = warp_sum_i(v);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  int tot = 0;
+  for (int w = 0; w < GB_THREADS / 32; ++w) tot += sh[w];
+  __syncthreads();
+  return tot;
+}
+
+// per tile: how many magnitudes are above / equal to the segment threshold
+__global__ void __launch_bounds__(GB_THREADS) k1_count(SegTable t, const float* __restrict__ work,
+                                                       const uint32_t* __restrict__ sel, uint32_t fixed_thr, int use_fixed,
+                                                       int ge, int32_t* tilecnt) {
+  __shared__ int sh[GB_THREADS / 32];
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    const uint32_t thr = use_fixed ? fixed_thr : sel[seg * 4];
+    int gt = 0, eq = 0;
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      float4 v = load4(work + base, e0, len);
+      const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (e0 + q >= len) break;
+        const uint32_t b = absbits(vv[q]);
+        gt += ge ? (b >= thr) : (b > thr);
+        eq += ge ? 0 : (b == thr);
+      }
+    }
+    gt = block_sum_i(gt, sh);
+    eq = block_sum_i(eq, sh);
+    if (threadIdx.x == 0) { tilecnt[tile * 2] = gt; tilecnt[tile * 2 + 1] = eq; }
+  }
+}
+
+// Exclusive scan of the tile counts.  PER_SEGMENT: one CTA per segment, positions start at the
+// segment's fixed payload base (TopK).  Otherwise one CTA scans the whole bucket (variable-size).
+// Output per tile: {first payload position, number of threshold ties before this tile}.
+template <bool PER_SEGMENT>
+__global__ void __launch_bounds__(GB_THREADS) k1_scan(SegTable t, const uint32_t* __restrict__ sel, int32_t* tilecnt) {
+  __shared__ int sg[GB_THREADS], se[GB_THREADS];
+  const int seg = blockIdx.x;
+  const int first = PER_SEGMENT ? t.seg_tile0[seg] : 0;
+  const int last = PER_SEGMENT ? t.seg_tile0[seg + 1] : t.ntiles;
+  const int take = PER_SEGMENT ? (int)sel[seg * 4 + 1] : 0;
+  const int64_t kbase = PER_SEGMENT ? t.seg_kbase[seg] : 0;
+  int carry_g = 0, carry_e = 0;
+  for (int c0 = first; c0 < last; c0 += GB_THREADS) {
+    const int tile = c0 + threadIdx.x;
+    const int g = tile < last ? tilecnt[tile * 2] : 0;
+    const int e = tile < last ? tilecnt[tile * 2 + 1] : 0;
+    sg[threadIdx.x] = g;
+    se[threadIdx.x] = e;
+    __syncthreads();
+    for (int o = 1; o < GB_THREADS; o <<= 1) {
+      int ag = threadIdx.x >= o ? sg[threadIdx.x - o] : 0;
+      int ae = threadIdx.x >= o ? se[threadIdx.x - o] : 0;
+      __syncthreads();
+      sg[threadIdx.x] += ag;
+      se[threadIdx.x] += ae;
+      __syncthreads();
+    }
+    const int g_before = carry_g + sg[threadIdx.x] - g;
+    const int e_before = carry_e + se[threadIdx.x] - e;
+    if (tile < last) {
+      tilecnt[tile * 2] = (int)kbase + g_before + min(e_before, take);
+      tilecnt[tile * 2 + 1] = e_before;
+    }
+    carry_g += sg[GB_THREADS - 1];
+    carry_e += se[GB_THREADS - 1];
+    __syncthreads();
+  }
+}
+
+// block-wide exclusive scan of one int per thread (256 threads); returns total in `total`
+__device__ __forceinline__ int block_excl_scan(int v, int* sh, int& total) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int n = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += n;
+  }
+  if (lane == 31) sh[wid] = inc;
+  __syncthreads();
+  int woff = 0, tot = 0;
+  for (int w = 0; w < GB_THREADS / 32; ++w) {
+    int s = sh[w];
+    if (w < wid) woff += s;
+    tot += s;
+  }
+  __syncthreads();
+  total = tot;
+  return woff + inc - v;
+}
+
+// Ordered compaction + peer stores + in-place residual update + flag release.
+template <bool ZERO>
+__global__ void __launch_bounds__(GB_THREADS) k1_emit(SegTable t, float* work, float* work2, const uint32_t* __restrict__ sel,
+                                                      uint32_t fixed_thr, int use_fixed, int ge,
+                                                      const int32_t* __restrict__ tilecnt,
+                                                      SparseOut out, int64_t capacity, uint32_t* status, uint32_t* done,
+                                                      PeerPtrs peers, int channel, uint32_t epoch, int release) {
+  __shared__ int sh[GB_THREADS / 32];
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    const uint32_t thr = use_fixed ? fixed_thr : sel[seg * 4];
+    const int take = use_fixed ? 0 : (int)sel[seg * 4 + 1];
+    const int begin = tilecnt[tile * 2];
+    int run_g = 0;                                   // selected-above-threshold so far in this tile
+    int run_e = tilecnt[tile * 2 + 1];               // ties seen so far in this segment
+    const int e_start = run_e;
+#pragma unroll 1
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (e0 < len) v = load4(work + base, e0, len);
+      const float vv[4] = {v.x, v.y, v.z, v.w};
+      int g = 0, e = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (e0 + q < len) {
+          const uint32_t b = absbits(vv[q]);
+          g += ge ? (b >= thr) : (b > thr);
+          e += ge ? 0 : (b == thr);
+        }
+      }
+      int tot;
+      const int packed = block_excl_scan(g | (e << 16), sh, tot);
+      int g_before = run_g + (packed & 0xFFFF);
+      int e_before = run_e + (packed >> 16);
+      bool changed = false;
+      bool pk[4] = {false, false, false, false};
+      float nv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (e0 + q < len) {
+          const uint32_t b = absbits(vv[q]);
+          const bool is_g = ge ? (b >= thr) : (b > thr), is_e = ge ? false : (b == thr);
+          const bool pick = is_g || (is_e && e_before < take);
+          if (pick) {
+            const int64_t pos = (int64_t)begin + g_before + (min(e_before, take) - min(e_start, take));
+            if (pos < capacity) {
+              const int32_t li = local0 + e0 + q;
+              for (int r = 0; r < out.n; ++r) { out.vals[r][pos] = vv[q]; out.idx[r][pos] = li; }
+            } else {
+              atomicOr(status, GB_STATUS_OVERFLOW);
+            }
+            nv[q] = 0.f;
+            pk[q] = true;
+            changed = true;
+          }
+          g_before += is_g;
+          e_before += is_e;
+        }
+      }
+      if (ZERO && changed) {
+        store4(work + base, e0, len, make_float4(nv[0], nv[1], nv[2], nv[3]));
+        if (work2) {                                   // DgcMemory.update masks u as well as v
+          float4 u = load4(work2 + base, e0, len);
+          if (pk[0]) u.x = 0.f;
+          if (pk[1]) u.y = 0.f;
+          if (pk[2]) u.z = 0.f;
+          if (pk[3]) u.w = 0.f;
+          store4(work2 + base, e0, len, u);
+        }
+      }
+      run_g += tot & 0xFFFF;
+      run_e += tot >> 16;
+    }
+    if (threadIdx.x == 0) {
+      int64_t cnt = run_g + (min(run_e, take) - min(e_start, take));
+      if ((int64_t)begin + cnt > capacity) cnt = max((int64_t)0, capacity - begin);
+      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = make_int2(begin, (int)cnt);
+    }
+  }
+  if (release) release_flags_last_block(done, peers, channel, epoch);
+}
+
+// Receive: ordered merge of W sparse lists into the dense aggregate.
+struct SparseIn {
+  const float* vals[GB_MAX_WORLD];
+  const int32_t* idx[GB_MAX_WORLD];
+  const int2* hdr[GB_MAX_WORLD];
+  int n;
+};
+
+__global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, float* out, float divisor, PeerPtrs peers,
+                                                       int channel, uint32_t epoch, uint32_t* status, uint64_t timeout_ns,
+                                                       int wait) {
+  __shared__ float acc[GB_TILE];
+  if (wait) wait_all_ranks(peers, channel, epoch, status, timeout_ns);
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    for (int i = threadIdx.x; i < GB_TILE; i += GB_THREADS) acc[i] = 0.f;
+    __syncthreads();
+    for (int r = 0; r < in.n; ++r) {
+      const int2 h = in.hdr[r][tile];
+      const float* v = in.vals[r] + h.x;
+      const int32_t* ix = in.idx[r] + h.x;
+      for (int i = threadIdx.x; i < h.y; i += GB_THREADS) {
+        const int li = ix[i] - local0;
+        if ((unsigned)li < (unsigned)GB_TILE) acc[li] += v[i];
+      }
+      __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      float4 v = make_float4(acc[e0], acc[e0 + 1], acc[e0 + 2], acc[e0 + 3]);
+      if (divisor != 1.f) {
+        v.x = __fdiv_rn(v.x, divisor); v.y = __fdiv_rn(v.y, divisor);
+        v.z = __fdiv_rn(v.z, divisor); v.w = __fdiv_rn(v.w, divisor);
+      }
+      store4(out + base, e0, len, v);
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------- RandomK
+__device__ __forceinline__ int find_segment(const int64_t* kbase, int nseg, int64_t p) {
+  int lo = 0, hi = nseg;                       // largest s with kbase[s] <= p
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (kbase[mid] <= p) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__device__ __forceinline__ int64_t randomk_index(const SegTable& t, int seg, int64_t j, uint32_t seed, uint32_t step) {
+  const Philox4 k = philox4x32(0u, step, GB_STREAM_PERMUTE, 0u, seed, t.seg_hash[seg]);
+  const uint32_t keys[4] = {k.x, k.y, k.z, k.w};
+  const uint64_t n = (uint64_t)t.seg_numel[seg];
+  return (int64_t)feistel_permute((uint64_t)j, n, feistel_half_bits(n), keys);
+}
+
+template <bool WRITE>
+__global__ void __launch_bounds__(GB_THREADS) k1_axpby(SegTable t, const float* __restrict__ grad, float* work, float beta,
+                                                       float gamma) {
+  const int64_t n4 = t.padded / 4;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 g = reinterpret_cast<const float4*>(grad)[i];
+    float4 r = reinterpret_cast<float4*>(work)[i];
+    r.x = compensate1(beta, r.x, gamma, g.x); r.y = compensate1(beta, r.y, gamma, g.y);
+    r.z = compensate1(beta, r.z, gamma, g.z); r.w = compensate1(beta, r.w, gamma, g.w);
+    reinterpret_cast<float4*>(work)[i] = r;
+  }
+}
+
+template <bool ZERO>
+__global__ void __launch_bounds__(GB_THREADS) k1_randomk_gather(SegTable t, float* work, int64_t ktotal, uint32_t seed,
+                                                               uint32_t step, SparseOut out, uint32_t* done, PeerPtrs peers,
+                                                               int channel, uint32_t epoch) {
+  for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < ktotal; p += (int64_t)gridDim.x * blockDim.x) {
+    const int seg = find_segment(t.seg_kbase, t.nseg, p);
+    const int64_t idx = randomk_index(t, seg, p - t.seg_kbase[seg], seed, step);
+    float* src = work + t.seg_off[seg] + idx;
+    const float v = *src;
+    for (int r = 0; r < out.n; ++r) out.vals[r][p] = v;
+    if (ZERO) *src = 0.f;
+  }
+  release_flags_last_block(done, peers, channel, epoch);
+}
+
+__global__ void __launch_bounds__(GB_THREADS) k1_randomk_scatter(SegTable t, int64_t ktotal, uint32_t seed, uint32_t step,
+                                                                SparseIn in, float* out, float divisor, PeerPtrs peers,
+                                                                int channel, uint32_t epoch, uint32_t* status,
+                                                                uint64_t timeout_ns) {
+  wait_all_ranks(peers, channel, epoch, status, timeout_ns);
+  for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < ktotal; p += (int64_t)gridDim.x * blockDim.x) {
+    const int seg = find_segment(t.seg_kbase, t.nseg, p);
+    const int64_t idx = randomk_index(t, seg, p - t.seg_kbase[seg], seed, step);
+    float s = 0.f;
+    for (int r = 0; r < in.n; ++r) s += in.vals[r][p];
+    out[t.seg_off[seg] + idx] = divisor != 1.f ? __fdiv_rn(s, divisor) : s;
+  }
+}
+
+// ---------------------------------------------------------------- host side
+static int grid_for(int ntiles) { return ntiles < 148 * 8 ? ntiles : 148 * 8; }
+
+static void slot_views(gb_plan* p, int parity, bool remote_side, SparseOut* o, SparseIn* in) {
+  // remote_side: pointers into every peer's arena at *my* slot (for sending);
+  // otherwise pointers into my arena at every source rank's slot (for receiving).
+  gb_comm* c = p->comm;
+  const size_t per = ((size_t)p->ktotal * 4 + 255) & ~size_t(255);
+  for (int r = 0; r < c->world; ++r) {
+    char* s = remote_side ? gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, parity, c->rank)
+                          : gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, parity, r);
+    if (o) { o->hdr[r] = (int2*)s; o->vals[r] = (float*)(s + p->hdr_bytes); o->idx[r] = (int32_t*)(s + p->hdr_bytes + per); }
+    if (in) { in->hdr[r] = (const int2*)s; in->vals[r] = (const float*)(s + p->hdr_bytes); in->idx[r] = (const int32_t*)(s + p->hdr_bytes + per); }
+  }
+  if (o) o->n = c->world;
+  if (in) in->n = c->world;
+}
+
+#define LAUNCHED(p) do { (p)->launches++; GB_CUDA(cudaGetLastError()); } while (0)
+
+static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st);
+
+int k1_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
+  if (p->prm.codec == GB_CODEC_DGC) return k1_dgc_send(p, d_grad, st);
+  gb_comm* c = p->comm;
+  const bool mem = p->prm.memory == GB_MEM_RESIDUAL;
+  // first call: the memory is empty, compensate() returns the gradient unchanged
+  const float beta = p->step == 0 ? 0.f : p->prm.beta;
+  const float gamma = p->step == 0 ? 1.f : p->prm.gamma;
+  float* work = mem ? p->d_state0 : const_cast<float*>(d_grad);
+  const uint32_t epoch = ++p->epoch;
+  SparseOut out;
+  slot_views(p, epoch & 1, true, &out, nullptr);
+  const PeerPtrs peers = gb_comm_peers(c);
+  const int grid = grid_for(p->ntiles);
+
+  if (p->prm.codec == GB_CODEC_RANDOMK) {
+    if (mem) { k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma); LAUNCHED(p); }
+    const int g2 = (int)std::min<int64_t>((p->ktotal + GB_THREADS - 1) / GB_THREADS, 148 * 8);
+    if (mem) k1_randomk_gather<true><<<g2, GB_THREADS, 0, st>>>(p->tab, work, p->ktotal, p->prm.seed, p->step, out, p->d_done, peers, p->channel, epoch);
+    else k1_randomk_gather<false><<<g2, GB_THREADS, 0, st>>>(p->tab, work, p->ktotal, p->prm.seed, p->step, out, p->d_done, peers, p->channel, epoch);
+    LAUNCHED(p);
+    return 0;
+  }
+
+  const bool fixed = p->prm.codec == GB_CODEC_THRESHOLD;
+  uint32_t thr_bits = 0u;
+  if (fixed) { const float th = p->prm.threshold < 0.f ? 0.f : p->prm.threshold; memcpy(&thr_bits, &th, 4); }
+  const int hgrid = std::min(p->ntiles, 148 * 4);
+  if (fixed) {
+    if (mem) { k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma); LAUNCHED(p); }
+  } else {
+    if (mem) k1_hist<0, true><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel);
+    else k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel);
+    LAUNCHED(p);
+    k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 0); LAUNCHED(p);
+    k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel); LAUNCHED(p);
+    k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 1); LAUNCHED(p);
+    k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel); LAUNCHED(p);
+    k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 2); LAUNCHED(p);
+  }
+  k1_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel, thr_bits, fixed, 0, p->d_tilecnt); LAUNCHED(p);
+  if (fixed) k1_scan<false><<<1, GB_THREADS, 0, st>>>(p->tab, p->d_sel, p->d_tilecnt);
+  else k1_scan<true><<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_sel, p->d_tilecnt);
+  LAUNCHED(p);
+  if (mem) k1_emit<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, fixed, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+  else k1_emit<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, fixed, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+  LAUNCHED(p);
+  return 0;
+}
+
+int k1_recv(gb_plan* p, float* d_out, cudaStream_t st) {
+  gb_comm* c = p->comm;
+  const uint32_t epoch = p->epoch;
+  SparseIn in;
+  slot_views(p, epoch & 1, false, nullptr, &in);
+  const PeerPtrs peers = gb_comm_peers(c);
+  const float divisor = p->prm.average ? (float)c->world : 1.f;
+  if (p->prm.codec == GB_CODEC_RANDOMK) {
+    GB_CUDA(cudaMemsetAsync(d_out, 0, (size_t)p->padded * 4, st));
+    const int g2 = (int)std::min<int64_t>((p->ktotal + GB_THREADS - 1) / GB_THREADS, 148 * 8);
+    k1_randomk_scatter<<<g2, GB_THREADS, 0, st>>>(p->tab, p->ktotal, p->prm.seed, p->step - 1, in, d_out, divisor, peers, p->channel, epoch, c->status_dev, c->timeout_ns);
+    LAUNCHED(p);
+    return 0;
+  }
+  k1_merge<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, epoch, c->status_dev, c->timeout_ns, 1);
+  LAUNCHED(p);
+  return 0;
+}
+
+
+// ---------------------------------------------------------------- DGC (+ DgcMemory)
+// Reference: compressor/dgc.py:12-50 and memory/dgc.py:15-39.  The reference needs up to 12
+// host round trips per tensor (.item()-style compares inside the refinement loop); here the
+// sampled threshold and the <=10 multiplicative refinements stay on the device.
+// sel[seg] = { threshold bits, 0, done flag, selected count }.
+
+__global__ void __launch_bounds__(GB_THREADS) k1_dgc_accumulate(SegTable t, const float* __restrict__ grad, float* v, float* u,
+                                                               float momentum) {
+  const int64_t n4 = t.padded / 4;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 g = reinterpret_cast<const float4*>(grad)[i];
+    float4 uu = reinterpret_cast<float4*>(u)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+    uu.x = __fadd_rn(__fmul_rn(momentum, uu.x), g.x); uu.y = __fadd_rn(__fmul_rn(momentum, uu.y), g.y);
+    uu.z = __fadd_rn(__fmul_rn(momentum, uu.z), g.z); uu.w = __fadd_rn(__fmul_rn(momentum, uu.w), g.w);
+    vv.x = __fadd_rn(vv.x, uu.x); vv.y = __fadd_rn(vv.y, uu.y); vv.z = __fadd_rn(vv.z, uu.z); vv.w = __fadd_rn(vv.w, uu.w);
+    reinterpret_cast<float4*>(u)[i] = uu;
+    reinterpret_cast<float4*>(v)[i] = vv;
+  }
+}
+
+// One CTA per segment: k-th largest magnitude among max(1, int(0.01 n)) positions sampled
+// with replacement (Philox stream 1), by three histogram rounds over the sample.
+__global__ void __launch_bounds__(GB_THREADS) k1_dgc_sample(SegTable t, const float* __restrict__ v, double ratio, uint32_t seed,
+                                                           uint32_t step, uint32_t* sel) {
+  __shared__ uint32_t hist[2048];
+  __shared__ uint32_t s_prefix, s_krem;
+  const int seg = blockIdx.x;
+  const int n = t.seg_numel[seg];
+  const int ns = max(1, (int)((double)n * 0.01));
+  int k = max(1, (int)((double)n * ratio * 0.01));
+  k = min(k, ns);
+  const float* x = v + t.seg_off[seg];
+  const uint32_t hash = t.seg_hash[seg];
+  if (threadIdx.x == 0) { s_prefix = 0; s_krem = (uint32_t)k; }
+  for (int round = 0; round < 3; ++round) {
+    const int nb = round == 0 ? 2048 : 1024;
+    for (int b = threadIdx.x; b < nb; b += blockDim.x) hist[b] = 0;
+    __syncthreads();
+    const uint32_t prefix = s_prefix;
+    for (int i4 = threadIdx.x; i4 * 4 < ns; i4 += blockDim.x) {
+      const Philox4 r = philox4x32((uint32_t)i4, step, GB_STREAM_SAMPLE, 0u, seed, hash);
+      const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+      for (int q = 0; q < 4 && i4 * 4 + q < ns; ++q) {
+        int pos = (int)__fmul_rn(u32_to_unit(rr[q]), (float)n);
+        pos = min(pos, n - 1);
+        const uint32_t b = absbits(x[pos]);
+        if (round == 0) atomicAdd(&hist[b >> 20], 1u);
+        else if (round == 1) { if ((b >> 20) == prefix) atomicAdd(&hist[(b >> 10) & 1023u], 1u); }
+        else { if ((b >> 10) == prefix) atomicAdd(&hist[b & 1023u], 1u); }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t running = 0, krem = s_krem;
+      for (int b = nb - 1; b >= 0; --b) {
+        const uint32_t c = hist[b];
+        if (running + c >= krem) {
+          s_prefix = round == 0 ? (uint32_t)b : ((prefix << 10) | (uint32_t)b);
+          s_krem = krem - running;
+          break;
+        }
+        running += c;
+      }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { sel[seg * 4] = s_prefix; sel[seg * 4 + 1] = 0; sel[seg * 4 + 2] = 0; sel[seg * 4 + 3] = 0; }
+}
+
+__global__ void __launch_bounds__(GB_THREADS) k1_dgc_count(SegTable t, const float* __restrict__ v, uint32_t* sel) {
+  __shared__ int sh[GB_THREADS / 32];
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    if (sel[seg * 4 + 2]) continue;                  // this segment's threshold is final
+    const uint32_t thr = sel[seg * 4];
+    int c = 0;
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      const float4 x = load4(v + base, e0, len);
+      const float xx[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) c += (e0 + q < len) && absbits(xx[q]) >= thr;
+    }
+    c = block_sum_i(c, sh);
+    if (threadIdx.x == 0 && c) atomicAdd(&sel[seg * 4 + 3], (uint32_t)c);
+  }
+}
+
+__global__ void k1_dgc_adjust(SegTable t, double ratio, uint32_t* sel) {
+  for (int seg = blockIdx.x * blockDim.x + threadIdx.x; seg < t.nseg; seg += gridDim.x * blockDim.x) {
+    if (sel[seg * 4 + 2]) continue;
+    const double n = (double)t.seg_numel[seg];
+    const double selected = (double)sel[seg * 4 + 3];
+    float thr = __uint_as_float(sel[seg * 4]);
+    if (selected > 1.3 * n * ratio) thr = __fmul_rn(1.3f, thr);
+    else if (selected < 0.7 * n * ratio) thr = __fmul_rn(0.7f, thr);
+    else sel[seg * 4 + 2] = 1;
+    sel[seg * 4] = __float_as_uint(thr);
+    sel[seg * 4 + 3] = 0;
+  }
+}
+
+static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
+  gb_comm* c = p->comm;
+  GB_CHECK(p->prm.memory == GB_MEM_DGC || p->prm.memory == GB_MEM_NONE || p->prm.memory == GB_MEM_RESIDUAL,
+           "unsupported memory for DGC");
+  const uint32_t epoch = ++p->epoch;
+  SparseOut out;
+  slot_views(p, epoch & 1, true, &out, nullptr);
+  const PeerPtrs peers = gb_comm_peers(c);
+  const int grid = grid_for(p->ntiles);
+  float* work;
+  float* work2 = nullptr;
+  if (p->prm.memory == GB_MEM_DGC) {
+    k1_dgc_accumulate<<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, p->d_state1, p->prm.momentum); LAUNCHED(p);
+    work = p->d_state0;
+    work2 = p->d_state1;
+  } else if (p->prm.memory == GB_MEM_RESIDUAL) {
+    k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, p->step == 0 ? 0.f : p->prm.beta,
+                                                  p->step == 0 ? 1.f : p->prm.gamma); LAUNCHED(p);
+    work = p->d_state0;
+  } else {
+    work = const_cast<float*>(d_grad);
+  }
+  k1_dgc_sample<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, work, p->prm.ratio, p->prm.seed, p->step, p->d_sel); LAUNCHED(p);
+  for (int it = 0; it < 10; ++it) {
+    k1_dgc_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel); LAUNCHED(p);
+    k1_dgc_adjust<<<(p->nseg + 127) / 128, 128, 0, st>>>(p->tab, p->prm.ratio, p->d_sel); LAUNCHED(p);
+  }
+  k1_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel, 0u, 0, 1, p->d_tilecnt); LAUNCHED(p);
+  k1_scan<false><<<1, GB_THREADS, 0, st>>>(p->tab, p->d_sel, p->d_tilecnt); LAUNCHED(p);
+  if (p->prm.memory != GB_MEM_NONE)
+    k1_emit<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 1, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+  else
+    k1_emit<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 1, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+  LAUNCHED(p);
+  return 0;
+}
+
+// ---------------------------------------------------------------- stand-alone single tensor
+// Scratch layout (all 256-byte aligned): tables | hist[2048] | sel[4] | tilecnt[2*ntiles+2] | hdr[ntiles+1]
+struct SingleLayout {
+  size_t off_tab, off_hist, off_sel, off_cnt, off_hdr, total;
+  int ntiles;
+};
+static SingleLayout single_layout(int64_t n) {
+  SingleLayout L;
+  L.ntiles = (int)((n + GB_TILE - 1) / GB_TILE);
+  size_t cur = 0;
+  auto add = [&](size_t b) { size_t o = cur; cur += (b + 255) & ~size_t(255); return o; };
+  L.off_tab = add(256 + (size_t)L.ntiles * 4);
+  L.off_hist = add(2048 * 4);
+  L.off_sel = add(16);
+  L.off_cnt = add(((size_t)L.ntiles * 2 + 2) * 4);
+  L.off_hdr = add(((size_t)L.ntiles + 1) * 8);
+  L.total = cur;
+  return L;
+}
+
+__global__ void k1_single_setup(char* tab, int64_t n, int64_t k, int ntiles, uint32_t* hist) {
+  int64_t* off = (int64_t*)tab;             // [0..1] seg_off, [2..3] kbase
+  int32_t* i32 = (int32_t*)(tab + 64);      // numel, k, hash, tile0[0..1]
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    off[0] = 0; off[1] = (n + GB_ALIGN - 1) / GB_ALIGN * GB_ALIGN; off[2] = 0; off[3] = k;
+    i32[0] = (int32_t)n; i32[1] = (int32_t)k; i32[2] = 0; i32[3] = 0; i32[4] = ntiles;
+  }
+  int32_t* tile_seg = (int32_t*)(tab + 256);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ntiles; i += gridDim.x * blockDim.x) tile_seg[i] = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2048; i += gridDim.x * blockDim.x) hist[i] = 0;
+}
+
+static SegTable single_table(char* tab, int64_t n, int ntiles) {
+  SegTable t;
+  t.seg_off = (const int64_t*)tab;
+  t.seg_kbase = (const int64_t*)tab + 2;
+  t.seg_numel = (const int32_t*)(tab + 64);
+  t.seg_k = (const int32_t*)(tab + 64) + 1;
+  t.seg_hash = (const uint32_t*)(tab + 64) + 2;
+  t.seg_tile0 = (const int32_t*)(tab + 64) + 3;
+  t.tile_seg = (const int32_t*)(tab + 256);
+  t.nseg = 1;
+  t.ntiles = ntiles;
+  t.padded = (n + GB_ALIGN - 1) / GB_ALIGN * GB_ALIGN;
+  return t;
+}
+
+extern "C" size_t gb_topk_scratch_bytes(int64_t n) { return single_layout(n).total; }
+
+// shared by gb_topk_compress and the allocation-free variant (k1_static.cu)
+int k1_topk_single(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_t* d_idx, char* scratch, cudaStream_t st) {
+  GB_CHECK(n >= 1 && n < (int64_t(1) << 31), "n = %lld out of range", (long long)n);
+  GB_CHECK(k >= 1 && k <= n, "k = %lld out of range for n = %lld", (long long)k, (long long)n);
+  GB_CHECK(((uintptr_t)d_x & 15) == 0, "input must be 16-byte aligned");
+  const SingleLayout L = single_layout(n);
+  char* tab = scratch + L.off_tab;
+  uint32_t* hist = (uint32_t*)(scratch + L.off_hist);
+  uint32_t* sel = (uint32_t*)(scratch + L.off_sel);
+  int32_t* cnt = (int32_t*)(scratch + L.off_cnt);
+  k1_single_setup<<<8, GB_THREADS, 0, st>>>(tab, n, k, L.ntiles, hist);
+  GB_CUDA(cudaGetLastError());
+  const SegTable t = single_table(tab, n, L.ntiles);
+  float* work = const_cast<float*>(d_x);
+  const int hgrid = std::min(L.ntiles, 148 * 4), grid = grid_for(L.ntiles);
+  k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
+  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 0);
+  k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
+  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 1);
+  k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
+  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 2);
+  k1_count<<<grid, GB_THREADS, 0, st>>>(t, work, sel, 0u, 0, 0, cnt);
+  k1_scan<true><<<1, GB_THREADS, 0, st>>>(t, sel, cnt);
+  SparseOut out;
+  out.n = 1;
+  out.vals[0] = d_vals;
+  out.idx[0] = d_idx;
+  out.hdr[0] = (int2*)(scratch + L.off_hdr);
+  PeerPtrs none;
+  memset(&none, 0, sizeof(none));
+  k1_emit<false><<<grid, GB_THREADS, 0, st>>>(t, work, nullptr, sel, 0u, 0, 0, cnt, out, k, (uint32_t*)(scratch + L.off_sel) + 3, nullptr, none, 0, 0, 0);
+  GB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int gb_topk_compress(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_t* d_idx, void* d_scratch,
+                                size_t scratch_bytes, void* stream) {
+  GB_CHECK(d_scratch && scratch_bytes >= gb_topk_scratch_bytes(n), "scratch too small: %zu < %zu", scratch_bytes,
+           gb_topk_scratch_bytes(n));
+  GB_CHECK(((uintptr_t)d_scratch & 255) == 0, "scratch must be 256-byte aligned");
+  return k1_topk_single(d_x, n, k, d_vals, d_idx, (char*)d_scratch, (cudaStream_t)stream);
+}
+
+__global__ void __launch_bounds__(GB_THREADS) k1_scatter_rank(const float* __restrict__ v, const int32_t* __restrict__ ix,
+                                                             int64_t count, float scale, float* out) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x)
+    out[ix[i]] += v[i] * scale;
+}
+
+extern "C" int gb_sparse_decompress(const float* const* d_vals, const int32_t* const* d_idx, const int64_t* counts, int nranks,
+                                    int64_t n, float scale, float* d_out, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  GB_CUDA(cudaMemsetAsync(d_out, 0, (size_t)n * 4, st));
+  for (int r = 0; r < nranks; ++r) {           // one launch per rank keeps the summation order fixed
+    if (counts[r] == 0) continue;
+    const int g = (int)std::min<int64_t>((counts[r] + GB_THREADS - 1) / GB_THREADS, 148 * 8);
+    k1_scatter_rank<<<g, GB_THREADS, 0, st>>>(d_vals[r], d_idx[r], counts[r], scale, d_out);
+  }
+  GB_CUDA(cudaGetLastError());
+  return 0;
+}

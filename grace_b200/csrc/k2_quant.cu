@@ -1,0 +1,435 @@
+// K2 -- quantiser family: None, FP16, QSGD, TernGrad, Natural, 8-bit, SignSGD, Signum,
+// EFSignSGD, OneBit.
+//
+// Per bucket instead of per tensor, replaces the reference op chains of
+//   compressor/{qsgd.py:12-38, terngrad.py:8-32, natural.py:13-40, signsgd.py:11-30,
+//   signum.py:13-37, efsignsgd.py:12-33}, torch/compressor/onebit.py:8-32,
+//   tensorflow/compressor/u8bit.py:10-110, memory/{residual.py,efsignsgd.py} and
+//   communicator/allgather.py:8-45
+// by (SURVEY §2.9-B quantiser rows):
+//   send:  k2_stats     one pass, per-tile partial reductions of the compensated gradient
+//          k2_finalize  per-segment scalars (norm / scalar / means), summed in a fixed order,
+//                       stored into every peer's slot header
+//          k2_encode    Philox + quantise + pack BITS-per-element words in registers + P2P
+//                       stores into every peer + residual / momentum update; last CTA
+//                       releases the flags
+//   recv:  k2_decode    acquire W flags; unpack the W ranks' codes, decode with the sender's
+//                       scalars, add in rank order (majority vote for sign codecs), write once
+// Wire formats are true bit-packs (1 bit sign codecs, 2-bit TernGrad, 4/8/16-bit QSGD) instead
+// of the reference's one byte per element.
+#include "kernels.cuh"
+#include <cuda_fp16.h>
+
+__constant__ float c_u8_table[128] = {
+    1.5000001e-06f, 2.75e-06f, 7.2499997e-06f, 1.8750001e-05f, 3.625e-05f, 5.8749996e-05f, 8.6249995e-05f, 1.4375e-04f,
+    2.3125e-04f, 3.1875001e-04f, 4.0625001e-04f, 5.1874999e-04f, 6.5624999e-04f, 7.9374999e-04f, 9.3124999e-04f,
+    1.21875e-03f, 1.65625e-03f, 2.0937501e-03f, 2.53125e-03f, 2.96875e-03f, 3.4062499e-03f, 3.8437501e-03f,
+    4.2812498e-03f, 4.84375e-03f, 5.53125e-03f, 6.21875e-03f, 6.90625e-03f, 7.59375e-03f, 8.2812496e-03f, 8.96875e-03f,
+    9.6562495e-03f, 1.109375e-02f, 1.328125e-02f, 1.546875e-02f, 1.765625e-02f, 1.984375e-02f, 2.2031249e-02f,
+    2.4218749e-02f, 2.6406251e-02f, 2.8593751e-02f, 3.078125e-02f, 3.2968748e-02f, 3.515625e-02f, 3.7343752e-02f,
+    3.953125e-02f, 4.1718751e-02f, 4.3906249e-02f, 4.671875e-02f, 5.0156251e-02f, 5.3593751e-02f, 5.7031251e-02f,
+    6.0468748e-02f, 6.3906237e-02f, 6.7343749e-02f, 7.0781253e-02f, 7.4218743e-02f, 7.7656247e-02f, 8.1093743e-02f,
+    8.453124e-02f, 8.7968737e-02f, 9.1406241e-02f, 9.4843738e-02f, 9.8281242e-02f, 1.0546875e-01f, 1.1640625e-01f,
+    1.2734374e-01f, 1.3828126e-01f, 1.4921875e-01f, 1.6015625e-01f, 1.7109375e-01f, 1.8203124e-01f, 1.9296876e-01f,
+    2.0390625e-01f, 2.1484375e-01f, 2.2578125e-01f, 2.3671874e-01f, 2.4765626e-01f, 2.5859374e-01f, 2.6953125e-01f,
+    2.8046876e-01f, 2.9140624e-01f, 3.0234376e-01f, 3.1328124e-01f, 3.2421875e-01f, 3.3515626e-01f, 3.4609374e-01f,
+    3.5703126e-01f, 3.6796874e-01f, 3.7890625e-01f, 3.8984376e-01f, 4.0078124e-01f, 4.1171876e-01f, 4.2265624e-01f,
+    4.3359375e-01f, 4.4453126e-01f, 4.5859376e-01f, 4.7578123e-01f, 4.9296874e-01f, 5.1015621e-01f, 5.2734375e-01f,
+    5.4453123e-01f, 5.617187e-01f, 5.7890624e-01f, 5.9609371e-01f, 6.1328125e-01f, 6.3046873e-01f, 6.476562e-01f,
+    6.6484374e-01f, 6.8203121e-01f, 6.9921869e-01f, 7.1640623e-01f, 7.335937e-01f, 7.5078118e-01f, 7.6796871e-01f,
+    7.8515619e-01f, 8.0234367e-01f, 8.195312e-01f, 8.3671868e-01f, 8.5390615e-01f, 8.7109369e-01f, 8.8828117e-01f,
+    9.0546864e-01f, 9.2265618e-01f, 9.3984365e-01f, 9.5703113e-01f, 9.7421867e-01f, 9.9140614e-01f, 9.9570298e-01f};
+
+struct QuantArgs {
+  int codec;
+  int has_mem;        // residual buffer present
+  float beta, gamma;  // compensate
+  float mom;          // signum momentum (0 on the first call)
+  int quantum;        // qsgd levels
+  uint32_t seed, step;
+};
+
+struct WireOut { char* slot[GB_MAX_WORLD]; int n; };   // my slot inside every peer
+struct WireIn { const char* slot[GB_MAX_WORLD]; int n; };  // every rank's slot inside my arena
+
+__device__ __forceinline__ float comp1(const QuantArgs& a, float r, float g) {
+  return a.has_mem ? __fadd_rn(__fmul_rn(a.beta, r), __fmul_rn(a.gamma, g)) : g;
+}
+
+// ---------------------------------------------------------------- pass 1: per-tile partials
+// tilestats[tile][8] = { sum x, sum x^2, max|x|, sum|x|, count(x<0), sum(x<0), -, - }
+__global__ void __launch_bounds__(GB_THREADS) k2_stats(SegTable t, const float* __restrict__ grad,
+                                                       const float* __restrict__ res, QuantArgs a, float* tilestats) {
+  __shared__ float sh[6][GB_THREADS / 32];
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    float s = 0.f, s2 = 0.f, mx = 0.f, sa = 0.f, cn = 0.f, sn = 0.f;
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      const float4 g = *reinterpret_cast<const float4*>(grad + base + e0);
+      float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (a.has_mem) r = *reinterpret_cast<const float4*>(res + base + e0);
+      const float x[4] = {comp1(a, r.x, g.x), comp1(a, r.y, g.y), comp1(a, r.z, g.z), comp1(a, r.w, g.w)};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (e0 + q < len) {
+          const float v = x[q];
+          s += v; s2 += v * v; mx = fmaxf(mx, fabsf(v)); sa += fabsf(v);
+          if (v < 0.f) { cn += 1.f; sn += v; }
+        }
+      }
+    }
+    s = warp_sum(s); s2 = warp_sum(s2); mx = warp_max(mx); sa = warp_sum(sa); cn = warp_sum(cn); sn = warp_sum(sn);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) { sh[0][wid] = s; sh[1][wid] = s2; sh[2][wid] = mx; sh[3][wid] = sa; sh[4][wid] = cn; sh[5][wid] = sn; }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+      float acc = 0.f;
+      for (int w = 0; w < GB_THREADS / 32; ++w) acc = threadIdx.x == 2 ? fmaxf(acc, sh[2][w]) : acc + sh[threadIdx.x][w];
+      tilestats[(size_t)tile * 8 + threadIdx.x] = acc;
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------- pass 1b: per-segment scalars
+// One warp per segment; tiles are combined in a fixed order in double precision, so the
+// scalars are reproducible run to run.  segstats[seg][4] is codec specific:
+//   QSGD {norm}  TERNGRAD {scalar}  EFSIGNSGD {mean|x|}  ONEBIT {mean_neg, mean_pos}  U8BIT {max|x|}
+__global__ void k2_finalize(SegTable t, const float* __restrict__ tilestats, int codec, float* segstats, WireOut out) {
+  const int seg = blockIdx.x;
+  const int lane = threadIdx.x;
+  const int first = t.seg_tile0[seg], last = t.seg_tile0[seg + 1];
+  double s = 0, s2 = 0, sa = 0, cn = 0, sn = 0;
+  float mx = 0.f;
+  for (int tile = first + lane; tile < last; tile += 32) {
+    const float* p = tilestats + (size_t)tile * 8;
+    s += p[0]; s2 += p[1]; mx = fmaxf(mx, p[2]); sa += p[3]; cn += p[4]; sn += p[5];
+  }
+  s = warp_sum_d(s); s2 = warp_sum_d(s2); sa = warp_sum_d(sa); cn = warp_sum_d(cn); sn = warp_sum_d(sn);
+  mx = warp_max(mx);
+  if (lane == 0) {
+    const double n = (double)t.seg_numel[seg];
+    float o[4] = {0.f, 0.f, 0.f, 0.f};
+    if (codec == GB_CODEC_QSGD) {
+      o[0] = (float)sqrt(s2);
+    } else if (codec == GB_CODEC_TERNGRAD) {
+      const double mean = s / n;
+      double var = s2 / n - mean * mean;
+      if (var < 0) var = 0;
+      o[0] = fminf(mx, (float)(2.5 * sqrt(var)));
+    } else if (codec == GB_CODEC_EFSIGNSGD) {
+      o[0] = (float)(sa / n);
+    } else if (codec == GB_CODEC_ONEBIT) {
+      const double sp = s - sn, np = n - cn;
+      o[0] = (float)(cn > 0 ? sn / cn : sn);
+      o[1] = (float)(np > 0 ? sp / np : sp);
+    } else if (codec == GB_CODEC_U8BIT) {
+      o[0] = mx;
+    }
+    const float4 v = make_float4(o[0], o[1], o[2], o[3]);
+    reinterpret_cast<float4*>(segstats)[seg] = v;
+    for (int r = 0; r < out.n; ++r) reinterpret_cast<float4*>(out.slot[r])[seg] = v;
+  }
+}
+
+// ---------------------------------------------------------------- codec arithmetic
+// encode: value (+ uniform draw) -> BITS-bit code; decode: code + sender's scalars -> float.
+template <int CODEC>
+__device__ __forceinline__ uint32_t encode1(float x, const float4& st, uint32_t rnd, int quantum) {
+  if (CODEC == GB_CODEC_NONE) return __float_as_uint(x);
+  if (CODEC == GB_CODEC_FP16) return (uint32_t)__half_as_ushort(__float2half_rn(x));
+  if (CODEC == GB_CODEC_SIGNSGD || CODEC == GB_CODEC_SIGNUM || CODEC == GB_CODEC_EFSIGNSGD) return x >= 0.f ? 1u : 0u;
+  if (CODEC == GB_CODEC_ONEBIT) return x < 0.f ? 1u : 0u;
+  if (CODEC == GB_CODEC_TERNGRAD) {
+    const float scalar = st.x;
+    const float mag = fminf(fabsf(x), scalar);
+    const bool keep = __fmul_rn(u32_to_unit(rnd), scalar) < mag;
+    if (!keep || x == 0.f) return 0u;
+    return x > 0.f ? 1u : 3u;                       // 2-bit two's complement of +1 / -1
+  }
+  if (CODEC == GB_CODEC_QSGD) {
+    const float norm = st.x;
+    const float scale = norm > 0.f ? __fdiv_rn((float)quantum, norm) : 0.f;
+    const float level = __fmul_rn(scale, fabsf(x));
+    const float low = floorf(level);
+    const float q = low + (u32_to_unit(rnd) < (level - low) ? 1.f : 0.f);
+    const int sq = x > 0.f ? (int)q : (x < 0.f ? -(int)q : 0);
+    return (uint32_t)sq;                            // caller masks to BITS
+  }
+  if (CODEC == GB_CODEC_NATURAL) {
+    const uint32_t b = __float_as_uint(x);
+    const uint32_t sign = b >> 31, mant = b & 0x7FFFFFu;
+    int e = (int)((b >> 23) & 0xFFu) + (mant > (rnd >> 9) ? 1 : 0);
+    e = min(max(e, 18), 145);
+    return (sign << 7) | (uint32_t)(e - 18);
+  }
+  if (CODEC == GB_CODEC_U8BIT) {
+    const float scaler = st.x;
+    const float inv = scaler > 0.f ? __fdiv_rn(1.0f, scaler) : 0.f;
+    const float y = __fmul_rn(fabsf(x), inv);
+    int lo = 0, hi = 128;                           // upper_bound(table, y)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (c_u8_table[mid] <= y) lo = mid + 1; else hi = mid;
+      }
+    }
+    int bin = min(max(lo - 1, 0), 127);
+    const int code = x > 0.f ? bin : (x < 0.f ? -bin : 0);
+    return (uint32_t)code;
+  }
+  return 0u;
+}
+
+template <int CODEC, int BITS>
+__device__ __forceinline__ float decode1(uint32_t code, const float4& st, int quantum) {
+  if (CODEC == GB_CODEC_NONE) return __uint_as_float(code);
+  if (CODEC == GB_CODEC_FP16) return __half2float(__ushort_as_half((unsigned short)code));
+  if (CODEC == GB_CODEC_SIGNSGD || CODEC == GB_CODEC_SIGNUM) return code ? 1.f : -1.f;
+  if (CODEC == GB_CODEC_EFSIGNSGD) return __fmul_rn(st.x, code ? 1.f : -1.f);
+  if (CODEC == GB_CODEC_ONEBIT) return code ? st.x : st.y;
+  const int sv = (int)(code << (32 - BITS)) >> (32 - BITS);     // sign-extend BITS
+  if (CODEC == GB_CODEC_TERNGRAD) return __fmul_rn((float)sv, st.x);
+  if (CODEC == GB_CODEC_QSGD) return __fmul_rn(__fdiv_rn(st.x, (float)quantum), (float)sv);
+  if (CODEC == GB_CODEC_NATURAL) {
+    const uint32_t e = code & 0x7Fu;
+    const float mag = __uint_as_float((e + 18u) << 23);
+    return e == 0u ? 0.f : ((code & 0x80u) ? -mag : mag);
+  }
+  if (CODEC == GB_CODEC_U8BIT) {
+    const int a = sv < 0 ? -sv : sv;
+    const float mag = __fmul_rn(c_u8_table[min(a, 127)], st.x);
+    return sv > 0 ? mag : (sv < 0 ? -mag : 0.f);
+  }
+  return 0.f;
+}
+
+template <int CODEC>
+struct NeedsRng { static constexpr bool value = CODEC == GB_CODEC_QSGD || CODEC == GB_CODEC_TERNGRAD || CODEC == GB_CODEC_NATURAL; };
+
+// ---------------------------------------------------------------- pass 2: encode + pack + push
+// Each thread owns 4 consecutive elements (one float4); their 4*BITS code bits are merged with
+// the neighbouring lanes' into full 32-bit words by a shuffle butterfly, so loads stay 16-byte
+// coalesced and each word is stored once per peer.
+template <int CODEC, int BITS>
+__global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float* __restrict__ grad, float* res, float* mom,
+                                                        const float* __restrict__ segstats, QuantArgs a, WireOut out,
+                                                        size_t hdr_bytes, uint32_t* done, PeerPtrs peers, int channel,
+                                                        uint32_t epoch) {
+  constexpr int SUB = 4 * BITS;                         // bits produced per thread
+  constexpr int LANES = SUB >= 32 ? 1 : 32 / SUB;       // lanes sharing one word
+  constexpr int WORDS = SUB >= 32 ? SUB / 32 : 1;       // words per thread
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    const float4 st = reinterpret_cast<const float4*>(segstats)[seg];
+    const uint32_t hash = t.seg_hash[seg];
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      // whole warps leave together (len is checked on the warp's first element), so the
+      // shuffles below always see full participation
+      if ((e0 & ~127) >= len) continue;
+      uint32_t code[4] = {0u, 0u, 0u, 0u};
+      if (e0 < len) {
+        const float4 g = *reinterpret_cast<const float4*>(grad + base + e0);
+        float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.has_mem) r = *reinterpret_cast<const float4*>(res + base + e0);
+        float x[4] = {comp1(a, r.x, g.x), comp1(a, r.y, g.y), comp1(a, r.z, g.z), comp1(a, r.w, g.w)};
+        float src[4] = {x[0], x[1], x[2], x[3]};
+        if (CODEC == GB_CODEC_SIGNUM) {
+          const float4 m = *reinterpret_cast<const float4*>(mom + base + e0);
+          const float mm[4] = {m.x, m.y, m.z, m.w};
+          const float om = 1.0f - a.mom;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) src[q] = a.mom == 0.f ? x[q] : __fadd_rn(__fmul_rn(om, x[q]), __fmul_rn(a.mom, mm[q]));
+          float4 w = make_float4(src[0], src[1], src[2], src[3]);
+          if (e0 + 4 > len) {                             // keep pad lanes at zero
+            if (e0 + 1 >= len) w.y = 0.f;
+            if (e0 + 2 >= len) w.z = 0.f;
+            if (e0 + 3 >= len) w.w = 0.f;
+          }
+          *reinterpret_cast<float4*>(mom + base + e0) = w;
+        }
+        Philox4 rnd = {0u, 0u, 0u, 0u};
+        if (NeedsRng<CODEC>::value) rnd = philox4x32((uint32_t)((local0 + e0) >> 2), a.step, GB_STREAM_UNIFORM, 0u, a.seed, hash);
+        const uint32_t rr[4] = {rnd.x, rnd.y, rnd.z, rnd.w};
+        float nres[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const bool live = e0 + q < len;
+          const uint32_t c = live ? (encode1<CODEC>(src[q], st, rr[q], a.quantum) & (0xFFFFFFFFu >> (32 - BITS))) : 0u;
+          code[q] = c;
+          nres[q] = live ? __fsub_rn(x[q], decode1<CODEC, BITS>(c, st, a.quantum)) : 0.f;
+        }
+        if (a.has_mem) *reinterpret_cast<float4*>(res + base + e0) = make_float4(nres[0], nres[1], nres[2], nres[3]);
+      }
+      const int64_t flat = base + e0;                   // flat element index of code[0]
+      if (WORDS > 1) {
+        // 16 or 32 bits per element: this thread owns WORDS whole words
+        uint32_t w[WORDS];
+        if (BITS == 32) { w[0] = code[0]; w[1 % WORDS] = code[1]; w[2 % WORDS] = code[2]; w[3 % WORDS] = code[3]; }
+        else { w[0] = code[0] | (code[1] << 16); w[1 % WORDS] = code[2] | (code[3] << 16); }
+        if (e0 < len) {
+          for (int r = 0; r < out.n; ++r) {
+            uint32_t* dst = reinterpret_cast<uint32_t*>(out.slot[r] + hdr_bytes) + flat * BITS / 32;
+            if (WORDS == 4) st_stream_u4(dst, make_uint4(w[0], w[1 % WORDS], w[2 % WORDS], w[3 % WORDS]));
+            else *reinterpret_cast<uint2*>(dst) = make_uint2(w[0], w[1 % WORDS]);
+          }
+        }
+      } else {
+        uint32_t sub = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) sub |= code[q] << (q * BITS);
+        const int lane = threadIdx.x & 31;
+        uint32_t word = sub << ((lane % LANES) * SUB);
+#pragma unroll
+        for (int o = 1; o < LANES; o <<= 1) word |= __shfl_xor_sync(0xffffffffu, word, o);
+        if ((lane % LANES) == 0 && e0 < len) {
+          for (int r = 0; r < out.n; ++r)
+            reinterpret_cast<uint32_t*>(out.slot[r] + hdr_bytes)[flat * BITS / 32] = word;
+        }
+      }
+    }
+  }
+  release_flags_last_block(done, peers, channel, epoch);
+}
+
+// ---------------------------------------------------------------- receive: unpack, decode, add
+// final: 0 -> sum / divisor;  1 -> majority vote (sum >= 0 -> +1 else -1);  2 -> sum / lr
+template <int CODEC, int BITS>
+__global__ void __launch_bounds__(GB_THREADS) k2_decode(SegTable t, WireIn in, size_t hdr_bytes, float* outp, int quantum,
+                                                        int final_mode, float divisor, PeerPtrs peers, int channel,
+                                                        uint32_t epoch, uint32_t* status, uint64_t timeout_ns) {
+  wait_all_ranks(peers, channel, epoch, status, timeout_ns);
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      const int64_t flat = base + e0;
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int r = 0; r < in.n; ++r) {
+        const float4 st = reinterpret_cast<const float4*>(in.slot[r])[seg];
+        const uint32_t* words = reinterpret_cast<const uint32_t*>(in.slot[r] + hdr_bytes);
+        uint32_t code[4];
+        if (BITS == 32) {
+          const uint4 w = *reinterpret_cast<const uint4*>(words + flat);
+          code[0] = w.x; code[1] = w.y; code[2] = w.z; code[3] = w.w;
+        } else if (BITS == 16) {
+          const uint2 w = *reinterpret_cast<const uint2*>(words + flat / 2);
+          code[0] = w.x & 0xFFFFu; code[1] = w.x >> 16; code[2] = w.y & 0xFFFFu; code[3] = w.y >> 16;
+        } else {
+          const uint32_t w = words[flat * BITS / 32];
+          const int sh = (int)((flat * BITS) & 31);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) code[q] = (w >> (sh + q * BITS)) & (0xFFFFFFFFu >> (32 - BITS));
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[q] += decode1<CODEC, BITS>(code[q], st, quantum);
+      }
+      float o[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (final_mode == 1) o[q] = acc[q] >= 0.f ? 1.f : -1.f;
+        else o[q] = divisor != 1.f ? __fdiv_rn(acc[q], divisor) : acc[q];
+        if (e0 + q >= len) o[q] = 0.f;
+      }
+      *reinterpret_cast<float4*>(outp + flat) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- host side
+#define LAUNCHED(p) do { (p)->launches++; GB_CUDA(cudaGetLastError()); } while (0)
+
+static int grid_for(int ntiles) { return ntiles < 148 * 8 ? ntiles : 148 * 8; }
+
+static bool needs_stats(int codec) {
+  return codec == GB_CODEC_QSGD || codec == GB_CODEC_TERNGRAD || codec == GB_CODEC_EFSIGNSGD || codec == GB_CODEC_ONEBIT ||
+         codec == GB_CODEC_U8BIT;
+}
+
+template <int CODEC, int BITS>
+static int launch_encode(gb_plan* p, const float* g, const QuantArgs& a, const WireOut& out, const PeerPtrs& peers,
+                         uint32_t epoch, cudaStream_t st) {
+  k2_encode<CODEC, BITS><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, g, p->d_state0, p->d_state1, p->d_segstats, a, out,
+                                                                    p->hdr_bytes, p->d_done, peers, p->channel, epoch);
+  LAUNCHED(p);
+  return 0;
+}
+
+template <int CODEC, int BITS>
+static int launch_decode(gb_plan* p, float* o, const WireIn& in, const PeerPtrs& peers, int mode, float divisor, cudaStream_t st) {
+  k2_decode<CODEC, BITS><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, p->hdr_bytes, o, p->prm.quantum_num, mode, divisor,
+                                                                    peers, p->channel, p->epoch, p->comm->status_dev,
+                                                                    p->comm->timeout_ns);
+  LAUNCHED(p);
+  return 0;
+}
+
+#define DISPATCH(FN, ...)                                                                         \
+  switch (p->prm.codec) {                                                                         \
+    case GB_CODEC_NONE: return FN<GB_CODEC_NONE, 32>(__VA_ARGS__);                                \
+    case GB_CODEC_FP16: return FN<GB_CODEC_FP16, 16>(__VA_ARGS__);                                \
+    case GB_CODEC_QSGD:                                                                           \
+      if (p->bits == 4) return FN<GB_CODEC_QSGD, 4>(__VA_ARGS__);                                 \
+      if (p->bits == 8) return FN<GB_CODEC_QSGD, 8>(__VA_ARGS__);                                 \
+      return FN<GB_CODEC_QSGD, 16>(__VA_ARGS__);                                                  \
+    case GB_CODEC_TERNGRAD: return FN<GB_CODEC_TERNGRAD, 2>(__VA_ARGS__);                         \
+    case GB_CODEC_NATURAL: return FN<GB_CODEC_NATURAL, 8>(__VA_ARGS__);                           \
+    case GB_CODEC_U8BIT: return FN<GB_CODEC_U8BIT, 8>(__VA_ARGS__);                               \
+    case GB_CODEC_SIGNSGD: return FN<GB_CODEC_SIGNSGD, 1>(__VA_ARGS__);                           \
+    case GB_CODEC_SIGNUM: return FN<GB_CODEC_SIGNUM, 1>(__VA_ARGS__);                             \
+    case GB_CODEC_EFSIGNSGD: return FN<GB_CODEC_EFSIGNSGD, 1>(__VA_ARGS__);                       \
+    case GB_CODEC_ONEBIT: return FN<GB_CODEC_ONEBIT, 1>(__VA_ARGS__);                             \
+    default: gb_set_error("codec %d is not a quantiser", p->prm.codec); return -1;                \
+  }
+
+int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
+  gb_comm* c = p->comm;
+  GB_CHECK(((uintptr_t)d_grad & 15) == 0, "gradient buffer must be 16-byte aligned");
+  QuantArgs a;
+  a.codec = p->prm.codec;
+  a.has_mem = p->prm.memory == GB_MEM_RESIDUAL;
+  a.beta = p->step == 0 ? 0.f : p->prm.beta;      // empty memory: compensate() is the identity
+  a.gamma = p->step == 0 ? 1.f : p->prm.gamma;
+  a.mom = p->step == 0 ? 0.f : p->prm.momentum;   // Signum: first call m = x
+  a.quantum = p->prm.quantum_num;
+  a.seed = p->prm.seed;
+  a.step = p->step;
+  const uint32_t epoch = ++p->epoch;
+  WireOut out;
+  out.n = c->world;
+  for (int r = 0; r < c->world; ++r) out.slot[r] = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, epoch & 1, c->rank);
+  const PeerPtrs peers = gb_comm_peers(c);
+  if (needs_stats(a.codec)) {
+    k2_stats<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_tilestats); LAUNCHED(p);
+    k2_finalize<<<p->nseg, 32, 0, st>>>(p->tab, p->d_tilestats, a.codec, p->d_segstats, out); LAUNCHED(p);
+  }
+  DISPATCH(launch_encode, p, d_grad, a, out, peers, epoch, st);
+}
+
+int k2_recv(gb_plan* p, float* d_out, cudaStream_t st) {
+  gb_comm* c = p->comm;
+  GB_CHECK(((uintptr_t)d_out & 15) == 0, "output buffer must be 16-byte aligned");
+  WireIn in;
+  in.n = c->world;
+  for (int r = 0; r < c->world; ++r) in.slot[r] = gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, p->epoch & 1, r);
+  const PeerPtrs peers = gb_comm_peers(c);
+  int mode = 0;
+  float divisor = p->prm.average ? (float)c->world : 1.f;
+  if (p->prm.codec == GB_CODEC_SIGNSGD || p->prm.codec == GB_CODEC_SIGNUM) mode = 1;
+  if (p->prm.codec == GB_CODEC_EFSIGNSGD) { mode = 2; divisor = p->prm.lr; }
+  DISPATCH(launch_decode, p, d_out, in, peers, mode, divisor, st);
+}

@@ -1,0 +1,35 @@
+// Launch entry points of the kernel families (one translation unit each).
+#pragma once
+#include "engine.cuh"
+
+bool gb_codec_is_sparse(int codec);
+
+// K1: sparsifiers -- compensate + select + ordered compaction + peer stores / ordered merge
+int k1_send(gb_plan* p, const float* d_grad, cudaStream_t st);
+int k1_recv(gb_plan* p, float* d_out, cudaStream_t st);
+// K2: quantisers -- stats + encode/pack + peer stores / unpack-and-sum (+ majority vote)
+int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st);
+int k2_recv(gb_plan* p, float* d_out, cudaStream_t st);
+
+// Last-block-done flag release shared by the send kernels: every CTA calls this after its
+// final peer store; the CTA that arrives last publishes `epoch` to all peers.
+__device__ __forceinline__ void release_flags_last_block(uint32_t* done, PeerPtrs peers, int channel, uint32_t epoch) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t ticket = atomicAdd(done, 1u);
+    if (ticket == gridDim.x - 1) {
+      __threadfence_system();
+      for (int r = 0; r < peers.world; ++r) st_release_sys(gb_flag(peers.base[r], channel, epoch & 1, peers.rank), epoch);
+      *done = 0;
+    }
+  }
+}
+
+// All threads of the CTA return once every rank's flag for `epoch` has arrived.
+__device__ __forceinline__ void wait_all_ranks(PeerPtrs peers, int channel, uint32_t epoch, uint32_t* status,
+                                               uint64_t timeout_ns) {
+  if (threadIdx.x < peers.world)
+    wait_flag(gb_flag(peers.base[peers.rank], channel, epoch & 1, threadIdx.x), epoch, status, timeout_ns);
+  __syncthreads();
+}

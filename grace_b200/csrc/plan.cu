@@ -1,0 +1,192 @@
+// Plans: geometry of one gradient bucket, its persistent error-feedback state, its wire slot.
+//
+// The reference keeps per-name python dicts of full-size tensors (grace_dl/dist/memory/
+// residual.py:6, memory/dgc.py:12-13, compressor/signum.py:11) and issues one collective per
+// payload tensor per parameter (SURVEY §2.8 "no bucketing").  A plan flattens a whole bucket:
+// state lives in two flat device buffers, and one send + one recv launch sequence serves every
+// tensor of the bucket through the segment/tile tables built here.
+#include "engine.cuh"
+#include "kernels.cuh"
+
+#include <algorithm>
+
+static int quant_bits(const gb_codec_params& p) {
+  switch (p.codec) {
+    case GB_CODEC_NONE: return 32;
+    case GB_CODEC_FP16: return 16;
+    case GB_CODEC_QSGD: return p.quantum_num <= 7 ? 4 : (p.quantum_num <= 127 ? 8 : 16);
+    case GB_CODEC_TERNGRAD: return 2;
+    case GB_CODEC_NATURAL:
+    case GB_CODEC_U8BIT: return 8;
+    case GB_CODEC_SIGNSGD:
+    case GB_CODEC_SIGNUM:
+    case GB_CODEC_EFSIGNSGD:
+    case GB_CODEC_ONEBIT: return 1;
+    default: return 0;
+  }
+}
+
+bool gb_codec_is_sparse(int codec) {
+  return codec == GB_CODEC_TOPK || codec == GB_CODEC_RANDOMK || codec == GB_CODEC_THRESHOLD || codec == GB_CODEC_DGC;
+}
+
+template <typename T>
+static T* carve(char*& cur, size_t count) {
+  T* p = (T*)cur;
+  cur += (count * sizeof(T) + 255) & ~size_t(255);
+  return p;
+}
+
+extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const uint32_t* name_hash,
+                              const gb_codec_params* params, gb_plan** out) {
+  GB_CHECK(nseg >= 1, "a plan needs at least one segment");
+  GB_CHECK(params->codec >= GB_CODEC_NONE && params->codec <= GB_CODEC_ONEBIT, "unknown codec %d", params->codec);
+  GB_CHECK(params->memory != GB_MEM_DGC || params->codec == GB_CODEC_DGC, "DGC memory needs the DGC codec");
+  gb_plan* p = new gb_plan();
+  p->comm = c;
+  p->prm = *params;
+  p->nseg = nseg;
+  p->epoch = 0;
+  p->step = 0;
+  p->launches = 0;
+  p->bits = quant_bits(*params);
+  const bool sparse = gb_codec_is_sparse(params->codec);
+
+  // ---- geometry (host)
+  p->h_off.resize(nseg + 1);
+  p->h_kbase.resize(nseg + 1);
+  p->h_numel.resize(nseg);
+  p->h_k.resize(nseg);
+  p->h_tile0.resize(nseg + 1);
+  std::vector<int32_t> tile_seg;
+  int64_t off = 0, kbase = 0;
+  for (int s = 0; s < nseg; ++s) {
+    GB_CHECK(numels[s] >= 1 && numels[s] < (int64_t(1) << 31), "segment %d has %lld elements (must be in [1, 2^31))", s,
+             (long long)numels[s]);
+    p->h_off[s] = off;
+    p->h_numel[s] = (int32_t)numels[s];
+    int64_t k = 0;
+    if (params->codec == GB_CODEC_TOPK || params->codec == GB_CODEC_RANDOMK)
+      k = std::max<int64_t>(1, (int64_t)((double)numels[s] * (double)params->ratio));
+    k = std::min<int64_t>(k, numels[s]);
+    p->h_k[s] = (int32_t)k;
+    p->h_kbase[s] = kbase;
+    kbase += k;
+    p->h_tile0[s] = (int32_t)tile_seg.size();
+    int nt = (int)((numels[s] + GB_TILE - 1) / GB_TILE);
+    for (int t = 0; t < nt; ++t) tile_seg.push_back(s);
+    off += (numels[s] + GB_ALIGN - 1) / GB_ALIGN * GB_ALIGN;
+  }
+  p->h_off[nseg] = off;
+  p->h_kbase[nseg] = kbase;
+  p->h_tile0[nseg] = (int32_t)tile_seg.size();
+  p->padded = off;
+  p->ntiles = (int)tile_seg.size();
+  if (params->codec == GB_CODEC_THRESHOLD || params->codec == GB_CODEC_DGC) {
+    float cap = params->capacity > 0.f ? params->capacity : 1.0f;
+    kbase = std::max<int64_t>(1, (int64_t)((double)cap * (double)off));
+  }
+  p->ktotal = kbase;
+
+  // ---- device tables, state and scratch in one allocation
+  size_t bytes = 0;
+  auto add = [&](size_t n) { bytes += (n + 255) & ~size_t(255); };
+  add((nseg + 1) * 8); add(nseg * 4); add(nseg * 4); add((nseg + 1) * 8); add(nseg * 4); add((nseg + 1) * 4);
+  add(p->ntiles * 4);
+  add((size_t)nseg * 2048 * 4); add((size_t)nseg * 4 * 4); add((size_t)p->ntiles * 2 * 4 + 8);
+  add((size_t)p->ntiles * 8 * 4); add((size_t)nseg * 4 * 4); add(64);
+  GB_CUDA(cudaMalloc(&p->d_tables, bytes));
+  GB_CUDA(cudaMemset(p->d_tables, 0, bytes));
+  char* cur = (char*)p->d_tables;
+  int64_t* d_off = carve<int64_t>(cur, nseg + 1);
+  int32_t* d_numel = carve<int32_t>(cur, nseg);
+  int32_t* d_k = carve<int32_t>(cur, nseg);
+  int64_t* d_kbase = carve<int64_t>(cur, nseg + 1);
+  uint32_t* d_hash = carve<uint32_t>(cur, nseg);
+  int32_t* d_tile0 = carve<int32_t>(cur, nseg + 1);
+  int32_t* d_tileseg = carve<int32_t>(cur, p->ntiles);
+  p->d_hist = carve<uint32_t>(cur, (size_t)nseg * 2048);
+  p->d_sel = carve<uint32_t>(cur, (size_t)nseg * 4);
+  p->d_tilecnt = carve<int32_t>(cur, (size_t)p->ntiles * 2 + 2);
+  p->d_tilestats = carve<float>(cur, (size_t)p->ntiles * 8);
+  p->d_segstats = carve<float>(cur, (size_t)nseg * 4);
+  p->d_done = carve<uint32_t>(cur, 16);
+  GB_CUDA(cudaMemcpy(d_off, p->h_off.data(), (nseg + 1) * 8, cudaMemcpyHostToDevice));
+  GB_CUDA(cudaMemcpy(d_numel, p->h_numel.data(), nseg * 4, cudaMemcpyHostToDevice));
+  GB_CUDA(cudaMemcpy(d_k, p->h_k.data(), nseg * 4, cudaMemcpyHostToDevice));
+  GB_CUDA(cudaMemcpy(d_kbase, p->h_kbase.data(), (nseg + 1) * 8, cudaMemcpyHostToDevice));
+  GB_CUDA(cudaMemcpy(d_hash, name_hash, nseg * 4, cudaMemcpyHostToDevice));
+  GB_CUDA(cudaMemcpy(d_tile0, p->h_tile0.data(), (nseg + 1) * 4, cudaMemcpyHostToDevice));
+  GB_CUDA(cudaMemcpy(d_tileseg, tile_seg.data(), p->ntiles * 4, cudaMemcpyHostToDevice));
+  p->tab = SegTable{d_off, d_numel, d_k, d_kbase, d_hash, d_tile0, d_tileseg, nseg, p->ntiles, p->padded};
+
+  p->d_state0 = p->d_state1 = nullptr;
+  const bool need0 = params->memory != GB_MEM_NONE;
+  const bool need1 = params->codec == GB_CODEC_SIGNUM || params->memory == GB_MEM_DGC;
+  if (need0) {
+    GB_CUDA(cudaMalloc((void**)&p->d_state0, p->padded * 4));
+    GB_CUDA(cudaMemset(p->d_state0, 0, p->padded * 4));
+  }
+  if (need1) {
+    GB_CUDA(cudaMalloc((void**)&p->d_state1, p->padded * 4));
+    GB_CUDA(cudaMemset(p->d_state1, 0, p->padded * 4));
+  }
+
+  // ---- wire slot
+  if (sparse) {
+    p->hdr_bytes = ((size_t)(p->ntiles + 1) * 2 * 4 + 255) & ~size_t(255);
+    size_t per = ((size_t)p->ktotal * 4 + 255) & ~size_t(255);
+    p->slot_bytes = p->hdr_bytes + (params->codec == GB_CODEC_RANDOMK ? per : 2 * per);
+  } else {
+    p->hdr_bytes = ((size_t)nseg * 4 * 4 + 255) & ~size_t(255);
+    p->slot_bytes = p->hdr_bytes + (((size_t)p->padded * p->bits / 8 + 255) & ~size_t(255));
+  }
+  if (gb_comm_alloc_channel(c, p->slot_bytes, &p->channel, &p->chan_off)) { gb_plan_destroy(p); return -1; }
+  p->slot_bytes = (p->slot_bytes + 255) & ~size_t(255);
+  GB_CUDA(cudaDeviceSynchronize());
+  *out = p;
+  return 0;
+}
+
+extern "C" int gb_plan_destroy(gb_plan* p) {
+  if (!p) return 0;
+  cudaDeviceSynchronize();
+  cudaFree(p->d_tables);
+  cudaFree(p->d_state0);
+  cudaFree(p->d_state1);
+  delete p;
+  return 0;
+}
+
+extern "C" int64_t gb_plan_padded_numel(gb_plan* p) { return p->padded; }
+
+extern "C" int gb_plan_offsets(gb_plan* p, int64_t* out) {
+  for (int s = 0; s < p->nseg; ++s) out[s] = p->h_off[s];
+  return 0;
+}
+
+extern "C" int64_t gb_plan_wire_bytes(gb_plan* p) { return (int64_t)p->slot_bytes; }
+
+extern "C" int gb_plan_state(gb_plan* p, int which, void** d_ptr, size_t* bytes) {
+  float* s = which == 0 ? p->d_state0 : p->d_state1;
+  *d_ptr = s;
+  *bytes = s ? (size_t)p->padded * 4 : 0;
+  return 0;
+}
+extern "C" int gb_plan_get_step(gb_plan* p, uint32_t* step) { *step = p->step; return 0; }
+extern "C" int gb_plan_set_step(gb_plan* p, uint32_t step) { p->step = step; return 0; }
+extern "C" int gb_plan_launches(gb_plan* p, int64_t* out) { *out = p->launches; return 0; }
+
+extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
+  if (rc) return rc;
+  p->step++;
+  return 0;
+}
+
+extern "C" int gb_plan_recv(gb_plan* p, float* d_out, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  GB_CHECK(p->epoch > 0, "gb_plan_recv before any gb_plan_send");
+  return gb_codec_is_sparse(p->prm.codec) ? k1_recv(p, d_out, st) : k2_recv(p, d_out, st);
+}

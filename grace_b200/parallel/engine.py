@@ -1,0 +1,184 @@
+"""Communicator / plan objects over the native library.
+
+``Engine`` is what Horovod's ``hvd.init()`` + C++ core is to the reference
+(``patch_files/horovod/torch/mpi_ops.py:42-55``): rank bootstrap, the peer-memory arena and
+the handle table.  The IPC handles travel once through ``torch.distributed``
+(``all_gather_object``); after that no collective library is involved in gradient exchange.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Sequence
+
+import torch
+from torch import distributed as dist
+
+from grace_b200.ops import native
+from grace_b200.ops.native import CodecParams, check
+from grace_b200.utils.philox import fnv1a
+
+
+def _stream_ptr(stream=None):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+class _RawCuda:
+    """Adapter exposing a raw device pointer through ``__cuda_array_interface__``."""
+
+    def __init__(self, ptr, count):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+
+
+class Engine:
+    """One rank's communicator.  ``Engine.create()`` joins the torch.distributed job (or runs
+    as a single rank); ``Engine.local(world)`` builds ``world`` virtual ranks on the current
+    GPU for protocol tests on one device."""
+
+    def __init__(self, handle, rank, world, group=None):
+        self._h = C.c_void_p(handle)
+        self.rank, self.world, self.group = rank, world, group
+        self.plans: List["Plan"] = []
+
+    # ------------------------------------------------------------------ construction
+    @staticmethod
+    def default_arena_bytes():
+        return int(os.environ.get("GRACE_B200_ARENA_MB", "1024")) << 20
+
+    @classmethod
+    def create(cls, arena_bytes=None, group=None):
+        L = native.lib()
+        if not torch.cuda.is_available():
+            raise native.NativeError("the fused engine needs a CUDA device")
+        check(L.gb_set_device(torch.cuda.current_device()))
+        live = dist.is_available() and dist.is_initialized()
+        rank = dist.get_rank(group) if live else 0
+        world = dist.get_world_size(group) if live else 1
+        h = C.c_void_p()
+        check(L.gb_comm_create(rank, world, arena_bytes or cls.default_arena_bytes(), C.byref(h)))
+        eng = cls(h.value, rank, world, group)
+        if world > 1:
+            buf = C.create_string_buffer(64)
+            check(L.gb_comm_ipc_handle(eng._h, buf))
+            gathered = [None] * world
+            dist.all_gather_object(gathered, bytes(buf.raw), group=group)
+            check(L.gb_comm_open_peers(eng._h, b"".join(gathered)))
+            dist.barrier(group=group)
+        return eng
+
+    @classmethod
+    def local(cls, world, arena_bytes=None):
+        L = native.lib()
+        check(L.gb_set_device(torch.cuda.current_device()))
+        arr = (C.c_void_p * world)()
+        check(L.gb_comm_create_local(world, arena_bytes or (256 << 20), arr))
+        return [cls(arr[r], r, world) for r in range(world)]
+
+    # ------------------------------------------------------------------ services
+    def status(self):
+        out = C.c_uint32()
+        check(native.lib().gb_comm_status(self._h, C.byref(out)))
+        return out.value
+
+    def check_status(self):
+        s = self.status()
+        if s:
+            native.lib().gb_comm_clear_status(self._h)
+            what = [n for b, n in ((1, "peer flag wait timed out (a rank is missing or hung)"),
+                                   (2, "variable-size payload exceeded the slot capacity")) if s & b]
+            raise native.NativeError("engine status 0x%x: %s" % (s, "; ".join(what)))
+
+    def set_timeout_ms(self, ms):
+        check(native.lib().gb_comm_set_timeout_ms(self._h, int(ms)))
+
+    def arena_free(self):
+        return native.lib().gb_comm_arena_free(self._h)
+
+    def barrier(self, stream=None):
+        check(native.lib().gb_comm_barrier(self._h, _stream_ptr(stream)))
+
+    def destroy(self):
+        for p in list(self.plans):
+            p.destroy()
+        if self._h:
+            native.lib().gb_comm_destroy(self._h)
+            self._h = None
+
+    def plan(self, numels: Sequence[int], names: Sequence[str], params: CodecParams) -> "Plan":
+        return Plan(self, numels, names, params)
+
+
+class Plan:
+    """One gradient bucket: geometry + error-feedback state + wire slot (``gb_plan``)."""
+
+    def __init__(self, engine: Engine, numels, names, params: CodecParams):
+        L = native.lib()
+        self.engine = engine
+        self.nseg = len(numels)
+        self.numels = [int(n) for n in numels]
+        self.names = list(names)
+        self.params = params
+        nm = (C.c_int64 * self.nseg)(*self.numels)
+        hs = (C.c_uint32 * self.nseg)(*[fnv1a(n) for n in names])
+        h = C.c_void_p()
+        check(L.gb_plan_create(engine._h, self.nseg, nm, hs, C.byref(params), C.byref(h)))
+        self._h = h
+        self.padded = L.gb_plan_padded_numel(h)
+        off = (C.c_int64 * self.nseg)()
+        check(L.gb_plan_offsets(h, off))
+        self.offsets = list(off)
+        self.wire_bytes = L.gb_plan_wire_bytes(h)
+        engine.plans.append(self)
+
+    def send(self, grad: torch.Tensor, stream=None):
+        assert grad.is_cuda and grad.dtype == torch.float32 and grad.numel() >= self.padded
+        check(native.lib().gb_plan_send(self._h, C.c_void_p(grad.data_ptr()), _stream_ptr(stream)))
+
+    def recv(self, out: torch.Tensor, stream=None):
+        assert out.is_cuda and out.dtype == torch.float32 and out.numel() >= self.padded
+        check(native.lib().gb_plan_recv(self._h, C.c_void_p(out.data_ptr()), _stream_ptr(stream)))
+
+    def launches(self):
+        out = C.c_int64()
+        check(native.lib().gb_plan_launches(self._h, C.byref(out)))
+        return out.value
+
+    # ---- state (checkpointing): copies, so a state_dict outlives the plan
+    def _state_view(self, which):
+        ptr, size = C.c_void_p(), C.c_size_t()
+        check(native.lib().gb_plan_state(self._h, which, C.byref(ptr), C.byref(size)))
+        return ptr.value, size.value
+
+    def state_tensor(self, which):
+        """Zero-copy float32 view of the plan-owned state buffer (None if the plan has none)."""
+        ptr, size = self._state_view(which)
+        if not ptr:
+            return None
+        return torch.as_tensor(_RawCuda(ptr, size // 4), device="cuda")
+
+    def get_state(self, which):
+        view = self.state_tensor(which)
+        return None if view is None else view.clone()
+
+    def set_state(self, which, tensor):
+        view = self.state_tensor(which)
+        if view is not None:
+            view.copy_(tensor.to(device="cuda", dtype=torch.float32).reshape(-1))
+
+    @property
+    def step(self):
+        out = C.c_uint32()
+        check(native.lib().gb_plan_get_step(self._h, C.byref(out)))
+        return out.value
+
+    @step.setter
+    def step(self, value):
+        check(native.lib().gb_plan_set_step(self._h, int(value)))
+
+    def destroy(self):
+        if self._h:
+            native.lib().gb_plan_destroy(self._h)
+            self._h = None
+            if self in self.engine.plans:
+                self.engine.plans.remove(self)

@@ -1,0 +1,123 @@
+/* libgrace_b200 -- C ABI of the Blackwell-native gradient-compression engine.
+ *
+ * The reference (Crystal-wxy/grace) ships no native code; the native pieces it relies on are
+ * Horovod's C++ core (handles, poll/synchronize), c10d/NCCL collectives and ATen/CuPy kernels
+ * (SURVEY.md §2.7).  This library replaces them with:
+ *   - a communicator owning a peer-mapped arena, epoch flags and a host-visible status word;
+ *   - "plans": one flattened gradient bucket + its error-feedback state + one compressed
+ *     exchange, executed as  gb_plan_send (compensate + compress + stores into every peer)
+ *     and gb_plan_recv (wait flags + decode + aggregate, written once);
+ *   - stand-alone single-tensor kernels used by the synchronous Communicator.step API.
+ * Every function returns 0 on success and -1 on failure (message in gb_last_error()).
+ * All pointers named d_* are device pointers; `stream` is a cudaStream_t passed as void*.
+ */
+#ifndef GRACE_B200_H
+#define GRACE_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gb_comm gb_comm;
+typedef struct gb_plan gb_plan;
+
+/* codecs (reference: grace_dl/dist/compressor/<name>.py) */
+enum {
+  GB_CODEC_NONE = 0,      /* none.py:4-12      fp32 on the wire            */
+  GB_CODEC_FP16 = 1,      /* fp16.py:6-22      fp16 on the wire            */
+  GB_CODEC_TOPK = 2,      /* topk.py:6-36      (fp32, int32) pairs         */
+  GB_CODEC_RANDOMK = 3,   /* randomk.py:6-40   fp32 values only            */
+  GB_CODEC_THRESHOLD = 4, /* threshold.py:6-27 variable-size pairs         */
+  GB_CODEC_DGC = 5,       /* dgc.py:6-50       variable-size pairs         */
+  GB_CODEC_QSGD = 6,      /* qsgd.py:6-38      4/8/16-bit levels + norm    */
+  GB_CODEC_TERNGRAD = 7,  /* terngrad.py:6-32  2-bit codes + scalar        */
+  GB_CODEC_NATURAL = 8,   /* natural.py:9-40   8-bit sign+exponent         */
+  GB_CODEC_U8BIT = 9,     /* tensorflow/compressor/u8bit.py:6-110          */
+  GB_CODEC_SIGNSGD = 10,  /* signsgd.py:6-30   1 bit, majority vote        */
+  GB_CODEC_SIGNUM = 11,   /* signum.py:6-37    1 bit of the momentum       */
+  GB_CODEC_EFSIGNSGD = 12,/* efsignsgd.py:6-33 1 bit + mean|x|             */
+  GB_CODEC_ONEBIT = 13    /* torch/compressor/onebit.py:6-32 1 bit + 2 means */
+};
+
+/* memories (reference: grace_dl/dist/memory/<name>.py) */
+enum {
+  GB_MEM_NONE = 0,     /* none.py:4-11                                         */
+  GB_MEM_RESIDUAL = 1, /* residual.py:4-20 and efsignsgd.py:4-19 (beta=1, gamma=lr) */
+  GB_MEM_DGC = 2       /* dgc.py:7-39  momentum correction + accumulation       */
+};
+
+typedef struct gb_codec_params {
+  double ratio;            /* topk / randomk / dgc compress_ratio (double: k = int(numel*ratio) as in python) */
+  int32_t codec;
+  int32_t memory;
+  float beta, gamma;       /* residual memory: x = beta*e + gamma*g                    */
+  float threshold;         /* threshold codec                                          */
+  int32_t quantum_num;     /* qsgd                                                     */
+  float momentum;          /* signum (codec) or dgc (memory)                           */
+  float lr;                /* efsignsgd: aggregate = sum / lr                          */
+  uint32_t seed;           /* Philox key word 0 (shared by all ranks)                  */
+  int32_t average;         /* divide the aggregate by world size                       */
+  float capacity;          /* variable-size codecs: slot capacity as a fraction of numel (0 -> 1.0) */
+} gb_codec_params;
+
+const char* gb_last_error(void);
+int gb_version(void);
+/* make `device` current for this thread inside the library's CUDA runtime instance */
+int gb_set_device(int device);
+
+/* ---- communicator: arena + peers (replaces Horovod core / c10d bootstrap) */
+int gb_comm_create(int rank, int world, size_t arena_bytes, gb_comm** out);
+int gb_comm_ipc_handle(gb_comm* c, void* out64);                 /* 64-byte cudaIpcMemHandle_t   */
+int gb_comm_open_peers(gb_comm* c, const void* handles);         /* world * 64 bytes, rank order */
+/* `world` virtual ranks on the current device (tests, single-GPU emulation of the protocol) */
+int gb_comm_create_local(int world, size_t arena_bytes, gb_comm** out /* [world] */);
+int gb_comm_destroy(gb_comm* c);
+int gb_comm_status(gb_comm* c, uint32_t* out);                   /* 0 ok; bit0 timeout; bit1 overflow */
+int gb_comm_clear_status(gb_comm* c);
+int gb_comm_set_timeout_ms(gb_comm* c, uint64_t ms);
+int gb_comm_rank(gb_comm* c);
+int gb_comm_world(gb_comm* c);
+size_t gb_comm_arena_free(gb_comm* c);
+/* all ranks reach this point (flag barrier over peer memory; used by tests and K0) */
+int gb_comm_barrier(gb_comm* c, void* stream);
+
+/* ---- events with integer handles (Horovod poll/synchronize, mpi_ops.py:420-439) */
+int gb_handle_record(void* stream, int64_t* out_handle);
+int gb_handle_poll(int64_t handle);            /* 1 done, 0 pending, -1 error */
+int gb_handle_wait(int64_t handle);            /* blocks the host; releases the handle */
+int gb_handle_stream_wait(int64_t handle, void* stream);  /* make `stream` wait; keeps the handle */
+int gb_handle_release(int64_t handle);
+
+/* ---- plans: one gradient bucket, one compressed exchange */
+int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const uint32_t* name_hash,
+                   const gb_codec_params* params, gb_plan** out);
+int gb_plan_destroy(gb_plan* p);
+int64_t gb_plan_padded_numel(gb_plan* p);
+int gb_plan_offsets(gb_plan* p, int64_t* out /* [nseg] element offsets into the flat buffer */);
+int64_t gb_plan_wire_bytes(gb_plan* p);        /* payload bytes one rank sends to one peer */
+/* compensate + compress + store into every peer's slot + release flags */
+int gb_plan_send(gb_plan* p, const float* d_grad, void* stream);
+/* wait for all ranks' flags, decode, aggregate; writes every element of d_out exactly once */
+int gb_plan_recv(gb_plan* p, float* d_out, void* stream);
+/* state access for state_dict(): which = 0 residual / dgc v, 1 momentum / dgc u */
+int gb_plan_state(gb_plan* p, int which, void** d_ptr, size_t* bytes);
+int gb_plan_get_step(gb_plan* p, uint32_t* step);
+int gb_plan_set_step(gb_plan* p, uint32_t step);
+int gb_plan_launches(gb_plan* p, int64_t* out);  /* kernels launched by this plan so far */
+
+/* ---- stand-alone single-tensor kernels (synchronous API, microbenchmarks) */
+/* exact top-k by magnitude: k (value, index) pairs in ascending index order.
+ * d_scratch: at least gb_topk_scratch_bytes(n) bytes of device memory, any contents. */
+size_t gb_topk_scratch_bytes(int64_t n);
+int gb_topk_compress(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_t* d_idx,
+                     void* d_scratch, size_t scratch_bytes, void* stream);
+/* dense = sum_r scatter(vals_r, idx_r) * scale, ranks added in order; lists sorted by index */
+int gb_sparse_decompress(const float* const* d_vals, const int32_t* const* d_idx, const int64_t* counts,
+                         int nranks, int64_t n, float scale, float* d_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRACE_B200_H */

@@ -1,0 +1,250 @@
+"""Numerics of the fused sm_100a kernels against the pure-torch codecs (fp32 oracle).
+
+W virtual ranks live on one GPU (``Engine.local``): every rank's send kernels run first,
+then every rank's receive kernels, so flag waits never block (B200_PROFILING.md: kernels that
+wait on one another must not be separate launches on one GPU)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from grace_b200 import compressor as C          # noqa: E402
+from grace_b200 import memory as M              # noqa: E402
+
+SIZES = [1000, 64, 4096, 5001, 1, 12345, 70000, 3]
+NAMES = ["seg%d.weight" % i for i in range(len(SIZES))]
+SEED = 1234
+
+
+def _params(codec, memory="none", **kw):
+    from grace_b200.ops.native import CodecParams, CODEC, MEMORY
+    p = CodecParams()
+    p.codec, p.memory = CODEC[codec], MEMORY[memory]
+    p.ratio = kw.get("ratio", 0.05)
+    p.beta, p.gamma = kw.get("beta", 1.0), kw.get("gamma", 1.0)
+    p.threshold = kw.get("threshold", 1.5)
+    p.quantum_num = kw.get("quantum_num", 64)
+    p.momentum = kw.get("momentum", 0.9)
+    p.lr = kw.get("lr", 0.1)
+    p.seed = SEED
+    p.average = kw.get("average", 1)
+    p.capacity = 1.0
+    return p
+
+
+def _flat(plan, tensors):
+    buf = torch.zeros(plan.padded, device="cuda")
+    for off, t in zip(plan.offsets, tensors):
+        buf[off:off + t.numel()] = t
+    return buf
+
+
+def _split(plan, buf):
+    return [buf[off:off + n].clone() for off, n in zip(plan.offsets, plan.numels)]
+
+
+def run_fused(world, params, grads_per_step):
+    """grads_per_step[step][rank] = list of tensors -> outs[step][rank] = list of tensors."""
+    from grace_b200.parallel.engine import Engine
+    engines = Engine.local(world)
+    plans = [e.plan(SIZES, NAMES, params) for e in engines]
+    outs = []
+    try:
+        for grads in grads_per_step:
+            bufs = [_flat(plans[r], grads[r]) for r in range(world)]
+            for r in range(world):
+                plans[r].send(bufs[r])
+            res = []
+            for r in range(world):
+                out = torch.full((plans[r].padded,), float("nan"), device="cuda")
+                plans[r].recv(out)
+                res.append(_split(plans[r], out))
+            torch.cuda.synchronize()
+            for e in engines:
+                e.check_status()
+            outs.append(res)
+        states = [[p.get_state(0), p.get_state(1)] for p in plans]
+        states = [[None if s is None else _split(plans[r], s) for s in st] for r, st in enumerate(states)]
+    finally:
+        for e in engines:
+            e.destroy()
+    return outs, states
+
+
+def run_oracle(world, make_comp, make_mem, grads_per_step):
+    comps = [make_comp() for _ in range(world)]
+    mems = [make_mem() for _ in range(world)]
+    outs = []
+    for grads in grads_per_step:
+        step_out = [[None] * len(SIZES) for _ in range(world)]
+        for i, name in enumerate(NAMES):
+            payloads, ctxs = [], []
+            for r in range(world):
+                x = mems[r].compensate(grads[r][i], name)
+                pl, ctx = comps[r].compress(x, name)
+                mems[r].update(x, name, comps[r], pl, ctx)
+                payloads.append(pl)
+                ctxs.append(ctx)
+            for r in range(world):
+                dec = [comps[r].decompress(pl, ctxs[r]) for pl in payloads]
+                agg = comps[r].aggregate(dec)
+                step_out[r][i] = agg / world if comps[r].average else agg
+        outs.append(step_out)
+    return outs, comps, mems
+
+
+def make_grads(world, steps, scale=1.0, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return [[[torch.randn(n, device="cuda", generator=g) * scale * (1 + 0.3 * r) for n in SIZES]
+             for r in range(world)] for _ in range(steps)]
+
+
+def assert_same(fused, oracle, exact=True, frac=0.0, rtol=1e-5, atol=1e-6, what=""):
+    for s, (fs, os_) in enumerate(zip(fused, oracle)):
+        for r, (fr, orr) in enumerate(zip(fs, os_)):
+            for i, (a, b) in enumerate(zip(fr, orr)):
+                b = b.reshape(-1).float()
+                if exact:
+                    bad = (a != b)
+                else:
+                    bad = (a - b).abs() > atol + rtol * b.abs()
+                nbad = int(bad.sum())
+                assert nbad <= frac * a.numel(), (
+                    "%s step %d rank %d seg %d (n=%d): %d mismatches, max|diff| %g, first idx %s" %
+                    (what, s, r, i, a.numel(), nbad, float((a - b).abs().max()), bad.nonzero()[:5].flatten().tolist()))
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("memory", ["none", "residual"])
+def test_topk(world, memory):
+    grads = make_grads(world, 3)
+    prm = _params("topk", memory, ratio=0.05, beta=0.9, gamma=1.1)
+    fused, states = run_fused(world, prm, grads)
+    mk = (lambda: M.ResidualMemory(0.9, 1.1)) if memory == "residual" else M.NoneMemory
+    oracle, _, mems = run_oracle(world, lambda: C.TopKCompressor(0.05), mk, grads)
+    assert_same(fused, oracle, exact=True, what="topk")
+    if memory == "residual":
+        for r in range(world):
+            for i, name in enumerate(NAMES):
+                assert torch.equal(states[r][0][i], mems[r].residuals[name].reshape(-1)), (r, name)
+
+
+def test_topk_ties_take_lowest_indices():
+    grads = [[[torch.randint(-3, 4, (n,), device="cuda").float() for n in SIZES]]]
+    fused, _ = run_fused(1, _params("topk", ratio=0.1), grads)
+    for out, g, n in zip(fused[0][0], grads[0][0], SIZES):
+        k = max(1, int(n * 0.1))
+        assert int((out != 0).sum()) <= k
+        kth = g.abs().sort(descending=True)[0][k - 1]
+        assert torch.equal(out[g.abs() > kth], g[g.abs() > kth])          # everything above the threshold
+        ties = (g.abs() == kth).nonzero().flatten()
+        taken = k - int((g.abs() > kth).sum())
+        if kth > 0:
+            assert torch.equal(out[ties[:taken]], g[ties[:taken]]) and (out[ties[taken:]] == 0).all()
+
+
+@pytest.mark.parametrize("world", [1, 3])
+def test_threshold(world):
+    grads = make_grads(world, 2)
+    fused, _ = run_fused(world, _params("threshold", "residual", threshold=1.5), grads)
+    oracle, _, _ = run_oracle(world, lambda: C.ThresholdCompressor(1.5), M.ResidualMemory, grads)
+    assert_same(fused, oracle, exact=True, what="threshold")
+
+
+@pytest.mark.parametrize("world", [1, 2])
+@pytest.mark.parametrize("memory", ["none", "residual"])
+def test_randomk(world, memory):
+    grads = make_grads(world, 3)
+    fused, _ = run_fused(world, _params("randomk", memory, ratio=0.05), grads)
+    mk = M.ResidualMemory if memory == "residual" else M.NoneMemory
+    oracle, _, _ = run_oracle(world, lambda: C.RandomKCompressor(0.05, seed=SEED), mk, grads)
+    assert_same(fused, oracle, exact=True, what="randomk")
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_dgc_with_dgc_memory(world):
+    grads = make_grads(world, 3)
+    fused, states = run_fused(world, _params("dgc", "dgc", ratio=0.05, momentum=0.9), grads)
+    oracle, _, mems = run_oracle(world, lambda: C.DgcCompressor(0.05, seed=SEED),
+                                 lambda: M.DgcMemory(0.9, False, world), grads)
+    assert_same(fused, oracle, exact=True, what="dgc")
+    for r in range(world):
+        for i, name in enumerate(NAMES):
+            assert torch.equal(states[r][0][i], mems[r].gradients[name].reshape(-1))
+            assert torch.equal(states[r][1][i], mems[r].residuals[name].reshape(-1))
+
+
+@pytest.mark.parametrize("codec,make,exact,frac", [
+    ("none", C.NoneCompressor, True, 0.0),
+    ("fp16", C.FP16Compressor, True, 0.0),
+    ("signsgd", C.SignSGDCompressor, True, 0.0),
+    ("signum", lambda: C.SignumCompressor(0.9), True, 0.0),
+    ("natural", lambda: C.NaturalCompressor(seed=SEED), True, 0.0),
+    ("efsignsgd", lambda: C.EFSignSGDCompressor(0.1), False, 0.0),
+    ("onebit", C.OneBitCompressor, False, 0.0),
+    ("qsgd", lambda: C.QSGDCompressor(64, seed=SEED), False, 0.002),
+    ("terngrad", lambda: C.TernGradCompressor(seed=SEED), False, 0.002),
+    ("u8bit", C.U8bitCompressor, False, 0.002),
+])
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("memory", ["none", "residual"])
+def test_quantizers(codec, make, exact, frac, world, memory):
+    grads = make_grads(world, 3, scale=0.02)
+    avg = 0 if codec in ("signsgd", "signum", "efsignsgd") else 1
+    fused, _ = run_fused(world, _params(codec, memory, average=avg, gamma=0.1 if codec == "efsignsgd" else 1.0), grads)
+    if memory == "residual":
+        mk = (lambda: M.EFSignSGDMemory(0.1)) if codec == "efsignsgd" else M.ResidualMemory
+    else:
+        mk = M.NoneMemory
+    oracle, _, _ = run_oracle(world, make, mk, grads)
+    assert_same(fused, oracle, exact=exact, frac=frac, rtol=2e-5, atol=1e-7, what=codec)
+
+
+@pytest.mark.parametrize("q,bits", [(4, 4), (64, 8), (256, 16)])
+def test_qsgd_bit_widths(q, bits):
+    grads = make_grads(2, 1, scale=0.5)
+    fused, _ = run_fused(2, _params("qsgd", quantum_num=q), grads)
+    oracle, _, _ = run_oracle(2, lambda: C.QSGDCompressor(q, seed=SEED), M.NoneMemory, grads)
+    assert_same(fused, oracle, exact=False, frac=0.002, rtol=2e-5, atol=1e-7, what="qsgd%d" % q)
+
+
+def test_standalone_topk_matches_torch():
+    import ctypes as ct
+    from grace_b200.ops import native
+    L = native.lib()
+    for n, k in [(1, 1), (777, 10), (4096, 40), (100000, 1000), (1 << 20, 10485)]:
+        x = torch.randn(n, device="cuda")
+        vals = torch.empty(k, device="cuda")
+        idx = torch.empty(k, dtype=torch.int32, device="cuda")
+        scratch = torch.empty(L.gb_topk_scratch_bytes(n), dtype=torch.uint8, device="cuda")
+        native.check(L.gb_topk_compress(ct.c_void_p(x.data_ptr()), n, k, ct.c_void_p(vals.data_ptr()),
+                                        ct.c_void_p(idx.data_ptr()), ct.c_void_p(scratch.data_ptr()), scratch.numel(),
+                                        ct.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        torch.cuda.synchronize()
+        ref = torch.topk(x.abs(), k)[1].sort()[0]
+        assert torch.equal(idx.long(), ref) and torch.equal(vals, x[ref])
+
+
+def test_state_survives_plan_roundtrip():
+    grads = make_grads(1, 2)
+    from grace_b200.parallel.engine import Engine
+    (e,) = Engine.local(1)
+    try:
+        p = e.plan(SIZES, NAMES, _params("topk", "residual"))
+        buf = _flat(p, grads[0][0])
+        p.send(buf)
+        out = torch.empty(p.padded, device="cuda")
+        p.recv(out)
+        torch.cuda.synchronize()
+        saved, step = p.get_state(0), p.step
+        q = e.plan(SIZES, NAMES, _params("topk", "residual"))
+        q.set_state(0, saved)
+        q.step = step
+        buf2 = _flat(p, grads[1][0])
+        o1, o2 = torch.empty(p.padded, device="cuda"), torch.empty(p.padded, device="cuda")
+        p.send(buf2); p.recv(o1)
+        q.send(buf2); q.recv(o2)
+        torch.cuda.synchronize()
+        assert step == 1 and torch.equal(o1, o2)
+    finally:
+        e.destroy()
