@@ -1,0 +1,264 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 synthetic training throughput (img/s, whole job) with gradient
+compression, the harness of the reference's ``examples/torch/pytorch_synthetic_benchmark.py``
+(batch 32 per GPU, fixed fake data 3x224x224) on BASELINE.json config 2: bf16 compute,
+TopK 1 % + ResidualMemory + Allgather.
+
+  python bench.py --gpus N --steps K --warmup W                # this framework (fused engine)
+  python bench.py --impl reference --gpus N --steps K ...      # UNMODIFIED reference from baseline/_ref
+
+For N > 1 launch through ``python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N``.
+Rank 0 prints ONE JSON line.  ``value`` is device-timed (CUDA events, max over ranks) with the
+batch resident on the GPU like the reference harness; ``e2e`` repeats the measurement with a
+per-step pinned-host -> device copy of the inputs and a device -> host read of the loss.
+"""
+import argparse
+import json
+import os
+import socket
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="resnet50")
+    ap.add_argument("--batch-size", type=int, default=32, help="per GPU (reference harness default)")
+    ap.add_argument("--compressor", default="topk")
+    ap.add_argument("--memory", default=None)
+    ap.add_argument("--communicator", default=None)
+    ap.add_argument("--compress-ratio", type=float, default=0.01)
+    ap.add_argument("--quantum-num", type=int, default=64)
+    ap.add_argument("--compress-rank", type=int, default=4)
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 <= t <= t1 and len(r) >= 7] or [r for _, r in self.rows if len(r) >= 7]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(r[0]) for r in rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "samples": len(rows),
+                "power_w_max": max(float(r[2]) for r in rows), "reasons": reasons}
+
+
+def triple(args):
+    comp = args.compressor
+    mem = args.memory or {"topk": "residual", "qsgd": "none", "powersgd": "powersgd", "efsignsgd": "efsignsgd",
+                          "dgc": "dgc", "none": "none"}.get(comp, "residual")
+    comm = args.communicator or ("allreduce" if comp in ("powersgd", "none", "fp16") else "allgather")
+    return comp, mem, comm
+
+
+def build_model(args, device):
+    import torch
+    import torchvision
+    torch.manual_seed(0)
+    model = getattr(torchvision.models, args.model)().to(device).to(memory_format=torch.channels_last)
+    return model
+
+
+def main():
+    args = parse()
+    comp, mem, comm = triple(args)
+    if args.impl == "reference":
+        ref_root = os.path.join(ROOT, "baseline", "_ref")
+        if not os.path.isdir(os.path.join(ref_root, "grace_dl", "dist")):
+            print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref/grace_dl/dist missing: run baseline/install_reference.sh"}))
+            return 0
+        sys.path.insert(0, ref_root)          # the reference's grace_dl must shadow this repo's import shim
+    else:
+        sys.path.insert(0, ROOT)
+
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
+    if args.gpus > 1 and world == 1:
+        # convenience: re-launch ourselves under torchrun
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", str(free_port()), os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1 or args.impl == "reference":
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", str(free_port()))
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+
+    torch.backends.cudnn.benchmark = True
+    model = build_model(args, device)
+    base_opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.9)
+    n_params = sum(p.numel() for p in model.parameters())
+
+    fused = None
+    if args.impl == "ours":
+        import grace_b200.torch as hvd
+        hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+        grc = hvd.grace_from_params({"compressor": comp, "memory": mem, "communicator": comm,
+                                     "compress_ratio": args.compress_ratio, "quantum_num": args.quantum_num,
+                                     "compress_rank": args.compress_rank, "world_size": world})
+        opt = hvd.DistributedOptimizer(base_opt, grc, named_parameters=model.named_parameters(), fused="auto")
+        fused = opt._fused
+
+        def exchange_and_step():
+            opt.step()
+
+        def zero():
+            opt.zero_grad()
+    else:
+        # the reference's own public API and stock code path: grace_from_params + the manual
+        # per-parameter loop of examples/dist/CIFAR10-dawndist/core.py:202-208
+        import grace_dl
+        assert os.path.realpath(grace_dl.__file__).startswith(os.path.realpath(os.path.join(ROOT, "baseline", "_ref")))
+        from grace_dl.dist.helper import grace_from_params
+        if world > 1:
+            for p in model.parameters():
+                dist.broadcast(p.data, 0)
+        params = {"compressor": comp, "memory": mem, "communicator": comm, "compress_ratio": args.compress_ratio,
+                  "quantum_num": args.quantum_num, "compress_rank": args.compress_rank, "world_size": world}
+        grc = grace_from_params(params)
+        if comp == "powersgd":       # the dist helper drops rank/world_size: set what it forgot
+            grc.compressor.rank, grc.compressor.world_size = args.compress_rank, world
+        named = list(model.named_parameters())
+
+        def exchange_and_step():
+            for name, p in named:
+                new_grad = grc.step(p.grad, name)
+                p.grad.copy_(new_grad)
+            base_opt.step()
+
+        def zero():
+            base_opt.zero_grad(set_to_none=False)
+
+    bs = args.batch_size
+    host_x = torch.randn(bs, 3, 224, 224).pin_memory()
+    host_y = torch.randint(0, 1000, (bs,)).pin_memory()
+    dev_x = host_x.to(device, non_blocking=True).contiguous(memory_format=torch.channels_last)
+    dev_y = host_y.to(device, non_blocking=True)
+
+    def step(x, y):
+        zero()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = F.cross_entropy(model(x), y)
+        loss.backward()
+        exchange_and_step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(n, e2e):
+        barrier()
+        launches0 = fused.launches() if fused is not None else 0
+        start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.time()
+        start.record()
+        last = None
+        for _ in range(n):
+            if e2e:
+                x = host_x.to(device, non_blocking=True).contiguous(memory_format=torch.channels_last)
+                y = host_y.to(device, non_blocking=True)
+                last = step(x, y).item()          # device -> host read of the step's result
+            else:
+                last = step(dev_x, dev_y)
+        stop.record()
+        barrier()
+        t1 = time.time()
+        ms = start.elapsed_time(stop)
+        if world > 1:
+            t = torch.tensor([ms], device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        launches = (fused.launches() - launches0) if fused is not None else 0
+        return ms, launches, (t0, t1), last
+
+    for _ in range(max(args.warmup, 3)):
+        step(dev_x, dev_y)
+    sampler = ClockSampler(torch.cuda.current_device()) if rank == 0 else None
+    ms, launches, window, _ = timed(args.steps, e2e=False)
+    clocks = sampler.stop(*window) if sampler else None
+    e2e = None
+    if not args.no_e2e:
+        step(dev_x, dev_y)
+        ems, _, _, last = timed(args.steps, e2e=True)
+        e2e = {"value": world * bs * args.steps / (ems / 1e3), "unit": "img/s", "ms_per_step": ems / args.steps,
+               "h2d_bytes_per_step": host_x.numel() * 4 + host_y.numel() * 8, "d2h_bytes_per_step": 4,
+               "last_loss": last}
+    if fused is not None:
+        fused.engine.check_status()
+
+    if rank == 0:
+        value = world * bs * args.steps / (ms / 1e3)
+        out = {
+            "metric": "ResNet-50 synthetic training throughput with %s gradient compression" % comp,
+            "value": value, "unit": "img/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic (fixed random batch, random-init weights)", "impl": args.impl,
+            "config": {"model": args.model, "global_batch": world * bs, "per_gpu_batch": bs, "seq_len": None,
+                       "image": "3x224x224", "parallelism": "dp%d" % world, "compressor": comp, "memory": mem,
+                       "communicator": comm, "compress_ratio": args.compress_ratio, "params": n_params,
+                       "grad_dtype": "fp32 master gradients, bf16 autocast compute, channels_last",
+                       "optimizer": "SGD momentum 0.9 (inside the timed region)",
+                       "l2": "per-step working set (activations, >1 GB) exceeds the 126 MB L2; no explicit flush"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+        }
+        if fused is not None:
+            out["config"]["buckets"] = len(fused.buckets)
+            out["config"]["wire_bytes_per_peer_per_step"] = fused.wire_bytes()
+        print(json.dumps(out))
+    if dist.is_initialized():
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -367,9 +367,10 @@ __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, 
       const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
       if (e0 >= len) continue;
       float4 v = make_float4(acc[e0], acc[e0 + 1], acc[e0 + 2], acc[e0 + 3]);
-      if (divisor != 1.f) {
-        v.x = __fdiv_rn(v.x, divisor); v.y = __fdiv_rn(v.y, divisor);
-        v.z = __fdiv_rn(v.z, divisor); v.w = __fdiv_rn(v.w, divisor);
+      if (divisor != 1.f) {          // torch's CUDA tensor / python-scalar is a multiply by the reciprocal
+        const float inv = __fdiv_rn(1.0f, divisor);
+        v.x = __fmul_rn(v.x, inv); v.y = __fmul_rn(v.y, inv);
+        v.z = __fmul_rn(v.z, inv); v.w = __fmul_rn(v.w, inv);
       }
       store4(out + base, e0, len, v);
     }
@@ -432,7 +433,7 @@ __global__ void __launch_bounds__(GB_THREADS) k1_randomk_scatter(SegTable t, int
     const int64_t idx = randomk_index(t, seg, p - t.seg_kbase[seg], seed, step);
     float s = 0.f;
     for (int r = 0; r < in.n; ++r) s += in.vals[r][p];
-    out[t.seg_off[seg] + idx] = divisor != 1.f ? __fdiv_rn(s, divisor) : s;
+    out[t.seg_off[seg] + idx] = divisor != 1.f ? __fmul_rn(s, __fdiv_rn(1.0f, divisor)) : s;
   }
 }
 

@@ -57,7 +57,7 @@ __device__ __forceinline__ float comp1(const QuantArgs& a, float r, float g) {
 }
 
 // ---------------------------------------------------------------- pass 1: per-tile partials
-// tilestats[tile][8] = { sum x, sum x^2, max|x|, sum|x|, count(x<0), sum(x<0), -, - }
+// tilestats[tile][8] = { sum x, sum x^2, max|x|, sum|x|, count(x<0), sum(x<0), M2 about the tile mean, - }
 __global__ void __launch_bounds__(GB_THREADS) k2_stats(SegTable t, const float* __restrict__ grad,
                                                        const float* __restrict__ res, QuantArgs a, float* tilestats) {
   __shared__ float sh[6][GB_THREADS / 32];
@@ -66,16 +66,20 @@ __global__ void __launch_bounds__(GB_THREADS) k2_stats(SegTable t, const float* 
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
     float s = 0.f, s2 = 0.f, mx = 0.f, sa = 0.f, cn = 0.f, sn = 0.f;
+    float keep[GB_TILE / GB_THREADS];                 // this thread's 16 values stay in registers
 #pragma unroll
     for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
       const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
-      if (e0 >= len) continue;
-      const float4 g = *reinterpret_cast<const float4*>(grad + base + e0);
-      float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (a.has_mem) r = *reinterpret_cast<const float4*>(res + base + e0);
-      const float x[4] = {comp1(a, r.x, g.x), comp1(a, r.y, g.y), comp1(a, r.z, g.z), comp1(a, r.w, g.w)};
+      float x[4] = {0.f, 0.f, 0.f, 0.f};
+      if (e0 < len) {
+        const float4 g = *reinterpret_cast<const float4*>(grad + base + e0);
+        float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.has_mem) r = *reinterpret_cast<const float4*>(res + base + e0);
+        x[0] = comp1(a, r.x, g.x); x[1] = comp1(a, r.y, g.y); x[2] = comp1(a, r.z, g.z); x[3] = comp1(a, r.w, g.w);
+      }
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
+        keep[j * 4 + q] = x[q];
         if (e0 + q < len) {
           const float v = x[q];
           s += v; s2 += v * v; mx = fmaxf(mx, fabsf(v)); sa += fabsf(v);
@@ -87,12 +91,36 @@ __global__ void __launch_bounds__(GB_THREADS) k2_stats(SegTable t, const float* 
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (lane == 0) { sh[0][wid] = s; sh[1][wid] = s2; sh[2][wid] = mx; sh[3][wid] = sa; sh[4][wid] = cn; sh[5][wid] = sn; }
     __syncthreads();
+    float tile_sum = 0.f;
+    for (int w = 0; w < GB_THREADS / 32; ++w) tile_sum += sh[0][w];
     if (threadIdx.x < 6) {
       float acc = 0.f;
       for (int w = 0; w < GB_THREADS / 32; ++w) acc = threadIdx.x == 2 ? fmaxf(acc, sh[2][w]) : acc + sh[threadIdx.x][w];
       tilestats[(size_t)tile * 8 + threadIdx.x] = acc;
     }
     __syncthreads();
+    if (a.codec == GB_CODEC_TERNGRAD) {
+      // centred second moment about the tile mean (combined across tiles by Chan's formula in
+      // k2_finalize): sum x^2 - n mean^2 would cancel catastrophically
+      const float tmean = tile_sum / (float)len;
+      float m2 = 0.f;
+#pragma unroll
+      for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (e0 + q < len) { const float d = keep[j * 4 + q] - tmean; m2 += d * d; }
+      }
+      m2 = warp_sum(m2);
+      if (lane == 0) sh[0][wid] = m2;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        float acc = 0.f;
+        for (int w = 0; w < GB_THREADS / 32; ++w) acc += sh[0][w];
+        tilestats[(size_t)tile * 8 + 6] = acc;
+      }
+      __syncthreads();
+    }
   }
 }
 
@@ -104,24 +132,32 @@ __global__ void k2_finalize(SegTable t, const float* __restrict__ tilestats, int
   const int seg = blockIdx.x;
   const int lane = threadIdx.x;
   const int first = t.seg_tile0[seg], last = t.seg_tile0[seg + 1];
-  double s = 0, s2 = 0, sa = 0, cn = 0, sn = 0;
+  double s = 0, s2 = 0, sa = 0, cn = 0, sn = 0, m2 = 0;
   float mx = 0.f;
   for (int tile = first + lane; tile < last; tile += 32) {
     const float* p = tilestats + (size_t)tile * 8;
-    s += p[0]; s2 += p[1]; mx = fmaxf(mx, p[2]); sa += p[3]; cn += p[4]; sn += p[5];
+    s += p[0]; s2 += p[1]; mx = fmaxf(mx, p[2]); sa += p[3]; cn += p[4]; sn += p[5]; m2 += p[6];
   }
   s = warp_sum_d(s); s2 = warp_sum_d(s2); sa = warp_sum_d(sa); cn = warp_sum_d(cn); sn = warp_sum_d(sn);
+  m2 = warp_sum_d(m2);
   mx = warp_max(mx);
+  if (codec == GB_CODEC_TERNGRAD) {               // + sum_t n_t (mean_t - mean)^2
+    const double mean = s / (double)t.seg_numel[seg];
+    double between = 0;
+    for (int tile = first + lane; tile < last; tile += 32) {
+      const int nt = min(GB_TILE, t.seg_numel[seg] - (tile - first) * GB_TILE);
+      const double d = (double)tilestats[(size_t)tile * 8] / nt - mean;
+      between += nt * d * d;
+    }
+    m2 += warp_sum_d(between);
+  }
   if (lane == 0) {
     const double n = (double)t.seg_numel[seg];
     float o[4] = {0.f, 0.f, 0.f, 0.f};
     if (codec == GB_CODEC_QSGD) {
       o[0] = (float)sqrt(s2);
     } else if (codec == GB_CODEC_TERNGRAD) {
-      const double mean = s / n;
-      double var = s2 / n - mean * mean;
-      if (var < 0) var = 0;
-      o[0] = fminf(mx, (float)(2.5 * sqrt(var)));
+      o[0] = fminf(mx, (float)(2.5 * sqrt(m2 / n)));
     } else if (codec == GB_CODEC_EFSIGNSGD) {
       o[0] = (float)(sa / n);
     } else if (codec == GB_CODEC_ONEBIT) {
@@ -342,7 +378,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_decode(SegTable t, WireIn in, s
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         if (final_mode == 1) o[q] = acc[q] >= 0.f ? 1.f : -1.f;
-        else o[q] = divisor != 1.f ? __fdiv_rn(acc[q], divisor) : acc[q];
+        else o[q] = divisor != 1.f ? __fmul_rn(acc[q], __fdiv_rn(1.0f, divisor)) : acc[q];
         if (e0 + q >= len) o[q] = 0.f;
       }
       *reinterpret_cast<float4*>(outp + flat) = make_float4(o[0], o[1], o[2], o[3]);

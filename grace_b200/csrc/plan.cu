@@ -173,6 +173,18 @@ extern "C" int gb_plan_state(gb_plan* p, int which, void** d_ptr, size_t* bytes)
   *bytes = s ? (size_t)p->padded * 4 : 0;
   return 0;
 }
+extern "C" int gb_plan_state_read(gb_plan* p, int which, void* d_dst, void* stream) {
+  float* s = which == 0 ? p->d_state0 : p->d_state1;
+  GB_CHECK(s, "plan has no state buffer %d", which);
+  GB_CUDA(cudaMemcpyAsync(d_dst, s, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int gb_plan_state_write(gb_plan* p, int which, const void* d_src, void* stream) {
+  float* s = which == 0 ? p->d_state0 : p->d_state1;
+  GB_CHECK(s, "plan has no state buffer %d", which);
+  GB_CUDA(cudaMemcpyAsync(s, d_src, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
 extern "C" int gb_plan_get_step(gb_plan* p, uint32_t* step) { *step = p->step; return 0; }
 extern "C" int gb_plan_set_step(gb_plan* p, uint32_t step) { p->step = step; return 0; }
 extern "C" int gb_plan_launches(gb_plan* p, int64_t* out) { *out = p->launches; return 0; }

@@ -23,12 +23,31 @@ def _live(world_size):
     return world_size > 1 and dist.is_available() and dist.is_initialized()
 
 
+class _NativeStep:
+    """Mixin: CUDA tensors of built-in triples take the native path (one single-segment plan
+    per tensor name, ``grace_b200/parallel/fused.py``); everything else runs the generic
+    pipeline of the base class.  ``fused=False`` (or ``GRACE_B200_FUSED=0``) disables it."""
+
+    fused = "auto"
+    _stepper = None
+
+    def step(self, tensor, name):
+        if self.fused and tensor.is_cuda:
+            if self._stepper is None:
+                from grace_b200.parallel.fused import FusedStepper
+                self._stepper = FusedStepper(self)
+            out = self._stepper.step(tensor, name)
+            if out is not None:
+                return out
+        return super().step(tensor, name)
+
+
 def _finish(compressor, decompressed, world_size):
     out = compressor.aggregate(decompressed)
     return out / world_size if compressor.average else out
 
 
-class Allreduce(Communicator):
+class Allreduce(_NativeStep, Communicator):
     """Reduce in the compressed domain, then decompress once.  Only valid for linear,
     rank-invariantly shaped payloads (none, fp16, random-k values, PowerSGD 1-D)."""
 
@@ -83,7 +102,7 @@ def gather_payload(tensors, world_size, same_size, group=None):
     return [list(col) for col in zip(*columns)]
 
 
-class Allgather(Communicator):
+class Allgather(_NativeStep, Communicator):
     """Gather every rank's payload, decompress each, aggregate."""
 
     def __init__(self, compressor, memory, world_size, group=None):
@@ -96,7 +115,7 @@ class Allgather(Communicator):
         return _finish(self.compressor, decompressed, self.world_size)
 
 
-class Broadcast(Communicator):
+class Broadcast(_NativeStep, Communicator):
     """Every rank broadcasts its payload in turn; same result as ``Allgather`` for
     fixed-size payloads."""
 

@@ -78,6 +78,8 @@ def _declare(L):
         "gb_plan_send": (i32, [vp, vp, vp]),
         "gb_plan_recv": (i32, [vp, vp, vp]),
         "gb_plan_state": (i32, [vp, i32, P(vp), P(sz)]),
+        "gb_plan_state_read": (i32, [vp, i32, vp, vp]),
+        "gb_plan_state_write": (i32, [vp, i32, vp, vp]),
         "gb_plan_get_step": (i32, [vp, P(u32)]),
         "gb_plan_set_step": (i32, [vp, u32]),
         "gb_plan_launches": (i32, [vp, P(i64)]),

@@ -24,13 +24,6 @@ def _stream_ptr(stream=None):
     return C.c_void_p(s.cuda_stream)
 
 
-class _RawCuda:
-    """Adapter exposing a raw device pointer through ``__cuda_array_interface__``."""
-
-    def __init__(self, ptr, count):
-        self.__cuda_array_interface__ = {"shape": (count,), "typestr": "<f4", "data": (ptr, False), "version": 2}
-
-
 class Engine:
     """One rank's communicator.  ``Engine.create()`` joins the torch.distributed job (or runs
     as a single rank); ``Engine.local(world)`` builds ``world`` virtual ranks on the current
@@ -150,21 +143,23 @@ class Plan:
         check(native.lib().gb_plan_state(self._h, which, C.byref(ptr), C.byref(size)))
         return ptr.value, size.value
 
-    def state_tensor(self, which):
-        """Zero-copy float32 view of the plan-owned state buffer (None if the plan has none)."""
+    def get_state(self, which):
+        """Copy of the plan-owned state buffer (padded, float32) or ``None``."""
         ptr, size = self._state_view(which)
         if not ptr:
             return None
-        return torch.as_tensor(_RawCuda(ptr, size // 4), device="cuda")
-
-    def get_state(self, which):
-        view = self.state_tensor(which)
-        return None if view is None else view.clone()
+        out = torch.empty(size // 4, dtype=torch.float32, device="cuda")
+        check(native.lib().gb_plan_state_read(self._h, which, C.c_void_p(out.data_ptr()), _stream_ptr()))
+        return out
 
     def set_state(self, which, tensor):
-        view = self.state_tensor(which)
-        if view is not None:
-            view.copy_(tensor.to(device="cuda", dtype=torch.float32).reshape(-1))
+        ptr, size = self._state_view(which)
+        if not ptr:
+            return
+        src = tensor.to(device="cuda", dtype=torch.float32).reshape(-1).contiguous()
+        assert src.numel() * 4 == size, "state size mismatch"
+        check(native.lib().gb_plan_state_write(self._h, which, C.c_void_p(src.data_ptr()), _stream_ptr()))
+        torch.cuda.current_stream().synchronize()
 
     @property
     def step(self):

@@ -103,6 +103,9 @@ int gb_plan_send(gb_plan* p, const float* d_grad, void* stream);
 int gb_plan_recv(gb_plan* p, float* d_out, void* stream);
 /* state access for state_dict(): which = 0 residual / dgc v, 1 momentum / dgc u */
 int gb_plan_state(gb_plan* p, int which, void** d_ptr, size_t* bytes);
+/* copy the whole padded state buffer out of / into the plan (device to device, on `stream`) */
+int gb_plan_state_read(gb_plan* p, int which, void* d_dst, void* stream);
+int gb_plan_state_write(gb_plan* p, int which, const void* d_src, void* stream);
 int gb_plan_get_step(gb_plan* p, uint32_t* step);
 int gb_plan_set_step(gb_plan* p, uint32_t step);
 int gb_plan_launches(gb_plan* p, int64_t* out);  /* kernels launched by this plan so far */
