@@ -135,7 +135,15 @@ class _Bucket:
         self.tensors = [p for _, p in named_params]
         self.plan = engine.plan([p.numel() for p in self.tensors], self.names, params)
         self.flat = torch.zeros(self.plan.padded, dtype=torch.float32, device=self.tensors[0].device)
-        self.views = [self.flat[o:o + p.numel()].view(p.shape) for o, p in zip(self.plan.offsets, self.tensors)]
+        # views follow the parameter's own (dense) memory format so autograd's in-place
+        # accumulation and the optimizer see matching strides (channels_last conv weights)
+        self.views = []
+        for o, p in zip(self.plan.offsets, self.tensors):
+            chunk = self.flat[o:o + p.numel()]
+            if p.dim() == 4 and not p.is_contiguous() and p.is_contiguous(memory_format=torch.channels_last):
+                self.views.append(chunk.as_strided(p.shape, p.stride()))
+            else:
+                self.views.append(chunk.view(p.shape))
         self.pending = len(self.tensors)
         self.sent = False
 

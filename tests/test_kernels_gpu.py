@@ -245,6 +245,8 @@ def test_state_survives_plan_roundtrip():
         p.send(buf2); p.recv(o1)
         q.send(buf2); q.recv(o2)
         torch.cuda.synchronize()
-        assert step == 1 and torch.equal(o1, o2)
+        assert step == 1
+        for a, b in zip(_split(p, o1), _split(p, o2)):          # pad elements are never written
+            assert torch.equal(a, b)
     finally:
         e.destroy()
