@@ -85,6 +85,8 @@ def _declare(L):
         "gb_plan_launches": (i32, [vp, P(i64)]),
         "gb_topk_scratch_bytes": (sz, [i64]),
         "gb_topk_compress": (i32, [vp, i64, i64, vp, vp, vp, sz, vp]),
+        "gb_topk_static_max_n": (i64, []),
+        "gb_topk_compress_static": (i32, [vp, i64, i64, vp, vp, vp]),
         "gb_sparse_decompress": (i32, [P(vp), P(vp), P(i64), i32, i64, C.c_float, vp, vp]),
     }
     for name, (res, args) in sigs.items():

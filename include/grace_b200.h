@@ -116,6 +116,17 @@ int gb_plan_launches(gb_plan* p, int64_t* out);  /* kernels launched by this pla
 size_t gb_topk_scratch_bytes(int64_t n);
 int gb_topk_compress(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_t* d_idx,
                      void* d_scratch, size_t scratch_bytes, void* stream);
+/* Same result as gb_topk_compress, for callers that cannot hand over a scratch buffer because
+ * they cannot allocate one (no allocator of their own and all device memory already reserved by
+ * another pool; or a hook / communication thread where cudaMalloc's device-wide synchronisation
+ * is not acceptable).  This entry point has no counterpart in the reference.  The scratch is a
+ * 96 KiB __device__ array inside the library, resident on every GPU that loads it; therefore
+ * n <= gb_topk_static_max_n() (2^24), larger inputs are refused with an error.  All calls on a
+ * GPU share that array: calls whose kernels overlap on the GPU race.  The first call on a device
+ * resolves the array's address (once); make it before starting any stream capture.  Never calls
+ * cudaMalloc/cudaFree. */
+int64_t gb_topk_static_max_n(void);
+int gb_topk_compress_static(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_t* d_idx, void* stream);
 /* dense = sum_r scatter(vals_r, idx_r) * scale, ranks added in order; lists sorted by index */
 int gb_sparse_decompress(const float* const* d_vals, const int32_t* const* d_idx, const int64_t* counts,
                          int nranks, int64_t n, float scale, float* d_out, void* stream);
