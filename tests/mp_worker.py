@@ -1,0 +1,101 @@
+"""Worker for the multi-GPU tests: one process per GPU under torchrun (NCCL only for bootstrap
+and for the generic-path oracle).  Compares the native peer-memory path with the generic
+torch.distributed path and checks that all ranks hold bit-identical results."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+
+def same_on_all_ranks(t):
+    ref = t.clone()
+    dist.broadcast(ref, 0)
+    return bool(torch.equal(ref, t))
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+    from grace_b200.dist import grace_from_params
+    failures = []
+    triples = [
+        ("topk", "residual", "allgather", True), ("threshold", "residual", "allgather", True),
+        ("randomk", "residual", "allreduce", True), ("dgc", "dgc", "allgather", True),
+        ("none", "none", "allreduce", True), ("fp16", "none", "allgather", True),
+        ("signsgd", "none", "allgather", True), ("signum", "residual", "allgather", True),
+        ("natural", "residual", "allgather", True), ("efsignsgd", "efsignsgd", "allgather", False),
+        ("onebit", "residual", "allgather", False), ("qsgd", "none", "allgather", False),
+        ("terngrad", "residual", "allgather", False), ("u8bit", "none", "allgather", False),
+    ]
+    shapes = {"conv.weight": (64, 33, 3, 3), "fc.weight": (100, 257), "bn.bias": (77,), "big": (300001,)}
+    for comp, mem, comm, exact in triples:
+        params = dict(compressor=comp, memory=mem, communicator=comm, world_size=world, compress_ratio=0.02,
+                      threshold=1.2, quantum_num=64, gradient_clipping=False, momentum=0.9, lr=0.1)
+        fast, slow = grace_from_params(params), grace_from_params(params)
+        slow.fused = False
+        gen = torch.Generator(device="cuda").manual_seed(1000 + rank)
+        for step in range(3):
+            for name, shape in shapes.items():
+                g = torch.randn(shape, device="cuda", generator=gen) * (0.02 if not exact else 1.0)
+                a = fast.step(g.clone(), name).clone()
+                b = slow.step(g.clone(), name)
+                if exact:
+                    ok = torch.equal(a, b)
+                else:
+                    ok = float(((a - b).abs() > 1e-7 + 2e-5 * b.abs()).float().mean()) < 0.003
+                if not ok:
+                    failures.append("%s/%s/%s step %d %s: max diff %g" % (comp, mem, comm, step, name,
+                                                                       float((a - b).abs().max())))
+                if not same_on_all_ranks(a):
+                    failures.append("%s/%s/%s step %d %s: ranks disagree" % (comp, mem, comm, step, name))
+        assert fast._stepper is not None and fast._stepper.enabled, comp
+
+    # fused, overlapped DistributedOptimizer: replicas stay bit-identical and match the generic path
+    import grace_b200.torch as hvd
+    from grace_b200.models import MnistNet
+
+    def train(fused):
+        torch.manual_seed(0)
+        model = MnistNet().cuda().eval()
+        opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.5)
+        hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+        grc = hvd.grace_from_params(dict(compressor="topk", memory="residual", communicator="allgather",
+                                         compress_ratio=0.01))
+        opt = hvd.DistributedOptimizer(opt, grc, named_parameters=model.named_parameters(), fused=fused,
+                                       bucket_bytes=40000)
+        gen = torch.Generator(device="cuda").manual_seed(5 + rank)
+        for _ in range(5):
+            x = torch.randn(16, 1, 28, 28, device="cuda", generator=gen)
+            y = torch.randint(0, 10, (16,), device="cuda", generator=gen)
+            opt.zero_grad()
+            F.nll_loss(model(x), y).backward()
+            opt.step()
+        return torch.cat([p.detach().flatten() for p in model.parameters()])
+
+    pf, pg = train(True), train(False)
+    if not same_on_all_ranks(pf):
+        failures.append("fused DistributedOptimizer: replicas diverged")
+    if not torch.allclose(pf, pg, rtol=1e-5, atol=1e-6):
+        failures.append("fused vs generic DistributedOptimizer differ by %g" % float((pf - pg).abs().max()))
+    from grace_b200.parallel.fused import get_engine
+    torch.cuda.synchronize()
+    get_engine().check_status()
+
+    flag = torch.tensor([len(failures)], device="cuda")
+    dist.all_reduce(flag)
+    for f in failures:
+        print("[rank %d] FAIL %s" % (rank, f), flush=True)
+    if rank == 0:
+        print("MULTIGPU %s world=%d" % ("OK" if int(flag) == 0 else "FAILED", world), flush=True)
+    dist.destroy_process_group()
+    sys.exit(1 if int(flag) else 0)
+
+
+if __name__ == "__main__":
+    main()
