@@ -111,6 +111,10 @@ def main():
     else:
         sys.path.insert(0, ROOT)
 
+    # keep stdout to the single JSON line: NCCL prints its version banner there at VERSION level
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"
+
     import torch
     import torch.distributed as dist
     import torch.nn.functional as F

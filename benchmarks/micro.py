@@ -1,0 +1,130 @@
+#!/usr/bin/env python
+"""Codec x communicator micro-benchmark (BASELINE.json config 5).
+
+Times one compressed exchange (send + receive kernels) of a gradient bucket for every built-in
+codec, device-timed with CUDA events (max over ranks), and reports the achieved fraction of the
+roofline  max(HBM bytes / measured copy bandwidth, wire bytes per direction / NVLink bandwidth).
+
+  python benchmarks/micro.py --shape resnet50 --iters 20                    # 1 GPU
+  torchrun --nproc-per-node 8 benchmarks/micro.py --shape flat:268435456     # 8 GPUs, 2^28 elements
+  python benchmarks/micro.py --reference   # also time the reference's op chain (baseline/_ref) per tensor
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch
+import torch.distributed as dist
+
+CODECS = [("none", "none"), ("fp16", "none"), ("topk", "residual"), ("randomk", "residual"), ("threshold", "residual"),
+          ("dgc", "dgc"), ("qsgd", "none"), ("terngrad", "residual"), ("natural", "residual"), ("u8bit", "none"),
+          ("signsgd", "none"), ("signum", "residual"), ("efsignsgd", "efsignsgd"), ("onebit", "residual")]
+
+
+def shapes_of(spec):
+    if spec.startswith("flat:"):
+        return [("flat", int(spec.split(":")[1]))]
+    import torchvision
+    model = getattr(torchvision.models, spec)()
+    return [(n, p.numel()) for n, p in model.named_parameters()]
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)["hbm_gbs"], "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--shape", default="resnet50")
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--codecs", default="")
+    ap.add_argument("--ratio", type=float, default=0.01)
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+    from grace_b200.parallel.engine import Engine
+    from grace_b200.parallel.fused import codec_params
+    from grace_b200.registry import build_compressor, build_memory
+
+    named = shapes_of(args.shape)
+    numel = sum(n for _, n in named)
+    hbm, how = peaks()
+    nvlink = 770.0
+    eng = Engine.create(arena_bytes=int(os.environ.get("GRACE_B200_ARENA_MB", "4096")) << 20)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")        # > 126 MB L2
+    rows = []
+    want = [c for c in args.codecs.split(",") if c]
+    for comp, mem in CODECS:
+        if want and comp not in want:
+            continue
+        prm = dict(compressor=comp, memory=mem, compress_ratio=args.ratio, threshold=2.5, quantum_num=64,
+                   gradient_clipping=False, momentum=0.9, lr=0.1, world_size=world)
+        c = build_compressor(prm, "dist", world)
+        m = build_memory(prm, "dist", world, c)
+        plan = eng.plan([n for _, n in named], [k for k, _ in named], codec_params(c, m))
+        grad = torch.randn(plan.padded, device="cuda")
+        out = torch.empty(plan.padded, device="cuda")
+        times = []
+        for it in range(args.warmup + args.iters):
+            flush.zero_()                                                   # flush L2 between iterations
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            plan.send(grad)
+            plan.recv(out)
+            b.record()
+            torch.cuda.synchronize()
+            if it >= args.warmup:
+                times.append(a.elapsed_time(b))
+        ms = sorted(times)[len(times) // 2]
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        eng.check_status()
+        wire = plan.wire_bytes
+        # algorithmic HBM traffic: read grad (+state r/w), write payload to W slots, read W slots, write out
+        state_passes = {"none": 0, "residual": 2, "dgc": 4, "efsignsgd": 2}[mem]
+        hbm_bytes = numel * 4 * (1 + state_passes + 1) + wire * 2 * world
+        t_hbm = hbm_bytes / (hbm * 1e9) * 1e3
+        t_link = wire * max(world - 1, 0) / (nvlink * 1e9) * 1e3
+        roof = max(t_hbm, t_link)
+        rows.append(dict(codec=comp, memory=mem, world=world, elements=numel, ms=ms, launches_per_exchange=None,
+                         wire_bytes_per_peer=wire, roofline_ms=roof, fraction_of_roofline=roof / ms,
+                         grad_gbs=numel * 4 / ms / 1e6, peaks=how))
+        n0 = plan.launches()
+        plan.send(grad); plan.recv(out)
+        rows[-1]["launches_per_exchange"] = plan.launches() - n0
+        torch.cuda.synchronize()
+        plan.destroy()
+        if rank == 0:
+            r = rows[-1]
+            print("%-10s %-9s W=%d  %8.3f ms  %7.1f GB/s of gradient  wire %9d B/peer  roofline %6.3f ms (%.2f of %s)  launches %d"
+                  % (comp, mem, world, r["ms"], r["grad_gbs"], wire, roof, r["fraction_of_roofline"], how,
+                     r["launches_per_exchange"]), flush=True)
+    if rank == 0 and args.out:
+        with open(args.out, "w") as f:
+            json.dump(rows, f, indent=1)
+    eng.destroy()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
