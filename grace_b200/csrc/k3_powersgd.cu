@@ -1,0 +1,716 @@
+// K3 -- PowerSGD (rank <= 4) as tcgen05/TMEM GEMMs fed by TMA, with the low-rank exchange
+// issued tile by tile from the GEMM epilogue.
+//
+// Reference: grace_dl/dist/compressor/powersgd.py:7-65 + memory/powersgd.py:12-37: per matrix
+//   M += e;  Q0 = orth(N(0,1));  P = M Q0;  all_reduce(P)/W;  P^ = orth(P);  Q = M^T P^;
+//   all_reduce(Q)/W;  out = P^ Q^T;  e = M - out
+// i.e. ~20 + 12r library launches, three cuBLAS SGEMMs and two blocking NCCL all-reduces per
+// matrix, x 54 matrices for ResNet-50 (SURVEY §2.9-B PowerSGD row, §3.4).
+//
+// Here, for ALL matrices of a bucket at once (grouped through a work-item table):
+//   phase 1 (gb_psgd_send):  k3_prep   work = grad + residual; zero accumulators
+//                            k3_q0     Philox normal Q0, CholeskyQR2 orthogonalisation, Q0^T (K-major B operand)
+//                            k3_gemm<1> P_r = M Q0 : TMA -> smem (128B swizzle) -> tcgen05.mma kind::tf32 ->
+//                                      TMEM -> tcgen05.ld epilogue.  Split-K partials are red.add'ed into a local
+//                                      accumulator; the CTA that completes a 128-row tile stores that tile straight
+//                                      into EVERY peer's slot (P2P st.global over NVLink) -- the all-reduce is an
+//                                      all-gather of tiny P_r tiles + rank-ordered sum on the receiver.
+//                            k3_flag   releases the epoch flags (and pushes tiles of matrices that took the
+//                                      CUDA-core fallback)
+//   phase 2 (gb_psgd_mid):   k3_orth   wait flags; P = mean_r P_r (rank order); CholeskyQR2; P^ and P^^T
+//                            k3_gemm<2> Q_r = M^T P^ : A operand is MN-major straight from the row-major M tile
+//                            k3_flag
+//   phase 3 (gb_psgd_recv):  k3_final  wait flags; Q = mean_r Q_r; out = P^ Q^T; residual = work - out
+// Results are bit-identical on all ranks (every rank sums the same W tiles in the same order).
+// Orthogonalisation: two rounds of Cholesky-QR (Gram matrix, Cholesky, triangular solve) -- the
+// same Q factor Gram-Schmidt produces, with the reference formula's missing epsilon added
+// (SURVEY §9 item 3), in 2 passes per round instead of ~6r launches.
+#include "kernels.cuh"
+
+#include <cuda.h>
+
+#include <algorithm>
+#include <vector>
+
+#define PS_R 4           // max rank handled natively (columns per stored row)
+#define PS_N 16          // UMMA N (rank padded to the minimum N for M=128)
+#define PS_BM 128        // UMMA M / rows of a tile in the GEMM's M dimension
+#define PS_BK 32         // K elements per pipeline stage (= one 128-byte swizzle row of tf32)
+#define PS_STAGES 6
+#define PS_A_BYTES (PS_BM * PS_BK * 4)   // 16 KiB
+#define PS_B_BYTES (PS_N * PS_BK * 4)    //  2 KiB
+#define PS_SMEM (PS_STAGES * (PS_A_BYTES + PS_B_BYTES) + 1024 + 256)
+
+struct PsMat {          // one matrix of the bucket (device copy)
+  int64_t off;          // element offset of M in the flat buffers
+  int32_t n, m, r;      // rows, cols, effective rank
+  int32_t prow0, qrow0; // first row of this matrix in the P / Q row spaces
+  uint32_t hash;
+  int32_t tc;           // 1: tcgen05 path, 0: CUDA-core fallback (TMA constraints not met)
+};
+
+struct PsBand { int32_t mat, i0; };   // one CTA of k3_final: 32 rows of one matrix
+
+struct PsItem {         // one CTA of a grouped GEMM launch
+  int32_t mat, tile, m0, k0, k1, nchunks;
+};
+
+struct gb_psgd {
+  gb_comm* comm;
+  int nmat, rank_r, has_mem, use_tc;
+  uint32_t seed, step, epoch;
+  int64_t padded, prows, qrows;
+  std::vector<PsMat> h_mat;
+  std::vector<int64_t> h_off;
+  PsMat* d_mat;
+  PsItem *d_items1, *d_items2;
+  int nitems1, nitems2, ntiles1, ntiles2;
+  CUtensorMap* d_maps;      // [nmat][4]: A1 (M, box 32x128), B1 (Q0^T), A2 (M, box 32x32), B2 (P^^T)
+  float *d_work, *d_res;    // compensated gradient / residual (padded floats)
+  float *d_q0t, *d_pht;     // Q0^T [16][qrows_pad], P^^T [16][prows_pad]  (per-matrix column windows)
+  float *d_pacc, *d_qacc;   // local accumulators [prows][4], [qrows][4]
+  float *d_ph;              // P^ [prows][4]
+  uint32_t *d_cnt1, *d_cnt2, *d_done;
+  struct PsBand* d_bands;
+  int nbands;
+  int64_t qpad, ppad;       // row pitch of d_q0t / d_pht
+  int chan_p, chan_q;
+  size_t off_p, off_q, slot_p, slot_q;
+  int64_t launches;
+};
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+                   smem_u32(dst)),
+               "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+        "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// shared-memory matrix descriptor, 128-byte swizzle, Blackwell version field = 1
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;      // descriptor version
+  d |= (uint64_t)2 << 61;      // SWIZZLE_128B
+  return d;
+}
+// instruction descriptor: D=f32, A=B=tf32, M=128, N=16, A major selectable (0 K-major, 1 MN-major)
+__host__ __device__ constexpr uint32_t idesc_tf32(int a_mn_major) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)(PS_N >> 3) << 17) |
+         ((uint32_t)(PS_BM >> 4) << 24);
+}
+
+// ---------------------------------------------------------------- grouped tcgen05 GEMM
+// MODE 1:  D[128 x 16] = M[m0:m0+128, k0:k1] * Q0[k0:k1, :]         (A K-major,  K = columns of M)
+// MODE 2:  D[128 x 16] = M[k0:k1, m0:m0+128]^T * P^[k0:k1, :]       (A MN-major, K = rows of M)
+// warp 0: TMA producer; warp 1: TMEM alloc + MMA issuer; warps 2-5: epilogue (TMEM lane quarter = warp % 4)
+struct PsPeers { float* slot[GB_MAX_WORLD]; int n; };
+
+template <int MODE>
+__global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ items, const PsMat* __restrict__ mats,
+                                                  const CUtensorMap* __restrict__ maps, float* acc, uint32_t* tile_cnt,
+                                                  PsPeers peers) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + PS_STAGES * PS_A_BYTES;
+  uint64_t* full = (uint64_t*)(smem + PS_STAGES * (PS_A_BYTES + PS_B_BYTES));
+  uint64_t* empty = full + PS_STAGES;
+  uint64_t* accum_ready = empty + PS_STAGES;
+  uint32_t* tmem_slot = (uint32_t*)(accum_ready + 1);
+  uint32_t* last_flag = tmem_slot + 1;
+
+  const PsItem it = items[blockIdx.x];
+  const PsMat mt = mats[it.mat];
+  const CUtensorMap* mapA = maps + it.mat * 4 + (MODE == 1 ? 0 : 2);
+  const CUtensorMap* mapB = maps + it.mat * 4 + (MODE == 1 ? 1 : 3);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nkb = (it.k1 - it.k0 + PS_BK - 1) / PS_BK;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < PS_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(accum_ready, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(32u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_d = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ---- TMA producer
+    for (int kb = 0; kb < nkb; ++kb) {
+      const int s = kb % PS_STAGES;
+      if (kb >= PS_STAGES) mbar_wait(&empty[s], ((kb / PS_STAGES) - 1) & 1);
+      mbar_expect_tx(&full[s], PS_A_BYTES + PS_B_BYTES);
+      const int k = it.k0 + kb * PS_BK;
+      if (MODE == 1) {
+        tma_load_2d(sA + s * PS_A_BYTES, mapA, &full[s], k, it.m0);               // box 32 (K) x 128 (rows)
+      } else {
+#pragma unroll
+        for (int b = 0; b < 4; ++b)                                                // 4 boxes 32 (cols) x 32 (K rows)
+          tma_load_2d(sA + s * PS_A_BYTES + b * 4096, mapA, &full[s], it.m0 + b * 32, k);
+      }
+      tma_load_2d(sB + s * PS_B_BYTES, mapB, &full[s], k, 0);                      // box 32 (K) x 16
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ---- MMA issuer (one thread)
+    constexpr uint32_t idesc = idesc_tf32(MODE == 2);
+    for (int kb = 0; kb < nkb; ++kb) {
+      const int s = kb % PS_STAGES;
+      mbar_wait(&full[s], (kb / PS_STAGES) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t a0 = smem_u32(sA + s * PS_A_BYTES), b0 = smem_u32(sB + s * PS_B_BYTES);
+#pragma unroll
+      for (int j = 0; j < PS_BK / 8; ++j) {                                        // UMMA_K = 8 for tf32
+        uint64_t ad, bd;
+        if (MODE == 1) ad = smem_desc_sw128(a0 + j * 32, 16, 1024);               // K-major: +32 B per K step
+        else ad = smem_desc_sw128(a0 + j * 1024, 4096, 1024);                      // MN-major: next 8 K rows
+        bd = smem_desc_sw128(b0 + j * 32, 16, 1024);
+        umma_tf32(tmem_d, ad, bd, idesc, (kb | j) != 0);
+      }
+      umma_commit(&empty[s]);                 // frees the smem stage once these MMAs have read it
+    }
+    umma_commit(accum_ready);
+  } else if (warp >= 2) {
+    // ---- epilogue: TMEM -> registers -> accumulate / push
+    mbar_wait(accum_ready, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const int q = warp & 3;
+    uint32_t v[16];
+    tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16), v);
+    const int row = it.m0 + q * 32 + lane;
+    const int nrows = MODE == 1 ? mt.n : mt.m;
+    const int row0 = MODE == 1 ? mt.prow0 : mt.qrow0;
+    float* dst = acc + (size_t)(row0 + row) * PS_R;
+    const bool live = row < nrows;
+    if (it.nchunks == 1) {
+      if (live) {
+        const float4 o = make_float4(__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3]));
+        for (int r = 0; r < peers.n; ++r) *reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * PS_R) = o;
+      }
+    } else {
+      if (live) {
+#pragma unroll
+        for (int c = 0; c < PS_R; ++c) atomicAdd(dst + c, __uint_as_float(v[c]));
+      }
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (threadIdx.x == 64) *last_flag = (atomicAdd(tile_cnt + it.tile, 1u) == (uint32_t)it.nchunks - 1) ? 1u : 0u;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (*last_flag && live) {                 // this CTA completed the tile: ship it to every peer
+        __threadfence();
+        const float4 o = __ldcg(reinterpret_cast<const float4*>(dst));
+        for (int r = 0; r < peers.n; ++r) *reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * PS_R) = o;
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(32u) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------- CUDA-core fallbacks (shapes TMA cannot address)
+__global__ void __launch_bounds__(GB_THREADS) k3_gemm1_simt(const PsMat* __restrict__ mats, int nmat, const float* __restrict__ work,
+                                                           const float* __restrict__ q0t, int64_t qpad, float* acc) {
+  // one warp per row: P[i][c] = sum_j M[i][j] Q0[j][c]
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  int base = 0;
+  for (int mi = 0; mi < nmat; ++mi) {
+    const PsMat mt = mats[mi];
+    if (mt.tc) continue;
+    if (gw >= base && gw < base + mt.n) {
+      const int i = gw - base;
+      const float* rowp = work + mt.off + (size_t)i * mt.m;
+      float s[PS_R] = {0.f, 0.f, 0.f, 0.f};
+      for (int j = lane; j < mt.m; j += 32) {
+        const float x = rowp[j];
+#pragma unroll
+        for (int c = 0; c < PS_R; ++c) s[c] += x * q0t[(size_t)c * qpad + mt.qrow0 + j];
+      }
+#pragma unroll
+      for (int c = 0; c < PS_R; ++c) s[c] = warp_sum(s[c]);
+      if (lane == 0) *reinterpret_cast<float4*>(acc + (size_t)(mt.prow0 + i) * PS_R) = make_float4(s[0], s[1], s[2], s[3]);
+      return;
+    }
+    base += mt.n;
+  }
+}
+
+__global__ void __launch_bounds__(GB_THREADS) k3_gemm2_simt(const PsMat* __restrict__ mats, int nmat, const float* __restrict__ work,
+                                                           const float* __restrict__ ph, float* acc) {
+  // one thread per column: Q[j][c] = sum_i M[i][j] P^[i][c]
+  const int gt = blockIdx.x * blockDim.x + threadIdx.x;
+  int base = 0;
+  for (int mi = 0; mi < nmat; ++mi) {
+    const PsMat mt = mats[mi];
+    if (mt.tc) continue;
+    if (gt >= base && gt < base + mt.m) {
+      const int j = gt - base;
+      float s[PS_R] = {0.f, 0.f, 0.f, 0.f};
+      for (int i = 0; i < mt.n; ++i) {
+        const float x = work[mt.off + (size_t)i * mt.m + j];
+        const float4 p = *reinterpret_cast<const float4*>(ph + (size_t)(mt.prow0 + i) * PS_R);
+        s[0] += x * p.x; s[1] += x * p.y; s[2] += x * p.z; s[3] += x * p.w;
+      }
+      *reinterpret_cast<float4*>(acc + (size_t)(mt.qrow0 + j) * PS_R) = make_float4(s[0], s[1], s[2], s[3]);
+      return;
+    }
+    base += mt.m;
+  }
+}
+
+// pushes the rows of fallback matrices to every peer, then the last CTA releases the epoch flags
+__global__ void __launch_bounds__(GB_THREADS) k3_flag(const PsMat* __restrict__ mats, int nmat, int which, const float* acc,
+                                                     PsPeers peers_slots, uint32_t* done, PeerPtrs peers, int channel,
+                                                     uint32_t epoch) {
+  for (int mi = 0; mi < nmat; ++mi) {
+    const PsMat mt = mats[mi];
+    if (mt.tc) continue;
+    const int rows = which == 1 ? mt.n : mt.m, row0 = which == 1 ? mt.prow0 : mt.qrow0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += gridDim.x * blockDim.x) {
+      const float4 o = *reinterpret_cast<const float4*>(acc + (size_t)(row0 + i) * PS_R);
+      for (int r = 0; r < peers_slots.n; ++r) *reinterpret_cast<float4*>(peers_slots.slot[r] + (size_t)(row0 + i) * PS_R) = o;
+    }
+  }
+  release_flags_last_block(done, peers, channel, epoch);
+}
+
+// ---------------------------------------------------------------- element-wise prep
+__global__ void __launch_bounds__(GB_THREADS) k3_prep(int64_t padded, const float* __restrict__ grad, const float* __restrict__ res,
+                                                     float* work, int has_res, float* pacc, int64_t np, float* qacc, int64_t nq,
+                                                     uint32_t* cnt, int ncnt) {
+  const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = tid; i < padded / 4; i += nth) {
+    float4 g = reinterpret_cast<const float4*>(grad)[i];
+    if (has_res) {
+      const float4 r = reinterpret_cast<const float4*>(res)[i];
+      g.x = __fadd_rn(g.x, r.x); g.y = __fadd_rn(g.y, r.y); g.z = __fadd_rn(g.z, r.z); g.w = __fadd_rn(g.w, r.w);
+    }
+    reinterpret_cast<float4*>(work)[i] = g;
+  }
+  for (int64_t i = tid; i < np; i += nth) pacc[i] = 0.f;
+  for (int64_t i = tid; i < nq; i += nth) qacc[i] = 0.f;
+  for (int64_t i = tid; i < ncnt; i += nth) cnt[i] = 0u;
+}
+
+// ---------------------------------------------------------------- Cholesky-QR on a tall [len][4] matrix
+// One CTA per matrix.  `x` rows are read through `load(i)`; two rounds.  Returns via `store`.
+__device__ __forceinline__ void block_reduce10(float (&g)[10], float* sh) {
+#pragma unroll
+  for (int e = 0; e < 10; ++e) g[e] = warp_sum(g[e]);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  if (lane == 0)
+    for (int e = 0; e < 10; ++e) sh[wid * 10 + e] = g[e];
+  __syncthreads();
+  if (threadIdx.x < 10) {
+    float s = 0.f;
+    for (int w = 0; w < nw; ++w) s += sh[w * 10 + threadIdx.x];
+    sh[320 + threadIdx.x] = s;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int e = 0; e < 10; ++e) g[e] = sh[320 + e];
+  __syncthreads();
+}
+
+// upper-triangular R with G = R^T R (eps-guarded), then Rinv = R^{-1}; columns >= r are dropped
+__device__ void chol_inv4(const float (&g)[10], int r, float (&inv)[4][4]) {
+  // g packs the symmetric Gram matrix: (0,0)(0,1)(0,2)(0,3)(1,1)(1,2)(1,3)(2,2)(2,3)(3,3)
+  float G[4][4] = {{g[0], g[1], g[2], g[3]}, {g[1], g[4], g[5], g[6]}, {g[2], g[5], g[7], g[8]}, {g[3], g[6], g[8], g[9]}};
+  float R[4][4] = {};
+  for (int i = 0; i < 4; ++i) {
+    if (i >= r) { R[i][i] = 1.f; continue; }
+    float d = G[i][i];
+    for (int k = 0; k < i; ++k) d -= R[k][i] * R[k][i];
+    const float rii = sqrtf(fmaxf(d, 0.f)) + 1e-8f;
+    R[i][i] = rii;
+    for (int j = i + 1; j < r; ++j) {
+      float s = G[i][j];
+      for (int k = 0; k < i; ++k) s -= R[k][i] * R[k][j];
+      R[i][j] = s / rii;
+    }
+  }
+  for (int j = 0; j < 4; ++j) {                     // back substitution: R * inv = I
+    for (int i = 3; i >= 0; --i) {
+      float s = (i == j) ? 1.f : 0.f;
+      for (int k = i + 1; k < 4; ++k) s -= R[i][k] * inv[k][j];
+      inv[i][j] = s / R[i][i];
+    }
+  }
+}
+
+__device__ __forceinline__ float4 apply_inv(const float4 x, const float (&inv)[4][4], int r) {
+  const float v[4] = {x.x, x.y, x.z, x.w};
+  float o[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int j = 0; j < 4; ++j) {
+    if (j >= r) break;
+    float s = 0.f;
+    for (int k = 0; k <= j; ++k) s += v[k] * inv[k][j];
+    o[j] = s;
+  }
+  return make_float4(o[0], o[1], o[2], o[3]);
+}
+
+__device__ __forceinline__ void gram_add(float (&g)[10], const float4 x) {
+  g[0] += x.x * x.x; g[1] += x.x * x.y; g[2] += x.x * x.z; g[3] += x.x * x.w;
+  g[4] += x.y * x.y; g[5] += x.y * x.z; g[6] += x.y * x.w;
+  g[7] += x.z * x.z; g[8] += x.z * x.w; g[9] += x.w * x.w;
+}
+
+// in-place CholeskyQR2 of buf[len][4] (row-major, first r columns live), by the whole CTA
+__device__ void cholqr2_inplace(float* buf, int len, int r, float* sh) {
+  for (int round = 0; round < 2; ++round) {
+    float g[10] = {};
+    for (int i = threadIdx.x; i < len; i += blockDim.x) gram_add(g, *reinterpret_cast<const float4*>(buf + (size_t)i * 4));
+    block_reduce10(g, sh);
+    float inv[4][4];
+    chol_inv4(g, r, inv);
+    for (int i = threadIdx.x; i < len; i += blockDim.x) {
+      float4* p = reinterpret_cast<float4*>(buf + (size_t)i * 4);
+      *p = apply_inv(*p, inv, r);
+    }
+    __syncthreads();
+  }
+}
+
+// Q0 = orth(normal) per matrix; scratch rows live in qacc (zeroed again afterwards by k3_prep order: prep runs first,
+// so k3_q0 uses its own scratch `q0` [qrows][4]) ; writes Q0^T [16][qpad]
+__global__ void __launch_bounds__(512) k3_q0(const PsMat* __restrict__ mats, float* q0, float* q0t, int64_t qpad, uint32_t seed,
+                                             uint32_t step) {
+  __shared__ float sh[512];
+  const PsMat mt = mats[blockIdx.x];
+  float* buf = q0 + (size_t)mt.qrow0 * 4;
+  for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int c = 0; c < mt.r; ++c) {
+      // element (j, c) of the (m, r) row-major normal draw: one Box-Muller pair per element index
+      const uint32_t e = (uint32_t)(j * mt.r + c);
+      const Philox4 p = philox4x32(e, step, GB_STREAM_NORMAL, 0u, seed, mt.hash);
+      const float u1 = (float)((p.x >> 8) + 1u) * (1.0f / 16777216.0f);
+      const float u2 = (float)(p.y >> 8) * (1.0f / 16777216.0f);
+      v[c] = sqrtf(-2.0f * logf(u1)) * cosf(6.283185307179586f * u2);
+    }
+    *reinterpret_cast<float4*>(buf + (size_t)j * 4) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  __syncthreads();
+  cholqr2_inplace(buf, mt.m, mt.r, sh);
+  for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
+    const float4 x = *reinterpret_cast<const float4*>(buf + (size_t)j * 4);
+    const float v[4] = {x.x, x.y, x.z, x.w};
+    for (int c = 0; c < 4; ++c) q0t[(size_t)c * qpad + mt.qrow0 + j] = c < mt.r ? v[c] : 0.f;
+  }
+}
+
+struct PsIn { const float* slot[GB_MAX_WORLD]; int n; };
+
+// wait flags; P = mean_r P_r; orthogonalise; write P^ [prows][4] and P^^T [16][ppad]
+__global__ void __launch_bounds__(512) k3_orth(const PsMat* __restrict__ mats, PsIn in, float inv_world, float* ph, float* pht,
+                                               int64_t ppad, PeerPtrs peers, int channel, uint32_t epoch, uint32_t* status,
+                                               uint64_t timeout_ns) {
+  __shared__ float sh[512];
+  wait_all_ranks(peers, channel, epoch, status, timeout_ns);
+  const PsMat mt = mats[blockIdx.x];
+  float* buf = ph + (size_t)mt.prow0 * 4;
+  for (int i = threadIdx.x; i < mt.n; i += blockDim.x) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < in.n; ++r) {
+      const float4 x = *reinterpret_cast<const float4*>(in.slot[r] + (size_t)(mt.prow0 + i) * 4);
+      s.x += x.x; s.y += x.y; s.z += x.z; s.w += x.w;
+    }
+    if (in.n > 1) { s.x *= inv_world; s.y *= inv_world; s.z *= inv_world; s.w *= inv_world; }
+    *reinterpret_cast<float4*>(buf + (size_t)i * 4) = s;
+  }
+  __syncthreads();
+  cholqr2_inplace(buf, mt.n, mt.r, sh);
+  for (int i = threadIdx.x; i < mt.n; i += blockDim.x) {
+    const float4 x = *reinterpret_cast<const float4*>(buf + (size_t)i * 4);
+    const float v[4] = {x.x, x.y, x.z, x.w};
+    for (int c = 0; c < 4; ++c) pht[(size_t)c * ppad + mt.prow0 + i] = c < mt.r ? v[c] : 0.f;
+  }
+}
+
+// wait flags; out = P^ (mean_r Q_r)^T; residual = work - out.  One CTA per (matrix, 32-row band).
+__global__ void __launch_bounds__(GB_THREADS) k3_final(const PsBand* __restrict__ bands, const PsMat* __restrict__ mats, PsIn in,
+                                                      float inv_world, const float* __restrict__ ph, const float* __restrict__ work,
+                                                      float* res, int has_res, float* out, PeerPtrs peers, int channel,
+                                                      uint32_t epoch, uint32_t* status, uint64_t timeout_ns) {
+  __shared__ float4 sp[32];
+  wait_all_ranks(peers, channel, epoch, status, timeout_ns);
+  const PsBand b = bands[blockIdx.x];
+  const PsMat mt = mats[b.mat];
+  const int nrow = min(32, mt.n - b.i0);
+  if (threadIdx.x < nrow) sp[threadIdx.x] = *reinterpret_cast<const float4*>(ph + (size_t)(mt.prow0 + b.i0 + threadIdx.x) * 4);
+  __syncthreads();
+  for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
+    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < in.n; ++r) {
+      const float4 x = *reinterpret_cast<const float4*>(in.slot[r] + (size_t)(mt.qrow0 + j) * 4);
+      q.x += x.x; q.y += x.y; q.z += x.z; q.w += x.w;
+    }
+    if (in.n > 1) { q.x *= inv_world; q.y *= inv_world; q.z *= inv_world; q.w *= inv_world; }
+    for (int i = 0; i < nrow; ++i) {
+      const float4 p = sp[i];
+      const size_t e = mt.off + (size_t)(b.i0 + i) * mt.m + j;
+      const float o = p.x * q.x + p.y * q.y + p.z * q.z + p.w * q.w;
+      if (has_res) res[e] = work[e] - o;
+      out[e] = o;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- host side
+#define LAUNCHED(p) do { (p)->launches++; GB_CUDA(cudaGetLastError()); } while (0)
+#define GB_CU(expr)                                                                      \
+  do {                                                                                   \
+    CUresult _r = (expr);                                                                \
+    if (_r != CUDA_SUCCESS) {                                                            \
+      const char* _s = nullptr;                                                          \
+      cuGetErrorString(_r, &_s);                                                         \
+      gb_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #expr, _s ? _s : "?");          \
+      return -1;                                                                         \
+    }                                                                                    \
+  } while (0)
+
+static int make_map(CUtensorMap* out, const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_elems, uint32_t box_inner,
+                    uint32_t box_outer) {
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {pitch_elems * 4};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  GB_CU(cuTensorMapEncodeTiled(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE));
+  return 0;
+}
+
+static void build_items(const std::vector<PsMat>& mats, int mode, std::vector<PsItem>& items, int& ntiles) {
+  // aim for >= ~3 CTAs per SM overall; never split K finer than 8 pipeline stages
+  int64_t total = 0;
+  for (auto& m : mats) if (m.tc) total += (int64_t)m.n * m.m;
+  const int64_t per_item = std::max<int64_t>((int64_t)PS_BM * PS_BK * 8, total / (148 * 3) + 1);
+  ntiles = 0;
+  for (int mi = 0; mi < (int)mats.size(); ++mi) {
+    const PsMat& m = mats[mi];
+    if (!m.tc) continue;
+    const int mdim = mode == 1 ? m.n : m.m, kdim = mode == 1 ? m.m : m.n;
+    const int mtiles = (mdim + PS_BM - 1) / PS_BM;
+    int chunk = (int)std::min<int64_t>(kdim, std::max<int64_t>(PS_BK * 8, per_item / PS_BM));
+    chunk = (chunk + PS_BK - 1) / PS_BK * PS_BK;
+    const int nch = (kdim + chunk - 1) / chunk;
+    for (int t = 0; t < mtiles; ++t) {
+      for (int c = 0; c < nch; ++c)
+        items.push_back(PsItem{mi, ntiles, t * PS_BM, c * chunk, std::min(kdim, (c + 1) * chunk), nch});
+      ++ntiles;
+    }
+  }
+}
+
+extern "C" int gb_psgd_destroy(gb_psgd* p);
+
+extern "C" int gb_psgd_create(gb_comm* c, int nmat, const int64_t* rows, const int64_t* cols, const uint32_t* name_hash, int rank_r,
+                              uint32_t seed, int has_memory, int use_tcgen05, gb_psgd** out) {
+  GB_CHECK(nmat >= 1, "need at least one matrix");
+  GB_CHECK(rank_r >= 1 && rank_r <= PS_R, "native PowerSGD supports rank 1..%d (got %d)", PS_R, rank_r);
+  gb_psgd* p = new gb_psgd();
+  p->comm = c; p->nmat = nmat; p->rank_r = rank_r; p->has_mem = has_memory; p->use_tc = use_tcgen05;
+  p->seed = seed; p->step = 0; p->epoch = 0; p->launches = 0;
+  int64_t off = 0, prow = 0, qrow = 0;
+  for (int i = 0; i < nmat; ++i) {
+    GB_CHECK(rows[i] >= 1 && cols[i] >= 1 && rows[i] * cols[i] < (int64_t(1) << 31), "matrix %d has a bad shape", i);
+    PsMat m;
+    m.off = off; m.n = (int)rows[i]; m.m = (int)cols[i];
+    m.r = (int)std::min<int64_t>(rank_r, std::min(rows[i], cols[i]));
+    m.prow0 = (int)prow; m.qrow0 = (int)qrow; m.hash = name_hash[i];
+    m.tc = use_tcgen05 && (m.m % 4 == 0) && m.n >= 8 && m.m >= 32;
+    p->h_mat.push_back(m);
+    p->h_off.push_back(off);
+    off += (rows[i] * cols[i] + GB_ALIGN - 1) / GB_ALIGN * GB_ALIGN;
+    prow += (rows[i] + 3) / 4 * 4;        // keep every matrix's row window 16-byte aligned in the transposed buffers
+    qrow += (cols[i] + 3) / 4 * 4;
+  }
+  p->padded = off; p->prows = prow; p->qrows = qrow;
+  p->ppad = (prow + 31) / 32 * 32; p->qpad = (qrow + 31) / 32 * 32;
+  std::vector<PsItem> it1, it2;
+  build_items(p->h_mat, 1, it1, p->ntiles1);
+  build_items(p->h_mat, 2, it2, p->ntiles2);
+  p->nitems1 = (int)it1.size(); p->nitems2 = (int)it2.size();
+  std::vector<PsBand> bands;
+  for (int i = 0; i < nmat; ++i)
+    for (int r0 = 0; r0 < p->h_mat[i].n; r0 += 32) bands.push_back(PsBand{i, r0});
+
+  GB_CUDA(cudaMalloc((void**)&p->d_mat, sizeof(PsMat) * nmat));
+  GB_CUDA(cudaMemcpy(p->d_mat, p->h_mat.data(), sizeof(PsMat) * nmat, cudaMemcpyHostToDevice));
+  GB_CUDA(cudaMalloc((void**)&p->d_items1, sizeof(PsItem) * (it1.size() + 1)));
+  GB_CUDA(cudaMalloc((void**)&p->d_items2, sizeof(PsItem) * (it2.size() + 1)));
+  if (!it1.empty()) GB_CUDA(cudaMemcpy(p->d_items1, it1.data(), sizeof(PsItem) * it1.size(), cudaMemcpyHostToDevice));
+  if (!it2.empty()) GB_CUDA(cudaMemcpy(p->d_items2, it2.data(), sizeof(PsItem) * it2.size(), cudaMemcpyHostToDevice));
+  GB_CUDA(cudaMalloc((void**)&p->d_work, p->padded * 4));
+  GB_CUDA(cudaMemset(p->d_work, 0, p->padded * 4));
+  p->d_res = nullptr;
+  if (has_memory) { GB_CUDA(cudaMalloc((void**)&p->d_res, p->padded * 4)); GB_CUDA(cudaMemset(p->d_res, 0, p->padded * 4)); }
+  GB_CUDA(cudaMalloc((void**)&p->d_q0t, PS_N * p->qpad * 4)); GB_CUDA(cudaMemset(p->d_q0t, 0, PS_N * p->qpad * 4));
+  GB_CUDA(cudaMalloc((void**)&p->d_pht, PS_N * p->ppad * 4)); GB_CUDA(cudaMemset(p->d_pht, 0, PS_N * p->ppad * 4));
+  GB_CUDA(cudaMalloc((void**)&p->d_pacc, (p->prows + 8) * PS_R * 4));
+  GB_CUDA(cudaMalloc((void**)&p->d_qacc, (p->qrows + 8) * PS_R * 4 * 2));   // second half: Q0 scratch for k3_q0
+  GB_CUDA(cudaMalloc((void**)&p->d_ph, (p->prows + 8) * PS_R * 4));
+  GB_CUDA(cudaMalloc((void**)&p->d_cnt1, (p->ntiles1 + p->ntiles2 + 64) * 4));
+  p->d_cnt2 = p->d_cnt1 + p->ntiles1;
+  p->d_done = p->d_cnt1 + p->ntiles1 + p->ntiles2;
+  GB_CUDA(cudaMemset(p->d_cnt1, 0, (p->ntiles1 + p->ntiles2 + 64) * 4));
+  p->nbands = (int)bands.size();
+  GB_CUDA(cudaMalloc((void**)&p->d_bands, sizeof(PsBand) * bands.size()));
+  GB_CUDA(cudaMemcpy(p->d_bands, bands.data(), sizeof(PsBand) * bands.size(), cudaMemcpyHostToDevice));
+  p->d_maps = nullptr;
+  // tensor maps
+  std::vector<CUtensorMap> maps(nmat * 4);
+  for (int i = 0; i < nmat; ++i) {
+    const PsMat& m = p->h_mat[i];
+    if (!m.tc) continue;
+    const float* M = p->d_work + m.off;
+    if (make_map(&maps[i * 4 + 0], M, m.m, m.n, m.m, PS_BK, PS_BM)) return -1;
+    if (make_map(&maps[i * 4 + 1], p->d_q0t + m.qrow0, m.m, PS_N, p->qpad, PS_BK, PS_N)) return -1;
+    if (make_map(&maps[i * 4 + 2], M, m.m, m.n, m.m, 32, PS_BK)) return -1;
+    if (make_map(&maps[i * 4 + 3], p->d_pht + m.prow0, m.n, PS_N, p->ppad, PS_BK, PS_N)) return -1;
+  }
+  GB_CUDA(cudaMalloc((void**)&p->d_maps, sizeof(CUtensorMap) * nmat * 4));
+  GB_CUDA(cudaMemcpy(p->d_maps, maps.data(), sizeof(CUtensorMap) * nmat * 4, cudaMemcpyHostToDevice));
+  GB_CUDA(cudaFuncSetAttribute(k3_gemm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
+  GB_CUDA(cudaFuncSetAttribute(k3_gemm<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
+  p->slot_p = ((size_t)(p->prows + 8) * PS_R * 4 + 255) & ~size_t(255);
+  p->slot_q = ((size_t)(p->qrows + 8) * PS_R * 4 + 255) & ~size_t(255);
+  if (gb_comm_alloc_channel(c, p->slot_p, &p->chan_p, &p->off_p)) return -1;
+  if (gb_comm_alloc_channel(c, p->slot_q, &p->chan_q, &p->off_q)) return -1;
+  GB_CUDA(cudaDeviceSynchronize());
+  *out = p;
+  return 0;
+}
+
+extern "C" int gb_psgd_destroy(gb_psgd* p) {
+  if (!p) return 0;
+  cudaDeviceSynchronize();
+  cudaFree(p->d_mat); cudaFree(p->d_items1); cudaFree(p->d_items2); cudaFree(p->d_work); cudaFree(p->d_res);
+  cudaFree(p->d_q0t); cudaFree(p->d_pht); cudaFree(p->d_pacc); cudaFree(p->d_qacc); cudaFree(p->d_ph); cudaFree(p->d_cnt1);
+  cudaFree(p->d_maps);
+  cudaFree(p->d_bands);
+  delete p;
+  return 0;
+}
+
+extern "C" int64_t gb_psgd_padded_numel(gb_psgd* p) { return p->padded; }
+extern "C" int gb_psgd_offsets(gb_psgd* p, int64_t* out) { for (int i = 0; i < p->nmat; ++i) out[i] = p->h_off[i]; return 0; }
+extern "C" int gb_psgd_launches(gb_psgd* p, int64_t* out) { *out = p->launches; return 0; }
+extern "C" int gb_psgd_tc_matrices(gb_psgd* p) { int n = 0; for (auto& m : p->h_mat) n += m.tc; return n; }
+extern "C" int gb_psgd_get_step(gb_psgd* p, uint32_t* s) { *s = p->step; return 0; }
+extern "C" int gb_psgd_set_step(gb_psgd* p, uint32_t s) { p->step = s; return 0; }
+extern "C" int gb_psgd_residual(gb_psgd* p, void** ptr, size_t* bytes) { *ptr = p->d_res; *bytes = p->d_res ? (size_t)p->padded * 4 : 0; return 0; }
+extern "C" int64_t gb_psgd_wire_bytes(gb_psgd* p) { return (int64_t)(p->prows + p->qrows) * PS_R * 4; }
+
+static PsPeers peer_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch) {
+  PsPeers s; gb_comm* c = p->comm; s.n = c->world;
+  for (int r = 0; r < c->world; ++r) s.slot[r] = (float*)gb_slot(c->peer[r], chan_off, slot_bytes, c->world, epoch & 1, c->rank);
+  return s;
+}
+static PsIn my_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch) {
+  PsIn s; gb_comm* c = p->comm; s.n = c->world;
+  for (int r = 0; r < c->world; ++r) s.slot[r] = (const float*)gb_slot(c->base, chan_off, slot_bytes, c->world, epoch & 1, r);
+  return s;
+}
+
+// phase 1: compensate, Q0, P_r = M Q0, push P tiles, release flags
+extern "C" int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  gb_comm* c = p->comm;
+  GB_CHECK(((uintptr_t)d_grad & 15) == 0, "gradient buffer must be 16-byte aligned");
+  const uint32_t epoch = ++p->epoch;
+  k3_prep<<<148 * 4, GB_THREADS, 0, st>>>(p->padded, d_grad, p->d_res, p->d_work, p->has_mem && p->step > 0, p->d_pacc,
+                                         p->prows * PS_R, p->d_qacc, p->qrows * PS_R, p->d_cnt1, p->ntiles1 + p->ntiles2);
+  LAUNCHED(p);
+  k3_q0<<<p->nmat, 512, 0, st>>>(p->d_mat, p->d_qacc + (size_t)(p->qrows + 8) * PS_R, p->d_q0t, p->qpad, p->seed, p->step);
+  LAUNCHED(p);
+  const PsPeers ps = peer_slots(p, p->off_p, p->slot_p, epoch);
+  if (p->nitems1) { k3_gemm<1><<<p->nitems1, 192, PS_SMEM, st>>>(p->d_items1, p->d_mat, p->d_maps, p->d_pacc, p->d_cnt1, ps); LAUNCHED(p); }
+  int simt_rows = 0;
+  for (auto& m : p->h_mat) if (!m.tc) simt_rows += m.n;
+  if (simt_rows) { k3_gemm1_simt<<<(simt_rows * 32 + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, p->d_work, p->d_q0t, p->qpad, p->d_pacc); LAUNCHED(p); }
+  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 1, p->d_pacc, ps, p->d_done, gb_comm_peers(c), p->chan_p, epoch);
+  LAUNCHED(p);
+  return 0;
+}
+
+// phase 2: reduce + orthogonalise P, Q_r = M^T P^, push Q tiles, release flags
+extern "C" int gb_psgd_mid(gb_psgd* p, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  gb_comm* c = p->comm;
+  const uint32_t epoch = p->epoch;
+  k3_orth<<<p->nmat, 512, 0, st>>>(p->d_mat, my_slots(p, p->off_p, p->slot_p, epoch), 1.0f / (float)c->world, p->d_ph, p->d_pht,
+                                  p->ppad, gb_comm_peers(c), p->chan_p, epoch, c->status_dev, c->timeout_ns);
+  LAUNCHED(p);
+  const PsPeers qs = peer_slots(p, p->off_q, p->slot_q, epoch);
+  if (p->nitems2) { k3_gemm<2><<<p->nitems2, 192, PS_SMEM, st>>>(p->d_items2, p->d_mat, p->d_maps, p->d_qacc, p->d_cnt2, qs); LAUNCHED(p); }
+  int simt_cols = 0;
+  for (auto& m : p->h_mat) if (!m.tc) simt_cols += m.m;
+  if (simt_cols) { k3_gemm2_simt<<<(simt_cols + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, p->d_work, p->d_ph, p->d_qacc); LAUNCHED(p); }
+  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 2, p->d_qacc, qs, p->d_done, gb_comm_peers(c), p->chan_q, epoch);
+  LAUNCHED(p);
+  return 0;
+}
+
+// phase 3: reduce Q, out = P^ Q^T, residual update
+extern "C" int gb_psgd_recv(gb_psgd* p, float* d_out, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  gb_comm* c = p->comm;
+  k3_final<<<p->nbands, GB_THREADS, 0, st>>>(p->d_bands, p->d_mat, my_slots(p, p->off_q, p->slot_q, p->epoch), 1.0f / (float)c->world, p->d_ph,
+                                     p->d_work, p->d_res, p->has_mem, d_out, gb_comm_peers(c), p->chan_q, p->epoch,
+                                     c->status_dev, c->timeout_ns);
+  LAUNCHED(p);
+  p->step++;
+  return 0;
+}

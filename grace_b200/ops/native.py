@@ -83,6 +83,19 @@ def _declare(L):
         "gb_plan_get_step": (i32, [vp, P(u32)]),
         "gb_plan_set_step": (i32, [vp, u32]),
         "gb_plan_launches": (i32, [vp, P(i64)]),
+        "gb_psgd_create": (i32, [vp, i32, P(i64), P(i64), P(u32), i32, u32, i32, i32, P(vp)]),
+        "gb_psgd_destroy": (i32, [vp]),
+        "gb_psgd_padded_numel": (i64, [vp]),
+        "gb_psgd_offsets": (i32, [vp, P(i64)]),
+        "gb_psgd_send": (i32, [vp, vp, vp]),
+        "gb_psgd_mid": (i32, [vp, vp]),
+        "gb_psgd_recv": (i32, [vp, vp, vp]),
+        "gb_psgd_launches": (i32, [vp, P(i64)]),
+        "gb_psgd_tc_matrices": (i32, [vp]),
+        "gb_psgd_get_step": (i32, [vp, P(u32)]),
+        "gb_psgd_set_step": (i32, [vp, u32]),
+        "gb_psgd_residual": (i32, [vp, P(vp), P(sz)]),
+        "gb_psgd_wire_bytes": (i64, [vp]),
         "gb_topk_scratch_bytes": (sz, [i64]),
         "gb_topk_compress": (i32, [vp, i64, i64, vp, vp, vp, sz, vp]),
         "gb_topk_static_max_n": (i64, []),

@@ -177,3 +177,62 @@ class Plan:
             self._h = None
             if self in self.engine.plans:
                 self.engine.plans.remove(self)
+
+
+class PowerSGDPlan:
+    """All >=2-D gradients of one bucket through the native PowerSGD pipeline (``gb_psgd``)."""
+
+    def __init__(self, engine: Engine, shapes, names, rank, seed, has_memory, use_tcgen05=True):
+        L = native.lib()
+        self.engine = engine
+        self.nmat = len(shapes)
+        self.shapes = [(int(r), int(c)) for r, c in shapes]
+        self.numels = [r * c for r, c in self.shapes]
+        self.names = list(names)
+        rows = (C.c_int64 * self.nmat)(*[r for r, _ in self.shapes])
+        cols = (C.c_int64 * self.nmat)(*[c for _, c in self.shapes])
+        hs = (C.c_uint32 * self.nmat)(*[fnv1a(n) for n in names])
+        h = C.c_void_p()
+        check(L.gb_psgd_create(engine._h, self.nmat, rows, cols, hs, int(rank), int(seed) & 0xFFFFFFFF,
+                               1 if has_memory else 0, 1 if use_tcgen05 else 0, C.byref(h)))
+        self._h = h
+        self.padded = L.gb_psgd_padded_numel(h)
+        off = (C.c_int64 * self.nmat)()
+        check(L.gb_psgd_offsets(h, off))
+        self.offsets = list(off)
+        self.wire_bytes = L.gb_psgd_wire_bytes(h)
+        self.tc_matrices = L.gb_psgd_tc_matrices(h)
+        engine.plans.append(self)
+
+    def send(self, grad, stream=None):
+        assert grad.is_cuda and grad.dtype == torch.float32 and grad.numel() >= self.padded
+        check(native.lib().gb_psgd_send(self._h, C.c_void_p(grad.data_ptr()), _stream_ptr(stream)))
+
+    def mid(self, stream=None):
+        check(native.lib().gb_psgd_mid(self._h, _stream_ptr(stream)))
+
+    def recv(self, out, stream=None):
+        assert out.is_cuda and out.dtype == torch.float32 and out.numel() >= self.padded
+        check(native.lib().gb_psgd_recv(self._h, C.c_void_p(out.data_ptr()), _stream_ptr(stream)))
+
+    def launches(self):
+        out = C.c_int64()
+        check(native.lib().gb_psgd_launches(self._h, C.byref(out)))
+        return out.value
+
+    @property
+    def step(self):
+        out = C.c_uint32()
+        check(native.lib().gb_psgd_get_step(self._h, C.byref(out)))
+        return out.value
+
+    @step.setter
+    def step(self, value):
+        check(native.lib().gb_psgd_set_step(self._h, int(value)))
+
+    def destroy(self):
+        if self._h:
+            native.lib().gb_psgd_destroy(self._h)
+            self._h = None
+            if self in self.engine.plans:
+                self.engine.plans.remove(self)

@@ -110,6 +110,28 @@ int gb_plan_get_step(gb_plan* p, uint32_t* step);
 int gb_plan_set_step(gb_plan* p, uint32_t step);
 int gb_plan_launches(gb_plan* p, int64_t* out);  /* kernels launched by this plan so far */
 
+/* ---- PowerSGD plans (reference: compressor/powersgd.py:7-65, memory/powersgd.py:6-37), rank <= 4.
+ * All >=2-D gradients of a bucket, flattened like a plan (128-element aligned).  One exchange is
+ *   gb_psgd_send  (M += e; Q0; P_r = M Q0 on tcgen05/TMEM via TMA; P tiles stored into every peer)
+ *   gb_psgd_mid   (wait; P = mean; orthogonalise; Q_r = M^T P^ on tcgen05; Q tiles to every peer)
+ *   gb_psgd_recv  (wait; Q = mean; out = P^ Q^T; e = M - out)
+ * use_tcgen05 = 0 forces the CUDA-core GEMMs (also taken per matrix when cols % 4 != 0). */
+typedef struct gb_psgd gb_psgd;
+int gb_psgd_create(gb_comm* c, int nmat, const int64_t* rows, const int64_t* cols, const uint32_t* name_hash,
+                   int rank, uint32_t seed, int has_memory, int use_tcgen05, gb_psgd** out);
+int gb_psgd_destroy(gb_psgd* p);
+int64_t gb_psgd_padded_numel(gb_psgd* p);
+int gb_psgd_offsets(gb_psgd* p, int64_t* out);
+int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream);
+int gb_psgd_mid(gb_psgd* p, void* stream);
+int gb_psgd_recv(gb_psgd* p, float* d_out, void* stream);
+int gb_psgd_launches(gb_psgd* p, int64_t* out);
+int gb_psgd_tc_matrices(gb_psgd* p);          /* how many matrices take the tcgen05 path */
+int gb_psgd_get_step(gb_psgd* p, uint32_t* step);
+int gb_psgd_set_step(gb_psgd* p, uint32_t step);
+int gb_psgd_residual(gb_psgd* p, void** d_ptr, size_t* bytes);
+int64_t gb_psgd_wire_bytes(gb_psgd* p);
+
 /* ---- stand-alone single-tensor kernels (synchronous API, microbenchmarks) */
 /* exact top-k by magnitude: k (value, index) pairs in ascending index order.
  * d_scratch: at least gb_topk_scratch_bytes(n) bytes of device memory, any contents. */
