@@ -20,7 +20,7 @@
 #include "kernels.cuh"
 #include <cuda_fp16.h>
 
-__constant__ float c_u8_table[128] = {
+__device__ const float g_u8_table[128] = {
     1.5000001e-06f, 2.75e-06f, 7.2499997e-06f, 1.8750001e-05f, 3.625e-05f, 5.8749996e-05f, 8.6249995e-05f, 1.4375e-04f,
     2.3125e-04f, 3.1875001e-04f, 4.0625001e-04f, 5.1874999e-04f, 6.5624999e-04f, 7.9374999e-04f, 9.3124999e-04f,
     1.21875e-03f, 1.65625e-03f, 2.0937501e-03f, 2.53125e-03f, 2.96875e-03f, 3.4062499e-03f, 3.8437501e-03f,
@@ -176,7 +176,7 @@ __global__ void k2_finalize(SegTable t, const float* __restrict__ tilestats, int
 // ---------------------------------------------------------------- codec arithmetic
 // encode: value (+ uniform draw) -> BITS-bit code; decode: code + sender's scalars -> float.
 template <int CODEC>
-__device__ __forceinline__ uint32_t encode1(float x, const float4& st, uint32_t rnd, int quantum) {
+__device__ __forceinline__ uint32_t encode1(float x, const float4& st, uint32_t rnd, int quantum, const float* tab) {
   if (CODEC == GB_CODEC_NONE) return __float_as_uint(x);
   if (CODEC == GB_CODEC_FP16) return (uint32_t)__half_as_ushort(__float2half_rn(x));
   if (CODEC == GB_CODEC_SIGNSGD || CODEC == GB_CODEC_SIGNUM || CODEC == GB_CODEC_EFSIGNSGD) return x >= 0.f ? 1u : 0u;
@@ -213,7 +213,7 @@ __device__ __forceinline__ uint32_t encode1(float x, const float4& st, uint32_t 
     for (int i = 0; i < 8; ++i) {
       if (lo < hi) {
         const int mid = (lo + hi) >> 1;
-        if (c_u8_table[mid] <= y) lo = mid + 1; else hi = mid;
+        if (tab[mid] <= y) lo = mid + 1; else hi = mid;
       }
     }
     int bin = min(max(lo - 1, 0), 127);
@@ -224,7 +224,7 @@ __device__ __forceinline__ uint32_t encode1(float x, const float4& st, uint32_t 
 }
 
 template <int CODEC, int BITS>
-__device__ __forceinline__ float decode1(uint32_t code, const float4& st, int quantum) {
+__device__ __forceinline__ float decode1(uint32_t code, const float4& st, int quantum, const float* tab) {
   if (CODEC == GB_CODEC_NONE) return __uint_as_float(code);
   if (CODEC == GB_CODEC_FP16) return __half2float(__ushort_as_half((unsigned short)code));
   if (CODEC == GB_CODEC_SIGNSGD || CODEC == GB_CODEC_SIGNUM) return code ? 1.f : -1.f;
@@ -240,7 +240,7 @@ __device__ __forceinline__ float decode1(uint32_t code, const float4& st, int qu
   }
   if (CODEC == GB_CODEC_U8BIT) {
     const int a = sv < 0 ? -sv : sv;
-    const float mag = __fmul_rn(c_u8_table[min(a, 127)], st.x);
+    const float mag = __fmul_rn(tab[min(a, 127)], st.x);
     return sv > 0 ? mag : (sv < 0 ? -mag : 0.f);
   }
   return 0.f;
@@ -261,6 +261,11 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
   constexpr int SUB = 4 * BITS;                         // bits produced per thread
   constexpr int LANES = SUB >= 32 ? 1 : 32 / SUB;       // lanes sharing one word
   constexpr int WORDS = SUB >= 32 ? SUB / 32 : 1;       // words per thread
+  __shared__ float s_tab[128];
+  if (CODEC == GB_CODEC_U8BIT) {
+    if (threadIdx.x < 128) s_tab[threadIdx.x] = g_u8_table[threadIdx.x];
+    __syncthreads();
+  }
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
@@ -301,9 +306,9 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const bool live = e0 + q < len;
-          const uint32_t c = live ? (encode1<CODEC>(src[q], st, rr[q], a.quantum) & (0xFFFFFFFFu >> (32 - BITS))) : 0u;
+          const uint32_t c = live ? (encode1<CODEC>(src[q], st, rr[q], a.quantum, s_tab) & (0xFFFFFFFFu >> (32 - BITS))) : 0u;
           code[q] = c;
-          nres[q] = live ? __fsub_rn(x[q], decode1<CODEC, BITS>(c, st, a.quantum)) : 0.f;
+          nres[q] = live ? __fsub_rn(x[q], decode1<CODEC, BITS>(c, st, a.quantum, s_tab)) : 0.f;
         }
         if (a.has_mem) *reinterpret_cast<float4*>(res + base + e0) = make_float4(nres[0], nres[1], nres[2], nres[3]);
       }
@@ -344,6 +349,8 @@ template <int CODEC, int BITS>
 __global__ void __launch_bounds__(GB_THREADS) k2_decode(SegTable t, WireIn in, size_t hdr_bytes, float* outp, int quantum,
                                                         int final_mode, float divisor, PeerPtrs peers, int channel,
                                                         uint32_t epoch, uint32_t* status, uint64_t timeout_ns) {
+  __shared__ float s_tab[128];
+  if (CODEC == GB_CODEC_U8BIT && threadIdx.x < 128) s_tab[threadIdx.x] = g_u8_table[threadIdx.x];
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
@@ -372,7 +379,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_decode(SegTable t, WireIn in, s
           for (int q = 0; q < 4; ++q) code[q] = (w >> (sh + q * BITS)) & (0xFFFFFFFFu >> (32 - BITS));
         }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) acc[q] += decode1<CODEC, BITS>(code[q], st, quantum);
+        for (int q = 0; q < 4; ++q) acc[q] += decode1<CODEC, BITS>(code[q], st, quantum, s_tab);
       }
       float o[4];
 #pragma unroll

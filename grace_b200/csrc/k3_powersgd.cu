@@ -29,6 +29,8 @@
 
 #include <cuda.h>
 
+#include <stdlib.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -125,13 +127,13 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
 }
 
 // shared-memory matrix descriptor, 128-byte swizzle, Blackwell version field = 1
-__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;      // descriptor version
-  d |= (uint64_t)2 << 61;      // SWIZZLE_128B
+  d |= (uint64_t)layout << 61; // 2 = SWIZZLE_128B, 1 = SWIZZLE_128B with 32-byte atoms (MN-major 32-bit operands)
   return d;
 }
 // instruction descriptor: D=f32, A=B=tf32, M=128, N=16, A major selectable (0 K-major, 1 MN-major)
@@ -145,6 +147,9 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int a_mn_major) {
 // MODE 2:  D[128 x 16] = M[k0:k1, m0:m0+128]^T * P^[k0:k1, :]       (A MN-major, K = rows of M)
 // warp 0: TMA producer; warp 1: TMEM alloc + MMA issuer; warps 2-5: epilogue (TMEM lane quarter = warp % 4)
 struct PsPeers { float* slot[GB_MAX_WORLD]; int n; };
+
+__device__ int g_dbg[8];   // debugging overrides for the MODE 2 descriptors: {enable, lbo, sbo, k_step, a_major, dump}
+__device__ float g_dbg_dump[8192];
 
 template <int MODE>
 __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ items, const PsMat* __restrict__ mats,
@@ -209,9 +214,17 @@ __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ ite
       for (int j = 0; j < PS_BK / 8; ++j) {                                        // UMMA_K = 8 for tf32
         uint64_t ad, bd;
         if (MODE == 1) ad = smem_desc_sw128(a0 + j * 32, 16, 1024);               // K-major: +32 B per K step
-        else ad = smem_desc_sw128(a0 + j * 1024, 4096, 1024);                      // MN-major: next 8 K rows
+        else if (g_dbg[0]) ad = smem_desc_sw128(a0 + j * g_dbg[3], g_dbg[1], g_dbg[2], g_dbg[6]);
+        // MN-major tf32 must use the 128B swizzle with 32-byte atoms (atom = 32 MN x 4 K): blocks of 32
+        // columns are 4096 B apart (LBO), groups of 4 K rows 512 B apart (SBO), 8 K rows per MMA
+        else ad = smem_desc_sw128(a0 + j * 1024, 4096, 512, 1);
         bd = smem_desc_sw128(b0 + j * 32, 16, 1024);
-        umma_tf32(tmem_d, ad, bd, idesc, (kb | j) != 0);
+        uint32_t id = idesc;
+        if (MODE == 2 && g_dbg[0]) id = (idesc & ~(1u << 15)) | ((uint32_t)g_dbg[4] << 15);
+        if (MODE == 2 && g_dbg[5] && kb == 0 && j == 0 && blockIdx.x == 0) {
+          for (int i = 0; i < 4096 + 512; ++i) g_dbg_dump[i] = i < 4096 ? ((float*)(sA))[i] : ((float*)(sB))[i - 4096];
+        }
+        umma_tf32(tmem_d, ad, bd, id, (kb | j) != 0);
       }
       umma_commit(&empty[s]);                 // frees the smem stage once these MMAs have read it
     }
@@ -520,13 +533,13 @@ __global__ void __launch_bounds__(GB_THREADS) k3_final(const PsBand* __restrict_
   } while (0)
 
 static int make_map(CUtensorMap* out, const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_elems, uint32_t box_inner,
-                    uint32_t box_outer) {
+                    uint32_t box_outer, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   cuuint64_t dims[2] = {inner, outer};
   cuuint64_t strides[1] = {pitch_elems * 4};
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
   GB_CU(cuTensorMapEncodeTiled(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
-                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE));
   return 0;
 }
@@ -535,7 +548,8 @@ static void build_items(const std::vector<PsMat>& mats, int mode, std::vector<Ps
   // aim for >= ~3 CTAs per SM overall; never split K finer than 8 pipeline stages
   int64_t total = 0;
   for (auto& m : mats) if (m.tc) total += (int64_t)m.n * m.m;
-  const int64_t per_item = std::max<int64_t>((int64_t)PS_BM * PS_BK * 8, total / (148 * 3) + 1);
+  int64_t per_item = std::max<int64_t>((int64_t)PS_BM * PS_BK * 8, total / (148 * 3) + 1);
+  if (getenv("GB_PSGD_NOSPLIT")) per_item = int64_t(1) << 40;      // debugging: one K chunk per tile
   ntiles = 0;
   for (int mi = 0; mi < (int)mats.size(); ++mi) {
     const PsMat& m = mats[mi];
@@ -617,7 +631,8 @@ extern "C" int gb_psgd_create(gb_comm* c, int nmat, const int64_t* rows, const i
     const float* M = p->d_work + m.off;
     if (make_map(&maps[i * 4 + 0], M, m.m, m.n, m.m, PS_BK, PS_BM)) return -1;
     if (make_map(&maps[i * 4 + 1], p->d_q0t + m.qrow0, m.m, PS_N, p->qpad, PS_BK, PS_N)) return -1;
-    if (make_map(&maps[i * 4 + 2], M, m.m, m.n, m.m, 32, PS_BK)) return -1;
+    if (make_map(&maps[i * 4 + 2], M, m.m, m.n, m.m, 32, PS_BK,
+                 getenv("GB_PSGD_SWZ128") ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return -1;
     if (make_map(&maps[i * 4 + 3], p->d_pht + m.prow0, m.n, PS_N, p->ppad, PS_BK, PS_N)) return -1;
   }
   GB_CUDA(cudaMalloc((void**)&p->d_maps, sizeof(CUtensorMap) * nmat * 4));
@@ -651,6 +666,20 @@ extern "C" int gb_psgd_tc_matrices(gb_psgd* p) { int n = 0; for (auto& m : p->h_
 extern "C" int gb_psgd_get_step(gb_psgd* p, uint32_t* s) { *s = p->step; return 0; }
 extern "C" int gb_psgd_set_step(gb_psgd* p, uint32_t s) { p->step = s; return 0; }
 extern "C" int gb_psgd_residual(gb_psgd* p, void** ptr, size_t* bytes) { *ptr = p->d_res; *bytes = p->d_res ? (size_t)p->padded * 4 : 0; return 0; }
+// debugging / tests: copy an internal buffer out.  what: 0 P accumulator, 1 Q accumulator, 2 Q0^T, 3 P^^T, 4 P^, 5 work
+extern "C" int gb_psgd_peek(gb_psgd* p, int what, float* d_dst, int64_t nfloats, void* stream) {
+  const float* src = what == 0 ? p->d_pacc : what == 1 ? p->d_qacc : what == 2 ? p->d_q0t : what == 3 ? p->d_pht : what == 4 ? p->d_ph : p->d_work;
+  GB_CUDA(cudaMemcpyAsync(d_dst, src, (size_t)nfloats * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int gb_psgd_debug_set(const int* v8) {
+  GB_CUDA(cudaMemcpyToSymbol(g_dbg, v8, 32));
+  return 0;
+}
+extern "C" int gb_psgd_debug_dump(float* h_dst) {
+  GB_CUDA(cudaMemcpyFromSymbol(h_dst, g_dbg_dump, 8192 * 4));
+  return 0;
+}
 extern "C" int64_t gb_psgd_wire_bytes(gb_psgd* p) { return (int64_t)(p->prows + p->qrows) * PS_R * 4; }
 
 static PsPeers peer_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch) {
