@@ -672,6 +672,16 @@ extern "C" int gb_psgd_peek(gb_psgd* p, int what, float* d_dst, int64_t nfloats,
   GB_CUDA(cudaMemcpyAsync(d_dst, src, (size_t)nfloats * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return 0;
 }
+extern "C" int gb_psgd_state_read(gb_psgd* p, void* d_dst, void* stream) {
+  GB_CHECK(p->d_res, "this PowerSGD plan has no residual memory");
+  GB_CUDA(cudaMemcpyAsync(d_dst, p->d_res, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int gb_psgd_state_write(gb_psgd* p, const void* d_src, void* stream) {
+  GB_CHECK(p->d_res, "this PowerSGD plan has no residual memory");
+  GB_CUDA(cudaMemcpyAsync(p->d_res, d_src, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
 extern "C" int gb_psgd_debug_set(const int* v8) {
   GB_CUDA(cudaMemcpyToSymbol(g_dbg, v8, 32));
   return 0;

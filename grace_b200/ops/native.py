@@ -96,6 +96,9 @@ def _declare(L):
         "gb_psgd_set_step": (i32, [vp, u32]),
         "gb_psgd_residual": (i32, [vp, P(vp), P(sz)]),
         "gb_psgd_wire_bytes": (i64, [vp]),
+        "gb_psgd_state_read": (i32, [vp, vp, vp]),
+        "gb_psgd_state_write": (i32, [vp, vp, vp]),
+        "gb_psgd_residual": (i32, [vp, P(vp), P(sz)]),
         "gb_psgd_peek": (i32, [vp, i32, vp, i64, vp]),
         "gb_topk_scratch_bytes": (sz, [i64]),
         "gb_topk_compress": (i32, [vp, i64, i64, vp, vp, vp, sz, vp]),

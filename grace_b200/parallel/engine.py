@@ -220,6 +220,22 @@ class PowerSGDPlan:
         check(native.lib().gb_psgd_launches(self._h, C.byref(out)))
         return out.value
 
+    def get_state(self, which=0):
+        ptr, size = C.c_void_p(), C.c_size_t()
+        check(native.lib().gb_psgd_residual(self._h, C.byref(ptr), C.byref(size)))
+        if which != 0 or not ptr.value:
+            return None
+        out = torch.empty(size.value // 4, dtype=torch.float32, device="cuda")
+        check(native.lib().gb_psgd_state_read(self._h, C.c_void_p(out.data_ptr()), _stream_ptr()))
+        return out
+
+    def set_state(self, which, tensor):
+        if which != 0 or tensor is None:
+            return
+        src = tensor.to(device="cuda", dtype=torch.float32).reshape(-1).contiguous()
+        check(native.lib().gb_psgd_state_write(self._h, C.c_void_p(src.data_ptr()), _stream_ptr()))
+        torch.cuda.current_stream().synchronize()
+
     @property
     def step(self):
         out = C.c_uint32()

@@ -129,29 +129,110 @@ def _native_or_raise():
     return native
 
 
+def _grad_view(chunk, p):
+    """View of a flat chunk with the parameter's own dense memory format, so autograd's in-place
+    accumulation and the optimizer see matching strides (channels_last conv weights)."""
+    if p.dim() == 4 and not p.is_contiguous() and p.is_contiguous(memory_format=torch.channels_last):
+        return chunk.as_strided(p.shape, p.stride())
+    return chunk.view(p.shape)
+
+
 class _Bucket:
+    """Parameters exchanged together through one plan."""
+
     def __init__(self, engine, named_params, params):
         self.names = [n for n, _ in named_params]
         self.tensors = [p for _, p in named_params]
         self.plan = engine.plan([p.numel() for p in self.tensors], self.names, params)
+        self.plans = [self.plan]
         self.flat = torch.zeros(self.plan.padded, dtype=torch.float32, device=self.tensors[0].device)
-        # views follow the parameter's own (dense) memory format so autograd's in-place
-        # accumulation and the optimizer see matching strides (channels_last conv weights)
-        self.views = []
-        for o, p in zip(self.plan.offsets, self.tensors):
-            chunk = self.flat[o:o + p.numel()]
-            if p.dim() == 4 and not p.is_contiguous() and p.is_contiguous(memory_format=torch.channels_last):
-                self.views.append(chunk.as_strided(p.shape, p.stride()))
-            else:
-                self.views.append(chunk.view(p.shape))
+        self.flats = [self.flat]
+        self.views = [_grad_view(self.flat[o:o + p.numel()], p) for o, p in zip(self.plan.offsets, self.tensors)]
         self.pending = len(self.tensors)
         self.sent = False
+
+    def send(self, stream):
+        self.plan.send(self.flat, stream=stream)
+
+    def mid(self, stream):
+        pass
+
+    def recv(self, stream):
+        self.plan.recv(self.flat, stream=stream)
+
+
+class _PowerSGDBucket(_Bucket):
+    """>=2-D gradients go through the native PowerSGD plan (K3), 1-D ones through a dense plan."""
+
+    def __init__(self, engine, named_params, rank, seed, has_memory, use_tc=True):
+        from grace_b200.ops.native import CodecParams, CODEC, MEMORY
+        from grace_b200.parallel.engine import PowerSGDPlan
+        self.names = [n for n, _ in named_params]
+        self.tensors = [p for _, p in named_params]
+        mats = [(n, p) for n, p in named_params if p.dim() >= 2]
+        vecs = [(n, p) for n, p in named_params if p.dim() < 2]
+        dev = self.tensors[0].device
+        self.plans, self.flats = [], []
+        view_of = {}
+        self.psgd = self.dense = None
+        if mats:
+            shapes = [(p.shape[0], p.numel() // p.shape[0]) for _, p in mats]
+            self.psgd = PowerSGDPlan(engine, shapes, [n for n, _ in mats], rank, seed, has_memory, use_tc)
+            self.flat_m = torch.zeros(self.psgd.padded, dtype=torch.float32, device=dev)
+            for off, (n, p) in zip(self.psgd.offsets, mats):
+                view_of[p] = _grad_view(self.flat_m[off:off + p.numel()], p)
+            self.plans.append(self.psgd)
+            self.flats.append(self.flat_m)
+        if vecs:
+            prm = CodecParams()
+            prm.codec, prm.memory, prm.average, prm.beta, prm.gamma = CODEC["none"], MEMORY["none"], 1, 1.0, 1.0
+            self.dense = engine.plan([p.numel() for _, p in vecs], [n for n, _ in vecs], prm)
+            self.flat_v = torch.zeros(self.dense.padded, dtype=torch.float32, device=dev)
+            for off, (n, p) in zip(self.dense.offsets, vecs):
+                view_of[p] = self.flat_v[off:off + p.numel()].view(p.shape)
+            self.plans.append(self.dense)
+            self.flats.append(self.flat_v)
+        self.views = [view_of[p] for p in self.tensors]
+        self.pending = len(self.tensors)
+        self.sent = False
+
+    def send(self, stream):
+        if self.psgd is not None:
+            self.psgd.send(self.flat_m, stream=stream)
+        if self.dense is not None:
+            self.dense.send(self.flat_v, stream=stream)
+
+    def mid(self, stream):
+        if self.psgd is not None:
+            self.psgd.mid(stream=stream)
+
+    def recv(self, stream):
+        if self.psgd is not None:
+            self.psgd.recv(self.flat_m, stream=stream)
+        if self.dense is not None:
+            self.dense.recv(self.flat_v, stream=stream)
+
+
+def powersgd_spec(grace):
+    """(rank, seed, has_memory) when ``grace`` is a natively supported PowerSGD triple, else None."""
+    from grace_b200.compressor.lowrank import RANK_KEY
+    c, m = grace.compressor, grace.memory
+    if type(c) is not C.PowerSGDCompressor or type(grace).__name__ != "Allreduce":
+        return None
+    if not type(grace).__module__.startswith("grace_b200."):
+        return None
+    if c.use_memory or c.warm_start or type(m) not in (M.PowerSGDMemory, M.NoneMemory):
+        return None
+    rank = c.q_memory.get(RANK_KEY, c.rank)
+    if not 1 <= rank <= 4:
+        return None
+    return rank, c.seed, type(m) is M.PowerSGDMemory
 
 
 class FusedDP:
     """Bucketed, overlapped, native gradient exchange behind ``DistributedOptimizer``."""
 
-    def __init__(self, optimizer, grace, named, params, bucket_bytes=None):
+    def __init__(self, optimizer, grace, named, params, bucket_bytes=None, powersgd=None):
         self.grace = grace
         self.engine = get_engine()
         self.passes = optimizer.backward_passes_per_step
@@ -166,10 +247,10 @@ class FusedDP:
             cur.append((n, p))
             cur_bytes += p.numel() * 4
             if cur_bytes >= bucket_bytes:
-                self.buckets.append(_Bucket(self.engine, cur, params))
+                self.buckets.append(self._make_bucket(cur, params, powersgd))
                 cur, cur_bytes = [], 0
         if cur:
-            self.buckets.append(_Bucket(self.engine, cur, params))
+            self.buckets.append(self._make_bucket(cur, params, powersgd))
         self._where: Dict[torch.Tensor, tuple] = {}
         self._countdown: Dict[torch.Tensor, int] = {}
         self._hooks = []
@@ -182,6 +263,13 @@ class FusedDP:
                 self._countdown[p] = self.passes
                 self._hooks.append(p.register_post_accumulate_grad_hook(self._hook))
         self._inflight = False
+
+    def _make_bucket(self, named_params, params, powersgd):
+        if powersgd is not None:
+            rank, seed, has_memory = powersgd
+            return _PowerSGDBucket(self.engine, named_params, rank, seed, has_memory,
+                                   use_tc=os.environ.get("GRACE_B200_PSGD_TCGEN05", "1") != "0")
+        return _Bucket(self.engine, named_params, params)
 
     # ------------------------------------------------------------------ autograd side
     def _hook(self, p):
@@ -205,7 +293,7 @@ class FusedDP:
         ready = torch.cuda.Event()
         ready.record()                                  # on the stream autograd is running on
         self.side.wait_event(ready)
-        b.plan.send(b.flat, stream=self.side)
+        b.send(self.side)
         b.sent = True
 
     # ------------------------------------------------------------------ optimizer side
@@ -215,7 +303,9 @@ class FusedDP:
             if not b.sent:
                 self._send(b)
         for b in self.buckets:
-            b.plan.recv(b.flat, stream=self.side)       # aggregate lands in the same views the optimizer reads
+            b.mid(self.side)                            # PowerSGD only: reduce P, second GEMM, push Q
+        for b in self.buckets:
+            b.recv(self.side)                           # aggregate lands in the same views the optimizer reads
             b.sent = False
             b.pending = len(b.tensors)
         done = torch.cuda.Event()
@@ -230,7 +320,8 @@ class FusedDP:
 
     def zero_grad(self):
         for b in self.buckets:
-            b.flat.zero_()
+            for flat in b.flats:
+                flat.zero_()
             for p, v in zip(b.tensors, b.views):
                 if p.grad is not v:
                     p.grad = v
@@ -241,27 +332,29 @@ class FusedDP:
             self._countdown[p] = passes
 
     def launches(self):
-        return sum(b.plan.launches() for b in self.buckets)
+        return sum(pl.launches() for b in self.buckets for pl in b.plans)
 
     def wire_bytes(self):
         """Bytes this rank stores into each peer per step."""
-        return sum(b.plan.wire_bytes for b in self.buckets)
+        return sum(pl.wire_bytes for b in self.buckets for pl in b.plans)
 
     # ------------------------------------------------------------------ checkpointing
     def state_dict(self):
         torch.cuda.synchronize()
-        return {"buckets": [{"names": b.names, "step": b.plan.step, "state0": b.plan.get_state(0),
-                             "state1": b.plan.get_state(1)} for b in self.buckets]}
+        return {"buckets": [{"names": b.names,
+                             "plans": [{"step": pl.step, "state0": pl.get_state(0), "state1": pl.get_state(1)}
+                                       for pl in b.plans]} for b in self.buckets]}
 
     def load_state_dict(self, state):
         torch.cuda.synchronize()
         for b, s in zip(self.buckets, state["buckets"]):
             if s["names"] != b.names:
                 raise ValueError("bucket layout differs from the checkpoint")
-            b.plan.step = s["step"]
-            for which in (0, 1):
-                if s["state%d" % which] is not None:
-                    b.plan.set_state(which, s["state%d" % which])
+            for pl, ps in zip(b.plans, s["plans"]):
+                pl.step = ps["step"]
+                for which in (0, 1):
+                    if ps["state%d" % which] is not None:
+                        pl.set_state(which, ps["state%d" % which])
 
 
 def try_build_fused(optimizer, grace, named, required=False, bucket_bytes=None) -> Optional[FusedDP]:
@@ -272,7 +365,8 @@ def try_build_fused(optimizer, grace, named, required=False, bucket_bytes=None) 
     elif not all(p.dtype == torch.float32 for p in trainable):
         why = "fused path needs float32 parameters/gradients"
     params = None
-    if why is None:
+    psgd = powersgd_spec(grace) if why is None else None
+    if why is None and psgd is None:
         params = codec_params(grace.compressor, grace.memory)
         if params is None:
             why = "no native kernels for %s + %s" % (type(grace.compressor).__name__, type(grace.memory).__name__)
@@ -283,7 +377,7 @@ def try_build_fused(optimizer, grace, named, required=False, bucket_bytes=None) 
             raise RuntimeError("fused=True but " + why)
         return None
     _native_or_raise()
-    return FusedDP(optimizer, grace, named, params, bucket_bytes)
+    return FusedDP(optimizer, grace, named, params, bucket_bytes, powersgd=psgd)
 
 
 class FusedStepper:

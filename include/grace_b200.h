@@ -130,6 +130,8 @@ int gb_psgd_tc_matrices(gb_psgd* p);          /* how many matrices take the tcge
 int gb_psgd_get_step(gb_psgd* p, uint32_t* step);
 int gb_psgd_set_step(gb_psgd* p, uint32_t step);
 int gb_psgd_residual(gb_psgd* p, void** d_ptr, size_t* bytes);
+int gb_psgd_state_read(gb_psgd* p, void* d_dst, void* stream);    /* residual buffer, padded floats */
+int gb_psgd_state_write(gb_psgd* p, const void* d_src, void* stream);
 int64_t gb_psgd_wire_bytes(gb_psgd* p);
 
 /* ---- stand-alone single-tensor kernels (synchronous API, microbenchmarks) */

@@ -42,6 +42,7 @@ def _manual_reference(params, data):
     (dict(compressor="dgc", memory="dgc", communicator="allgather", compress_ratio=0.05, gradient_clipping=False,
           momentum=0.9), 0.0),
     (dict(compressor="none", memory="none", communicator="allreduce"), 0.0),
+    (dict(compressor="powersgd", memory="powersgd", communicator="allreduce", compress_rank=4), 3e-2),
 ])
 def test_distributed_optimizer_fused_matches_manual_loop(params, tol):
     import grace_b200.torch as hvd
@@ -95,7 +96,7 @@ def test_grad_accumulation_and_state_dict():
             F.nll_loss(model(x), y).backward()
         opt.step()
     state = opt.grace_state_dict()
-    assert state["buckets"][0]["step"] == 2 and state["buckets"][0]["state0"].abs().sum() > 0
+    assert state["buckets"][0]["plans"][0]["step"] == 2 and state["buckets"][0]["plans"][0]["state0"].abs().sum() > 0
     opt.load_grace_state_dict(state)
     with pytest.raises(AssertionError):
         F.nll_loss(model(data[0][0]), data[0][1]).backward()
