@@ -39,6 +39,7 @@ def parse():
     ap.add_argument("--quantum-num", type=int, default=64)
     ap.add_argument("--compress-rank", type=int, default=4)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--memory-format", default="auto", choices=["auto", "channels_last", "contiguous"])
     return ap.parse_args()
 
 
@@ -95,7 +96,15 @@ def build_model(args, device):
     import torch
     import torchvision
     torch.manual_seed(0)
-    model = getattr(torchvision.models, args.model)().to(device).to(memory_format=torch.channels_last)
+    model = getattr(torchvision.models, args.model)().to(device)
+    fmt = args.memory_format
+    if fmt == "auto":
+        # the reference's PowerSGD does tensor.view(shape[0], -1) (compressor/powersgd.py:35), which
+        # cannot take channels_last gradients; every other configuration runs channels_last
+        fmt = "contiguous" if (args.impl == "reference" and args.compressor == "powersgd") else "channels_last"
+    args.memory_format = fmt
+    if fmt == "channels_last":
+        model = model.to(memory_format=torch.channels_last)
     return model
 
 
@@ -184,7 +193,8 @@ def main():
     bs = args.batch_size
     host_x = torch.randn(bs, 3, 224, 224).pin_memory()
     host_y = torch.randint(0, 1000, (bs,)).pin_memory()
-    dev_x = host_x.to(device, non_blocking=True).contiguous(memory_format=torch.channels_last)
+    mf = torch.channels_last if args.memory_format == "channels_last" else torch.contiguous_format
+    dev_x = host_x.to(device, non_blocking=True).contiguous(memory_format=mf)
     dev_y = host_y.to(device, non_blocking=True)
 
     def step(x, y):
@@ -209,7 +219,7 @@ def main():
         last = None
         for _ in range(n):
             if e2e:
-                x = host_x.to(device, non_blocking=True).contiguous(memory_format=torch.channels_last)
+                x = host_x.to(device, non_blocking=True).contiguous(memory_format=mf)
                 y = host_y.to(device, non_blocking=True)
                 last = step(x, y).item()          # device -> host read of the step's result
             else:
@@ -250,7 +260,7 @@ def main():
             "config": {"model": args.model, "global_batch": world * bs, "per_gpu_batch": bs, "seq_len": None,
                        "image": "3x224x224", "parallelism": "dp%d" % world, "compressor": comp, "memory": mem,
                        "communicator": comm, "compress_ratio": args.compress_ratio, "params": n_params,
-                       "grad_dtype": "fp32 master gradients, bf16 autocast compute, channels_last",
+                       "grad_dtype": "fp32 master gradients, bf16 autocast compute", "memory_format": args.memory_format,
                        "optimizer": "SGD momentum 0.9 (inside the timed region)",
                        "l2": "per-step working set (activations, >1 GB) exceeds the 126 MB L2; no explicit flush"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
