@@ -1,0 +1,100 @@
+#!/usr/bin/env python
+"""CIFAR10 DAWNBench-style ResNet-9 with the torch.distributed-style manual loop (workload of the
+reference's ``examples/dist/CIFAR10-dawndist/{dawn,core}.py``): piecewise-linear LR, Nesterov SGD,
+batch 512, after ``backward()`` one ``grc.step(grad, name)`` per parameter.  Synthetic CIFAR-shaped
+data unless ``--data-dir`` holds the real set.
+
+  torchrun --standalone --nproc-per-node 2 examples/dist/cifar10_dawn.py --epochs 2
+"""
+import argparse
+import os
+import sys
+import time
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", ".."))
+from grace_b200.dist import grace_from_params  # noqa: E402
+from grace_b200.models import resnet9  # noqa: E402
+from grace_b200.utils.metrics import TableLogger  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--epochs", type=int, default=24)
+ap.add_argument("--batch-size", type=int, default=512)
+ap.add_argument("--data-dir", default="")
+ap.add_argument("--backend", default="nccl" if torch.cuda.is_available() else "gloo")
+ap.add_argument("--compressor", default="none")
+ap.add_argument("--memory", default="none")
+ap.add_argument("--communicator", default="allreduce")
+ap.add_argument("--compress-ratio", type=float, default=0.01)
+args = ap.parse_args()
+
+rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+if world > 1:
+    dist.init_process_group(args.backend)
+device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))) if torch.cuda.is_available() else torch.device("cpu")
+if device.type == "cuda":
+    torch.cuda.set_device(device)
+torch.manual_seed(0)
+
+
+def load():
+    try:
+        import torchvision
+        tr = torchvision.datasets.CIFAR10(args.data_dir, train=True, download=False)
+        te = torchvision.datasets.CIFAR10(args.data_dir, train=False, download=False)
+        f = lambda d: (torch.tensor(d.data).permute(0, 3, 1, 2).float() / 255, torch.tensor(d.targets))
+        return f(tr), f(te)
+    except Exception:
+        g = torch.Generator().manual_seed(1)
+        def fake(n):
+            y = torch.randint(0, 10, (n,), generator=g)
+            x = torch.rand(n, 3, 32, 32, generator=g) * 0.5
+            for c in range(10):
+                x[y == c, c % 3, 3 * c:3 * c + 5, :] += 0.5
+            return x, y
+        return fake(8192), fake(2048)
+
+
+(train_x, train_y), (test_x, test_y) = load()
+mean, std = train_x.mean((0, 2, 3), keepdim=True), train_x.std((0, 2, 3), keepdim=True)
+train_x, test_x = (train_x - mean) / std, (test_x - mean) / std
+model = resnet9().to(device).to(memory_format=torch.channels_last)
+if world > 1:
+    for p in model.parameters():
+        dist.broadcast(p.data, 0)
+steps_per_epoch = len(train_x) // (args.batch_size * world)
+lr_at = lambda e: max(0.0, (e / 5 if e < 5 else (args.epochs - e) / max(args.epochs - 5, 1))) * 0.4   # piecewise linear
+opt = torch.optim.SGD(model.parameters(), lr=0.0, momentum=0.9, nesterov=True, weight_decay=5e-4 * args.batch_size)
+grc = grace_from_params({"compressor": args.compressor, "memory": args.memory, "communicator": args.communicator,
+                         "compress_ratio": args.compress_ratio, "world_size": world})
+table = TableLogger(rank=rank)
+t0 = time.time()
+for epoch in range(args.epochs):
+    model.train()
+    perm = torch.randperm(len(train_x), generator=torch.Generator().manual_seed(epoch))
+    loss_sum = 0.0
+    for s in range(steps_per_epoch):
+        idx = perm[(s * world + rank) * args.batch_size:(s * world + rank + 1) * args.batch_size]
+        x = train_x[idx].to(device).contiguous(memory_format=torch.channels_last)
+        y = train_y[idx].to(device)
+        for g in opt.param_groups:
+            g["lr"] = lr_at(epoch + s / steps_per_epoch) / args.batch_size
+        opt.zero_grad(set_to_none=False)
+        with torch.autocast(device.type, dtype=torch.bfloat16, enabled=device.type == "cuda"):
+            loss = F.cross_entropy(model(x), y, reduction="sum")
+        loss.backward()
+        for name, p in model.named_parameters():               # the reference's sequential exchange loop
+            p.grad.copy_(grc.step(p.grad, name))
+        opt.step()
+        loss_sum += float(loss)
+    model.eval()
+    with torch.no_grad():
+        correct = sum(int((model(test_x[i:i + 1000].to(device)).argmax(1) == test_y[i:i + 1000].to(device)).sum())
+                      for i in range(0, len(test_x), 1000))
+    table.append({"epoch": epoch + 1, "lr": lr_at(epoch + 1), "train_loss": loss_sum / (steps_per_epoch * args.batch_size),
+                  "test_acc": correct / len(test_x), "total_time": time.time() - t0})
+if world > 1:
+    dist.destroy_process_group()

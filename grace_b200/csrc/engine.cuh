@@ -60,6 +60,9 @@ struct gb_plan {
   uint32_t* d_done;      // last-block-done counters
   // wire
   int channel;
+  int channel2;          // K0 only: flags of the second (gather) phase
+  uint32_t mid_epoch;    // K0 only: epoch whose reduce phase has been enqueued
+  bool dense2;           // K0 two-shot path active (None/FP16 codec, world > 1)
   size_t chan_off, slot_bytes;
   size_t hdr_bytes;      // per-slot header (counts / stats)
   int bits;              // quantiser bits per element

@@ -11,6 +11,12 @@ int k1_recv(gb_plan* p, float* d_out, cudaStream_t st);
 int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 int k2_recv(gb_plan* p, float* d_out, cudaStream_t st);
 
+// K0: dense two-shot all-reduce over peer memory (None / FP16 codecs, world > 1)
+int k0_send(gb_plan* p, const float* d_grad, cudaStream_t st);
+int k0_mid(gb_plan* p, cudaStream_t st);
+int k0_recv(gb_plan* p, float* d_out, cudaStream_t st);
+size_t k0_slot_bytes(int64_t padded, int world, int bits);
+
 // Last-block-done flag release shared by the send kernels: every CTA calls this after its
 // final peer store; the CTA that arrives last publishes `epoch` to all peers.
 __device__ __forceinline__ void release_flags_last_block(uint32_t* done, PeerPtrs peers, int channel, uint32_t epoch) {

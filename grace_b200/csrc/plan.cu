@@ -8,6 +8,8 @@
 #include "engine.cuh"
 #include "kernels.cuh"
 
+#include <stdlib.h>
+
 #include <algorithm>
 
 static int quant_bits(const gb_codec_params& p) {
@@ -141,7 +143,16 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
     p->hdr_bytes = ((size_t)nseg * 4 * 4 + 255) & ~size_t(255);
     p->slot_bytes = p->hdr_bytes + (((size_t)p->padded * p->bits / 8 + 255) & ~size_t(255));
   }
+  p->channel2 = 0;
+  p->mid_epoch = 0;
+  p->dense2 = (params->codec == GB_CODEC_NONE || params->codec == GB_CODEC_FP16) && c->world > 1 && !getenv("GRACE_B200_NO_K0");
+  if (p->dense2) p->slot_bytes = k0_slot_bytes(p->padded, c->world, p->bits);
   if (gb_comm_alloc_channel(c, p->slot_bytes, &p->channel, &p->chan_off)) { gb_plan_destroy(p); return -1; }
+  if (p->dense2) {
+    // second flag channel for the gather phase (no payload of its own)
+    size_t unused;
+    if (gb_comm_alloc_channel(c, 0, &p->channel2, &unused)) { gb_plan_destroy(p); return -1; }
+  }
   p->slot_bytes = (p->slot_bytes + 255) & ~size_t(255);
   GB_CUDA(cudaDeviceSynchronize());
   *out = p;
@@ -191,7 +202,7 @@ extern "C" int gb_plan_launches(gb_plan* p, int64_t* out) { *out = p->launches; 
 
 extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  int rc = gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
+  int rc = p->dense2 ? k0_send(p, d_grad, st) : gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
   if (rc) return rc;
   p->step++;
   return 0;
@@ -200,5 +211,14 @@ extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
 extern "C" int gb_plan_recv(gb_plan* p, float* d_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   GB_CHECK(p->epoch > 0, "gb_plan_recv before any gb_plan_send");
+  if (p->dense2) return k0_recv(p, d_out, st);
   return gb_codec_is_sparse(p->prm.codec) ? k1_recv(p, d_out, st) : k2_recv(p, d_out, st);
+}
+
+// Optional middle phase (only the dense two-shot path has one): lets a caller enqueue every
+// bucket's reduce before any bucket's gather.  gb_plan_recv runs it itself when skipped.
+extern "C" int gb_plan_mid(gb_plan* p, void* stream) {
+  if (!p->dense2) return 0;
+  GB_CHECK(p->epoch > 0, "gb_plan_mid before any gb_plan_send");
+  return k0_mid(p, (cudaStream_t)stream);
 }

@@ -128,6 +128,9 @@ class Plan:
         assert grad.is_cuda and grad.dtype == torch.float32 and grad.numel() >= self.padded
         check(native.lib().gb_plan_send(self._h, C.c_void_p(grad.data_ptr()), _stream_ptr(stream)))
 
+    def mid(self, stream=None):
+        check(native.lib().gb_plan_mid(self._h, _stream_ptr(stream)))
+
     def recv(self, out: torch.Tensor, stream=None):
         assert out.is_cuda and out.dtype == torch.float32 and out.numel() >= self.padded
         check(native.lib().gb_plan_recv(self._h, C.c_void_p(out.data_ptr()), _stream_ptr(stream)))

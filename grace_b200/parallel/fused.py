@@ -155,7 +155,7 @@ class _Bucket:
         self.plan.send(self.flat, stream=stream)
 
     def mid(self, stream):
-        pass
+        self.plan.mid(stream=stream)
 
     def recv(self, stream):
         self.plan.recv(self.flat, stream=stream)
@@ -205,6 +205,8 @@ class _PowerSGDBucket(_Bucket):
     def mid(self, stream):
         if self.psgd is not None:
             self.psgd.mid(stream=stream)
+        if self.dense is not None:
+            self.dense.mid(stream=stream)
 
     def recv(self, stream):
         if self.psgd is not None:

@@ -99,6 +99,9 @@ int gb_plan_offsets(gb_plan* p, int64_t* out /* [nseg] element offsets into the 
 int64_t gb_plan_wire_bytes(gb_plan* p);        /* payload bytes one rank sends to one peer */
 /* compensate + compress + store into every peer's slot + release flags */
 int gb_plan_send(gb_plan* p, const float* d_grad, void* stream);
+/* optional middle phase: the dense two-shot all-reduce (None/FP16 codec, world > 1) reduces its shard
+ * here; a no-op for every other codec; gb_plan_recv runs it itself if the caller did not */
+int gb_plan_mid(gb_plan* p, void* stream);
 /* wait for all ranks' flags, decode, aggregate; writes every element of d_out exactly once */
 int gb_plan_recv(gb_plan* p, float* d_out, void* stream);
 /* state access for state_dict(): which = 0 residual / dgc v, 1 momentum / dgc u */

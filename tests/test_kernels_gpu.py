@@ -54,6 +54,8 @@ def run_fused(world, params, grads_per_step):
             bufs = [_flat(plans[r], grads[r]) for r in range(world)]
             for r in range(world):
                 plans[r].send(bufs[r])
+            for r in range(world):
+                plans[r].mid()
             res = []
             for r in range(world):
                 out = torch.full((plans[r].padded,), float("nan"), device="cuda")
