@@ -120,9 +120,11 @@ def main():
     else:
         sys.path.insert(0, ROOT)
 
-    # keep stdout to the single JSON line: NCCL prints its version banner there at VERSION level
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # keep the real stdout for the single JSON line: libraries (NCCL's version banner, torchrun
+    # notices) write to fd 1, so everything else is diverted to stderr
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     import torch
     import torch.distributed as dist
@@ -268,7 +270,8 @@ def main():
         if fused is not None:
             out["config"]["buckets"] = len(fused.buckets)
             out["config"]["wire_bytes_per_peer_per_step"] = fused.wire_bytes()
-        print(json.dumps(out))
+        real_stdout.write(json.dumps(out) + "\n")
+        real_stdout.flush()
     if dist.is_initialized():
         dist.destroy_process_group()
     return 0

@@ -45,8 +45,12 @@ def main():
                 g = torch.randn(shape, device="cuda", generator=gen) * (0.02 if not exact else 1.0)
                 a = fast.step(g.clone(), name).clone()
                 b = slow.step(g.clone(), name)
-                if exact:
+                if exact and (comm != "allreduce" or world <= 2):
                     ok = torch.equal(a, b)
+                elif exact:
+                    # the generic all-reduce path sums in NCCL's ring/tree order, the native path in
+                    # rank order: equal up to rounding once more than two ranks contribute
+                    ok = torch.allclose(a, b, rtol=1e-5, atol=1e-6)
                 else:
                     ok = float(((a - b).abs() > 1e-7 + 2e-5 * b.abs()).float().mean()) < 0.003
                 if not ok:
