@@ -115,9 +115,13 @@ __global__ void __launch_bounds__(GB_THREADS) k1_hist(SegTable t, const float* _
 
 // One CTA per segment: walk the histogram from the top bin down to the bin holding the
 // k-th largest magnitude; extend the prefix, update k_remaining, re-zero the histogram.
-__global__ void __launch_bounds__(GB_THREADS) k1_select(SegTable t, uint32_t* hist, uint32_t* sel, int round) {
+// Round 2 also (a) clears the segment's payload cursor sel[seg][2] and (b) raises *tieflag when the
+// number of elements equal to the threshold differs from the number still to take: only then does
+// the choice among equal magnitudes matter and the index-ordered (slow) compaction run.
+__global__ void __launch_bounds__(GB_THREADS) k1_select(SegTable t, uint32_t* hist, uint32_t* sel, int round, uint32_t* tieflag) {
   __shared__ uint32_t part[GB_THREADS];
   const int seg = blockIdx.x;
+  if (round == 0 && seg == 0 && threadIdx.x == 0) *tieflag = 0;
   const int nb = round == 0 ? 2048 : 1024;
   const int per = nb / GB_THREADS;
   uint32_t* h = hist + (size_t)seg * 2048;
@@ -141,6 +145,10 @@ __global__ void __launch_bounds__(GB_THREADS) k1_select(SegTable t, uint32_t* hi
       const uint32_t bin = (uint32_t)(hi - i);
       sel[seg * 4] = round == 0 ? bin : ((prefix << 10) | bin);
       sel[seg * 4 + 1] = k_rem - running;           // still to take inside this bin
+      if (round == 2) {
+        sel[seg * 4 + 2] = 0;
+        if (c[i] != k_rem - running) atomicOr(tieflag, 1u);
+      }
     }
     running += c[i];
   }
@@ -159,8 +167,9 @@ __device__ __forceinline__ int block_sum_i(int v, int* sh) {
 // per tile: how many magnitudes are above / equal to the segment threshold
 __global__ void __launch_bounds__(GB_THREADS) k1_count(SegTable t, const float* __restrict__ work,
                                                        const uint32_t* __restrict__ sel, uint32_t fixed_thr, int use_fixed,
-                                                       int ge, int32_t* tilecnt) {
+                                                       int ge, int32_t* tilecnt, const uint32_t* tieflag) {
   __shared__ int sh[GB_THREADS / 32];
+  if (tieflag && *tieflag == 0) return;            // no tie ambiguity: k1_emit_fast does the whole job
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
@@ -191,8 +200,10 @@ __global__ void __launch_bounds__(GB_THREADS) k1_count(SegTable t, const float* 
 // segment's fixed payload base (TopK).  Otherwise one CTA scans the whole bucket (variable-size).
 // Output per tile: {first payload position, number of threshold ties before this tile}.
 template <bool PER_SEGMENT>
-__global__ void __launch_bounds__(GB_THREADS) k1_scan(SegTable t, const uint32_t* __restrict__ sel, int32_t* tilecnt) {
+__global__ void __launch_bounds__(GB_THREADS) k1_scan(SegTable t, const uint32_t* __restrict__ sel, int32_t* tilecnt,
+                                                      const uint32_t* tieflag) {
   __shared__ int sg[GB_THREADS], se[GB_THREADS];
+  if (tieflag && *tieflag == 0) return;
   const int seg = blockIdx.x;
   const int first = PER_SEGMENT ? t.seg_tile0[seg] : 0;
   const int last = PER_SEGMENT ? t.seg_tile0[seg + 1] : t.ntiles;
@@ -254,8 +265,10 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit(SegTable t, float* work, f
                                                       uint32_t fixed_thr, int use_fixed, int ge,
                                                       const int32_t* __restrict__ tilecnt,
                                                       SparseOut out, int64_t capacity, uint32_t* status, uint32_t* done,
-                                                      PeerPtrs peers, int channel, uint32_t epoch, int release) {
+                                                      PeerPtrs peers, int channel, uint32_t epoch, int release,
+                                                      const uint32_t* tieflag) {
   __shared__ int sh[GB_THREADS / 32];
+  if (tieflag && *tieflag == 0) return;
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
@@ -331,6 +344,95 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit(SegTable t, float* work, f
     }
   }
   if (release) release_flags_last_block(done, peers, channel, epoch);
+}
+
+// Unordered, single-pass compaction (the common case: no ambiguity among equal magnitudes).
+// Per tile: ballot-compact the picked (value, index) pairs into shared memory, claim a range of the
+// payload with one atomicAdd (per-segment cursor for TopK, one global cursor for the variable-size
+// codecs), then copy the staged pairs to every peer with coalesced stores.  The receiver only needs
+// the per-tile {begin, count} header, so neither the order of tiles in the payload nor the order
+// inside a tile matters for the (deterministic) dense result.
+template <bool ZERO>
+__global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* work, float* work2, uint32_t* sel, uint32_t fixed_thr,
+                                                           int use_fixed, int per_segment, uint32_t* cursor, SparseOut out,
+                                                           int64_t capacity, uint32_t* status, uint32_t* done, PeerPtrs peers,
+                                                           int channel, uint32_t epoch, const uint32_t* tieflag) {
+  __shared__ float sval[GB_TILE];
+  __shared__ int32_t sidx[GB_TILE];
+  __shared__ int scount, sbegin;
+  if (tieflag && *tieflag != 0) return;            // ties matter: the ordered kernels take over (and release)
+  const int lane = threadIdx.x & 31;
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    const uint32_t thr = use_fixed ? fixed_thr : sel[seg * 4];
+    if (threadIdx.x == 0) scount = 0;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (e0 < len) v = load4(work + base, e0, len);
+      float vv[4] = {v.x, v.y, v.z, v.w};
+      bool changed = false;
+      bool pk[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t b = absbits(vv[q]);
+        // TopK (per_segment): >= threshold; Threshold codec: > fixed; DGC: >= per-segment threshold
+        const bool pick = (e0 + q < len) && (use_fixed ? (b > thr) : (b >= thr));
+        pk[q] = pick;
+        const uint32_t mask = __ballot_sync(0xffffffffu, pick);
+        if (mask) {
+          int wbase = 0;
+          if (lane == 0) wbase = atomicAdd(&scount, __popc(mask));
+          wbase = __shfl_sync(0xffffffffu, wbase, 0);
+          if (pick) {
+            const int pos = wbase + __popc(mask & ((1u << lane) - 1u));
+            sval[pos] = vv[q];
+            sidx[pos] = local0 + e0 + q;
+            vv[q] = 0.f;
+            changed = true;
+          }
+        }
+      }
+      if (ZERO && changed) {
+        store4(work + base, e0, len, make_float4(vv[0], vv[1], vv[2], vv[3]));
+        if (work2) {
+          float4 u = load4(work2 + base, e0, len);
+          if (pk[0]) u.x = 0.f;
+          if (pk[1]) u.y = 0.f;
+          if (pk[2]) u.z = 0.f;
+          if (pk[3]) u.w = 0.f;
+          store4(work2 + base, e0, len, u);
+        }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int cnt = scount;
+      int64_t begin;
+      if (per_segment) begin = t.seg_kbase[seg] + atomicAdd(&sel[seg * 4 + 2], (uint32_t)cnt);
+      else begin = atomicAdd(cursor, (uint32_t)cnt);
+      if (begin + cnt > capacity) {
+        atomicOr(status, GB_STATUS_OVERFLOW);
+        cnt = (int)max((int64_t)0, capacity - begin);
+        scount = cnt;
+      }
+      sbegin = (int)begin;
+      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = make_int2((int)begin, cnt);
+    }
+    __syncthreads();
+    const int cnt = scount, begin = sbegin;
+    for (int r = 0; r < out.n; ++r) {
+      float* dv = out.vals[r] + begin;
+      int32_t* di = out.idx[r] + begin;
+      for (int i = threadIdx.x; i < cnt; i += GB_THREADS) { dv[i] = sval[i]; di[i] = sidx[i]; }
+    }
+    __syncthreads();
+  }
+  release_flags_last_block(done, peers, channel, epoch);
 }
 
 // Receive: ordered merge of W sparse lists into the dense aggregate.
@@ -486,24 +588,33 @@ int k1_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   uint32_t thr_bits = 0u;
   if (fixed) { const float th = p->prm.threshold < 0.f ? 0.f : p->prm.threshold; memcpy(&thr_bits, &th, 4); }
   const int hgrid = std::min(p->ntiles, 148 * 4);
+  uint32_t* tieflag = p->d_done + 1;
+  uint32_t* cursor = p->d_done + 2;
   if (fixed) {
+    // variable-size payload: one global cursor, a single compaction pass
     if (mem) { k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma); LAUNCHED(p); }
-  } else {
-    if (mem) k1_hist<0, true><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel);
-    else k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel);
+    GB_CUDA(cudaMemsetAsync(cursor, 0, 4, st));
+    if (mem) k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, 1, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, nullptr);
+    else k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, 1, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, nullptr);
     LAUNCHED(p);
-    k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 0); LAUNCHED(p);
-    k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel); LAUNCHED(p);
-    k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 1); LAUNCHED(p);
-    k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel); LAUNCHED(p);
-    k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 2); LAUNCHED(p);
+    return 0;
   }
-  k1_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel, thr_bits, fixed, 0, p->d_tilecnt); LAUNCHED(p);
-  if (fixed) k1_scan<false><<<1, GB_THREADS, 0, st>>>(p->tab, p->d_sel, p->d_tilecnt);
-  else k1_scan<true><<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_sel, p->d_tilecnt);
+  if (mem) k1_hist<0, true><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel);
+  else k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel);
   LAUNCHED(p);
-  if (mem) k1_emit<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, fixed, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
-  else k1_emit<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, fixed, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+  k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 0, tieflag); LAUNCHED(p);
+  k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel); LAUNCHED(p);
+  k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 1, tieflag); LAUNCHED(p);
+  k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel); LAUNCHED(p);
+  k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 2, tieflag); LAUNCHED(p);
+  // common case: one unordered compaction pass; with threshold ties: count / scan / ordered emit
+  if (mem) k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 1, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, tieflag);
+  else k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 1, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, tieflag);
+  LAUNCHED(p);
+  k1_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel, 0u, 0, 0, p->d_tilecnt, tieflag); LAUNCHED(p);
+  k1_scan<true><<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_sel, p->d_tilecnt, tieflag); LAUNCHED(p);
+  if (mem) k1_emit<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1, tieflag);
+  else k1_emit<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1, tieflag);
   LAUNCHED(p);
   return 0;
 }
@@ -662,12 +773,12 @@ static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
     k1_dgc_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel); LAUNCHED(p);
     k1_dgc_adjust<<<(p->nseg + 127) / 128, 128, 0, st>>>(p->tab, p->prm.ratio, p->d_sel); LAUNCHED(p);
   }
-  k1_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel, 0u, 0, 1, p->d_tilecnt); LAUNCHED(p);
-  k1_scan<false><<<1, GB_THREADS, 0, st>>>(p->tab, p->d_sel, p->d_tilecnt); LAUNCHED(p);
+  uint32_t* cursor = p->d_done + 2;
+  GB_CUDA(cudaMemsetAsync(cursor, 0, 4, st));
   if (p->prm.memory != GB_MEM_NONE)
-    k1_emit<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 1, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+    k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, nullptr);
   else
-    k1_emit<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 1, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+    k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, nullptr);
   LAUNCHED(p);
   return 0;
 }
@@ -737,13 +848,13 @@ int k1_topk_single(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_
   float* work = const_cast<float*>(d_x);
   const int hgrid = std::min(L.ntiles, 148 * 4), grid = grid_for(L.ntiles);
   k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
-  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 0);
+  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 0, sel + 3);
   k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
-  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 1);
+  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 1, sel + 3);
   k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
-  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 2);
-  k1_count<<<grid, GB_THREADS, 0, st>>>(t, work, sel, 0u, 0, 0, cnt);
-  k1_scan<true><<<1, GB_THREADS, 0, st>>>(t, sel, cnt);
+  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 2, sel + 3);
+  k1_count<<<grid, GB_THREADS, 0, st>>>(t, work, sel, 0u, 0, 0, cnt, nullptr);
+  k1_scan<true><<<1, GB_THREADS, 0, st>>>(t, sel, cnt, nullptr);
   SparseOut out;
   out.n = 1;
   out.vals[0] = d_vals;
@@ -751,7 +862,7 @@ int k1_topk_single(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_
   out.hdr[0] = (int2*)(scratch + L.off_hdr);
   PeerPtrs none;
   memset(&none, 0, sizeof(none));
-  k1_emit<false><<<grid, GB_THREADS, 0, st>>>(t, work, nullptr, sel, 0u, 0, 0, cnt, out, k, (uint32_t*)(scratch + L.off_sel) + 3, nullptr, none, 0, 0, 0);
+  k1_emit<false><<<grid, GB_THREADS, 0, st>>>(t, work, nullptr, sel, 0u, 0, 0, cnt, out, k, (uint32_t*)(scratch + L.off_sel) + 3, nullptr, none, 0, 0, 0, nullptr);
   GB_CUDA(cudaGetLastError());
   return 0;
 }
