@@ -115,13 +115,13 @@ __global__ void __launch_bounds__(GB_THREADS) k1_hist(SegTable t, const float* _
 
 // One CTA per segment: walk the histogram from the top bin down to the bin holding the
 // k-th largest magnitude; extend the prefix, update k_remaining, re-zero the histogram.
-// Round 2 also (a) clears the segment's payload cursor sel[seg][2] and (b) raises *tieflag when the
-// number of elements equal to the threshold differs from the number still to take: only then does
-// the choice among equal magnitudes matter and the index-ordered (slow) compaction run.
-__global__ void __launch_bounds__(GB_THREADS) k1_select(SegTable t, uint32_t* hist, uint32_t* sel, int round, uint32_t* tieflag) {
+// Round 2 also clears the segment's payload cursor sel[seg][2] and sets sel[seg][3] = 1 when the
+// number of elements equal to the threshold differs from the number still to take: only for such a
+// segment does the choice among equal magnitudes matter, and only its tiles go through the
+// index-ordered (count / scan / emit) compaction; every other segment is done by k1_emit_fast.
+__global__ void __launch_bounds__(GB_THREADS) k1_select(SegTable t, uint32_t* hist, uint32_t* sel, int round) {
   __shared__ uint32_t part[GB_THREADS];
   const int seg = blockIdx.x;
-  if (round == 0 && seg == 0 && threadIdx.x == 0) *tieflag = 0;
   const int nb = round == 0 ? 2048 : 1024;
   const int per = nb / GB_THREADS;
   uint32_t* h = hist + (size_t)seg * 2048;
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(GB_THREADS) k1_select(SegTable t, uint32_t* hi
       sel[seg * 4 + 1] = k_rem - running;           // still to take inside this bin
       if (round == 2) {
         sel[seg * 4 + 2] = 0;
-        if (c[i] != k_rem - running) atomicOr(tieflag, 1u);
+        sel[seg * 4 + 3] = (c[i] != k_rem - running) ? 1u : 0u;
       }
     }
     running += c[i];
@@ -167,13 +167,13 @@ __device__ __forceinline__ int block_sum_i(int v, int* sh) {
 // per tile: how many magnitudes are above / equal to the segment threshold
 __global__ void __launch_bounds__(GB_THREADS) k1_count(SegTable t, const float* __restrict__ work,
                                                        const uint32_t* __restrict__ sel, uint32_t fixed_thr, int use_fixed,
-                                                       int ge, int32_t* tilecnt, const uint32_t* tieflag) {
+                                                       int ge, int32_t* tilecnt, int only_ambiguous) {
   __shared__ int sh[GB_THREADS / 32];
-  if (tieflag && *tieflag == 0) return;            // no tie ambiguity: k1_emit_fast does the whole job
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
+    if (only_ambiguous && sel[seg * 4 + 3] == 0) continue;      // k1_emit_fast owns this segment
     const uint32_t thr = use_fixed ? fixed_thr : sel[seg * 4];
     int gt = 0, eq = 0;
 #pragma unroll
@@ -201,9 +201,9 @@ __global__ void __launch_bounds__(GB_THREADS) k1_count(SegTable t, const float* 
 // Output per tile: {first payload position, number of threshold ties before this tile}.
 template <bool PER_SEGMENT>
 __global__ void __launch_bounds__(GB_THREADS) k1_scan(SegTable t, const uint32_t* __restrict__ sel, int32_t* tilecnt,
-                                                      const uint32_t* tieflag) {
+                                                      int only_ambiguous) {
   __shared__ int sg[GB_THREADS], se[GB_THREADS];
-  if (tieflag && *tieflag == 0) return;
+  if (PER_SEGMENT && only_ambiguous && sel[blockIdx.x * 4 + 3] == 0) return;
   const int seg = blockIdx.x;
   const int first = PER_SEGMENT ? t.seg_tile0[seg] : 0;
   const int last = PER_SEGMENT ? t.seg_tile0[seg + 1] : t.ntiles;
@@ -266,13 +266,13 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit(SegTable t, float* work, f
                                                       const int32_t* __restrict__ tilecnt,
                                                       SparseOut out, int64_t capacity, uint32_t* status, uint32_t* done,
                                                       PeerPtrs peers, int channel, uint32_t epoch, int release,
-                                                      const uint32_t* tieflag) {
+                                                      int only_ambiguous) {
   __shared__ int sh[GB_THREADS / 32];
-  if (tieflag && *tieflag == 0) return;
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
+    if (only_ambiguous && sel[seg * 4 + 3] == 0) continue;
     const uint32_t thr = use_fixed ? fixed_thr : sel[seg * 4];
     const int take = use_fixed ? 0 : (int)sel[seg * 4 + 1];
     const int begin = tilecnt[tile * 2];
@@ -356,16 +356,16 @@ template <bool ZERO>
 __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* work, float* work2, uint32_t* sel, uint32_t fixed_thr,
                                                            int use_fixed, int per_segment, uint32_t* cursor, SparseOut out,
                                                            int64_t capacity, uint32_t* status, uint32_t* done, PeerPtrs peers,
-                                                           int channel, uint32_t epoch, const uint32_t* tieflag) {
+                                                           int channel, uint32_t epoch, int release) {
   __shared__ float sval[GB_TILE];
   __shared__ int32_t sidx[GB_TILE];
   __shared__ int scount, sbegin;
-  if (tieflag && *tieflag != 0) return;            // ties matter: the ordered kernels take over (and release)
   const int lane = threadIdx.x & 31;
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
+    if (per_segment && sel[seg * 4 + 3] != 0) continue;          // ambiguous ties: ordered kernels do this segment
     const uint32_t thr = use_fixed ? fixed_thr : sel[seg * 4];
     if (threadIdx.x == 0) scount = 0;
     __syncthreads();
@@ -432,7 +432,7 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* wo
     }
     __syncthreads();
   }
-  release_flags_last_block(done, peers, channel, epoch);
+  if (release) release_flags_last_block(done, peers, channel, epoch);
 }
 
 // Receive: ordered merge of W sparse lists into the dense aggregate.
@@ -588,33 +588,33 @@ int k1_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   uint32_t thr_bits = 0u;
   if (fixed) { const float th = p->prm.threshold < 0.f ? 0.f : p->prm.threshold; memcpy(&thr_bits, &th, 4); }
   const int hgrid = std::min(p->ntiles, 148 * 4);
-  uint32_t* tieflag = p->d_done + 1;
   uint32_t* cursor = p->d_done + 2;
   if (fixed) {
     // variable-size payload: one global cursor, a single compaction pass
     if (mem) { k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma); LAUNCHED(p); }
     GB_CUDA(cudaMemsetAsync(cursor, 0, 4, st));
-    if (mem) k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, 1, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, nullptr);
-    else k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, 1, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, nullptr);
+    if (mem) k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, 1, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+    else k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, 1, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
     LAUNCHED(p);
     return 0;
   }
   if (mem) k1_hist<0, true><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel);
   else k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel);
   LAUNCHED(p);
-  k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 0, tieflag); LAUNCHED(p);
+  k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 0); LAUNCHED(p);
   k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel); LAUNCHED(p);
-  k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 1, tieflag); LAUNCHED(p);
+  k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 1); LAUNCHED(p);
   k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel); LAUNCHED(p);
-  k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 2, tieflag); LAUNCHED(p);
-  // common case: one unordered compaction pass; with threshold ties: count / scan / ordered emit
-  if (mem) k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 1, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, tieflag);
-  else k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 1, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, tieflag);
+  k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 2); LAUNCHED(p);
+  // segments without tie ambiguity (nearly all): one unordered compaction pass; the others: count /
+  // scan / index-ordered emit restricted to their tiles.  The last kernel releases the flags.
+  if (mem) k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 1, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 0);
+  else k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 1, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 0);
   LAUNCHED(p);
-  k1_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel, 0u, 0, 0, p->d_tilecnt, tieflag); LAUNCHED(p);
-  k1_scan<true><<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_sel, p->d_tilecnt, tieflag); LAUNCHED(p);
-  if (mem) k1_emit<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1, tieflag);
-  else k1_emit<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1, tieflag);
+  k1_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel, 0u, 0, 0, p->d_tilecnt, 1); LAUNCHED(p);
+  k1_scan<true><<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_sel, p->d_tilecnt, 1); LAUNCHED(p);
+  if (mem) k1_emit<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1, 1);
+  else k1_emit<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1, 1);
   LAUNCHED(p);
   return 0;
 }
@@ -776,9 +776,9 @@ static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   uint32_t* cursor = p->d_done + 2;
   GB_CUDA(cudaMemsetAsync(cursor, 0, 4, st));
   if (p->prm.memory != GB_MEM_NONE)
-    k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, nullptr);
+    k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
   else
-    k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, nullptr);
+    k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
   LAUNCHED(p);
   return 0;
 }
@@ -848,13 +848,13 @@ int k1_topk_single(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_
   float* work = const_cast<float*>(d_x);
   const int hgrid = std::min(L.ntiles, 148 * 4), grid = grid_for(L.ntiles);
   k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
-  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 0, sel + 3);
+  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 0);
   k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
-  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 1, sel + 3);
+  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 1);
   k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
-  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 2, sel + 3);
-  k1_count<<<grid, GB_THREADS, 0, st>>>(t, work, sel, 0u, 0, 0, cnt, nullptr);
-  k1_scan<true><<<1, GB_THREADS, 0, st>>>(t, sel, cnt, nullptr);
+  k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 2);
+  k1_count<<<grid, GB_THREADS, 0, st>>>(t, work, sel, 0u, 0, 0, cnt, 0);
+  k1_scan<true><<<1, GB_THREADS, 0, st>>>(t, sel, cnt, 0);
   SparseOut out;
   out.n = 1;
   out.vals[0] = d_vals;
@@ -862,7 +862,7 @@ int k1_topk_single(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_
   out.hdr[0] = (int2*)(scratch + L.off_hdr);
   PeerPtrs none;
   memset(&none, 0, sizeof(none));
-  k1_emit<false><<<grid, GB_THREADS, 0, st>>>(t, work, nullptr, sel, 0u, 0, 0, cnt, out, k, (uint32_t*)(scratch + L.off_sel) + 3, nullptr, none, 0, 0, 0, nullptr);
+  k1_emit<false><<<grid, GB_THREADS, 0, st>>>(t, work, nullptr, sel, 0u, 0, 0, cnt, out, k, (uint32_t*)(scratch + L.off_sel) + 2, nullptr, none, 0, 0, 0, 0);
   GB_CUDA(cudaGetLastError());
   return 0;
 }

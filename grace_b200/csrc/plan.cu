@@ -145,7 +145,8 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   }
   p->channel2 = 0;
   p->mid_epoch = 0;
-  p->dense2 = (params->codec == GB_CODEC_NONE || params->codec == GB_CODEC_FP16) && c->world > 1 && !getenv("GRACE_B200_NO_K0");
+  p->dense2 = (params->codec == GB_CODEC_NONE || params->codec == GB_CODEC_FP16) && params->memory == GB_MEM_NONE &&
+              c->world > 1 && !getenv("GRACE_B200_NO_K0");   // with a residual memory the K2 path keeps the state
   if (p->dense2) p->slot_bytes = k0_slot_bytes(p->padded, c->world, p->bits);
   if (gb_comm_alloc_channel(c, p->slot_bytes, &p->channel, &p->chan_off)) { gb_plan_destroy(p); return -1; }
   if (p->dense2) {
