@@ -57,7 +57,7 @@ __device__ __forceinline__ void flush_hist(uint32_t* sh, uint32_t* dst, int nbin
 // ROUND 0: compensate (+ write) and histogram bits[30:20].  ROUND 1/2: histogram the next 10
 // bits of the elements whose leading bits equal the prefix chosen so far.
 template <int ROUND, bool WRITE>
-__global__ void __launch_bounds__(GB_THREADS) k1_hist(SegTable t, const float* __restrict__ grad, float* work, float beta,
+__global__ void __launch_bounds__(GB_THREADS, 8) k1_hist(SegTable t, const float* __restrict__ grad, float* work, float beta,
                                                       float gamma, uint32_t* hist, const uint32_t* __restrict__ sel) {
   constexpr int NB = ROUND == 0 ? 2048 : 1024;
   __shared__ uint32_t sh[NB];
@@ -369,66 +369,91 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* wo
     const uint32_t thr = use_fixed ? fixed_thr : sel[seg * 4];
     if (threadIdx.x == 0) scount = 0;
     __syncthreads();
+    // all 16 values of this thread stay in registers; one warp prefix sum and one shared-memory
+    // atomic per warp and tile place the picked pairs in the staging buffers
+    float vv[4][4];
+    uint32_t picks = 0;
+    int cnt = 0;
 #pragma unroll
     for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
       const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (e0 < len) v = load4(work + base, e0, len);
-      float vv[4] = {v.x, v.y, v.z, v.w};
-      bool changed = false;
-      bool pk[4];
+      vv[j][0] = v.x; vv[j][1] = v.y; vv[j][2] = v.z; vv[j][3] = v.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const uint32_t b = absbits(vv[q]);
-        // TopK (per_segment): >= threshold; Threshold codec: > fixed; DGC: >= per-segment threshold
+        const uint32_t b = absbits(vv[j][q]);
+        // TopK: >= exact threshold; Threshold codec: > fixed; DGC: >= per-segment threshold
         const bool pick = (e0 + q < len) && (use_fixed ? (b > thr) : (b >= thr));
-        pk[q] = pick;
-        const uint32_t mask = __ballot_sync(0xffffffffu, pick);
-        if (mask) {
-          int wbase = 0;
-          if (lane == 0) wbase = atomicAdd(&scount, __popc(mask));
-          wbase = __shfl_sync(0xffffffffu, wbase, 0);
-          if (pick) {
-            const int pos = wbase + __popc(mask & ((1u << lane) - 1u));
-            sval[pos] = vv[q];
-            sidx[pos] = local0 + e0 + q;
-            vv[q] = 0.f;
-            changed = true;
-          }
-        }
+        picks |= (pick ? 1u : 0u) << (j * 4 + q);
+        cnt += pick;
       }
-      if (ZERO && changed) {
-        store4(work + base, e0, len, make_float4(vv[0], vv[1], vv[2], vv[3]));
-        if (work2) {
-          float4 u = load4(work2 + base, e0, len);
-          if (pk[0]) u.x = 0.f;
-          if (pk[1]) u.y = 0.f;
-          if (pk[2]) u.z = 0.f;
-          if (pk[3]) u.w = 0.f;
-          store4(work2 + base, e0, len, u);
+    }
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += n;
+    }
+    const int wtotal = __shfl_sync(0xffffffffu, incl, 31);
+    int wbase = 0;
+    if (wtotal) {
+      if (lane == 0) wbase = atomicAdd(&scount, wtotal);
+      wbase = __shfl_sync(0xffffffffu, wbase, 0);
+    }
+    if (picks) {
+      int pos = wbase + incl - cnt;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+        if ((picks >> (j * 4)) & 0xFu) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if ((picks >> (j * 4 + q)) & 1u) {
+              sval[pos] = vv[j][q];
+              sidx[pos] = local0 + e0 + q;
+              ++pos;
+              vv[j][q] = 0.f;
+            }
+          }
+          if (ZERO) {
+            store4(work + base, e0, len, make_float4(vv[j][0], vv[j][1], vv[j][2], vv[j][3]));
+            if (work2) {
+              float4 u = load4(work2 + base, e0, len);
+              if ((picks >> (j * 4 + 0)) & 1u) u.x = 0.f;
+              if ((picks >> (j * 4 + 1)) & 1u) u.y = 0.f;
+              if ((picks >> (j * 4 + 2)) & 1u) u.z = 0.f;
+              if ((picks >> (j * 4 + 3)) & 1u) u.w = 0.f;
+              store4(work2 + base, e0, len, u);
+            }
+          }
         }
       }
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-      int cnt = scount;
+      int tc = scount;
       int64_t begin;
-      if (per_segment) begin = t.seg_kbase[seg] + atomicAdd(&sel[seg * 4 + 2], (uint32_t)cnt);
-      else begin = atomicAdd(cursor, (uint32_t)cnt);
-      if (begin + cnt > capacity) {
+      if (per_segment) begin = t.seg_kbase[seg] + atomicAdd(&sel[seg * 4 + 2], (uint32_t)tc);
+      else begin = atomicAdd(cursor, (uint32_t)tc);
+      if (begin + tc > capacity) {
         atomicOr(status, GB_STATUS_OVERFLOW);
-        cnt = (int)max((int64_t)0, capacity - begin);
-        scount = cnt;
+        tc = (int)max((int64_t)0, capacity - begin);
+        scount = tc;
       }
       sbegin = (int)begin;
-      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = make_int2((int)begin, cnt);
+      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = make_int2((int)begin, tc);
     }
     __syncthreads();
-    const int cnt = scount, begin = sbegin;
+    const int tcnt = scount, begin = sbegin;
     for (int r = 0; r < out.n; ++r) {
       float* dv = out.vals[r] + begin;
       int32_t* di = out.idx[r] + begin;
-      for (int i = threadIdx.x; i < cnt; i += GB_THREADS) { dv[i] = sval[i]; di[i] = sidx[i]; }
+      for (int i = threadIdx.x; i < tcnt; i += GB_THREADS) { dv[i] = sval[i]; di[i] = sidx[i]; }
     }
     __syncthreads();
   }
@@ -587,7 +612,7 @@ int k1_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   const bool fixed = p->prm.codec == GB_CODEC_THRESHOLD;
   uint32_t thr_bits = 0u;
   if (fixed) { const float th = p->prm.threshold < 0.f ? 0.f : p->prm.threshold; memcpy(&thr_bits, &th, 4); }
-  const int hgrid = std::min(p->ntiles, 148 * 4);
+  const int hgrid = std::min(p->ntiles, 148 * 8);
   uint32_t* cursor = p->d_done + 2;
   if (fixed) {
     // variable-size payload: one global cursor, a single compaction pass
@@ -846,7 +871,7 @@ int k1_topk_single(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_
   GB_CUDA(cudaGetLastError());
   const SegTable t = single_table(tab, n, L.ntiles);
   float* work = const_cast<float*>(d_x);
-  const int hgrid = std::min(L.ntiles, 148 * 4), grid = grid_for(L.ntiles);
+  const int hgrid = std::min(L.ntiles, 148 * 8), grid = grid_for(L.ntiles);
   k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
   k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 0);
   k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
