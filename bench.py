@@ -30,7 +30,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--model", default="resnet50")
+    ap.add_argument("--model", default="resnet50", help="torchvision model name, or bert-large / bert-base")
+    ap.add_argument("--seq-len", type=int, default=128, help="BERT only")
     ap.add_argument("--batch-size", type=int, default=32, help="per GPU (reference harness default)")
     ap.add_argument("--compressor", default="topk")
     ap.add_argument("--memory", default=None)
@@ -94,8 +95,16 @@ def triple(args):
 
 def build_model(args, device):
     import torch
-    import torchvision
     torch.manual_seed(0)
+    if args.model.startswith("bert"):
+        # BASELINE.json config 4: BERT pre-training (MLM + NSP heads), random init, synthetic token ids
+        from transformers import BertConfig, BertForPreTraining
+        large = args.model == "bert-large"
+        cfg = BertConfig(hidden_size=1024 if large else 768, num_hidden_layers=24 if large else 12,
+                         num_attention_heads=16 if large else 12, intermediate_size=4096 if large else 3072)
+        args.memory_format = "contiguous"
+        return BertForPreTraining(cfg).to(device)
+    import torchvision
     model = getattr(torchvision.models, args.model)().to(device)
     fmt = args.memory_format
     if fmt == "auto":
@@ -193,16 +202,29 @@ def main():
             base_opt.zero_grad(set_to_none=False)
 
     bs = args.batch_size
-    host_x = torch.randn(bs, 3, 224, 224).pin_memory()
-    host_y = torch.randint(0, 1000, (bs,)).pin_memory()
+    is_bert = args.model.startswith("bert")
     mf = torch.channels_last if args.memory_format == "channels_last" else torch.contiguous_format
-    dev_x = host_x.to(device, non_blocking=True).contiguous(memory_format=mf)
+    if is_bert:
+        S = args.seq_len
+        host_x = torch.randint(0, 30522, (bs, S)).pin_memory()                  # token ids (also the MLM labels)
+        host_y = torch.randint(0, 2, (bs,)).pin_memory()                        # next-sentence labels
+        to_dev = lambda x: x.to(device, non_blocking=True)
+        units_per_sample, unit = S, "tokens/s"
+    else:
+        host_x = torch.randn(bs, 3, 224, 224).pin_memory()
+        host_y = torch.randint(0, 1000, (bs,)).pin_memory()
+        to_dev = lambda x: x.to(device, non_blocking=True).contiguous(memory_format=mf)
+        units_per_sample, unit = 1, "img/s"
+    dev_x = to_dev(host_x)
     dev_y = host_y.to(device, non_blocking=True)
 
     def step(x, y):
         zero()
         with torch.autocast("cuda", dtype=torch.bfloat16):
-            loss = F.cross_entropy(model(x), y)
+            if is_bert:
+                loss = model(input_ids=x, labels=x, next_sentence_label=y).loss
+            else:
+                loss = F.cross_entropy(model(x), y)
         loss.backward()
         exchange_and_step()
         return loss
@@ -221,7 +243,7 @@ def main():
         last = None
         for _ in range(n):
             if e2e:
-                x = host_x.to(device, non_blocking=True).contiguous(memory_format=mf)
+                x = to_dev(host_x)
                 y = host_y.to(device, non_blocking=True)
                 last = step(x, y).item()          # device -> host read of the step's result
             else:
@@ -246,21 +268,22 @@ def main():
     if not args.no_e2e:
         step(dev_x, dev_y)
         ems, _, _, last = timed(args.steps, e2e=True)
-        e2e = {"value": world * bs * args.steps / (ems / 1e3), "unit": "img/s", "ms_per_step": ems / args.steps,
-               "h2d_bytes_per_step": host_x.numel() * 4 + host_y.numel() * 8, "d2h_bytes_per_step": 4,
+        e2e = {"value": world * bs * units_per_sample * args.steps / (ems / 1e3), "unit": unit, "ms_per_step": ems / args.steps,
+               "h2d_bytes_per_step": host_x.numel() * host_x.element_size() + host_y.numel() * 8, "d2h_bytes_per_step": 4,
                "last_loss": last}
     if fused is not None:
         fused.engine.check_status()
 
     if rank == 0:
-        value = world * bs * args.steps / (ms / 1e3)
+        value = world * bs * units_per_sample * args.steps / (ms / 1e3)
         out = {
-            "metric": "ResNet-50 synthetic training throughput with %s gradient compression" % comp,
-            "value": value, "unit": "img/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "metric": "%s synthetic training throughput with %s gradient compression"
+                      % ("ResNet-50" if args.model == "resnet50" else args.model, comp),
+            "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic (fixed random batch, random-init weights)", "impl": args.impl,
-            "config": {"model": args.model, "global_batch": world * bs, "per_gpu_batch": bs, "seq_len": None,
-                       "image": "3x224x224", "parallelism": "dp%d" % world, "compressor": comp, "memory": mem,
+            "config": {"model": args.model, "global_batch": world * bs, "per_gpu_batch": bs, "seq_len": args.seq_len if is_bert else None,
+                       "image": None if is_bert else "3x224x224", "parallelism": "dp%d" % world, "compressor": comp, "memory": mem,
                        "communicator": comm, "compress_ratio": args.compress_ratio, "params": n_params,
                        "grad_dtype": "fp32 master gradients, bf16 autocast compute", "memory_format": args.memory_format,
                        "optimizer": "SGD momentum 0.9 (inside the timed region)",

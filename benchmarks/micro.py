@@ -118,6 +118,51 @@ def main():
             print("%-10s %-9s W=%d  %8.3f ms  %7.1f GB/s of gradient  wire %9d B/peer  roofline %6.3f ms (%.2f of %s)  launches %d"
                   % (comp, mem, world, r["ms"], r["grad_gbs"], wire, roof, r["fraction_of_roofline"], how,
                      r["launches_per_exchange"]), flush=True)
+    if not want or "powersgd" in want:
+        # K3: all >=2-D tensors through the native PowerSGD plan (rank 4, with residual memory)
+        from grace_b200.parallel.engine import PowerSGDPlan
+        import torchvision
+        mats = [(n, tuple(p.shape)) for n, p in getattr(torchvision.models, args.shape)().named_parameters() if p.dim() >= 2] \
+            if not args.shape.startswith("flat:") else [("flat", (int(args.shape.split(":")[1]) // 4096, 4096))]
+        shapes = [(sh[0], int(torch.tensor(sh[1:]).prod())) for _, sh in mats]
+        for use_tc in (True, False):
+            plan = PowerSGDPlan(eng, shapes, [n for n, _ in mats], 4, 1234, True, use_tc)
+            grad = torch.randn(plan.padded, device="cuda")
+            out = torch.empty(plan.padded, device="cuda")
+            times = []
+            for it in range(args.warmup + args.iters):
+                flush.zero_()
+                if world > 1:
+                    dist.barrier()
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                plan.send(grad); plan.mid(); plan.recv(out)
+                b.record()
+                torch.cuda.synchronize()
+                if it >= args.warmup:
+                    times.append(a.elapsed_time(b))
+            ms = sorted(times)[len(times) // 2]
+            if world > 1:
+                t = torch.tensor([ms], device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t)
+            eng.check_status()
+            n_el = sum(r * c for r, c in shapes)
+            # M is read by prep (+residual r/w), GEMM 1, GEMM 2 and the final pass (+ out and residual writes)
+            hbm_bytes = n_el * 4 * 8
+            roof = max(hbm_bytes / (hbm * 1e9) * 1e3, plan.wire_bytes * max(world - 1, 0) / (nvlink * 1e9) * 1e3)
+            n0 = plan.launches(); plan.send(grad); plan.mid(); plan.recv(out); torch.cuda.synchronize()
+            rows.append(dict(codec="powersgd-r4" + ("-tcgen05" if use_tc else "-simt"), memory="powersgd", world=world,
+                             elements=n_el, ms=ms, launches_per_exchange=plan.launches() - n0,
+                             wire_bytes_per_peer=plan.wire_bytes, roofline_ms=roof, fraction_of_roofline=roof / ms,
+                             grad_gbs=n_el * 4 / ms / 1e6, peaks=how, tc_matrices=plan.tc_matrices))
+            if rank == 0:
+                r = rows[-1]
+                print("%-22s W=%d  %8.3f ms  %7.1f GB/s of gradient  wire %9d B/peer  roofline %6.3f ms (%.2f of %s)  launches %d  tcgen05 matrices %d/%d"
+                      % (r["codec"], world, ms, r["grad_gbs"], plan.wire_bytes, roof, r["fraction_of_roofline"], how,
+                         r["launches_per_exchange"], plan.tc_matrices, len(shapes)), flush=True)
+            plan.destroy()
     if rank == 0 and args.out:
         with open(args.out, "w") as f:
             json.dump(rows, f, indent=1)

@@ -31,13 +31,36 @@ DEFAULT_BUCKET_BYTES = int(os.environ.get("GRACE_B200_BUCKET_MB", "32")) << 20
 _engine = None
 
 
-def get_engine():
-    """Process-wide communicator (created on first use, like ``hvd.init()``)."""
+def get_engine(min_arena_bytes=0):
+    """Process-wide communicator (created on first use, like ``hvd.init()``).  The peer arena is
+    sized for the first caller's needs (``min_arena_bytes``) or ``GRACE_B200_ARENA_MB``, whichever
+    is larger; later plans that do not fit raise a clear error from the native allocator."""
     global _engine
     if _engine is None:
         from grace_b200.parallel.engine import Engine
-        _engine = Engine.create()
+        _engine = Engine.create(arena_bytes=max(Engine.default_arena_bytes(), int(min_arena_bytes)))
     return _engine
+
+
+def estimate_arena_bytes(numels, params, powersgd, world):
+    """Upper bound of the peer-arena bytes the plans of one model need (2 parities x W slots)."""
+    n = sum((x + 127) // 128 * 128 for x in numels)
+    if powersgd is not None:
+        slot = n * 4 // 8 + (1 << 20)           # P/Q rows are at most numel/ min(n, m) ... generous
+        slot += n * 4                            # dense plan for the vectors (worst case)
+    else:
+        from grace_b200.ops.native import CODEC
+        code = params.codec
+        if code in (CODEC["threshold"], CODEC["dgc"]):
+            slot = int(8 * n * (params.capacity or 1.0))
+        elif code in (CODEC["topk"], CODEC["randomk"]):
+            slot = int(8 * (n * params.ratio + len(numels)))
+        elif code in (CODEC["none"], CODEC["fp16"]):
+            slot = 4 * n if world == 1 else 8 * n // world + 4096
+        else:
+            slot = 2 * n                          # <= 16 bits per element
+        slot += 16 * len(numels) + 8 * (n // 4096 + len(numels)) + 4096
+    return int(slot * 2 * world * 1.1) + (64 << 20)
 
 
 def shutdown_engine():
@@ -236,7 +259,10 @@ class FusedDP:
 
     def __init__(self, optimizer, grace, named, params, bucket_bytes=None, powersgd=None):
         self.grace = grace
-        self.engine = get_engine()
+        import torch.distributed as _dist
+        world = _dist.get_world_size() if (_dist.is_available() and _dist.is_initialized()) else 1
+        numels = [p.numel() for _, p in named if p.requires_grad]
+        self.engine = get_engine(estimate_arena_bytes(numels, params, powersgd, world))
         self.passes = optimizer.backward_passes_per_step
         self.side = torch.cuda.Stream()
         bucket_bytes = bucket_bytes or DEFAULT_BUCKET_BYTES
