@@ -429,10 +429,7 @@ class FusedStepper:
             self.enabled = ok
         return self.enabled
 
-    def step(self, tensor, name):
-        """Returns the aggregated tensor, or ``None`` when this call must take the generic path."""
-        if not self._probe(tensor) or tensor.dtype != torch.float32 or not tensor.is_cuda:
-            return None
+    def _entry(self, tensor, name):
         key = (name, tensor.numel())
         entry = self.plans.get(key)
         if entry is None:
@@ -440,9 +437,43 @@ class FusedStepper:
             entry = (plan, torch.zeros(plan.padded, dtype=torch.float32, device=tensor.device),
                      torch.empty(plan.padded, dtype=torch.float32, device=tensor.device))
             self.plans[key] = entry
-        plan, staging, out = entry
+        return entry
+
+    def usable(self, tensor):
+        return self._probe(tensor) and tensor.dtype == torch.float32 and tensor.is_cuda
+
+    def step(self, tensor, name):
+        """Returns the aggregated tensor, or ``None`` when this call must take the generic path."""
+        if not self.usable(tensor):
+            return None
+        plan, staging, out = self._entry(tensor, name)
         n = tensor.numel()
         staging[:n].copy_(tensor.reshape(-1))
         plan.send(staging)
         plan.recv(out)
         return out[:n].view(tensor.shape)
+
+    # ---- asynchronous halves (Horovod-flavour send_step / receive_step)
+    def send(self, tensor, name):
+        """Compensate + compress + push on a side stream; returns an opaque ticket or ``None``."""
+        if not self.usable(tensor):
+            return None
+        if not hasattr(self, "_side"):
+            self._side = torch.cuda.Stream()
+        plan, staging, out = self._entry(tensor, name)
+        n = tensor.numel()
+        ready = torch.cuda.Event()
+        ready.record()
+        self._side.wait_event(ready)
+        with torch.cuda.stream(self._side):
+            staging[:n].copy_(tensor.reshape(-1), non_blocking=True)
+        plan.send(staging, stream=self._side)
+        return ("native", plan, out, n, tuple(tensor.shape))
+
+    def receive(self, ticket):
+        _, plan, out, n, shape = ticket
+        plan.recv(out, stream=self._side)
+        done = torch.cuda.Event()
+        done.record(self._side)
+        torch.cuda.current_stream().wait_event(done)
+        return out[:n].view(shape)

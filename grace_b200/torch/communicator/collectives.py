@@ -9,12 +9,36 @@ from grace_b200.core import AsyncCommunicator
 from grace_b200.torch import mpi_ops as ops
 
 
+class _NativeAsync:
+    """Mixin: ``send_step`` / ``receive_step`` of built-in triples on CUDA fp32 tensors run on
+    single-tensor native plans (compress + peer stores on a side stream at send time, decode +
+    aggregate at receive time); everything else takes the generic handle-based path."""
+
+    fused = "auto"
+    _stepper = None
+
+    def send_step(self, tensor, name):
+        if self.fused and tensor.is_cuda:
+            if self._stepper is None:
+                from grace_b200.parallel.fused import FusedStepper
+                self._stepper = FusedStepper(self)
+            ticket = self._stepper.send(tensor, name)
+            if ticket is not None:
+                return ticket, None
+        return super().send_step(tensor, name)
+
+    def receive_step(self, handles, ctx):
+        if isinstance(handles, tuple) and handles and handles[0] == "native":
+            return self._stepper.receive(handles)
+        return super().receive_step(handles, ctx)
+
+
 def _finish(compressor, decompressed, world_size):
     out = compressor.aggregate(decompressed)
     return out / world_size if compressor.average else out
 
 
-class Allreduce(AsyncCommunicator):
+class Allreduce(_NativeAsync, AsyncCommunicator):
     def async_send(self, tensors, name):
         return [ops.allreduce_async_(t.contiguous(), self.compressor.average, "%s%d" % (name, i))
                 for i, t in enumerate(tensors)]
@@ -23,7 +47,7 @@ class Allreduce(AsyncCommunicator):
         return self.compressor.decompress([ops.synchronize(h) for h in handles], ctx)
 
 
-class Allgather(AsyncCommunicator):
+class Allgather(_NativeAsync, AsyncCommunicator):
     def __init__(self, compressor, memory, world_size=None):
         super().__init__(compressor, memory)
         self.world_size = ops.size() if world_size is None else world_size
@@ -52,7 +76,7 @@ class Allgather(AsyncCommunicator):
         return _finish(self.compressor, decompressed, self.world_size)
 
 
-class Broadcast(AsyncCommunicator):
+class Broadcast(_NativeAsync, AsyncCommunicator):
     def __init__(self, compressor, memory, world_size=None):
         super().__init__(compressor, memory)
         self.world_size = ops.size() if world_size is None else world_size

@@ -55,6 +55,8 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         self._synchronized = False
         self._should_synchronize = True
         self._fused = None
+        if fused is False and hasattr(grace, "fused"):
+            grace.fused = False          # fused=False means: generic path everywhere
         if fused:
             from grace_b200.parallel.fused import try_build_fused
             self._fused = try_build_fused(self, grace, named, required=(fused is True),

@@ -81,6 +81,21 @@ def test_sync_step_api_uses_native_plans():
     assert fast._stepper is not None and fast._stepper.enabled and len(fast._stepper.plans) == 1
 
 
+def test_async_send_receive_api_uses_native_plans():
+    import grace_b200.torch as hvd
+    params = dict(compressor="qsgd", memory="residual", communicator="allgather", quantum_num=64)
+    fast, slow = hvd.grace_from_params(params), hvd.grace_from_params(params)
+    slow.fused = False
+    g = torch.Generator(device="cuda").manual_seed(2)
+    for _ in range(3):
+        w = torch.randn(50, 70, device="cuda", generator=g) * 0.01
+        ha, ca = fast.send_step(w, "w")
+        hb, cb = slow.send_step(w, "w")
+        a, b = fast.receive_step(ha, ca), slow.receive_step(hb, cb)
+        assert float(((a - b).abs() > 1e-7 + 2e-5 * b.abs()).float().mean()) < 0.003
+    assert fast._stepper is not None and fast._stepper.enabled
+
+
 def test_grad_accumulation_and_state_dict():
     import grace_b200.torch as hvd
     data = _data(6)
