@@ -292,6 +292,7 @@ def main():
         }
         if fused is not None:
             out["config"]["buckets"] = len(fused.buckets)
+            out["config"]["transport"] = fused.transport
             out["config"]["wire_bytes_per_peer_per_step"] = fused.wire_bytes()
         real_stdout.write(json.dumps(out) + "\n")
         real_stdout.flush()

@@ -146,3 +146,103 @@ int k0_recv(gb_plan* p, float* d_out, cudaStream_t st) {
   LAUNCHED(p);
   return 0;
 }
+
+// ---------------------------------------------------------------- NVLS (in-switch reduction) variant
+// When the host exposes NVLink SHARP multicast (NCCL_DEBUG=INFO shows "NVLS multicast support is
+// available"), the gradient bucket itself lives in symmetric memory bound to a multicast address.
+// One kernel per bucket then does the whole all-reduce in place:
+//   wait until every rank has signalled "my gradients are final"          (epoch flags, channel A)
+//   for my shard:  v = multimem.ld_reduce.add.f32x4 [mc + i]  -- the switch adds all W copies
+//                  multimem.st.f32x4 [mc + i] = v / W         -- and broadcasts the result to all W copies
+//   last CTA: release "my shard is stored" to every rank; then wait for all W such flags (channel B)
+// Traffic per GPU: N/W in, N/W out -- the NVSwitch does the W-fold fan-in/fan-out.
+// Every rank receives the same bits (one rank computes each shard); the switch's summation order is
+// its own, so the value can differ in the last ulp from the rank-ordered P2P path.
+struct gb_nvls {
+  gb_comm* comm;
+  int64_t padded;
+  int chan_a, chan_b;
+  uint32_t epoch;
+  uint32_t* d_done;
+  int64_t launches;
+};
+
+__global__ void k0_nvls_signal(PeerPtrs peers, int channel, uint32_t epoch) {
+  if (threadIdx.x < peers.world) {
+    __threadfence_system();
+    st_release_sys(gb_flag(peers.base[threadIdx.x], channel, epoch & 1, peers.rank), epoch);
+  }
+}
+
+__global__ void __launch_bounds__(GB_THREADS) k0_nvls_reduce(float* mc, int64_t start, int64_t len, float inv_world, uint32_t* done,
+                                                             PeerPtrs peers, int chan_a, int chan_b, uint32_t epoch,
+                                                             uint32_t* status, uint64_t timeout_ns) {
+  wait_all_ranks(peers, chan_a, epoch, status, timeout_ns);
+  const int64_t n4 = len / 4;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float* p = mc + start + i * 4;
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    v.x *= inv_world; v.y *= inv_world; v.z *= inv_world; v.w *= inv_world;
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+  }
+  // publish "my shard is stored", then wait until every rank's shard is
+  __threadfence_system();
+  __syncthreads();
+  __shared__ uint32_t last;
+  if (threadIdx.x == 0) last = (atomicAdd(done, 1u) == gridDim.x - 1) ? 1u : 0u;
+  __syncthreads();
+  if (last) {
+    if (threadIdx.x == 0) *done = 0;
+    if (threadIdx.x < peers.world) {
+      __threadfence_system();
+      st_release_sys(gb_flag(peers.base[threadIdx.x], chan_b, epoch & 1, peers.rank), epoch);
+      wait_flag(gb_flag(peers.base[peers.rank], chan_b, epoch & 1, threadIdx.x), epoch, status, timeout_ns);
+    }
+  }
+}
+
+extern "C" int gb_nvls_create(gb_comm* c, int64_t padded, gb_nvls** out) {
+  GB_CHECK(padded % 128 == 0, "bucket length must be a multiple of 128 elements");
+  gb_nvls* p = new gb_nvls();
+  p->comm = c; p->padded = padded; p->epoch = 0; p->launches = 0;
+  size_t unused;
+  if (gb_comm_alloc_channel(c, 0, &p->chan_a, &unused)) return -1;
+  if (gb_comm_alloc_channel(c, 0, &p->chan_b, &unused)) return -1;
+  GB_CUDA(cudaMalloc((void**)&p->d_done, 64));
+  GB_CUDA(cudaMemset(p->d_done, 0, 64));
+  *out = p;
+  return 0;
+}
+extern "C" int gb_nvls_destroy(gb_nvls* p) {
+  if (!p) return 0;
+  cudaDeviceSynchronize();
+  cudaFree(p->d_done);
+  delete p;
+  return 0;
+}
+// "my copy of the bucket is final" -- enqueue right after the last gradient of the bucket
+extern "C" int gb_nvls_signal(gb_nvls* p, void* stream) {
+  const uint32_t epoch = ++p->epoch;
+  k0_nvls_signal<<<1, 32, 0, (cudaStream_t)stream>>>(gb_comm_peers(p->comm), p->chan_a, epoch);
+  LAUNCHED(p);
+  return 0;
+}
+// in-place mean over all ranks of the multicast-bound bucket; returns (in stream order) once every shard is in place
+extern "C" int gb_nvls_reduce(gb_nvls* p, void* d_multicast, int average, void* stream) {
+  gb_comm* c = p->comm;
+  GB_CHECK(p->epoch > 0, "gb_nvls_reduce before gb_nvls_signal");
+  const int64_t cap = k0_shard_cap(p->padded, c->world);
+  const int64_t start = (int64_t)c->rank * cap;
+  int64_t len = std::min<int64_t>(cap, p->padded - start);
+  if (len < 0) len = 0;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((len / 4 + GB_THREADS - 1) / GB_THREADS, 148 * 4));
+  k0_nvls_reduce<<<grid, GB_THREADS, 0, (cudaStream_t)stream>>>((float*)d_multicast, start, len, average ? 1.0f / (float)c->world : 1.0f,
+                                                               p->d_done, gb_comm_peers(c), p->chan_a, p->chan_b, p->epoch,
+                                                               c->status_dev, c->timeout_ns);
+  LAUNCHED(p);
+  return 0;
+}
+extern "C" int gb_nvls_launches(gb_nvls* p, int64_t* out) { *out = p->launches; return 0; }

@@ -84,6 +84,11 @@ def _declare(L):
         "gb_plan_get_step": (i32, [vp, P(u32)]),
         "gb_plan_set_step": (i32, [vp, u32]),
         "gb_plan_launches": (i32, [vp, P(i64)]),
+        "gb_nvls_create": (i32, [vp, i64, P(vp)]),
+        "gb_nvls_destroy": (i32, [vp]),
+        "gb_nvls_signal": (i32, [vp, vp]),
+        "gb_nvls_reduce": (i32, [vp, vp, i32, vp]),
+        "gb_nvls_launches": (i32, [vp, P(i64)]),
         "gb_psgd_create": (i32, [vp, i32, P(i64), P(i64), P(u32), i32, u32, i32, i32, P(vp)]),
         "gb_psgd_destroy": (i32, [vp]),
         "gb_psgd_padded_numel": (i64, [vp]),

@@ -255,3 +255,41 @@ class PowerSGDPlan:
             self._h = None
             if self in self.engine.plans:
                 self.engine.plans.remove(self)
+
+
+class NvlsPlan:
+    """In-place NVLS all-reduce of one bucket that lives in multicast-bound symmetric memory."""
+
+    def __init__(self, engine: Engine, padded: int, multicast_ptr: int, average=True):
+        h = C.c_void_p()
+        check(native.lib().gb_nvls_create(engine._h, int(padded), C.byref(h)))
+        self._h, self.engine, self.padded = h, engine, int(padded)
+        self.mc, self.average = int(multicast_ptr), bool(average)
+        self.wire_bytes = (self.padded * 4) // max(engine.world, 1)
+        self.step = 0
+        engine.plans.append(self)
+
+    def signal(self, stream=None):
+        check(native.lib().gb_nvls_signal(self._h, _stream_ptr(stream)))
+
+    def reduce(self, stream=None):
+        check(native.lib().gb_nvls_reduce(self._h, C.c_void_p(self.mc), 1 if self.average else 0, _stream_ptr(stream)))
+        self.step += 1
+
+    def launches(self):
+        out = C.c_int64()
+        check(native.lib().gb_nvls_launches(self._h, C.byref(out)))
+        return out.value
+
+    def get_state(self, which):
+        return None
+
+    def set_state(self, which, tensor):
+        pass
+
+    def destroy(self):
+        if self._h:
+            native.lib().gb_nvls_destroy(self._h)
+            self._h = None
+            if self in self.engine.plans:
+                self.engine.plans.remove(self)

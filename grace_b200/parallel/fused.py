@@ -238,6 +238,55 @@ class _PowerSGDBucket(_Bucket):
             self.dense.recv(self.flat_v, stream=stream)
 
 
+class _NvlsBucket(_Bucket):
+    """Dense (None codec) bucket whose flat gradient buffer is a symmetric allocation bound to an
+    NVLS multicast address: the all-reduce is one in-place kernel using multimem.ld_reduce /
+    multimem.st (``csrc/k0_dense.cu``).  Construction is collective and may raise when the host does
+    not expose multicast; ``FusedDP`` then falls back to the P2P two-shot plan on every rank."""
+
+    def __init__(self, engine, named_params, average):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        from grace_b200.parallel.engine import NvlsPlan
+        self.names = [n for n, _ in named_params]
+        self.tensors = [p for _, p in named_params]
+        offsets, off = [], 0
+        for p in self.tensors:
+            offsets.append(off)
+            off += (p.numel() + 127) // 128 * 128
+        dev = self.tensors[0].device
+        self.flat = symm.empty(off, dtype=torch.float32, device=dev)
+        handle = symm.rendezvous(self.flat, dist.group.WORLD)
+        mc = int(handle.multicast_ptr or 0)
+        if not mc:
+            raise RuntimeError("no NVLS multicast address for this allocation")
+        self.handle = handle
+        self.flat.zero_()
+        self.plan = NvlsPlan(engine, off, mc + int(getattr(handle, "offset", 0) or 0), average)
+        self.plans, self.flats = [self.plan], [self.flat]
+        self.views = [_grad_view(self.flat[o:o + p.numel()], p) for o, p in zip(offsets, self.tensors)]
+        self.pending = len(self.tensors)
+        self.sent = False
+
+    def send(self, stream):
+        self.plan.signal(stream=stream)          # "my copy is final"; the reduction itself happens in recv
+
+    def mid(self, stream):
+        pass
+
+    def recv(self, stream):
+        self.plan.reduce(stream=stream)
+
+
+def _all_ranks_agree(ok):
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return ok
+    t = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(int(t))
+
+
 def powersgd_spec(grace):
     """(rank, seed, has_memory) when ``grace`` is a natively supported PowerSGD triple, else None."""
     from grace_b200.compressor.lowrank import RANK_KEY
@@ -265,6 +314,8 @@ class FusedDP:
         self.engine = get_engine(estimate_arena_bytes(numels, params, powersgd, world))
         self.passes = optimizer.backward_passes_per_step
         self.side = torch.cuda.Stream()
+        self.transport = "p2p-store"                      # or "nvls-multimem" for dense buckets on NVLS hosts
+        self.nvls_error = None
         bucket_bytes = bucket_bytes or DEFAULT_BUCKET_BYTES
         trainable = [(n, p) for n, p in named if p.requires_grad]
         # gradients become ready roughly in reverse registration order
@@ -293,6 +344,20 @@ class FusedDP:
         self._inflight = False
 
     def _make_bucket(self, named_params, params, powersgd):
+        from grace_b200.ops.native import CODEC, MEMORY
+        if (powersgd is None and self.engine.world > 1 and params.codec == CODEC["none"]
+                and params.memory == MEMORY["none"] and os.environ.get("GRACE_B200_NVLS", "1") != "0"
+                and not getattr(self, "_nvls_failed", False)):
+            bucket, err = None, None
+            try:
+                bucket = _NvlsBucket(self.engine, named_params, bool(params.average))
+            except Exception as exc:                       # no multicast on this host / old driver
+                err = exc
+            if _all_ranks_agree(bucket is not None):
+                self.transport = "nvls-multimem"
+                return bucket
+            self._nvls_failed = True
+            self.nvls_error = repr(err)
         if powersgd is not None:
             rank, seed, has_memory = powersgd
             return _PowerSGDBucket(self.engine, named_params, rank, seed, has_memory,

@@ -113,6 +113,17 @@ int gb_plan_get_step(gb_plan* p, uint32_t* step);
 int gb_plan_set_step(gb_plan* p, uint32_t step);
 int gb_plan_launches(gb_plan* p, int64_t* out);  /* kernels launched by this plan so far */
 
+/* ---- NVLS (NVLink SHARP multicast) dense all-reduce, in place on a multicast-bound bucket.
+ * Reference: communicator/allreduce.py:8-13 with compressor/none.py (NCCL all-reduce + div_).
+ * The caller provides the multicast address of a symmetric allocation that holds the bucket on
+ * every rank (e.g. torch.distributed._symmetric_memory); flags travel through the communicator. */
+typedef struct gb_nvls gb_nvls;
+int gb_nvls_create(gb_comm* c, int64_t padded_numel, gb_nvls** out);
+int gb_nvls_destroy(gb_nvls* p);
+int gb_nvls_signal(gb_nvls* p, void* stream);                 /* this rank's copy is final */
+int gb_nvls_reduce(gb_nvls* p, void* d_multicast, int average, void* stream);
+int gb_nvls_launches(gb_nvls* p, int64_t* out);
+
 /* ---- PowerSGD plans (reference: compressor/powersgd.py:7-65, memory/powersgd.py:6-37), rank <= 4.
  * All >=2-D gradients of a bucket, flattened like a plan (128-element aligned).  One exchange is
  *   gb_psgd_send  (M += e; Q0; P_r = M Q0 on tcgen05/TMEM via TMA; P tiles stored into every peer)

@@ -82,6 +82,41 @@ def main():
             opt.step()
         return torch.cat([p.detach().flatten() for p in model.parameters()])
 
+    # dense buckets: NVLS multimem when the host has it, else the P2P two-shot plan -- same API
+    def train_dense():
+        torch.manual_seed(0)
+        model = MnistNet().cuda().eval()
+        opt = torch.optim.SGD(model.parameters(), lr=0.05)
+        hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+        grc = hvd.grace_from_params(dict(compressor="none", memory="none", communicator="allreduce"))
+        opt = hvd.DistributedOptimizer(opt, grc, named_parameters=model.named_parameters(), fused=True)
+        gen = torch.Generator(device="cuda").manual_seed(5 + rank)
+        x = torch.randn(16, 1, 28, 28, device="cuda", generator=gen)
+        y = torch.randint(0, 10, (16,), device="cuda", generator=gen)
+        outs = []
+        for _ in range(3):
+            opt.zero_grad()
+            F.nll_loss(model(x), y).backward()
+            mine = torch.cat([p.grad.detach().flatten().clone() for p in model.parameters()])
+            want = mine.clone()
+            dist.all_reduce(want)
+            want /= world
+            opt.synchronize()
+            got = torch.cat([p.grad.detach().flatten() for p in model.parameters()])
+            outs.append((got.clone(), want))
+            with opt.skip_synchronize():
+                opt.step()
+        return outs, opt._fused.transport, opt._fused.nvls_error
+
+    dense, transport, nvls_err = train_dense()
+    if rank == 0:
+        print("dense transport: %s (nvls error: %s)" % (transport, nvls_err), flush=True)
+    for got, want in dense:
+        if not torch.allclose(got, want, rtol=1e-5, atol=1e-7):
+            failures.append("dense all-reduce (%s) differs by %g" % (transport, float((got - want).abs().max())))
+        if not same_on_all_ranks(got):
+            failures.append("dense all-reduce (%s): ranks disagree" % transport)
+
     pf, pg = train(True), train(False)
     if not same_on_all_ranks(pf):
         failures.append("fused DistributedOptimizer: replicas diverged")
