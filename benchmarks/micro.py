@@ -118,6 +118,42 @@ def main():
             print("%-10s %-9s W=%d  %8.3f ms  %7.1f GB/s of gradient  wire %9d B/peer  roofline %6.3f ms (%.2f of %s)  launches %d"
                   % (comp, mem, world, r["ms"], r["grad_gbs"], wire, roof, r["fraction_of_roofline"], how,
                      r["launches_per_exchange"]), flush=True)
+    if world > 1 and (not want or "nvls" in want):
+        # dense all-reduce in place on an NVLS multicast-bound bucket (multimem.ld_reduce / multimem.st)
+        try:
+            import torch.distributed._symmetric_memory as symm
+            from grace_b200.parallel.engine import NvlsPlan
+            padded = (numel + 127) // 128 * 128
+            buf = symm.empty(padded, dtype=torch.float32, device="cuda")
+            hd = symm.rendezvous(buf, dist.group.WORLD)
+            plan = NvlsPlan(eng, padded, hd.multicast_ptr + (buf.data_ptr() - hd.buffer_ptrs[rank]), True)
+            buf.normal_()
+            times = []
+            for it in range(args.warmup + args.iters):
+                flush.zero_()
+                dist.barrier()
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                plan.signal(); plan.reduce()
+                b.record()
+                torch.cuda.synchronize()
+                if it >= args.warmup:
+                    times.append(a.elapsed_time(b))
+            ms = sorted(times)[len(times) // 2]
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+            eng.check_status()
+            busbw = 2 * (world - 1) / world * numel * 4 / ms / 1e6
+            rows.append(dict(codec="none-nvls", memory="none", world=world, elements=numel, ms=ms, launches_per_exchange=2,
+                             bus_bandwidth_gbs=busbw, peaks=how))
+            if rank == 0:
+                print("%-10s %-9s W=%d  %8.3f ms  all-reduce bus bandwidth %.0f GB/s (NCCL reference on this pool: 725 GB/s at 1 GiB)"
+                      % ("none-nvls", "none", world, ms, busbw), flush=True)
+        except Exception as exc:
+            if rank == 0:
+                print("none-nvls  unavailable: %r" % (exc,), flush=True)
     if not want or "powersgd" in want:
         # K3: all >=2-D tensors through the native PowerSGD plan (rank 4, with residual memory)
         from grace_b200.parallel.engine import PowerSGDPlan

@@ -84,23 +84,27 @@ def main():
 
     # dense buckets: NVLS multimem when the host has it, else the P2P two-shot plan -- same API
     def train_dense():
+        import copy
         torch.manual_seed(0)
         model = MnistNet().cuda().eval()
-        opt = torch.optim.SGD(model.parameters(), lr=0.05)
         hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+        twin = copy.deepcopy(model)                    # plain replica: source of the expected gradients
+        opt = torch.optim.SGD(model.parameters(), lr=0.0)
         grc = hvd.grace_from_params(dict(compressor="none", memory="none", communicator="allreduce"))
         opt = hvd.DistributedOptimizer(opt, grc, named_parameters=model.named_parameters(), fused=True)
         gen = torch.Generator(device="cuda").manual_seed(5 + rank)
         x = torch.randn(16, 1, 28, 28, device="cuda", generator=gen)
         y = torch.randint(0, 10, (16,), device="cuda", generator=gen)
+        F.nll_loss(twin(x), y).backward()
+        want = torch.cat([p.grad.detach().flatten() for p in twin.parameters()])
+        dist.all_reduce(want)
+        want /= world
         outs = []
         for _ in range(3):
             opt.zero_grad()
             F.nll_loss(model(x), y).backward()
-            mine = torch.cat([p.grad.detach().flatten().clone() for p in model.parameters()])
-            want = mine.clone()
-            dist.all_reduce(want)
-            want /= world
+            # (between backward and synchronize the bucket belongs to the exchange: with NVLS peers
+            #  already write reduced shards into it, so gradients are only inspected afterwards)
             opt.synchronize()
             got = torch.cat([p.grad.detach().flatten() for p in model.parameters()])
             outs.append((got.clone(), want))
