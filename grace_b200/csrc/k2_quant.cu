@@ -58,8 +58,10 @@ __device__ __forceinline__ float comp1(const QuantArgs& a, float r, float g) {
 
 // ---------------------------------------------------------------- pass 1: per-tile partials
 // tilestats[tile][8] = { sum x, sum x^2, max|x|, sum|x|, count(x<0), sum(x<0), M2 about the tile mean, - }
-__global__ void __launch_bounds__(GB_THREADS) k2_stats(SegTable t, const float* __restrict__ grad,
-                                                       const float* __restrict__ res, QuantArgs a, float* tilestats) {
+template <bool NEED_M2>
+__global__ void __launch_bounds__(GB_THREADS, NEED_M2 ? 4 : 8) k2_stats(SegTable t, const float* __restrict__ grad,
+                                                                        const float* __restrict__ res, QuantArgs a,
+                                                                        float* tilestats) {
   __shared__ float sh[6][GB_THREADS / 32];
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
@@ -79,7 +81,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_stats(SegTable t, const float* 
       }
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        keep[j * 4 + q] = x[q];
+        if (NEED_M2) keep[j * 4 + q] = x[q];
         if (e0 + q < len) {
           const float v = x[q];
           s += v; s2 += v * v; mx = fmaxf(mx, fabsf(v)); sa += fabsf(v);
@@ -99,7 +101,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_stats(SegTable t, const float* 
       tilestats[(size_t)tile * 8 + threadIdx.x] = acc;
     }
     __syncthreads();
-    if (a.codec == GB_CODEC_TERNGRAD) {
+    if (NEED_M2) {
       // centred second moment about the tile mean (combined across tiles by Chan's formula in
       // k2_finalize): sum x^2 - n mean^2 would cancel catastrophically
       const float tmean = tile_sum / (float)len;
@@ -175,8 +177,23 @@ __global__ void k2_finalize(SegTable t, const float* __restrict__ tilestats, int
 
 // ---------------------------------------------------------------- codec arithmetic
 // encode: value (+ uniform draw) -> BITS-bit code; decode: code + sender's scalars -> float.
+// Per-(segment, sender) constants that the element loops must not recompute: IEEE divisions run on the
+// XU pipe and were the top cost of the first version (ncu: 44 % XU utilisation in k2_encode<QSGD>).
+struct CodecConst { float enc, dec; };
 template <int CODEC>
-__device__ __forceinline__ uint32_t encode1(float x, const float4& st, uint32_t rnd, int quantum, const float* tab) {
+__device__ __forceinline__ CodecConst codec_const(const float4& st, int quantum) {
+  CodecConst c = {0.f, 0.f};
+  if (CODEC == GB_CODEC_QSGD) {
+    c.enc = st.x > 0.f ? __fdiv_rn((float)quantum, st.x) : 0.f;     // s / norm
+    c.dec = __fdiv_rn(st.x, (float)quantum);                        // norm / s
+  } else if (CODEC == GB_CODEC_U8BIT) {
+    c.enc = st.x > 0.f ? __fdiv_rn(1.0f, st.x) : 0.f;
+  }
+  return c;
+}
+
+template <int CODEC>
+__device__ __forceinline__ uint32_t encode1(float x, const float4& st, uint32_t rnd, const CodecConst& cc, const float* tab) {
   if (CODEC == GB_CODEC_NONE) return __float_as_uint(x);
   if (CODEC == GB_CODEC_FP16) return (uint32_t)__half_as_ushort(__float2half_rn(x));
   if (CODEC == GB_CODEC_SIGNSGD || CODEC == GB_CODEC_SIGNUM || CODEC == GB_CODEC_EFSIGNSGD) return x >= 0.f ? 1u : 0u;
@@ -189,9 +206,7 @@ __device__ __forceinline__ uint32_t encode1(float x, const float4& st, uint32_t 
     return x > 0.f ? 1u : 3u;                       // 2-bit two's complement of +1 / -1
   }
   if (CODEC == GB_CODEC_QSGD) {
-    const float norm = st.x;
-    const float scale = norm > 0.f ? __fdiv_rn((float)quantum, norm) : 0.f;
-    const float level = __fmul_rn(scale, fabsf(x));
+    const float level = __fmul_rn(cc.enc, fabsf(x));
     const float low = floorf(level);
     const float q = low + (u32_to_unit(rnd) < (level - low) ? 1.f : 0.f);
     const int sq = x > 0.f ? (int)q : (x < 0.f ? -(int)q : 0);
@@ -205,9 +220,7 @@ __device__ __forceinline__ uint32_t encode1(float x, const float4& st, uint32_t 
     return (sign << 7) | (uint32_t)(e - 18);
   }
   if (CODEC == GB_CODEC_U8BIT) {
-    const float scaler = st.x;
-    const float inv = scaler > 0.f ? __fdiv_rn(1.0f, scaler) : 0.f;
-    const float y = __fmul_rn(fabsf(x), inv);
+    const float y = __fmul_rn(fabsf(x), cc.enc);
     int lo = 0, hi = 128;                           // upper_bound(table, y)
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -224,7 +237,7 @@ __device__ __forceinline__ uint32_t encode1(float x, const float4& st, uint32_t 
 }
 
 template <int CODEC, int BITS>
-__device__ __forceinline__ float decode1(uint32_t code, const float4& st, int quantum, const float* tab) {
+__device__ __forceinline__ float decode1(uint32_t code, const float4& st, const CodecConst& cc, const float* tab) {
   if (CODEC == GB_CODEC_NONE) return __uint_as_float(code);
   if (CODEC == GB_CODEC_FP16) return __half2float(__ushort_as_half((unsigned short)code));
   if (CODEC == GB_CODEC_SIGNSGD || CODEC == GB_CODEC_SIGNUM) return code ? 1.f : -1.f;
@@ -232,7 +245,7 @@ __device__ __forceinline__ float decode1(uint32_t code, const float4& st, int qu
   if (CODEC == GB_CODEC_ONEBIT) return code ? st.x : st.y;
   const int sv = (int)(code << (32 - BITS)) >> (32 - BITS);     // sign-extend BITS
   if (CODEC == GB_CODEC_TERNGRAD) return __fmul_rn((float)sv, st.x);
-  if (CODEC == GB_CODEC_QSGD) return __fmul_rn(__fdiv_rn(st.x, (float)quantum), (float)sv);
+  if (CODEC == GB_CODEC_QSGD) return __fmul_rn(cc.dec, (float)sv);
   if (CODEC == GB_CODEC_NATURAL) {
     const uint32_t e = code & 0x7Fu;
     const float mag = __uint_as_float((e + 18u) << 23);
@@ -271,6 +284,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
     const float4 st = reinterpret_cast<const float4*>(segstats)[seg];
+    const CodecConst cc = codec_const<CODEC>(st, a.quantum);
     const uint32_t hash = t.seg_hash[seg];
 #pragma unroll
     for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
@@ -306,9 +320,9 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const bool live = e0 + q < len;
-          const uint32_t c = live ? (encode1<CODEC>(src[q], st, rr[q], a.quantum, s_tab) & (0xFFFFFFFFu >> (32 - BITS))) : 0u;
+          const uint32_t c = live ? (encode1<CODEC>(src[q], st, rr[q], cc, s_tab) & (0xFFFFFFFFu >> (32 - BITS))) : 0u;
           code[q] = c;
-          nres[q] = live ? __fsub_rn(x[q], decode1<CODEC, BITS>(c, st, a.quantum, s_tab)) : 0.f;
+          nres[q] = live ? __fsub_rn(x[q], decode1<CODEC, BITS>(c, st, cc, s_tab)) : 0.f;
         }
         if (a.has_mem) *reinterpret_cast<float4*>(res + base + e0) = make_float4(nres[0], nres[1], nres[2], nres[3]);
       }
@@ -356,14 +370,25 @@ __global__ void __launch_bounds__(GB_THREADS) k2_decode(SegTable t, WireIn in, s
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
+    float4 sts[GB_MAX_WORLD];
+    CodecConst ccs[GB_MAX_WORLD];
+#pragma unroll
+    for (int r = 0; r < GB_MAX_WORLD; ++r) {
+      if (r < in.n) {
+        sts[r] = reinterpret_cast<const float4*>(in.slot[r])[seg];
+        ccs[r] = codec_const<CODEC>(sts[r], quantum);
+      }
+    }
+    const float inv_div = divisor != 1.f ? __fdiv_rn(1.0f, divisor) : 1.f;
 #pragma unroll
     for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
       const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
       if (e0 >= len) continue;
       const int64_t flat = base + e0;
       float acc[4] = {0.f, 0.f, 0.f, 0.f};
-      for (int r = 0; r < in.n; ++r) {
-        const float4 st = reinterpret_cast<const float4*>(in.slot[r])[seg];
+#pragma unroll
+      for (int r = 0; r < GB_MAX_WORLD; ++r) {
+        if (r >= in.n) break;
         const uint32_t* words = reinterpret_cast<const uint32_t*>(in.slot[r] + hdr_bytes);
         uint32_t code[4];
         if (BITS == 32) {
@@ -379,13 +404,13 @@ __global__ void __launch_bounds__(GB_THREADS) k2_decode(SegTable t, WireIn in, s
           for (int q = 0; q < 4; ++q) code[q] = (w >> (sh + q * BITS)) & (0xFFFFFFFFu >> (32 - BITS));
         }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) acc[q] += decode1<CODEC, BITS>(code[q], st, quantum, s_tab);
+        for (int q = 0; q < 4; ++q) acc[q] += decode1<CODEC, BITS>(code[q], sts[r], ccs[r], s_tab);
       }
       float o[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         if (final_mode == 1) o[q] = acc[q] >= 0.f ? 1.f : -1.f;
-        else o[q] = divisor != 1.f ? __fmul_rn(acc[q], __fdiv_rn(1.0f, divisor)) : acc[q];
+        else o[q] = divisor != 1.f ? __fmul_rn(acc[q], inv_div) : acc[q];
         if (e0 + q >= len) o[q] = 0.f;
       }
       *reinterpret_cast<float4*>(outp + flat) = make_float4(o[0], o[1], o[2], o[3]);
@@ -457,7 +482,9 @@ int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   for (int r = 0; r < c->world; ++r) out.slot[r] = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, epoch & 1, c->rank);
   const PeerPtrs peers = gb_comm_peers(c);
   if (needs_stats(a.codec)) {
-    k2_stats<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_tilestats); LAUNCHED(p);
+    if (a.codec == GB_CODEC_TERNGRAD) k2_stats<true><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_tilestats);
+    else k2_stats<false><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_tilestats);
+    LAUNCHED(p);
     k2_finalize<<<p->nseg, 32, 0, st>>>(p->tab, p->d_tilestats, a.codec, p->d_segstats, out); LAUNCHED(p);
   }
   DISPATCH(launch_encode, p, d_grad, a, out, peers, epoch, st);
