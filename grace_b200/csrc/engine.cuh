@@ -37,6 +37,7 @@ __host__ __device__ __forceinline__ char* gb_slot(char* arena, size_t chan_off, 
   return arena + chan_off + ((size_t)parity * world + src) * slot_bytes;
 }
 
+struct StepCtl;
 struct gb_plan {
   gb_comm* comm;
   gb_codec_params prm;
@@ -58,6 +59,8 @@ struct gb_plan {
   float* d_tilestats;    // [ntiles][4]
   float* d_segstats;     // [nseg][4]
   uint32_t* d_done;      // last-block-done counters
+  struct StepCtl* d_ctl; // device-side epoch / step (graph-replayable)
+  size_t par_stride;     // bytes between the parity-0 and parity-1 slot of one source rank
   // wire
   int channel;
   int channel2;          // K0 only: flags of the second (gather) phase

@@ -14,12 +14,17 @@
 #include <cuda_fp16.h>
 
 struct K0Slots { char* slot[GB_MAX_WORLD]; int n; };
+__device__ __forceinline__ void shift(K0Slots& o, size_t bytes) {
+  for (int r = 0; r < o.n; ++r) o.slot[r] += bytes;
+}
 
 // slot layout: [shard copy: cap elements (fp32 or fp16)] [reduced piece: cap fp32]
 template <bool HALF>
 __global__ void __launch_bounds__(GB_THREADS) k0_scatter(const float* __restrict__ grad, int64_t padded, int64_t cap,
                                                          K0Slots mine_in_peer, uint32_t* done, PeerPtrs peers, int channel,
-                                                         uint32_t epoch) {
+                                                         const StepCtl* ctl, size_t par_stride) {
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(mine_in_peer, par_stride);
   const int64_t n4 = padded / 4;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t e = i * 4;
@@ -42,8 +47,10 @@ __global__ void __launch_bounds__(GB_THREADS) k0_scatter(const float* __restrict
 template <bool HALF>
 __global__ void __launch_bounds__(GB_THREADS) k0_reduce(int64_t shard_len, int64_t cap, K0Slots in_mine, K0Slots mine_in_peer,
                                                         size_t result_off, float inv_world, uint32_t* done, PeerPtrs peers,
-                                                        int chan_in, int chan_out, uint32_t epoch, uint32_t* status,
-                                                        uint64_t timeout_ns) {
+                                                        int chan_in, int chan_out, const StepCtl* ctl, size_t par_stride,
+                                                        uint32_t* status, uint64_t timeout_ns) {
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) { shift(in_mine, par_stride); shift(mine_in_peer, par_stride); }
   wait_all_ranks(peers, chan_in, epoch, status, timeout_ns);
   const int64_t n4 = shard_len / 4;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
@@ -70,8 +77,10 @@ __global__ void __launch_bounds__(GB_THREADS) k0_reduce(int64_t shard_len, int64
 }
 
 __global__ void __launch_bounds__(GB_THREADS) k0_gather(float* out, int64_t padded, int64_t cap, K0Slots in_mine, size_t result_off,
-                                                        PeerPtrs peers, int channel, uint32_t epoch, uint32_t* status,
-                                                        uint64_t timeout_ns) {
+                                                        PeerPtrs peers, int channel, const StepCtl* ctl, size_t par_stride,
+                                                        uint32_t* status, uint64_t timeout_ns) {
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(in_mine, par_stride);
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   const int64_t n4 = padded / 4;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
@@ -84,7 +93,7 @@ __global__ void __launch_bounds__(GB_THREADS) k0_gather(float* out, int64_t padd
 
 #define LAUNCHED(p) do { (p)->launches++; GB_CUDA(cudaGetLastError()); } while (0)
 
-static K0Slots slots_of(gb_plan* p, bool remote, uint32_t epoch) {
+static K0Slots slots_of(gb_plan* p, bool remote, uint32_t epoch = 0) {   // parity 0; kernels shift by the device epoch
   K0Slots s;
   gb_comm* c = p->comm;
   s.n = c->world;
@@ -104,12 +113,12 @@ size_t k0_slot_bytes(int64_t padded, int world, int bits) {
 int k0_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   gb_comm* c = p->comm;
   GB_CHECK(((uintptr_t)d_grad & 15) == 0, "gradient buffer must be 16-byte aligned");
-  const uint32_t epoch = ++p->epoch;
+  ++p->epoch;
   const int64_t cap = k0_shard_cap(p->padded, c->world);
-  const K0Slots out = slots_of(p, true, epoch);
+  const K0Slots out = slots_of(p, true);
   const int grid = (int)std::min<int64_t>((p->padded / 4 + GB_THREADS - 1) / GB_THREADS, 148 * 8);
-  if (p->bits == 16) k0_scatter<true><<<grid, GB_THREADS, 0, st>>>(d_grad, p->padded, cap, out, p->d_done, gb_comm_peers(c), p->channel, epoch);
-  else k0_scatter<false><<<grid, GB_THREADS, 0, st>>>(d_grad, p->padded, cap, out, p->d_done, gb_comm_peers(c), p->channel, epoch);
+  if (p->bits == 16) k0_scatter<true><<<grid, GB_THREADS, 0, st>>>(d_grad, p->padded, cap, out, p->d_done, gb_comm_peers(c), p->channel, p->d_ctl, p->par_stride);
+  else k0_scatter<false><<<grid, GB_THREADS, 0, st>>>(d_grad, p->padded, cap, out, p->d_done, gb_comm_peers(c), p->channel, p->d_ctl, p->par_stride);
   LAUNCHED(p);
   return 0;
 }
@@ -125,9 +134,9 @@ int k0_mid(gb_plan* p, cudaStream_t st) {
   const float inv = p->prm.average ? 1.0f / (float)c->world : 1.0f;
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((len / 4 + GB_THREADS - 1) / GB_THREADS, 148 * 8));
   if (p->bits == 16)
-    k0_reduce<true><<<grid, GB_THREADS, 0, st>>>(len, cap, slots_of(p, false, epoch), slots_of(p, true, epoch), result_off, inv, p->d_done, gb_comm_peers(c), p->channel, p->channel2, epoch, c->status_dev, c->timeout_ns);
+    k0_reduce<true><<<grid, GB_THREADS, 0, st>>>(len, cap, slots_of(p, false), slots_of(p, true), result_off, inv, p->d_done, gb_comm_peers(c), p->channel, p->channel2, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns);
   else
-    k0_reduce<false><<<grid, GB_THREADS, 0, st>>>(len, cap, slots_of(p, false, epoch), slots_of(p, true, epoch), result_off, inv, p->d_done, gb_comm_peers(c), p->channel, p->channel2, epoch, c->status_dev, c->timeout_ns);
+    k0_reduce<false><<<grid, GB_THREADS, 0, st>>>(len, cap, slots_of(p, false), slots_of(p, true), result_off, inv, p->d_done, gb_comm_peers(c), p->channel, p->channel2, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns);
   LAUNCHED(p);
   p->mid_epoch = epoch;
   return 0;
@@ -142,7 +151,7 @@ int k0_recv(gb_plan* p, float* d_out, cudaStream_t st) {
   const int64_t cap = k0_shard_cap(p->padded, c->world);
   const size_t result_off = (size_t)cap * (p->bits / 8);
   const int grid = (int)std::min<int64_t>((p->padded / 4 + GB_THREADS - 1) / GB_THREADS, 148 * 8);
-  k0_gather<<<grid, GB_THREADS, 0, st>>>(d_out, p->padded, cap, slots_of(p, false, p->epoch), result_off, gb_comm_peers(c), p->channel2, p->epoch, c->status_dev, c->timeout_ns);
+  k0_gather<<<grid, GB_THREADS, 0, st>>>(d_out, p->padded, cap, slots_of(p, false), result_off, gb_comm_peers(c), p->channel2, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns);
   LAUNCHED(p);
   return 0;
 }
@@ -164,10 +173,15 @@ struct gb_nvls {
   int chan_a, chan_b;
   uint32_t epoch;
   uint32_t* d_done;
+  StepCtl* d_ctl;
   int64_t launches;
 };
 
-__global__ void k0_nvls_signal(PeerPtrs peers, int channel, uint32_t epoch) {
+__global__ void k0_nvls_signal(PeerPtrs peers, int channel, StepCtl* ctl) {
+  __shared__ uint32_t s_epoch;
+  if (threadIdx.x == 0) { ctl->epoch += 1; s_epoch = ctl->epoch; }     // device-side epoch: graph-replayable
+  __syncthreads();
+  const uint32_t epoch = s_epoch;
   if (threadIdx.x < peers.world) {
     __threadfence_system();
     st_release_sys(gb_flag(peers.base[threadIdx.x], channel, epoch & 1, peers.rank), epoch);
@@ -175,8 +189,9 @@ __global__ void k0_nvls_signal(PeerPtrs peers, int channel, uint32_t epoch) {
 }
 
 __global__ void __launch_bounds__(GB_THREADS) k0_nvls_reduce(float* mc, int64_t start, int64_t len, float inv_world, uint32_t* done,
-                                                             PeerPtrs peers, int chan_a, int chan_b, uint32_t epoch,
+                                                             PeerPtrs peers, int chan_a, int chan_b, const StepCtl* ctl,
                                                              uint32_t* status, uint64_t timeout_ns) {
+  const uint32_t epoch = ctl->epoch;
   wait_all_ranks(peers, chan_a, epoch, status, timeout_ns);
   const int64_t n4 = len / 4;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
@@ -211,8 +226,9 @@ extern "C" int gb_nvls_create(gb_comm* c, int64_t padded, gb_nvls** out) {
   size_t unused;
   if (gb_comm_alloc_channel(c, 0, &p->chan_a, &unused)) return -1;
   if (gb_comm_alloc_channel(c, 0, &p->chan_b, &unused)) return -1;
-  GB_CUDA(cudaMalloc((void**)&p->d_done, 64));
-  GB_CUDA(cudaMemset(p->d_done, 0, 64));
+  GB_CUDA(cudaMalloc((void**)&p->d_done, 128));
+  GB_CUDA(cudaMemset(p->d_done, 0, 128));
+  p->d_ctl = (StepCtl*)(p->d_done + 16);
   *out = p;
   return 0;
 }
@@ -225,8 +241,8 @@ extern "C" int gb_nvls_destroy(gb_nvls* p) {
 }
 // "my copy of the bucket is final" -- enqueue right after the last gradient of the bucket
 extern "C" int gb_nvls_signal(gb_nvls* p, void* stream) {
-  const uint32_t epoch = ++p->epoch;
-  k0_nvls_signal<<<1, 32, 0, (cudaStream_t)stream>>>(gb_comm_peers(p->comm), p->chan_a, epoch);
+  ++p->epoch;
+  k0_nvls_signal<<<1, 32, 0, (cudaStream_t)stream>>>(gb_comm_peers(p->comm), p->chan_a, p->d_ctl);
   LAUNCHED(p);
   return 0;
 }
@@ -240,7 +256,7 @@ extern "C" int gb_nvls_reduce(gb_nvls* p, void* d_multicast, int average, void* 
   if (len < 0) len = 0;
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((len / 4 + GB_THREADS - 1) / GB_THREADS, 148 * 4));
   k0_nvls_reduce<<<grid, GB_THREADS, 0, (cudaStream_t)stream>>>((float*)d_multicast, start, len, average ? 1.0f / (float)c->world : 1.0f,
-                                                               p->d_done, gb_comm_peers(c), p->chan_a, p->chan_b, p->epoch,
+                                                               p->d_done, gb_comm_peers(c), p->chan_a, p->chan_b, p->d_ctl,
                                                                c->status_dev, c->timeout_ns);
   LAUNCHED(p);
   return 0;

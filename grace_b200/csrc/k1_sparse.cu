@@ -24,6 +24,28 @@ struct SparseOut {
   int n;
 };
 
+struct SparseIn {
+  const float* vals[GB_MAX_WORLD];
+  const int32_t* idx[GB_MAX_WORLD];
+  const int2* hdr[GB_MAX_WORLD];
+  int n;
+};
+// host code passes the parity-0 slot pointers; kernels move them to the parity of the device-side epoch
+__device__ __forceinline__ void shift(SparseOut& o, size_t bytes) {
+  for (int r = 0; r < o.n; ++r) {
+    o.vals[r] = (float*)((char*)o.vals[r] + bytes);
+    o.idx[r] = (int32_t*)((char*)o.idx[r] + bytes);
+    o.hdr[r] = (int2*)((char*)o.hdr[r] + bytes);
+  }
+}
+__device__ __forceinline__ void shift(SparseIn& o, size_t bytes) {
+  for (int r = 0; r < o.n; ++r) {
+    o.vals[r] = (const float*)((const char*)o.vals[r] + bytes);
+    o.idx[r] = (const int32_t*)((const char*)o.idx[r] + bytes);
+    o.hdr[r] = (const int2*)((const char*)o.hdr[r] + bytes);
+  }
+}
+
 __device__ __forceinline__ float4 load4(const float* p, int e0, int len) {
   if (e0 + 4 <= len) return *reinterpret_cast<const float4*>(p + e0);
   float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -58,8 +80,10 @@ __device__ __forceinline__ void flush_hist(uint32_t* sh, uint32_t* dst, int nbin
 // bits of the elements whose leading bits equal the prefix chosen so far.
 template <int ROUND, bool WRITE>
 __global__ void __launch_bounds__(GB_THREADS, 8) k1_hist(SegTable t, const float* __restrict__ grad, float* work, float beta,
-                                                      float gamma, uint32_t* hist, const uint32_t* __restrict__ sel) {
+                                                      float gamma, uint32_t* hist, const uint32_t* __restrict__ sel,
+                                                      const StepCtl* ctl) {
   constexpr int NB = ROUND == 0 ? 2048 : 1024;
+  if (ROUND == 0 && WRITE && ctl->step == 0) { beta = 0.f; gamma = 1.f; }   // empty memory: compensate() is the identity
   __shared__ uint32_t sh[NB];
   const int per = (t.ntiles + gridDim.x - 1) / gridDim.x;
   const int t0 = blockIdx.x * per;
@@ -265,9 +289,11 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit(SegTable t, float* work, f
                                                       uint32_t fixed_thr, int use_fixed, int ge,
                                                       const int32_t* __restrict__ tilecnt,
                                                       SparseOut out, int64_t capacity, uint32_t* status, uint32_t* done,
-                                                      PeerPtrs peers, int channel, uint32_t epoch, int release,
-                                                      int only_ambiguous) {
+                                                      PeerPtrs peers, int channel, const StepCtl* ctl, size_t par_stride,
+                                                      int release, int only_ambiguous) {
   __shared__ int sh[GB_THREADS / 32];
+  const uint32_t epoch = ctl ? ctl->epoch : 0u;
+  if (epoch & 1) shift(out, par_stride);
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
@@ -356,8 +382,10 @@ template <bool ZERO>
 __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* work, float* work2, uint32_t* sel, uint32_t fixed_thr,
                                                            int use_fixed, int per_segment, uint32_t* cursor, SparseOut out,
                                                            int64_t capacity, uint32_t* status, uint32_t* done, PeerPtrs peers,
-                                                           int channel, uint32_t epoch, int release) {
+                                                           int channel, const StepCtl* ctl, size_t par_stride, int release) {
   __shared__ float sval[GB_TILE];
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(out, par_stride);
   __shared__ int32_t sidx[GB_TILE];
   __shared__ int scount, sbegin;
   const int lane = threadIdx.x & 31;
@@ -461,17 +489,13 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* wo
 }
 
 // Receive: ordered merge of W sparse lists into the dense aggregate.
-struct SparseIn {
-  const float* vals[GB_MAX_WORLD];
-  const int32_t* idx[GB_MAX_WORLD];
-  const int2* hdr[GB_MAX_WORLD];
-  int n;
-};
 
 __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, float* out, float divisor, PeerPtrs peers,
-                                                       int channel, uint32_t epoch, uint32_t* status, uint64_t timeout_ns,
-                                                       int wait) {
+                                                       int channel, const StepCtl* ctl, size_t par_stride, uint32_t* status,
+                                                       uint64_t timeout_ns, int wait) {
   __shared__ float acc[GB_TILE];
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(in, par_stride);
   if (wait) wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
@@ -524,7 +548,8 @@ __device__ __forceinline__ int64_t randomk_index(const SegTable& t, int seg, int
 
 template <bool WRITE>
 __global__ void __launch_bounds__(GB_THREADS) k1_axpby(SegTable t, const float* __restrict__ grad, float* work, float beta,
-                                                       float gamma) {
+                                                       float gamma, const StepCtl* ctl) {
+  if (ctl->step == 0) { beta = 0.f; gamma = 1.f; }
   const int64_t n4 = t.padded / 4;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
     float4 g = reinterpret_cast<const float4*>(grad)[i];
@@ -537,8 +562,10 @@ __global__ void __launch_bounds__(GB_THREADS) k1_axpby(SegTable t, const float* 
 
 template <bool ZERO>
 __global__ void __launch_bounds__(GB_THREADS) k1_randomk_gather(SegTable t, float* work, int64_t ktotal, uint32_t seed,
-                                                               uint32_t step, SparseOut out, uint32_t* done, PeerPtrs peers,
-                                                               int channel, uint32_t epoch) {
+                                                               SparseOut out, uint32_t* done, PeerPtrs peers, int channel,
+                                                               const StepCtl* ctl, size_t par_stride) {
+  const uint32_t epoch = ctl->epoch, step = ctl->step;
+  if (epoch & 1) shift(out, par_stride);
   for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < ktotal; p += (int64_t)gridDim.x * blockDim.x) {
     const int seg = find_segment(t.seg_kbase, t.nseg, p);
     const int64_t idx = randomk_index(t, seg, p - t.seg_kbase[seg], seed, step);
@@ -550,10 +577,12 @@ __global__ void __launch_bounds__(GB_THREADS) k1_randomk_gather(SegTable t, floa
   release_flags_last_block(done, peers, channel, epoch);
 }
 
-__global__ void __launch_bounds__(GB_THREADS) k1_randomk_scatter(SegTable t, int64_t ktotal, uint32_t seed, uint32_t step,
-                                                                SparseIn in, float* out, float divisor, PeerPtrs peers,
-                                                                int channel, uint32_t epoch, uint32_t* status,
+__global__ void __launch_bounds__(GB_THREADS) k1_randomk_scatter(SegTable t, int64_t ktotal, uint32_t seed, SparseIn in,
+                                                                float* out, float divisor, PeerPtrs peers, int channel,
+                                                                const StepCtl* ctl, size_t par_stride, uint32_t* status,
                                                                 uint64_t timeout_ns) {
+  const uint32_t epoch = ctl->epoch, step = ctl->step;
+  if (epoch & 1) shift(in, par_stride);
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < ktotal; p += (int64_t)gridDim.x * blockDim.x) {
     const int seg = find_segment(t.seg_kbase, t.nseg, p);
@@ -591,20 +620,21 @@ int k1_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   gb_comm* c = p->comm;
   const bool mem = p->prm.memory == GB_MEM_RESIDUAL;
   // first call: the memory is empty, compensate() returns the gradient unchanged
-  const float beta = p->step == 0 ? 0.f : p->prm.beta;
-  const float gamma = p->step == 0 ? 1.f : p->prm.gamma;
+  const float beta = p->prm.beta, gamma = p->prm.gamma;     // kernels apply the first-call rule (device-side step)
   float* work = mem ? p->d_state0 : const_cast<float*>(d_grad);
-  const uint32_t epoch = ++p->epoch;
+  ++p->epoch;                                               // host mirror of the device-side epoch
   SparseOut out;
-  slot_views(p, epoch & 1, true, &out, nullptr);
+  slot_views(p, 0, true, &out, nullptr);
+  StepCtl* ctl = p->d_ctl;
+  const size_t ps = p->par_stride;
   const PeerPtrs peers = gb_comm_peers(c);
   const int grid = grid_for(p->ntiles);
 
   if (p->prm.codec == GB_CODEC_RANDOMK) {
-    if (mem) { k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma); LAUNCHED(p); }
+    if (mem) { k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, ctl); LAUNCHED(p); }
     const int g2 = (int)std::min<int64_t>((p->ktotal + GB_THREADS - 1) / GB_THREADS, 148 * 8);
-    if (mem) k1_randomk_gather<true><<<g2, GB_THREADS, 0, st>>>(p->tab, work, p->ktotal, p->prm.seed, p->step, out, p->d_done, peers, p->channel, epoch);
-    else k1_randomk_gather<false><<<g2, GB_THREADS, 0, st>>>(p->tab, work, p->ktotal, p->prm.seed, p->step, out, p->d_done, peers, p->channel, epoch);
+    if (mem) k1_randomk_gather<true><<<g2, GB_THREADS, 0, st>>>(p->tab, work, p->ktotal, p->prm.seed, out, p->d_done, peers, p->channel, ctl, ps);
+    else k1_randomk_gather<false><<<g2, GB_THREADS, 0, st>>>(p->tab, work, p->ktotal, p->prm.seed, out, p->d_done, peers, p->channel, ctl, ps);
     LAUNCHED(p);
     return 0;
   }
@@ -616,49 +646,48 @@ int k1_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   uint32_t* cursor = p->d_done + 2;
   if (fixed) {
     // variable-size payload: one global cursor, a single compaction pass
-    if (mem) { k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma); LAUNCHED(p); }
+    if (mem) { k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, ctl); LAUNCHED(p); }
     GB_CUDA(cudaMemsetAsync(cursor, 0, 4, st));
-    if (mem) k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, 1, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
-    else k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, 1, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+    if (mem) k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, 1, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, ctl, ps, 1);
+    else k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, thr_bits, 1, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, ctl, ps, 1);
     LAUNCHED(p);
     return 0;
   }
-  if (mem) k1_hist<0, true><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel);
-  else k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel);
+  if (mem) k1_hist<0, true><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel, ctl);
+  else k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel, ctl);
   LAUNCHED(p);
   k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 0); LAUNCHED(p);
-  k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel); LAUNCHED(p);
+  k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel, ctl); LAUNCHED(p);
   k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 1); LAUNCHED(p);
-  k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel); LAUNCHED(p);
+  k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, beta, gamma, p->d_hist, p->d_sel, ctl); LAUNCHED(p);
   k1_select<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_hist, p->d_sel, 2); LAUNCHED(p);
   // segments without tie ambiguity (nearly all): one unordered compaction pass; the others: count /
   // scan / index-ordered emit restricted to their tiles.  The last kernel releases the flags.
-  if (mem) k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 1, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 0);
-  else k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 1, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 0);
+  if (mem) k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 1, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, ctl, ps, 0);
+  else k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 1, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, ctl, ps, 0);
   LAUNCHED(p);
   k1_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel, 0u, 0, 0, p->d_tilecnt, 1); LAUNCHED(p);
   k1_scan<true><<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_sel, p->d_tilecnt, 1); LAUNCHED(p);
-  if (mem) k1_emit<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1, 1);
-  else k1_emit<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1, 1);
+  if (mem) k1_emit<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, ctl, ps, 1, 1);
+  else k1_emit<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, nullptr, p->d_sel, 0u, 0, 0, p->d_tilecnt, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, ctl, ps, 1, 1);
   LAUNCHED(p);
   return 0;
 }
 
 int k1_recv(gb_plan* p, float* d_out, cudaStream_t st) {
   gb_comm* c = p->comm;
-  const uint32_t epoch = p->epoch;
   SparseIn in;
-  slot_views(p, epoch & 1, false, nullptr, &in);
+  slot_views(p, 0, false, nullptr, &in);
   const PeerPtrs peers = gb_comm_peers(c);
   const float divisor = p->prm.average ? (float)c->world : 1.f;
   if (p->prm.codec == GB_CODEC_RANDOMK) {
     GB_CUDA(cudaMemsetAsync(d_out, 0, (size_t)p->padded * 4, st));
     const int g2 = (int)std::min<int64_t>((p->ktotal + GB_THREADS - 1) / GB_THREADS, 148 * 8);
-    k1_randomk_scatter<<<g2, GB_THREADS, 0, st>>>(p->tab, p->ktotal, p->prm.seed, p->step - 1, in, d_out, divisor, peers, p->channel, epoch, c->status_dev, c->timeout_ns);
+    k1_randomk_scatter<<<g2, GB_THREADS, 0, st>>>(p->tab, p->ktotal, p->prm.seed, in, d_out, divisor, peers, p->channel, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns);
     LAUNCHED(p);
     return 0;
   }
-  k1_merge<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, epoch, c->status_dev, c->timeout_ns, 1);
+  k1_merge<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns, 1);
   LAUNCHED(p);
   return 0;
 }
@@ -688,7 +717,8 @@ __global__ void __launch_bounds__(GB_THREADS) k1_dgc_accumulate(SegTable t, cons
 // One CTA per segment: k-th largest magnitude among max(1, int(0.01 n)) positions sampled
 // with replacement (Philox stream 1), by three histogram rounds over the sample.
 __global__ void __launch_bounds__(GB_THREADS) k1_dgc_sample(SegTable t, const float* __restrict__ v, double ratio, uint32_t seed,
-                                                           uint32_t step, uint32_t* sel) {
+                                                           const StepCtl* ctl, uint32_t* sel) {
+  const uint32_t step = ctl->step;
   __shared__ uint32_t hist[2048];
   __shared__ uint32_t s_prefix, s_krem;
   const int seg = blockIdx.x;
@@ -775,9 +805,11 @@ static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   gb_comm* c = p->comm;
   GB_CHECK(p->prm.memory == GB_MEM_DGC || p->prm.memory == GB_MEM_NONE || p->prm.memory == GB_MEM_RESIDUAL,
            "unsupported memory for DGC");
-  const uint32_t epoch = ++p->epoch;
+  ++p->epoch;
   SparseOut out;
-  slot_views(p, epoch & 1, true, &out, nullptr);
+  slot_views(p, 0, true, &out, nullptr);
+  StepCtl* ctl = p->d_ctl;
+  const size_t ps = p->par_stride;
   const PeerPtrs peers = gb_comm_peers(c);
   const int grid = grid_for(p->ntiles);
   float* work;
@@ -787,13 +819,12 @@ static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
     work = p->d_state0;
     work2 = p->d_state1;
   } else if (p->prm.memory == GB_MEM_RESIDUAL) {
-    k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, p->step == 0 ? 0.f : p->prm.beta,
-                                                  p->step == 0 ? 1.f : p->prm.gamma); LAUNCHED(p);
+    k1_axpby<true><<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, p->prm.beta, p->prm.gamma, ctl); LAUNCHED(p);
     work = p->d_state0;
   } else {
     work = const_cast<float*>(d_grad);
   }
-  k1_dgc_sample<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, work, p->prm.ratio, p->prm.seed, p->step, p->d_sel); LAUNCHED(p);
+  k1_dgc_sample<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, work, p->prm.ratio, p->prm.seed, ctl, p->d_sel); LAUNCHED(p);
   for (int it = 0; it < 10; ++it) {
     k1_dgc_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel); LAUNCHED(p);
     k1_dgc_adjust<<<(p->nseg + 127) / 128, 128, 0, st>>>(p->tab, p->prm.ratio, p->d_sel); LAUNCHED(p);
@@ -801,9 +832,9 @@ static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   uint32_t* cursor = p->d_done + 2;
   GB_CUDA(cudaMemsetAsync(cursor, 0, 4, st));
   if (p->prm.memory != GB_MEM_NONE)
-    k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+    k1_emit_fast<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, ctl, ps, 1);
   else
-    k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, epoch, 1);
+    k1_emit_fast<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, work2, p->d_sel, 0u, 0, 0, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, ctl, ps, 1);
   LAUNCHED(p);
   return 0;
 }
@@ -872,11 +903,11 @@ int k1_topk_single(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_
   const SegTable t = single_table(tab, n, L.ntiles);
   float* work = const_cast<float*>(d_x);
   const int hgrid = std::min(L.ntiles, 148 * 8), grid = grid_for(L.ntiles);
-  k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
+  k1_hist<0, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel, nullptr);
   k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 0);
-  k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
+  k1_hist<1, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel, nullptr);
   k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 1);
-  k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel);
+  k1_hist<2, false><<<hgrid, GB_THREADS, 0, st>>>(t, d_x, work, 0.f, 1.f, hist, sel, nullptr);
   k1_select<<<1, GB_THREADS, 0, st>>>(t, hist, sel, 2);
   k1_count<<<grid, GB_THREADS, 0, st>>>(t, work, sel, 0u, 0, 0, cnt, 0);
   k1_scan<true><<<1, GB_THREADS, 0, st>>>(t, sel, cnt, 0);
@@ -887,7 +918,7 @@ int k1_topk_single(const float* d_x, int64_t n, int64_t k, float* d_vals, int32_
   out.hdr[0] = (int2*)(scratch + L.off_hdr);
   PeerPtrs none;
   memset(&none, 0, sizeof(none));
-  k1_emit<false><<<grid, GB_THREADS, 0, st>>>(t, work, nullptr, sel, 0u, 0, 0, cnt, out, k, (uint32_t*)(scratch + L.off_sel) + 2, nullptr, none, 0, 0, 0, 0);
+  k1_emit<false><<<grid, GB_THREADS, 0, st>>>(t, work, nullptr, sel, 0u, 0, 0, cnt, out, k, (uint32_t*)(scratch + L.off_sel) + 2, nullptr, none, 0, nullptr, 0, 0, 0);
   GB_CUDA(cudaGetLastError());
   return 0;
 }

@@ -52,6 +52,21 @@ struct QuantArgs {
 struct WireOut { char* slot[GB_MAX_WORLD]; int n; };   // my slot inside every peer
 struct WireIn { const char* slot[GB_MAX_WORLD]; int n; };  // every rank's slot inside my arena
 
+// first-call rules (empty memory: compensate() is the identity; Signum: m = x) and the Philox step
+// come from the device-side control block
+__device__ __forceinline__ QuantArgs resolve(QuantArgs a, const StepCtl* ctl) {
+  const uint32_t s = ctl->step;
+  if (s == 0) { a.beta = 0.f; a.gamma = 1.f; a.mom = 0.f; }
+  a.step = s;
+  return a;
+}
+__device__ __forceinline__ void shift(WireOut& o, size_t bytes) {
+  for (int r = 0; r < o.n; ++r) o.slot[r] += bytes;
+}
+__device__ __forceinline__ void shift(WireIn& o, size_t bytes) {
+  for (int r = 0; r < o.n; ++r) o.slot[r] += bytes;
+}
+
 __device__ __forceinline__ float comp1(const QuantArgs& a, float r, float g) {
   return a.has_mem ? __fadd_rn(__fmul_rn(a.beta, r), __fmul_rn(a.gamma, g)) : g;
 }
@@ -60,9 +75,10 @@ __device__ __forceinline__ float comp1(const QuantArgs& a, float r, float g) {
 // tilestats[tile][8] = { sum x, sum x^2, max|x|, sum|x|, count(x<0), sum(x<0), M2 about the tile mean, - }
 template <bool NEED_M2>
 __global__ void __launch_bounds__(GB_THREADS, NEED_M2 ? 4 : 8) k2_stats(SegTable t, const float* __restrict__ grad,
-                                                                        const float* __restrict__ res, QuantArgs a,
-                                                                        float* tilestats) {
+                                                                        const float* __restrict__ res, QuantArgs a_in,
+                                                                        const StepCtl* ctl, float* tilestats) {
   __shared__ float sh[6][GB_THREADS / 32];
+  const QuantArgs a = resolve(a_in, ctl);
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
@@ -130,7 +146,9 @@ __global__ void __launch_bounds__(GB_THREADS, NEED_M2 ? 4 : 8) k2_stats(SegTable
 // One warp per segment; tiles are combined in a fixed order in double precision, so the
 // scalars are reproducible run to run.  segstats[seg][4] is codec specific:
 //   QSGD {norm}  TERNGRAD {scalar}  EFSIGNSGD {mean|x|}  ONEBIT {mean_neg, mean_pos}  U8BIT {max|x|}
-__global__ void k2_finalize(SegTable t, const float* __restrict__ tilestats, int codec, float* segstats, WireOut out) {
+__global__ void k2_finalize(SegTable t, const float* __restrict__ tilestats, int codec, float* segstats, WireOut out,
+                            const StepCtl* ctl, size_t par_stride) {
+  if (ctl->epoch & 1) shift(out, par_stride);
   const int seg = blockIdx.x;
   const int lane = threadIdx.x;
   const int first = t.seg_tile0[seg], last = t.seg_tile0[seg + 1];
@@ -268,9 +286,12 @@ struct NeedsRng { static constexpr bool value = CODEC == GB_CODEC_QSGD || CODEC 
 // coalesced and each word is stored once per peer.
 template <int CODEC, int BITS>
 __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float* __restrict__ grad, float* res, float* mom,
-                                                        const float* __restrict__ segstats, QuantArgs a, WireOut out,
+                                                        const float* __restrict__ segstats, QuantArgs a_in, WireOut out,
                                                         size_t hdr_bytes, uint32_t* done, PeerPtrs peers, int channel,
-                                                        uint32_t epoch) {
+                                                        const StepCtl* ctl, size_t par_stride) {
+  const QuantArgs a = resolve(a_in, ctl);
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(out, par_stride);
   constexpr int SUB = 4 * BITS;                         // bits produced per thread
   constexpr int LANES = SUB >= 32 ? 1 : 32 / SUB;       // lanes sharing one word
   constexpr int WORDS = SUB >= 32 ? SUB / 32 : 1;       // words per thread
@@ -362,7 +383,10 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
 template <int CODEC, int BITS>
 __global__ void __launch_bounds__(GB_THREADS) k2_decode(SegTable t, WireIn in, size_t hdr_bytes, float* outp, int quantum,
                                                         int final_mode, float divisor, PeerPtrs peers, int channel,
-                                                        uint32_t epoch, uint32_t* status, uint64_t timeout_ns) {
+                                                        const StepCtl* ctl, size_t par_stride, uint32_t* status,
+                                                        uint64_t timeout_ns) {
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(in, par_stride);
   __shared__ float s_tab[128];
   if (CODEC == GB_CODEC_U8BIT && threadIdx.x < 128) s_tab[threadIdx.x] = g_u8_table[threadIdx.x];
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
@@ -430,9 +454,10 @@ static bool needs_stats(int codec) {
 
 template <int CODEC, int BITS>
 static int launch_encode(gb_plan* p, const float* g, const QuantArgs& a, const WireOut& out, const PeerPtrs& peers,
-                         uint32_t epoch, cudaStream_t st) {
+                         cudaStream_t st) {
   k2_encode<CODEC, BITS><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, g, p->d_state0, p->d_state1, p->d_segstats, a, out,
-                                                                    p->hdr_bytes, p->d_done, peers, p->channel, epoch);
+                                                                    p->hdr_bytes, p->d_done, peers, p->channel, p->d_ctl,
+                                                                    p->par_stride);
   LAUNCHED(p);
   return 0;
 }
@@ -440,8 +465,8 @@ static int launch_encode(gb_plan* p, const float* g, const QuantArgs& a, const W
 template <int CODEC, int BITS>
 static int launch_decode(gb_plan* p, float* o, const WireIn& in, const PeerPtrs& peers, int mode, float divisor, cudaStream_t st) {
   k2_decode<CODEC, BITS><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, p->hdr_bytes, o, p->prm.quantum_num, mode, divisor,
-                                                                    peers, p->channel, p->epoch, p->comm->status_dev,
-                                                                    p->comm->timeout_ns);
+                                                                    peers, p->channel, p->d_ctl, p->par_stride,
+                                                                    p->comm->status_dev, p->comm->timeout_ns);
   LAUNCHED(p);
   return 0;
 }
@@ -470,24 +495,24 @@ int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   QuantArgs a;
   a.codec = p->prm.codec;
   a.has_mem = p->prm.memory == GB_MEM_RESIDUAL;
-  a.beta = p->step == 0 ? 0.f : p->prm.beta;      // empty memory: compensate() is the identity
-  a.gamma = p->step == 0 ? 1.f : p->prm.gamma;
-  a.mom = p->step == 0 ? 0.f : p->prm.momentum;   // Signum: first call m = x
+  a.beta = p->prm.beta;                 // steady-state values; kernels apply the first-call rules
+  a.gamma = p->prm.gamma;
+  a.mom = p->prm.momentum;
   a.quantum = p->prm.quantum_num;
   a.seed = p->prm.seed;
-  a.step = p->step;
-  const uint32_t epoch = ++p->epoch;
+  a.step = 0;
+  ++p->epoch;                           // host mirror of the device-side epoch
   WireOut out;
   out.n = c->world;
-  for (int r = 0; r < c->world; ++r) out.slot[r] = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, epoch & 1, c->rank);
+  for (int r = 0; r < c->world; ++r) out.slot[r] = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, 0, c->rank);
   const PeerPtrs peers = gb_comm_peers(c);
   if (needs_stats(a.codec)) {
-    if (a.codec == GB_CODEC_TERNGRAD) k2_stats<true><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_tilestats);
-    else k2_stats<false><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_tilestats);
+    if (a.codec == GB_CODEC_TERNGRAD) k2_stats<true><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_ctl, p->d_tilestats);
+    else k2_stats<false><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_ctl, p->d_tilestats);
     LAUNCHED(p);
-    k2_finalize<<<p->nseg, 32, 0, st>>>(p->tab, p->d_tilestats, a.codec, p->d_segstats, out); LAUNCHED(p);
+    k2_finalize<<<p->nseg, 32, 0, st>>>(p->tab, p->d_tilestats, a.codec, p->d_segstats, out, p->d_ctl, p->par_stride); LAUNCHED(p);
   }
-  DISPATCH(launch_encode, p, d_grad, a, out, peers, epoch, st);
+  DISPATCH(launch_encode, p, d_grad, a, out, peers, st);
 }
 
 int k2_recv(gb_plan* p, float* d_out, cudaStream_t st) {
@@ -495,7 +520,7 @@ int k2_recv(gb_plan* p, float* d_out, cudaStream_t st) {
   GB_CHECK(((uintptr_t)d_out & 15) == 0, "output buffer must be 16-byte aligned");
   WireIn in;
   in.n = c->world;
-  for (int r = 0; r < c->world; ++r) in.slot[r] = gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, p->epoch & 1, r);
+  for (int r = 0; r < c->world; ++r) in.slot[r] = gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, 0, r);
   const PeerPtrs peers = gb_comm_peers(c);
   int mode = 0;
   float divisor = p->prm.average ? (float)c->world : 1.f;

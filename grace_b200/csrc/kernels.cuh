@@ -17,6 +17,13 @@ int k0_mid(gb_plan* p, cudaStream_t st);
 int k0_recv(gb_plan* p, float* d_out, cudaStream_t st);
 size_t k0_slot_bytes(int64_t padded, int world, int bits);
 
+// Per-plan step control block in DEVICE memory.  Kernels take the epoch (flag value, slot parity)
+// and the codec step (Philox counter, first-call rules) from here instead of from kernel
+// arguments, so a captured CUDA graph of a whole training step can be replayed: the tick kernel
+// at the head of every send advances the block on the device.
+struct StepCtl { uint32_t epoch, step, next_step, pad; };
+void gb_launch_tick(StepCtl* ctl, cudaStream_t st);       // plan.cu
+
 // Last-block-done flag release shared by the send kernels: every CTA calls this after its
 // final peer store; the CTA that arrives last publishes `epoch` to all peers.
 __device__ __forceinline__ void release_flags_last_block(uint32_t* done, PeerPtrs peers, int channel, uint32_t epoch) {

@@ -96,7 +96,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   add((nseg + 1) * 8); add(nseg * 4); add(nseg * 4); add((nseg + 1) * 8); add(nseg * 4); add((nseg + 1) * 4);
   add(p->ntiles * 4);
   add((size_t)nseg * 2048 * 4); add((size_t)nseg * 4 * 4); add((size_t)p->ntiles * 2 * 4 + 8);
-  add((size_t)p->ntiles * 8 * 4); add((size_t)nseg * 4 * 4); add(64);
+  add((size_t)p->ntiles * 8 * 4); add((size_t)nseg * 4 * 4); add(64); add(64);
   GB_CUDA(cudaMalloc(&p->d_tables, bytes));
   GB_CUDA(cudaMemset(p->d_tables, 0, bytes));
   char* cur = (char*)p->d_tables;
@@ -113,6 +113,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->d_tilestats = carve<float>(cur, (size_t)p->ntiles * 8);
   p->d_segstats = carve<float>(cur, (size_t)nseg * 4);
   p->d_done = carve<uint32_t>(cur, 16);
+  p->d_ctl = (StepCtl*)carve<uint32_t>(cur, 16);
   GB_CUDA(cudaMemcpy(d_off, p->h_off.data(), (nseg + 1) * 8, cudaMemcpyHostToDevice));
   GB_CUDA(cudaMemcpy(d_numel, p->h_numel.data(), nseg * 4, cudaMemcpyHostToDevice));
   GB_CUDA(cudaMemcpy(d_k, p->h_k.data(), nseg * 4, cudaMemcpyHostToDevice));
@@ -155,6 +156,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
     if (gb_comm_alloc_channel(c, 0, &p->channel2, &unused)) { gb_plan_destroy(p); return -1; }
   }
   p->slot_bytes = (p->slot_bytes + 255) & ~size_t(255);
+  p->par_stride = (size_t)c->world * p->slot_bytes;
   GB_CUDA(cudaDeviceSynchronize());
   *out = p;
   return 0;
@@ -197,12 +199,30 @@ extern "C" int gb_plan_state_write(gb_plan* p, int which, const void* d_src, voi
   GB_CUDA(cudaMemcpyAsync(s, d_src, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return 0;
 }
-extern "C" int gb_plan_get_step(gb_plan* p, uint32_t* step) { *step = p->step; return 0; }
-extern "C" int gb_plan_set_step(gb_plan* p, uint32_t step) { p->step = step; return 0; }
+// the device copy is authoritative: replays of a captured graph advance it without the host
+extern "C" int gb_plan_get_step(gb_plan* p, uint32_t* step) {
+  GB_CUDA(cudaMemcpy(step, &p->d_ctl->next_step, 4, cudaMemcpyDeviceToHost));
+  p->step = *step;
+  return 0;
+}
+extern "C" int gb_plan_set_step(gb_plan* p, uint32_t step) {
+  p->step = step;
+  GB_CUDA(cudaMemcpy(&p->d_ctl->next_step, &step, 4, cudaMemcpyHostToDevice));
+  return 0;
+}
 extern "C" int gb_plan_launches(gb_plan* p, int64_t* out) { *out = p->launches; return 0; }
+
+__global__ void gb_tick_kernel(StepCtl* c) {
+  c->epoch += 1;
+  c->step = c->next_step;
+  c->next_step += 1;
+}
+void gb_launch_tick(StepCtl* ctl, cudaStream_t st) { gb_tick_kernel<<<1, 1, 0, st>>>(ctl); }
 
 extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
+  gb_launch_tick(p->d_ctl, st);
+  p->launches++;
   int rc = p->dense2 ? k0_send(p, d_grad, st) : gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
   if (rc) return rc;
   p->step++;
@@ -211,7 +231,7 @@ extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
 
 extern "C" int gb_plan_recv(gb_plan* p, float* d_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  GB_CHECK(p->epoch > 0, "gb_plan_recv before any gb_plan_send");
+  GB_CHECK(p->epoch > 0, "gb_plan_recv before any gb_plan_send");   // host mirror; counts captured sends too
   if (p->dense2) return k0_recv(p, d_out, st);
   return gb_codec_is_sparse(p->prm.codec) ? k1_recv(p, d_out, st) : k2_recv(p, d_out, st);
 }

@@ -82,6 +82,26 @@ def main():
             opt.step()
         return torch.cat([p.detach().flatten() for p in model.parameters()])
 
+    # flag-protocol stress: ranks arrive in random order with random device-side delays, many
+    # back-to-back exchanges on the same double-buffered slots (SURVEY §5 race-detection row)
+    import random
+    rnd = random.Random(1234 + rank)
+    params = dict(compressor="topk", memory="residual", communicator="allgather", world_size=world, compress_ratio=0.02)
+    fast = grace_from_params(params)
+    gen = torch.Generator(device="cuda").manual_seed(77 + rank)
+    for it in range(40):
+        if rnd.random() < 0.5:
+            torch.cuda._sleep(int(rnd.random() * 3e6))          # up to ~1.5 ms of skew on this rank
+        g = torch.randn(50000, device="cuda", generator=gen)
+        a = fast.step(g, "stress").clone()
+        if not same_on_all_ranks(a):
+            failures.append("stress iteration %d: ranks disagree" % it)
+            break
+        k = max(1, int(50000 * 0.02))
+        if int((a != 0).sum()) > world * k:
+            failures.append("stress iteration %d: %d non-zeros > W*k" % (it, int((a != 0).sum())))
+            break
+
     # dense buckets: NVLS multimem when the host has it, else the P2P two-shot plan -- same API
     def train_dense():
         import copy
