@@ -73,6 +73,7 @@ struct gb_psgd {
   float *d_pacc, *d_qacc;   // local accumulators [prows][4], [qrows][4]
   float *d_ph;              // P^ [prows][4]
   uint32_t *d_cnt1, *d_cnt2, *d_done;
+  StepCtl* d_ctl;           // device-side epoch / step (graph-replayable)
   struct PsBand* d_bands;
   int nbands;
   int64_t qpad, ppad;       // row pitch of d_q0t / d_pht
@@ -147,6 +148,9 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int a_mn_major) {
 // MODE 2:  D[128 x 16] = M[k0:k1, m0:m0+128]^T * P^[k0:k1, :]       (A MN-major, K = rows of M)
 // warp 0: TMA producer; warp 1: TMEM alloc + MMA issuer; warps 2-5: epilogue (TMEM lane quarter = warp % 4)
 struct PsPeers { float* slot[GB_MAX_WORLD]; int n; };
+__device__ __forceinline__ void shift(PsPeers& o, size_t bytes) {
+  for (int r = 0; r < o.n; ++r) o.slot[r] = (float*)((char*)o.slot[r] + bytes);
+}
 
 __device__ int g_dbg[8];   // debugging overrides for the MODE 2 descriptors: {enable, lbo, sbo, k_step, a_major, dump}
 __device__ float g_dbg_dump[8192];
@@ -154,8 +158,9 @@ __device__ float g_dbg_dump[8192];
 template <int MODE>
 __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ items, const PsMat* __restrict__ mats,
                                                   const CUtensorMap* __restrict__ maps, float* acc, uint32_t* tile_cnt,
-                                                  PsPeers peers) {
+                                                  PsPeers peers, const StepCtl* ctl, size_t par_stride) {
   extern __shared__ uint8_t smem_raw[];
+  if (ctl->epoch & 1) shift(peers, par_stride);
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
   uint8_t* sB = smem + PS_STAGES * PS_A_BYTES;
@@ -323,7 +328,9 @@ __global__ void __launch_bounds__(GB_THREADS) k3_gemm2_simt(const PsMat* __restr
 // pushes the rows of fallback matrices to every peer, then the last CTA releases the epoch flags
 __global__ void __launch_bounds__(GB_THREADS) k3_flag(const PsMat* __restrict__ mats, int nmat, int which, const float* acc,
                                                      PsPeers peers_slots, uint32_t* done, PeerPtrs peers, int channel,
-                                                     uint32_t epoch) {
+                                                     const StepCtl* ctl, size_t par_stride) {
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(peers_slots, par_stride);
   for (int mi = 0; mi < nmat; ++mi) {
     const PsMat mt = mats[mi];
     if (mt.tc) continue;
@@ -338,8 +345,9 @@ __global__ void __launch_bounds__(GB_THREADS) k3_flag(const PsMat* __restrict__ 
 
 // ---------------------------------------------------------------- element-wise prep
 __global__ void __launch_bounds__(GB_THREADS) k3_prep(int64_t padded, const float* __restrict__ grad, const float* __restrict__ res,
-                                                     float* work, int has_res, float* pacc, int64_t np, float* qacc, int64_t nq,
-                                                     uint32_t* cnt, int ncnt) {
+                                                     float* work, int has_mem, float* pacc, int64_t np, float* qacc, int64_t nq,
+                                                     uint32_t* cnt, int ncnt, const StepCtl* ctl) {
+  const int has_res = has_mem && ctl->step > 0;      // first call: the memory is empty
   const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = tid; i < padded / 4; i += nth) {
     float4 g = reinterpret_cast<const float4*>(grad)[i];
@@ -437,7 +445,8 @@ __device__ void cholqr2_inplace(float* buf, int len, int r, float* sh) {
 // Q0 = orth(normal) per matrix; scratch rows live in qacc (zeroed again afterwards by k3_prep order: prep runs first,
 // so k3_q0 uses its own scratch `q0` [qrows][4]) ; writes Q0^T [16][qpad]
 __global__ void __launch_bounds__(512) k3_q0(const PsMat* __restrict__ mats, float* q0, float* q0t, int64_t qpad, uint32_t seed,
-                                             uint32_t step) {
+                                             const StepCtl* ctl) {
+  const uint32_t step = ctl->step;
   __shared__ float sh[512];
   const PsMat mt = mats[blockIdx.x];
   float* buf = q0 + (size_t)mt.qrow0 * 4;
@@ -463,11 +472,16 @@ __global__ void __launch_bounds__(512) k3_q0(const PsMat* __restrict__ mats, flo
 }
 
 struct PsIn { const float* slot[GB_MAX_WORLD]; int n; };
+__device__ __forceinline__ void shift(PsIn& o, size_t bytes) {
+  for (int r = 0; r < o.n; ++r) o.slot[r] = (const float*)((const char*)o.slot[r] + bytes);
+}
 
 // wait flags; P = mean_r P_r; orthogonalise; write P^ [prows][4] and P^^T [16][ppad]
 __global__ void __launch_bounds__(512) k3_orth(const PsMat* __restrict__ mats, PsIn in, float inv_world, float* ph, float* pht,
-                                               int64_t ppad, PeerPtrs peers, int channel, uint32_t epoch, uint32_t* status,
-                                               uint64_t timeout_ns) {
+                                               int64_t ppad, PeerPtrs peers, int channel, const StepCtl* ctl, size_t par_stride,
+                                               uint32_t* status, uint64_t timeout_ns) {
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(in, par_stride);
   __shared__ float sh[512];
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   const PsMat mt = mats[blockIdx.x];
@@ -494,7 +508,10 @@ __global__ void __launch_bounds__(512) k3_orth(const PsMat* __restrict__ mats, P
 __global__ void __launch_bounds__(GB_THREADS) k3_final(const PsBand* __restrict__ bands, const PsMat* __restrict__ mats, PsIn in,
                                                       float inv_world, const float* __restrict__ ph, const float* __restrict__ work,
                                                       float* res, int has_res, float* out, PeerPtrs peers, int channel,
-                                                      uint32_t epoch, uint32_t* status, uint64_t timeout_ns) {
+                                                      const StepCtl* ctl, size_t par_stride, uint32_t* status,
+                                                      uint64_t timeout_ns) {
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(in, par_stride);
   __shared__ float4 sp[32];
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   const PsBand b = bands[blockIdx.x];
@@ -618,6 +635,7 @@ extern "C" int gb_psgd_create(gb_comm* c, int nmat, const int64_t* rows, const i
   GB_CUDA(cudaMalloc((void**)&p->d_cnt1, (p->ntiles1 + p->ntiles2 + 64) * 4));
   p->d_cnt2 = p->d_cnt1 + p->ntiles1;
   p->d_done = p->d_cnt1 + p->ntiles1 + p->ntiles2;
+  p->d_ctl = (StepCtl*)(p->d_done + 16);
   GB_CUDA(cudaMemset(p->d_cnt1, 0, (p->ntiles1 + p->ntiles2 + 64) * 4));
   p->nbands = (int)bands.size();
   GB_CUDA(cudaMalloc((void**)&p->d_bands, sizeof(PsBand) * bands.size()));
@@ -663,8 +681,16 @@ extern "C" int64_t gb_psgd_padded_numel(gb_psgd* p) { return p->padded; }
 extern "C" int gb_psgd_offsets(gb_psgd* p, int64_t* out) { for (int i = 0; i < p->nmat; ++i) out[i] = p->h_off[i]; return 0; }
 extern "C" int gb_psgd_launches(gb_psgd* p, int64_t* out) { *out = p->launches; return 0; }
 extern "C" int gb_psgd_tc_matrices(gb_psgd* p) { int n = 0; for (auto& m : p->h_mat) n += m.tc; return n; }
-extern "C" int gb_psgd_get_step(gb_psgd* p, uint32_t* s) { *s = p->step; return 0; }
-extern "C" int gb_psgd_set_step(gb_psgd* p, uint32_t s) { p->step = s; return 0; }
+extern "C" int gb_psgd_get_step(gb_psgd* p, uint32_t* s) {
+  GB_CUDA(cudaMemcpy(s, &p->d_ctl->next_step, 4, cudaMemcpyDeviceToHost));
+  p->step = *s;
+  return 0;
+}
+extern "C" int gb_psgd_set_step(gb_psgd* p, uint32_t s) {
+  p->step = s;
+  GB_CUDA(cudaMemcpy(&p->d_ctl->next_step, &s, 4, cudaMemcpyHostToDevice));
+  return 0;
+}
 extern "C" int gb_psgd_residual(gb_psgd* p, void** ptr, size_t* bytes) { *ptr = p->d_res; *bytes = p->d_res ? (size_t)p->padded * 4 : 0; return 0; }
 // debugging / tests: copy an internal buffer out.  what: 0 P accumulator, 1 Q accumulator, 2 Q0^T, 3 P^^T, 4 P^, 5 work
 extern "C" int gb_psgd_peek(gb_psgd* p, int what, float* d_dst, int64_t nfloats, void* stream) {
@@ -692,12 +718,12 @@ extern "C" int gb_psgd_debug_dump(float* h_dst) {
 }
 extern "C" int64_t gb_psgd_wire_bytes(gb_psgd* p) { return (int64_t)(p->prows + p->qrows) * PS_R * 4; }
 
-static PsPeers peer_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch) {
+static PsPeers peer_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch = 0) {   // parity 0
   PsPeers s; gb_comm* c = p->comm; s.n = c->world;
   for (int r = 0; r < c->world; ++r) s.slot[r] = (float*)gb_slot(c->peer[r], chan_off, slot_bytes, c->world, epoch & 1, c->rank);
   return s;
 }
-static PsIn my_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch) {
+static PsIn my_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch = 0) {        // parity 0
   PsIn s; gb_comm* c = p->comm; s.n = c->world;
   for (int r = 0; r < c->world; ++r) s.slot[r] = (const float*)gb_slot(c->base, chan_off, slot_bytes, c->world, epoch & 1, r);
   return s;
@@ -708,18 +734,21 @@ extern "C" int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   gb_comm* c = p->comm;
   GB_CHECK(((uintptr_t)d_grad & 15) == 0, "gradient buffer must be 16-byte aligned");
-  const uint32_t epoch = ++p->epoch;
-  k3_prep<<<148 * 4, GB_THREADS, 0, st>>>(p->padded, d_grad, p->d_res, p->d_work, p->has_mem && p->step > 0, p->d_pacc,
-                                         p->prows * PS_R, p->d_qacc, p->qrows * PS_R, p->d_cnt1, p->ntiles1 + p->ntiles2);
+  ++p->epoch;
+  gb_launch_tick(p->d_ctl, st);
+  const size_t psp = (size_t)c->world * p->slot_p, psq = (size_t)c->world * p->slot_q;
+  (void)psq;
+  k3_prep<<<148 * 4, GB_THREADS, 0, st>>>(p->padded, d_grad, p->d_res, p->d_work, p->has_mem, p->d_pacc,
+                                         p->prows * PS_R, p->d_qacc, p->qrows * PS_R, p->d_cnt1, p->ntiles1 + p->ntiles2, p->d_ctl);
   LAUNCHED(p);
-  k3_q0<<<p->nmat, 512, 0, st>>>(p->d_mat, p->d_qacc + (size_t)(p->qrows + 8) * PS_R, p->d_q0t, p->qpad, p->seed, p->step);
+  k3_q0<<<p->nmat, 512, 0, st>>>(p->d_mat, p->d_qacc + (size_t)(p->qrows + 8) * PS_R, p->d_q0t, p->qpad, p->seed, p->d_ctl);
   LAUNCHED(p);
-  const PsPeers ps = peer_slots(p, p->off_p, p->slot_p, epoch);
-  if (p->nitems1) { k3_gemm<1><<<p->nitems1, 192, PS_SMEM, st>>>(p->d_items1, p->d_mat, p->d_maps, p->d_pacc, p->d_cnt1, ps); LAUNCHED(p); }
+  const PsPeers ps = peer_slots(p, p->off_p, p->slot_p);
+  if (p->nitems1) { k3_gemm<1><<<p->nitems1, 192, PS_SMEM, st>>>(p->d_items1, p->d_mat, p->d_maps, p->d_pacc, p->d_cnt1, ps, p->d_ctl, psp); LAUNCHED(p); }
   int simt_rows = 0;
   for (auto& m : p->h_mat) if (!m.tc) simt_rows += m.n;
   if (simt_rows) { k3_gemm1_simt<<<(simt_rows * 32 + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, p->d_work, p->d_q0t, p->qpad, p->d_pacc); LAUNCHED(p); }
-  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 1, p->d_pacc, ps, p->d_done, gb_comm_peers(c), p->chan_p, epoch);
+  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 1, p->d_pacc, ps, p->d_done, gb_comm_peers(c), p->chan_p, p->d_ctl, psp);
   LAUNCHED(p);
   return 0;
 }
@@ -728,16 +757,16 @@ extern "C" int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream) {
 extern "C" int gb_psgd_mid(gb_psgd* p, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   gb_comm* c = p->comm;
-  const uint32_t epoch = p->epoch;
-  k3_orth<<<p->nmat, 512, 0, st>>>(p->d_mat, my_slots(p, p->off_p, p->slot_p, epoch), 1.0f / (float)c->world, p->d_ph, p->d_pht,
-                                  p->ppad, gb_comm_peers(c), p->chan_p, epoch, c->status_dev, c->timeout_ns);
+  const size_t psp = (size_t)c->world * p->slot_p, psq = (size_t)c->world * p->slot_q;
+  k3_orth<<<p->nmat, 512, 0, st>>>(p->d_mat, my_slots(p, p->off_p, p->slot_p), 1.0f / (float)c->world, p->d_ph, p->d_pht,
+                                  p->ppad, gb_comm_peers(c), p->chan_p, p->d_ctl, psp, c->status_dev, c->timeout_ns);
   LAUNCHED(p);
-  const PsPeers qs = peer_slots(p, p->off_q, p->slot_q, epoch);
-  if (p->nitems2) { k3_gemm<2><<<p->nitems2, 192, PS_SMEM, st>>>(p->d_items2, p->d_mat, p->d_maps, p->d_qacc, p->d_cnt2, qs); LAUNCHED(p); }
+  const PsPeers qs = peer_slots(p, p->off_q, p->slot_q);
+  if (p->nitems2) { k3_gemm<2><<<p->nitems2, 192, PS_SMEM, st>>>(p->d_items2, p->d_mat, p->d_maps, p->d_qacc, p->d_cnt2, qs, p->d_ctl, psq); LAUNCHED(p); }
   int simt_cols = 0;
   for (auto& m : p->h_mat) if (!m.tc) simt_cols += m.m;
   if (simt_cols) { k3_gemm2_simt<<<(simt_cols + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, p->d_work, p->d_ph, p->d_qacc); LAUNCHED(p); }
-  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 2, p->d_qacc, qs, p->d_done, gb_comm_peers(c), p->chan_q, epoch);
+  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 2, p->d_qacc, qs, p->d_done, gb_comm_peers(c), p->chan_q, p->d_ctl, psq);
   LAUNCHED(p);
   return 0;
 }
@@ -746,8 +775,9 @@ extern "C" int gb_psgd_mid(gb_psgd* p, void* stream) {
 extern "C" int gb_psgd_recv(gb_psgd* p, float* d_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   gb_comm* c = p->comm;
-  k3_final<<<p->nbands, GB_THREADS, 0, st>>>(p->d_bands, p->d_mat, my_slots(p, p->off_q, p->slot_q, p->epoch), 1.0f / (float)c->world, p->d_ph,
-                                     p->d_work, p->d_res, p->has_mem, d_out, gb_comm_peers(c), p->chan_q, p->epoch,
+  k3_final<<<p->nbands, GB_THREADS, 0, st>>>(p->d_bands, p->d_mat, my_slots(p, p->off_q, p->slot_q), 1.0f / (float)c->world, p->d_ph,
+                                     p->d_work, p->d_res, p->has_mem, d_out, gb_comm_peers(c), p->chan_q, p->d_ctl,
+                                     (size_t)c->world * p->slot_q,
                                      c->status_dev, c->timeout_ns);
   LAUNCHED(p);
   p->step++;

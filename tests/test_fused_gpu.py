@@ -96,6 +96,38 @@ def test_async_send_receive_api_uses_native_plans():
     assert fast._stepper is not None and fast._stepper.enabled
 
 
+def test_graphed_step_matches_eager_step():
+    """Whole-step CUDA graph (forward, backward, fused TopK exchange, SGD) replays to the same
+    parameters as the eager loop: the exchange takes epoch/step from device memory."""
+    import grace_b200.torch as hvd
+    data = _data(8)
+
+    def run(graphed):
+        torch.manual_seed(0)
+        model = MnistNet().cuda().eval()
+        opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.5)
+        grc = hvd.grace_from_params(dict(compressor="topk", memory="residual", communicator="allgather",
+                                         compress_ratio=0.01))
+        opt = hvd.DistributedOptimizer(opt, grc, named_parameters=model.named_parameters(), fused=True,
+                                       bucket_bytes=40000)
+        loss_fn = lambda m, x, y: F.nll_loss(m(x), y)
+        if graphed:
+            step = hvd.GraphedStep(model, opt, loss_fn, data[0], amp_dtype=None, warmup=3)   # 3 eager warm-up steps on data[0], then capture
+            for x, y in data[4:]:
+                step(x, y)
+            assert step.native_launches_per_step > 0
+        else:
+            for x, y in [data[0]] * 3 + data[4:]:                 # capture itself executes nothing
+                opt.zero_grad()
+                loss_fn(model, x, y).backward()
+                opt.step()
+        torch.cuda.synchronize()
+        return torch.cat([p.detach().flatten() for p in model.parameters()])
+
+    a, b = run(True), run(False)
+    assert torch.allclose(a, b, rtol=1e-5, atol=1e-6), float((a - b).abs().max())
+
+
 def test_grad_accumulation_and_state_dict():
     import grace_b200.torch as hvd
     data = _data(6)
