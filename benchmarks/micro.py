@@ -75,11 +75,21 @@ def main():
                    gradient_clipping=False, momentum=0.9, lr=0.1, world_size=world)
         c = build_compressor(prm, "dist", world)
         m = build_memory(prm, "dist", world, c)
-        plan = eng.plan([n for _, n in named], [k for k, _ in named], codec_params(c, m))
+        cp = codec_params(c, m)
+        if comp in ("threshold", "dgc"):
+            cp.capacity = 0.1              # variable-size payload: slots hold up to 10 % of the bucket
+        try:
+            plan = eng.plan([n for _, n in named], [k for k, _ in named], cp)
+        except Exception as exc:
+            if rank == 0:
+                print("%-10s skipped: %s" % (comp, str(exc)[:120]), flush=True)
+            continue
         grad = torch.randn(plan.padded, device="cuda")
         out = torch.empty(plan.padded, device="cuda")
         times = []
         for it in range(args.warmup + args.iters):
+            if mem != "none":
+                grad.normal_()             # fresh gradient every exchange so residuals do not pile up on one sample
             flush.zero_()                                                   # flush L2 between iterations
             if world > 1:
                 dist.barrier()
