@@ -18,5 +18,5 @@ done
 for p in $pids; do wait $p; done
 OBJS=""
 for s in $SRCS; do OBJS="$OBJS $OUT/${s%.cu}.o"; done
-"$NVCC" -shared -gencode arch=compute_100a,code=sm_100a $OBJS -o "$OUT/libgrace_b200.so" -lcuda
+"$NVCC" -shared -gencode arch=compute_100a,code=sm_100a $OBJS -o "$OUT/libgrace_b200.so"
 echo "built $OUT/libgrace_b200.so"

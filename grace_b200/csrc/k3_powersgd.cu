@@ -538,16 +538,22 @@ __global__ void __launch_bounds__(GB_THREADS) k3_final(const PsBand* __restrict_
 
 // ---------------------------------------------------------------- host side
 #define LAUNCHED(p) do { (p)->launches++; GB_CUDA(cudaGetLastError()); } while (0)
-#define GB_CU(expr)                                                                      \
-  do {                                                                                   \
-    CUresult _r = (expr);                                                                \
-    if (_r != CUDA_SUCCESS) {                                                            \
-      const char* _s = nullptr;                                                          \
-      cuGetErrorString(_r, &_s);                                                         \
-      gb_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #expr, _s ? _s : "?");          \
-      return -1;                                                                         \
-    }                                                                                    \
-  } while (0)
+// cuTensorMapEncodeTiled is fetched through the runtime (cudaGetDriverEntryPoint) so that the library
+// has no link-time dependency on libcuda.so and can be loaded on a machine without a driver.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)sym;
+  }
+  return fn;
+}
 
 static int make_map(CUtensorMap* out, const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_elems, uint32_t box_inner,
                     uint32_t box_outer, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
@@ -555,9 +561,13 @@ static int make_map(CUtensorMap* out, const float* base, uint64_t inner, uint64_
   cuuint64_t strides[1] = {pitch_elems * 4};
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
-  GB_CU(cuTensorMapEncodeTiled(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
-                               CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE));
+  EncodeTiledFn enc = encode_tiled_fn();
+  GB_CHECK(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  const CUresult rc = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  GB_CHECK(rc == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (shape %llu x %llu, pitch %llu)", (int)rc,
+           (unsigned long long)outer, (unsigned long long)inner, (unsigned long long)pitch_elems);
   return 0;
 }
 
