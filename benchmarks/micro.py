@@ -107,7 +107,11 @@ def main():
             t = torch.tensor([ms], device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t)
-        eng.check_status()
+        try:
+            eng.check_status()
+        except Exception as exc:
+            if rank == 0:
+                print("%-10s status: %s" % (comp, str(exc)[:100]), flush=True)
         wire = plan.wire_bytes
         # algorithmic HBM traffic: read grad (+state r/w), write payload to W slots, read W slots, write out
         state_passes = {"none": 0, "residual": 2, "dgc": 4, "efsignsgd": 2}[mem]
