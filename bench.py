@@ -244,8 +244,33 @@ def main():
             torch.cuda.synchronize()
 
     if graphed is not None:
-        def step(x, y):                               # noqa: F811
+        eager_step = step
+
+        def graph_step(x, y):
             return graphed(x, y)
+
+        def quick(fn, n=5):
+            for _ in range(3):                        # re-warm (allocator pools differ between the two modes)
+                fn(dev_x, dev_y)
+            torch.cuda.synchronize()
+            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(n):
+                fn(dev_x, dev_y)
+            b_.record()
+            torch.cuda.synchronize()
+            return a.elapsed_time(b_) / n
+        # keep whichever execution mode is faster for this model (all ranks must agree)
+        t_graph, t_eager = quick(graph_step), quick(eager_step)
+        pick = torch.tensor([1.0 if t_graph <= t_eager else 0.0], device=device)
+        if world > 1:
+            dist.all_reduce(pick, op=dist.ReduceOp.MIN)
+        if float(pick) > 0:
+            step = graph_step
+            graph_note = "cuda-graph (whole step; probe %.2f ms vs %.2f ms eager)" % (t_graph, t_eager)
+        else:
+            graphed = None
+            graph_note = "eager (whole-step graph probed slower: %.2f ms vs %.2f ms)" % (t_graph, t_eager)
 
     def barrier():
         if world > 1:
