@@ -1,3 +1,4 @@
+# NOTE: needs the debug hooks: rebuild with  GB_NVCC_EXTRA=-DGB_K3_DEBUG bash grace_b200/csrc/build.sh
 import os, sys, ctypes as C
 sys.path.insert(0, os.getcwd())
 import torch, numpy as np

@@ -152,8 +152,10 @@ __device__ __forceinline__ void shift(PsPeers& o, size_t bytes) {
   for (int r = 0; r < o.n; ++r) o.slot[r] = (float*)((char*)o.slot[r] + bytes);
 }
 
-__device__ int g_dbg[8];   // debugging overrides for the MODE 2 descriptors: {enable, lbo, sbo, k_step, a_major, dump}
+#ifdef GB_K3_DEBUG   // descriptor experiments of benchmarks/dbg_k3.py (build with GB_NVCC_EXTRA=-DGB_K3_DEBUG)
+__device__ int g_dbg[8];   // {enable, lbo, sbo, k_step, a_major, dump, layout}
 __device__ float g_dbg_dump[8192];
+#endif
 
 template <int MODE>
 __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ items, const PsMat* __restrict__ mats,
@@ -219,16 +221,20 @@ __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ ite
       for (int j = 0; j < PS_BK / 8; ++j) {                                        // UMMA_K = 8 for tf32
         uint64_t ad, bd;
         if (MODE == 1) ad = smem_desc_sw128(a0 + j * 32, 16, 1024);               // K-major: +32 B per K step
+#ifdef GB_K3_DEBUG
         else if (g_dbg[0]) ad = smem_desc_sw128(a0 + j * g_dbg[3], g_dbg[1], g_dbg[2], g_dbg[6]);
+#endif
         // MN-major tf32 must use the 128B swizzle with 32-byte atoms (atom = 32 MN x 4 K): blocks of 32
         // columns are 4096 B apart (LBO), groups of 4 K rows 512 B apart (SBO), 8 K rows per MMA
         else ad = smem_desc_sw128(a0 + j * 1024, 4096, 512, 1);
         bd = smem_desc_sw128(b0 + j * 32, 16, 1024);
         uint32_t id = idesc;
+#ifdef GB_K3_DEBUG
         if (MODE == 2 && g_dbg[0]) id = (idesc & ~(1u << 15)) | ((uint32_t)g_dbg[4] << 15);
         if (MODE == 2 && g_dbg[5] && kb == 0 && j == 0 && blockIdx.x == 0) {
           for (int i = 0; i < 4096 + 512; ++i) g_dbg_dump[i] = i < 4096 ? ((float*)(sA))[i] : ((float*)(sB))[i - 4096];
         }
+#endif
         umma_tf32(tmem_d, ad, bd, id, (kb | j) != 0);
       }
       umma_commit(&empty[s]);                 // frees the smem stage once these MMAs have read it
@@ -718,6 +724,7 @@ extern "C" int gb_psgd_state_write(gb_psgd* p, const void* d_src, void* stream) 
   GB_CUDA(cudaMemcpyAsync(p->d_res, d_src, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return 0;
 }
+#ifdef GB_K3_DEBUG
 extern "C" int gb_psgd_debug_set(const int* v8) {
   GB_CUDA(cudaMemcpyToSymbol(g_dbg, v8, 32));
   return 0;
@@ -726,6 +733,7 @@ extern "C" int gb_psgd_debug_dump(float* h_dst) {
   GB_CUDA(cudaMemcpyFromSymbol(h_dst, g_dbg_dump, 8192 * 4));
   return 0;
 }
+#endif
 extern "C" int64_t gb_psgd_wire_bytes(gb_psgd* p) { return (int64_t)(p->prows + p->qrows) * PS_R * 4; }
 
 static PsPeers peer_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch = 0) {   // parity 0
