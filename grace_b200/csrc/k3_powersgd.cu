@@ -319,6 +319,7 @@ __global__ void __launch_bounds__(GB_THREADS) k3_gemm2_simt(const PsMat* __restr
     if (gt >= base && gt < base + mt.m) {
       const int j = gt - base;
       float s[PS_R] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 8
       for (int i = 0; i < mt.n; ++i) {
         const float x = work[mt.off + (size_t)i * mt.m + j];
         const float4 p = *reinterpret_cast<const float4*>(ph + (size_t)(mt.prow0 + i) * PS_R);
@@ -511,10 +512,25 @@ __global__ void __launch_bounds__(512) k3_orth(const PsMat* __restrict__ mats, P
 }
 
 // wait flags; out = P^ (mean_r Q_r)^T; residual = work - out.  One CTA per (matrix, 32-row band).
+__device__ __forceinline__ float dot4(const float4 a, const float4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
+
+__device__ __forceinline__ float4 mean_q(const PsIn& in, size_t row, float inv_world) {
+  float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int r = 0; r < in.n; ++r) {
+    const float4 x = *reinterpret_cast<const float4*>(in.slot[r] + row * 4);
+    q.x += x.x; q.y += x.y; q.z += x.z; q.w += x.w;
+  }
+  if (in.n > 1) { q.x *= inv_world; q.y *= inv_world; q.z *= inv_world; q.w *= inv_world; }
+  return q;
+}
+
+// One CTA per (matrix, 32-row band).  A thread owns four consecutive columns (16-byte accesses) and walks
+// the band eight rows at a time with all loads issued before the dependent stores (first version: scalar
+// accesses with load->store->store chains, 245 us for ResNet-50 under ncu = half of the whole exchange).
 __global__ void __launch_bounds__(GB_THREADS) k3_final(const PsBand* __restrict__ bands, const PsMat* __restrict__ mats, PsIn in,
                                                       float inv_world, const float* __restrict__ ph, const float* __restrict__ work,
-                                                      float* res, int has_res, float* out, PeerPtrs peers, int channel,
-                                                      const StepCtl* ctl, size_t par_stride, uint32_t* status,
+                                                      float* __restrict__ res, int has_res, float* __restrict__ out, PeerPtrs peers,
+                                                      int channel, const StepCtl* ctl, size_t par_stride, uint32_t* status,
                                                       uint64_t timeout_ns) {
   const uint32_t epoch = ctl->epoch;
   if (epoch & 1) shift(in, par_stride);
@@ -525,19 +541,38 @@ __global__ void __launch_bounds__(GB_THREADS) k3_final(const PsBand* __restrict_
   const int nrow = min(32, mt.n - b.i0);
   if (threadIdx.x < nrow) sp[threadIdx.x] = *reinterpret_cast<const float4*>(ph + (size_t)(mt.prow0 + b.i0 + threadIdx.x) * 4);
   __syncthreads();
-  for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
-    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int r = 0; r < in.n; ++r) {
-      const float4 x = *reinterpret_cast<const float4*>(in.slot[r] + (size_t)(mt.qrow0 + j) * 4);
-      q.x += x.x; q.y += x.y; q.z += x.z; q.w += x.w;
+  const size_t band0 = mt.off + (size_t)b.i0 * mt.m;
+  if ((mt.m & 3) == 0) {
+    for (int j = threadIdx.x * 4; j < mt.m; j += blockDim.x * 4) {
+      float4 q[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) q[c] = mean_q(in, (size_t)(mt.qrow0 + j + c), inv_world);
+      for (int i0 = 0; i0 < nrow; i0 += 8) {
+        float4 w[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          if (has_res && i0 + u < nrow) w[u] = *reinterpret_cast<const float4*>(work + band0 + (size_t)(i0 + u) * mt.m + j);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (i0 + u < nrow) {
+            const float4 pr = sp[i0 + u];
+            const float4 o = make_float4(dot4(pr, q[0]), dot4(pr, q[1]), dot4(pr, q[2]), dot4(pr, q[3]));
+            const size_t e = band0 + (size_t)(i0 + u) * mt.m + j;
+            if (has_res) *reinterpret_cast<float4*>(res + e) = make_float4(w[u].x - o.x, w[u].y - o.y, w[u].z - o.z, w[u].w - o.w);
+            *reinterpret_cast<float4*>(out + e) = o;
+          }
+        }
+      }
     }
-    if (in.n > 1) { q.x *= inv_world; q.y *= inv_world; q.z *= inv_world; q.w *= inv_world; }
-    for (int i = 0; i < nrow; ++i) {
-      const float4 p = sp[i];
-      const size_t e = mt.off + (size_t)(b.i0 + i) * mt.m + j;
-      const float o = p.x * q.x + p.y * q.y + p.z * q.z + p.w * q.w;
-      if (has_res) res[e] = work[e] - o;
-      out[e] = o;
+  } else {
+    for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
+      const float4 q = mean_q(in, (size_t)(mt.qrow0 + j), inv_world);
+      for (int i = 0; i < nrow; ++i) {
+        const size_t e = band0 + (size_t)i * mt.m + j;
+        const float o = dot4(sp[i], q);
+        if (has_res) res[e] = work[e] - o;
+        out[e] = o;
+      }
     }
   }
 }
