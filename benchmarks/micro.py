@@ -23,7 +23,8 @@ import torch.distributed as dist
 
 CODECS = [("none", "none"), ("fp16", "none"), ("topk", "residual"), ("randomk", "residual"), ("threshold", "residual"),
           ("dgc", "dgc"), ("qsgd", "none"), ("terngrad", "residual"), ("natural", "residual"), ("u8bit", "none"),
-          ("signsgd", "none"), ("signum", "residual"), ("efsignsgd", "efsignsgd"), ("onebit", "residual")]
+          ("signsgd", "none"), ("signum", "residual"), ("efsignsgd", "efsignsgd"), ("onebit", "residual"),
+          ("sketch", "residual")]
 
 
 def shapes_of(spec):

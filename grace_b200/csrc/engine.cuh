@@ -72,4 +72,5 @@ struct gb_plan {
   uint32_t epoch;        // exchanges completed (flag value of the next send = epoch + 1)
   uint32_t step;         // codec call counter (Philox counter word 1)
   int64_t launches;
+  void* sketch;          // SketchML buffers (k2_sketch.cu)
 };

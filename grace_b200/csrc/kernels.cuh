@@ -11,6 +11,13 @@ int k1_recv(gb_plan* p, float* d_out, cudaStream_t st);
 int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 int k2_recv(gb_plan* p, float* d_out, cudaStream_t st);
 
+// K2-sketch: SketchML (quantile buckets) -- k2_sketch.cu
+int sk_init(gb_plan* p);
+void sk_free(gb_plan* p);
+int sk_send(gb_plan* p, const float* d_grad, cudaStream_t st);
+int sk_recv(gb_plan* p, float* d_out, cudaStream_t st);
+size_t sk_header_bytes(int nseg, int q);
+
 // K0: dense two-shot all-reduce over peer memory (None / FP16 codecs, world > 1)
 int k0_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 int k0_mid(gb_plan* p, cudaStream_t st);

@@ -19,6 +19,7 @@ static int quant_bits(const gb_codec_params& p) {
     case GB_CODEC_QSGD: return p.quantum_num <= 7 ? 4 : (p.quantum_num <= 127 ? 8 : 16);
     case GB_CODEC_TERNGRAD: return 2;
     case GB_CODEC_NATURAL:
+    case GB_CODEC_SKETCH:
     case GB_CODEC_U8BIT: return 8;
     case GB_CODEC_SIGNSGD:
     case GB_CODEC_SIGNUM:
@@ -42,7 +43,7 @@ static T* carve(char*& cur, size_t count) {
 extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const uint32_t* name_hash,
                               const gb_codec_params* params, gb_plan** out) {
   GB_CHECK(nseg >= 1, "a plan needs at least one segment");
-  GB_CHECK(params->codec >= GB_CODEC_NONE && params->codec <= GB_CODEC_ONEBIT, "unknown codec %d", params->codec);
+  GB_CHECK(params->codec >= GB_CODEC_NONE && params->codec <= GB_CODEC_SKETCH, "unknown codec %d", params->codec);
   GB_CHECK(params->memory != GB_MEM_DGC || params->codec == GB_CODEC_DGC, "DGC memory needs the DGC codec");
   gb_plan* p = new gb_plan();
   p->comm = c;
@@ -51,6 +52,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->epoch = 0;
   p->step = 0;
   p->launches = 0;
+  p->sketch = nullptr;
   p->bits = quant_bits(*params);
   const bool sparse = gb_codec_is_sparse(params->codec);
 
@@ -141,7 +143,8 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
     size_t per = ((size_t)p->ktotal * 4 + 255) & ~size_t(255);
     p->slot_bytes = p->hdr_bytes + (params->codec == GB_CODEC_RANDOMK ? per : 2 * per);
   } else {
-    p->hdr_bytes = ((size_t)nseg * 4 * 4 + 255) & ~size_t(255);
+    p->hdr_bytes = params->codec == GB_CODEC_SKETCH ? sk_header_bytes(nseg, params->quantum_num)
+                                                    : (((size_t)nseg * 4 * 4 + 255) & ~size_t(255));
     p->slot_bytes = p->hdr_bytes + (((size_t)p->padded * p->bits / 8 + 255) & ~size_t(255));
   }
   p->channel2 = 0;
@@ -157,6 +160,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   }
   p->slot_bytes = (p->slot_bytes + 255) & ~size_t(255);
   p->par_stride = (size_t)c->world * p->slot_bytes;
+  if (params->codec == GB_CODEC_SKETCH && sk_init(p)) { gb_plan_destroy(p); return -1; }
   GB_CUDA(cudaDeviceSynchronize());
   *out = p;
   return 0;
@@ -165,6 +169,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
 extern "C" int gb_plan_destroy(gb_plan* p) {
   if (!p) return 0;
   cudaDeviceSynchronize();
+  sk_free(p);
   cudaFree(p->d_tables);
   cudaFree(p->d_state0);
   cudaFree(p->d_state1);
@@ -223,7 +228,7 @@ extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   gb_launch_tick(p->d_ctl, st);
   p->launches++;
-  int rc = p->dense2 ? k0_send(p, d_grad, st) : gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
+  int rc = p->prm.codec == GB_CODEC_SKETCH ? sk_send(p, d_grad, st) : p->dense2 ? k0_send(p, d_grad, st) : gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
   if (rc) return rc;
   p->step++;
   return 0;
@@ -232,6 +237,7 @@ extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
 extern "C" int gb_plan_recv(gb_plan* p, float* d_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   GB_CHECK(p->epoch > 0, "gb_plan_recv before any gb_plan_send");   // host mirror; counts captured sends too
+  if (p->prm.codec == GB_CODEC_SKETCH) return sk_recv(p, d_out, st);
   if (p->dense2) return k0_recv(p, d_out, st);
   return gb_codec_is_sparse(p->prm.codec) ? k1_recv(p, d_out, st) : k2_recv(p, d_out, st);
 }

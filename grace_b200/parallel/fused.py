@@ -72,7 +72,7 @@ def shutdown_engine():
 
 def codec_params(compressor, memory):
     """Translate a built-in (compressor, memory) pair into ``gb_codec_params``; ``None`` if the
-    pair has no native implementation (PowerSGD, SketchML, AdaQ, INCEPTIONN, user classes)."""
+    pair has no native implementation (AdaQ, INCEPTIONN, user classes; PowerSGD has its own plan type)."""
     from grace_b200.ops.native import CodecParams, CODEC, MEMORY
     p = CodecParams()
     p.beta = p.gamma = 1.0
@@ -110,6 +110,8 @@ def codec_params(compressor, memory):
         p.codec, p.lr = CODEC["efsignsgd"], compressor.learning_rate
     elif t is C.OneBitCompressor:
         p.codec = CODEC["onebit"]
+    elif t is C.SketchCompressor and 2 <= int(compressor.quantiles) <= 255:
+        p.codec, p.quantum_num = CODEC["sketch"], int(compressor.quantiles)
     else:
         return None
     m = type(memory)

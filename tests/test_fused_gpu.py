@@ -43,6 +43,7 @@ def _manual_reference(params, data):
           momentum=0.9), 0.0),
     (dict(compressor="none", memory="none", communicator="allreduce"), 0.0),
     (dict(compressor="powersgd", memory="powersgd", communicator="allreduce", compress_rank=4), 3e-2),
+    (dict(compressor="sketch", memory="none", communicator="allgather", quantiles=64), 2e-3),
 ])
 def test_distributed_optimizer_fused_matches_manual_loop(params, tol):
     import grace_b200.torch as hvd

@@ -23,7 +23,7 @@ def _params(codec, memory="none", **kw):
     p.ratio = kw.get("ratio", 0.05)
     p.beta, p.gamma = kw.get("beta", 1.0), kw.get("gamma", 1.0)
     p.threshold = kw.get("threshold", 1.5)
-    p.quantum_num = kw.get("quantum_num", 64)
+    p.quantum_num = kw.get("quantum_num", 64)       # also SketchML's number of quantiles
     p.momentum = kw.get("momentum", 0.9)
     p.lr = kw.get("lr", 0.1)
     p.seed = SEED
@@ -187,6 +187,8 @@ def test_dgc_with_dgc_memory(world):
     ("qsgd", lambda: C.QSGDCompressor(64, seed=SEED), False, 0.002),
     ("terngrad", lambda: C.TernGradCompressor(seed=SEED), False, 0.002),
     ("u8bit", C.U8bitCompressor, False, 0.002),
+    # with a residual, ulp-level differences in the bucket means move a few values across cut points
+    ("sketch", lambda: C.SketchCompressor(64), False, 0.05),
 ])
 @pytest.mark.parametrize("world", [1, 2, 4])
 @pytest.mark.parametrize("memory", ["none", "residual"])
