@@ -74,11 +74,20 @@ class Compressor(_Stateful, ABC):
 
 class _CommBase(_Stateful, ABC):
     def state_dict(self):
-        return {"compressor": self.compressor.state_dict(), "memory": self.memory.state_dict()}
+        out = {"compressor": self.compressor.state_dict(), "memory": self.memory.state_dict()}
+        stepper = getattr(self, "_stepper", None)
+        if stepper is not None and stepper.plans:           # state held by native per-tensor plans
+            out["native"] = stepper.state_dict()
+        return out
 
     def load_state_dict(self, state):
         self.compressor.load_state_dict(state.get("compressor", {}))
         self.memory.load_state_dict(state.get("memory", {}))
+        if "native" in state:
+            if getattr(self, "_stepper", None) is None:
+                from grace_b200.parallel.fused import FusedStepper
+                self._stepper = FusedStepper(self)
+            self._stepper.load_state_dict(state["native"])
 
     def _pipeline(self, tensor, name):
         tensor = self.memory.compensate(tensor, name)

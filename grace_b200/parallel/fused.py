@@ -46,8 +46,9 @@ def estimate_arena_bytes(numels, params, powersgd, world):
     """Upper bound of the peer-arena bytes the plans of one model need (2 parities x W slots)."""
     n = sum((x + 127) // 128 * 128 for x in numels)
     if powersgd is not None:
-        slot = n * 4 // 8 + (1 << 20)           # P/Q rows are at most numel/ min(n, m) ... generous
-        slot += n * 4                            # dense plan for the vectors (worst case)
+        # P and Q tiles: (rows + cols) x 4 floats per matrix, bounded by numel / 2 floats in total;
+        # plus the dense plan of the 1-D tensors (bounded by the whole bucket)
+        slot = n * 2 + (1 << 20) + (4 * n if world == 1 else 8 * n // world + 4096)
     else:
         from grace_b200.ops.native import CODEC
         code = params.codec
@@ -504,6 +505,7 @@ class FusedStepper:
             entry = (plan, torch.zeros(plan.padded, dtype=torch.float32, device=tensor.device),
                      torch.empty(plan.padded, dtype=torch.float32, device=tensor.device))
             self.plans[key] = entry
+            self._apply_state("%s/%d" % key, plan)
         return entry
 
     def usable(self, tensor):
@@ -519,6 +521,27 @@ class FusedStepper:
         plan.send(staging)
         plan.recv(out)
         return out[:n].view(tensor.shape)
+
+    def state_dict(self):
+        """Error-feedback state of the per-tensor plans (residuals, momenta, step counters)."""
+        torch.cuda.synchronize()
+        return {"%s/%d" % key: {"step": plan.step, "state0": plan.get_state(0), "state1": plan.get_state(1)}
+                for key, (plan, _, _) in self.plans.items()}
+
+    def load_state_dict(self, state):
+        """Restore plans that already exist; entries for tensors not seen yet are kept and applied on
+        first use."""
+        self._pending_state = dict(state)
+        for key, (plan, _, _) in self.plans.items():
+            self._apply_state("%s/%d" % key, plan)
+
+    def _apply_state(self, tag, plan):
+        st = getattr(self, "_pending_state", {}).pop(tag, None)
+        if st is not None:
+            plan.step = st["step"]
+            for which in (0, 1):
+                if st["state%d" % which] is not None:
+                    plan.set_state(which, st["state%d" % which])
 
     # ---- asynchronous halves (Horovod-flavour send_step / receive_step)
     def send(self, tensor, name):

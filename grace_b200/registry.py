@@ -7,6 +7,7 @@ The reference resolves names with an if/elif ladder that must be edited to add a
 from __future__ import annotations
 
 from grace_b200 import compressor as C
+from grace_b200.compressor._common import StochasticCompressor
 from grace_b200 import memory as M
 
 # name -> (class, [(ctor kwarg, params key, dist default, torch default)])
@@ -64,8 +65,7 @@ def build_compressor(params, flavour, world_size):
     if cls is C.PowerSGDCompressor:
         kw["world_size"] = world_size                 # form the mean
         kw["warm_start"] = bool(params.get("warm_start", False))
-    if "seed" in params and hasattr(C._common.StochasticCompressor, "__init__") and \
-            issubclass(cls, C._common.StochasticCompressor):
+    if "seed" in params and issubclass(cls, StochasticCompressor):
         kw["seed"] = params["seed"]
     return cls(**kw)
 

@@ -82,6 +82,19 @@ def test_sync_step_api_uses_native_plans():
     assert fast._stepper is not None and fast._stepper.enabled and len(fast._stepper.plans) == 1
 
 
+def test_sync_step_state_dict_roundtrip():
+    from grace_b200.dist import grace_from_params
+    params = dict(compressor="topk", memory="residual", communicator="allgather", compress_ratio=0.05, world_size=1)
+    a, b = grace_from_params(params), grace_from_params(params)
+    g = torch.Generator(device="cuda").manual_seed(4)
+    xs = [torch.randn(40, 50, device="cuda", generator=g) for _ in range(4)]
+    for x in xs[:2]:
+        a.step(x, "w")
+    b.load_state_dict(a.state_dict())                       # restored before b has seen the tensor
+    for x in xs[2:]:
+        assert torch.equal(a.step(x, "w"), b.step(x, "w"))
+
+
 def test_async_send_receive_api_uses_native_plans():
     import grace_b200.torch as hvd
     params = dict(compressor="qsgd", memory="residual", communicator="allgather", quantum_num=64)
