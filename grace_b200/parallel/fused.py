@@ -42,6 +42,27 @@ def get_engine(min_arena_bytes=0):
     return _engine
 
 
+_topology_ok = None
+
+
+def single_nvlink_domain():
+    """The peer-memory engine needs every rank on one host (CUDA IPC + NVLink/NVSwitch) and at most
+    8 ranks.  Jobs that span hosts keep working through the generic torch.distributed path."""
+    global _topology_ok
+    if _topology_ok is None:
+        import socket
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+            _topology_ok = True
+        elif dist.get_world_size() > 8:
+            _topology_ok = False
+        else:
+            hosts = [None] * dist.get_world_size()
+            dist.all_gather_object(hosts, socket.gethostname())
+            _topology_ok = len(set(hosts)) == 1
+    return _topology_ok
+
+
 def estimate_arena_bytes(numels, params, powersgd, world):
     """Upper bound of the peer-arena bytes the plans of one model need (2 parities x W slots)."""
     n = sum((x + 127) // 128 * 128 for x in numels)
@@ -336,11 +357,21 @@ class FusedDP:
         self._where: Dict[torch.Tensor, tuple] = {}
         self._countdown: Dict[torch.Tensor, int] = {}
         self._hooks = []
+        # bf16 / fp16 parameters: their .grad keeps the parameter dtype; the exchange (and all error
+        # feedback state) runs on an fp32 staging view that is filled when the gradient is final and
+        # copied back after the receive
+        self._lowp = [p for b in self.buckets for p in b.tensors if p.dtype != torch.float32]
+        self._lowp_views = []
         for b in self.buckets:
             for i, p in enumerate(b.tensors):
-                if p.grad is not None:
-                    b.views[i].copy_(p.grad)
-                p.grad = b.views[i]
+                if p.dtype != torch.float32:
+                    if p.grad is None:
+                        p.grad = torch.zeros_like(p)
+                    self._lowp_views.append(b.views[i])
+                else:
+                    if p.grad is not None:
+                        b.views[i].copy_(p.grad)
+                    p.grad = b.views[i]
                 self._where[p] = (b, i)
                 self._countdown[p] = self.passes
                 self._hooks.append(p.register_post_accumulate_grad_hook(self._hook))
@@ -371,7 +402,8 @@ class FusedDP:
     def _hook(self, p):
         b, i = self._where[p]
         view = b.views[i]
-        if p.grad is not view:
+        lowp = p.dtype != torch.float32
+        if not lowp and p.grad is not view:
             if p.grad.data_ptr() != view.data_ptr():     # someone replaced .grad (set_to_none): re-attach
                 view.copy_(p.grad)
             p.grad = view
@@ -381,6 +413,8 @@ class FusedDP:
         self._countdown[p] -= 1
         self._inflight = True
         if self._countdown[p] == 0:
+            if lowp:
+                view.copy_(p.grad)                       # final low-precision gradient -> fp32 staging
             b.pending -= 1
             if b.pending == 0:
                 self._send(b)
@@ -407,6 +441,8 @@ class FusedDP:
         done = torch.cuda.Event()
         done.record(self.side)
         torch.cuda.current_stream().wait_event(done)
+        if self._lowp:
+            torch._foreach_copy_([p.grad for p in self._lowp], self._lowp_views)
         for p in self._countdown:
             self._countdown[p] = self.passes
         self._inflight = False
@@ -419,8 +455,13 @@ class FusedDP:
             for flat in b.flats:
                 flat.zero_()
             for p, v in zip(b.tensors, b.views):
-                if p.grad is not v:
+                if p.dtype == torch.float32 and p.grad is not v:
                     p.grad = v
+        if self._lowp:
+            for p in self._lowp:
+                if p.grad is None:
+                    p.grad = torch.zeros_like(p)
+            torch._foreach_zero_([p.grad for p in self._lowp])
 
     def set_backward_passes_per_step(self, passes):
         self.passes = passes
@@ -458,8 +499,10 @@ def try_build_fused(optimizer, grace, named, required=False, bucket_bytes=None) 
     why = None
     if not trainable or not all(p.is_cuda for p in trainable):
         why = "parameters are not on a CUDA device"
-    elif not all(p.dtype == torch.float32 for p in trainable):
-        why = "fused path needs float32 parameters/gradients"
+    elif not all(p.dtype in (torch.float32, torch.bfloat16, torch.float16) for p in trainable):
+        why = "fused path needs float32 / bfloat16 / float16 parameters"
+    elif not single_nvlink_domain():
+        why = "ranks span several hosts or exceed 8: the peer-memory engine covers one NVLink domain"
     params = None
     psgd = powersgd_spec(grace) if why is None else None
     if why is None and psgd is None:
@@ -491,6 +534,7 @@ class FusedStepper:
             if ok:
                 self.params = codec_params(self.grace.compressor, self.grace.memory)
                 ok = self.params is not None and communicator_is_fusable(self.grace, self.params)
+            ok = ok and single_nvlink_domain()
             if ok:
                 _native_or_raise()
                 ok = get_engine().world == getattr(self.grace, "world_size", get_engine().world)

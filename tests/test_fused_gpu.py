@@ -82,6 +82,31 @@ def test_sync_step_api_uses_native_plans():
     assert fast._stepper is not None and fast._stepper.enabled and len(fast._stepper.plans) == 1
 
 
+def test_bf16_parameters_use_fp32_staging():
+    """bf16 model: gradients stay bf16 for autograd/optimizer, the exchange and the residual run in fp32."""
+    import grace_b200.torch as hvd
+    torch.manual_seed(0)
+    model = MnistNet().cuda().eval().bfloat16()
+    opt = torch.optim.SGD(model.parameters(), lr=0.05)
+    grc = hvd.grace_from_params(dict(compressor="topk", memory="residual", communicator="allgather", compress_ratio=0.05))
+    opt = hvd.DistributedOptimizer(opt, grc, named_parameters=model.named_parameters(), fused=True)
+    x, y = _data(1)[0]
+    before = torch.cat([p.detach().float().flatten() for p in model.parameters()])
+    for _ in range(3):
+        opt.zero_grad()
+        F.nll_loss(model(x.bfloat16()).float(), y).backward()
+        opt.synchronize()
+        n_params = sum(p.numel() for p in model.parameters())
+        nz = sum(int((p.grad != 0).sum()) for p in model.parameters())
+        assert all(p.grad.dtype == torch.bfloat16 for p in model.parameters())
+        assert 0 < nz <= int(0.05 * n_params) + 8                 # only the selected 5 % survive
+        with opt.skip_synchronize():
+            opt.step()
+    after = torch.cat([p.detach().float().flatten() for p in model.parameters()])
+    assert not torch.equal(before, after)
+    assert opt.grace_state_dict()["buckets"][0]["plans"][0]["state0"].dtype == torch.float32
+
+
 def test_sync_step_state_dict_roundtrip():
     from grace_b200.dist import grace_from_params
     params = dict(compressor="topk", memory="residual", communicator="allgather", compress_ratio=0.05, world_size=1)
