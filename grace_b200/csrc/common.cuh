@@ -188,12 +188,22 @@ struct SegTable {
   const uint32_t* seg_hash;   // [nseg]   fnv1a(name)
   const int32_t* seg_tile0;   // [nseg+1] first tile of each segment
   const int32_t* tile_seg;    // [ntiles]
+  const int4* tile_desc;      // [ntiles] {base lo, base hi, segment, valid length}: one 16-byte load per tile (may be null)
   int32_t nseg;
   int32_t ntiles;
   int64_t padded;             // total padded elements
 };
 
 __device__ __forceinline__ void tile_bounds(const SegTable& t, int tile, int& seg, int64_t& base, int& local0, int& len) {
+  if (t.tile_desc) {
+    // precomputed descriptor: a single load instead of a chain of four dependent table look-ups
+    const int4 d = __ldg(t.tile_desc + tile);
+    base = (int64_t)(((uint64_t)(uint32_t)d.y << 32) | (uint32_t)d.x);
+    seg = d.z;
+    len = d.w & 0xFFFF;                       // 1..4096 fits 13 bits
+    local0 = (d.w >> 16) * GB_TILE;           // tile index inside the segment (< 2^15 for < 2^27-element tensors)
+    return;
+  }
   seg = t.tile_seg[tile];
   int within = tile - t.seg_tile0[seg];
   local0 = within * GB_TILE;

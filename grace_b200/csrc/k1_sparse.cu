@@ -880,6 +880,7 @@ static SegTable single_table(char* tab, int64_t n, int ntiles) {
   t.seg_hash = (const uint32_t*)(tab + 64) + 2;
   t.seg_tile0 = (const int32_t*)(tab + 64) + 3;
   t.tile_seg = (const int32_t*)(tab + 256);
+  t.tile_desc = nullptr;
   t.nseg = 1;
   t.ntiles = ntiles;
   t.padded = (n + GB_ALIGN - 1) / GB_ALIGN * GB_ALIGN;

@@ -96,7 +96,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   size_t bytes = 0;
   auto add = [&](size_t n) { bytes += (n + 255) & ~size_t(255); };
   add((nseg + 1) * 8); add(nseg * 4); add(nseg * 4); add((nseg + 1) * 8); add(nseg * 4); add((nseg + 1) * 4);
-  add(p->ntiles * 4);
+  add(p->ntiles * 4); add((size_t)p->ntiles * 16);
   add((size_t)nseg * 2048 * 4); add((size_t)nseg * 4 * 4); add((size_t)p->ntiles * 2 * 4 + 8);
   add((size_t)p->ntiles * 8 * 4); add((size_t)nseg * 4 * 4); add(64); add(64);
   GB_CUDA(cudaMalloc(&p->d_tables, bytes));
@@ -109,6 +109,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   uint32_t* d_hash = carve<uint32_t>(cur, nseg);
   int32_t* d_tile0 = carve<int32_t>(cur, nseg + 1);
   int32_t* d_tileseg = carve<int32_t>(cur, p->ntiles);
+  int4* d_tiledesc = carve<int4>(cur, p->ntiles);
   p->d_hist = carve<uint32_t>(cur, (size_t)nseg * 2048);
   p->d_sel = carve<uint32_t>(cur, (size_t)nseg * 4);
   p->d_tilecnt = carve<int32_t>(cur, (size_t)p->ntiles * 2 + 2);
@@ -123,7 +124,22 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   GB_CUDA(cudaMemcpy(d_hash, name_hash, nseg * 4, cudaMemcpyHostToDevice));
   GB_CUDA(cudaMemcpy(d_tile0, p->h_tile0.data(), (nseg + 1) * 4, cudaMemcpyHostToDevice));
   GB_CUDA(cudaMemcpy(d_tileseg, tile_seg.data(), p->ntiles * 4, cudaMemcpyHostToDevice));
-  p->tab = SegTable{d_off, d_numel, d_k, d_kbase, d_hash, d_tile0, d_tileseg, nseg, p->ntiles, p->padded};
+  bool desc_ok = true;
+  {
+    std::vector<int4> desc(p->ntiles);
+    for (int tile = 0; tile < p->ntiles; ++tile) {
+      const int sg = tile_seg[tile];
+      const int within = tile - p->h_tile0[sg];
+      const int64_t base = p->h_off[sg] + (int64_t)within * GB_TILE;
+      const int len = (int)std::min<int64_t>(GB_TILE, p->h_numel[sg] - (int64_t)within * GB_TILE);
+      if (within >= (1 << 15)) desc_ok = false;
+      desc[tile] = make_int4((int)(uint32_t)(base & 0xFFFFFFFFll), (int)(uint32_t)((uint64_t)base >> 32), sg,
+                             (len == GB_TILE ? 4096 : len) | (within << 16));
+    }
+    GB_CUDA(cudaMemcpy(d_tiledesc, desc.data(), (size_t)p->ntiles * 16, cudaMemcpyHostToDevice));
+  }
+  p->tab = SegTable{d_off, d_numel, d_k, d_kbase, d_hash, d_tile0, d_tileseg, desc_ok ? d_tiledesc : nullptr, nseg, p->ntiles,
+                    p->padded};
 
   p->d_state0 = p->d_state1 = nullptr;
   const bool need0 = params->memory != GB_MEM_NONE;
