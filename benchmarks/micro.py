@@ -24,7 +24,7 @@ import torch.distributed as dist
 CODECS = [("none", "none"), ("fp16", "none"), ("topk", "residual"), ("randomk", "residual"), ("threshold", "residual"),
           ("dgc", "dgc"), ("qsgd", "none"), ("terngrad", "residual"), ("natural", "residual"), ("u8bit", "none"),
           ("signsgd", "none"), ("signum", "residual"), ("efsignsgd", "efsignsgd"), ("onebit", "residual"),
-          ("sketch", "residual")]
+          ("sketch", "residual"), ("adaq", "residual")]
 
 
 def shapes_of(spec):
@@ -77,7 +77,7 @@ def main():
         c = build_compressor(prm, "dist", world)
         m = build_memory(prm, "dist", world, c)
         cp = codec_params(c, m)
-        if comp in ("threshold", "dgc"):
+        if comp in ("threshold", "dgc", "adaq"):
             cp.capacity = 0.1              # variable-size payload: slots hold up to 10 % of the bucket
         try:
             plan = eng.plan([n for _, n in named], [k for k, _ in named], cp)

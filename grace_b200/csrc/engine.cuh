@@ -73,4 +73,5 @@ struct gb_plan {
   uint32_t step;         // codec call counter (Philox counter word 1)
   int64_t launches;
   void* sketch;          // SketchML buffers (k2_sketch.cu)
+  void* adaq;            // AdaQ buffers (k1_adaq.cu)
 };

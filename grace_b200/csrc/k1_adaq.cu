@@ -1,0 +1,642 @@
+// K1-adaq -- AdaQ / AdaComp-style sparsifier (SURVEY §2.3 row 15, §2.9-B row "AdaQ").
+//
+// Reference: grace_dl/tensorflow/compressor/adaq.py:16-93 (TF graph: boolean_mask, a sampled top-k,
+// a tf.while_loop of <= 20 threshold refinements per sign, two means, one int32 vector on the wire).
+// Oracle of the numerics: grace_b200/compressor/sparse.py (_adaq_part / AdaqCompressor).
+//
+// Per bucket, for every tensor and both signs at once:
+//   aq_count     compensate (ResidualMemory) + count positives / negatives per 128-element sub-block
+//   aq_scan      exclusive prefix of the per-tile counts inside each tensor
+//   aq_sample    one warp per sample: the r-th positive (negative) element is located through the
+//                tile prefix, the 32 sub-block counts of that tile and one 128-element ballot -- the
+//                reference's boolean_mask + gather without ever materialising the masked tensor
+//   aq_kth       k-th largest sampled magnitude (3 histogram rounds, one CTA per tensor and sign)
+//   21 x (aq_select, aq_adjust)   the refinement loop, device-resident (no host round trips)
+//   aq_select<final> + aq_mean    fixed-order sums -> one mean per tensor and sign, stored to every peer
+//   aq_emit      unordered compaction of the picked indices (sign in bit 31) straight into every peer's
+//                slot; residual = x - mean at the picked positions; the last CTA releases the flags
+//   aq_merge     receive: each CTA owns an output tile and adds mean_r[sign] at rank r's indices in
+//                rank order (bit-identical on all ranks)
+// Wire per rank: 2 floats per tensor + 4 bytes per kept element (the reference sends the same int32
+// list; values never travel).
+#include "kernels.cuh"
+
+#include <math.h>
+
+#include <algorithm>
+#include <vector>
+
+struct AdaqBuf {
+  void* d_all;
+  uint8_t* sub;       // [ntiles][2][32]  positives / negatives per 128-element sub-block
+  int32_t* tcnt;      // [ntiles][2]      per-tile counts, then exclusive prefix inside the tensor
+  int32_t* segcnt;    // [nseg][2]
+  int64_t* samp_off;  // [nseg+1]         sample capacity prefix: ceil(0.01 n) + 1 per tensor
+  float* samp;        // [2][samp_total]  sampled magnitudes
+  uint32_t* sel;      // [nseg][2][4]     {threshold bits, done, selected, adjustments made}
+  double* tsum;       // [ntiles][2]      per-tile sum of the finally selected values
+  int32_t* tsel;      // [ntiles][2]      per-tile count of the finally selected values
+  float* means;       // [nseg][2]
+  int64_t samp_total;
+};
+
+struct AdaqOut {
+  int2* hdr[GB_MAX_WORLD];
+  float* means[GB_MAX_WORLD];
+  int32_t* idx[GB_MAX_WORLD];
+  int n;
+};
+__device__ __forceinline__ void shift(AdaqOut& o, size_t bytes) {
+  for (int r = 0; r < o.n; ++r) {
+    o.hdr[r] = (int2*)((char*)o.hdr[r] + bytes);
+    o.means[r] = (float*)((char*)o.means[r] + bytes);
+    o.idx[r] = (int32_t*)((char*)o.idx[r] + bytes);
+  }
+}
+
+size_t aq_means_bytes(int nseg) { return ((size_t)nseg * 2 * 4 + 255) & ~size_t(255); }
+
+namespace {
+
+__device__ __forceinline__ float4 ld4(const float* p, int e0, int len) {
+  if (e0 + 4 <= len) return *reinterpret_cast<const float4*>(p + e0);
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (e0 < len) v.x = p[e0];
+  if (e0 + 1 < len) v.y = p[e0 + 1];
+  if (e0 + 2 < len) v.z = p[e0 + 2];
+  if (e0 + 3 < len) v.w = p[e0 + 3];
+  return v;
+}
+__device__ __forceinline__ void st4(float* p, int e0, int len, float4 v) {
+  if (e0 + 4 <= len) { *reinterpret_cast<float4*>(p + e0) = v; return; }
+  if (e0 < len) p[e0] = v.x;
+  if (e0 + 1 < len) p[e0 + 1] = v.y;
+  if (e0 + 2 < len) p[e0 + 2] = v.z;
+  if (e0 + 3 < len) p[e0 + 3] = v.w;
+}
+__device__ __forceinline__ float comp1(float beta, float r, float gamma, float g) {
+  return __fadd_rn(__fmul_rn(beta, r), __fmul_rn(gamma, g));   // two roundings, like torch's beta*e + gamma*g
+}
+__device__ __forceinline__ int warp_incl_scan(int v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int n = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += n;
+  }
+  return v;
+}
+
+// ---------------------------------------------------------------- counting
+template <bool WRITE>
+__global__ void __launch_bounds__(GB_THREADS) aq_count(SegTable t, const float* __restrict__ grad, float* work, float beta,
+                                                       float gamma, const StepCtl* ctl, uint8_t* sub, int32_t* tcnt) {
+  if (ctl->step == 0) { beta = 0.f; gamma = 1.f; }             // first call: compensate() returns the gradient
+  __shared__ int scnt[2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    if (threadIdx.x < 2) scnt[threadIdx.x] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (e0 < len) {
+        if (WRITE) {
+          const float4 g = ld4(grad + base, e0, len);
+          const float4 r = ld4(work + base, e0, len);
+          v = make_float4(comp1(beta, r.x, gamma, g.x), comp1(beta, r.y, gamma, g.y), comp1(beta, r.z, gamma, g.z),
+                          comp1(beta, r.w, gamma, g.w));
+          st4(work + base, e0, len, v);
+        } else {
+          v = ld4(work + base, e0, len);
+        }
+      }
+      int cp = (v.x > 0.f) + (v.y > 0.f) + (v.z > 0.f) + (v.w > 0.f);
+      int cn = (v.x < 0.f) + (v.y < 0.f) + (v.z < 0.f) + (v.w < 0.f);
+      cp = warp_sum_i(cp);
+      cn = warp_sum_i(cn);
+      if (lane == 0) {
+        sub[((size_t)tile * 2 + 0) * 32 + j * 8 + warp] = (uint8_t)cp;
+        sub[((size_t)tile * 2 + 1) * 32 + j * 8 + warp] = (uint8_t)cn;
+        if (cp) atomicAdd(&scnt[0], cp);
+        if (cn) atomicAdd(&scnt[1], cn);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < 2) tcnt[tile * 2 + threadIdx.x] = scnt[threadIdx.x];
+    __syncthreads();
+  }
+}
+
+// One CTA per tensor: exclusive prefix of the tile counts (both signs), totals, reset of the selection state.
+__global__ void __launch_bounds__(GB_THREADS) aq_scan(SegTable t, int32_t* tcnt, int32_t* segcnt, uint32_t* sel) {
+  __shared__ int wsum[GB_THREADS / 32];
+  __shared__ int carry;
+  const int seg = blockIdx.x;
+  const int t0 = t.seg_tile0[seg], t1 = t.seg_tile0[seg + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int s = 0; s < 2; ++s) {
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int c0 = t0; c0 < t1; c0 += GB_THREADS) {
+      const int tile = c0 + threadIdx.x;
+      const int v = tile < t1 ? tcnt[tile * 2 + s] : 0;
+      const int incl = warp_incl_scan(v, lane);
+      if (lane == 31) wsum[warp] = incl;
+      __syncthreads();
+      int woff = 0;
+      for (int w = 0; w < warp; ++w) woff += wsum[w];
+      const int before = carry;
+      if (tile < t1) tcnt[tile * 2 + s] = before + woff + incl - v;
+      __syncthreads();
+      if (threadIdx.x == GB_THREADS - 1) carry = before + woff + incl;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      segcnt[seg * 2 + s] = carry;
+      uint32_t* q = sel + (seg * 2 + s) * 4;
+      q[0] = 0; q[1] = 0; q[2] = 0; q[3] = 0;
+    }
+    __syncthreads();
+  }
+}
+
+__device__ __forceinline__ int aq_find_seg(const int64_t* off, int nseg, int64_t p) {
+  int lo = 0, hi = nseg;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (off[mid] <= p) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// ---------------------------------------------------------------- sampling
+// One warp per sample.  The reference gathers `boolean_mask(x, sign)[pos]`; here the pos-th element of that
+// sign is found through three levels of counts (tile prefix -> 32 sub-block counts -> 128-element ballot).
+__global__ void __launch_bounds__(GB_THREADS) aq_sample(SegTable t, const float* __restrict__ work, const int32_t* __restrict__ tcnt,
+                                                        const int32_t* __restrict__ segcnt, const uint8_t* __restrict__ sub,
+                                                        const int64_t* __restrict__ samp_off, float* samp, int64_t samp_total,
+                                                        uint32_t seed, const StepCtl* ctl) {
+  const uint32_t step = ctl->step;
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = (int64_t)gridDim.x * (GB_THREADS / 32);
+  for (int64_t w = (int64_t)blockIdx.x * (GB_THREADS / 32) + (threadIdx.x >> 5); w < 2 * samp_total; w += nwarps) {
+    const int s = w >= samp_total ? 1 : 0;
+    const int64_t j = w - (int64_t)s * samp_total;
+    const int seg = aq_find_seg(samp_off, t.nseg, j);
+    const int i = (int)(j - samp_off[seg]);
+    const int count = segcnt[seg * 2 + s];
+    const int ns = (int)ceil((double)count * 0.01);
+    if (i >= ns) continue;
+    const Philox4 r4 = philox4x32((uint32_t)(i >> 2), 2u * step + (uint32_t)s, GB_STREAM_SAMPLE, 0u, seed, t.seg_hash[seg]);
+    const uint32_t bits = (i & 3) == 0 ? r4.x : (i & 3) == 1 ? r4.y : (i & 3) == 2 ? r4.z : r4.w;
+    int r = (int)__fmul_rn(u32_to_unit(bits), (float)count);
+    r = min(r, count - 1);
+    // tile: the last one whose exclusive prefix is <= r
+    int lo = t.seg_tile0[seg], hi = t.seg_tile0[seg + 1];
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (tcnt[mid * 2 + s] <= r) lo = mid; else hi = mid;
+    }
+    int rr = r - tcnt[lo * 2 + s];
+    // sub-block
+    const int c = sub[((size_t)lo * 2 + s) * 32 + lane];
+    const int incl = warp_incl_scan(c, lane);
+    const uint32_t above = __ballot_sync(0xffffffffu, incl > rr);
+    const int sb = above ? __ffs(above) - 1 : 31;
+    rr -= __shfl_sync(0xffffffffu, incl - c, sb);
+    // element
+    int sg2, local0, len;
+    int64_t base;
+    tile_bounds(t, lo, sg2, base, local0, len);
+    const int e0 = sb * 128 + lane * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (e0 < len) v = ld4(work + base, e0, len);
+    const float vv[4] = {v.x, v.y, v.z, v.w};
+    uint32_t m = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) m |= ((s ? vv[q] < 0.f : vv[q] > 0.f) ? 1u : 0u) << q;
+    const int c4 = __popc(m);
+    const int incl4 = warp_incl_scan(c4, lane);
+    const uint32_t above4 = __ballot_sync(0xffffffffu, incl4 > rr);
+    const int ls = above4 ? __ffs(above4) - 1 : 31;
+    const int rr2 = rr - __shfl_sync(0xffffffffu, incl4 - c4, ls);
+    if (lane == ls) {
+      int seen = 0;
+      float val = 0.f;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if ((m >> q) & 1u) {
+          if (seen == rr2) val = fabsf(vv[q]);
+          ++seen;
+        }
+      }
+      samp[(int64_t)s * samp_total + j] = val;
+    }
+  }
+}
+
+// One CTA per (tensor, sign): k-th largest of the ns sampled magnitudes -> initial threshold.
+__global__ void __launch_bounds__(GB_THREADS) aq_kth(SegTable t, const int32_t* __restrict__ segcnt, const int64_t* __restrict__ samp_off,
+                                                     const float* __restrict__ samp, int64_t samp_total, double ratio, uint32_t* sel) {
+  __shared__ uint32_t hist[2048];
+  __shared__ uint32_t s_prefix, s_krem;
+  const int seg = blockIdx.x >> 1, s = blockIdx.x & 1;
+  const int count = segcnt[seg * 2 + s];
+  uint32_t* q = sel + (seg * 2 + s) * 4;
+  if (count == 0) {                                   // empty half: nothing selected, mean 0
+    if (threadIdx.x == 0) { q[0] = 0x7F800000u; q[1] = 1u; q[2] = 0u; q[3] = 0u; }
+    return;
+  }
+  const int ns = (int)ceil((double)count * 0.01);
+  int k = (int)ceil((double)count * 0.01 * ratio);
+  k = max(1, min(ns, k));
+  const float* x = samp + (int64_t)s * samp_total + samp_off[seg];
+  if (threadIdx.x == 0) { s_prefix = 0; s_krem = (uint32_t)k; }
+  for (int round = 0; round < 3; ++round) {
+    const int nb = round == 0 ? 2048 : 1024;
+    for (int b = threadIdx.x; b < nb; b += blockDim.x) hist[b] = 0;
+    __syncthreads();
+    const uint32_t prefix = s_prefix;
+    for (int i = threadIdx.x; i < ns; i += blockDim.x) {
+      const uint32_t b = __float_as_uint(x[i]) & 0x7FFFFFFFu;
+      if (round == 0) atomicAdd(&hist[b >> 20], 1u);
+      else if (round == 1) { if ((b >> 20) == prefix) atomicAdd(&hist[(b >> 10) & 1023u], 1u); }
+      else { if ((b >> 10) == prefix) atomicAdd(&hist[b & 1023u], 1u); }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t running = 0;
+      const uint32_t krem = s_krem;
+      for (int b = nb - 1; b >= 0; --b) {
+        const uint32_t c = hist[b];
+        if (running + c >= krem) {
+          s_prefix = round == 0 ? (uint32_t)b : ((prefix << 10) | (uint32_t)b);
+          s_krem = krem - running;
+          break;
+        }
+        running += c;
+      }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { q[0] = s_prefix; q[1] = 0u; q[2] = 0u; q[3] = 0u; }
+}
+
+// ---------------------------------------------------------------- threshold refinement
+// Oracle (sparse.py:_adaq_part): `masked` is |x| on this sign's elements and 0 elsewhere; the first count
+// uses `>`, every recount after an adjustment `>=`, the final mask `>` again.
+__device__ __forceinline__ double block_sum_d(double v, double* sh) {
+  v = warp_sum_d(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double tot = 0.0;
+  for (int w = 0; w < GB_THREADS / 32; ++w) tot += sh[w];          // fixed order
+  return tot;
+}
+
+template <bool FINAL>
+__global__ void __launch_bounds__(GB_THREADS) aq_select(SegTable t, const float* __restrict__ work, uint32_t* sel, double* tsum,
+                                                        int32_t* tsel) {
+  __shared__ double shd[GB_THREADS / 32];
+  __shared__ int shc[2];
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    const uint32_t* q0 = sel + (seg * 2) * 4;
+    const uint32_t* q1 = q0 + 4;
+    const bool d0 = q0[1] != 0, d1 = q1[1] != 0;
+    if (!FINAL && d0 && d1) continue;
+    const float thr0 = __uint_as_float(q0[0]), thr1 = __uint_as_float(q1[0]);
+    const bool ge0 = q0[3] != 0, ge1 = q1[3] != 0;
+    if (threadIdx.x < 2) shc[threadIdx.x] = 0;
+    __syncthreads();
+    int c0 = 0, c1 = 0;
+    double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      const float4 v = ld4(work + base, e0, len);
+      const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (e0 + q >= len) continue;
+        const float mp = vv[q] > 0.f ? vv[q] : 0.f;
+        const float mn = vv[q] < 0.f ? -vv[q] : 0.f;
+        if (FINAL) {
+          if (mp > thr0) { ++c0; s0 += (double)vv[q]; }
+          if (mn > thr1) { ++c1; s1 += (double)vv[q]; }
+        } else {
+          c0 += !d0 && (ge0 ? mp >= thr0 : mp > thr0);
+          c1 += !d1 && (ge1 ? mn >= thr1 : mn > thr1);
+        }
+      }
+    }
+    c0 = warp_sum_i(c0);
+    c1 = warp_sum_i(c1);
+    if ((threadIdx.x & 31) == 0) {
+      if (c0) atomicAdd(&shc[0], c0);
+      if (c1) atomicAdd(&shc[1], c1);
+    }
+    if (FINAL) {
+      const double a = block_sum_d(s0, shd);
+      const double b = block_sum_d(s1, shd);
+      if (threadIdx.x == 0) { tsum[tile * 2] = a; tsum[tile * 2 + 1] = b; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+      const int c = shc[threadIdx.x];
+      if (FINAL) tsel[tile * 2 + threadIdx.x] = c;
+      else if (c) atomicAdd(&sel[(seg * 2 + threadIdx.x) * 4 + 2], (uint32_t)c);
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void aq_adjust(SegTable t, const int32_t* __restrict__ segcnt, double ratio, uint32_t* sel) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < t.nseg * 2; i += gridDim.x * blockDim.x) {
+    uint32_t* q = sel + i * 4;
+    if (q[1]) continue;
+    const double target = ceil((double)segcnt[i] * ratio);
+    const double selected = (double)q[2];
+    float thr = __uint_as_float(q[0]);
+    const bool over = selected > 1.25 * target, under = selected < 0.8 * target;
+    if (q[3] < 20u && (over || under)) {
+      thr = over ? __fmul_rn(1.25f, thr) : __fmul_rn(0.9f, thr);
+      q[3] += 1u;
+      q[2] = 0u;
+    } else {
+      if (selected < 1.0) thr = __fmul_rn(0.8f, thr);
+      q[1] = 1u;
+    }
+    q[0] = __float_as_uint(thr);
+  }
+}
+
+// One CTA per tensor: fixed-order sum of the tile partials -> mean per sign, stored locally and to every peer.
+__global__ void __launch_bounds__(GB_THREADS) aq_mean(SegTable t, const double* __restrict__ tsum, const int32_t* __restrict__ tsel,
+                                                      float* means, AdaqOut out, const StepCtl* ctl, size_t par_stride) {
+  __shared__ double shd[GB_THREADS / 32];
+  __shared__ int shi[GB_THREADS / 32];
+  if (ctl->epoch & 1) shift(out, par_stride);
+  const int seg = blockIdx.x;
+  const int t0 = t.seg_tile0[seg], t1 = t.seg_tile0[seg + 1];
+  for (int s = 0; s < 2; ++s) {
+    double a = 0.0;
+    int c = 0;
+    for (int tile = t0 + threadIdx.x; tile < t1; tile += GB_THREADS) { a += tsum[tile * 2 + s]; c += tsel[tile * 2 + s]; }
+    a = block_sum_d(a, shd);
+    c = warp_sum_i(c);
+    if ((threadIdx.x & 31) == 0) shi[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int n = 0;
+      for (int w = 0; w < GB_THREADS / 32; ++w) n += shi[w];
+      const float m = n ? (float)(a / (double)n) : 0.f;
+      means[seg * 2 + s] = m;
+      for (int r = 0; r < out.n; ++r) out.means[r][seg * 2 + s] = m;
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------- emit / merge
+template <bool WRITE>
+__global__ void __launch_bounds__(GB_THREADS) aq_emit(SegTable t, float* work, const uint32_t* __restrict__ sel,
+                                                      const float* __restrict__ means, uint32_t* cursor, AdaqOut out, int64_t capacity,
+                                                      uint32_t* status, uint32_t* done, PeerPtrs peers, int channel,
+                                                      const StepCtl* ctl, size_t par_stride) {
+  __shared__ int32_t sidx[GB_TILE];
+  __shared__ int scount, sbegin;
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(out, par_stride);
+  const int lane = threadIdx.x & 31;
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    const float thr0 = __uint_as_float(sel[(seg * 2) * 4]), thr1 = __uint_as_float(sel[(seg * 2 + 1) * 4]);
+    const float m0 = means[seg * 2], m1 = means[seg * 2 + 1];
+    if (threadIdx.x == 0) scount = 0;
+    __syncthreads();
+    float vv[4][4];
+    uint32_t picks = 0, negs = 0;
+    int cnt = 0;
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (e0 < len) v = ld4(work + base, e0, len);
+      vv[j][0] = v.x; vv[j][1] = v.y; vv[j][2] = v.z; vv[j][3] = v.w;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float x = vv[j][q];
+        const bool in = e0 + q < len;
+        const bool pp = in && x > 0.f && x > thr0;
+        const bool pn = in && x < 0.f && -x > thr1;
+        picks |= ((pp || pn) ? 1u : 0u) << (j * 4 + q);
+        negs |= (pn ? 1u : 0u) << (j * 4 + q);
+        cnt += pp || pn;
+      }
+    }
+    const int incl = warp_incl_scan(cnt, lane);
+    const int wtotal = __shfl_sync(0xffffffffu, incl, 31);
+    int wbase = 0;
+    if (wtotal) {
+      if (lane == 0) wbase = atomicAdd(&scount, wtotal);
+      wbase = __shfl_sync(0xffffffffu, wbase, 0);
+    }
+    if (picks) {
+      int pos = wbase + incl - cnt;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+        if ((picks >> (j * 4)) & 0xFu) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if ((picks >> (j * 4 + q)) & 1u) {
+              const bool neg = (negs >> (j * 4 + q)) & 1u;
+              sidx[pos++] = (local0 + e0 + q) | (neg ? (int32_t)0x80000000 : 0);
+              vv[j][q] = __fsub_rn(vv[j][q], neg ? m1 : m0);        // residual = x - decompress(compress(x))
+            }
+          }
+          if (WRITE) st4(work + base, e0, len, make_float4(vv[j][0], vv[j][1], vv[j][2], vv[j][3]));
+        }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int tc = scount;
+      const int64_t begin = atomicAdd(cursor, (uint32_t)tc);
+      if (begin + tc > capacity) {
+        atomicOr(status, GB_STATUS_OVERFLOW);
+        tc = (int)max((int64_t)0, capacity - begin);
+        scount = tc;
+      }
+      sbegin = (int)min(begin, capacity);
+      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = make_int2(sbegin, tc);
+    }
+    __syncthreads();
+    const int tcnt = scount, begin = sbegin;
+    for (int r = 0; r < out.n; ++r) {
+      int32_t* di = out.idx[r] + begin;
+      for (int i = threadIdx.x; i < tcnt; i += GB_THREADS) di[i] = sidx[i];
+    }
+    __syncthreads();
+  }
+  release_flags_last_block(done, peers, channel, epoch);
+}
+
+struct AdaqIn {
+  const int2* hdr[GB_MAX_WORLD];
+  const float* means[GB_MAX_WORLD];
+  const int32_t* idx[GB_MAX_WORLD];
+  int n;
+};
+
+__global__ void __launch_bounds__(GB_THREADS) aq_merge(SegTable t, AdaqIn in, float* outp, float divisor, PeerPtrs peers, int channel,
+                                                       const StepCtl* ctl, size_t par_stride, uint32_t* status, uint64_t timeout_ns) {
+  __shared__ float acc[GB_TILE];
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) {
+    for (int r = 0; r < in.n; ++r) {
+      in.hdr[r] = (const int2*)((const char*)in.hdr[r] + par_stride);
+      in.means[r] = (const float*)((const char*)in.means[r] + par_stride);
+      in.idx[r] = (const int32_t*)((const char*)in.idx[r] + par_stride);
+    }
+  }
+  wait_all_ranks(peers, channel, epoch, status, timeout_ns);
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    for (int i = threadIdx.x; i < GB_TILE; i += GB_THREADS) acc[i] = 0.f;
+    __syncthreads();
+    for (int r = 0; r < in.n; ++r) {
+      const int2 h = in.hdr[r][tile];
+      const float m0 = in.means[r][seg * 2], m1 = in.means[r][seg * 2 + 1];
+      const int32_t* ix = in.idx[r] + h.x;
+      for (int i = threadIdx.x; i < h.y; i += GB_THREADS) {
+        const int32_t w = ix[i];
+        const int li = (w & 0x7FFFFFFF) - local0;
+        if ((unsigned)li < (unsigned)GB_TILE) acc[li] += w < 0 ? m1 : m0;      // indices are unique per rank
+      }
+      __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      float4 v = make_float4(acc[e0], acc[e0 + 1], acc[e0 + 2], acc[e0 + 3]);
+      if (divisor != 1.f) {          // torch's CUDA tensor / python-scalar is a multiply by the reciprocal
+        const float inv = __fdiv_rn(1.0f, divisor);
+        v.x = __fmul_rn(v.x, inv); v.y = __fmul_rn(v.y, inv); v.z = __fmul_rn(v.z, inv); v.w = __fmul_rn(v.w, inv);
+      }
+      st4(outp + base, e0, len, v);
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- host side
+#define AQ_LAUNCHED(p) do { (p)->launches++; GB_CUDA(cudaGetLastError()); } while (0)
+
+int aq_init(gb_plan* p) {
+  AdaqBuf* b = new AdaqBuf();
+  p->adaq = b;
+  std::vector<int64_t> off(p->nseg + 1);
+  int64_t tot = 0;
+  for (int s = 0; s < p->nseg; ++s) {
+    off[s] = tot;
+    tot += (int64_t)ceil((double)p->h_numel[s] * 0.01) + 1;
+  }
+  off[p->nseg] = tot;
+  b->samp_total = tot;
+  size_t bytes = 0;
+  auto add = [&](size_t n) { size_t o = bytes; bytes += (n + 255) & ~size_t(255); return o; };
+  const size_t o_sub = add((size_t)p->ntiles * 64), o_tcnt = add((size_t)p->ntiles * 8), o_seg = add((size_t)p->nseg * 8);
+  const size_t o_off = add((size_t)(p->nseg + 1) * 8), o_samp = add((size_t)tot * 2 * 4), o_sel = add((size_t)p->nseg * 32);
+  const size_t o_tsum = add((size_t)p->ntiles * 16), o_tsel = add((size_t)p->ntiles * 8), o_means = add((size_t)p->nseg * 8);
+  GB_CUDA(cudaMalloc(&b->d_all, bytes));
+  GB_CUDA(cudaMemset(b->d_all, 0, bytes));
+  char* base = (char*)b->d_all;
+  b->sub = (uint8_t*)(base + o_sub); b->tcnt = (int32_t*)(base + o_tcnt); b->segcnt = (int32_t*)(base + o_seg);
+  b->samp_off = (int64_t*)(base + o_off); b->samp = (float*)(base + o_samp); b->sel = (uint32_t*)(base + o_sel);
+  b->tsum = (double*)(base + o_tsum); b->tsel = (int32_t*)(base + o_tsel); b->means = (float*)(base + o_means);
+  GB_CUDA(cudaMemcpy(b->samp_off, off.data(), (size_t)(p->nseg + 1) * 8, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+void aq_free(gb_plan* p) {
+  AdaqBuf* b = (AdaqBuf*)p->adaq;
+  if (!b) return;
+  cudaFree(b->d_all);
+  delete b;
+  p->adaq = nullptr;
+}
+
+static int aq_grid(int ntiles) { return ntiles < 148 * 8 ? ntiles : 148 * 8; }
+
+int aq_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
+  gb_comm* c = p->comm;
+  AdaqBuf* b = (AdaqBuf*)p->adaq;
+  GB_CHECK(p->prm.memory == GB_MEM_NONE || p->prm.memory == GB_MEM_RESIDUAL, "unsupported memory for AdaQ");
+  const bool mem = p->prm.memory == GB_MEM_RESIDUAL;
+  float* work = mem ? p->d_state0 : const_cast<float*>(d_grad);
+  ++p->epoch;
+  AdaqOut out;
+  const size_t mb = aq_means_bytes(p->nseg);
+  for (int r = 0; r < c->world; ++r) {
+    char* s = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, 0, c->rank);
+    out.hdr[r] = (int2*)s; out.means[r] = (float*)(s + p->hdr_bytes); out.idx[r] = (int32_t*)(s + p->hdr_bytes + mb);
+  }
+  out.n = c->world;
+  StepCtl* ctl = p->d_ctl;
+  const PeerPtrs peers = gb_comm_peers(c);
+  const int grid = aq_grid(p->ntiles);
+  if (mem) aq_count<true><<<grid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, p->prm.beta, p->prm.gamma, ctl, b->sub, b->tcnt);
+  else aq_count<false><<<grid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, 0.f, 1.f, ctl, b->sub, b->tcnt);
+  AQ_LAUNCHED(p);
+  aq_scan<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, b->tcnt, b->segcnt, b->sel); AQ_LAUNCHED(p);
+  const int sgrid = (int)std::min<int64_t>((2 * b->samp_total + 7) / 8, 148 * 8);
+  aq_sample<<<sgrid, GB_THREADS, 0, st>>>(p->tab, work, b->tcnt, b->segcnt, b->sub, b->samp_off, b->samp, b->samp_total,
+                                           p->prm.seed, ctl); AQ_LAUNCHED(p);
+  aq_kth<<<p->nseg * 2, GB_THREADS, 0, st>>>(p->tab, b->segcnt, b->samp_off, b->samp, b->samp_total, p->prm.ratio, b->sel);
+  AQ_LAUNCHED(p);
+  for (int it = 0; it <= 20; ++it) {
+    aq_select<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel); AQ_LAUNCHED(p);
+    aq_adjust<<<(p->nseg * 2 + 127) / 128, 128, 0, st>>>(p->tab, b->segcnt, p->prm.ratio, b->sel); AQ_LAUNCHED(p);
+  }
+  aq_select<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel); AQ_LAUNCHED(p);
+  aq_mean<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, b->tsum, b->tsel, b->means, out, ctl, p->par_stride); AQ_LAUNCHED(p);
+  uint32_t* cursor = p->d_done + 2;
+  GB_CUDA(cudaMemsetAsync(cursor, 0, 4, st));
+  if (mem) aq_emit<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->means, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, ctl, p->par_stride);
+  else aq_emit<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->means, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, ctl, p->par_stride);
+  AQ_LAUNCHED(p);
+  return 0;
+}
+
+int aq_recv(gb_plan* p, float* d_out, cudaStream_t st) {
+  gb_comm* c = p->comm;
+  AdaqIn in;
+  const size_t mb = aq_means_bytes(p->nseg);
+  for (int r = 0; r < c->world; ++r) {
+    const char* s = gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, 0, r);
+    in.hdr[r] = (const int2*)s; in.means[r] = (const float*)(s + p->hdr_bytes); in.idx[r] = (const int32_t*)(s + p->hdr_bytes + mb);
+  }
+  in.n = c->world;
+  const float divisor = p->prm.average ? (float)c->world : 1.f;
+  aq_merge<<<aq_grid(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, gb_comm_peers(c), p->channel, p->d_ctl,
+                                                      p->par_stride, c->status_dev, c->timeout_ns);
+  AQ_LAUNCHED(p);
+  return 0;
+}

@@ -18,6 +18,13 @@ int sk_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 int sk_recv(gb_plan* p, float* d_out, cudaStream_t st);
 size_t sk_header_bytes(int nseg, int q);
 
+// K1-adaq: AdaQ (two sampled thresholds, indices + 2 means per tensor) -- k1_adaq.cu
+int aq_init(gb_plan* p);
+void aq_free(gb_plan* p);
+int aq_send(gb_plan* p, const float* d_grad, cudaStream_t st);
+int aq_recv(gb_plan* p, float* d_out, cudaStream_t st);
+size_t aq_means_bytes(int nseg);
+
 // K0: dense two-shot all-reduce over peer memory (None / FP16 codecs, world > 1)
 int k0_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 int k0_mid(gb_plan* p, cudaStream_t st);

@@ -30,7 +30,8 @@ static int quant_bits(const gb_codec_params& p) {
 }
 
 bool gb_codec_is_sparse(int codec) {
-  return codec == GB_CODEC_TOPK || codec == GB_CODEC_RANDOMK || codec == GB_CODEC_THRESHOLD || codec == GB_CODEC_DGC;
+  return codec == GB_CODEC_TOPK || codec == GB_CODEC_RANDOMK || codec == GB_CODEC_THRESHOLD || codec == GB_CODEC_DGC ||
+         codec == GB_CODEC_ADAQ;
 }
 
 template <typename T>
@@ -43,7 +44,7 @@ static T* carve(char*& cur, size_t count) {
 extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const uint32_t* name_hash,
                               const gb_codec_params* params, gb_plan** out) {
   GB_CHECK(nseg >= 1, "a plan needs at least one segment");
-  GB_CHECK(params->codec >= GB_CODEC_NONE && params->codec <= GB_CODEC_SKETCH, "unknown codec %d", params->codec);
+  GB_CHECK(params->codec >= GB_CODEC_NONE && params->codec <= GB_CODEC_ADAQ, "unknown codec %d", params->codec);
   GB_CHECK(params->memory != GB_MEM_DGC || params->codec == GB_CODEC_DGC, "DGC memory needs the DGC codec");
   gb_plan* p = new gb_plan();
   p->comm = c;
@@ -53,6 +54,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->step = 0;
   p->launches = 0;
   p->sketch = nullptr;
+  p->adaq = nullptr;
   p->bits = quant_bits(*params);
   const bool sparse = gb_codec_is_sparse(params->codec);
 
@@ -86,7 +88,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->h_tile0[nseg] = (int32_t)tile_seg.size();
   p->padded = off;
   p->ntiles = (int)tile_seg.size();
-  if (params->codec == GB_CODEC_THRESHOLD || params->codec == GB_CODEC_DGC) {
+  if (params->codec == GB_CODEC_THRESHOLD || params->codec == GB_CODEC_DGC || params->codec == GB_CODEC_ADAQ) {
     float cap = params->capacity > 0.f ? params->capacity : 1.0f;
     kbase = std::max<int64_t>(1, (int64_t)((double)cap * (double)off));
   }
@@ -158,6 +160,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
     p->hdr_bytes = ((size_t)(p->ntiles + 1) * 2 * 4 + 255) & ~size_t(255);
     size_t per = ((size_t)p->ktotal * 4 + 255) & ~size_t(255);
     p->slot_bytes = p->hdr_bytes + (params->codec == GB_CODEC_RANDOMK ? per : 2 * per);
+    if (params->codec == GB_CODEC_ADAQ) p->slot_bytes = p->hdr_bytes + aq_means_bytes(nseg) + per;   // indices only
   } else {
     p->hdr_bytes = params->codec == GB_CODEC_SKETCH ? sk_header_bytes(nseg, params->quantum_num)
                                                     : (((size_t)nseg * 4 * 4 + 255) & ~size_t(255));
@@ -177,6 +180,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->slot_bytes = (p->slot_bytes + 255) & ~size_t(255);
   p->par_stride = (size_t)c->world * p->slot_bytes;
   if (params->codec == GB_CODEC_SKETCH && sk_init(p)) { gb_plan_destroy(p); return -1; }
+  if (params->codec == GB_CODEC_ADAQ && aq_init(p)) { gb_plan_destroy(p); return -1; }
   GB_CUDA(cudaDeviceSynchronize());
   *out = p;
   return 0;
@@ -186,6 +190,7 @@ extern "C" int gb_plan_destroy(gb_plan* p) {
   if (!p) return 0;
   cudaDeviceSynchronize();
   sk_free(p);
+  aq_free(p);
   cudaFree(p->d_tables);
   cudaFree(p->d_state0);
   cudaFree(p->d_state1);
@@ -244,7 +249,7 @@ extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   gb_launch_tick(p->d_ctl, st);
   p->launches++;
-  int rc = p->prm.codec == GB_CODEC_SKETCH ? sk_send(p, d_grad, st) : p->dense2 ? k0_send(p, d_grad, st) : gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
+  int rc = p->prm.codec == GB_CODEC_SKETCH ? sk_send(p, d_grad, st) : p->prm.codec == GB_CODEC_ADAQ ? aq_send(p, d_grad, st) : p->dense2 ? k0_send(p, d_grad, st) : gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
   if (rc) return rc;
   p->step++;
   return 0;
@@ -254,6 +259,7 @@ extern "C" int gb_plan_recv(gb_plan* p, float* d_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   GB_CHECK(p->epoch > 0, "gb_plan_recv before any gb_plan_send");   // host mirror; counts captured sends too
   if (p->prm.codec == GB_CODEC_SKETCH) return sk_recv(p, d_out, st);
+  if (p->prm.codec == GB_CODEC_ADAQ) return aq_recv(p, d_out, st);
   if (p->dense2) return k0_recv(p, d_out, st);
   return gb_codec_is_sparse(p->prm.codec) ? k1_recv(p, d_out, st) : k2_recv(p, d_out, st);
 }

@@ -73,7 +73,7 @@ def estimate_arena_bytes(numels, params, powersgd, world):
     else:
         from grace_b200.ops.native import CODEC
         code = params.codec
-        if code in (CODEC["threshold"], CODEC["dgc"]):
+        if code in (CODEC["threshold"], CODEC["dgc"], CODEC["adaq"]):
             slot = int(8 * n * (params.capacity or 1.0))
         elif code in (CODEC["topk"], CODEC["randomk"]):
             slot = int(8 * (n * params.ratio + len(numels)))
@@ -94,7 +94,7 @@ def shutdown_engine():
 
 def codec_params(compressor, memory):
     """Translate a built-in (compressor, memory) pair into ``gb_codec_params``; ``None`` if the
-    pair has no native implementation (AdaQ, INCEPTIONN, user classes; PowerSGD has its own plan type)."""
+    pair has no native implementation (INCEPTIONN, user classes; PowerSGD has its own plan type)."""
     from grace_b200.ops.native import CodecParams, CODEC, MEMORY
     p = CodecParams()
     p.beta = p.gamma = 1.0
@@ -132,6 +132,8 @@ def codec_params(compressor, memory):
         p.codec, p.lr = CODEC["efsignsgd"], compressor.learning_rate
     elif t is C.OneBitCompressor:
         p.codec = CODEC["onebit"]
+    elif t is C.AdaqCompressor:
+        p.codec, p.ratio = CODEC["adaq"], compressor.compress_ratio
     elif t is C.SketchCompressor and 2 <= int(compressor.quantiles) <= 255:
         p.codec, p.quantum_num = CODEC["sketch"], int(compressor.quantiles)
     else:

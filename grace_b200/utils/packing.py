@@ -1,0 +1,27 @@
+"""2-bit x 4 -> byte helpers (reference: ``grace_dl/tensorflow/compressor/packing.py:4-30``,
+``encode_byte`` / ``decode_byte``; SURVEY §2.3 last row).
+
+The reference keeps these as a stand-alone TF helper that duplicates the inline packing of
+INCEPTIONN.  Here both names are thin aliases of the one implementation the INCEPTIONN codec
+uses (``grace_b200/compressor/inceptionn.py``), and the native K2-inceptionn kernel writes
+the same byte layout: element ``i`` of quarter ``j`` of the (padded) tag vector lands in
+bits ``2j..2j+1`` of byte ``i``.
+"""
+from __future__ import annotations
+
+import torch
+
+from grace_b200.compressor.inceptionn import pack_tags, unpack_tags
+
+
+def encode_byte(tags: torch.Tensor) -> torch.Tensor:
+    """Pack a 1-D tensor of values in ``0..3`` four to a byte (uint8, ``numel // 4 + 1`` bytes)."""
+    return pack_tags(tags.flatten())
+
+
+def decode_byte(packed: torch.Tensor, numel: int) -> torch.Tensor:
+    """Inverse of :func:`encode_byte`: the first ``numel`` 2-bit values as int32."""
+    return unpack_tags(packed.flatten(), numel)
+
+
+__all__ = ["encode_byte", "decode_byte"]

@@ -39,7 +39,8 @@ enum {
   GB_CODEC_SIGNUM = 11,   /* signum.py:6-37    1 bit of the momentum       */
   GB_CODEC_EFSIGNSGD = 12,/* efsignsgd.py:6-33 1 bit + mean|x|             */
   GB_CODEC_ONEBIT = 13,   /* torch/compressor/onebit.py:6-32 1 bit + 2 means */
-  GB_CODEC_SKETCH = 14    /* tensorflow/compressor/sketch.py:6-39  8-bit quantile bucket + q means (quantum_num = q) */
+  GB_CODEC_SKETCH = 14,   /* tensorflow/compressor/sketch.py:6-39  8-bit quantile bucket + q means (quantum_num = q) */
+  GB_CODEC_ADAQ = 15      /* tensorflow/compressor/adaq.py:6-93    int32 indices (sign in bit 31) + 2 means per tensor */
 };
 
 /* memories (reference: grace_dl/dist/memory/<name>.py) */

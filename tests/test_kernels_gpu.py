@@ -176,6 +176,29 @@ def test_dgc_with_dgc_memory(world):
             assert torch.equal(states[r][1][i], mems[r].residuals[name].reshape(-1))
 
 
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("memory", ["none", "residual"])
+def test_adaq(world, memory):
+    """K1-adaq: same picked index sets as the torch oracle (sampling, k-th sample, <= 20 refinements per sign
+    are all integer/fp32-exact); the two means per tensor are fixed-order double sums, so values agree to an ulp."""
+    grads = make_grads(world, 3)
+    fused, states = run_fused(world, _params("adaq", memory, ratio=0.05, beta=0.9, gamma=1.1), grads)
+    mk = (lambda: M.ResidualMemory(0.9, 1.1)) if memory == "residual" else M.NoneMemory
+    oracle, _, mems = run_oracle(world, lambda: C.AdaqCompressor(0.05, seed=SEED), mk, grads)
+    for s in range(len(grads)):                       # support (which positions were kept) must match exactly
+        for r in range(world):
+            for i in range(len(SIZES)):
+                a, b = fused[s][r][i], oracle[s][r][i].reshape(-1)
+                if memory == "none" or s == 0:
+                    assert torch.equal(a != 0, b != 0), (s, r, i)
+    assert_same(fused, oracle, exact=False, frac=0.001 if memory == "residual" else 0.0, rtol=1e-5, what="adaq")
+    if memory == "residual":
+        for r in range(world):
+            for i, name in enumerate(NAMES):
+                a, b = states[r][0][i], mems[r].residuals[name].reshape(-1)
+                assert int(((a - b).abs() > 1e-5 + 1e-5 * b.abs()).sum()) <= 0.001 * a.numel() + 1, (r, name)
+
+
 @pytest.mark.parametrize("codec,make,exact,frac", [
     ("none", C.NoneCompressor, True, 0.0),
     ("fp16", C.FP16Compressor, True, 0.0),
