@@ -24,7 +24,7 @@ import torch.distributed as dist
 CODECS = [("none", "none"), ("fp16", "none"), ("topk", "residual"), ("randomk", "residual"), ("threshold", "residual"),
           ("dgc", "dgc"), ("qsgd", "none"), ("terngrad", "residual"), ("natural", "residual"), ("u8bit", "none"),
           ("signsgd", "none"), ("signum", "residual"), ("efsignsgd", "efsignsgd"), ("onebit", "residual"),
-          ("sketch", "residual"), ("adaq", "residual")]
+          ("sketch", "residual"), ("adaq", "residual"), ("inceptionn", "residual")]
 
 
 def shapes_of(spec):

@@ -1,0 +1,339 @@
+// K2-inceptionn -- INCEPTIONN variable-width codec.
+//
+// Reference: grace_dl/tensorflow/compressor/inceptionn.py:8-188 (TF graph: per element a 32/16/8/0-bit
+// encoding chosen by the binary exponent, four separate boolean_mask gathers, 2-bit tags packed by a chain of
+// reshape/bitwise ops, decode through find_bins and scatter_nd into freshly created Variables).
+// Oracle of the numerics: grace_b200/compressor/inceptionn.py.
+//
+// One pass per direction, no reductions, no host round trips:
+//   in_send   compensate (ResidualMemory) -> classify by exponent -> tag byte per 4 elements stored straight
+//             into every peer -> block-wide ordered scan of the three class counts (one 64-bit packed word) ->
+//             the tile's values are staged in shared memory as [fp32 ...][16-bit ...][8-bit ...], a byte range
+//             of the stream is claimed with one atomic, the staged words go to every peer with coalesced
+//             stores; residual = x - decode(x) in place; the last CTA releases the flags.
+//   in_recv   each CTA owns an output tile: re-derives the per-element offsets from the sender's tags with the
+//             same scan, decodes from the sender's stream, adds the W ranks in rank order in registers.
+// Wire per rank: 2 bits per element + 4/2/1/0 bytes per element + 16 bytes per tile.
+// quantum_num carries the two exponent cut points: low_exp | mid_exp << 8.
+#include "kernels.cuh"
+
+#include <algorithm>
+
+struct IncOut {
+  int4* hdr[GB_MAX_WORLD];
+  uint8_t* tags[GB_MAX_WORLD];
+  uint32_t* stream[GB_MAX_WORLD];
+  int n;
+};
+
+size_t in_hdr_bytes(int ntiles) { return ((size_t)ntiles * 16 + 255) & ~size_t(255); }
+size_t in_tag_bytes(int64_t padded) { return ((size_t)padded / 4 + 255) & ~size_t(255); }
+
+namespace {
+
+__device__ __forceinline__ float4 ld4(const float* p, int e0, int len) {
+  if (e0 + 4 <= len) return *reinterpret_cast<const float4*>(p + e0);
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (e0 < len) v.x = p[e0];
+  if (e0 + 1 < len) v.y = p[e0 + 1];
+  if (e0 + 2 < len) v.z = p[e0 + 2];
+  if (e0 + 3 < len) v.w = p[e0 + 3];
+  return v;
+}
+__device__ __forceinline__ void st4(float* p, int e0, int len, float4 v) {
+  if (e0 + 4 <= len) { *reinterpret_cast<float4*>(p + e0) = v; return; }
+  if (e0 < len) p[e0] = v.x;
+  if (e0 + 1 < len) p[e0 + 1] = v.y;
+  if (e0 + 2 < len) p[e0 + 2] = v.z;
+  if (e0 + 3 < len) p[e0 + 3] = v.w;
+}
+
+__device__ __forceinline__ int classify(float x, int low_exp, int mid_exp) {
+  const int e = (int)((__float_as_uint(x) >> 23) & 0xFFu);
+  if (e >= 127) return 3;
+  if (e >= mid_exp) return 2;
+  if (e >= low_exp) return 1;            // low_exp <= e < mid_exp
+  return 0;
+}
+// class counts of one thread packed as 16-bit fields: [15:0] 32-bit values, [31:16] 16-bit, [47:32] 8-bit
+__device__ __forceinline__ uint64_t class_word(int cls) { return cls == 3 ? 1ull : cls == 2 ? (1ull << 16) : cls == 1 ? (1ull << 32) : 0ull; }
+
+__device__ __forceinline__ uint64_t warp_incl_scan64(uint64_t v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint64_t n = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += n;
+  }
+  return v;
+}
+
+// Exclusive offsets of this thread's four 4-element groups in (j, thread) order; returns the tile totals.
+__device__ __forceinline__ uint64_t ordered_offsets(const uint64_t pc[4], uint64_t offs[4], uint64_t (*wtot)[GB_THREADS / 32],
+                                                    uint64_t* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint64_t incl[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    incl[j] = warp_incl_scan64(pc[j], lane);
+    if (lane == 31) wtot[j][warp] = incl[j];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint64_t running = 0;
+    for (int j = 0; j < 4; ++j)
+      for (int w = 0; w < GB_THREADS / 32; ++w) {
+        const uint64_t c = wtot[j][w];
+        wtot[j][w] = running;
+        running += c;
+      }
+    *total = running;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 4; ++j) offs[j] = wtot[j][warp] + incl[j] - pc[j];
+  return *total;
+}
+
+__device__ __forceinline__ float dec16(uint32_t w) {
+  const float m = __fmul_rn((float)(w & 0x7FFFu), 1.0f / 16384.0f);
+  return (w >> 15) & 1u ? -m : m;
+}
+__device__ __forceinline__ float dec8(uint32_t w) {
+  const float m = __fmul_rn((float)(w & 0x7Fu), 1.0f / 64.0f);
+  return (w >> 7) & 1u ? -m : m;
+}
+
+template <bool WRITE>
+__global__ void __launch_bounds__(GB_THREADS) in_send_k(SegTable t, const float* __restrict__ grad, float* work, float beta, float gamma,
+                                                        int low_exp, int mid_exp, uint32_t* cursor, IncOut out, int64_t cap_words,
+                                                        uint32_t* status, uint32_t* done, PeerPtrs peers, int channel,
+                                                        const StepCtl* ctl, size_t par_stride) {
+  __shared__ uint32_t stage[GB_TILE];
+  __shared__ uint64_t wtot[4][GB_THREADS / 32];
+  __shared__ uint64_t s_total;
+  __shared__ int s_begin;
+  const uint32_t epoch = ctl->epoch;
+  if (ctl->step == 0) { beta = 0.f; gamma = 1.f; }
+  if (epoch & 1) {
+    for (int r = 0; r < out.n; ++r) {
+      out.hdr[r] = (int4*)((char*)out.hdr[r] + par_stride);
+      out.tags[r] = out.tags[r] + par_stride;
+      out.stream[r] = (uint32_t*)((char*)out.stream[r] + par_stride);
+    }
+  }
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    float vv[4][4];
+    uint64_t pc[4], offs[4];
+    uint32_t tagw = 0;                                  // this thread's 4 tag bytes (one per j)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (e0 < len) {
+        if (WRITE) {
+          const float4 g = ld4(grad + base, e0, len);
+          const float4 r = ld4(work + base, e0, len);
+          v.x = __fadd_rn(__fmul_rn(beta, r.x), __fmul_rn(gamma, g.x)); v.y = __fadd_rn(__fmul_rn(beta, r.y), __fmul_rn(gamma, g.y));
+          v.z = __fadd_rn(__fmul_rn(beta, r.z), __fmul_rn(gamma, g.z)); v.w = __fadd_rn(__fmul_rn(beta, r.w), __fmul_rn(gamma, g.w));
+        } else {
+          v = ld4(work + base, e0, len);
+        }
+      }
+      vv[j][0] = v.x; vv[j][1] = v.y; vv[j][2] = v.z; vv[j][3] = v.w;
+      pc[j] = 0;
+      uint32_t tb = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int cls = (e0 + q < len) ? classify(vv[j][q], low_exp, mid_exp) : 0;
+        tb |= (uint32_t)cls << (2 * q);
+        pc[j] += class_word(cls);
+      }
+      tagw |= tb << (8 * j);
+      if (e0 < len)
+        for (int r = 0; r < out.n; ++r) out.tags[r][(base + e0) >> 2] = (uint8_t)tb;
+    }
+    const uint64_t total = ordered_offsets(pc, offs, wtot, &s_total);
+    const int n32 = (int)(total & 0xFFFFu), n16 = (int)((total >> 16) & 0xFFFFu), n8 = (int)((total >> 32) & 0xFFFFu);
+    uint16_t* st16 = reinterpret_cast<uint16_t*>(stage + n32);
+    uint8_t* st8 = reinterpret_cast<uint8_t*>(stage + n32) + 2 * n16;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      int o32 = (int)(offs[j] & 0xFFFFu), o16 = (int)((offs[j] >> 16) & 0xFFFFu), o8 = (int)((offs[j] >> 32) & 0xFFFFu);
+      if (((tagw >> (8 * j)) & 0xFFu) == 0) continue;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int cls = (tagw >> (8 * j + 2 * q)) & 3u;
+        const float x = vv[j][q];
+        const uint32_t neg = x < 0.f ? 1u : 0u;
+        if (cls == 3) {
+          stage[o32++] = __float_as_uint(x);
+          vv[j][q] = 0.f;
+        } else if (cls == 2) {
+          const uint32_t w = (uint32_t)floorf(__fmul_rn(fabsf(x), 16384.0f)) | (neg << 15);
+          st16[o16++] = (uint16_t)w;
+          vv[j][q] = __fsub_rn(x, dec16(w));
+        } else if (cls == 1) {
+          const uint32_t w = (uint32_t)floorf(__fmul_rn(fabsf(x), 64.0f)) | (neg << 7);
+          st8[o8++] = (uint8_t)w;
+          vv[j][q] = __fsub_rn(x, dec8(w));
+        }
+      }
+      if (WRITE) st4(work + base, e0, len, make_float4(vv[j][0], vv[j][1], vv[j][2], vv[j][3]));
+    }
+    if (WRITE) {
+      // groups without any coded element still need the compensated value written back
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+        if (e0 < len && ((tagw >> (8 * j)) & 0xFFu) == 0) st4(work + base, e0, len, make_float4(vv[j][0], vv[j][1], vv[j][2], vv[j][3]));
+      }
+    }
+    const int words = n32 + (2 * n16 + n8 + 3) / 4;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int64_t begin = words ? (int64_t)atomicAdd(cursor, (uint32_t)words) : 0;
+      int4 h = make_int4((int)begin, n32, n16, n8);
+      if (begin + words > cap_words) {
+        atomicOr(status, GB_STATUS_OVERFLOW);
+        h = make_int4(-1, 0, 0, 0);                     // receivers skip this tile; the host raises on the status word
+      }
+      s_begin = h.x;
+      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = h;
+    }
+    __syncthreads();
+    const int begin = s_begin;
+    if (begin >= 0) {
+      for (int r = 0; r < out.n; ++r) {
+        uint32_t* d = out.stream[r] + begin;
+        for (int i = threadIdx.x; i < words; i += GB_THREADS) d[i] = stage[i];
+      }
+    }
+    __syncthreads();
+  }
+  release_flags_last_block(done, peers, channel, epoch);
+}
+
+struct IncIn {
+  const int4* hdr[GB_MAX_WORLD];
+  const uint8_t* tags[GB_MAX_WORLD];
+  const uint32_t* stream[GB_MAX_WORLD];
+  int n;
+};
+
+__global__ void __launch_bounds__(GB_THREADS) in_recv_k(SegTable t, IncIn in, float* outp, float divisor, PeerPtrs peers, int channel,
+                                                        const StepCtl* ctl, size_t par_stride, uint32_t* status, uint64_t timeout_ns) {
+  __shared__ uint64_t wtot[4][GB_THREADS / 32];
+  __shared__ uint64_t s_total;
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) {
+    for (int r = 0; r < in.n; ++r) {
+      in.hdr[r] = (const int4*)((const char*)in.hdr[r] + par_stride);
+      in.tags[r] = in.tags[r] + par_stride;
+      in.stream[r] = (const uint32_t*)((const char*)in.stream[r] + par_stride);
+    }
+  }
+  wait_all_ranks(peers, channel, epoch, status, timeout_ns);
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    float acc[4][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[j][q] = 0.f;
+    for (int r = 0; r < in.n; ++r) {
+      const int4 h = in.hdr[r][tile];
+      if (h.x < 0) continue;                            // sender overflowed its slot (status already raised)
+      uint64_t pc[4], offs[4];
+      uint32_t tagw = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+        const uint32_t tb = e0 < len ? in.tags[r][(base + e0) >> 2] : 0u;
+        tagw |= tb << (8 * j);
+        pc[j] = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) pc[j] += class_word((tb >> (2 * q)) & 3u);
+      }
+      ordered_offsets(pc, offs, wtot, &s_total);
+      const uint32_t* sp = in.stream[r] + h.x;
+      const uint16_t* s16 = reinterpret_cast<const uint16_t*>(sp + h.y);
+      const uint8_t* s8 = reinterpret_cast<const uint8_t*>(sp + h.y) + 2 * h.z;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (((tagw >> (8 * j)) & 0xFFu) == 0) continue;
+        int o32 = (int)(offs[j] & 0xFFFFu), o16 = (int)((offs[j] >> 16) & 0xFFFFu), o8 = (int)((offs[j] >> 32) & 0xFFFFu);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int cls = (tagw >> (8 * j + 2 * q)) & 3u;
+          if (cls == 3) acc[j][q] += __uint_as_float(sp[o32++]);
+          else if (cls == 2) acc[j][q] += dec16(s16[o16++]);
+          else if (cls == 1) acc[j][q] += dec8(s8[o8++]);
+        }
+      }
+      __syncthreads();                                  // wtot / s_total are reused by the next rank
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      float4 v = make_float4(acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+      if (divisor != 1.f) {          // torch's CUDA tensor / python-scalar is a multiply by the reciprocal
+        const float inv = __fdiv_rn(1.0f, divisor);
+        v.x = __fmul_rn(v.x, inv); v.y = __fmul_rn(v.y, inv); v.z = __fmul_rn(v.z, inv); v.w = __fmul_rn(v.w, inv);
+      }
+      st4(outp + base, e0, len, v);
+    }
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- host side
+#define IN_LAUNCHED(p) do { (p)->launches++; GB_CUDA(cudaGetLastError()); } while (0)
+
+static int in_grid(int ntiles) { return ntiles < 148 * 8 ? ntiles : 148 * 8; }
+
+int in_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
+  gb_comm* c = p->comm;
+  GB_CHECK(p->prm.memory == GB_MEM_NONE || p->prm.memory == GB_MEM_RESIDUAL, "unsupported memory for INCEPTIONN");
+  const bool mem = p->prm.memory == GB_MEM_RESIDUAL;
+  float* work = mem ? p->d_state0 : const_cast<float*>(d_grad);
+  ++p->epoch;
+  IncOut out;
+  const size_t tb = in_tag_bytes(p->padded);
+  for (int r = 0; r < c->world; ++r) {
+    char* s = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, 0, c->rank);
+    out.hdr[r] = (int4*)s; out.tags[r] = (uint8_t*)(s + p->hdr_bytes); out.stream[r] = (uint32_t*)(s + p->hdr_bytes + tb);
+  }
+  out.n = c->world;
+  const int low_exp = p->prm.quantum_num & 0xFF, mid_exp = (p->prm.quantum_num >> 8) & 0x1FF;
+  uint32_t* cursor = p->d_done + 2;
+  GB_CUDA(cudaMemsetAsync(cursor, 0, 4, st));
+  const PeerPtrs peers = gb_comm_peers(c);
+  if (mem) in_send_k<true><<<in_grid(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, work, p->prm.beta, p->prm.gamma, low_exp, mid_exp, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, p->d_ctl, p->par_stride);
+  else in_send_k<false><<<in_grid(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, work, 0.f, 1.f, low_exp, mid_exp, cursor, out, p->ktotal, c->status_dev, p->d_done, peers, p->channel, p->d_ctl, p->par_stride);
+  IN_LAUNCHED(p);
+  return 0;
+}
+
+int in_recv(gb_plan* p, float* d_out, cudaStream_t st) {
+  gb_comm* c = p->comm;
+  IncIn in;
+  const size_t tb = in_tag_bytes(p->padded);
+  for (int r = 0; r < c->world; ++r) {
+    const char* s = gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, 0, r);
+    in.hdr[r] = (const int4*)s; in.tags[r] = (const uint8_t*)(s + p->hdr_bytes); in.stream[r] = (const uint32_t*)(s + p->hdr_bytes + tb);
+  }
+  in.n = c->world;
+  const float divisor = p->prm.average ? (float)c->world : 1.f;
+  in_recv_k<<<in_grid(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, gb_comm_peers(c), p->channel, p->d_ctl, p->par_stride,
+                                                      c->status_dev, c->timeout_ns);
+  IN_LAUNCHED(p);
+  return 0;
+}

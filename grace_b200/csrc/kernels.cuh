@@ -25,6 +25,12 @@ int aq_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 int aq_recv(gb_plan* p, float* d_out, cudaStream_t st);
 size_t aq_means_bytes(int nseg);
 
+// K2-inceptionn: INCEPTIONN (2-bit tag + 32/16/8/0-bit value per element) -- k2_inceptionn.cu
+int in_send(gb_plan* p, const float* d_grad, cudaStream_t st);
+int in_recv(gb_plan* p, float* d_out, cudaStream_t st);
+size_t in_hdr_bytes(int ntiles);
+size_t in_tag_bytes(int64_t padded);
+
 // K0: dense two-shot all-reduce over peer memory (None / FP16 codecs, world > 1)
 int k0_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 int k0_mid(gb_plan* p, cudaStream_t st);

@@ -44,7 +44,7 @@ static T* carve(char*& cur, size_t count) {
 extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const uint32_t* name_hash,
                               const gb_codec_params* params, gb_plan** out) {
   GB_CHECK(nseg >= 1, "a plan needs at least one segment");
-  GB_CHECK(params->codec >= GB_CODEC_NONE && params->codec <= GB_CODEC_ADAQ, "unknown codec %d", params->codec);
+  GB_CHECK(params->codec >= GB_CODEC_NONE && params->codec <= GB_CODEC_INCEPTIONN, "unknown codec %d", params->codec);
   GB_CHECK(params->memory != GB_MEM_DGC || params->codec == GB_CODEC_DGC, "DGC memory needs the DGC codec");
   gb_plan* p = new gb_plan();
   p->comm = c;
@@ -88,7 +88,8 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->h_tile0[nseg] = (int32_t)tile_seg.size();
   p->padded = off;
   p->ntiles = (int)tile_seg.size();
-  if (params->codec == GB_CODEC_THRESHOLD || params->codec == GB_CODEC_DGC || params->codec == GB_CODEC_ADAQ) {
+  if (params->codec == GB_CODEC_THRESHOLD || params->codec == GB_CODEC_DGC || params->codec == GB_CODEC_ADAQ ||
+      params->codec == GB_CODEC_INCEPTIONN) {            // INCEPTIONN: capacity of the value stream in 32-bit words
     float cap = params->capacity > 0.f ? params->capacity : 1.0f;
     kbase = std::max<int64_t>(1, (int64_t)((double)cap * (double)off));
   }
@@ -161,6 +162,9 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
     size_t per = ((size_t)p->ktotal * 4 + 255) & ~size_t(255);
     p->slot_bytes = p->hdr_bytes + (params->codec == GB_CODEC_RANDOMK ? per : 2 * per);
     if (params->codec == GB_CODEC_ADAQ) p->slot_bytes = p->hdr_bytes + aq_means_bytes(nseg) + per;   // indices only
+  } else if (params->codec == GB_CODEC_INCEPTIONN) {
+    p->hdr_bytes = in_hdr_bytes(p->ntiles);
+    p->slot_bytes = p->hdr_bytes + in_tag_bytes(p->padded) + (((size_t)p->ktotal * 4 + 255) & ~size_t(255));
   } else {
     p->hdr_bytes = params->codec == GB_CODEC_SKETCH ? sk_header_bytes(nseg, params->quantum_num)
                                                     : (((size_t)nseg * 4 * 4 + 255) & ~size_t(255));
@@ -249,7 +253,7 @@ extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   gb_launch_tick(p->d_ctl, st);
   p->launches++;
-  int rc = p->prm.codec == GB_CODEC_SKETCH ? sk_send(p, d_grad, st) : p->prm.codec == GB_CODEC_ADAQ ? aq_send(p, d_grad, st) : p->dense2 ? k0_send(p, d_grad, st) : gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
+  int rc = p->prm.codec == GB_CODEC_SKETCH ? sk_send(p, d_grad, st) : p->prm.codec == GB_CODEC_ADAQ ? aq_send(p, d_grad, st) : p->prm.codec == GB_CODEC_INCEPTIONN ? in_send(p, d_grad, st) : p->dense2 ? k0_send(p, d_grad, st) : gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
   if (rc) return rc;
   p->step++;
   return 0;
@@ -260,6 +264,7 @@ extern "C" int gb_plan_recv(gb_plan* p, float* d_out, void* stream) {
   GB_CHECK(p->epoch > 0, "gb_plan_recv before any gb_plan_send");   // host mirror; counts captured sends too
   if (p->prm.codec == GB_CODEC_SKETCH) return sk_recv(p, d_out, st);
   if (p->prm.codec == GB_CODEC_ADAQ) return aq_recv(p, d_out, st);
+  if (p->prm.codec == GB_CODEC_INCEPTIONN) return in_recv(p, d_out, st);
   if (p->dense2) return k0_recv(p, d_out, st);
   return gb_codec_is_sparse(p->prm.codec) ? k1_recv(p, d_out, st) : k2_recv(p, d_out, st);
 }

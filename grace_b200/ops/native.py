@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libgrace_b200.so")
 BUILD_SH = os.path.join(os.path.dirname(_HERE), "csrc", "build.sh")
 
 CODEC = dict(none=0, fp16=1, topk=2, randomk=3, threshold=4, dgc=5, qsgd=6, terngrad=7, natural=8, u8bit=9,
-             signsgd=10, signum=11, efsignsgd=12, onebit=13, sketch=14, adaq=15)
+             signsgd=10, signum=11, efsignsgd=12, onebit=13, sketch=14, adaq=15, inceptionn=16)
 MEMORY = dict(none=0, residual=1, dgc=2)
 
 

@@ -75,6 +75,8 @@ def estimate_arena_bytes(numels, params, powersgd, world):
         code = params.codec
         if code in (CODEC["threshold"], CODEC["dgc"], CODEC["adaq"]):
             slot = int(8 * n * (params.capacity or 1.0))
+        elif code == CODEC["inceptionn"]:
+            slot = int(4 * n * (params.capacity or 1.0)) + n // 4
         elif code in (CODEC["topk"], CODEC["randomk"]):
             slot = int(8 * (n * params.ratio + len(numels)))
         elif code in (CODEC["none"], CODEC["fp16"]):
@@ -94,7 +96,7 @@ def shutdown_engine():
 
 def codec_params(compressor, memory):
     """Translate a built-in (compressor, memory) pair into ``gb_codec_params``; ``None`` if the
-    pair has no native implementation (INCEPTIONN, user classes; PowerSGD has its own plan type)."""
+    pair has no native implementation (user classes; PowerSGD has its own plan type)."""
     from grace_b200.ops.native import CodecParams, CODEC, MEMORY
     p = CodecParams()
     p.beta = p.gamma = 1.0
@@ -134,6 +136,8 @@ def codec_params(compressor, memory):
         p.codec = CODEC["onebit"]
     elif t is C.AdaqCompressor:
         p.codec, p.ratio = CODEC["adaq"], compressor.compress_ratio
+    elif t is C.INCEPTIONNCompressor and 0 < compressor.low_exp <= compressor.mid_exp <= 127:
+        p.codec, p.quantum_num = CODEC["inceptionn"], int(compressor.low_exp) | (int(compressor.mid_exp) << 8)
     elif t is C.SketchCompressor and 2 <= int(compressor.quantiles) <= 255:
         p.codec, p.quantum_num = CODEC["sketch"], int(compressor.quantiles)
     else:

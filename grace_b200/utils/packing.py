@@ -3,9 +3,9 @@
 
 The reference keeps these as a stand-alone TF helper that duplicates the inline packing of
 INCEPTIONN.  Here both names are thin aliases of the one implementation the INCEPTIONN codec
-uses (``grace_b200/compressor/inceptionn.py``), and the native K2-inceptionn kernel writes
-the same byte layout: element ``i`` of quarter ``j`` of the (padded) tag vector lands in
-bits ``2j..2j+1`` of byte ``i``.
+uses (``grace_b200/compressor/inceptionn.py``): element ``i`` of quarter ``j`` of the (padded)
+tag vector lands in bits ``2j..2j+1`` of byte ``i``.  (The native K2-inceptionn kernel keeps
+its tags tile-local instead: element ``e`` sits in bits ``2(e%4)`` of byte ``e//4``.)
 """
 from __future__ import annotations
 

@@ -40,7 +40,9 @@ enum {
   GB_CODEC_EFSIGNSGD = 12,/* efsignsgd.py:6-33 1 bit + mean|x|             */
   GB_CODEC_ONEBIT = 13,   /* torch/compressor/onebit.py:6-32 1 bit + 2 means */
   GB_CODEC_SKETCH = 14,   /* tensorflow/compressor/sketch.py:6-39  8-bit quantile bucket + q means (quantum_num = q) */
-  GB_CODEC_ADAQ = 15      /* tensorflow/compressor/adaq.py:6-93    int32 indices (sign in bit 31) + 2 means per tensor */
+  GB_CODEC_ADAQ = 15,     /* tensorflow/compressor/adaq.py:6-93    int32 indices (sign in bit 31) + 2 means per tensor */
+  GB_CODEC_INCEPTIONN = 16 /* tensorflow/compressor/inceptionn.py:8-188  2-bit tag + 32/16/8/0-bit value per element
+                              (quantum_num = low_exp | mid_exp << 8) */
 };
 
 /* memories (reference: grace_dl/dist/memory/<name>.py) */

@@ -199,6 +199,26 @@ def test_adaq(world, memory):
                 assert int(((a - b).abs() > 1e-5 + 1e-5 * b.abs()).sum()) <= 0.001 * a.numel() + 1, (r, name)
 
 
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("memory", ["none", "residual"])
+def test_inceptionn(world, memory):
+    """K2-inceptionn: every step of the codec is exact fp32 / integer arithmetic -> bit-exact against the oracle.
+    Gradients span all four encodings (0, 8, 16, 32 bits: |x| from 1e-5 to ~6)."""
+    g = torch.Generator(device="cuda").manual_seed(7)
+    grads = [[[torch.randn(n, device="cuda", generator=g) * torch.pow(10.0, torch.rand(n, device="cuda", generator=g) * 5 - 4.5)
+               for n in SIZES] for r in range(world)] for _ in range(3)]
+    comp = C.INCEPTIONNCompressor()
+    prm = _params("inceptionn", memory, beta=0.9, gamma=1.1, quantum_num=comp.low_exp | (comp.mid_exp << 8))
+    fused, states = run_fused(world, prm, grads)
+    mk = (lambda: M.ResidualMemory(0.9, 1.1)) if memory == "residual" else M.NoneMemory
+    oracle, _, mems = run_oracle(world, C.INCEPTIONNCompressor, mk, grads)
+    assert_same(fused, oracle, exact=True, what="inceptionn")
+    if memory == "residual":
+        for r in range(world):
+            for i, name in enumerate(NAMES):
+                assert torch.equal(states[r][0][i], mems[r].residuals[name].reshape(-1)), (r, name)
+
+
 @pytest.mark.parametrize("codec,make,exact,frac", [
     ("none", C.NoneCompressor, True, 0.0),
     ("fp16", C.FP16Compressor, True, 0.0),
