@@ -73,48 +73,73 @@ __device__ __forceinline__ float comp1(const QuantArgs& a, float r, float g) {
 
 // ---------------------------------------------------------------- pass 1: per-tile partials
 // tilestats[tile][8] = { sum x, sum x^2, max|x|, sum|x|, count(x<0), sum(x<0), M2 about the tile mean, - }
-template <bool NEED_M2>
-__global__ void __launch_bounds__(GB_THREADS, NEED_M2 ? 4 : 8) k2_stats(SegTable t, const float* __restrict__ grad,
-                                                                        const float* __restrict__ res, QuantArgs a_in,
-                                                                        const StepCtl* ctl, float* tilestats) {
+// Only the reductions the codec's scalars need are computed (QSGD: sum x^2; TernGrad: sum, max, M2;
+// EFSignSGD: sum|x|; OneBit: sum, count/sum of negatives; 8-bit: max) -- the generic version spent more
+// issue slots on six shuffle reductions per tile than on the loads.  Unused tilestats fields stay zero.
+template <int CODEC>
+__global__ void __launch_bounds__(GB_THREADS, 4) k2_stats(SegTable t, const float* __restrict__ grad,
+                                                                                          const float* __restrict__ res, QuantArgs a_in,
+                                                                                          const StepCtl* ctl, float* tilestats) {
+  constexpr bool NEED_M2 = CODEC == GB_CODEC_TERNGRAD;
+  constexpr bool W_S = CODEC == GB_CODEC_TERNGRAD || CODEC == GB_CODEC_ONEBIT;
+  constexpr bool W_S2 = CODEC == GB_CODEC_QSGD;
+  constexpr bool W_MX = CODEC == GB_CODEC_TERNGRAD || CODEC == GB_CODEC_U8BIT;
+  constexpr bool W_SA = CODEC == GB_CODEC_EFSIGNSGD;
+  constexpr bool W_NEG = CODEC == GB_CODEC_ONEBIT;
   __shared__ float sh[6][GB_THREADS / 32];
   const QuantArgs a = resolve(a_in, ctl);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
     float s = 0.f, s2 = 0.f, mx = 0.f, sa = 0.f, cn = 0.f, sn = 0.f;
     float keep[GB_TILE / GB_THREADS];                 // this thread's 16 values stay in registers
+    float4 gg[GB_TILE / (GB_THREADS * 4)], rr[GB_TILE / (GB_THREADS * 4)];
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {       // all loads of the tile in flight first
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      gg[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      rr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (e0 < len) {
+        gg[j] = *reinterpret_cast<const float4*>(grad + base + e0);
+        if (a.has_mem) rr[j] = *reinterpret_cast<const float4*>(res + base + e0);
+      }
+    }
 #pragma unroll
     for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
       const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
-      float x[4] = {0.f, 0.f, 0.f, 0.f};
-      if (e0 < len) {
-        const float4 g = *reinterpret_cast<const float4*>(grad + base + e0);
-        float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (a.has_mem) r = *reinterpret_cast<const float4*>(res + base + e0);
-        x[0] = comp1(a, r.x, g.x); x[1] = comp1(a, r.y, g.y); x[2] = comp1(a, r.z, g.z); x[3] = comp1(a, r.w, g.w);
-      }
+      const float x[4] = {comp1(a, rr[j].x, gg[j].x), comp1(a, rr[j].y, gg[j].y), comp1(a, rr[j].z, gg[j].z), comp1(a, rr[j].w, gg[j].w)};
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         if (NEED_M2) keep[j * 4 + q] = x[q];
         if (e0 + q < len) {
           const float v = x[q];
-          s += v; s2 += v * v; mx = fmaxf(mx, fabsf(v)); sa += fabsf(v);
-          if (v < 0.f) { cn += 1.f; sn += v; }
+          if (W_S) s += v;
+          if (W_S2) s2 += v * v;
+          if (W_MX) mx = fmaxf(mx, fabsf(v));
+          if (W_SA) sa += fabsf(v);
+          if (W_NEG && v < 0.f) { cn += 1.f; sn += v; }
         }
       }
     }
-    s = warp_sum(s); s2 = warp_sum(s2); mx = warp_max(mx); sa = warp_sum(sa); cn = warp_sum(cn); sn = warp_sum(sn);
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (lane == 0) { sh[0][wid] = s; sh[1][wid] = s2; sh[2][wid] = mx; sh[3][wid] = sa; sh[4][wid] = cn; sh[5][wid] = sn; }
+    if (W_S) { s = warp_sum(s); if (lane == 0) sh[0][wid] = s; }
+    if (W_S2) { s2 = warp_sum(s2); if (lane == 0) sh[1][wid] = s2; }
+    if (W_MX) { mx = warp_max(mx); if (lane == 0) sh[2][wid] = mx; }
+    if (W_SA) { sa = warp_sum(sa); if (lane == 0) sh[3][wid] = sa; }
+    if (W_NEG) { cn = warp_sum(cn); sn = warp_sum(sn); if (lane == 0) { sh[4][wid] = cn; sh[5][wid] = sn; } }
     __syncthreads();
     float tile_sum = 0.f;
-    for (int w = 0; w < GB_THREADS / 32; ++w) tile_sum += sh[0][w];
+    if (NEED_M2)
+      for (int w = 0; w < GB_THREADS / 32; ++w) tile_sum += sh[0][w];
     if (threadIdx.x < 6) {
-      float acc = 0.f;
-      for (int w = 0; w < GB_THREADS / 32; ++w) acc = threadIdx.x == 2 ? fmaxf(acc, sh[2][w]) : acc + sh[threadIdx.x][w];
-      tilestats[(size_t)tile * 8 + threadIdx.x] = acc;
+      const int f = threadIdx.x;
+      const bool used = (f == 0 && W_S) || (f == 1 && W_S2) || (f == 2 && W_MX) || (f == 3 && W_SA) || (f >= 4 && W_NEG);
+      if (used) {
+        float acc = 0.f;
+        for (int w = 0; w < GB_THREADS / 32; ++w) acc = f == 2 ? fmaxf(acc, sh[2][w]) : acc + sh[f][w];
+        tilestats[(size_t)tile * 8 + f] = acc;
+      }
     }
     __syncthreads();
     if (NEED_M2) {
@@ -381,27 +406,34 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
 // ---------------------------------------------------------------- receive: unpack, decode, add
 // final: 0 -> sum / divisor;  1 -> majority vote (sum >= 0 -> +1 else -1);  2 -> sum / lr
 template <int CODEC, int BITS>
-__global__ void __launch_bounds__(GB_THREADS) k2_decode(SegTable t, WireIn in, size_t hdr_bytes, float* outp, int quantum,
+__global__ void __launch_bounds__(GB_THREADS, 6) k2_decode(SegTable t, WireIn in, size_t hdr_bytes, float* outp, int quantum,
                                                         int final_mode, float divisor, PeerPtrs peers, int channel,
                                                         const StepCtl* ctl, size_t par_stride, uint32_t* status,
                                                         uint64_t timeout_ns) {
   const uint32_t epoch = ctl->epoch;
   if (epoch & 1) shift(in, par_stride);
   __shared__ float s_tab[128];
+  __shared__ float4 sts[GB_MAX_WORLD];
+  __shared__ CodecConst ccs[GB_MAX_WORLD];
+  constexpr bool HAS_STATS = CODEC == GB_CODEC_QSGD || CODEC == GB_CODEC_TERNGRAD || CODEC == GB_CODEC_EFSIGNSGD ||
+                             CODEC == GB_CODEC_ONEBIT || CODEC == GB_CODEC_U8BIT;
+  if (threadIdx.x < GB_MAX_WORLD) { sts[threadIdx.x] = make_float4(0.f, 0.f, 0.f, 0.f); ccs[threadIdx.x] = CodecConst{0.f, 0.f}; }
   if (CODEC == GB_CODEC_U8BIT && threadIdx.x < 128) s_tab[threadIdx.x] = g_u8_table[threadIdx.x];
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
-    float4 sts[GB_MAX_WORLD];
-    CodecConst ccs[GB_MAX_WORLD];
-#pragma unroll
-    for (int r = 0; r < GB_MAX_WORLD; ++r) {
-      if (r < in.n) {
-        sts[r] = reinterpret_cast<const float4*>(in.slot[r])[seg];
-        ccs[r] = codec_const<CODEC>(sts[r], quantum);
+    // the senders' per-tensor scalars live in shared memory (8 ranks x 24 bytes in registers halved the
+    // occupancy of this bandwidth-bound kernel); codecs without scalars skip the loads altogether
+    if (HAS_STATS) {
+      __syncthreads();
+      if (threadIdx.x < in.n) {
+        const float4 s4 = reinterpret_cast<const float4*>(in.slot[threadIdx.x])[seg];
+        sts[threadIdx.x] = s4;
+        ccs[threadIdx.x] = codec_const<CODEC>(s4, quantum);
       }
+      __syncthreads();
     }
     const float inv_div = divisor != 1.f ? __fdiv_rn(1.0f, divisor) : 1.f;
 #pragma unroll
@@ -507,8 +539,14 @@ int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   for (int r = 0; r < c->world; ++r) out.slot[r] = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, 0, c->rank);
   const PeerPtrs peers = gb_comm_peers(c);
   if (needs_stats(a.codec)) {
-    if (a.codec == GB_CODEC_TERNGRAD) k2_stats<true><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_ctl, p->d_tilestats);
-    else k2_stats<false><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_ctl, p->d_tilestats);
+    const int g = grid_for(p->ntiles);
+    switch (a.codec) {
+      case GB_CODEC_QSGD: k2_stats<GB_CODEC_QSGD><<<g, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_ctl, p->d_tilestats); break;
+      case GB_CODEC_TERNGRAD: k2_stats<GB_CODEC_TERNGRAD><<<g, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_ctl, p->d_tilestats); break;
+      case GB_CODEC_EFSIGNSGD: k2_stats<GB_CODEC_EFSIGNSGD><<<g, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_ctl, p->d_tilestats); break;
+      case GB_CODEC_ONEBIT: k2_stats<GB_CODEC_ONEBIT><<<g, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_ctl, p->d_tilestats); break;
+      default: k2_stats<GB_CODEC_U8BIT><<<g, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, a, p->d_ctl, p->d_tilestats); break;
+    }
     LAUNCHED(p);
     k2_finalize<<<p->nseg, 32, 0, st>>>(p->tab, p->d_tilestats, a.codec, p->d_segstats, out, p->d_ctl, p->par_stride); LAUNCHED(p);
   }

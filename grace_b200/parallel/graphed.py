@@ -10,10 +10,94 @@ collective library.
 
     step = GraphedStep(model, optimizer, loss_fn, example_inputs)   # optimizer: hvd.DistributedOptimizer
     loss = step(x, y)                                               # copies inputs into static buffers, replays
+
+Feeding from the host (data loader with pinned memory) is pipelined the usual way -- the next batch's
+host -> device copy runs on a copy stream while the current step executes, and a step's loss comes back
+through pinned memory without stalling the launch of the next step:
+
+    step.feed(x0, y0)
+    for i in range(n):
+        pending = step.run()                    # consumes the fed batch, replays, starts the loss read-back
+        if i + 1 < n:
+            step.feed(*next_batch())            # overlaps the replay that is in flight
+        log(previous.item()) if i else None     # loss of step i-1: already on the host
+        previous = pending
+
+(the reference harness copies and synchronises inside the step: examples/torch/pytorch_mnist.py:148-155).
 """
 from __future__ import annotations
 
 import torch
+
+
+class PendingScalar:
+    """A device scalar on its way to pinned host memory; ``item()`` waits for the copy only."""
+
+    def __init__(self, host, event):
+        self._host, self._event = host, event
+
+    def done(self):
+        return self._event.query()
+
+    def item(self):
+        self._event.synchronize()
+        return self._host.item()
+
+    def __float__(self):
+        return float(self.item())
+
+
+class PinnedPrefetcher:
+    """Double-buffered host -> device input pipeline on a dedicated copy stream.
+
+    ``feed(*host_tensors)`` starts the asynchronous copies of one batch (pinned memory makes them truly
+    asynchronous) into one of two device staging sets; ``get()`` makes the current stream wait for the oldest
+    fed batch and returns its device tensors; ``release()`` (called by the consumer once it has enqueued
+    its reads) lets a later ``feed`` reuse that staging set."""
+
+    def __init__(self, example_inputs, device=None, depth=2):
+        device = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        self.stream = torch.cuda.Stream(device=device)
+        self.slots = [[torch.empty(t.shape, dtype=t.dtype, device=device) for t in example_inputs] for _ in range(depth)]
+        self.ready = [torch.cuda.Event() for _ in range(depth)]
+        self.consumed = [None] * depth
+        self.fed, self.taken = 0, 0
+        self.bytes_per_batch = sum(t.numel() * t.element_size() for t in example_inputs)
+
+    def feed(self, *host_inputs):
+        if self.fed - self.taken >= len(self.slots):
+            raise RuntimeError("PinnedPrefetcher: %d batches already in flight" % len(self.slots))
+        slot = self.fed % len(self.slots)
+        with torch.cuda.stream(self.stream):
+            if self.consumed[slot] is not None:
+                self.stream.wait_event(self.consumed[slot])       # the previous user of this staging set is done
+            for dst, src in zip(self.slots[slot], host_inputs):
+                dst.copy_(src, non_blocking=True)
+            self.ready[slot].record(self.stream)
+        self.fed += 1
+
+    def get(self):
+        if self.taken >= self.fed:
+            raise RuntimeError("PinnedPrefetcher.get() without a fed batch")
+        slot = self.taken % len(self.slots)
+        torch.cuda.current_stream().wait_event(self.ready[slot])
+        self._current = slot
+        self.taken += 1
+        return self.slots[slot]
+
+    def release(self):
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.consumed[self._current] = ev
+
+
+def read_back(scalar, host=None):
+    """Start the device -> pinned-host copy of a scalar tensor on the current stream."""
+    host = torch.empty((), dtype=scalar.dtype, pin_memory=True) if host is None else host
+    host.copy_(scalar, non_blocking=True)
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream())
+    return PendingScalar(host, ev)
 
 
 class GraphedStep:
@@ -38,6 +122,8 @@ class GraphedStep:
             self.static_loss = self._step_body()
         self.native_launches_per_step = (fused.launches() - n0) if fused is not None else 0
         self.replays = 0
+        self._feeder = None
+        self._loss_host = None
 
     def _step_body(self):
         self.optimizer.zero_grad()
@@ -54,3 +140,21 @@ class GraphedStep:
         self.graph.replay()
         self.replays += 1
         return self.static_loss
+
+    # ---- pipelined host feeding (see the module docstring)
+    def feed(self, *host_inputs):
+        """Start the host -> device copy of the next step's inputs on the copy stream."""
+        if self._feeder is None:
+            self._feeder = PinnedPrefetcher(host_inputs, device=self.static_inputs[0].device)
+            self._loss_host = [torch.empty((), dtype=self.static_loss.dtype, pin_memory=True) for _ in range(4)]
+        self._feeder.feed(*host_inputs)
+
+    def run(self):
+        """One step on the oldest fed batch; returns a :class:`PendingScalar` for its loss."""
+        staged = self._feeder.get()
+        for dst, src in zip(self.static_inputs, staged):
+            dst.copy_(src, non_blocking=True)                     # device -> device (+ memory-format change)
+        self._feeder.release()
+        self.graph.replay()
+        self.replays += 1
+        return read_back(self.static_loss, self._loss_host[self.replays % 4])      # ring of 4: read a loss within 3 steps

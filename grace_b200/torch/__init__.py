@@ -11,4 +11,4 @@ from grace_b200.torch.mpi_ops import (  # noqa: F401
 from grace_b200.torch.optimizer import (  # noqa: F401
     DistributedOptimizer, broadcast_parameters, broadcast_optimizer_state)
 from grace_b200.torch.helper import grace_from_params  # noqa: F401
-from grace_b200.parallel.graphed import GraphedStep  # noqa: F401,E402
+from grace_b200.parallel.graphed import GraphedStep, PinnedPrefetcher, PendingScalar, read_back  # noqa: F401,E402

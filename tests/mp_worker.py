@@ -32,7 +32,8 @@ def main():
         ("natural", "residual", "allgather", True), ("efsignsgd", "efsignsgd", "allgather", False),
         ("onebit", "residual", "allgather", False), ("qsgd", "none", "allgather", False),
         ("terngrad", "residual", "allgather", False), ("u8bit", "none", "allgather", False),
-        ("sketch", "none", "allgather", False),
+        ("sketch", "none", "allgather", False), ("adaq", "residual", "allgather", False),
+        ("inceptionn", "residual", "allgather", True),
     ]
     shapes = {"conv.weight": (64, 33, 3, 3), "fc.weight": (100, 257), "bn.bias": (77,), "big": (300001,)}
     for comp, mem, comm, exact in triples:

@@ -167,6 +167,60 @@ def test_graphed_step_matches_eager_step():
     assert torch.allclose(a, b, rtol=1e-5, atol=1e-6), float((a - b).abs().max())
 
 
+def test_graphed_step_pipelined_host_feeding():
+    """feed()/run(): pinned-host batches copied on the copy stream while the previous replay runs, losses
+    read back one step late -- same parameters and same losses as feeding device tensors directly."""
+    import grace_b200.torch as hvd
+    data = _data(10)
+    host = [(x.cpu().pin_memory(), y.cpu().pin_memory()) for x, y in data]
+
+    def run(pipelined):
+        torch.manual_seed(0)
+        model = MnistNet().cuda().eval()
+        opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.5)
+        grc = hvd.grace_from_params(dict(compressor="qsgd", memory="none", communicator="allgather"))
+        opt = hvd.DistributedOptimizer(opt, grc, named_parameters=model.named_parameters(), fused=True)
+        step = hvd.GraphedStep(model, opt, lambda m, x, y: F.nll_loss(m(x), y), data[0], amp_dtype=None, warmup=2)
+        losses = []
+        if pipelined:
+            step.feed(*host[2])
+            prev = None
+            for i in range(2, 10):
+                pend = step.run()
+                if i + 1 < 10:
+                    step.feed(*host[i + 1])
+                if prev is not None:
+                    losses.append(prev.item())
+                prev = pend
+            losses.append(prev.item())
+        else:
+            for x, y in data[2:]:
+                losses.append(step(x, y).item())
+        torch.cuda.synchronize()
+        return torch.cat([p.detach().flatten() for p in model.parameters()]), losses
+
+    (a, la), (b, lb) = run(True), run(False)
+    # (cuDNN's backward kernels are not bit-reproducible run to run, hence tolerances as in the test above)
+    assert torch.allclose(a, b, rtol=1e-4, atol=1e-5), float((a - b).abs().max())
+    assert len(la) == 8 and all(abs(p - q) <= 1e-4 * max(1.0, abs(q)) for p, q in zip(la, lb)), (la, lb)
+
+
+def test_pinned_prefetcher_guards():
+    import grace_b200.torch as hvd
+    h = torch.arange(8.0).pin_memory()
+    pf = hvd.PinnedPrefetcher([h])
+    with pytest.raises(RuntimeError):
+        pf.get()
+    pf.feed(h); pf.feed(h + 1)
+    with pytest.raises(RuntimeError):
+        pf.feed(h)                                    # two batches already in flight
+    (a,) = pf.get(); a = a.clone(); pf.release()
+    (b,) = pf.get(); b = b.clone(); pf.release()
+    torch.cuda.synchronize()
+    assert torch.equal(a.cpu(), h) and torch.equal(b.cpu(), h + 1)
+    assert hvd.read_back(b.sum()).item() == float((h + 1).sum())
+
+
 def test_grad_accumulation_and_state_dict():
     import grace_b200.torch as hvd
     data = _data(6)
