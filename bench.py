@@ -29,7 +29,8 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "ddp"],
+                    help="ours | reference (unmodified baseline/_ref) | ddp (library baseline: torch DDP + NCCL, no compression)")
     ap.add_argument("--model", default="resnet50", help="torchvision model name, or bert-large / bert-base")
     ap.add_argument("--seq-len", type=int, default=128, help="BERT only")
     ap.add_argument("--batch-size", type=int, default=32, help="per GPU (reference harness default)")
@@ -177,6 +178,18 @@ def main():
 
         def zero():
             opt.zero_grad()
+    elif args.impl == "ddp":
+        # library baseline: uncompressed gradients through torch DDP + NCCL all-reduce
+        if world > 1:
+            from torch.nn.parallel import DistributedDataParallel as DDP
+            model = DDP(model, device_ids=[local_rank], gradient_as_bucket_view=True)
+        comp, mem, comm = "none (torch DDP)", "none", "nccl all-reduce"
+
+        def exchange_and_step():
+            base_opt.step()
+
+        def zero():
+            base_opt.zero_grad(set_to_none=False)
     else:
         # the reference's own public API and stock code path: grace_from_params + the manual
         # per-parameter loop of examples/dist/CIFAR10-dawndist/core.py:202-208

@@ -169,6 +169,32 @@ def main():
         except Exception as exc:
             if rank == 0:
                 print("none-nvls  unavailable: %r" % (exc,), flush=True)
+    if world > 1 and (not want or "nccl" in want):
+        # library baseline: one NCCL all-reduce (+ 1/W scale) of the same 102 MB buffer, timed the same way
+        buf = torch.randn((numel + 127) // 128 * 128, device="cuda")
+        times = []
+        for it in range(args.warmup + args.iters):
+            flush.zero_()
+            dist.barrier()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            dist.all_reduce(buf)
+            buf.div_(world)
+            b.record()
+            torch.cuda.synchronize()
+            if it >= args.warmup:
+                times.append(a.elapsed_time(b))
+        ms = sorted(times)[len(times) // 2]
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t)
+        busbw = 2 * (world - 1) / world * numel * 4 / ms / 1e6
+        rows.append(dict(codec="nccl-allreduce", memory="none", world=world, elements=numel, ms=ms, launches_per_exchange=2,
+                         bus_bandwidth_gbs=busbw, peaks=how))
+        if rank == 0:
+            print("%-10s %-9s W=%d  %8.3f ms  all-reduce bus bandwidth %.0f GB/s (library baseline: dist.all_reduce + div_)"
+                  % ("nccl", "none", world, ms, busbw), flush=True)
     if not want or "powersgd" in want:
         # K3: all >=2-D tensors through the native PowerSGD plan (rank 4, with residual memory)
         from grace_b200.parallel.engine import PowerSGDPlan

@@ -74,4 +74,5 @@ struct gb_plan {
   int64_t launches;
   void* sketch;          // SketchML buffers (k2_sketch.cu)
   void* adaq;            // AdaQ buffers (k1_adaq.cu)
+  uint32_t* d_samp;      // DGC: sampled magnitudes (k1_sparse.cu)
 };

@@ -7,11 +7,12 @@
 // Per bucket, for every tensor and both signs at once:
 //   aq_count     compensate (ResidualMemory) + count positives / negatives per 128-element sub-block
 //   aq_scan      exclusive prefix of the per-tile counts inside each tensor
-//   aq_sample    one warp per sample: the r-th positive (negative) element is located through the
-//                tile prefix, the 32 sub-block counts of that tile and one 128-element ballot -- the
+//   aq_sample    one thread per sample: the r-th positive (negative) element is located through the
+//                tile prefix, the 32 sub-block counts of that tile and a scan of one 128-element sub-block -- the
 //                reference's boolean_mask + gather without ever materialising the masked tensor
 //   aq_kth       k-th largest sampled magnitude (3 histogram rounds, one CTA per tensor and sign)
-//   21 x (aq_select, aq_adjust)   the refinement loop, device-resident (no host round trips)
+//   21 x aq_select   the refinement loop, device-resident: count above the current thresholds; the CTA that
+//                finishes last applies the x1.25 / x0.9 rule to every (tensor, sign) -- no host round trips
 //   aq_select<final> + aq_mean    fixed-order sums -> one mean per tensor and sign, stored to every peer
 //   aq_emit      unordered compaction of the picked indices (sign in bit 31) straight into every peer's
 //                slot; residual = x - mean at the picked positions; the last CTA releases the flags
@@ -38,6 +39,7 @@ struct AdaqBuf {
   int32_t* tsel;      // [ntiles][2]      per-tile count of the finally selected values
   float* means;       // [nseg][2]
   int64_t samp_total;
+  int64_t max_samples;  // largest per-tensor sample capacity
 };
 
 struct AdaqOut {
@@ -164,86 +166,109 @@ __global__ void __launch_bounds__(GB_THREADS) aq_scan(SegTable t, int32_t* tcnt,
   }
 }
 
-__device__ __forceinline__ int aq_find_seg(const int64_t* off, int nseg, int64_t p) {
-  int lo = 0, hi = nseg;
-  while (hi - lo > 1) {
-    const int mid = (lo + hi) >> 1;
-    if (off[mid] <= p) lo = mid; else hi = mid;
-  }
-  return lo;
-}
-
 // ---------------------------------------------------------------- sampling
-// One warp per sample.  The reference gathers `boolean_mask(x, sign)[pos]`; here the pos-th element of that
-// sign is found through three levels of counts (tile prefix -> 32 sub-block counts -> 128-element ballot).
+// One THREAD per sample, grid = (sample chunks, tensor x sign).  The reference gathers
+// `boolean_mask(x, sign)[pos]`; here the pos-th element of that sign is found through three levels of counts
+// (binary search over the tile prefix -> the tile's 32 sub-block counts -> a scan of one 128-element
+// sub-block, 16 elements at a time).  A first version used one warp per sample and was latency-bound
+// (226 us for ResNet-50's 511 K samples: ~20 dependent loads per warp, 54 waves); with a thread per sample the
+// same chains run 32x more in parallel.
 __global__ void __launch_bounds__(GB_THREADS) aq_sample(SegTable t, const float* __restrict__ work, const int32_t* __restrict__ tcnt,
                                                         const int32_t* __restrict__ segcnt, const uint8_t* __restrict__ sub,
                                                         const int64_t* __restrict__ samp_off, float* samp, int64_t samp_total,
                                                         uint32_t seed, const StepCtl* ctl) {
+  const int seg = blockIdx.y >> 1, s = blockIdx.y & 1;
+  const int count = segcnt[seg * 2 + s];
+  const int ns = (int)ceil((double)count * 0.01);
+  const int i = blockIdx.x * GB_THREADS + threadIdx.x;
+  if (i >= ns) return;
   const uint32_t step = ctl->step;
-  const int lane = threadIdx.x & 31;
-  const int64_t nwarps = (int64_t)gridDim.x * (GB_THREADS / 32);
-  for (int64_t w = (int64_t)blockIdx.x * (GB_THREADS / 32) + (threadIdx.x >> 5); w < 2 * samp_total; w += nwarps) {
-    const int s = w >= samp_total ? 1 : 0;
-    const int64_t j = w - (int64_t)s * samp_total;
-    const int seg = aq_find_seg(samp_off, t.nseg, j);
-    const int i = (int)(j - samp_off[seg]);
-    const int count = segcnt[seg * 2 + s];
-    const int ns = (int)ceil((double)count * 0.01);
-    if (i >= ns) continue;
-    const Philox4 r4 = philox4x32((uint32_t)(i >> 2), 2u * step + (uint32_t)s, GB_STREAM_SAMPLE, 0u, seed, t.seg_hash[seg]);
-    const uint32_t bits = (i & 3) == 0 ? r4.x : (i & 3) == 1 ? r4.y : (i & 3) == 2 ? r4.z : r4.w;
-    int r = (int)__fmul_rn(u32_to_unit(bits), (float)count);
-    r = min(r, count - 1);
-    // tile: the last one whose exclusive prefix is <= r
-    int lo = t.seg_tile0[seg], hi = t.seg_tile0[seg + 1];
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      if (tcnt[mid * 2 + s] <= r) lo = mid; else hi = mid;
-    }
-    int rr = r - tcnt[lo * 2 + s];
-    // sub-block
-    const int c = sub[((size_t)lo * 2 + s) * 32 + lane];
-    const int incl = warp_incl_scan(c, lane);
-    const uint32_t above = __ballot_sync(0xffffffffu, incl > rr);
-    const int sb = above ? __ffs(above) - 1 : 31;
-    rr -= __shfl_sync(0xffffffffu, incl - c, sb);
-    // element
-    int sg2, local0, len;
-    int64_t base;
-    tile_bounds(t, lo, sg2, base, local0, len);
-    const int e0 = sb * 128 + lane * 4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (e0 < len) v = ld4(work + base, e0, len);
-    const float vv[4] = {v.x, v.y, v.z, v.w};
-    uint32_t m = 0;
+  const Philox4 r4 = philox4x32((uint32_t)(i >> 2), 2u * step + (uint32_t)s, GB_STREAM_SAMPLE, 0u, seed, t.seg_hash[seg]);
+  const uint32_t bits = (i & 3) == 0 ? r4.x : (i & 3) == 1 ? r4.y : (i & 3) == 2 ? r4.z : r4.w;
+  int r = (int)__fmul_rn(u32_to_unit(bits), (float)count);
+  r = min(r, count - 1);
+  // tile: the last one whose exclusive prefix is <= r
+  int lo = t.seg_tile0[seg], hi = t.seg_tile0[seg + 1];
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (tcnt[mid * 2 + s] <= r) lo = mid; else hi = mid;
+  }
+  int rr = r - tcnt[lo * 2 + s];
+  // sub-block: 32 one-byte counts = two 16-byte loads
+  const uint4* sc = reinterpret_cast<const uint4*>(sub + ((size_t)lo * 2 + s) * 32);
+  const uint4 c0 = sc[0], c1 = sc[1];
+  const uint32_t cw[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+  int sb = 31;
+  {
+    int acc = 0;
+    bool found = false;
 #pragma unroll
-    for (int q = 0; q < 4; ++q) m |= ((s ? vv[q] < 0.f : vv[q] > 0.f) ? 1u : 0u) << q;
-    const int c4 = __popc(m);
-    const int incl4 = warp_incl_scan(c4, lane);
-    const uint32_t above4 = __ballot_sync(0xffffffffu, incl4 > rr);
-    const int ls = above4 ? __ffs(above4) - 1 : 31;
-    const int rr2 = rr - __shfl_sync(0xffffffffu, incl4 - c4, ls);
-    if (lane == ls) {
-      int seen = 0;
-      float val = 0.f;
+    for (int k = 0; k < 32; ++k) {
+      const int c = (int)((cw[k >> 2] >> (8 * (k & 3))) & 0xFFu);
+      if (!found && acc + c > rr) { sb = k; rr -= acc; found = true; }
+      acc += c;
+    }
+  }
+  // element inside the 128-element sub-block
+  int sg2, local0, len;
+  int64_t base;
+  tile_bounds(t, lo, sg2, base, local0, len);
+  const float* x = work + base;
+  float val = 0.f;
+  int seen = 0;
+  bool done = false;
+  for (int e0 = sb * 128; e0 < sb * 128 + 128 && !done; e0 += 16) {
+    float4 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = (e0 + 4 * k < len) ? ld4(x, e0 + 4 * k, len) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float vv[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        if ((m >> q) & 1u) {
-          if (seen == rr2) val = fabsf(vv[q]);
+        const bool hit = s ? vv[q] < 0.f : vv[q] > 0.f;
+        if (hit) {
+          if (!done && seen == rr) { val = fabsf(vv[q]); done = true; }
           ++seen;
         }
       }
-      samp[(int64_t)s * samp_total + j] = val;
     }
   }
+  samp[(int64_t)s * samp_total + samp_off[seg] + i] = val;
+}
+
+// Parallel version of "walk the histogram from the top bin down to the bin that holds the k-th largest":
+// every thread sums nb/GB_THREADS bins (highest first), a block-wide inclusive scan gives the number of elements
+// in strictly higher bins.  Thread 0 walking 2048 shared-memory bins serially cost ~20 us per round.
+__device__ __forceinline__ void select_bin(const uint32_t* hist, int nb, uint32_t krem, uint32_t* part, uint32_t* out_bin,
+                                           uint32_t* out_krem) {
+  const int per = nb / GB_THREADS;
+  const int hi = nb - 1 - threadIdx.x * per;
+  uint32_t c[8];
+  uint32_t mine = 0;
+  for (int k = 0; k < per; ++k) { c[k] = hist[hi - k]; mine += c[k]; }
+  part[threadIdx.x] = mine;
+  __syncthreads();
+  for (int o = 1; o < GB_THREADS; o <<= 1) {
+    const uint32_t add = threadIdx.x >= o ? part[threadIdx.x - o] : 0u;
+    __syncthreads();
+    part[threadIdx.x] += add;
+    __syncthreads();
+  }
+  uint32_t running = part[threadIdx.x] - mine;
+  for (int k = 0; k < per; ++k) {
+    if (running < krem && running + c[k] >= krem) { *out_bin = (uint32_t)(hi - k); *out_krem = krem - running; }
+    running += c[k];
+  }
+  __syncthreads();
 }
 
 // One CTA per (tensor, sign): k-th largest of the ns sampled magnitudes -> initial threshold.
 __global__ void __launch_bounds__(GB_THREADS) aq_kth(SegTable t, const int32_t* __restrict__ segcnt, const int64_t* __restrict__ samp_off,
                                                      const float* __restrict__ samp, int64_t samp_total, double ratio, uint32_t* sel) {
   __shared__ uint32_t hist[2048];
-  __shared__ uint32_t s_prefix, s_krem;
+  __shared__ uint32_t part[GB_THREADS];
+  __shared__ uint32_t s_prefix, s_krem, s_bin;
   const int seg = blockIdx.x >> 1, s = blockIdx.x & 1;
   const int count = segcnt[seg * 2 + s];
   uint32_t* q = sel + (seg * 2 + s) * 4;
@@ -268,19 +293,10 @@ __global__ void __launch_bounds__(GB_THREADS) aq_kth(SegTable t, const int32_t* 
       else { if ((b >> 10) == prefix) atomicAdd(&hist[b & 1023u], 1u); }
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-      uint32_t running = 0;
-      const uint32_t krem = s_krem;
-      for (int b = nb - 1; b >= 0; --b) {
-        const uint32_t c = hist[b];
-        if (running + c >= krem) {
-          s_prefix = round == 0 ? (uint32_t)b : ((prefix << 10) | (uint32_t)b);
-          s_krem = krem - running;
-          break;
-        }
-        running += c;
-      }
-    }
+    const uint32_t krem = s_krem;
+    __syncthreads();
+    select_bin(hist, nb, krem, part, &s_bin, &s_krem);
+    if (threadIdx.x == 0) s_prefix = round == 0 ? s_bin : ((prefix << 10) | s_bin);
     __syncthreads();
   }
   if (threadIdx.x == 0) { q[0] = s_prefix; q[1] = 0u; q[2] = 0u; q[3] = 0u; }
@@ -299,11 +315,30 @@ __device__ __forceinline__ double block_sum_d(double v, double* sh) {
   return tot;
 }
 
+__device__ __forceinline__ void aq_adjust_one(uint32_t* q, int count, double ratio) {
+  if (q[1]) return;
+  const double target = ceil((double)count * ratio);
+  const double selected = (double)q[2];
+  float thr = __uint_as_float(q[0]);
+  const bool over = selected > 1.25 * target, under = selected < 0.8 * target;
+  if (q[3] < 20u && (over || under)) {
+    thr = over ? __fmul_rn(1.25f, thr) : __fmul_rn(0.9f, thr);
+    q[3] += 1u;
+    q[2] = 0u;
+  } else {
+    if (selected < 1.0) thr = __fmul_rn(0.8f, thr);
+    q[1] = 1u;
+  }
+  q[0] = __float_as_uint(thr);
+}
+
 template <bool FINAL>
 __global__ void __launch_bounds__(GB_THREADS) aq_select(SegTable t, const float* __restrict__ work, uint32_t* sel, double* tsum,
-                                                        int32_t* tsel) {
+                                                        int32_t* tsel, const int32_t* __restrict__ segcnt, double ratio,
+                                                        uint32_t* done) {
   __shared__ double shd[GB_THREADS / 32];
   __shared__ int shc[2];
+  __shared__ int s_last;
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
@@ -357,25 +392,17 @@ __global__ void __launch_bounds__(GB_THREADS) aq_select(SegTable t, const float*
     }
     __syncthreads();
   }
-}
-
-__global__ void aq_adjust(SegTable t, const int32_t* __restrict__ segcnt, double ratio, uint32_t* sel) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < t.nseg * 2; i += gridDim.x * blockDim.x) {
-    uint32_t* q = sel + i * 4;
-    if (q[1]) continue;
-    const double target = ceil((double)segcnt[i] * ratio);
-    const double selected = (double)q[2];
-    float thr = __uint_as_float(q[0]);
-    const bool over = selected > 1.25 * target, under = selected < 0.8 * target;
-    if (q[3] < 20u && (over || under)) {
-      thr = over ? __fmul_rn(1.25f, thr) : __fmul_rn(0.9f, thr);
-      q[3] += 1u;
-      q[2] = 0u;
-    } else {
-      if (selected < 1.0) thr = __fmul_rn(0.8f, thr);
-      q[1] = 1u;
+  if (!FINAL) {
+    // the CTA that finishes last applies the refinement rule to every (tensor, sign): one launch per iteration
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      for (int i = threadIdx.x; i < t.nseg * 2; i += GB_THREADS) aq_adjust_one(sel + i * 4, segcnt[i], ratio);
+      if (threadIdx.x == 0) *done = 0;
     }
-    q[0] = __float_as_uint(thr);
   }
 }
 
@@ -550,13 +577,17 @@ __global__ void __launch_bounds__(GB_THREADS) aq_merge(SegTable t, AdaqIn in, fl
 #define AQ_LAUNCHED(p) do { (p)->launches++; GB_CUDA(cudaGetLastError()); } while (0)
 
 int aq_init(gb_plan* p) {
+  GB_CHECK(p->nseg * 2 <= 65535, "AdaQ plan: too many tensors in one bucket (%d)", p->nseg);
   AdaqBuf* b = new AdaqBuf();
+  b->max_samples = 1;
   p->adaq = b;
   std::vector<int64_t> off(p->nseg + 1);
   int64_t tot = 0;
   for (int s = 0; s < p->nseg; ++s) {
     off[s] = tot;
-    tot += (int64_t)ceil((double)p->h_numel[s] * 0.01) + 1;
+    const int64_t cap = (int64_t)ceil((double)p->h_numel[s] * 0.01) + 1;
+    tot += cap;
+    b->max_samples = std::max(b->max_samples, cap);
   }
   off[p->nseg] = tot;
   b->samp_total = tot;
@@ -606,16 +637,18 @@ int aq_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   else aq_count<false><<<grid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, 0.f, 1.f, ctl, b->sub, b->tcnt);
   AQ_LAUNCHED(p);
   aq_scan<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, b->tcnt, b->segcnt, b->sel); AQ_LAUNCHED(p);
-  const int sgrid = (int)std::min<int64_t>((2 * b->samp_total + 7) / 8, 148 * 8);
+  const dim3 sgrid((unsigned)((b->max_samples + GB_THREADS - 1) / GB_THREADS), (unsigned)(p->nseg * 2));
   aq_sample<<<sgrid, GB_THREADS, 0, st>>>(p->tab, work, b->tcnt, b->segcnt, b->sub, b->samp_off, b->samp, b->samp_total,
                                            p->prm.seed, ctl); AQ_LAUNCHED(p);
   aq_kth<<<p->nseg * 2, GB_THREADS, 0, st>>>(p->tab, b->segcnt, b->samp_off, b->samp, b->samp_total, p->prm.ratio, b->sel);
   AQ_LAUNCHED(p);
+  uint32_t* adj_done = p->d_done + 4;
   for (int it = 0; it <= 20; ++it) {
-    aq_select<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel); AQ_LAUNCHED(p);
-    aq_adjust<<<(p->nseg * 2 + 127) / 128, 128, 0, st>>>(p->tab, b->segcnt, p->prm.ratio, b->sel); AQ_LAUNCHED(p);
+    aq_select<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel, b->segcnt, p->prm.ratio, adj_done);
+    AQ_LAUNCHED(p);
   }
-  aq_select<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel); AQ_LAUNCHED(p);
+  aq_select<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel, b->segcnt, p->prm.ratio, adj_done);
+  AQ_LAUNCHED(p);
   aq_mean<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, b->tsum, b->tsel, b->means, out, ctl, p->par_stride); AQ_LAUNCHED(p);
   uint32_t* cursor = p->d_done + 2;
   GB_CUDA(cudaMemsetAsync(cursor, 0, 4, st));

@@ -714,49 +714,70 @@ __global__ void __launch_bounds__(GB_THREADS) k1_dgc_accumulate(SegTable t, cons
   }
 }
 
-// One CTA per segment: k-th largest magnitude among max(1, int(0.01 n)) positions sampled
-// with replacement (Philox stream 1), by three histogram rounds over the sample.
-__global__ void __launch_bounds__(GB_THREADS) k1_dgc_sample(SegTable t, const float* __restrict__ v, double ratio, uint32_t seed,
-                                                           const StepCtl* ctl, uint32_t* sel) {
-  const uint32_t step = ctl->step;
+// Sampling with replacement (Philox stream 1), one thread per sample on a (chunk, tensor) grid: magnitudes of
+// max(1, int(0.01 n)) positions go to a scratch list (seg_k = samples per tensor, seg_kbase = their offsets).
+__global__ void __launch_bounds__(GB_THREADS) k1_dgc_gather(SegTable t, const float* __restrict__ v, uint32_t seed, const StepCtl* ctl,
+                                                           uint32_t* samp) {
+  const int seg = blockIdx.y;
+  const int ns = t.seg_k[seg];
+  const int i = blockIdx.x * GB_THREADS + threadIdx.x;
+  if (i >= ns) return;
+  const int n = t.seg_numel[seg];
+  const Philox4 r = philox4x32((uint32_t)(i >> 2), ctl->step, GB_STREAM_SAMPLE, 0u, seed, t.seg_hash[seg]);
+  const uint32_t bits = (i & 3) == 0 ? r.x : (i & 3) == 1 ? r.y : (i & 3) == 2 ? r.z : r.w;
+  int pos = (int)__fmul_rn(u32_to_unit(bits), (float)n);
+  pos = min(pos, n - 1);
+  samp[t.seg_kbase[seg] + i] = absbits(v[t.seg_off[seg] + pos]);
+}
+
+// One CTA per segment: k-th largest of the sampled magnitudes by three histogram rounds over the scratch list.
+__global__ void __launch_bounds__(GB_THREADS) k1_dgc_sample(SegTable t, const uint32_t* __restrict__ samp, double ratio, uint32_t* sel) {
   __shared__ uint32_t hist[2048];
+  __shared__ uint32_t part[GB_THREADS];
   __shared__ uint32_t s_prefix, s_krem;
   const int seg = blockIdx.x;
   const int n = t.seg_numel[seg];
-  const int ns = max(1, (int)((double)n * 0.01));
+  const int ns = t.seg_k[seg];
   int k = max(1, (int)((double)n * ratio * 0.01));
   k = min(k, ns);
-  const float* x = v + t.seg_off[seg];
-  const uint32_t hash = t.seg_hash[seg];
+  const uint32_t* x = samp + t.seg_kbase[seg];
   if (threadIdx.x == 0) { s_prefix = 0; s_krem = (uint32_t)k; }
   for (int round = 0; round < 3; ++round) {
     const int nb = round == 0 ? 2048 : 1024;
     for (int b = threadIdx.x; b < nb; b += blockDim.x) hist[b] = 0;
     __syncthreads();
     const uint32_t prefix = s_prefix;
-    for (int i4 = threadIdx.x; i4 * 4 < ns; i4 += blockDim.x) {
-      const Philox4 r = philox4x32((uint32_t)i4, step, GB_STREAM_SAMPLE, 0u, seed, hash);
-      const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
-      for (int q = 0; q < 4 && i4 * 4 + q < ns; ++q) {
-        int pos = (int)__fmul_rn(u32_to_unit(rr[q]), (float)n);
-        pos = min(pos, n - 1);
-        const uint32_t b = absbits(x[pos]);
-        if (round == 0) atomicAdd(&hist[b >> 20], 1u);
-        else if (round == 1) { if ((b >> 20) == prefix) atomicAdd(&hist[(b >> 10) & 1023u], 1u); }
-        else { if ((b >> 10) == prefix) atomicAdd(&hist[b & 1023u], 1u); }
-      }
+    for (int i = threadIdx.x; i < ns; i += blockDim.x) {
+      const uint32_t b = x[i];
+      if (round == 0) atomicAdd(&hist[b >> 20], 1u);
+      else if (round == 1) { if ((b >> 20) == prefix) atomicAdd(&hist[(b >> 10) & 1023u], 1u); }
+      else { if ((b >> 10) == prefix) atomicAdd(&hist[b & 1023u], 1u); }
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-      uint32_t running = 0, krem = s_krem;
-      for (int b = nb - 1; b >= 0; --b) {
-        const uint32_t c = hist[b];
-        if (running + c >= krem) {
-          s_prefix = round == 0 ? (uint32_t)b : ((prefix << 10) | (uint32_t)b);
+    {
+      // parallel walk from the top bin down to the one holding the k-th largest sample (a single thread
+      // walking 2048 shared-memory bins cost ~20 us per round)
+      const uint32_t krem = s_krem;
+      const int per = nb / GB_THREADS;
+      const int hi = nb - 1 - threadIdx.x * per;
+      uint32_t c[8];
+      uint32_t mine = 0;
+      for (int i = 0; i < per; ++i) { c[i] = hist[hi - i]; mine += c[i]; }
+      part[threadIdx.x] = mine;
+      __syncthreads();
+      for (int o = 1; o < GB_THREADS; o <<= 1) {
+        const uint32_t add = threadIdx.x >= o ? part[threadIdx.x - o] : 0u;
+        __syncthreads();
+        part[threadIdx.x] += add;
+        __syncthreads();
+      }
+      uint32_t running = part[threadIdx.x] - mine;
+      for (int i = 0; i < per; ++i) {
+        if (running < krem && running + c[i] >= krem) {
+          s_prefix = round == 0 ? (uint32_t)(hi - i) : ((prefix << 10) | (uint32_t)(hi - i));
           s_krem = krem - running;
-          break;
         }
-        running += c;
+        running += c[i];
       }
     }
     __syncthreads();
@@ -764,8 +785,10 @@ __global__ void __launch_bounds__(GB_THREADS) k1_dgc_sample(SegTable t, const fl
   if (threadIdx.x == 0) { sel[seg * 4] = s_prefix; sel[seg * 4 + 1] = 0; sel[seg * 4 + 2] = 0; sel[seg * 4 + 3] = 0; }
 }
 
-__global__ void __launch_bounds__(GB_THREADS) k1_dgc_count(SegTable t, const float* __restrict__ v, uint32_t* sel) {
+__global__ void __launch_bounds__(GB_THREADS) k1_dgc_count(SegTable t, const float* __restrict__ v, uint32_t* sel, double ratio,
+                                                          uint32_t* done) {
   __shared__ int sh[GB_THREADS / 32];
+  __shared__ int s_last;
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
@@ -785,21 +808,28 @@ __global__ void __launch_bounds__(GB_THREADS) k1_dgc_count(SegTable t, const flo
     c = block_sum_i(c, sh);
     if (threadIdx.x == 0 && c) atomicAdd(&sel[seg * 4 + 3], (uint32_t)c);
   }
-}
-
-__global__ void k1_dgc_adjust(SegTable t, double ratio, uint32_t* sel) {
-  for (int seg = blockIdx.x * blockDim.x + threadIdx.x; seg < t.nseg; seg += gridDim.x * blockDim.x) {
-    if (sel[seg * 4 + 2]) continue;
-    const double n = (double)t.seg_numel[seg];
-    const double selected = (double)sel[seg * 4 + 3];
-    float thr = __uint_as_float(sel[seg * 4]);
-    if (selected > 1.3 * n * ratio) thr = __fmul_rn(1.3f, thr);
-    else if (selected < 0.7 * n * ratio) thr = __fmul_rn(0.7f, thr);
-    else sel[seg * 4 + 2] = 1;
-    sel[seg * 4] = __float_as_uint(thr);
-    sel[seg * 4 + 3] = 0;
+  // the CTA that finishes last applies the x1.3 / x0.7 refinement rule (compressor/dgc.py:28-36) to every tensor
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(done, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (s_last) {
+    __threadfence();
+    for (int seg = threadIdx.x; seg < t.nseg; seg += GB_THREADS) {
+      if (sel[seg * 4 + 2]) continue;
+      const double n = (double)t.seg_numel[seg];
+      const double selected = (double)sel[seg * 4 + 3];
+      float thr = __uint_as_float(sel[seg * 4]);
+      if (selected > 1.3 * n * ratio) thr = __fmul_rn(1.3f, thr);
+      else if (selected < 0.7 * n * ratio) thr = __fmul_rn(0.7f, thr);
+      else sel[seg * 4 + 2] = 1;
+      sel[seg * 4] = __float_as_uint(thr);
+      sel[seg * 4 + 3] = 0;
+    }
+    if (threadIdx.x == 0) *done = 0;
   }
 }
+
 
 static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   gb_comm* c = p->comm;
@@ -824,10 +854,14 @@ static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   } else {
     work = const_cast<float*>(d_grad);
   }
-  k1_dgc_sample<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, work, p->prm.ratio, p->prm.seed, ctl, p->d_sel); LAUNCHED(p);
+  int max_ns = 1;
+  for (int s = 0; s < p->nseg; ++s) max_ns = std::max(max_ns, (int)p->h_k[s]);
+  GB_CHECK(p->nseg <= 65535 && p->d_samp, "DGC plan: sample scratch missing or too many tensors (%d)", p->nseg);
+  k1_dgc_gather<<<dim3((max_ns + GB_THREADS - 1) / GB_THREADS, p->nseg), GB_THREADS, 0, st>>>(p->tab, work, p->prm.seed, ctl, p->d_samp);
+  LAUNCHED(p);
+  k1_dgc_sample<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, p->d_samp, p->prm.ratio, p->d_sel); LAUNCHED(p);
   for (int it = 0; it < 10; ++it) {
-    k1_dgc_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel); LAUNCHED(p);
-    k1_dgc_adjust<<<(p->nseg + 127) / 128, 128, 0, st>>>(p->tab, p->prm.ratio, p->d_sel); LAUNCHED(p);
+    k1_dgc_count<<<grid, GB_THREADS, 0, st>>>(p->tab, work, p->d_sel, p->prm.ratio, p->d_done + 4); LAUNCHED(p);
   }
   uint32_t* cursor = p->d_done + 2;
   GB_CUDA(cudaMemsetAsync(cursor, 0, 4, st));

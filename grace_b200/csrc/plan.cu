@@ -55,6 +55,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->launches = 0;
   p->sketch = nullptr;
   p->adaq = nullptr;
+  p->d_samp = nullptr;
   p->bits = quant_bits(*params);
   const bool sparse = gb_codec_is_sparse(params->codec);
 
@@ -74,6 +75,8 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
     int64_t k = 0;
     if (params->codec == GB_CODEC_TOPK || params->codec == GB_CODEC_RANDOMK)
       k = std::max<int64_t>(1, (int64_t)((double)numels[s] * (double)params->ratio));
+    if (params->codec == GB_CODEC_DGC)          // samples per tensor (dgc.py:17); seg_kbase = offsets into the sample scratch
+      k = std::max<int64_t>(1, (int64_t)((double)numels[s] * 0.01));
     k = std::min<int64_t>(k, numels[s]);
     p->h_k[s] = (int32_t)k;
     p->h_kbase[s] = kbase;
@@ -156,6 +159,9 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
     GB_CUDA(cudaMemset(p->d_state1, 0, p->padded * 4));
   }
 
+  p->d_samp = nullptr;
+  if (params->codec == GB_CODEC_DGC) GB_CUDA(cudaMalloc((void**)&p->d_samp, (size_t)(p->h_kbase[nseg] + 1) * 4));
+
   // ---- wire slot
   if (sparse) {
     p->hdr_bytes = ((size_t)(p->ntiles + 1) * 2 * 4 + 255) & ~size_t(255);
@@ -198,6 +204,7 @@ extern "C" int gb_plan_destroy(gb_plan* p) {
   cudaFree(p->d_tables);
   cudaFree(p->d_state0);
   cudaFree(p->d_state1);
+  cudaFree(p->d_samp);
   delete p;
   return 0;
 }
