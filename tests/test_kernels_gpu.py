@@ -314,3 +314,57 @@ def test_state_survives_plan_roundtrip():
             assert torch.equal(a, b)
     finally:
         e.destroy()
+
+
+def test_missing_peer_sets_timeout_status_instead_of_hanging():
+    """Failure detection: a rank that never sends makes the receiver's bounded flag wait expire; the
+    kernel returns, the host-mapped status word carries the reason and check_status() raises.  The next exchange
+    works again once the late rank has caught up."""
+    from grace_b200.ops.native import NativeError
+    from grace_b200.parallel.engine import Engine
+    engines = Engine.local(2)
+    try:
+        for e in engines:
+            e.set_timeout_ms(30)
+        plans = [e.plan(SIZES, NAMES, _params("signsgd")) for e in engines]
+        bufs = [torch.randn(plans[0].padded, device="cuda") for _ in range(2)]
+        outs = [torch.empty(plans[0].padded, device="cuda") for _ in range(2)]
+        plans[0].send(bufs[0])                      # rank 1 stays silent
+        plans[0].recv(outs[0])
+        torch.cuda.synchronize()
+        with pytest.raises(NativeError, match="timed out"):
+            engines[0].check_status()
+        engines[0].check_status()                   # reading the status clears it
+        plans[1].send(bufs[1]); plans[1].recv(outs[1])      # the late rank catches up with epoch 1
+        for r in range(2):
+            plans[r].send(bufs[r])
+        for r in range(2):
+            plans[r].recv(outs[r])
+        torch.cuda.synchronize()
+        for e in engines:
+            e.check_status()
+        assert torch.equal(outs[0], outs[1])
+        vote = torch.where(torch.sign(bufs[0]) + torch.sign(bufs[1]) + (bufs[0] == 0).float() + (bufs[1] == 0).float() >= 0, 1.0, -1.0)
+        for off, n in zip(plans[0].offsets, plans[0].numels):
+            assert torch.equal(outs[0][off:off + n], vote[off:off + n])
+    finally:
+        for e in engines:
+            e.destroy()
+
+
+def test_variable_size_payload_overflow_is_reported():
+    from grace_b200.ops.native import NativeError
+    from grace_b200.parallel.engine import Engine
+    (e,) = Engine.local(1)
+    try:
+        prm = _params("threshold", threshold=0.001)
+        prm.capacity = 0.01                          # slots hold 1 % of the bucket, ~100 % of it is selected
+        p = e.plan(SIZES, NAMES, prm)
+        buf = torch.randn(p.padded, device="cuda")
+        out = torch.empty(p.padded, device="cuda")
+        p.send(buf); p.recv(out)
+        torch.cuda.synchronize()
+        with pytest.raises(NativeError, match="capacity"):
+            e.check_status()
+    finally:
+        e.destroy()
