@@ -194,14 +194,30 @@ __global__ void __launch_bounds__(GB_THREADS) k0_nvls_reduce(float* mc, int64_t 
   const uint32_t epoch = ctl->epoch;
   wait_all_ranks(peers, chan_a, epoch, status, timeout_ns);
   const int64_t n4 = len / 4;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
-    float* p = mc + start + i * 4;
-    float4 v;
-    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
-    v.x *= inv_world; v.y *= inv_world; v.z *= inv_world; v.w *= inv_world;
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-                 : "memory");
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  // four switch reductions in flight per thread: a multimem.ld_reduce round trip through NVSwitch is several
+  // microseconds, one outstanding request per thread leaves the links idle
+  for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i0 < n4; i0 += 4 * stride) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i < n4) {
+        float* p = mc + start + i * 4;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(p) : "memory");
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i < n4) {
+        float* p = mc + start + i * 4;
+        const float4 w = make_float4(v[u].x * inv_world, v[u].y * inv_world, v[u].z * inv_world, v[u].w * inv_world);
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(w.x), "f"(w.y), "f"(w.z), "f"(w.w)
+                     : "memory");
+      }
+    }
   }
   // publish "my shard is stored", then wait until every rank's shard is
   __threadfence_system();
