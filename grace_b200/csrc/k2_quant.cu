@@ -321,6 +321,11 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
   constexpr int LANES = SUB >= 32 ? 1 : 32 / SUB;       // lanes sharing one word
   constexpr int WORDS = SUB >= 32 ? SUB / 32 : 1;       // words per thread
   __shared__ float s_tab[128];
+  // Sub-word codes (1/2/4/8 bit): the tile's packed words are staged in shared memory and go to every peer
+  // as 16-byte stores of one contiguous run (512 B .. 4 KB per tile and peer).  Storing each word straight
+  // from the lane that finished it produced 16-byte NVLink writes for the 1-bit codecs.
+  constexpr int STAGE_WORDS = WORDS == 1 ? GB_TILE * BITS / 32 : 4;
+  __shared__ __align__(16) uint32_t s_words[STAGE_WORDS];
   if (CODEC == GB_CODEC_U8BIT) {
     if (threadIdx.x < 128) s_tab[threadIdx.x] = g_u8_table[threadIdx.x];
     __syncthreads();
@@ -393,11 +398,21 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
         uint32_t word = sub << ((lane % LANES) * SUB);
 #pragma unroll
         for (int o = 1; o < LANES; o <<= 1) word |= __shfl_xor_sync(0xffffffffu, word, o);
-        if ((lane % LANES) == 0 && e0 < len) {
-          for (int r = 0; r < out.n; ++r)
-            reinterpret_cast<uint32_t*>(out.slot[r] + hdr_bytes)[flat * BITS / 32] = word;
-        }
+        if ((lane % LANES) == 0 && e0 < len) s_words[e0 * BITS / 32] = word;
       }
+    }
+    if (WORDS == 1) {
+      __syncthreads();
+      const int nwords = (len * BITS + 31) / 32;
+      const int n4 = nwords >> 2;
+      const int64_t w0 = base * BITS / 32;              // base is a multiple of 128 elements -> 16-byte aligned
+      for (int r = 0; r < out.n; ++r) {
+        uint32_t* dst = reinterpret_cast<uint32_t*>(out.slot[r] + hdr_bytes) + w0;
+        for (int i = threadIdx.x; i < n4; i += GB_THREADS)
+          st_stream_u4(dst + 4 * i, *reinterpret_cast<const uint4*>(s_words + 4 * i));
+        if (threadIdx.x < (nwords & 3)) dst[4 * n4 + threadIdx.x] = s_words[4 * n4 + threadIdx.x];
+      }
+      __syncthreads();
     }
   }
   release_flags_last_block(done, peers, channel, epoch);
@@ -471,6 +486,59 @@ __global__ void __launch_bounds__(GB_THREADS, 6) k2_decode(SegTable t, WireIn in
       }
       *reinterpret_cast<float4*>(outp + flat) = make_float4(o[0], o[1], o[2], o[3]);
     }
+  }
+}
+
+// ---------------------------------------------------------------- receive for SignSGD / Signum: majority vote
+// sum_r (2 b_r - 1) >= 0  <=>  popcount over ranks >= ceil(W / 2)  (tie -> +1, signsgd.py:25-30).  The W bitmaps
+// of a tile are added bit-sliced (a 4-bit carry-save counter per element position, ~7 bitwise ops per rank
+// for 32 elements) instead of decoding W x 32 floats; the vote word is then expanded to +-1 with coalesced
+// 16-byte stores.
+__global__ void __launch_bounds__(GB_THREADS) k2_vote(SegTable t, WireIn in, size_t hdr_bytes, float* outp, PeerPtrs peers, int channel,
+                                                      const StepCtl* ctl, size_t par_stride, uint32_t* status, uint64_t timeout_ns) {
+  __shared__ uint32_t s_vote[GB_TILE / 32];
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(in, par_stride);
+  wait_all_ranks(peers, channel, epoch, status, timeout_ns);
+  const uint32_t need = (uint32_t)(in.n + 1) / 2;
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    if (threadIdx.x < GB_TILE / 32 && threadIdx.x * 32 < len) {
+      uint32_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+#pragma unroll
+      for (int r = 0; r < GB_MAX_WORLD; ++r) {
+        if (r >= in.n) break;
+        const uint32_t w = reinterpret_cast<const uint32_t*>(in.slot[r] + hdr_bytes)[base / 32 + threadIdx.x];
+        const uint32_t k0 = c0 & w; c0 ^= w;
+        const uint32_t k1 = c1 & k0; c1 ^= k0;
+        const uint32_t k2 = c2 & k1; c2 ^= k1;
+        c3 ^= k2;
+      }
+      // count >= need, bit-sliced compare from the most significant plane down
+      const uint32_t cs[4] = {c0, c1, c2, c3};
+      uint32_t gt = 0u, eq = 0xFFFFFFFFu;
+#pragma unroll
+      for (int b = 3; b >= 0; --b) {
+        const uint32_t tb = (need >> b) & 1u ? 0xFFFFFFFFu : 0u;
+        gt |= eq & cs[b] & ~tb;
+        eq &= ~(cs[b] ^ tb);
+      }
+      s_vote[threadIdx.x] = gt | eq;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      const uint32_t w = s_vote[e0 >> 5] >> (e0 & 31);
+      float o[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) o[q] = (e0 + q < len) ? (((w >> q) & 1u) ? 1.f : -1.f) : 0.f;
+      *reinterpret_cast<float4*>(outp + base + e0) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+    __syncthreads();
   }
 }
 
@@ -562,7 +630,12 @@ int k2_recv(gb_plan* p, float* d_out, cudaStream_t st) {
   const PeerPtrs peers = gb_comm_peers(c);
   int mode = 0;
   float divisor = p->prm.average ? (float)c->world : 1.f;
-  if (p->prm.codec == GB_CODEC_SIGNSGD || p->prm.codec == GB_CODEC_SIGNUM) mode = 1;
+  if (p->prm.codec == GB_CODEC_SIGNSGD || p->prm.codec == GB_CODEC_SIGNUM) {
+    k2_vote<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, p->hdr_bytes, d_out, peers, p->channel, p->d_ctl, p->par_stride,
+                                                        c->status_dev, c->timeout_ns);
+    LAUNCHED(p);
+    return 0;
+  }
   if (p->prm.codec == GB_CODEC_EFSIGNSGD) { mode = 2; divisor = p->prm.lr; }
   DISPATCH(launch_decode, p, d_out, in, peers, mode, divisor, st);
 }

@@ -343,10 +343,10 @@ def test_missing_peer_sets_timeout_status_instead_of_hanging():
         torch.cuda.synchronize()
         for e in engines:
             e.check_status()
-        assert torch.equal(outs[0], outs[1])
         vote = torch.where(torch.sign(bufs[0]) + torch.sign(bufs[1]) + (bufs[0] == 0).float() + (bufs[1] == 0).float() >= 0, 1.0, -1.0)
         for off, n in zip(plans[0].offsets, plans[0].numels):
             assert torch.equal(outs[0][off:off + n], vote[off:off + n])
+            assert torch.equal(outs[0][off:off + n], outs[1][off:off + n])     # pad elements are never written
     finally:
         for e in engines:
             e.destroy()
