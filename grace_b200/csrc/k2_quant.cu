@@ -421,7 +421,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
 // ---------------------------------------------------------------- receive: unpack, decode, add
 // final: 0 -> sum / divisor;  1 -> majority vote (sum >= 0 -> +1 else -1);  2 -> sum / lr
 template <int CODEC, int BITS>
-__global__ void __launch_bounds__(GB_THREADS, 6) k2_decode(SegTable t, WireIn in, size_t hdr_bytes, float* outp, int quantum,
+__global__ void __launch_bounds__(GB_THREADS, 4) k2_decode(SegTable t, WireIn in, size_t hdr_bytes, float* outp, int quantum,
                                                         int final_mode, float divisor, PeerPtrs peers, int channel,
                                                         const StepCtl* ctl, size_t par_stride, uint32_t* status,
                                                         uint64_t timeout_ns) {
@@ -451,40 +451,68 @@ __global__ void __launch_bounds__(GB_THREADS, 6) k2_decode(SegTable t, WireIn in
       __syncthreads();
     }
     const float inv_div = divisor != 1.f ? __fdiv_rn(1.0f, divisor) : 1.f;
+    // Loads first, arithmetic second: every rank's words of JCH element groups are requested before any of them
+    // is decoded (rank indices beyond the world size re-read rank 0 and are ignored).  The earlier loop left the
+    // rank loop through a `break`, which serialised W x 4 four-byte loads per thread and tile and capped the
+    // kernel at ~1 TB/s at W = 8.
+    constexpr int NJ = GB_TILE / (GB_THREADS * 4);
+    constexpr int WPT = BITS == 32 ? 4 : (BITS == 16 ? 2 : 1);      // 32-bit words per thread, rank and group
+    constexpr int JCH = BITS == 32 ? 1 : (BITS == 16 ? 2 : 4);      // groups whose loads are in flight together
 #pragma unroll
-    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
-      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
-      if (e0 >= len) continue;
-      const int64_t flat = base + e0;
-      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int j0 = 0; j0 < NJ; j0 += JCH) {
+      uint32_t raw[JCH][GB_MAX_WORLD][WPT];
 #pragma unroll
-      for (int r = 0; r < GB_MAX_WORLD; ++r) {
-        if (r >= in.n) break;
-        const uint32_t* words = reinterpret_cast<const uint32_t*>(in.slot[r] + hdr_bytes);
-        uint32_t code[4];
-        if (BITS == 32) {
-          const uint4 w = *reinterpret_cast<const uint4*>(words + flat);
-          code[0] = w.x; code[1] = w.y; code[2] = w.z; code[3] = w.w;
-        } else if (BITS == 16) {
-          const uint2 w = *reinterpret_cast<const uint2*>(words + flat / 2);
-          code[0] = w.x & 0xFFFFu; code[1] = w.x >> 16; code[2] = w.y & 0xFFFFu; code[3] = w.y >> 16;
-        } else {
-          const uint32_t w = words[flat * BITS / 32];
-          const int sh = (int)((flat * BITS) & 31);
+      for (int jj = 0; jj < JCH; ++jj) {
+        const int e0 = ((j0 + jj) * GB_THREADS + threadIdx.x) * 4;
+        const int64_t flat = base + (e0 < len ? e0 : 0);
 #pragma unroll
-          for (int q = 0; q < 4; ++q) code[q] = (w >> (sh + q * BITS)) & (0xFFFFFFFFu >> (32 - BITS));
+        for (int r = 0; r < GB_MAX_WORLD; ++r) {
+          const uint32_t* words = reinterpret_cast<const uint32_t*>(in.slot[r < in.n ? r : 0] + hdr_bytes);
+          if (BITS == 32) {
+            const uint4 w = *reinterpret_cast<const uint4*>(words + flat);
+            raw[jj][r][0] = w.x; raw[jj][r][1 % WPT] = w.y; raw[jj][r][2 % WPT] = w.z; raw[jj][r][3 % WPT] = w.w;
+          } else if (BITS == 16) {
+            const uint2 w = *reinterpret_cast<const uint2*>(words + flat / 2);
+            raw[jj][r][0] = w.x; raw[jj][r][1 % WPT] = w.y;
+          } else {
+            raw[jj][r][0] = words[flat * BITS / 32];
+          }
         }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) acc[q] += decode1<CODEC, BITS>(code[q], sts[r], ccs[r], s_tab);
       }
-      float o[4];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        if (final_mode == 1) o[q] = acc[q] >= 0.f ? 1.f : -1.f;
-        else o[q] = divisor != 1.f ? __fmul_rn(acc[q], inv_div) : acc[q];
-        if (e0 + q >= len) o[q] = 0.f;
+      for (int jj = 0; jj < JCH; ++jj) {
+        const int e0 = ((j0 + jj) * GB_THREADS + threadIdx.x) * 4;
+        const int64_t flat = base + (e0 < len ? e0 : 0);
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int r = 0; r < GB_MAX_WORLD; ++r) {
+          uint32_t code[4];
+          if (BITS == 32) {
+            code[0] = raw[jj][r][0]; code[1] = raw[jj][r][1 % WPT]; code[2] = raw[jj][r][2 % WPT]; code[3] = raw[jj][r][3 % WPT];
+          } else if (BITS == 16) {
+            code[0] = raw[jj][r][0] & 0xFFFFu; code[1] = raw[jj][r][0] >> 16;
+            code[2] = raw[jj][r][1 % WPT] & 0xFFFFu; code[3] = raw[jj][r][1 % WPT] >> 16;
+          } else {
+            const int sh = (int)((flat * BITS) & 31);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) code[q] = (raw[jj][r][0] >> (sh + q * BITS)) & (0xFFFFFFFFu >> (32 - BITS));
+          }
+          if (r < in.n) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[q] += decode1<CODEC, BITS>(code[q], sts[r], ccs[r], s_tab);
+          }
+        }
+        if (e0 < len) {
+          float o[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (final_mode == 1) o[q] = acc[q] >= 0.f ? 1.f : -1.f;
+            else o[q] = divisor != 1.f ? __fmul_rn(acc[q], inv_div) : acc[q];
+            if (e0 + q >= len) o[q] = 0.f;
+          }
+          *reinterpret_cast<float4*>(outp + flat) = make_float4(o[0], o[1], o[2], o[3]);
+        }
       }
-      *reinterpret_cast<float4*>(outp + flat) = make_float4(o[0], o[1], o[2], o[3]);
     }
   }
 }
@@ -508,9 +536,9 @@ __global__ void __launch_bounds__(GB_THREADS) k2_vote(SegTable t, WireIn in, siz
     if (threadIdx.x < GB_TILE / 32 && threadIdx.x * 32 < len) {
       uint32_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;
 #pragma unroll
-      for (int r = 0; r < GB_MAX_WORLD; ++r) {
-        if (r >= in.n) break;
-        const uint32_t w = reinterpret_cast<const uint32_t*>(in.slot[r] + hdr_bytes)[base / 32 + threadIdx.x];
+      for (int r = 0; r < GB_MAX_WORLD; ++r) {      // no early exit: the W loads stay independent
+        uint32_t w = reinterpret_cast<const uint32_t*>(in.slot[r < in.n ? r : 0] + hdr_bytes)[base / 32 + threadIdx.x];
+        if (r >= in.n) w = 0u;
         const uint32_t k0 = c0 & w; c0 ^= w;
         const uint32_t k1 = c1 & k0; c1 ^= k0;
         const uint32_t k2 = c2 & k1; c2 ^= k1;
