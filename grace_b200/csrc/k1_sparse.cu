@@ -79,7 +79,7 @@ __device__ __forceinline__ void flush_hist(uint32_t* sh, uint32_t* dst, int nbin
 // ROUND 0: compensate (+ write) and histogram bits[30:20].  ROUND 1/2: histogram the next 10
 // bits of the elements whose leading bits equal the prefix chosen so far.
 template <int ROUND, bool WRITE>
-__global__ void __launch_bounds__(GB_THREADS, 8) k1_hist(SegTable t, const float* __restrict__ grad, float* work, float beta,
+__global__ void __launch_bounds__(GB_THREADS, 5) k1_hist(SegTable t, const float* __restrict__ grad, float* work, float beta,
                                                       float gamma, uint32_t* hist, const uint32_t* __restrict__ sel,
                                                       const StepCtl* ctl) {
   constexpr int NB = ROUND == 0 ? 2048 : 1024;
@@ -103,6 +103,46 @@ __global__ void __launch_bounds__(GB_THREADS, 8) k1_hist(SegTable t, const float
       __syncthreads();
       cur = seg;
       if (ROUND != 0) prefix = sel[cur * 4];
+    }
+    if (len == GB_TILE) {
+      // full tile (the common case): all 16-byte loads are issued before the first histogram update; the
+      // generic loop below has a bounds branch in front of every load, which keeps one load in flight per thread
+      float4 vv4[GB_TILE / (GB_THREADS * 4)];
+      if (ROUND == 0 && WRITE) {
+        float4 rr4[GB_TILE / (GB_THREADS * 4)];
+#pragma unroll
+        for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+          const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+          vv4[j] = *reinterpret_cast<const float4*>(grad + base + e0);
+          rr4[j] = *reinterpret_cast<const float4*>(work + base + e0);
+        }
+#pragma unroll
+        for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+          const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+          vv4[j].x = compensate1(beta, rr4[j].x, gamma, vv4[j].x);
+          vv4[j].y = compensate1(beta, rr4[j].y, gamma, vv4[j].y);
+          vv4[j].z = compensate1(beta, rr4[j].z, gamma, vv4[j].z);
+          vv4[j].w = compensate1(beta, rr4[j].w, gamma, vv4[j].w);
+          *reinterpret_cast<float4*>(work + base + e0) = vv4[j];
+        }
+      } else {
+        const float* src = ROUND == 0 ? grad : work;
+#pragma unroll
+        for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j)
+          vv4[j] = *reinterpret_cast<const float4*>(src + base + (j * GB_THREADS + threadIdx.x) * 4);
+      }
+#pragma unroll
+      for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+        const float vv[4] = {vv4[j].x, vv4[j].y, vv4[j].z, vv4[j].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t b = absbits(vv[q]);
+          if (ROUND == 0) atomicAdd(&sh[b >> 20], 1u);
+          else if (ROUND == 1) { if ((b >> 20) == prefix) atomicAdd(&sh[(b >> 10) & 1023u], 1u); }
+          else { if ((b >> 10) == prefix) atomicAdd(&sh[b & 1023u], 1u); }
+        }
+      }
+      continue;
     }
 #pragma unroll
     for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
@@ -402,12 +442,20 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* wo
     float vv[4][4];
     uint32_t picks = 0;
     int cnt = 0;
+    if (len == GB_TILE) {
 #pragma unroll
-    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
-      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (e0 < len) v = load4(work + base, e0, len);
-      vv[j][0] = v.x; vv[j][1] = v.y; vv[j][2] = v.z; vv[j][3] = v.w;
+      for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {       // four independent 16-byte loads per thread
+        const float4 v = *reinterpret_cast<const float4*>(work + base + (j * GB_THREADS + threadIdx.x) * 4);
+        vv[j][0] = v.x; vv[j][1] = v.y; vv[j][2] = v.z; vv[j][3] = v.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (e0 < len) v = load4(work + base, e0, len);
+        vv[j][0] = v.x; vv[j][1] = v.y; vv[j][2] = v.z; vv[j][3] = v.w;
+      }
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
