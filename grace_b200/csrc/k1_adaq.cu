@@ -543,18 +543,40 @@ __global__ void __launch_bounds__(GB_THREADS) aq_merge(SegTable t, AdaqIn in, fl
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
+    // headers and means of all ranks, then all ranks' first GB_THREADS indices, are loaded before the adds
+    int2 h[GB_MAX_WORLD];
+    float m0[GB_MAX_WORLD], m1[GB_MAX_WORLD];
+#pragma unroll
+    for (int r = 0; r < GB_MAX_WORLD; ++r) {
+      const int rr = r < in.n ? r : 0;
+      h[r] = in.hdr[rr][tile];
+      m0[r] = in.means[rr][seg * 2];
+      m1[r] = in.means[rr][seg * 2 + 1];
+    }
+    int32_t pw[GB_MAX_WORLD];
+    bool have[GB_MAX_WORLD];
+#pragma unroll
+    for (int r = 0; r < GB_MAX_WORLD; ++r) {
+      have[r] = r < in.n && threadIdx.x < h[r].y;
+      pw[r] = have[r] ? in.idx[r][h[r].x + threadIdx.x] : 0;
+    }
     for (int i = threadIdx.x; i < GB_TILE; i += GB_THREADS) acc[i] = 0.f;
     __syncthreads();
-    for (int r = 0; r < in.n; ++r) {
-      const int2 h = in.hdr[r][tile];
-      const float m0 = in.means[r][seg * 2], m1 = in.means[r][seg * 2 + 1];
-      const int32_t* ix = in.idx[r] + h.x;
-      for (int i = threadIdx.x; i < h.y; i += GB_THREADS) {
-        const int32_t w = ix[i];
-        const int li = (w & 0x7FFFFFFF) - local0;
-        if ((unsigned)li < (unsigned)GB_TILE) acc[li] += w < 0 ? m1 : m0;      // indices are unique per rank
+#pragma unroll
+    for (int r = 0; r < GB_MAX_WORLD; ++r) {
+      if (r < in.n) {
+        if (have[r]) {
+          const int l0 = (pw[r] & 0x7FFFFFFF) - local0;
+          if ((unsigned)l0 < (unsigned)GB_TILE) acc[l0] += pw[r] < 0 ? m1[r] : m0[r];   // indices are unique per rank
+        }
+        const int32_t* ix = in.idx[r] + h[r].x;
+        for (int i = threadIdx.x + GB_THREADS; i < h[r].y; i += GB_THREADS) {
+          const int32_t w = ix[i];
+          const int li = (w & 0x7FFFFFFF) - local0;
+          if ((unsigned)li < (unsigned)GB_TILE) acc[li] += w < 0 ? m1[r] : m0[r];
+        }
+        __syncthreads();
       }
-      __syncthreads();
     }
 #pragma unroll
     for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {

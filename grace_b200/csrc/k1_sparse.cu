@@ -549,17 +549,37 @@ __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, 
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
+    // all ranks' headers, then all ranks' first GB_THREADS entries, are requested before anything is added:
+    // two dependent memory latencies per tile instead of two per rank.  The adds keep rank order.
+    int2 h[GB_MAX_WORLD];
+#pragma unroll
+    for (int r = 0; r < GB_MAX_WORLD; ++r) h[r] = in.hdr[r < in.n ? r : 0][tile];
+    float pv[GB_MAX_WORLD];
+    int32_t pi[GB_MAX_WORLD];
+#pragma unroll
+    for (int r = 0; r < GB_MAX_WORLD; ++r) {
+      pv[r] = 0.f;
+      pi[r] = -1;
+      if (r < in.n && threadIdx.x < h[r].y) {
+        pi[r] = in.idx[r][h[r].x + threadIdx.x];
+        pv[r] = in.vals[r][h[r].x + threadIdx.x];
+      }
+    }
     for (int i = threadIdx.x; i < GB_TILE; i += GB_THREADS) acc[i] = 0.f;
     __syncthreads();
-    for (int r = 0; r < in.n; ++r) {
-      const int2 h = in.hdr[r][tile];
-      const float* v = in.vals[r] + h.x;
-      const int32_t* ix = in.idx[r] + h.x;
-      for (int i = threadIdx.x; i < h.y; i += GB_THREADS) {
-        const int li = ix[i] - local0;
-        if ((unsigned)li < (unsigned)GB_TILE) acc[li] += v[i];
+#pragma unroll
+    for (int r = 0; r < GB_MAX_WORLD; ++r) {
+      if (r < in.n) {
+        const int l0 = pi[r] - local0;
+        if (pi[r] >= 0 && (unsigned)l0 < (unsigned)GB_TILE) acc[l0] += pv[r];
+        const float* v = in.vals[r] + h[r].x;
+        const int32_t* ix = in.idx[r] + h[r].x;
+        for (int i = threadIdx.x + GB_THREADS; i < h[r].y; i += GB_THREADS) {
+          const int li = ix[i] - local0;
+          if ((unsigned)li < (unsigned)GB_TILE) acc[li] += v[i];
+        }
+        __syncthreads();
       }
-      __syncthreads();
     }
 #pragma unroll
     for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {

@@ -26,7 +26,10 @@ struct IncOut {
   int n;
 };
 
-size_t in_hdr_bytes(int ntiles) { return ((size_t)ntiles * 16 + 255) & ~size_t(255); }
+// per tile: int4 {first stream word, #32-bit, #16-bit, #8-bit} + the exclusive class offsets of its 32 warp chunks
+// (128 elements each, packed like class_word) -- the receiver needs no block-wide scan
+#define IN_HDR_STRIDE 272
+size_t in_hdr_bytes(int ntiles) { return ((size_t)ntiles * IN_HDR_STRIDE + 255) & ~size_t(255); }
 size_t in_tag_bytes(int64_t padded) { return ((size_t)padded / 4 + 255) & ~size_t(255); }
 
 namespace {
@@ -78,15 +81,12 @@ __device__ __forceinline__ uint64_t ordered_offsets(const uint64_t pc[4], uint64
     if (lane == 31) wtot[j][warp] = incl[j];
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    uint64_t running = 0;
-    for (int j = 0; j < 4; ++j)
-      for (int w = 0; w < GB_THREADS / 32; ++w) {
-        const uint64_t c = wtot[j][w];
-        wtot[j][w] = running;
-        running += c;
-      }
-    *total = running;
+  if (warp == 0) {                                     // the 4 x 8 warp totals are exactly one warp's worth of lanes
+    uint64_t* flat = &wtot[0][0];
+    const uint64_t c = flat[lane];
+    const uint64_t inc = warp_incl_scan64(c, lane);
+    flat[lane] = inc - c;
+    if (lane == 31) *total = inc;
   }
   __syncthreads();
 #pragma unroll
@@ -156,6 +156,11 @@ __global__ void __launch_bounds__(GB_THREADS) in_send_k(SegTable t, const float*
         for (int r = 0; r < out.n; ++r) out.tags[r][(base + e0) >> 2] = (uint8_t)tb;
     }
     const uint64_t total = ordered_offsets(pc, offs, wtot, &s_total);
+    if (threadIdx.x < 32) {                             // exclusive offsets of the tile's 32 warp chunks -> header
+      const uint64_t c = (&wtot[0][0])[threadIdx.x];
+      for (int r = 0; r < out.n; ++r)
+        reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(out.hdr[r]) + (size_t)tile * IN_HDR_STRIDE + 16)[threadIdx.x] = c;
+    }
     const int n32 = (int)(total & 0xFFFFu), n16 = (int)((total >> 16) & 0xFFFFu), n8 = (int)((total >> 32) & 0xFFFFu);
     uint16_t* st16 = reinterpret_cast<uint16_t*>(stage + n32);
     uint8_t* st8 = reinterpret_cast<uint8_t*>(stage + n32) + 2 * n16;
@@ -202,7 +207,7 @@ __global__ void __launch_bounds__(GB_THREADS) in_send_k(SegTable t, const float*
         h = make_int4(-1, 0, 0, 0);                     // receivers skip this tile; the host raises on the status word
       }
       s_begin = h.x;
-      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = h;
+      for (int r = 0; r < out.n; ++r) *reinterpret_cast<int4*>(reinterpret_cast<char*>(out.hdr[r]) + (size_t)tile * IN_HDR_STRIDE) = h;
     }
     __syncthreads();
     const int begin = s_begin;
@@ -226,9 +231,8 @@ struct IncIn {
 
 __global__ void __launch_bounds__(GB_THREADS) in_recv_k(SegTable t, IncIn in, float* outp, float divisor, PeerPtrs peers, int channel,
                                                         const StepCtl* ctl, size_t par_stride, uint32_t* status, uint64_t timeout_ns) {
-  __shared__ uint64_t wtot[4][GB_THREADS / 32];
-  __shared__ uint64_t s_total;
   const uint32_t epoch = ctl->epoch;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (epoch & 1) {
     for (int r = 0; r < in.n; ++r) {
       in.hdr[r] = (const int4*)((const char*)in.hdr[r] + par_stride);
@@ -246,37 +250,89 @@ __global__ void __launch_bounds__(GB_THREADS) in_recv_k(SegTable t, IncIn in, fl
     for (int j = 0; j < 4; ++j)
 #pragma unroll
       for (int q = 0; q < 4; ++q) acc[j][q] = 0.f;
-    for (int r = 0; r < in.n; ++r) {
-      const int4 h = in.hdr[r][tile];
-      if (h.x < 0) continue;                            // sender overflowed its slot (status already raised)
-      uint64_t pc[4], offs[4];
-      uint32_t tagw = 0;
+    // No block-wide synchronisation in this kernel: the sender's header carries the class offsets of every
+    // 128-element warp chunk, a warp scan of the tags gives the rest.  Headers and tag bytes of every rank are
+    // requested up front (independent loads); only the value fetches depend on them.
+    int4 hh[GB_MAX_WORLD];
+    uint32_t tg[GB_MAX_WORLD];
+#pragma unroll
+    for (int r = 0; r < GB_MAX_WORLD; ++r) {
+      const int rr = r < in.n ? r : 0;
+      hh[r] = *reinterpret_cast<const int4*>(reinterpret_cast<const char*>(in.hdr[rr]) + (size_t)tile * IN_HDR_STRIDE);
+      tg[r] = 0u;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
-        const uint32_t tb = e0 < len ? in.tags[r][(base + e0) >> 2] : 0u;
-        tagw |= tb << (8 * j);
-        pc[j] = 0;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) pc[j] += class_word((tb >> (2 * q)) & 3u);
+        const uint32_t tb = e0 < len ? in.tags[rr][(base + e0) >> 2] : 0u;
+        tg[r] |= tb << (8 * j);
       }
-      ordered_offsets(pc, offs, wtot, &s_total);
-      const uint32_t* sp = in.stream[r] + h.x;
-      const uint16_t* s16 = reinterpret_cast<const uint16_t*>(sp + h.y);
-      const uint8_t* s8 = reinterpret_cast<const uint8_t*>(sp + h.y) + 2 * h.z;
+    }
+#pragma unroll
+    for (int r = 0; r < GB_MAX_WORLD; ++r) {
+      if (r >= in.n) continue;
+      const int4 h = hh[r];
+      if (h.x < 0) continue;                            // sender overflowed its slot (status already raised)
+      int o32s[4], o16s[4], o8s[4];
+      const uint32_t tagw = tg[r];
+      const uint64_t* chunk = reinterpret_cast<const uint64_t*>(reinterpret_cast<const char*>(in.hdr[r]) + (size_t)tile * IN_HDR_STRIDE + 16);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        if (((tagw >> (8 * j)) & 0xFFu) == 0) continue;
-        int o32 = (int)(offs[j] & 0xFFFFu), o16 = (int)((offs[j] >> 16) & 0xFFFFu), o8 = (int)((offs[j] >> 32) & 0xFFFFu);
+        const uint32_t tb = (tagw >> (8 * j)) & 0xFFu;
+        // inside a 128-element chunk every class count fits 8 bits: one 32-bit warp scan for all three
+        uint32_t pc = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t cls = (tb >> (2 * q)) & 3u;
+          pc += cls == 3u ? 1u : (cls == 2u ? (1u << 8) : (cls == 1u ? (1u << 16) : 0u));
+        }
+        uint32_t inc = pc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t nb = __shfl_up_sync(0xffffffffu, inc, o);
+          if (lane >= o) inc += nb;
+        }
+        const uint32_t ex = inc - pc;
+        const uint64_t cb = chunk[j * (GB_THREADS / 32) + warp];
+        o32s[j] = (int)(cb & 0xFFFFu) + (int)(ex & 0xFFu);
+        o16s[j] = (int)((cb >> 16) & 0xFFFFu) + (int)((ex >> 8) & 0xFFu);
+        o8s[j] = (int)((cb >> 32) & 0xFFFFu) + (int)((ex >> 16) & 0xFFu);
+      }
+      // Branch-free fetch: every coded element reads the aligned 32-bit word that holds its 4/2/1-byte value
+      // (predicated, all 16 loads independent), the class only selects the extraction.  Loads inside the
+      // three-way class branch serialised up to 3 x 16 memory latencies per rank.
+      const uint32_t* sp = in.stream[r] + h.x;
+      const int b16 = 4 * h.y, b8 = 4 * h.y + 2 * h.z;           // byte offsets of the 16-bit and 8-bit runs
+      uint32_t wv[4][4];
+      uint32_t shf[4];                                             // 4 x 4 shift amounts (bits), 8 bits each
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        int o32 = o32s[j], o16 = o16s[j], o8 = o8s[j];
+        shf[j] = 0u;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int cls = (tagw >> (8 * j + 2 * q)) & 3u;
-          if (cls == 3) acc[j][q] += __uint_as_float(sp[o32++]);
-          else if (cls == 2) acc[j][q] += dec16(s16[o16++]);
-          else if (cls == 1) acc[j][q] += dec8(s8[o8++]);
+          const bool c3 = cls == 3, c2 = cls == 2, c1 = cls == 1;
+          const int bo = c3 ? 4 * o32 : (c2 ? b16 + 2 * o16 : b8 + o8);
+          o32 += c3; o16 += c2; o8 += c1;
+          wv[j][q] = cls ? sp[bo >> 2] : 0u;
+          shf[j] |= (uint32_t)((bo & 3) * 8) << (8 * q);
         }
       }
-      __syncthreads();                                  // wtot / s_total are reused by the next rank
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int cls = (tagw >> (8 * j + 2 * q)) & 3u;
+          const uint32_t w = wv[j][q] >> ((shf[j] >> (8 * q)) & 0xFFu);
+          // 16- and 8-bit forms share one path: sign + magnitude / 2^14 (or 2^6); exact in fp32
+          const bool wide = cls == 2;
+          const uint32_t mag = w & (wide ? 0x7FFFu : 0x7Fu);
+          const uint32_t sgn = (w >> (wide ? 15 : 7)) & 1u;
+          const float m = __fmul_rn((float)mag, wide ? (1.0f / 16384.0f) : (1.0f / 64.0f));
+          const float x = cls == 3 ? __uint_as_float(wv[j][q]) : __uint_as_float(__float_as_uint(m) | (sgn << 31));
+          if (cls) acc[j][q] += x;
+        }
+      }
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {

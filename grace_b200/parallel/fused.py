@@ -76,7 +76,7 @@ def estimate_arena_bytes(numels, params, powersgd, world):
         if code in (CODEC["threshold"], CODEC["dgc"], CODEC["adaq"]):
             slot = int(8 * n * (params.capacity or 1.0))
         elif code == CODEC["inceptionn"]:
-            slot = int(4 * n * (params.capacity or 1.0)) + n // 4
+            slot = int(4 * n * (params.capacity or 1.0)) + n // 4 + 272 * (n // 4096 + len(numels))   # tags + per-tile headers
         elif code in (CODEC["topk"], CODEC["randomk"]):
             slot = int(8 * (n * params.ratio + len(numels)))
         elif code in (CODEC["none"], CODEC["fp16"]):
