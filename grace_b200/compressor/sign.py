@@ -54,6 +54,10 @@ class SignumCompressor(Compressor):
         flat = tensor.flatten()
         if name in self.momentums:
             flat = (1.0 - self.momentum) * flat + self.momentum * self.momentums[name]
+        else:
+            # the reference keeps this view (signum.py:19-23): its own training loop then overwrites the gradient
+            # with the decompressed signs and zeroes it, which silently replaces the first momentum by +-1 / 0
+            flat = flat.clone()
         self.momentums[name] = flat
         return [(flat >= 0).to(torch.uint8)], tensor.size()
 

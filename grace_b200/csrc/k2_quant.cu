@@ -45,6 +45,7 @@ struct QuantArgs {
   int has_mem;        // residual buffer present
   float beta, gamma;  // compensate
   float mom;          // signum momentum (0 on the first call)
+  float om;           // (float)(1 - momentum), rounded from double like python's scalar
   int quantum;        // qsgd levels
   uint32_t seed, step;
 };
@@ -353,7 +354,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
         if (CODEC == GB_CODEC_SIGNUM) {
           const float4 m = *reinterpret_cast<const float4*>(mom + base + e0);
           const float mm[4] = {m.x, m.y, m.z, m.w};
-          const float om = 1.0f - a.mom;
+          const float om = a.om;
 #pragma unroll
           for (int q = 0; q < 4; ++q) src[q] = a.mom == 0.f ? x[q] : __fadd_rn(__fmul_rn(om, x[q]), __fmul_rn(a.mom, mm[q]));
           float4 w = make_float4(src[0], src[1], src[2], src[3]);
@@ -626,6 +627,7 @@ int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   a.beta = p->prm.beta;                 // steady-state values; kernels apply the first-call rules
   a.gamma = p->prm.gamma;
   a.mom = p->prm.momentum;
+  a.om = p->prm.one_minus_momentum != 0.f ? p->prm.one_minus_momentum : 1.0f - p->prm.momentum;
   a.quantum = p->prm.quantum_num;
   a.seed = p->prm.seed;
   a.step = 0;

@@ -27,7 +27,8 @@ class CodecParams(C.Structure):
     """Mirror of ``gb_codec_params``."""
     _fields_ = [("ratio", C.c_double), ("codec", C.c_int32), ("memory", C.c_int32), ("beta", C.c_float),
                 ("gamma", C.c_float), ("threshold", C.c_float), ("quantum_num", C.c_int32), ("momentum", C.c_float),
-                ("lr", C.c_float), ("seed", C.c_uint32), ("average", C.c_int32), ("capacity", C.c_float)]
+                ("lr", C.c_float), ("seed", C.c_uint32), ("average", C.c_int32), ("capacity", C.c_float),
+                ("one_minus_momentum", C.c_float)]
 
 
 _lib = None

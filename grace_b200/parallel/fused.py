@@ -130,6 +130,7 @@ def codec_params(compressor, memory):
         p.codec = CODEC["signsgd"]
     elif t is C.SignumCompressor:
         p.codec, p.momentum = CODEC["signum"], compressor.momentum
+        p.one_minus_momentum = 1.0 - compressor.momentum        # rounded to fp32 from the double, as torch does for a python scalar
     elif t is C.EFSignSGDCompressor:
         p.codec, p.lr = CODEC["efsignsgd"], compressor.learning_rate
     elif t is C.OneBitCompressor:

@@ -64,6 +64,7 @@ typedef struct gb_codec_params {
   uint32_t seed;           /* Philox key word 0 (shared by all ranks)                  */
   int32_t average;         /* divide the aggregate by world size                       */
   float capacity;          /* variable-size codecs: slot capacity as a fraction of numel (0 -> 1.0) */
+  float one_minus_momentum;/* signum: (float)(1.0 - momentum) evaluated in double like python; 0 -> 1.0f - momentum */
 } gb_codec_params;
 
 const char* gb_last_error(void);

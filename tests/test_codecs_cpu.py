@@ -228,3 +228,14 @@ def test_state_dict_roundtrip(make):
     pa, ca = a.compress(X, "w")
     pb, cb = b.compress(X, "w")
     assert torch.allclose(a.decompress(pa, ca), b.decompress(pb, cb))
+
+
+def test_signum_momentum_does_not_alias_the_callers_gradient():
+    """The manual loop of the reference (core.py:202-208) overwrites the gradient in place after step();
+    the first momentum must survive that."""
+    c = C.SignumCompressor(0.9)
+    g = torch.tensor([0.5, -0.25, 0.125])
+    payload, ctx = c.compress(g, "w")
+    g.copy_(c.decompress(payload, ctx))              # what `grad.copy_(grc.step(grad, name))` does
+    g.zero_()                                        # optimizer.zero_grad(set_to_none=False)
+    assert torch.equal(c.momentums["w"], torch.tensor([0.5, -0.25, 0.125]))

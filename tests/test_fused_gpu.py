@@ -44,6 +44,15 @@ def _manual_reference(params, data):
     (dict(compressor="none", memory="none", communicator="allreduce"), 0.0),
     (dict(compressor="powersgd", memory="powersgd", communicator="allreduce", compress_rank=4), 3e-2),
     (dict(compressor="sketch", memory="none", communicator="allgather", quantiles=64), 2e-3),
+    (dict(compressor="adaq", memory="residual", communicator="allgather", compress_ratio=0.05), 1e-3),
+    (dict(compressor="inceptionn", memory="residual", communicator="allgather"), 0.0),
+    (dict(compressor="threshold", memory="residual", communicator="allgather", threshold=0.001), 0.0),
+    (dict(compressor="randomk", memory="residual", communicator="allreduce", compress_ratio=0.05), 0.0),
+    (dict(compressor="terngrad", memory="residual", communicator="allgather"), 2e-3),
+    (dict(compressor="onebit", memory="residual", communicator="allgather"), 1e-4),
+    (dict(compressor="signum", memory="residual", communicator="allgather", momentum=0.9), 1e-5),
+    (dict(compressor="u8bit", memory="none", communicator="allgather"), 2e-3),
+    (dict(compressor="fp16", memory="none", communicator="allgather"), 1e-5),
 ])
 def test_distributed_optimizer_fused_matches_manual_loop(params, tol):
     import grace_b200.torch as hvd
