@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) k2_stats(SegTable t, const floa
 //   QSGD {norm}  TERNGRAD {scalar}  EFSIGNSGD {mean|x|}  ONEBIT {mean_neg, mean_pos}  U8BIT {max|x|}
 __global__ void k2_finalize(SegTable t, const float* __restrict__ tilestats, int codec, float* segstats, WireOut out,
                             const StepCtl* ctl, size_t par_stride) {
-  if (ctl->epoch & 1) shift(out, par_stride);
+  const size_t poff = (ctl->epoch & 1) ? par_stride : 0;      // parity slot; the parameter struct stays in the constant bank
   const int seg = blockIdx.x;
   const int lane = threadIdx.x;
   const int first = t.seg_tile0[seg], last = t.seg_tile0[seg + 1];
@@ -215,7 +215,7 @@ __global__ void k2_finalize(SegTable t, const float* __restrict__ tilestats, int
     }
     const float4 v = make_float4(o[0], o[1], o[2], o[3]);
     reinterpret_cast<float4*>(segstats)[seg] = v;
-    for (int r = 0; r < out.n; ++r) reinterpret_cast<float4*>(out.slot[r])[seg] = v;
+    for (int r = 0; r < out.n; ++r) reinterpret_cast<float4*>(out.slot[r] + poff)[seg] = v;
   }
 }
 
@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
                                                         const StepCtl* ctl, size_t par_stride) {
   const QuantArgs a = resolve(a_in, ctl);
   const uint32_t epoch = ctl->epoch;
-  if (epoch & 1) shift(out, par_stride);
+  const size_t poff = (epoch & 1) ? par_stride : 0;           // parity slot; the parameter struct stays in the constant bank
   constexpr int SUB = 4 * BITS;                         // bits produced per thread
   constexpr int LANES = SUB >= 32 ? 1 : 32 / SUB;       // lanes sharing one word
   constexpr int WORDS = SUB >= 32 ? SUB / 32 : 1;       // words per thread
@@ -386,7 +386,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
         else { w[0] = code[0] | (code[1] << 16); w[1 % WORDS] = code[2] | (code[3] << 16); }
         if (e0 < len) {
           for (int r = 0; r < out.n; ++r) {
-            uint32_t* dst = reinterpret_cast<uint32_t*>(out.slot[r] + hdr_bytes) + flat * BITS / 32;
+            uint32_t* dst = reinterpret_cast<uint32_t*>(out.slot[r] + poff + hdr_bytes) + flat * BITS / 32;
             if (WORDS == 4) st_stream_u4(dst, make_uint4(w[0], w[1 % WORDS], w[2 % WORDS], w[3 % WORDS]));
             else *reinterpret_cast<uint2*>(dst) = make_uint2(w[0], w[1 % WORDS]);
           }
@@ -408,7 +408,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
       const int n4 = nwords >> 2;
       const int64_t w0 = base * BITS / 32;              // base is a multiple of 128 elements -> 16-byte aligned
       for (int r = 0; r < out.n; ++r) {
-        uint32_t* dst = reinterpret_cast<uint32_t*>(out.slot[r] + hdr_bytes) + w0;
+        uint32_t* dst = reinterpret_cast<uint32_t*>(out.slot[r] + poff + hdr_bytes) + w0;
         for (int i = threadIdx.x; i < n4; i += GB_THREADS)
           st_stream_u4(dst + 4 * i, *reinterpret_cast<const uint4*>(s_words + 4 * i));
         if (threadIdx.x < (nwords & 3)) dst[4 * n4 + threadIdx.x] = s_words[4 * n4 + threadIdx.x];
@@ -427,7 +427,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) k2_decode(SegTable t, WireIn in
                                                         const StepCtl* ctl, size_t par_stride, uint32_t* status,
                                                         uint64_t timeout_ns) {
   const uint32_t epoch = ctl->epoch;
-  if (epoch & 1) shift(in, par_stride);
+  const size_t poff = (epoch & 1) ? par_stride : 0;           // parity slot; the parameter struct stays in the constant bank
   __shared__ float s_tab[128];
   __shared__ float4 sts[GB_MAX_WORLD];
   __shared__ CodecConst ccs[GB_MAX_WORLD];
@@ -445,7 +445,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) k2_decode(SegTable t, WireIn in
     if (HAS_STATS) {
       __syncthreads();
       if (threadIdx.x < in.n) {
-        const float4 s4 = reinterpret_cast<const float4*>(in.slot[threadIdx.x])[seg];
+        const float4 s4 = reinterpret_cast<const float4*>(in.slot[threadIdx.x] + poff)[seg];
         sts[threadIdx.x] = s4;
         ccs[threadIdx.x] = codec_const<CODEC>(s4, quantum);
       }
@@ -468,7 +468,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) k2_decode(SegTable t, WireIn in
         const int64_t flat = base + (e0 < len ? e0 : 0);
 #pragma unroll
         for (int r = 0; r < GB_MAX_WORLD; ++r) {
-          const uint32_t* words = reinterpret_cast<const uint32_t*>(in.slot[r < in.n ? r : 0] + hdr_bytes);
+          const uint32_t* words = reinterpret_cast<const uint32_t*>(in.slot[r < in.n ? r : 0] + poff + hdr_bytes);
           if (BITS == 32) {
             const uint4 w = *reinterpret_cast<const uint4*>(words + flat);
             raw[jj][r][0] = w.x; raw[jj][r][1 % WPT] = w.y; raw[jj][r][2 % WPT] = w.z; raw[jj][r][3 % WPT] = w.w;
@@ -527,7 +527,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_vote(SegTable t, WireIn in, siz
                                                       const StepCtl* ctl, size_t par_stride, uint32_t* status, uint64_t timeout_ns) {
   __shared__ uint32_t s_vote[GB_TILE / 32];
   const uint32_t epoch = ctl->epoch;
-  if (epoch & 1) shift(in, par_stride);
+  const size_t poff = (epoch & 1) ? par_stride : 0;           // parity slot; the parameter struct stays in the constant bank
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   const uint32_t need = (uint32_t)(in.n + 1) / 2;
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
@@ -538,7 +538,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_vote(SegTable t, WireIn in, siz
       uint32_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;
 #pragma unroll
       for (int r = 0; r < GB_MAX_WORLD; ++r) {      // no early exit: the W loads stay independent
-        uint32_t w = reinterpret_cast<const uint32_t*>(in.slot[r < in.n ? r : 0] + hdr_bytes)[base / 32 + threadIdx.x];
+        uint32_t w = reinterpret_cast<const uint32_t*>(in.slot[r < in.n ? r : 0] + poff + hdr_bytes)[base / 32 + threadIdx.x];
         if (r >= in.n) w = 0u;
         const uint32_t k0 = c0 & w; c0 ^= w;
         const uint32_t k1 = c1 & k0; c1 ^= k0;
