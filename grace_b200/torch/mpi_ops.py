@@ -122,7 +122,23 @@ def allreduce_(tensor, average=True, name=None):
     return synchronize(allreduce_async_(tensor, average, name))
 
 
+class _AllreduceFn(torch.autograd.Function):
+    """Differentiable all-reduce (reference: ``HorovodAllreduce``, patch_files/horovod/torch/mpi_ops.py:116-127):
+    the gradient of a sum / mean over ranks is the same reduction of the upstream gradients."""
+
+    @staticmethod
+    def forward(ctx, tensor, average, name):
+        ctx.average = average
+        return synchronize(allreduce_async(tensor.detach(), average, name))
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        return synchronize(allreduce_async(grad_output.contiguous(), ctx.average, None)), None, None
+
+
 def allreduce(tensor, average=True, name=None):
+    if tensor.requires_grad and torch.is_grad_enabled():
+        return _AllreduceFn.apply(tensor, average, name)
     return synchronize(allreduce_async(tensor, average, name))
 
 
@@ -148,7 +164,28 @@ def allgather_async(tensor, name=None):
                                                dim=0), (wire, slots))
 
 
+class _AllgatherFn(torch.autograd.Function):
+    """Differentiable all-gather (reference: ``HorovodAllgather``, mpi_ops.py:237-255): the upstream gradient is
+    summed over ranks and every rank keeps the rows it contributed."""
+
+    @staticmethod
+    def forward(ctx, tensor, name):
+        ctx.rows = tensor.shape[0] if tensor.dim() else 1
+        ctx.scalar = tensor.dim() == 0
+        rows = synchronize(allgather_async(torch.tensor([ctx.rows], dtype=torch.int64, device=tensor.device), None))
+        ctx.offset = int(rows[:rank()].sum())
+        return synchronize(allgather_async(tensor.detach(), name))
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        total = synchronize(allreduce_async(grad_output.contiguous(), False, None))
+        mine = total.narrow(0, ctx.offset, ctx.rows)
+        return (mine.reshape(()) if ctx.scalar else mine), None
+
+
 def allgather(tensor, name=None):
+    if tensor.requires_grad and torch.is_grad_enabled():
+        return _AllgatherFn.apply(tensor, name)
     return synchronize(allgather_async(tensor, name))
 
 
@@ -174,5 +211,24 @@ def broadcast_(tensor, root_rank, name=None):
     return synchronize(broadcast_async_(tensor, root_rank, name))
 
 
+class _BroadcastFn(torch.autograd.Function):
+    """Differentiable broadcast (reference: ``HorovodBroadcast``, mpi_ops.py:319-333): the root receives the sum of
+    all ranks' upstream gradients, every other rank a zero gradient."""
+
+    @staticmethod
+    def forward(ctx, tensor, root_rank, name):
+        ctx.root = root_rank
+        return synchronize(broadcast_async(tensor.detach(), root_rank, name))
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        total = synchronize(allreduce_async(grad_output.contiguous(), False, None))
+        if rank() != ctx.root:
+            total = torch.zeros_like(total)
+        return total, None, None
+
+
 def broadcast(tensor, root_rank, name=None):
+    if tensor.requires_grad and torch.is_grad_enabled():
+        return _BroadcastFn.apply(tensor, root_rank, name)
     return synchronize(broadcast_async(tensor, root_rank, name))

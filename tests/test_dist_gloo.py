@@ -187,3 +187,39 @@ def test_config1_small_cnn_topk_residual_allgather(flavour):
     (p0, l0), (p1, l1) = _spawn(_train_small_cnn, 2, flavour)
     assert torch.equal(p0, p1)                              # replicas stay bit-identical
     assert sum(l0[-4:]) < sum(l0[:4])                       # and the loss goes down
+
+
+def _autograd_collectives(rank, world):
+    import grace_b200.torch as hvd
+    hvd.init()
+    out = {}
+    # allreduce (mean): d/dx sum(w * mean_r x_r) = mean_r w_r
+    x = torch.full((3,), float(rank + 1), requires_grad=True)
+    w = torch.arange(3.0) + 10 * rank
+    (hvd.allreduce(x, average=True) * w).sum().backward()
+    out["allreduce"] = x.grad.clone()
+    # allgather with different first dimensions: every rank gets back the rows it contributed, summed over ranks
+    y = torch.full((rank + 1, 2), float(rank), requires_grad=True)
+    g = hvd.allgather(y)
+    coef = torch.arange(float(g.numel())).view_as(g) * (rank + 1)
+    (g * coef).sum().backward()
+    out["allgather_shape"] = tuple(g.shape)
+    out["allgather"] = y.grad.clone()
+    # broadcast from rank 1: only the root gets a gradient (the sum over ranks)
+    z = torch.full((2,), float(rank), requires_grad=True)
+    (hvd.broadcast(z, root_rank=1) * (rank + 1)).sum().backward()
+    out["broadcast"] = z.grad.clone()
+    # plain tensors keep the non-differentiable path
+    out["plain"] = hvd.allreduce(torch.ones(2) * rank, average=False)
+    return out
+
+
+def test_blocking_collectives_are_differentiable():
+    """Reference: the autograd Functions of patch_files/horovod/torch/mpi_ops.py:116-127,237-255,319-333."""
+    r0, r1 = _spawn(_autograd_collectives, 2)
+    assert torch.equal(r0["allreduce"], torch.tensor([5.0, 6.0, 7.0])) and torch.equal(r1["allreduce"], r0["allreduce"])
+    assert r0["allgather_shape"] == (3, 2)
+    coef_sum = torch.arange(6.0).view(3, 2) * 3            # (1 + 2) x position index
+    assert torch.equal(r0["allgather"], coef_sum[:1]) and torch.equal(r1["allgather"], coef_sum[1:])
+    assert torch.equal(r0["broadcast"], torch.zeros(2)) and torch.equal(r1["broadcast"], torch.full((2,), 3.0))
+    assert torch.equal(r0["plain"], torch.ones(2))
