@@ -51,6 +51,9 @@ def main():
     ap.add_argument("--codecs", default="")
     ap.add_argument("--ratio", type=float, default=0.01)
     ap.add_argument("--out", default="")
+    ap.add_argument("--flush", default="write", choices=["write", "write+read"],
+                    help="L2 flush between iterations: write 256 MB (leaves the L2 full of DIRTY lines whose write-back "
+                         "overlaps the timed kernels) or write 256 MB and then read another 256 MB (cold, clean L2)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -66,7 +69,15 @@ def main():
     hbm, how = peaks()
     nvlink = 770.0
     eng = Engine.create(arena_bytes=int(os.environ.get("GRACE_B200_ARENA_MB", "4096")) << 20)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")        # > 126 MB L2
+    flush_w = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
+    flush_r = torch.ones(64 << 20, dtype=torch.float32, device="cuda") if args.flush == "write+read" else None
+
+    class _Flush:
+        def zero_(self):
+            flush_w.zero_()
+            if flush_r is not None:
+                flush_r.sum()              # evicts the dirty lines of the write before the timed region starts
+    flush = _Flush()
     rows = []
     want = [c for c in args.codecs.split(",") if c]
     for comp, mem in CODECS:
