@@ -51,6 +51,7 @@ def main():
     ap.add_argument("--codecs", default="")
     ap.add_argument("--ratio", type=float, default=0.01)
     ap.add_argument("--out", default="")
+    ap.add_argument("--graph", action="store_true", help="time the exchange as a CUDA-graph replay (how it runs inside GraphedStep)")
     ap.add_argument("--flush", default="write", choices=["write", "write+read"],
                     help="L2 flush between iterations: write 256 MB (leaves the L2 full of DIRTY lines whose write-back "
                          "overlaps the timed kernels) or write 256 MB and then read another 256 MB (cold, clean L2)")
@@ -99,6 +100,19 @@ def main():
         grad = torch.randn(plan.padded, device="cuda")
         out = torch.empty(plan.padded, device="cuda")
         times = []
+        graph = None
+        if args.graph:
+            # epochs and codec steps live in device memory, so one captured exchange can be replayed
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                plan.send(grad, stream=side); plan.recv(out, stream=side)          # warm-up outside the capture
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                plan.send(grad, stream=torch.cuda.current_stream())
+                plan.recv(out, stream=torch.cuda.current_stream())
         for it in range(args.warmup + args.iters):
             if mem != "none":
                 grad.normal_()             # fresh gradient every exchange so residuals do not pile up on one sample
@@ -108,8 +122,11 @@ def main():
             torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            plan.send(grad)
-            plan.recv(out)
+            if graph is not None:
+                graph.replay()
+            else:
+                plan.send(grad)
+                plan.recv(out)
             b.record()
             torch.cuda.synchronize()
             if it >= args.warmup:
