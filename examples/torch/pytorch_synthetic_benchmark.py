@@ -30,6 +30,9 @@ ap.add_argument("--memory", default="residual")
 ap.add_argument("--communicator", default="allgather")
 ap.add_argument("--compress-ratio", type=float, default=0.01)
 ap.add_argument("--bf16", action="store_true")
+ap.add_argument("--graph", action="store_true",
+                help="replay the whole step (forward, backward, fused exchange, optimizer) as ONE CUDA graph and feed it "
+                     "from pinned host memory with hvd.GraphedStep.feed/run")
 ap.add_argument("--no-cuda", action="store_true")
 args = ap.parse_args()
 cuda = not args.no_cuda and torch.cuda.is_available()
@@ -62,6 +65,23 @@ def benchmark_step():
     stats.step()
     if cuda:
         torch.cuda.synchronize()
+
+
+graphed = None
+if args.graph and cuda:
+    graphed = hvd.GraphedStep(model, optimizer, lambda m, x, y: F.cross_entropy(m(x), y), [data, target],
+                              amp_dtype=torch.bfloat16 if args.bf16 else None)
+    stats.graph_launches_per_step = graphed.native_launches_per_step
+    host_data, host_target = data.cpu().contiguous().pin_memory(), target.cpu().pin_memory()   # "data loader" output
+    graphed.feed(host_data, host_target)
+    pending = []
+
+    def benchmark_step():                       # noqa: F811
+        pending.append(graphed.run())           # consumes the fed batch, replays, starts the loss read-back
+        graphed.feed(host_data, host_target)    # next batch: copied on the copy stream while the replay runs
+        if len(pending) > 1:
+            pending.pop(0).item()               # loss of the previous step, already on the host
+        stats.step()
 
 
 def log(s):

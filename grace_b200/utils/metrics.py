@@ -76,6 +76,7 @@ class CompressionStats:
         self.fused = getattr(optimizer, "_fused", None)
         self.steps = 0
         self._launch0 = self.fused.launches() if self.fused else 0
+        self.graph_launches_per_step = None     # set to GraphedStep.native_launches_per_step: replays bypass the host counter
 
     def step(self):
         self.steps += 1
@@ -89,7 +90,8 @@ class CompressionStats:
         out = {"fused": True, "buckets": len(self.fused.buckets), "world": world, "dense_gradient_bytes": dense,
                "wire_bytes_per_peer_per_step": wire, "compression_ratio": dense / max(wire, 1),
                "egress_bytes_per_step": wire * max(world - 1, 0),
-               "launches_per_step": (self.fused.launches() - self._launch0) / max(self.steps, 1)}
+               "launches_per_step": self.graph_launches_per_step if self.graph_launches_per_step is not None
+               else (self.fused.launches() - self._launch0) / max(self.steps, 1)}
         if step_ms:
             out["egress_GBps"] = out["egress_bytes_per_step"] / step_ms / 1e6
         return out
