@@ -46,7 +46,9 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   GB_CHECK(nseg >= 1, "a plan needs at least one segment");
   GB_CHECK(params->codec >= GB_CODEC_NONE && params->codec <= GB_CODEC_INCEPTIONN, "unknown codec %d", params->codec);
   GB_CHECK(params->memory != GB_MEM_DGC || params->codec == GB_CODEC_DGC, "DGC memory needs the DGC codec");
-  gb_plan* p = new gb_plan();
+  gb_plan* p = new gb_plan();            // value-initialised: every pointer member starts as nullptr
+  // any failure below leaves through this lambda; the partially built plan is then released in one place
+  auto build = [&]() -> int {
   p->comm = c;
   p->prm = *params;
   p->nseg = nseg;
@@ -181,17 +183,23 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->dense2 = (params->codec == GB_CODEC_NONE || params->codec == GB_CODEC_FP16) && params->memory == GB_MEM_NONE &&
               c->world > 1 && !getenv("GRACE_B200_NO_K0");   // with a residual memory the K2 path keeps the state
   if (p->dense2) p->slot_bytes = k0_slot_bytes(p->padded, c->world, p->bits);
-  if (gb_comm_alloc_channel(c, p->slot_bytes, &p->channel, &p->chan_off)) { gb_plan_destroy(p); return -1; }
+  if (gb_comm_alloc_channel(c, p->slot_bytes, &p->channel, &p->chan_off)) return -1;
   if (p->dense2) {
     // second flag channel for the gather phase (no payload of its own)
     size_t unused;
-    if (gb_comm_alloc_channel(c, 0, &p->channel2, &unused)) { gb_plan_destroy(p); return -1; }
+    if (gb_comm_alloc_channel(c, 0, &p->channel2, &unused)) return -1;
   }
   p->slot_bytes = (p->slot_bytes + 255) & ~size_t(255);
   p->par_stride = (size_t)c->world * p->slot_bytes;
-  if (params->codec == GB_CODEC_SKETCH && sk_init(p)) { gb_plan_destroy(p); return -1; }
-  if (params->codec == GB_CODEC_ADAQ && aq_init(p)) { gb_plan_destroy(p); return -1; }
+  if (params->codec == GB_CODEC_SKETCH && sk_init(p)) return -1;
+  if (params->codec == GB_CODEC_ADAQ && aq_init(p)) return -1;
   GB_CUDA(cudaDeviceSynchronize());
+  return 0;
+  };
+  if (build()) {
+    gb_plan_destroy(p);
+    return -1;
+  }
   *out = p;
   return 0;
 }

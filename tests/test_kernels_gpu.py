@@ -368,3 +368,22 @@ def test_variable_size_payload_overflow_is_reported():
             e.check_status()
     finally:
         e.destroy()
+
+
+def test_failed_plan_creation_is_clean():
+    """A plan that does not fit the peer arena is refused with a message and released; the engine keeps working."""
+    from grace_b200.ops.native import NativeError
+    from grace_b200.parallel.engine import Engine
+    (e,) = Engine.local(1, arena_bytes=8 << 20)
+    try:
+        with pytest.raises(NativeError, match="arena"):
+            e.plan([8 << 20], ["huge.weight"], _params("qsgd"))          # needs 2 x 8 MB of slots + headers
+        p = e.plan(SIZES, NAMES, _params("qsgd"))
+        buf = torch.randn(p.padded, device="cuda")
+        out = torch.empty(p.padded, device="cuda")
+        p.send(buf); p.recv(out)
+        torch.cuda.synchronize()
+        e.check_status()
+        assert float((out[:1000] - buf[:1000]).abs().max()) < 0.6        # one QSGD quantum = norm / 64 ~ 0.5
+    finally:
+        e.destroy()
