@@ -387,3 +387,30 @@ def test_failed_plan_creation_is_clean():
         assert float((out[:1000] - buf[:1000]).abs().max()) < 0.6        # one QSGD quantum = norm / 64 ~ 0.5
     finally:
         e.destroy()
+
+
+@pytest.mark.parametrize("codec,memory", [
+    ("topk", "residual"), ("randomk", "residual"), ("threshold", "residual"), ("dgc", "dgc"), ("qsgd", "none"),
+    ("terngrad", "residual"), ("natural", "residual"), ("u8bit", "none"), ("signsgd", "none"), ("signum", "residual"),
+    ("efsignsgd", "residual"), ("onebit", "residual"), ("sketch", "residual"), ("adaq", "residual"),
+    ("inceptionn", "residual"), ("none", "none"), ("fp16", "none")])
+def test_degenerate_gradients_stay_finite(codec, memory):
+    """All-zero and constant gradients (dead layers, frozen inputs): zero norms, empty selections, k-way ties and
+    single-bucket quantiles must neither produce NaN/Inf nor trip the overflow / timeout status."""
+    comp = C.INCEPTIONNCompressor()
+    prm = _params(codec, memory, ratio=0.05, quantum_num=(comp.low_exp | (comp.mid_exp << 8)) if codec == "inceptionn" else 64)
+    zeros = [[[torch.zeros(n, device="cuda") for n in SIZES]] for _ in range(2)]
+    outs, states = run_fused(1, prm, zeros)
+    for step in outs:
+        for t in step[0]:
+            assert torch.isfinite(t).all(), codec
+            if codec not in ("signsgd", "signum", "onebit"):
+                assert float(t.abs().max()) == 0.0, (codec, float(t.abs().max()))
+    const = [[[torch.full((n,), -0.75, device="cuda") for n in SIZES]] for _ in range(2)]
+    outs, states = run_fused(1, prm, const)
+    for step in outs:
+        for t in step[0]:
+            assert torch.isfinite(t).all(), codec
+    for st in states[0]:
+        if st is not None:
+            assert all(torch.isfinite(s).all() for s in st), codec
