@@ -59,6 +59,9 @@ class PinnedPrefetcher:
         device = torch.device("cuda", torch.cuda.current_device()) if device is None else device
         self.stream = torch.cuda.Stream(device=device)
         self.slots = [[torch.empty(t.shape, dtype=t.dtype, device=device) for t in example_inputs] for _ in range(depth)]
+        for slot in self.slots:                      # the staging sets are written on the copy stream: tell the caching
+            for t in slot:                            # allocator, so their memory is not handed out again while a copy runs
+                t.record_stream(self.stream)
         self.ready = [torch.cuda.Event() for _ in range(depth)]
         self.consumed = [None] * depth
         self.fed, self.taken = 0, 0
