@@ -1,1 +1,1 @@
-from grace_b200.compressor import PowerSGDCompressor  # noqa: F401
+from grace_b200.compressor.powersgd import PowerSGDCompressor, orthogonalize  # noqa: F401

@@ -1,1 +1,1 @@
-from grace_b200.compressor import RandomKCompressor  # noqa: F401
+from grace_b200.compressor.randomk import RandomKCompressor, sparsify  # noqa: F401

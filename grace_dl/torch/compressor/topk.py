@@ -1,1 +1,1 @@
-from grace_b200.compressor import TopKCompressor  # noqa: F401
+from grace_b200.compressor.topk import TopKCompressor, sparsify, desparsify  # noqa: F401
