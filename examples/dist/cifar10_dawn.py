@@ -23,13 +23,28 @@ from grace_b200.utils.metrics import TableLogger  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--epochs", type=int, default=24)
 ap.add_argument("--batch-size", type=int, default=512)
-ap.add_argument("--data-dir", default="")
+ap.add_argument("--data-dir", "--data_dir", dest="data_dir", default="")
 ap.add_argument("--backend", default="nccl" if torch.cuda.is_available() else "gloo")
-ap.add_argument("--compressor", default="none")
-ap.add_argument("--memory", default="none")
-ap.add_argument("--communicator", default="allreduce")
-ap.add_argument("--compress-ratio", type=float, default=0.01)
+ap.add_argument("--compressor", "--compression_method", dest="compressor", default="none")
+ap.add_argument("--memory", nargs="?", const="residual", default="none",
+                help="memory name; the reference's bare --memory flag (dawn.py:18) selects the residual memory")
+ap.add_argument("--communicator", "--communication_method", dest="communicator", default="allreduce")
+ap.add_argument("--compress-ratio", "--compress_ratio", dest="compress_ratio", type=float, default=0.01)
+# flags of the reference's dawn.py:8-22, accepted so its command lines keep working (the reference parses most of them
+# and then ignores them in favour of hard-coded params, dawn.py:125-127; here they are honoured)
+ap.add_argument("--log_dir", default=".")
+ap.add_argument("--master_address", "-m", default="127.0.0.1")
+ap.add_argument("--rank", "-r", type=int, default=None)
+ap.add_argument("--world_size", "-w", type=int, default=None)
+ap.add_argument("--clipping", action="store_true")
+ap.add_argument("--efsgdlr", type=float, default=0.1)
+ap.add_argument("--momentum", type=float, default=0.9)
+ap.add_argument("--threshold", type=float, default=0.01)
+ap.add_argument("--qstates", type=int, default=256)
 args = ap.parse_args()
+if args.rank is not None and "RANK" not in os.environ:          # reference style: explicit rank / world size / master
+    os.environ.update(RANK=str(args.rank), WORLD_SIZE=str(args.world_size or 2), MASTER_ADDR=args.master_address,
+                      MASTER_PORT=os.environ.get("MASTER_PORT", "1111"), LOCAL_RANK=os.environ.get("LOCAL_RANK", str(args.rank)))
 
 rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 if world > 1:
@@ -69,7 +84,9 @@ steps_per_epoch = len(train_x) // (args.batch_size * world)
 lr_at = lambda e: max(0.0, (e / 5 if e < 5 else (args.epochs - e) / max(args.epochs - 5, 1))) * 0.4   # piecewise linear
 opt = torch.optim.SGD(model.parameters(), lr=0.0, momentum=0.9, nesterov=True, weight_decay=5e-4 * args.batch_size)
 grc = grace_from_params({"compressor": args.compressor, "memory": args.memory, "communicator": args.communicator,
-                         "compress_ratio": args.compress_ratio, "world_size": world})
+                         "compress_ratio": args.compress_ratio, "world_size": world, "threshold": args.threshold,
+                         "quantum_num": args.qstates, "lr": args.efsgdlr, "momentum": args.momentum,
+                         "gradient_clipping": args.clipping})
 table = TableLogger(rank=rank)
 t0 = time.time()
 for epoch in range(args.epochs):
@@ -89,7 +106,7 @@ for epoch in range(args.epochs):
         for name, p in model.named_parameters():               # the reference's sequential exchange loop
             p.grad.copy_(grc.step(p.grad, name))
         opt.step()
-        loss_sum += float(loss)
+        loss_sum += float(loss.detach())
     model.eval()
     with torch.no_grad():
         correct = sum(int((model(test_x[i:i + 1000].to(device)).argmax(1) == test_y[i:i + 1000].to(device)).sum())

@@ -27,7 +27,15 @@ ap.add_argument("--compressor", default="topk")
 ap.add_argument("--memory", default="residual")
 ap.add_argument("--communicator", default="allgather")
 ap.add_argument("--no-cuda", action="store_true")
+# remaining flags of the reference example (pytorch_mnist.py:15-40)
+ap.add_argument("--test-batch-size", type=int, default=1000)
+ap.add_argument("--seed", type=int, default=42)
+ap.add_argument("--log-interval", type=int, default=10)
+ap.add_argument("--fp16-allreduce", action="store_true", help="use the fp16 codec (what Horovod's fp16 compression did)")
 args = ap.parse_args()
+if args.fp16_allreduce:
+    args.compressor, args.memory, args.communicator = "fp16", "none", "allreduce"
+torch.manual_seed(args.seed)
 cuda = not args.no_cuda and torch.cuda.is_available()
 hvd.init()
 torch.manual_seed(42)

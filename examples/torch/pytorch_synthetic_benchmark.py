@@ -34,7 +34,18 @@ ap.add_argument("--graph", action="store_true",
                 help="replay the whole step (forward, backward, fused exchange, optimizer) as ONE CUDA graph and feed it "
                      "from pinned host memory with hvd.GraphedStep.feed/run")
 ap.add_argument("--no-cuda", action="store_true")
+# remaining flags of the reference harness (pytorch_synthetic_benchmark.py:42-72); --use-adasum has no equivalent
+ap.add_argument("--fp16-allreduce", action="store_true", help="use the fp16 codec")
+ap.add_argument("--use-adasum", action="store_true", help="accepted and ignored")
+ap.add_argument("--seed", type=int, default=42)
+ap.add_argument("--lr", type=float, default=0.01)
+ap.add_argument("--momentum", type=float, default=0.5)
+ap.add_argument("--epochs", type=int, default=1, help="accepted and ignored (the harness runs --num-iters x --num-batches-per-iter)")
+ap.add_argument("--log-interval", type=int, default=10, help="accepted and ignored")
 args = ap.parse_args()
+if args.fp16_allreduce:
+    args.compressor, args.memory, args.communicator = "fp16", "none", "allreduce"
+torch.manual_seed(args.seed)
 cuda = not args.no_cuda and torch.cuda.is_available()
 
 hvd.init()
@@ -42,7 +53,7 @@ import torchvision  # noqa: E402
 model = getattr(torchvision.models, args.model)()
 if cuda:
     model = model.cuda().to(memory_format=torch.channels_last)
-optimizer = torch.optim.SGD(model.parameters(), lr=0.01 * hvd.size(), momentum=0.5)
+optimizer = torch.optim.SGD(model.parameters(), lr=args.lr * hvd.size(), momentum=args.momentum)
 hvd.broadcast_parameters(model.state_dict(), root_rank=0)
 hvd.broadcast_optimizer_state(optimizer, root_rank=0)
 grc = hvd.grace_from_params({"compressor": args.compressor, "memory": args.memory, "communicator": args.communicator,
