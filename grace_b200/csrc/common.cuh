@@ -200,8 +200,8 @@ __device__ __forceinline__ void tile_bounds(const SegTable& t, int tile, int& se
     const int4 d = __ldg(t.tile_desc + tile);
     base = (int64_t)(((uint64_t)(uint32_t)d.y << 32) | (uint32_t)d.x);
     seg = d.z;
-    len = d.w & 0xFFFF;                       // 1..4096 fits 13 bits
-    local0 = (d.w >> 16) * GB_TILE;           // tile index inside the segment (< 2^15 for < 2^27-element tensors)
+    len = d.w & 0x1FFF;                       // 1..4096 fits 13 bits
+    local0 = (int)((uint32_t)d.w >> 13) * GB_TILE;   // tile index inside the segment: 19 bits cover 2^31 elements
     return;
   }
   seg = t.tile_seg[tile];

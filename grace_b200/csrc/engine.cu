@@ -10,6 +10,7 @@
 #include "engine.cuh"
 
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <mutex>
 #include <unordered_map>
@@ -42,7 +43,14 @@ static int comm_init_common(gb_comm* c, size_t arena_bytes) {
   GB_CUDA(cudaHostGetDevicePointer((void**)&c->status_dev, c->status_host, 0));
   c->cursor = GB_FLAG_BYTES;
   c->next_channel = 1;  // channel 0 is the barrier
-  c->timeout_ns = 20ull * 1000 * 1000 * 1000;
+  // NCCL-like patience by default (a rank may be saving a checkpoint); GRACE_B200_TIMEOUT_MS overrides
+  c->timeout_ns = 120ull * 1000 * 1000 * 1000;
+  if (const char* e = getenv("GRACE_B200_TIMEOUT_MS")) {
+    const long long ms = atoll(e);
+    if (ms > 0) c->timeout_ns = (uint64_t)ms * 1000000ull;
+  }
+  c->need_bytes = 0;
+  c->siblings = nullptr;
   c->barrier_epoch = 0;
   for (int i = 0; i < GB_MAX_WORLD; ++i) { c->peer[i] = nullptr; c->opened[i] = false; }
   c->peer[c->rank] = c->base;
@@ -95,6 +103,9 @@ extern "C" int gb_comm_create_local(int world, size_t arena_bytes, gb_comm** out
   }
   for (int r = 0; r < world; ++r)
     for (int q = 0; q < world; ++q) out[r]->peer[q] = out[q]->base;
+  gb_comm** sib = new gb_comm*[world];           // shared by the group; released with rank 0
+  for (int r = 0; r < world; ++r) sib[r] = out[r];
+  for (int r = 0; r < world; ++r) out[r]->siblings = sib;
   return 0;
 }
 
@@ -103,6 +114,12 @@ extern "C" int gb_comm_destroy(gb_comm* c) {
   cudaDeviceSynchronize();
   for (int r = 0; r < c->world; ++r)
     if (c->opened[r]) cudaIpcCloseMemHandle(c->peer[r]);
+  for (gb_region& g : c->extra) {
+    for (int r = 0; r < c->world; ++r)
+      if (g.opened[r]) cudaIpcCloseMemHandle(g.peer[r]);
+    cudaFree(g.base);
+  }
+  if (c->siblings && c->rank == 0) delete[] c->siblings;
   cudaFree(c->base);
   cudaFreeHost(c->status_host);
   delete c;
@@ -123,17 +140,78 @@ extern "C" int gb_comm_set_timeout_ms(gb_comm* c, uint64_t ms) {
 }
 extern "C" int gb_comm_rank(gb_comm* c) { return c->rank; }
 extern "C" int gb_comm_world(gb_comm* c) { return c->world; }
-extern "C" size_t gb_comm_arena_free(gb_comm* c) { return c->bytes - c->cursor; }
+extern "C" size_t gb_comm_arena_free(gb_comm* c) {
+  return c->extra.empty() ? c->bytes - c->cursor : c->extra.back().bytes - c->extra.back().cursor;
+}
+extern "C" size_t gb_comm_arena_need(gb_comm* c) { return c->need_bytes; }
+extern "C" int gb_comm_regions(gb_comm* c) { return 1 + (int)c->extra.size(); }
 
+// Channels are carved from the LAST region only, so every rank (same call sequence, same region list) takes the
+// same decision.  When the slot does not fit, need_bytes tells the caller how much to add (gb_comm_region_add is
+// collective: every rank adds a region of the same size, exchanges its IPC handle, and retries).
 int gb_comm_alloc_channel(gb_comm* c, size_t slot_bytes, int* channel, size_t* offset) {
   size_t need = ((slot_bytes + 255) & ~size_t(255)) * 2 * (size_t)c->world;
   GB_CHECK(c->next_channel < GB_MAX_CHANNELS, "out of flag channels (%d)", GB_MAX_CHANNELS);
-  GB_CHECK(c->cursor + need <= c->bytes,
-           "peer arena exhausted: need %zu more bytes, %zu free (create the communicator with a larger arena)", need,
-           c->bytes - c->cursor);
+  size_t& cursor = c->extra.empty() ? c->cursor : c->extra.back().cursor;
+  const size_t bytes = c->extra.empty() ? c->bytes : c->extra.back().bytes;
+  if (cursor + need > bytes) {
+    c->need_bytes = need;
+    gb_set_error("peer arena exhausted: need %zu more bytes, %zu free (grow it with gb_comm_region_add)", need, bytes - cursor);
+    return -1;
+  }
+  c->need_bytes = 0;
   *channel = c->next_channel++;
-  *offset = c->cursor;
-  c->cursor += need;
+  *offset = cursor | ((size_t)c->extra.size() << GB_REGION_SHIFT);
+  cursor += need;
+  return 0;
+}
+
+static int region_alloc(gb_comm* c, size_t bytes) {
+  gb_region g;
+  memset(&g, 0, sizeof(g));
+  g.bytes = (bytes + 255) & ~size_t(255);
+  GB_CUDA(cudaMalloc((void**)&g.base, g.bytes));
+  GB_CUDA(cudaMemset(g.base, 0, g.bytes));
+  GB_CUDA(cudaDeviceSynchronize());
+  g.peer[c->rank] = g.base;
+  c->extra.push_back(g);
+  c->need_bytes = 0;
+  return 0;
+}
+
+extern "C" int gb_comm_region_add(gb_comm* c, size_t bytes, int* index) {
+  if (c->local_group && c->siblings) {            // single-process group: grow every virtual rank at once
+    for (int r = 0; r < c->world; ++r)
+      if (region_alloc(c->siblings[r], bytes)) return -1;
+    for (int r = 0; r < c->world; ++r)
+      for (int q = 0; q < c->world; ++q) c->siblings[r]->extra.back().peer[q] = c->siblings[q]->extra.back().base;
+  } else if (region_alloc(c, bytes)) {
+    return -1;
+  }
+  if (index) *index = (int)c->extra.size();
+  return 0;
+}
+
+extern "C" int gb_comm_region_ipc_handle(gb_comm* c, int index, void* out64) {
+  GB_CHECK(index >= 1 && index <= (int)c->extra.size(), "no region %d", index);
+  cudaIpcMemHandle_t h;
+  GB_CUDA(cudaIpcGetMemHandle(&h, c->extra[index - 1].base));
+  memcpy(out64, &h, 64);
+  return 0;
+}
+
+extern "C" int gb_comm_region_open_peers(gb_comm* c, int index, const void* handles) {
+  GB_CHECK(index >= 1 && index <= (int)c->extra.size(), "no region %d", index);
+  gb_region& g = c->extra[index - 1];
+  for (int r = 0; r < c->world; ++r) {
+    if (r == c->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)handles + 64 * r, 64);
+    void* p = nullptr;
+    GB_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    g.peer[r] = (char*)p;
+    g.opened[r] = true;
+  }
   return 0;
 }
 

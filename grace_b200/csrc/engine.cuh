@@ -5,13 +5,23 @@
 
 #include <vector>
 
-#define GB_MAX_CHANNELS 512
+#define GB_MAX_CHANNELS 4096
 // flags[channel][parity][src_rank] : uint32 epochs, at the start of every arena
 #define GB_FLAG_BYTES (GB_MAX_CHANNELS * 2 * GB_MAX_WORLD * 4)
 
 __host__ __device__ __forceinline__ uint32_t* gb_flag(char* arena, int channel, int parity, int src) {
   return (uint32_t*)arena + ((size_t)channel * 2 + parity) * GB_MAX_WORLD + src;
 }
+
+// Additional arena regions (index >= 1).  Region 0 is gb_comm::base and also holds the flags; further regions are
+// added collectively when a plan does not fit (gb_comm_region_add), so the arena is no longer sized by the first caller.
+struct gb_region {
+  char* base;
+  size_t bytes, cursor;
+  char* peer[GB_MAX_WORLD];
+  bool opened[GB_MAX_WORLD];
+};
+#define GB_REGION_SHIFT 48   // a channel offset carries its region index in the bits above this
 
 struct gb_comm {
   int rank, world, device;
@@ -26,10 +36,20 @@ struct gb_comm {
   uint32_t* status_dev;
   uint64_t timeout_ns;
   uint32_t barrier_epoch;
+  std::vector<gb_region> extra;   // regions 1.. (same order and sizes on every rank)
+  size_t need_bytes;              // bytes the last failed channel allocation asked for (0 = none pending)
+  gb_comm** siblings;             // local (single-process) groups: all virtual ranks, for collective growth
 };
 
 int gb_comm_alloc_channel(gb_comm* c, size_t slot_bytes, int* channel, size_t* offset);
 PeerPtrs gb_comm_peers(const gb_comm* c);
+
+// Slot `src` of parity `parity` of a channel inside rank `arena_rank`'s arena (host side; region aware).
+static inline char* gb_slot_of(const gb_comm* c, int arena_rank, size_t chan_off, size_t slot_bytes, int parity, int src) {
+  const size_t reg = chan_off >> GB_REGION_SHIFT, off = chan_off & ((size_t(1) << GB_REGION_SHIFT) - 1);
+  char* base = reg == 0 ? c->peer[arena_rank] : c->extra[reg - 1].peer[arena_rank];
+  return base + off + ((size_t)parity * c->world + src) * slot_bytes;
+}
 
 // Slot r of parity q of a channel inside one arena.
 __host__ __device__ __forceinline__ char* gb_slot(char* arena, size_t chan_off, size_t slot_bytes, int world, int parity,

@@ -98,8 +98,8 @@ static K0Slots slots_of(gb_plan* p, bool remote, uint32_t epoch = 0) {   // pari
   gb_comm* c = p->comm;
   s.n = c->world;
   for (int r = 0; r < c->world; ++r)
-    s.slot[r] = remote ? gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, epoch & 1, c->rank)
-                       : gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, epoch & 1, r);
+    s.slot[r] = remote ? gb_slot_of(c, r, p->chan_off, p->slot_bytes, epoch & 1, c->rank)
+                       : gb_slot_of(c, c->rank, p->chan_off, p->slot_bytes, epoch & 1, r);
   return s;
 }
 

@@ -648,7 +648,7 @@ int aq_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   AdaqOut out;
   const size_t mb = aq_means_bytes(p->nseg);
   for (int r = 0; r < c->world; ++r) {
-    char* s = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, 0, c->rank);
+    char* s = gb_slot_of(c, r, p->chan_off, p->slot_bytes, 0, c->rank);
     out.hdr[r] = (int2*)s; out.means[r] = (float*)(s + p->hdr_bytes); out.idx[r] = (int32_t*)(s + p->hdr_bytes + mb);
   }
   out.n = c->world;
@@ -685,7 +685,7 @@ int aq_recv(gb_plan* p, float* d_out, cudaStream_t st) {
   AdaqIn in;
   const size_t mb = aq_means_bytes(p->nseg);
   for (int r = 0; r < c->world; ++r) {
-    const char* s = gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, 0, r);
+    const char* s = gb_slot_of(c, c->rank, p->chan_off, p->slot_bytes, 0, r);
     in.hdr[r] = (const int2*)s; in.means[r] = (const float*)(s + p->hdr_bytes); in.idx[r] = (const int32_t*)(s + p->hdr_bytes + mb);
   }
   in.n = c->world;

@@ -670,8 +670,8 @@ static void slot_views(gb_plan* p, int parity, bool remote_side, SparseOut* o, S
   gb_comm* c = p->comm;
   const size_t per = ((size_t)p->ktotal * 4 + 255) & ~size_t(255);
   for (int r = 0; r < c->world; ++r) {
-    char* s = remote_side ? gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, parity, c->rank)
-                          : gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, parity, r);
+    char* s = remote_side ? gb_slot_of(c, r, p->chan_off, p->slot_bytes, parity, c->rank)
+                          : gb_slot_of(c, c->rank, p->chan_off, p->slot_bytes, parity, r);
     if (o) { o->hdr[r] = (int2*)s; o->vals[r] = (float*)(s + p->hdr_bytes); o->idx[r] = (int32_t*)(s + p->hdr_bytes + per); }
     if (in) { in->hdr[r] = (const int2*)s; in->vals[r] = (const float*)(s + p->hdr_bytes); in->idx[r] = (const int32_t*)(s + p->hdr_bytes + per); }
   }

@@ -364,7 +364,7 @@ int in_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   IncOut out;
   const size_t tb = in_tag_bytes(p->padded);
   for (int r = 0; r < c->world; ++r) {
-    char* s = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, 0, c->rank);
+    char* s = gb_slot_of(c, r, p->chan_off, p->slot_bytes, 0, c->rank);
     out.hdr[r] = (int4*)s; out.tags[r] = (uint8_t*)(s + p->hdr_bytes); out.stream[r] = (uint32_t*)(s + p->hdr_bytes + tb);
   }
   out.n = c->world;
@@ -383,7 +383,7 @@ int in_recv(gb_plan* p, float* d_out, cudaStream_t st) {
   IncIn in;
   const size_t tb = in_tag_bytes(p->padded);
   for (int r = 0; r < c->world; ++r) {
-    const char* s = gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, 0, r);
+    const char* s = gb_slot_of(c, c->rank, p->chan_off, p->slot_bytes, 0, r);
     in.hdr[r] = (const int4*)s; in.tags[r] = (const uint8_t*)(s + p->hdr_bytes); in.stream[r] = (const uint32_t*)(s + p->hdr_bytes + tb);
   }
   in.n = c->world;

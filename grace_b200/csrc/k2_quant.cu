@@ -652,7 +652,7 @@ int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   ++p->epoch;                           // host mirror of the device-side epoch
   WireOut out;
   out.n = c->world;
-  for (int r = 0; r < c->world; ++r) out.slot[r] = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, 0, c->rank);
+  for (int r = 0; r < c->world; ++r) out.slot[r] = gb_slot_of(c, r, p->chan_off, p->slot_bytes, 0, c->rank);
   const PeerPtrs peers = gb_comm_peers(c);
   if (needs_stats(a.codec)) {
     const int g = grid_for(p->ntiles);
@@ -674,7 +674,7 @@ int k2_recv(gb_plan* p, float* d_out, cudaStream_t st) {
   GB_CHECK(((uintptr_t)d_out & 15) == 0, "output buffer must be 16-byte aligned");
   WireIn in;
   in.n = c->world;
-  for (int r = 0; r < c->world; ++r) in.slot[r] = gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, 0, r);
+  for (int r = 0; r < c->world; ++r) in.slot[r] = gb_slot_of(c, c->rank, p->chan_off, p->slot_bytes, 0, r);
   const PeerPtrs peers = gb_comm_peers(c);
   int mode = 0;
   float divisor = p->prm.average ? (float)c->world : 1.f;

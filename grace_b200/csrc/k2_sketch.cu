@@ -263,7 +263,7 @@ int sk_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   ++p->epoch;
   SkSlots out;
   out.n = c->world;
-  for (int r = 0; r < c->world; ++r) out.slot[r] = gb_slot(c->peer[r], p->chan_off, p->slot_bytes, c->world, 0, c->rank);
+  for (int r = 0; r < c->world; ++r) out.slot[r] = gb_slot_of(c, r, p->chan_off, p->slot_bytes, 0, c->rank);
   sk_prep<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, b->vals, b->keys, has_mem, p->prm.beta, p->prm.gamma,
                                                      p->d_ctl);
   LAUNCHED(p);
@@ -282,7 +282,7 @@ int sk_recv(gb_plan* p, float* d_out, cudaStream_t st) {
   gb_comm* c = p->comm;
   SkIn in;
   in.n = c->world;
-  for (int r = 0; r < c->world; ++r) in.slot[r] = gb_slot(c->base, p->chan_off, p->slot_bytes, c->world, 0, r);
+  for (int r = 0; r < c->world; ++r) in.slot[r] = gb_slot_of(c, c->rank, p->chan_off, p->slot_bytes, 0, r);
   sk_decode<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, p->hdr_bytes, p->prm.quantum_num, d_out,
                                                        p->prm.average ? (float)c->world : 1.f, gb_comm_peers(c), p->channel, p->d_ctl,
                                                        p->par_stride, c->status_dev, c->timeout_ns);

@@ -773,12 +773,12 @@ extern "C" int64_t gb_psgd_wire_bytes(gb_psgd* p) { return (int64_t)(p->prows + 
 
 static PsPeers peer_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch = 0) {   // parity 0
   PsPeers s; gb_comm* c = p->comm; s.n = c->world;
-  for (int r = 0; r < c->world; ++r) s.slot[r] = (float*)gb_slot(c->peer[r], chan_off, slot_bytes, c->world, epoch & 1, c->rank);
+  for (int r = 0; r < c->world; ++r) s.slot[r] = (float*)gb_slot_of(c, r, chan_off, slot_bytes, epoch & 1, c->rank);
   return s;
 }
 static PsIn my_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch = 0) {        // parity 0
   PsIn s; gb_comm* c = p->comm; s.n = c->world;
-  for (int r = 0; r < c->world; ++r) s.slot[r] = (const float*)gb_slot(c->base, chan_off, slot_bytes, c->world, epoch & 1, r);
+  for (int r = 0; r < c->world; ++r) s.slot[r] = (const float*)gb_slot_of(c, c->rank, chan_off, slot_bytes, epoch & 1, r);
   return s;
 }
 

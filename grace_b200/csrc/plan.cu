@@ -140,9 +140,9 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
       const int within = tile - p->h_tile0[sg];
       const int64_t base = p->h_off[sg] + (int64_t)within * GB_TILE;
       const int len = (int)std::min<int64_t>(GB_TILE, p->h_numel[sg] - (int64_t)within * GB_TILE);
-      if (within >= (1 << 15)) desc_ok = false;
+      if (within >= (1 << 19)) desc_ok = false;          // cannot happen below 2^31 elements; kept as a guard
       desc[tile] = make_int4((int)(uint32_t)(base & 0xFFFFFFFFll), (int)(uint32_t)((uint64_t)base >> 32), sg,
-                             (len == GB_TILE ? 4096 : len) | (within << 16));
+                             (int)((uint32_t)len | ((uint32_t)within << 13)));
     }
     GB_CUDA(cudaMemcpy(d_tiledesc, desc.data(), (size_t)p->ntiles * 16, cudaMemcpyHostToDevice));
   }

@@ -66,6 +66,11 @@ def _declare(L):
         "gb_comm_world": (i32, [vp]),
         "gb_comm_arena_free": (sz, [vp]),
         "gb_comm_barrier": (i32, [vp, vp]),
+        "gb_comm_arena_need": (sz, [vp]),
+        "gb_comm_regions": (i32, [vp]),
+        "gb_comm_region_add": (i32, [vp, sz, P(i32)]),
+        "gb_comm_region_ipc_handle": (i32, [vp, i32, vp]),
+        "gb_comm_region_open_peers": (i32, [vp, i32, vp]),
         "gb_handle_record": (i32, [vp, P(i64)]),
         "gb_handle_poll": (i32, [i64]),
         "gb_handle_wait": (i32, [i64]),

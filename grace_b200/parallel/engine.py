@@ -32,6 +32,7 @@ class Engine:
     def __init__(self, handle, rank, world, group=None):
         self._h = C.c_void_p(handle)
         self.rank, self.world, self.group = rank, world, group
+        self._local = False
         self.plans: List["Plan"] = []
 
     # ------------------------------------------------------------------ construction
@@ -66,7 +67,10 @@ class Engine:
         check(L.gb_set_device(torch.cuda.current_device()))
         arr = (C.c_void_p * world)()
         check(L.gb_comm_create_local(world, arena_bytes or (256 << 20), arr))
-        return [cls(arr[r], r, world) for r in range(world)]
+        engines = [cls(arr[r], r, world) for r in range(world)]
+        for e in engines:
+            e._local = True
+        return engines
 
     # ------------------------------------------------------------------ services
     def status(self):
@@ -87,6 +91,38 @@ class Engine:
 
     def arena_free(self):
         return native.lib().gb_comm_arena_free(self._h)
+
+    def grow(self, nbytes):
+        """Collective: every rank adds an arena region of at least ``nbytes`` (same size everywhere), exports it
+        with CUDA IPC and maps the peers' regions.  Called automatically when a plan's wire slot does not fit,
+        so the arena is not limited to what the first model needed."""
+        L = native.lib()
+        nbytes = max(int(nbytes) + (1 << 20), int(os.environ.get("GRACE_B200_ARENA_GROW_MB", "256")) << 20)
+        idx = C.c_int()
+        check(L.gb_comm_region_add(self._h, nbytes, C.byref(idx)))
+        if self.world > 1 and not self._local:
+            buf = C.create_string_buffer(64)
+            check(L.gb_comm_region_ipc_handle(self._h, idx.value, buf))
+            gathered = [None] * self.world
+            dist.all_gather_object(gathered, bytes(buf.raw), group=self.group)
+            check(L.gb_comm_region_open_peers(self._h, idx.value, b"".join(gathered)))
+            dist.barrier(group=self.group)
+        return idx.value
+
+    def create_with_growth(self, create):
+        """Run ``create()`` (a native plan constructor returning its status); on "arena exhausted" grow the
+        arena by what was missing and retry."""
+        L = native.lib()
+        rc = -1
+        for _ in range(4):
+            rc = create()
+            if rc == 0:
+                return
+            need = L.gb_comm_arena_need(self._h)
+            if not need:
+                break
+            self.grow(need)
+        check(rc)
 
     def barrier(self, stream=None):
         check(native.lib().gb_comm_barrier(self._h, _stream_ptr(stream)))
@@ -115,7 +151,7 @@ class Plan:
         nm = (C.c_int64 * self.nseg)(*self.numels)
         hs = (C.c_uint32 * self.nseg)(*[fnv1a(n) for n in names])
         h = C.c_void_p()
-        check(L.gb_plan_create(engine._h, self.nseg, nm, hs, C.byref(params), C.byref(h)))
+        engine.create_with_growth(lambda: L.gb_plan_create(engine._h, self.nseg, nm, hs, C.byref(params), C.byref(h)))
         self._h = h
         self.padded = L.gb_plan_padded_numel(h)
         off = (C.c_int64 * self.nseg)()
@@ -196,8 +232,8 @@ class PowerSGDPlan:
         cols = (C.c_int64 * self.nmat)(*[c for _, c in self.shapes])
         hs = (C.c_uint32 * self.nmat)(*[fnv1a(n) for n in names])
         h = C.c_void_p()
-        check(L.gb_psgd_create(engine._h, self.nmat, rows, cols, hs, int(rank), int(seed) & 0xFFFFFFFF,
-                               1 if has_memory else 0, 1 if use_tcgen05 else 0, C.byref(h)))
+        engine.create_with_growth(lambda: L.gb_psgd_create(engine._h, self.nmat, rows, cols, hs, int(rank), int(seed) & 0xFFFFFFFF,
+                                                           1 if has_memory else 0, 1 if use_tcgen05 else 0, C.byref(h)))
         self._h = h
         self.padded = L.gb_psgd_padded_numel(h)
         off = (C.c_int64 * self.nmat)()

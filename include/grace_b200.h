@@ -85,6 +85,15 @@ int gb_comm_set_timeout_ms(gb_comm* c, uint64_t ms);
 int gb_comm_rank(gb_comm* c);
 int gb_comm_world(gb_comm* c);
 size_t gb_comm_arena_free(gb_comm* c);
+/* The arena grows by whole regions.  When a plan's wire slot does not fit, gb_plan_create / gb_psgd_create fail and
+ * gb_comm_arena_need() reports the missing bytes; every rank then adds a region of the same size (collective:
+ * gb_comm_region_add, exchange the 64-byte IPC handles, gb_comm_region_open_peers) and retries.  The Python Engine
+ * does this automatically (Horovod's fusion buffer and NCCL's buffers also grow on demand). */
+size_t gb_comm_arena_need(gb_comm* c);
+int gb_comm_regions(gb_comm* c);
+int gb_comm_region_add(gb_comm* c, size_t bytes, int* index);
+int gb_comm_region_ipc_handle(gb_comm* c, int index, void* out64);
+int gb_comm_region_open_peers(gb_comm* c, int index, const void* handles);
 /* all ranks reach this point (flag barrier over peer memory; used by tests and K0) */
 int gb_comm_barrier(gb_comm* c, void* stream);
 
