@@ -457,6 +457,21 @@ class FusedDP:
     def in_flight(self):
         return self._inflight
 
+    def close(self):
+        """Detach from the model: remove the hooks, give every parameter a private ``.grad`` again and release the
+        plans (their arena slots are not returned -- the arena only grows -- but device state and tables are)."""
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+        torch.cuda.synchronize()
+        for b in self.buckets:
+            for p, v in zip(b.tensors, b.views):
+                if p.grad is v:
+                    p.grad = v.clone()
+            for pl in b.plans:
+                pl.destroy()
+        self.buckets = []
+
     def zero_grad(self):
         for b in self.buckets:
             for flat in b.flats:

@@ -33,14 +33,16 @@ import torch
 class PendingScalar:
     """A device scalar on its way to pinned host memory; ``item()`` waits for the copy only."""
 
-    def __init__(self, host, event):
-        self._host, self._event = host, event
+    def __init__(self, host, event, check=None):
+        self._host, self._event, self._check = host, event, check
 
     def done(self):
         return self._event.query()
 
     def item(self):
         self._event.synchronize()
+        if self._check is not None:
+            self._check()           # the step that produced this value has finished: report a timeout / overflow now
         return self._host.item()
 
     def __float__(self):
@@ -94,13 +96,13 @@ class PinnedPrefetcher:
         self.consumed[self._current] = ev
 
 
-def read_back(scalar, host=None):
+def read_back(scalar, host=None, check=None):
     """Start the device -> pinned-host copy of a scalar tensor on the current stream."""
     host = torch.empty((), dtype=scalar.dtype, pin_memory=True) if host is None else host
     host.copy_(scalar, non_blocking=True)
     ev = torch.cuda.Event()
     ev.record(torch.cuda.current_stream())
-    return PendingScalar(host, ev)
+    return PendingScalar(host, ev, check)
 
 
 class GraphedStep:
@@ -124,6 +126,9 @@ class GraphedStep:
         with torch.cuda.graph(self.graph):
             self.static_loss = self._step_body()
         self.native_launches_per_step = (fused.launches() - n0) if fused is not None else 0
+        # Python (and with it FusedDP.synchronize's status check) does not run during a replay: the pinned status
+        # word is read around every replay instead -- a plain host load, no device synchronisation
+        self._check = fused.engine.check_status if fused is not None else None
         self.replays = 0
         self._feeder = None
         self._loss_host = None
@@ -140,6 +145,8 @@ class GraphedStep:
         for dst, src in zip(self.static_inputs, inputs):
             if src is not dst:
                 dst.copy_(src, non_blocking=True)
+        if self._check is not None:
+            self._check()                                         # problems reported by earlier replays
         self.graph.replay()
         self.replays += 1
         return self.static_loss
@@ -158,6 +165,8 @@ class GraphedStep:
         for dst, src in zip(self.static_inputs, staged):
             dst.copy_(src, non_blocking=True)                     # device -> device (+ memory-format change)
         self._feeder.release()
+        if self._check is not None:
+            self._check()
         self.graph.replay()
         self.replays += 1
-        return read_back(self.static_loss, self._loss_host[self.replays % 4])      # ring of 4: read a loss within 3 steps
+        return read_back(self.static_loss, self._loss_host[self.replays % 4], self._check)      # ring of 4: read a loss within 3 steps

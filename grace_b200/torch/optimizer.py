@@ -133,6 +133,10 @@ class _DistributedOptimizer(torch.optim.Optimizer):
                               "optimizer.synchronize(). This can cause training slowdown.")
             self.synchronize()
         self._synchronized = False
+        if self._fused is not None and not torch.cuda.is_current_stream_capturing():
+            # anything the exchange kernels have reported so far (timeout, overflow) stops the update; a plain
+            # host read of the pinned status word, no device synchronisation
+            self._fused.engine.check_status()
         return super(self.__class__, self).step(closure)
 
     def zero_grad(self, set_to_none=None):
@@ -145,6 +149,15 @@ class _DistributedOptimizer(torch.optim.Optimizer):
         if self._hook_refs:
             return super(self.__class__, self).zero_grad(set_to_none=False)
         return super(self.__class__, self).zero_grad(*(() if set_to_none is None else (set_to_none,)))
+
+    def close(self):
+        """Remove the gradient hooks and release the native plans (the optimizer keeps working un-distributed)."""
+        for h in self._hook_refs:
+            h.remove()
+        self._hook_refs = []
+        if self._fused is not None:
+            self._fused.close()
+            self._fused = None
 
     # ------------------------------------------------------------------ checkpointing
     def grace_state_dict(self):
@@ -204,8 +217,11 @@ def broadcast_optimizer_state(optimizer, root_rank):
                 continue
             t = torch.tensor([float(value)], dtype=torch.float64)
             tensors.append(("%s.%d" % (key, gi), t))
+            # root's value goes into the live group AND into the dict that load_state_dict() applies below
+            # (load_state_dict replaces param_groups by the copies taken before the broadcast)
             writers.append(lambda t=t, gi=gi, key=key, kind=type(value):
-                           optimizer.param_groups[gi].__setitem__(key, kind(t.item())))
+                           (optimizer.param_groups[gi].__setitem__(key, kind(t.item())),
+                            state["param_groups"][gi].__setitem__(key, kind(t.item()))))
         for pid in group["params"]:
             for key, value in sorted(state["state"].get(pid, {}).items(), key=lambda kv: str(kv[0])):
                 if torch.is_tensor(value):

@@ -223,3 +223,28 @@ def test_blocking_collectives_are_differentiable():
     assert torch.equal(r0["allgather"], coef_sum[:1]) and torch.equal(r1["allgather"], coef_sum[1:])
     assert torch.equal(r0["broadcast"], torch.zeros(2)) and torch.equal(r1["broadcast"], torch.full((2,), 3.0))
     assert torch.equal(r0["plain"], torch.ones(2))
+
+
+def _optimizer_state_from_root(rank, world):
+    import grace_b200.torch as hvd
+    hvd.init()
+    torch.manual_seed(rank)
+    model = torch.nn.Linear(4, 3)
+    # a resumed rank 0 and a fresh rank 1: different hyper-parameters and different momentum buffers
+    opt = torch.optim.SGD(model.parameters(), lr=0.5 if rank == 0 else 0.1, momentum=0.9 if rank == 0 else 0.5,
+                          weight_decay=1e-3 if rank == 0 else 0.0)
+    model(torch.randn(2, 4)).sum().backward()
+    opt.step()
+    hvd.broadcast_optimizer_state(opt, root_rank=0)
+    g = opt.param_groups[0]
+    bufs = torch.cat([opt.state[p]["momentum_buffer"].flatten() for p in model.parameters()])
+    return (g["lr"], g["momentum"], g["weight_decay"]), bufs
+
+
+def test_broadcast_optimizer_state_propagates_hyperparameters():
+    """Reference: patch_files/horovod/torch/__init__.py:356-403 writes root's lr/momentum/... into every rank's
+    param_groups; replicas that keep their own lr after a resume diverge silently."""
+    (h0, b0), (h1, b1) = _spawn(_optimizer_state_from_root, 2)
+    assert h0 == (0.5, 0.9, 1e-3)
+    assert h1 == h0
+    assert torch.equal(b0, b1)
