@@ -41,6 +41,32 @@ class _NativeStep:
                 return out
         return super().step(tensor, name)
 
+    def step_all(self, named_grads, inplace=False):
+        """Bucketed form of the reference's manual loop (``examples/dist/CIFAR10-dawndist/core.py:202-208``:
+        ``for name, p in named_parameters(): grad.copy_(grc.step(grad, name))``): exchange every ``(name, grad)`` pair
+        of the list in one call.  On CUDA, built-in triples run as O(#buckets) native launches (the per-tensor ``k``,
+        norms, residuals are preserved by the segment tables) instead of O(#tensors x #ops); anything else falls back
+        to ``step`` per tensor.  Returns the aggregated tensors in order; with ``inplace=True`` they are also copied
+        into the given gradient tensors (one multi-tensor copy).  On the native path the returned tensors are views of
+        persistent bucket memory and are overwritten by the next ``step_all``."""
+        named_grads = list(named_grads)
+        outs = None
+        if self.fused and named_grads and named_grads[0][1].is_cuda:
+            if self._stepper is None:
+                from grace_b200.parallel.fused import FusedStepper
+                self._stepper = FusedStepper(self)
+            outs = self._stepper.step_all(named_grads)
+        if outs is None:
+            outs = [self.step(g, n) for n, g in named_grads]
+        if inplace and named_grads:
+            torch._foreach_copy_([g for _, g in named_grads], [o.view_as(g) for o, (_, g) in zip(outs, named_grads)])
+        return outs
+
+    def close(self):
+        """Release the native plans created by ``step`` / ``step_all`` (no-op on the generic path)."""
+        if self._stepper is not None:
+            self._stepper.close()
+
 
 def _finish(compressor, decompressed, world_size):
     out = compressor.aggregate(decompressed)

@@ -505,15 +505,9 @@ class FusedDP:
                                        for pl in b.plans]} for b in self.buckets]}
 
     def load_state_dict(self, state):
+        """Residual / momentum state is rank-local: save and restore one ``grace_state_dict()`` per rank."""
         torch.cuda.synchronize()
-        for b, s in zip(self.buckets, state["buckets"]):
-            if s["names"] != b.names:
-                raise ValueError("bucket layout differs from the checkpoint")
-            for pl, ps in zip(b.plans, s["plans"]):
-                pl.step = ps["step"]
-                for which in (0, 1):
-                    if ps["state%d" % which] is not None:
-                        pl.set_state(which, ps["state%d" % which])
+        _restore_buckets(self.buckets, state["buckets"])
 
 
 def try_build_fused(optimizer, grace, named, required=False, bucket_bytes=None) -> Optional[FusedDP]:
@@ -541,21 +535,78 @@ def try_build_fused(optimizer, grace, named, required=False, bucket_bytes=None) 
     return FusedDP(optimizer, grace, named, params, bucket_bytes, powersgd=psgd)
 
 
+class _StepAllSet:
+    """Buckets + plans for one fixed list of (name, shape) pairs: the bucketed form of the reference's manual
+    ``for name, p in named_parameters(): grc.step(p.grad, name)`` loop (examples/dist/CIFAR10-dawndist/core.py:202-208)."""
+
+    def __init__(self, engine, named_tensors, params, powersgd, bucket_bytes):
+        self.engine = engine
+        self.buckets = []
+        cur, cur_bytes = [], 0
+        for n, t in named_tensors:
+            cur.append((n, t))
+            cur_bytes += t.numel() * 4
+            if cur_bytes >= bucket_bytes:
+                self.buckets.append(self._make(cur, params, powersgd))
+                cur, cur_bytes = [], 0
+        if cur:
+            self.buckets.append(self._make(cur, params, powersgd))
+        for b in self.buckets:
+            b.tensors = [None] * len(b.tensors)      # geometry only: do not keep the first call's gradients alive
+        self.views = [v for b in self.buckets for v in b.views]
+
+    def _make(self, named_tensors, params, powersgd):
+        if powersgd is not None:
+            rank, seed, has_memory = powersgd
+            return _PowerSGDBucket(self.engine, named_tensors, rank, seed, has_memory,
+                                   use_tc=os.environ.get("GRACE_B200_PSGD_TCGEN05", "1") != "0")
+        return _Bucket(self.engine, named_tensors, params)
+
+    def exchange(self, grads):
+        """Copy the gradients into the buckets (one multi-tensor copy), run every bucket's send, then every mid, then
+        every recv on the current stream -- peers' payloads for bucket b arrive while this rank still compresses
+        bucket b+1 -- and return the views that now hold the aggregates."""
+        torch._foreach_copy_(self.views, grads)
+        for b in self.buckets:
+            b.send(None)
+        for b in self.buckets:
+            b.mid(None)
+        for b in self.buckets:
+            b.recv(None)
+        return self.views
+
+    def launches(self):
+        return sum(pl.launches() for b in self.buckets for pl in b.plans)
+
+    def destroy(self):
+        for b in self.buckets:
+            for pl in b.plans:
+                pl.destroy()
+        self.buckets = []
+
+
 class FusedStepper:
-    """Native fast path of the synchronous ``Communicator.step(tensor, name)`` API."""
+    """Native fast path of the synchronous ``Communicator.step(tensor, name)`` API and of its bucketed form
+    ``Communicator.step_all(named_grads)``."""
 
     def __init__(self, grace):
         self.grace = grace
         self.params = None
+        self.psgd = None
         self.plans = {}
+        self.sets = {}
         self.enabled = None
+        self._closed_launches = 0
 
     def _probe(self, tensor):
         if self.enabled is None:
             ok = tensor.is_cuda and os.environ.get("GRACE_B200_FUSED", "1") != "0"
+            ok = ok and getattr(self.grace, "group", None) is None      # plans always span the global engine
             if ok:
-                self.params = codec_params(self.grace.compressor, self.grace.memory)
-                ok = self.params is not None and communicator_is_fusable(self.grace, self.params)
+                self.psgd = powersgd_spec(self.grace)
+                if self.psgd is None:
+                    self.params = codec_params(self.grace.compressor, self.grace.memory)
+                    ok = self.params is not None and communicator_is_fusable(self.grace, self.params)
             ok = ok and single_nvlink_domain()
             if ok:
                 _native_or_raise()
@@ -564,21 +615,27 @@ class FusedStepper:
         return self.enabled
 
     def _entry(self, tensor, name):
-        key = (name, tensor.numel())
+        key = (name, tuple(tensor.shape))
         entry = self.plans.get(key)
         if entry is None:
             plan = get_engine().plan([tensor.numel()], [name], self.params)
             entry = (plan, torch.zeros(plan.padded, dtype=torch.float32, device=tensor.device),
                      torch.empty(plan.padded, dtype=torch.float32, device=tensor.device))
             self.plans[key] = entry
-            self._apply_state("%s/%d" % key, plan)
+            self._apply_state(self._tag(key), plan)
         return entry
 
+    @staticmethod
+    def _tag(key):
+        return "%s/%s" % (key[0], "x".join(str(d) for d in key[1]))
+
     def usable(self, tensor):
-        return self._probe(tensor) and tensor.dtype == torch.float32 and tensor.is_cuda
+        # PowerSGD has no single-tensor plan: its native path is step_all (grouped matrices of a bucket)
+        return self._probe(tensor) and self.psgd is None and tensor.dtype == torch.float32 and tensor.is_cuda
 
     def step(self, tensor, name):
-        """Returns the aggregated tensor, or ``None`` when this call must take the generic path."""
+        """Returns the aggregated tensor (a fresh tensor, like the reference), or ``None`` when this call must
+        take the generic path."""
         if not self.usable(tensor):
             return None
         plan, staging, out = self._entry(tensor, name)
@@ -586,20 +643,60 @@ class FusedStepper:
         staging[:n].copy_(tensor.reshape(-1))
         plan.send(staging)
         plan.recv(out)
-        return out[:n].view(tensor.shape)
+        return out[:n].view(tensor.shape).clone()
+
+    # ---- bucketed manual loop
+    def step_all(self, named_grads):
+        """``named_grads``: list of (name, tensor).  Returns a list of aggregated tensors (views into persistent
+        bucket memory, overwritten by the next call) or ``None`` when the generic path must run."""
+        if not named_grads:
+            return []
+        first = named_grads[0][1]
+        if not self._probe(first):
+            return None
+        if not all(g.is_cuda and g.dtype == torch.float32 for _, g in named_grads):
+            return None
+        key = tuple((n, tuple(g.shape), tuple(g.stride())) for n, g in named_grads)
+        st = self.sets.get(key)
+        if st is None:
+            st = _StepAllSet(get_engine(), named_grads, self.params, self.psgd, DEFAULT_BUCKET_BYTES)
+            self.sets[key] = st
+        return st.exchange([g for _, g in named_grads])
+
+    def launches(self):
+        return (self._closed_launches + sum(pl.launches() for pl, _, _ in self.plans.values())
+                + sum(st.launches() for st in self.sets.values()))
+
+    def close(self):
+        torch.cuda.synchronize()
+        self._closed_launches = self.launches()
+        for plan, _, _ in self.plans.values():
+            plan.destroy()
+        for st in self.sets.values():
+            st.destroy()
+        self.plans, self.sets = {}, {}
 
     def state_dict(self):
-        """Error-feedback state of the per-tensor plans (residuals, momenta, step counters)."""
+        """Error-feedback state of the per-tensor plans and bucket sets (residuals, momenta, step counters)."""
         torch.cuda.synchronize()
-        return {"%s/%d" % key: {"step": plan.step, "state0": plan.get_state(0), "state1": plan.get_state(1)}
-                for key, (plan, _, _) in self.plans.items()}
+        out = {self._tag(key): {"step": plan.step, "state0": plan.get_state(0), "state1": plan.get_state(1)}
+               for key, (plan, _, _) in self.plans.items()}
+        for i, st in enumerate(self.sets.values()):
+            out["__set%d__" % i] = [{"names": b.names, "plans": [{"step": pl.step, "state0": pl.get_state(0),
+                                                                  "state1": pl.get_state(1)} for pl in b.plans]}
+                                    for b in st.buckets]
+        return out
 
     def load_state_dict(self, state):
         """Restore plans that already exist; entries for tensors not seen yet are kept and applied on
         first use."""
         self._pending_state = dict(state)
         for key, (plan, _, _) in self.plans.items():
-            self._apply_state("%s/%d" % key, plan)
+            self._apply_state(self._tag(key), plan)
+        for i, st in enumerate(self.sets.values()):
+            saved = self._pending_state.pop("__set%d__" % i, None)
+            if saved is not None:
+                _restore_buckets(st.buckets, saved)
 
     def _apply_state(self, tag, plan):
         st = getattr(self, "_pending_state", {}).pop(tag, None)
@@ -632,4 +729,29 @@ class FusedStepper:
         done = torch.cuda.Event()
         done.record(self._side)
         torch.cuda.current_stream().wait_event(done)
-        return out[:n].view(shape)
+        return out[:n].view(shape).clone()
+
+
+def _restore_buckets(buckets, saved):
+    """Shared by FusedDP and the step_all sets: strict about the layout, so a checkpoint taken with another
+    bucket size or model is refused instead of being applied partially."""
+    if len(saved) != len(buckets):
+        raise ValueError("checkpoint has %d buckets, this run has %d (GRACE_B200_BUCKET_MB changed?)"
+                         % (len(saved), len(buckets)))
+    for b, s in zip(buckets, saved):
+        if s["names"] != b.names:
+            raise ValueError("bucket layout differs from the checkpoint")
+        if len(s["plans"]) != len(b.plans):
+            raise ValueError("bucket %s...: %d plans in the checkpoint, %d here" % (b.names[0], len(s["plans"]), len(b.plans)))
+        for pl, ps in zip(b.plans, s["plans"]):
+            for which in (0, 1):
+                t = ps["state%d" % which]
+                if t is not None and t.numel() != pl.padded:
+                    raise ValueError("state buffer of bucket %s... has %d elements, the plan expects %d"
+                                     % (b.names[0], t.numel(), pl.padded))
+    for b, s in zip(buckets, saved):
+        for pl, ps in zip(b.plans, s["plans"]):
+            pl.step = ps["step"]
+            for which in (0, 1):
+                if ps["state%d" % which] is not None:
+                    pl.set_state(which, ps["state%d" % which])
