@@ -1,18 +1,27 @@
 #!/usr/bin/env python
 """Headline benchmark: ResNet-50 synthetic training throughput (img/s, whole job) with gradient
-compression, the harness of the reference's ``examples/torch/pytorch_synthetic_benchmark.py``
-(batch 32 per GPU, fixed fake data 3x224x224) on BASELINE.json config 2: bf16 compute,
-TopK 1 % + ResidualMemory + Allgather.
+compression -- the harness of the reference's ``examples/torch/pytorch_synthetic_benchmark.py``
+(batch 32 per GPU, fixed fake data 3x224x224), bf16 compute, for the three codecs BASELINE.json's
+metric names: TopK 1 % + ResidualMemory + Allgather (the headline ``value``), QSGD + Allgather and
+PowerSGD rank 4 + PowerSGDMemory + Allreduce (``sub_results``).
 
-  python bench.py --gpus N --steps K --warmup W                # this framework (fused engine)
+  python bench.py --gpus N --steps K --warmup W                # this framework: all three codecs
   python bench.py --impl reference --gpus N --steps K ...      # UNMODIFIED reference from baseline/_ref
+  python bench.py --compressor qsgd ...                        # one codec only
 
 For N > 1 launch through ``python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N``.
 Rank 0 prints ONE JSON line.  ``value`` is device-timed (CUDA events, max over ranks) with the
 batch resident on the GPU like the reference harness; ``e2e`` repeats the measurement with a
-per-step pinned-host -> device copy of the inputs and a device -> host read of the loss.
+per-step pinned-host -> device copy of the inputs and a device -> host read of the loss.  Our arm
+also reports how the gap to the reference decomposes (``decomposition``: the same engine run eagerly,
+and the graph fed synchronously like the reference loop) and, after every timed region, proves that
+what it timed was correct: all ranks hold bit-identical parameters (``replicas_identical``) and two
+exchanges of rank-dependent gradients at the model's real geometry match the generic
+torch.distributed implementation of the same triple (``matches_generic``) and are bit-identical on
+all ranks.  A failed check makes the process exit non-zero.
 """
 import argparse
+import gc
 import json
 import os
 import socket
@@ -22,6 +31,7 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+HEADLINE_CODECS = ["topk", "qsgd", "powersgd"]
 
 
 def parse():
@@ -34,7 +44,7 @@ def parse():
     ap.add_argument("--model", default="resnet50", help="torchvision model name, or bert-large / bert-base")
     ap.add_argument("--seq-len", type=int, default=128, help="BERT only")
     ap.add_argument("--batch-size", type=int, default=32, help="per GPU (reference harness default)")
-    ap.add_argument("--compressor", default="topk")
+    ap.add_argument("--compressor", default="all", help="'all' = topk (headline) + qsgd + powersgd sub-results; or a comma list")
     ap.add_argument("--memory", default=None)
     ap.add_argument("--communicator", default=None)
     ap.add_argument("--compress-ratio", type=float, default=0.01)
@@ -42,6 +52,11 @@ def parse():
     ap.add_argument("--compress-rank", type=int, default=4)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="ours: run the step eagerly instead of as one CUDA graph")
+    ap.add_argument("--no-check", action="store_true", help="ours: skip the replica / generic-path correctness checks")
+    ap.add_argument("--no-decomposition", action="store_true", help="ours: skip the eager and synchronous-feed timings")
+    ap.add_argument("--api", default="torch", choices=["torch", "dist"],
+                    help="ours: torch = DistributedOptimizer (hooks, overlap); dist = the reference's manual loop shape "
+                         "through grace_b200.dist (bucketed step_all)")
     ap.add_argument("--memory-format", default="auto", choices=["auto", "channels_last", "contiguous"])
     return ap.parse_args()
 
@@ -87,15 +102,14 @@ class ClockSampler:
                 "power_w_max": max(float(r[2]) for r in rows), "reasons": reasons}
 
 
-def triple(args):
-    comp = args.compressor
+def triple(args, comp):
     mem = args.memory or {"topk": "residual", "qsgd": "none", "powersgd": "powersgd", "efsignsgd": "efsignsgd",
                           "dgc": "dgc", "none": "none"}.get(comp, "residual")
     comm = args.communicator or ("allreduce" if comp in ("powersgd", "none", "fp16") else "allgather")
     return comp, mem, comm
 
 
-def build_model(args, device):
+def build_model(args, comp, device):
     import torch
     torch.manual_seed(0)
     if args.model.startswith("bert"):
@@ -104,72 +118,61 @@ def build_model(args, device):
         large = args.model == "bert-large"
         cfg = BertConfig(hidden_size=1024 if large else 768, num_hidden_layers=24 if large else 12,
                          num_attention_heads=16 if large else 12, intermediate_size=4096 if large else 3072)
-        args.memory_format = "contiguous"
-        return BertForPreTraining(cfg).to(device)
+        return BertForPreTraining(cfg).to(device), "contiguous"
     import torchvision
     model = getattr(torchvision.models, args.model)().to(device)
     fmt = args.memory_format
     if fmt == "auto":
         # the reference's PowerSGD does tensor.view(shape[0], -1) (compressor/powersgd.py:35), which
         # cannot take channels_last gradients; every other configuration runs channels_last
-        fmt = "contiguous" if (args.impl == "reference" and args.compressor == "powersgd") else "channels_last"
-    args.memory_format = fmt
+        fmt = "contiguous" if (args.impl == "reference" and comp == "powersgd") else "channels_last"
     if fmt == "channels_last":
         model = model.to(memory_format=torch.channels_last)
-    return model
+    return model, fmt
 
 
-def main():
-    args = parse()
-    comp, mem, comm = triple(args)
-    if args.impl == "reference":
-        ref_root = os.path.join(ROOT, "baseline", "_ref")
-        if not os.path.isdir(os.path.join(ref_root, "grace_dl", "dist")):
-            print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref/grace_dl/dist missing: run baseline/install_reference.sh"}))
-            return 0
-        sys.path.insert(0, ref_root)          # the reference's grace_dl must shadow this repo's import shim
-    else:
-        sys.path.insert(0, ROOT)
+def param_digest(tensors):
+    """Two 64-bit checksums of the bit patterns of a list of tensors (order-sensitive), as a device tensor."""
+    import torch
+    acc = torch.zeros(2, dtype=torch.int64, device=tensors[0].device)
+    for i, t in enumerate(tensors):
+        bits = t.detach().contiguous().view(-1)
+        bits = bits.view(torch.int32) if bits.element_size() == 4 else bits.view(torch.int16).to(torch.int32)
+        b64 = bits.to(torch.int64)
+        acc[0] += b64.sum() * (2 * i + 1)
+        acc[1] += (b64 * (torch.arange(b64.numel(), device=b64.device) % 8191 + 1)).sum()
+    return acc
 
-    # keep the real stdout for the single JSON line: libraries (NCCL's version banner, torchrun
-    # notices) write to fd 1, so everything else is diverted to stderr
-    sys.stdout.flush()
-    real_stdout = os.fdopen(os.dup(1), "w")
-    os.dup2(2, 1)
 
+def same_on_all_ranks(digest, world):
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return True
+    got = [torch.zeros_like(digest) for _ in range(world)]
+    dist.all_gather(got, digest)
+    return all(bool(torch.equal(g, got[0])) for g in got)
+
+
+def run_codec(args, comp_name, env):
+    """Build the model + optimizer for one (compressor, memory, communicator) triple, time it, check it."""
     import torch
     import torch.distributed as dist
     import torch.nn.functional as F
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus and world > 1:
-        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
-    if args.gpus > 1 and world == 1:
-        # convenience: re-launch ourselves under torchrun
-        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
-               "--master-addr", "127.0.0.1", "--master-port", str(free_port()), os.path.abspath(__file__)] + sys.argv[1:]
-        return subprocess.call(cmd, stdout=real_stdout)
-    torch.cuda.set_device(local_rank)
-    device = torch.device("cuda", local_rank)
-    if world > 1 or args.impl == "reference":
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("MASTER_PORT", str(free_port()))
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
-
-    torch.backends.cudnn.benchmark = True
-    model = build_model(args, device)
+    world, rank, local_rank, device = env["world"], env["rank"], env["local_rank"], env["device"]
+    comp, mem, comm = triple(args, comp_name)
+    model, memory_format = build_model(args, comp, device)
     base_opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.9)
     n_params = sum(p.numel() for p in model.parameters())
+    gparams = {"compressor": comp, "memory": mem, "communicator": comm, "compress_ratio": args.compress_ratio,
+               "quantum_num": args.quantum_num, "compress_rank": args.compress_rank, "world_size": world}
 
-    fused = None
-    if args.impl == "ours":
+    fused, opt, hvd, dist_grc = None, None, None, None
+    if args.impl == "ours" and args.api == "torch":
         import grace_b200.torch as hvd
         hvd.broadcast_parameters(model.state_dict(), root_rank=0)
-        grc = hvd.grace_from_params({"compressor": comp, "memory": mem, "communicator": comm,
-                                     "compress_ratio": args.compress_ratio, "quantum_num": args.quantum_num,
-                                     "compress_rank": args.compress_rank, "world_size": world})
+        grc = hvd.grace_from_params(gparams)
         opt = hvd.DistributedOptimizer(base_opt, grc, named_parameters=model.named_parameters(), fused="auto")
         fused = opt._fused
 
@@ -178,6 +181,22 @@ def main():
 
         def zero():
             opt.zero_grad()
+    elif args.impl == "ours":
+        # the reference's integration for the torch.distributed flavour is a manual loop over the parameters
+        # (examples/dist/CIFAR10-dawndist/core.py:202-208); grace_b200.dist offers the same call per tensor
+        # and, used here, the bucketed form of that loop: one step_all over (name, grad) pairs
+        import grace_b200.torch as hvd
+        from grace_b200.dist import grace_from_params as dist_from_params
+        hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+        dist_grc = dist_from_params(gparams)
+        named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+
+        def exchange_and_step():
+            dist_grc.step_all([(n, p.grad) for n, p in named], inplace=True)
+            base_opt.step()
+
+        def zero():
+            base_opt.zero_grad(set_to_none=False)
     elif args.impl == "ddp":
         # library baseline: uncompressed gradients through torch DDP + NCCL all-reduce
         if world > 1:
@@ -199,9 +218,7 @@ def main():
         if world > 1:
             for p in model.parameters():
                 dist.broadcast(p.data, 0)
-        params = {"compressor": comp, "memory": mem, "communicator": comm, "compress_ratio": args.compress_ratio,
-                  "quantum_num": args.quantum_num, "compress_rank": args.compress_rank, "world_size": world}
-        grc = grace_from_params(params)
+        grc = grace_from_params(dict(gparams))
         if comp == "powersgd":       # the dist helper drops rank/world_size: set what it forgot
             grc.compressor.rank, grc.compressor.world_size = args.compress_rank, world
         named = list(model.named_parameters())
@@ -217,7 +234,7 @@ def main():
 
     bs = args.batch_size
     is_bert = args.model.startswith("bert")
-    mf = torch.channels_last if args.memory_format == "channels_last" else torch.contiguous_format
+    mf = torch.channels_last if memory_format == "channels_last" else torch.contiguous_format
     if is_bert:
         S = args.seq_len
         host_x = torch.randint(0, 30522, (bs, S)).pin_memory()                  # token ids (also the MLM labels)
@@ -232,7 +249,7 @@ def main():
     dev_x = to_dev(host_x)
     dev_y = host_y.to(device, non_blocking=True)
 
-    def step(x, y):
+    def eager_step(x, y):
         zero()
         with torch.autocast("cuda", dtype=torch.bfloat16):
             if is_bert:
@@ -243,9 +260,10 @@ def main():
         exchange_and_step()
         return loss
 
+    step = eager_step
     # ours: the whole step (forward, backward, fused exchange, optimizer) as ONE CUDA graph
     graphed, graph_note = None, "eager"
-    if args.impl == "ours" and not args.no_graph:
+    if args.impl == "ours" and opt is not None and not args.no_graph:
         try:
             def loss_fn(m, x, y):
                 return m(input_ids=x, labels=x, next_sentence_label=y).loss if is_bert else F.cross_entropy(m(x), y)
@@ -256,23 +274,21 @@ def main():
             graphed, graph_note = None, "eager (graph capture failed: %r)" % (exc,)
             torch.cuda.synchronize()
 
-    if graphed is not None:
-        eager_step = step
+    def quick(fn, n=5):
+        for _ in range(3):                            # re-warm (allocator pools differ between the two modes)
+            fn(dev_x, dev_y)
+        torch.cuda.synchronize()
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(n):
+            fn(dev_x, dev_y)
+        b_.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b_) / n
 
+    if graphed is not None:
         def graph_step(x, y):
             return graphed(x, y)
-
-        def quick(fn, n=5):
-            for _ in range(3):                        # re-warm (allocator pools differ between the two modes)
-                fn(dev_x, dev_y)
-            torch.cuda.synchronize()
-            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            for _ in range(n):
-                fn(dev_x, dev_y)
-            b_.record()
-            torch.cuda.synchronize()
-            return a.elapsed_time(b_) / n
         # keep whichever execution mode is faster for this model (all ranks must agree)
         t_graph, t_eager = quick(graph_step), quick(eager_step)
         pick = torch.tensor([1.0 if t_graph <= t_eager else 0.0], device=device)
@@ -290,27 +306,38 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(n, e2e):
+    def native_launch_count():
+        if fused is not None:
+            return fused.launches()
+        if dist_grc is not None and getattr(dist_grc, "_stepper", None) is not None:
+            return dist_grc._stepper.launches()
+        return 0
+
+    def timed(n, mode, fn=None):
+        """mode: 'device' (batch resident on the GPU), 'pipelined' (our host-feeding API), 'sync' (copy, step,
+        loss.item() per step -- the loop shape of the reference examples)."""
+        fn = fn or step
+        use_graph = graphed is not None and fn is step
         barrier()
-        launches0 = fused.launches() if fused is not None else 0
+        launches0 = native_launch_count()
         start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.time()
         start.record()
         last = None
-        if e2e and args.impl == "ours":
+        if mode == "pipelined":
             # The repo's host-feeding API (grace_b200.torch.GraphedStep.feed/run, PinnedPrefetcher, read_back):
             # every step's inputs are copied from pinned host memory inside the timed region -- on a copy stream,
             # overlapping the step in flight -- and every step's loss is read back on the host (one step late,
             # so the read never stalls the next launch).  n copies in, n losses out for n steps.
             feeder = None
-            if graphed is not None:
+            if use_graph:
                 graphed.feed(host_x, host_y)
             else:
                 feeder = hvd.PinnedPrefetcher([host_x, host_y])
                 feeder.feed(host_x, host_y)
             prev = None
             for i in range(n):
-                if graphed is not None:
+                if use_graph:
                     pend = graphed.run()
                     if i + 1 < n:
                         graphed.feed(host_x, host_y)
@@ -318,7 +345,7 @@ def main():
                     x, y = feeder.get()
                     if not is_bert:
                         x = x.contiguous(memory_format=mf)
-                    loss = step(x, y)
+                    loss = fn(x, y)
                     feeder.release()
                     pend = hvd.read_back(loss.detach())
                     if i + 1 < n:
@@ -327,14 +354,14 @@ def main():
                     last = prev.item()                     # device -> host read of step i-1's loss
                 prev = pend
             last = prev.item()
+        elif mode == "sync":
+            for _ in range(n):
+                x = to_dev(host_x)
+                y = host_y.to(device, non_blocking=True)
+                last = fn(x, y).item()                     # device -> host read of the step's result
         else:
             for _ in range(n):
-                if e2e:                                    # reference arm: the reference examples' own loop shape
-                    x = to_dev(host_x)
-                    y = host_y.to(device, non_blocking=True)
-                    last = step(x, y).item()               # device -> host read of the step's result
-                else:
-                    last = step(dev_x, dev_y)
+                last = fn(dev_x, dev_y)
         stop.record()
         barrier()
         t1 = time.time()
@@ -343,55 +370,202 @@ def main():
             t = torch.tensor([ms], device=device)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t)
-        launches = (fused.launches() - launches0) if fused is not None else 0
-        if graphed is not None:                       # replays do not pass through the host-side counter
+        launches = native_launch_count() - launches0
+        if use_graph:                                  # replays do not pass through the host-side counter
             launches = graphed.native_launches_per_step * n
         return ms, launches, (t0, t1), last
+
+    def throughput(ms, n):
+        return world * bs * units_per_sample * n / (ms / 1e3)
 
     for _ in range(max(args.warmup, 3)):
         step(dev_x, dev_y)
     sampler = ClockSampler(torch.cuda.current_device()) if rank == 0 else None
-    ms, launches, window, _ = timed(args.steps, e2e=False)
+    ms, launches, window, _ = timed(args.steps, "device")
     clocks = sampler.stop(*window) if sampler else None
     e2e = None
     if not args.no_e2e:
         step(dev_x, dev_y)
-        ems, _, _, last = timed(args.steps, e2e=True)
-        e2e = {"value": world * bs * units_per_sample * args.steps / (ems / 1e3), "unit": unit, "ms_per_step": ems / args.steps,
+        e2e_mode = "pipelined" if args.impl == "ours" else "sync"
+        ems, _, _, last = timed(args.steps, e2e_mode)
+        e2e = {"value": throughput(ems, args.steps), "unit": unit, "ms_per_step": ems / args.steps,
                "h2d_bytes_per_step": host_x.numel() * host_x.element_size() + host_y.numel() * 8, "d2h_bytes_per_step": 4,
                "last_loss": last,
                "feeding": ("pipelined through GraphedStep.feed/run / PinnedPrefetcher: each step's pinned-host -> device copy "
                            "is issued inside the timed region on a copy stream (overlapping the previous step), each step's "
                            "loss is read on the host one step late") if args.impl == "ours" else
                           "synchronous per step (copy, step, loss.item()) like the reference examples"}
-    if fused is not None:
-        fused.engine.check_status()
 
-    if rank == 0:
-        value = world * bs * units_per_sample * args.steps / (ms / 1e3)
-        out = {
-            "metric": "%s synthetic training throughput with %s gradient compression"
-                      % ("ResNet-50" if args.model == "resnet50" else args.model, comp),
-            "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic (fixed random batch, random-init weights)", "impl": args.impl,
-            "config": {"model": args.model, "global_batch": world * bs, "per_gpu_batch": bs, "seq_len": args.seq_len if is_bert else None,
-                       "image": None if is_bert else "3x224x224", "parallelism": "dp%d" % world, "compressor": comp, "memory": mem,
-                       "communicator": comm, "compress_ratio": args.compress_ratio, "params": n_params,
-                       "grad_dtype": "fp32 master gradients, bf16 autocast compute", "memory_format": args.memory_format,
-                       "optimizer": "SGD momentum 0.9 (inside the timed region)",
-                       "l2": "per-step working set (activations, >1 GB) exceeds the 126 MB L2; no explicit flush"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
-        }
+    # how the gap to the reference arm decomposes: same engine without the graph, and the graph fed like the reference loop
+    decomposition = None
+    if args.impl == "ours" and not args.no_decomposition:
+        decomposition = {}
+        if graphed is not None:
+            for _ in range(3):
+                eager_step(dev_x, dev_y)
+            dms, _, _, _ = timed(args.steps, "device", fn=eager_step)
+            decomposition["eager"] = {"value": throughput(dms, args.steps), "ms_per_step": dms / args.steps,
+                                      "what": "same fused engine and overlap, step issued eagerly (no CUDA graph), batch resident"}
+            for _ in range(3):
+                step(dev_x, dev_y)
+        if not args.no_e2e:
+            sms, _, _, _ = timed(args.steps, "sync")
+            decomposition["sync_feed"] = {"value": throughput(sms, args.steps), "ms_per_step": sms / args.steps,
+                                          "what": "e2e with the reference loop shape: blocking copy, step, loss.item() every step"}
+
+    checks = None
+    if args.impl == "ours" and not args.no_check:
+        torch.cuda.synchronize()
         if fused is not None:
-            out["config"]["buckets"] = len(fused.buckets)
-            out["config"]["transport"] = fused.transport
-            out["config"]["execution"] = graph_note
-            out["config"]["wire_bytes_per_peer_per_step"] = fused.wire_bytes()
+            fused.engine.check_status()
+        checks = {"replicas_identical": same_on_all_ranks(param_digest(list(model.parameters())), world)}
+
+    result = {
+        "metric": "%s synthetic training throughput with %s gradient compression"
+                  % ("ResNet-50" if args.model == "resnet50" else args.model, comp),
+        "value": throughput(ms, args.steps), "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic (fixed random batch, random-init weights)", "impl": args.impl,
+        "config": {"model": args.model, "global_batch": world * bs, "per_gpu_batch": bs, "seq_len": args.seq_len if is_bert else None,
+                   "image": None if is_bert else "3x224x224", "parallelism": "dp%d" % world, "compressor": comp, "memory": mem,
+                   "communicator": comm, "compress_ratio": args.compress_ratio, "quantum_num": args.quantum_num,
+                   "compress_rank": args.compress_rank, "params": n_params,
+                   "grad_dtype": "fp32 master gradients, bf16 autocast compute", "memory_format": memory_format,
+                   "optimizer": "SGD momentum 0.9 (inside the timed region)",
+                   "l2": "per-step working set (activations, >1 GB) exceeds the 126 MB L2; no explicit flush"},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+    }
+    if args.impl == "ours":
+        result["config"]["api"] = args.api
+        result["config"]["execution"] = graph_note
+        if fused is not None:
+            result["config"]["buckets"] = len(fused.buckets)
+            result["config"]["transport"] = fused.transport
+            result["config"]["wire_bytes_per_peer_per_step"] = fused.wire_bytes()
+        if decomposition is not None:
+            result["decomposition"] = decomposition
+
+    # ---- tear down, then (ours) two exchanges at the model's geometry against the generic implementation
+    shapes = [(n, tuple(p.shape)) for n, p in model.named_parameters() if p.requires_grad]
+    graphed = step = eager_step = None
+    if opt is not None:
+        opt.close()
+    if dist_grc is not None and hasattr(dist_grc, "close"):
+        dist_grc.close()
+    opt = fused = dist_grc = model = base_opt = exchange_and_step = zero = None
+    gc.collect()
+    torch.cuda.empty_cache()
+    if checks is not None:
+        checks.update(exchange_check(gparams, shapes, memory_format, env))
+        result.update(checks)
+        result["checks_ok"] = bool(checks["replicas_identical"] and checks["matches_generic"]
+                                   and checks["exchange_identical_on_all_ranks"])
+    gc.collect()
+    torch.cuda.empty_cache()
+    return result
+
+
+def exchange_check(gparams, shapes, memory_format, env):
+    """Two exchanges of rank-dependent random gradients with the model's tensor shapes: the bucketed native path
+    (step_all) against the generic torch.distributed implementation of the same triple, and across ranks.
+    PowerSGD is checked on contiguous gradients: its random projection is defined on view(shape[0], -1), so both
+    implementations must see the same matrix."""
+    import torch
+    from grace_b200.dist import grace_from_params
+    world, rank = env["world"], env["rank"]
+    fast, slow = grace_from_params(dict(gparams)), grace_from_params(dict(gparams))
+    slow.fused = False
+    gen = torch.Generator(device="cuda").manual_seed(4242 + rank)
+    corrupt = os.environ.get("GRACE_B200_BENCH_CORRUPT")            # self-test of the checker: see BASELINE.md
+    num = den = 0.0
+    identical = True
+    channels_last = memory_format == "channels_last" and gparams["compressor"] != "powersgd"
+    for it in range(2):
+        grads = []
+        for name, shape in shapes:
+            g = torch.randn(shape, device="cuda", generator=gen) * 0.01
+            if len(shape) == 4 and channels_last:
+                g = g.contiguous(memory_format=torch.channels_last)
+            grads.append((name, g))
+        outs = fast.step_all([(n, g.clone()) for n, g in grads])
+        if corrupt is not None and rank == int(corrupt) % world:
+            outs[0].view(-1)[0] += 1.0
+        identical = identical and same_on_all_ranks(param_digest(outs), world)
+        for (name, g), a in zip(grads, outs):
+            b = slow.step(g.clone(), name)
+            num += float((a.float() - b.float()).pow(2).sum())
+            den += float(b.float().pow(2).sum())
+    rel = (num / max(den, 1e-30)) ** 0.5
+    tol = {"topk": 1e-6, "qsgd": 5e-3, "powersgd": 3e-2}.get(gparams["compressor"], 5e-3)
+    native = getattr(fast, "_stepper", None) is not None and bool(fast._stepper.enabled)
+    if hasattr(fast, "close"):
+        fast.close()
+    t = torch.tensor([rel], device="cuda")
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return {"matches_generic": bool(float(t) <= tol) and native, "generic_rel_err": float(t), "generic_tol": tol,
+            "exchange_identical_on_all_ranks": identical, "exchange_check_native": native}
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        ref_root = os.path.join(ROOT, "baseline", "_ref")
+        if not os.path.isdir(os.path.join(ref_root, "grace_dl", "dist")):
+            print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref/grace_dl/dist missing: run baseline/install_reference.sh"}))
+            return 0
+        sys.path.insert(0, ref_root)          # the reference's grace_dl must shadow this repo's import shim
+    else:
+        sys.path.insert(0, ROOT)
+
+    # keep the real stdout for the single JSON line: libraries (NCCL's version banner, torchrun
+    # notices) write to fd 1, so everything else is diverted to stderr
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
+    if args.gpus > 1 and world == 1:
+        # convenience: re-launch ourselves under torchrun
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", str(free_port()), os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd, stdout=real_stdout)
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1 or args.impl == "reference":
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", str(free_port()))
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+    torch.backends.cudnn.benchmark = True
+    env = {"world": world, "rank": rank, "local_rank": local_rank, "device": device}
+
+    if args.compressor == "all":
+        codecs = HEADLINE_CODECS if not args.model.startswith("bert") else ["qsgd", "efsignsgd"]
+    else:
+        codecs = [c for c in args.compressor.split(",") if c]
+    results = [run_codec(args, c, env) for c in codecs]
+    out = results[0]
+    if len(results) > 1:
+        out["sub_results"] = {r["config"]["compressor"]: r for r in results[1:]}
+    ok = all(r.get("checks_ok", True) for r in results)
+    if rank == 0:
         real_stdout.write(json.dumps(out) + "\n")
         real_stdout.flush()
     if dist.is_initialized():
         dist.destroy_process_group()
+    if not ok:
+        sys.stderr.write("bench.py: correctness check FAILED: %s\n" % json.dumps(
+            {r["config"]["compressor"]: {k: r.get(k) for k in ("replicas_identical", "matches_generic", "generic_rel_err",
+                                                                "exchange_identical_on_all_ranks")} for r in results}))
+        return 3
     return 0
 
 
