@@ -43,11 +43,12 @@ def _split(plan, buf):
     return [buf[off:off + n].clone() for off, n in zip(plan.offsets, plan.numels)]
 
 
-def run_fused(world, params, grads_per_step):
+def run_fused(world, params, grads_per_step, sizes=None, names=None, arena_bytes=None):
     """grads_per_step[step][rank] = list of tensors -> outs[step][rank] = list of tensors."""
     from grace_b200.parallel.engine import Engine
-    engines = Engine.local(world)
-    plans = [e.plan(SIZES, NAMES, params) for e in engines]
+    sizes, names = sizes or SIZES, names or NAMES
+    engines = Engine.local(world, arena_bytes=arena_bytes)
+    plans = [e.plan(sizes, names, params) for e in engines]
     outs = []
     try:
         for grads in grads_per_step:
@@ -73,13 +74,14 @@ def run_fused(world, params, grads_per_step):
     return outs, states
 
 
-def run_oracle(world, make_comp, make_mem, grads_per_step):
+def run_oracle(world, make_comp, make_mem, grads_per_step, names=None):
+    names = names or NAMES
     comps = [make_comp() for _ in range(world)]
     mems = [make_mem() for _ in range(world)]
     outs = []
     for grads in grads_per_step:
-        step_out = [[None] * len(SIZES) for _ in range(world)]
-        for i, name in enumerate(NAMES):
+        step_out = [[None] * len(names) for _ in range(world)]
+        for i, name in enumerate(names):
             payloads, ctxs = [], []
             for r in range(world):
                 x = mems[r].compensate(grads[r][i], name)
@@ -95,9 +97,9 @@ def run_oracle(world, make_comp, make_mem, grads_per_step):
     return outs, comps, mems
 
 
-def make_grads(world, steps, scale=1.0, seed=0):
+def make_grads(world, steps, scale=1.0, seed=0, sizes=None):
     g = torch.Generator(device="cuda").manual_seed(seed)
-    return [[[torch.randn(n, device="cuda", generator=g) * scale * (1 + 0.3 * r) for n in SIZES]
+    return [[[torch.randn(n, device="cuda", generator=g) * scale * (1 + 0.3 * r) for n in (sizes or SIZES)]
              for r in range(world)] for _ in range(steps)]
 
 
@@ -371,13 +373,13 @@ def test_variable_size_payload_overflow_is_reported():
 
 
 def test_failed_plan_creation_is_clean():
-    """A plan that does not fit the peer arena is refused with a message and released; the engine keeps working."""
+    """A plan that cannot be built is refused with a message and released; the engine keeps working."""
     from grace_b200.ops.native import NativeError
     from grace_b200.parallel.engine import Engine
     (e,) = Engine.local(1, arena_bytes=8 << 20)
     try:
-        with pytest.raises(NativeError, match="arena"):
-            e.plan([8 << 20], ["huge.weight"], _params("qsgd"))          # needs 2 x 8 MB of slots + headers
+        with pytest.raises(NativeError, match="elements"):
+            e.plan([100, 1 << 31], ["ok.weight", "huge.weight"], _params("qsgd"))      # refused inside the builder
         p = e.plan(SIZES, NAMES, _params("qsgd"))
         buf = torch.randn(p.padded, device="cuda")
         out = torch.empty(p.padded, device="cuda")
@@ -385,6 +387,106 @@ def test_failed_plan_creation_is_clean():
         torch.cuda.synchronize()
         e.check_status()
         assert float((out[:1000] - buf[:1000]).abs().max()) < 0.6        # one QSGD quantum = norm / 64 ~ 0.5
+    finally:
+        e.destroy()
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_arena_grows_when_a_plan_does_not_fit(world):
+    """The peer arena is no longer sized by the first caller: a plan whose slots do not fit makes every (virtual)
+    rank add a region, and exchanges through the new region give the same result as the oracle."""
+    from grace_b200.ops import native
+    sizes, names = [3 << 20, 1000], ["huge.weight", "small.bias"]
+    grads = make_grads(world, 2, scale=0.02, sizes=sizes)
+    prm = _params("signsgd", "none", average=0)
+    from grace_b200.parallel.engine import Engine
+    engines = Engine.local(world, arena_bytes=2 << 20)          # flags + < 2 MB of slots
+    try:
+        small = [e.plan(SIZES, NAMES, prm) for e in engines]     # fits region 0
+        big = [e.plan(sizes, names, _params("fp16", "none")) for e in engines]      # several MB of slots: needs a new region
+        assert all(native.lib().gb_comm_regions(e._h) >= 2 for e in engines)
+        for step in grads:
+            bufs = [_flat(big[r], step[r]) for r in range(world)]
+            for r in range(world):
+                big[r].send(bufs[r])
+            for r in range(world):
+                big[r].mid()
+            outs = []
+            for r in range(world):
+                out = torch.full((big[r].padded,), float("nan"), device="cuda")
+                big[r].recv(out)
+                outs.append(out)
+            torch.cuda.synchronize()
+            for e in engines:
+                e.check_status()
+            for r in range(1, world):
+                assert torch.equal(outs[0][:sizes[0]], outs[r][:sizes[0]])
+            want = sum(step[r][0] for r in range(world)) / world
+            assert float((outs[0][:sizes[0]] - want).abs().max()) < 1e-4          # fp16 rounding of |x| < 0.2
+        # the plan created before the growth still works
+        g2 = make_grads(world, 1)
+        bufs = [_flat(small[r], g2[0][r]) for r in range(world)]
+        for r in range(world):
+            small[r].send(bufs[r])
+        for r in range(world):
+            out = torch.empty(small[r].padded, device="cuda")
+            small[r].recv(out)
+        torch.cuda.synchronize()
+        for e in engines:
+            e.check_status()
+    finally:
+        for e in engines:
+            e.destroy()
+
+
+def _resnet50_shapes():
+    import torchvision
+    m = torchvision.models.resnet50()
+    return [(n, tuple(p.shape)) for n, p in m.named_parameters()]
+
+
+@pytest.mark.parametrize("codec", ["topk", "qsgd", "signsgd"])
+def test_resnet50_geometry(codec):
+    """One plan over the 161 gradient tensors of ResNet-50 (25.6 M elements, 64 ... 2.4 M per tensor, 6 300 tiles) on two
+    virtual ranks against the per-tensor torch oracle: the shapes the headline benchmark runs, not toy segments."""
+    shapes = _resnet50_shapes()
+    names = [n for n, _ in shapes]
+    sizes = [int(torch.Size(s).numel()) for _, s in shapes]
+    assert len(sizes) == 161
+    world = 2
+    grads = make_grads(world, 2, scale=0.02, sizes=sizes, seed=11)
+    if codec == "topk":
+        prm, mk_c, mk_m, exact, frac = _params("topk", "residual", ratio=0.01), (lambda: C.TopKCompressor(0.01)), M.ResidualMemory, True, 0.0
+    elif codec == "qsgd":
+        prm, mk_c, mk_m, exact, frac = _params("qsgd", "none"), (lambda: C.QSGDCompressor(64, seed=SEED)), M.NoneMemory, False, 0.002
+    else:
+        prm, mk_c, mk_m, exact, frac = _params("signsgd", "none", average=0), C.SignSGDCompressor, M.NoneMemory, True, 0.0
+    fused, _ = run_fused(world, prm, grads, sizes=sizes, names=names, arena_bytes=1 << 30)
+    oracle, _, _ = run_oracle(world, mk_c, mk_m, grads, names=names)
+    assert_same(fused, oracle, exact=exact, frac=frac, rtol=2e-5, atol=1e-7, what="resnet50/" + codec)
+
+
+def test_topk_tensor_larger_than_2_pow_27():
+    """Tile descriptors address tensors up to 2^31 elements (BASELINE config 5 goes to 1 B); 2^27 + 5 elements is the
+    first size whose tile index needs more than 15 bits."""
+    n = (1 << 27) + 5
+    from grace_b200.parallel.engine import Engine
+    (e,) = Engine.local(1, arena_bytes=64 << 20)
+    try:
+        ratio = 0.001
+        p = e.plan([n], ["giant.weight"], _params("topk", "none", ratio=ratio))
+        g = torch.randn(p.padded, device="cuda")
+        g[n:] = 0
+        out = torch.empty(p.padded, device="cuda")
+        p.send(g); p.recv(out)
+        torch.cuda.synchronize()
+        e.check_status()
+        k = max(1, int(n * ratio))
+        x = g[:n]
+        kth = torch.topk(x.abs(), k, sorted=True)[0][-1]
+        want = torch.where(x.abs() >= kth, x, torch.zeros_like(x))
+        assert int((want != 0).sum()) == k                   # no ties at the threshold for continuous data
+        assert torch.equal(out[:n], want)
     finally:
         e.destroy()
 
