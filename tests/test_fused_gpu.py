@@ -261,7 +261,7 @@ def test_smoke_entry():
 @pytest.mark.parametrize("params,tol", [
     (dict(compressor="topk", memory="residual", communicator="allgather", compress_ratio=0.01), 0.0),
     (dict(compressor="qsgd", memory="none", communicator="allgather", quantum_num=64), 2e-3),
-    (dict(compressor="powersgd", memory="powersgd", communicator="allreduce", compress_rank=4), 3e-2),
+    (dict(compressor="powersgd", memory="powersgd", communicator="allreduce", compress_rank=4), 5e-2),
     (dict(compressor="signsgd", memory="none", communicator="allgather"), 0.0),
 ])
 def test_step_all_matches_the_per_tensor_loop(params, tol):
