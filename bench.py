@@ -468,8 +468,8 @@ def run_codec(args, comp_name, env):
 def exchange_check(gparams, shapes, memory_format, env):
     """Two exchanges of rank-dependent random gradients with the model's tensor shapes: the bucketed native path
     (step_all) against the generic torch.distributed implementation of the same triple, and across ranks.
-    PowerSGD is checked on contiguous gradients: its random projection is defined on view(shape[0], -1), so both
-    implementations must see the same matrix."""
+    The stochastic codecs and PowerSGD are checked on contiguous gradients: their random streams / projections are
+    indexed by memory order (native) and by view(-1) order (generic), which coincide only for contiguous tensors."""
     import torch
     from grace_b200.dist import grace_from_params
     world, rank = env["world"], env["rank"]
@@ -479,7 +479,7 @@ def exchange_check(gparams, shapes, memory_format, env):
     corrupt = os.environ.get("GRACE_B200_BENCH_CORRUPT")            # self-test of the checker: see BASELINE.md
     num = den = 0.0
     identical = True
-    channels_last = memory_format == "channels_last" and gparams["compressor"] != "powersgd"
+    channels_last = memory_format == "channels_last" and gparams["compressor"] == "topk"
     for it in range(2):
         grads = []
         for name, shape in shapes:

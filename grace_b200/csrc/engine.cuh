@@ -94,5 +94,6 @@ struct gb_plan {
   int64_t launches;
   void* sketch;          // SketchML buffers (k2_sketch.cu)
   void* adaq;            // AdaQ buffers (k1_adaq.cu)
+  void* topk2;           // two-pass TopK buffers (k1_topk2.cu)
   uint32_t* d_samp;      // DGC: sampled magnitudes (k1_sparse.cu)
 };

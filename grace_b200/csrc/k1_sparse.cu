@@ -538,6 +538,7 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* wo
 
 // Receive: ordered merge of W sparse lists into the dense aggregate.
 
+template <bool EXTRAS>
 __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, float* out, float divisor, PeerPtrs peers,
                                                        int channel, const StepCtl* ctl, size_t par_stride, uint32_t* status,
                                                        uint64_t timeout_ns, int wait) {
@@ -554,6 +555,11 @@ __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, 
     int2 h[GB_MAX_WORLD];
 #pragma unroll
     for (int r = 0; r < GB_MAX_WORLD; ++r) h[r] = in.hdr[r < in.n ? r : 0][tile];
+    int2 xh[GB_MAX_WORLD];                           // TopK: second range of the tile (picks from the threshold bin)
+    if (EXTRAS) {
+#pragma unroll
+      for (int r = 0; r < GB_MAX_WORLD; ++r) xh[r] = in.hdr[r < in.n ? r : 0][t.ntiles + 1 + tile];
+    }
     float pv[GB_MAX_WORLD];
     int32_t pi[GB_MAX_WORLD];
 #pragma unroll
@@ -577,6 +583,14 @@ __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, 
         for (int i = threadIdx.x + GB_THREADS; i < h[r].y; i += GB_THREADS) {
           const int li = ix[i] - local0;
           if ((unsigned)li < (unsigned)GB_TILE) acc[li] += v[i];
+        }
+        if (EXTRAS) {                                  // indices are unique within a rank: no conflict with the range above
+          const float* xv = in.vals[r] + xh[r].x;
+          const int32_t* xi = in.idx[r] + xh[r].x;
+          for (int i = threadIdx.x; i < xh[r].y; i += GB_THREADS) {
+            const int li = xi[i] - local0;
+            if ((unsigned)li < (unsigned)GB_TILE) acc[li] += xv[i];
+          }
         }
         __syncthreads();
       }
@@ -685,6 +699,7 @@ static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 
 int k1_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   if (p->prm.codec == GB_CODEC_DGC) return k1_dgc_send(p, d_grad, st);
+  if (p->topk2) return tk_send(p, d_grad, st);
   gb_comm* c = p->comm;
   const bool mem = p->prm.memory == GB_MEM_RESIDUAL;
   // first call: the memory is empty, compensate() returns the gradient unchanged
@@ -755,7 +770,10 @@ int k1_recv(gb_plan* p, float* d_out, cudaStream_t st) {
     LAUNCHED(p);
     return 0;
   }
-  k1_merge<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns, 1);
+  if (p->prm.codec == GB_CODEC_TOPK)
+    k1_merge<true><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns, 1);
+  else
+    k1_merge<false><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns, 1);
   LAUNCHED(p);
   return 0;
 }

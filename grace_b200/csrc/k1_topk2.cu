@@ -1,0 +1,633 @@
+// K1-topk, two streaming passes.
+//
+// Replaces the reference chain  memory/residual.py:10-20 (compensate / update) + compressor/topk.py:6-18
+// (abs, topk, gather, zeros + scatter_) + communicator/allgather.py:8-45 per tensor by five launches per
+// BUCKET (all tensors of the bucket, per-tensor k and residual preserved):
+//
+//   tk_pass1   reads gradient + residual once, writes the compensated values, 11-bit histogram of |x| per tensor;
+//              the CTA that completes a tensor's last tile picks the bin that holds the k-th largest magnitude
+//              (no separate select launch); the last CTA of the grid advances the device-side step block.
+//   tk_pass2   reads the compensated values once: everything in a HIGHER bin is certain to be selected -> staged in
+//              shared memory and stored straight into every peer's payload slot, zeroed in place (new residual);
+//              elements IN the threshold bin (~1 % of the data) are only marked in a 4096-bit mask per tile and
+//              histogrammed by their next 10 bits; the CTA finishing a tensor extends the threshold prefix to 21 bits.
+//   tk_refine  one warp per tile walks the mask, histograms the last 10 bits of the few values matching the 21-bit
+//              prefix; the warp finishing a tensor fixes the exact 31-bit threshold and how many equal values to take.
+//   tk_ties    only for tensors where more values EQUAL the threshold than may be taken (common with bf16-valued
+//              gradients): per-tile tie counts + exclusive scan, so ties are taken in index order (lowest first).
+//   tk_finish  one warp per tile: the chosen threshold-bin elements go to the peers as a second (value, index) range
+//              of the tile, are zeroed in place; the last CTA releases the epoch flags.
+//
+// The big data is therefore streamed twice (pass 1: 2 reads + 1 write, pass 2: 1 read) instead of four times; the
+// three tail kernels touch the masks (0.125 B / element) and gather ~1 % of the values from L2.
+#include "kernels.cuh"
+
+#define TK_SEL 8
+enum { S_BIN = 0, S_KREM = 1, S_CURA = 2, S_FLAGS = 3, S_THR = 4, S_TAKE = 5 };
+#define TKF_TAKEALL 1u   // fewer non-zero candidates than still needed: every candidate is selected
+#define TKF_AMBIG 2u     // more values equal to the threshold than may be taken: ties go by index order
+#define TK_WPT 8         // warps (tiles) per CTA in the tail kernels
+
+struct TkDev {
+  uint32_t* hist0;    // [nseg][2048]
+  uint32_t* hist1;    // [nseg][1024]
+  uint32_t* hist2;    // [nseg][1024]
+  uint32_t* sel;      // [nseg][TK_SEL]
+  uint32_t* segdone;  // [nseg][4]   tiles finished per pass (last-done detection), self-resetting
+  uint32_t* mask;     // [ntiles][128]  bit e of a tile = element e lies in the tensor's threshold bin
+  int32_t* tiecnt;    // [ntiles]
+  uint32_t* done;     // [16] grid-wide last-block counters
+};
+
+struct TkHost {
+  TkDev d;
+  void* block;
+};
+
+__device__ __forceinline__ uint32_t tk_absbits(float v) { return __float_as_uint(v) & 0x7FFFFFFFu; }
+__device__ __forceinline__ float tk_comp(float beta, float r, float gamma, float g) {
+  return __fadd_rn(__fmul_rn(beta, r), __fmul_rn(gamma, g));     // two roundings, like torch's beta * e + gamma * g
+}
+__device__ __forceinline__ uint32_t ldcg_u32(const uint32_t* p) { return __ldcg(p); }
+
+// Block-wide search of the bin that holds the krem-th largest element: bins are walked from NB-1 downwards.
+// Every thread must call it.  Zeroes the histogram.  Returns false when the histogram holds fewer than krem entries.
+template <int NB>
+__device__ __forceinline__ bool cta_select(uint32_t* h, uint32_t krem, uint32_t& bin, uint32_t& rem, uint32_t& cnt) {
+  constexpr int PER = NB / GB_THREADS;
+  __shared__ uint32_t wsum[GB_THREADS / 32];
+  __shared__ uint32_t res[4];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int hi = NB - 1 - threadIdx.x * PER;
+  uint32_t c[PER];
+  uint32_t mine = 0;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) { c[i] = ldcg_u32(h + hi - i); mine += c[i]; }
+#pragma unroll
+  for (int i = 0; i < PER; ++i) if (c[i]) h[hi - i] = 0;
+  uint32_t inc = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += n;
+  }
+  if (threadIdx.x == 0) res[3] = 0;
+  if (lane == 31) wsum[wid] = inc;
+  __syncthreads();
+  uint32_t before = 0;
+  for (int w = 0; w < wid; ++w) before += wsum[w];
+  uint32_t running = before + inc - mine;                    // elements in strictly higher bins
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    if (running < krem && running + c[i] >= krem) { res[0] = (uint32_t)(hi - i); res[1] = krem - running; res[2] = c[i]; res[3] = 1; }
+    running += c[i];
+  }
+  __syncthreads();
+  bin = res[0]; rem = res[1]; cnt = res[2];
+  const bool found = res[3] != 0;
+  __syncthreads();
+  return found;
+}
+
+// the same for one warp and 1024 bins (32 per lane)
+__device__ __forceinline__ bool warp_select1024(uint32_t* h, uint32_t krem, uint32_t& bin, uint32_t& rem, uint32_t& cnt) {
+  const int lane = threadIdx.x & 31;
+  const int hi = 1023 - lane * 32;
+  uint32_t mine = 0;
+  for (int i = 0; i < 32; ++i) mine += ldcg_u32(h + hi - i);
+  uint32_t inc = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += n;
+  }
+  uint32_t running = inc - mine;
+  uint32_t fb = 0, fr = 0, fc = 0;
+  bool found = false;
+  if (running < krem && running + mine >= krem) {
+    for (int i = 0; i < 32; ++i) {
+      const uint32_t c = ldcg_u32(h + hi - i);
+      if (!found && running < krem && running + c >= krem) { fb = (uint32_t)(hi - i); fr = krem - running; fc = c; found = true; }
+      running += c;
+    }
+  }
+  for (int i = 0; i < 32; ++i) h[hi - i] = 0;
+  const uint32_t who = __ballot_sync(0xffffffffu, found);
+  if (!who) return false;
+  const int src = __ffs(who) - 1;
+  bin = __shfl_sync(0xffffffffu, fb, src);
+  rem = __shfl_sync(0xffffffffu, fr, src);
+  cnt = __shfl_sync(0xffffffffu, fc, src);
+  return true;
+}
+
+// ---------------------------------------------------------------- pass 1
+template <bool WRITE>
+__global__ void __launch_bounds__(GB_THREADS, 4) tk_pass1(SegTable t, const float* __restrict__ grad, float* work, float beta,
+                                                       float gamma, TkDev d, StepCtl* ctl) {
+  __shared__ uint32_t sh[2048];
+  __shared__ int s_last;
+  if (WRITE && ctl->next_step == 0) { beta = 0.f; gamma = 1.f; }   // empty memory: compensate() is the identity
+  const int t0 = (int)((int64_t)blockIdx.x * t.ntiles / gridDim.x);          // even split: the grid is a multiple of the SM count
+  const int t1 = (int)((int64_t)(blockIdx.x + 1) * t.ntiles / gridDim.x);
+  for (int b = threadIdx.x; b < 2048; b += GB_THREADS) sh[b] = 0;
+  __syncthreads();
+  int cur = t0 < t1 ? t.tile_seg[t0] : -1;
+  int mine = 0;                                   // tiles of `cur` done by this CTA
+  auto close_segment = [&]() {
+    __syncthreads();
+    uint32_t* hg = d.hist0 + (size_t)cur * 2048;
+    for (int b = threadIdx.x; b < 2048; b += GB_THREADS) {
+      const uint32_t c = sh[b];
+      if (c) atomicAdd(hg + b, c);
+      sh[b] = 0;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint32_t total = (uint32_t)(t.seg_tile0[cur + 1] - t.seg_tile0[cur]);
+      const uint32_t old = atomicAdd(d.segdone + cur * 4, (uint32_t)mine);
+      s_last = (old + (uint32_t)mine == total);
+    }
+    __syncthreads();
+    if (s_last) {                                  // this CTA finished the tensor: choose its threshold bin
+      __threadfence();
+      uint32_t bin, rem, cnt;
+      cta_select<2048>(hg, (uint32_t)t.seg_k[cur], bin, rem, cnt);      // always found: the histogram holds numel >= k
+      if (threadIdx.x == 0) {
+        uint32_t* s = d.sel + cur * TK_SEL;
+        s[S_BIN] = bin; s[S_KREM] = rem; s[S_CURA] = 0; s[S_FLAGS] = 0; s[S_THR] = 0; s[S_TAKE] = 0;
+        d.segdone[cur * 4] = 0;
+      }
+    }
+    mine = 0;
+  };
+  for (int tile = t0; tile < t1; ++tile) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    if (seg != cur) { close_segment(); cur = seg; }
+    ++mine;
+    float4 vv4[4];
+    if (len == GB_TILE) {
+      if (WRITE) {
+        float4 rr4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+          vv4[j] = ld_stream_f4(grad + base + e0);
+          rr4[j] = *reinterpret_cast<const float4*>(work + base + e0);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+          vv4[j].x = tk_comp(beta, rr4[j].x, gamma, vv4[j].x);
+          vv4[j].y = tk_comp(beta, rr4[j].y, gamma, vv4[j].y);
+          vv4[j].z = tk_comp(beta, rr4[j].z, gamma, vv4[j].z);
+          vv4[j].w = tk_comp(beta, rr4[j].w, gamma, vv4[j].w);
+          *reinterpret_cast<float4*>(work + base + e0) = vv4[j];
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) vv4[j] = ld_stream_f4(grad + base + (j * GB_THREADS + threadIdx.x) * 4);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        atomicAdd(&sh[tk_absbits(vv4[j].x) >> 20], 1u);
+        atomicAdd(&sh[tk_absbits(vv4[j].y) >> 20], 1u);
+        atomicAdd(&sh[tk_absbits(vv4[j].z) >> 20], 1u);
+        atomicAdd(&sh[tk_absbits(vv4[j].w) >> 20], 1u);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (e0 + q < len) {
+            float v = grad[base + e0 + q];
+            if (WRITE) { v = tk_comp(beta, work[base + e0 + q], gamma, v); work[base + e0 + q] = v; }
+            atomicAdd(&sh[tk_absbits(v) >> 20], 1u);
+          }
+        }
+      }
+    }
+  }
+  if (cur >= 0) close_segment();
+  // grid-wide last block: advance the device-side step block (what gb_tick_kernel does for the other codecs)
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(d.done, 1u) == gridDim.x - 1) {
+      d.done[0] = 0;
+      ctl->epoch += 1;
+      ctl->step = ctl->next_step;
+      ctl->next_step += 1;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- pass 2
+struct TkOut {
+  float* vals[GB_MAX_WORLD];
+  int32_t* idx[GB_MAX_WORLD];
+  int2* hdr[GB_MAX_WORLD];      // [ntiles + 1] certain picks, then [ntiles + 1] threshold-bin picks
+  int n;
+};
+__device__ __forceinline__ void tk_shift(TkOut& o, size_t bytes) {
+  for (int r = 0; r < o.n; ++r) {
+    o.vals[r] = (float*)((char*)o.vals[r] + bytes);
+    o.idx[r] = (int32_t*)((char*)o.idx[r] + bytes);
+    o.hdr[r] = (int2*)((char*)o.hdr[r] + bytes);
+  }
+}
+
+template <bool ZERO>
+__global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* work, TkDev d, TkOut out, const StepCtl* ctl,
+                                                       size_t par_stride) {
+  __shared__ float sval[GB_TILE];
+  __shared__ int32_t sidx[GB_TILE];
+  __shared__ uint32_t sh1[1024];
+  __shared__ int scount[2];
+  __shared__ int sbegin, s_last;
+  if (ctl->epoch & 1) tk_shift(out, par_stride);
+  const int t0 = (int)((int64_t)blockIdx.x * t.ntiles / gridDim.x);
+  const int t1 = (int)((int64_t)(blockIdx.x + 1) * t.ntiles / gridDim.x);
+  if (t0 >= t1) return;
+  for (int b = threadIdx.x; b < 1024; b += GB_THREADS) sh1[b] = 0;
+  if (threadIdx.x < 2) scount[threadIdx.x] = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  int cur = t.tile_seg[t0];
+  uint32_t bin = d.sel[cur * TK_SEL + S_BIN];
+  int mine = 0;
+  auto close_segment = [&]() {
+    __syncthreads();
+    uint32_t* hg = d.hist1 + (size_t)cur * 1024;
+    for (int b = threadIdx.x; b < 1024; b += GB_THREADS) {
+      const uint32_t c = sh1[b];
+      if (c) atomicAdd(hg + b, c);
+      sh1[b] = 0;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint32_t total = (uint32_t)(t.seg_tile0[cur + 1] - t.seg_tile0[cur]);
+      const uint32_t old = atomicAdd(d.segdone + cur * 4 + 1, (uint32_t)mine);
+      s_last = (old + (uint32_t)mine == total);
+    }
+    __syncthreads();
+    if (s_last) {                                  // tensor complete: extend the threshold prefix by 10 bits
+      __threadfence();
+      uint32_t* s = d.sel + cur * TK_SEL;
+      uint32_t b1, rem, cnt;
+      const bool found = cta_select<1024>(hg, s[S_KREM], b1, rem, cnt);
+      if (threadIdx.x == 0) {
+        if (found) { s[S_BIN] = (s[S_BIN] << 10) | b1; s[S_KREM] = rem; }
+        else s[S_FLAGS] = TKF_TAKEALL;             // only zeros are left in the bin: they would add nothing
+        d.segdone[cur * 4 + 1] = 0;
+      }
+    }
+    mine = 0;
+  };
+  for (int tile = t0; tile < t1; ++tile) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    if (seg != cur) { close_segment(); cur = seg; bin = d.sel[cur * TK_SEL + S_BIN]; }
+    ++mine;
+    const int par = (tile - t0) & 1;
+    float vv[4][4];
+    if (len == GB_TILE) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float4 v = *reinterpret_cast<const float4*>(work + base + (j * GB_THREADS + threadIdx.x) * 4);
+        vv[j][0] = v.x; vv[j][1] = v.y; vv[j][2] = v.z; vv[j][3] = v.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) vv[j][q] = (e0 + q < len) ? work[base + e0 + q] : 0.f;     // zero fill: never picked, never marked
+      }
+    }
+    uint32_t* mrow = d.mask + (size_t)tile * 128;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      uint32_t dm = 0, cm = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t b = tk_absbits(vv[j][q]);
+        const uint32_t hi = b >> 20;
+        dm |= (hi > bin ? 1u : 0u) << q;
+        cm |= ((hi == bin && b != 0u) ? 1u : 0u) << q;
+      }
+      // mask word = 8 consecutive threads x 4 elements
+      uint32_t w = cm << ((lane & 7) * 4);
+      w |= __shfl_xor_sync(0xffffffffu, w, 1);
+      w |= __shfl_xor_sync(0xffffffffu, w, 2);
+      w |= __shfl_xor_sync(0xffffffffu, w, 4);
+      if ((lane & 7) == 0) mrow[(j * GB_THREADS + threadIdx.x) >> 3] = w;
+      if (cm) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if ((cm >> q) & 1u) atomicAdd(&sh1[(tk_absbits(vv[j][q]) >> 10) & 1023u], 1u);
+      }
+      if (dm) {                                    // rare (< k per tensor): one shared-memory atomic per pick
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if ((dm >> q) & 1u) {
+            const int pos = atomicAdd(&scount[par], 1);
+            sval[pos] = vv[j][q];
+            sidx[pos] = local0 + e0 + q;
+            vv[j][q] = 0.f;
+          }
+        }
+        if (ZERO) {
+          if (len == GB_TILE) {
+            *reinterpret_cast<float4*>(work + base + e0) = make_float4(vv[j][0], vv[j][1], vv[j][2], vv[j][3]);
+          } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) if ((dm >> q) & 1u) work[base + e0 + q] = 0.f;
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const int tc = scount[par];
+      const int begin = (int)t.seg_kbase[seg] + (int)atomicAdd(d.sel + seg * TK_SEL + S_CURA, (uint32_t)tc);
+      sbegin = begin;
+      scount[par ^ 1] = 0;
+      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = make_int2(begin, tc);
+    }
+    __syncthreads();
+    const int tc = scount[par], begin = sbegin;
+    if (tc) {
+      for (int r = 0; r < out.n; ++r) {
+        float* dv = out.vals[r] + begin;
+        int32_t* di = out.idx[r] + begin;
+        for (int i = threadIdx.x; i < tc; i += GB_THREADS) { dv[i] = sval[i]; di[i] = sidx[i]; }
+      }
+    }
+    __syncthreads();
+  }
+  close_segment();
+}
+
+// ---------------------------------------------------------------- tail kernels: one warp per tile
+__device__ __forceinline__ bool tk_tile(const SegTable& t, int& tile, int& seg, int64_t& base, int& local0, int& len) {
+  tile = blockIdx.x * TK_WPT + (threadIdx.x >> 5);
+  if (tile >= t.ntiles) return false;
+  tile_bounds(t, tile, seg, base, local0, len);
+  return true;
+}
+
+__global__ void __launch_bounds__(TK_WPT * 32) tk_refine(SegTable t, const float* __restrict__ work, TkDev d) {
+  int tile, seg, local0, len;
+  int64_t base;
+  if (!tk_tile(t, tile, seg, base, local0, len)) return;
+  uint32_t* s = d.sel + seg * TK_SEL;
+  if (s[S_FLAGS] & TKF_TAKEALL) return;
+  const int lane = threadIdx.x & 31;
+  const uint32_t prefix = s[S_BIN];                            // 21 bits
+  const uint4 m = *reinterpret_cast<const uint4*>(d.mask + (size_t)tile * 128 + lane * 4);
+  const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
+  uint32_t* h2 = d.hist2 + (size_t)seg * 1024;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    uint32_t w = mw[i];
+    while (w) {
+      const int bit = __ffs(w) - 1;
+      w &= w - 1;
+      const uint32_t key = tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit));
+      if ((key >> 10) == prefix) atomicAdd(h2 + (key & 1023u), 1u);
+    }
+  }
+  __threadfence();
+  __syncwarp();
+  int last = 0;
+  if (lane == 0) {
+    const uint32_t total = (uint32_t)(t.seg_tile0[seg + 1] - t.seg_tile0[seg]);
+    last = atomicAdd(d.segdone + seg * 4 + 2, 1u) == total - 1;
+  }
+  last = __shfl_sync(0xffffffffu, last, 0);
+  if (last) {                                                  // this warp finished the tensor: exact threshold
+    __threadfence();
+    uint32_t b2 = 0, take = 0, cnt = 0;
+    const bool found = warp_select1024(h2, s[S_KREM], b2, take, cnt);
+    if (lane == 0) {
+      if (found) {
+        s[S_THR] = (prefix << 10) | b2;
+        s[S_TAKE] = take;
+        if (cnt != take) s[S_FLAGS] = TKF_AMBIG;
+      } else {
+        s[S_FLAGS] = TKF_TAKEALL;                              // cannot happen (the prefix bin holds >= KREM values); safe
+      }
+      d.segdone[seg * 4 + 2] = 0;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(TK_WPT * 32) tk_ties(SegTable t, const float* __restrict__ work, TkDev d) {
+  int tile, seg, local0, len;
+  int64_t base;
+  if (!tk_tile(t, tile, seg, base, local0, len)) return;
+  const uint32_t* s = d.sel + seg * TK_SEL;
+  if (!(s[S_FLAGS] & TKF_AMBIG)) return;
+  const int lane = threadIdx.x & 31;
+  const uint32_t thr = s[S_THR];
+  const uint4 m = *reinterpret_cast<const uint4*>(d.mask + (size_t)tile * 128 + lane * 4);
+  const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
+  int c = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    uint32_t w = mw[i];
+    while (w) {
+      const int bit = __ffs(w) - 1;
+      w &= w - 1;
+      c += tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit)) == thr;
+    }
+  }
+  c = warp_sum_i(c);
+  const int first = t.seg_tile0[seg], ntile = t.seg_tile0[seg + 1] - first;
+  int last = 0;
+  if (lane == 0) {
+    d.tiecnt[tile] = c;
+    __threadfence();
+    last = atomicAdd(d.segdone + seg * 4 + 3, 1u) == (uint32_t)ntile - 1;
+  }
+  last = __shfl_sync(0xffffffffu, last, 0);
+  if (last) {                                                  // exclusive scan of the tensor's tile counts, in tile order
+    __threadfence();
+    int carry = 0;
+    for (int c0 = 0; c0 < ntile; c0 += 32) {
+      const int i = c0 + lane;
+      const int v = i < ntile ? __ldcg(d.tiecnt + first + i) : 0;
+      int inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+      }
+      if (i < ntile) d.tiecnt[first + i] = carry + inc - v;
+      carry += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) d.segdone[seg * 4 + 3] = 0;
+  }
+}
+
+template <bool ZERO>
+__global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work, TkDev d, TkOut out, PeerPtrs peers, int channel,
+                                                        const StepCtl* ctl, size_t par_stride) {
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) tk_shift(out, par_stride);
+  int tile, seg, local0, len;
+  int64_t base;
+  if (tk_tile(t, tile, seg, base, local0, len)) {
+    uint32_t* s = d.sel + seg * TK_SEL;
+    const int lane = threadIdx.x & 31;
+    const uint32_t flags = s[S_FLAGS], thr = s[S_THR];
+    const int take = (int)s[S_TAKE];
+    const bool takeall = flags & TKF_TAKEALL, ambig = flags & TKF_AMBIG;
+    const uint4 m = *reinterpret_cast<const uint4*>(d.mask + (size_t)tile * 128 + lane * 4);
+    const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
+    // which marked elements are selected: above the threshold, or equal to it (all of them, or -- when ambiguous --
+    // the first `take` in index order: lanes own 128 consecutive elements, so lane order x bit order = index order)
+    uint32_t gt[4] = {0, 0, 0, 0}, eq[4] = {0, 0, 0, 0};
+    int neq = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t w = mw[i];
+      while (w) {
+        const int bit = __ffs(w) - 1;
+        w &= w - 1;
+        const uint32_t key = tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit));
+        if (takeall || key > thr) gt[i] |= 1u << bit;
+        else if (key == thr) { eq[i] |= 1u << bit; ++neq; }
+      }
+    }
+    uint32_t ch[4] = {gt[0], gt[1], gt[2], gt[3]};
+    if (!ambig) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) ch[i] |= eq[i];
+    } else {
+      int inc = neq;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+      }
+      int rank = d.tiecnt[tile] + inc - neq;                   // ties before this lane's first element
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint32_t w = eq[i];
+        while (w) {
+          const int bit = __ffs(w) - 1;
+          w &= w - 1;
+          if (rank < take) ch[i] |= 1u << bit;
+          ++rank;
+        }
+      }
+    }
+    const int mine = __popc(ch[0]) + __popc(ch[1]) + __popc(ch[2]) + __popc(ch[3]);
+    int inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += n;
+    }
+    const int total = __shfl_sync(0xffffffffu, inc, 31);
+    int begin = 0;
+    if (lane == 0) {
+      if (total) begin = (int)t.seg_kbase[seg] + (int)atomicAdd(s + S_CURA, (uint32_t)total);
+      const int xoff = t.ntiles + 1;
+      for (int r = 0; r < out.n; ++r) out.hdr[r][xoff + tile] = make_int2(begin, total);
+    }
+    begin = __shfl_sync(0xffffffffu, begin, 0);
+    int pos = begin + inc - mine;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t w = ch[i];
+      while (w) {
+        const int bit = __ffs(w) - 1;
+        w &= w - 1;
+        const int e = lane * 128 + i * 32 + bit;
+        const float v = __ldcg(work + base + e);
+        for (int r = 0; r < out.n; ++r) { out.vals[r][pos] = v; out.idx[r][pos] = local0 + e; }
+        if (ZERO) work[base + e] = 0.f;
+        ++pos;
+      }
+    }
+  }
+  release_flags_last_block(d.done + 4, peers, channel, epoch);
+}
+
+// ---------------------------------------------------------------- host side
+#define TK_LAUNCHED(p) do { (p)->launches++; GB_CUDA(cudaGetLastError()); } while (0)
+
+int tk_init(gb_plan* p) {
+  TkHost* h = new TkHost();
+  memset(h, 0, sizeof(*h));
+  p->topk2 = h;
+  size_t bytes = 0;
+  auto add = [&](size_t n) { size_t o = bytes; bytes += (n + 255) & ~size_t(255); return o; };
+  const size_t o_h1 = add((size_t)p->nseg * 1024 * 4), o_h2 = add((size_t)p->nseg * 1024 * 4);
+  const size_t o_sel = add((size_t)p->nseg * TK_SEL * 4), o_sd = add((size_t)p->nseg * 4 * 4);
+  const size_t o_mask = add((size_t)p->ntiles * 512), o_tc = add((size_t)p->ntiles * 4), o_done = add(64);
+  GB_CUDA(cudaMalloc(&h->block, bytes));
+  GB_CUDA(cudaMemset(h->block, 0, bytes));
+  char* b = (char*)h->block;
+  h->d.hist0 = p->d_hist;
+  h->d.hist1 = (uint32_t*)(b + o_h1);
+  h->d.hist2 = (uint32_t*)(b + o_h2);
+  h->d.sel = (uint32_t*)(b + o_sel);
+  h->d.segdone = (uint32_t*)(b + o_sd);
+  h->d.mask = (uint32_t*)(b + o_mask);
+  h->d.tiecnt = (int32_t*)(b + o_tc);
+  h->d.done = (uint32_t*)(b + o_done);
+  return 0;
+}
+
+void tk_free(gb_plan* p) {
+  TkHost* h = (TkHost*)p->topk2;
+  if (!h) return;
+  cudaFree(h->block);
+  delete h;
+  p->topk2 = nullptr;
+}
+
+int tk_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
+  gb_comm* c = p->comm;
+  TkHost* h = (TkHost*)p->topk2;
+  const bool mem = p->prm.memory == GB_MEM_RESIDUAL;
+  float* work = mem ? p->d_state0 : const_cast<float*>(d_grad);
+  ++p->epoch;                                               // host mirror of the device-side epoch
+  TkOut out;
+  const size_t per = ((size_t)p->ktotal * 4 + 255) & ~size_t(255);
+  for (int r = 0; r < c->world; ++r) {
+    char* s = gb_slot_of(c, r, p->chan_off, p->slot_bytes, 0, c->rank);
+    out.hdr[r] = (int2*)s;
+    out.vals[r] = (float*)(s + p->hdr_bytes);
+    out.idx[r] = (int32_t*)(s + p->hdr_bytes + per);
+  }
+  out.n = c->world;
+  const int grid = std::min(p->ntiles, 148 * 4);
+  const int wgrid = (p->ntiles + TK_WPT - 1) / TK_WPT;
+  if (mem) tk_pass1<true><<<grid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, p->prm.beta, p->prm.gamma, h->d, p->d_ctl);
+  else tk_pass1<false><<<grid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, p->prm.beta, p->prm.gamma, h->d, p->d_ctl);
+  TK_LAUNCHED(p);
+  if (mem) tk_pass2<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, h->d, out, p->d_ctl, p->par_stride);
+  else tk_pass2<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, h->d, out, p->d_ctl, p->par_stride);
+  TK_LAUNCHED(p);
+  tk_refine<<<wgrid, TK_WPT * 32, 0, st>>>(p->tab, work, h->d);
+  TK_LAUNCHED(p);
+  tk_ties<<<wgrid, TK_WPT * 32, 0, st>>>(p->tab, work, h->d);
+  TK_LAUNCHED(p);
+  if (mem) tk_finish<true><<<wgrid, TK_WPT * 32, 0, st>>>(p->tab, work, h->d, out, gb_comm_peers(c), p->channel, p->d_ctl, p->par_stride);
+  else tk_finish<false><<<wgrid, TK_WPT * 32, 0, st>>>(p->tab, work, h->d, out, gb_comm_peers(c), p->channel, p->d_ctl, p->par_stride);
+  TK_LAUNCHED(p);
+  return 0;
+}

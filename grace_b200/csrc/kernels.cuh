@@ -7,6 +7,10 @@ bool gb_codec_is_sparse(int codec);
 // K1: sparsifiers -- compensate + select + ordered compaction + peer stores / ordered merge
 int k1_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 int k1_recv(gb_plan* p, float* d_out, cudaStream_t st);
+// K1-topk, two-pass pipeline (k1_topk2.cu); GRACE_B200_TOPK_V1=1 keeps the four-pass kernels of k1_sparse.cu
+int tk_init(gb_plan* p);
+void tk_free(gb_plan* p);
+int tk_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 // K2: quantisers -- stats + encode/pack + peer stores / unpack-and-sum (+ majority vote)
 int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st);
 int k2_recv(gb_plan* p, float* d_out, cudaStream_t st);

@@ -57,6 +57,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->launches = 0;
   p->sketch = nullptr;
   p->adaq = nullptr;
+  p->topk2 = nullptr;
   p->d_samp = nullptr;
   p->bits = quant_bits(*params);
   const bool sparse = gb_codec_is_sparse(params->codec);
@@ -166,7 +167,8 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
 
   // ---- wire slot
   if (sparse) {
-    p->hdr_bytes = ((size_t)(p->ntiles + 1) * 2 * 4 + 255) & ~size_t(255);
+    // per-tile {begin, count}; TopK carries a second range per tile (threshold-bin picks, k1_topk2.cu)
+    p->hdr_bytes = ((size_t)(p->ntiles + 1) * 2 * 4 * (params->codec == GB_CODEC_TOPK ? 2 : 1) + 255) & ~size_t(255);
     size_t per = ((size_t)p->ktotal * 4 + 255) & ~size_t(255);
     p->slot_bytes = p->hdr_bytes + (params->codec == GB_CODEC_RANDOMK ? per : 2 * per);
     if (params->codec == GB_CODEC_ADAQ) p->slot_bytes = p->hdr_bytes + aq_means_bytes(nseg) + per;   // indices only
@@ -193,6 +195,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->par_stride = (size_t)c->world * p->slot_bytes;
   if (params->codec == GB_CODEC_SKETCH && sk_init(p)) return -1;
   if (params->codec == GB_CODEC_ADAQ && aq_init(p)) return -1;
+  if (params->codec == GB_CODEC_TOPK && !getenv("GRACE_B200_TOPK_V1") && tk_init(p)) return -1;
   GB_CUDA(cudaDeviceSynchronize());
   return 0;
   };
@@ -209,6 +212,7 @@ extern "C" int gb_plan_destroy(gb_plan* p) {
   cudaDeviceSynchronize();
   sk_free(p);
   aq_free(p);
+  tk_free(p);
   cudaFree(p->d_tables);
   cudaFree(p->d_state0);
   cudaFree(p->d_state1);
@@ -266,8 +270,10 @@ void gb_launch_tick(StepCtl* ctl, cudaStream_t st) { gb_tick_kernel<<<1, 1, 0, s
 
 extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  gb_launch_tick(p->d_ctl, st);
-  p->launches++;
+  if (!p->topk2) {                       // the two-pass TopK advances the step block in its first kernel
+    gb_launch_tick(p->d_ctl, st);
+    p->launches++;
+  }
   int rc = p->prm.codec == GB_CODEC_SKETCH ? sk_send(p, d_grad, st) : p->prm.codec == GB_CODEC_ADAQ ? aq_send(p, d_grad, st) : p->prm.codec == GB_CODEC_INCEPTIONN ? in_send(p, d_grad, st) : p->dense2 ? k0_send(p, d_grad, st) : gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
   if (rc) return rc;
   p->step++;
