@@ -538,7 +538,8 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* wo
 
 // Receive: ordered merge of W sparse lists into the dense aggregate.
 
-template <bool EXTRAS>
+// NW: compile-time bound of the number of ranks (1, 2, 4, 8): keeps the per-rank prefetch registers to what is needed
+template <bool EXTRAS, int NW>
 __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, float* out, float divisor, PeerPtrs peers,
                                                        int channel, const StepCtl* ctl, size_t par_stride, uint32_t* status,
                                                        uint64_t timeout_ns, int wait) {
@@ -552,18 +553,18 @@ __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, 
     tile_bounds(t, tile, seg, base, local0, len);
     // all ranks' headers, then all ranks' first GB_THREADS entries, are requested before anything is added:
     // two dependent memory latencies per tile instead of two per rank.  The adds keep rank order.
-    int2 h[GB_MAX_WORLD];
+    int2 h[NW];
 #pragma unroll
-    for (int r = 0; r < GB_MAX_WORLD; ++r) h[r] = in.hdr[r < in.n ? r : 0][tile];
-    int2 xh[GB_MAX_WORLD];                           // TopK: second range of the tile (picks from the threshold bin)
+    for (int r = 0; r < NW; ++r) h[r] = in.hdr[r < in.n ? r : 0][tile];
+    int2 xh[NW];                           // TopK: second range of the tile (picks from the threshold bin)
     if (EXTRAS) {
 #pragma unroll
-      for (int r = 0; r < GB_MAX_WORLD; ++r) xh[r] = in.hdr[r < in.n ? r : 0][t.ntiles + 1 + tile];
+      for (int r = 0; r < NW; ++r) xh[r] = in.hdr[r < in.n ? r : 0][t.ntiles + 1 + tile];
     }
-    float pv[GB_MAX_WORLD];
-    int32_t pi[GB_MAX_WORLD];
+    float pv[NW];
+    int32_t pi[NW];
 #pragma unroll
-    for (int r = 0; r < GB_MAX_WORLD; ++r) {
+    for (int r = 0; r < NW; ++r) {
       pv[r] = 0.f;
       pi[r] = -1;
       if (r < in.n && threadIdx.x < h[r].y) {
@@ -574,7 +575,7 @@ __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, 
     for (int i = threadIdx.x; i < GB_TILE; i += GB_THREADS) acc[i] = 0.f;
     __syncthreads();
 #pragma unroll
-    for (int r = 0; r < GB_MAX_WORLD; ++r) {
+    for (int r = 0; r < NW; ++r) {
       if (r < in.n) {
         const int l0 = pi[r] - local0;
         if (pi[r] >= 0 && (unsigned)l0 < (unsigned)GB_TILE) acc[l0] += pv[r];
@@ -770,10 +771,13 @@ int k1_recv(gb_plan* p, float* d_out, cudaStream_t st) {
     LAUNCHED(p);
     return 0;
   }
-  if (p->prm.codec == GB_CODEC_TOPK)
-    k1_merge<true><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns, 1);
-  else
-    k1_merge<false><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns, 1);
+#define MERGE(EX, NW) k1_merge<EX, NW><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns, 1)
+  const bool ex = p->prm.codec == GB_CODEC_TOPK;
+  if (c->world == 1) { if (ex) MERGE(true, 1); else MERGE(false, 1); }
+  else if (c->world == 2) { if (ex) MERGE(true, 2); else MERGE(false, 2); }
+  else if (c->world <= 4) { if (ex) MERGE(true, 4); else MERGE(false, 4); }
+  else { if (ex) MERGE(true, 8); else MERGE(false, 8); }
+#undef MERGE
   LAUNCHED(p);
   return 0;
 }

@@ -234,13 +234,11 @@ struct TkOut {
   int2* hdr[GB_MAX_WORLD];      // [ntiles + 1] certain picks, then [ntiles + 1] threshold-bin picks
   int n;
 };
-__device__ __forceinline__ void tk_shift(TkOut& o, size_t bytes) {
-  for (int r = 0; r < o.n; ++r) {
-    o.vals[r] = (float*)((char*)o.vals[r] + bytes);
-    o.idx[r] = (int32_t*)((char*)o.idx[r] + bytes);
-    o.hdr[r] = (int2*)((char*)o.hdr[r] + bytes);
-  }
-}
+// peers are addressed with compile-time indices (the kernel parameter stays in the constant bank, no local copy)
+#define TK_PEERS(r) _Pragma("unroll") for (int r = 0; r < GB_MAX_WORLD; ++r) if (r < out.n)
+#define TK_VALS(o, r, sh) ((float*)((char*)(o).vals[r] + (sh)))
+#define TK_IDX(o, r, sh) ((int32_t*)((char*)(o).idx[r] + (sh)))
+#define TK_HDR(o, r, sh) ((int2*)((char*)(o).hdr[r] + (sh)))
 
 template <bool ZERO>
 __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* work, TkDev d, TkOut out, const StepCtl* ctl,
@@ -250,7 +248,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
   __shared__ uint32_t sh1[1024];
   __shared__ int scount[2];
   __shared__ int sbegin, s_last;
-  if (ctl->epoch & 1) tk_shift(out, par_stride);
+  const size_t psh = (ctl->epoch & 1) ? par_stride : 0;       // parity of the device-side epoch selects the slot
   const int t0 = (int)((int64_t)blockIdx.x * t.ntiles / gridDim.x);
   const int t1 = (int)((int64_t)(blockIdx.x + 1) * t.ntiles / gridDim.x);
   if (t0 >= t1) return;
@@ -361,14 +359,14 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
       const int begin = (int)t.seg_kbase[seg] + (int)atomicAdd(d.sel + seg * TK_SEL + S_CURA, (uint32_t)tc);
       sbegin = begin;
       scount[par ^ 1] = 0;
-      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = make_int2(begin, tc);
+      TK_PEERS(r) TK_HDR(out, r, psh)[tile] = make_int2(begin, tc);
     }
     __syncthreads();
     const int tc = scount[par], begin = sbegin;
     if (tc) {
-      for (int r = 0; r < out.n; ++r) {
-        float* dv = out.vals[r] + begin;
-        int32_t* di = out.idx[r] + begin;
+      TK_PEERS(r) {
+        float* dv = TK_VALS(out, r, psh) + begin;
+        int32_t* di = TK_IDX(out, r, psh) + begin;
         for (int i = threadIdx.x; i < tc; i += GB_THREADS) { dv[i] = sval[i]; di[i] = sidx[i]; }
       }
     }
@@ -385,33 +383,79 @@ __device__ __forceinline__ bool tk_tile(const SegTable& t, int& tile, int& seg, 
   return true;
 }
 
+// Marked elements of a tile as a list in shared memory (index order), so that the gathers of their values are
+// independent loads spread over the 32 lanes instead of a dependent chain per lane.  Returns the number of marked
+// elements; the list is only built when it fits TK_LIST entries (else the callers walk the mask lane by lane).
+#define TK_LIST 256
+__device__ __forceinline__ int tk_build_list(const uint32_t mw[4], int lane, uint16_t* pos) {
+  const int mine = __popc(mw[0]) + __popc(mw[1]) + __popc(mw[2]) + __popc(mw[3]);
+  int inc = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int n = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += n;
+  }
+  const int total = __shfl_sync(0xffffffffu, inc, 31);
+  if (total <= TK_LIST) {
+    int o = inc - mine;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t w = mw[i];
+      while (w) {
+        const int bit = __ffs(w) - 1;
+        w &= w - 1;
+        pos[o++] = (uint16_t)(lane * 128 + i * 32 + bit);
+      }
+    }
+  }
+  __syncwarp();
+  return total;
+}
+
 __global__ void __launch_bounds__(TK_WPT * 32) tk_refine(SegTable t, const float* __restrict__ work, TkDev d) {
+  __shared__ uint16_t s_pos[TK_WPT][TK_LIST];
   int tile, seg, local0, len;
   int64_t base;
   if (!tk_tile(t, tile, seg, base, local0, len)) return;
   uint32_t* s = d.sel + seg * TK_SEL;
   if (s[S_FLAGS] & TKF_TAKEALL) return;
   const int lane = threadIdx.x & 31;
+  uint16_t* pos = s_pos[threadIdx.x >> 5];
   const uint32_t prefix = s[S_BIN];                            // 21 bits
   const uint4 m = *reinterpret_cast<const uint4*>(d.mask + (size_t)tile * 128 + lane * 4);
   const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
   uint32_t* h2 = d.hist2 + (size_t)seg * 1024;
+  const int total = tk_build_list(mw, lane, pos);
+  if (total <= TK_LIST) {
+    for (int i0 = 0; i0 < total; i0 += 128) {                  // four independent gathers per lane in flight
+      uint32_t key[4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    uint32_t w = mw[i];
-    while (w) {
-      const int bit = __ffs(w) - 1;
-      w &= w - 1;
-      const uint32_t key = tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit));
-      if ((key >> 10) == prefix) atomicAdd(h2 + (key & 1023u), 1u);
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * 32 + lane;
+        key[u] = i < total ? tk_absbits(__ldcg(work + base + pos[i])) : 0xFFFFFFFFu;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if ((key[u] >> 10) == prefix) atomicAdd(h2 + (key[u] & 1023u), 1u);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t w = mw[i];
+      while (w) {
+        const int bit = __ffs(w) - 1;
+        w &= w - 1;
+        const uint32_t key = tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit));
+        if ((key >> 10) == prefix) atomicAdd(h2 + (key & 1023u), 1u);
+      }
     }
   }
   __threadfence();
   __syncwarp();
   int last = 0;
   if (lane == 0) {
-    const uint32_t total = (uint32_t)(t.seg_tile0[seg + 1] - t.seg_tile0[seg]);
-    last = atomicAdd(d.segdone + seg * 4 + 2, 1u) == total - 1;
+    const uint32_t total_tiles = (uint32_t)(t.seg_tile0[seg + 1] - t.seg_tile0[seg]);
+    last = atomicAdd(d.segdone + seg * 4 + 2, 1u) == total_tiles - 1;
   }
   last = __shfl_sync(0xffffffffu, last, 0);
   if (last) {                                                  // this warp finished the tensor: exact threshold
@@ -432,23 +476,39 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_refine(SegTable t, const float
 }
 
 __global__ void __launch_bounds__(TK_WPT * 32) tk_ties(SegTable t, const float* __restrict__ work, TkDev d) {
+  __shared__ uint16_t s_pos[TK_WPT][TK_LIST];
   int tile, seg, local0, len;
   int64_t base;
   if (!tk_tile(t, tile, seg, base, local0, len)) return;
   const uint32_t* s = d.sel + seg * TK_SEL;
   if (!(s[S_FLAGS] & TKF_AMBIG)) return;
   const int lane = threadIdx.x & 31;
+  uint16_t* pos = s_pos[threadIdx.x >> 5];
   const uint32_t thr = s[S_THR];
   const uint4 m = *reinterpret_cast<const uint4*>(d.mask + (size_t)tile * 128 + lane * 4);
   const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
   int c = 0;
+  const int total = tk_build_list(mw, lane, pos);
+  if (total <= TK_LIST) {
+    for (int i0 = 0; i0 < total; i0 += 128) {
+      uint32_t key[4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    uint32_t w = mw[i];
-    while (w) {
-      const int bit = __ffs(w) - 1;
-      w &= w - 1;
-      c += tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit)) == thr;
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * 32 + lane;
+        key[u] = i < total ? tk_absbits(__ldcg(work + base + pos[i])) : 0xFFFFFFFFu;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) c += key[u] == thr;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t w = mw[i];
+      while (w) {
+        const int bit = __ffs(w) - 1;
+        w &= w - 1;
+        c += tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit)) == thr;
+      }
     }
   }
   c = warp_sum_i(c);
@@ -482,83 +542,142 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_ties(SegTable t, const float* 
 template <bool ZERO>
 __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work, TkDev d, TkOut out, PeerPtrs peers, int channel,
                                                         const StepCtl* ctl, size_t par_stride) {
+  __shared__ uint16_t s_pos[TK_WPT][TK_LIST];
+  __shared__ float s_val[TK_WPT][TK_LIST];
   const uint32_t epoch = ctl->epoch;
-  if (epoch & 1) tk_shift(out, par_stride);
+  const size_t psh = (epoch & 1) ? par_stride : 0;
   int tile, seg, local0, len;
   int64_t base;
   if (tk_tile(t, tile, seg, base, local0, len)) {
     uint32_t* s = d.sel + seg * TK_SEL;
     const int lane = threadIdx.x & 31;
+    uint16_t* pos = s_pos[threadIdx.x >> 5];
+    float* val = s_val[threadIdx.x >> 5];
     const uint32_t flags = s[S_FLAGS], thr = s[S_THR];
     const int take = (int)s[S_TAKE];
     const bool takeall = flags & TKF_TAKEALL, ambig = flags & TKF_AMBIG;
     const uint4 m = *reinterpret_cast<const uint4*>(d.mask + (size_t)tile * 128 + lane * 4);
     const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
-    // which marked elements are selected: above the threshold, or equal to it (all of them, or -- when ambiguous --
-    // the first `take` in index order: lanes own 128 consecutive elements, so lane order x bit order = index order)
-    uint32_t gt[4] = {0, 0, 0, 0}, eq[4] = {0, 0, 0, 0};
-    int neq = 0;
+    const int xoff = t.ntiles + 1;
+    const int nmarked = tk_build_list(mw, lane, pos);
+    if (nmarked <= TK_LIST) {
+      // common case: gather all marked values at once (independent loads), decide in index order with ballots,
+      // compact the selected ones in place in shared memory, claim one payload range, store
+      for (int i0 = 0; i0 < nmarked; i0 += 128) {
+        float v[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      uint32_t w = mw[i];
-      while (w) {
-        const int bit = __ffs(w) - 1;
-        w &= w - 1;
-        const uint32_t key = tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit));
-        if (takeall || key > thr) gt[i] |= 1u << bit;
-        else if (key == thr) { eq[i] |= 1u << bit; ++neq; }
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * 32 + lane;
+          v[u] = i < nmarked ? __ldcg(work + base + pos[i]) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * 32 + lane;
+          if (i < nmarked) val[i] = v[u];
+        }
       }
-    }
-    uint32_t ch[4] = {gt[0], gt[1], gt[2], gt[3]};
-    if (!ambig) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) ch[i] |= eq[i];
+      __syncwarp();
+      int nsel = 0;
+      int tie_run = ambig ? d.tiecnt[tile] : 0;
+      const uint32_t lt = (1u << lane) - 1u;
+      for (int i0 = 0; i0 < nmarked; i0 += 32) {
+        const int i = i0 + lane;
+        const bool in = i < nmarked;
+        const float v = in ? val[i] : 0.f;
+        const uint16_t e = in ? pos[i] : (uint16_t)0;
+        const uint32_t key = tk_absbits(v);
+        const bool gt = in && (takeall || key > thr);
+        const bool eq = in && !gt && key == thr;
+        bool chosen = gt || eq;
+        if (ambig) {
+          const uint32_t eb = __ballot_sync(0xffffffffu, eq);
+          chosen = gt || (eq && tie_run + __popc(eb & lt) < take);
+          tie_run += __popc(eb);
+        }
+        const uint32_t cb = __ballot_sync(0xffffffffu, chosen);
+        __syncwarp();
+        if (chosen) { const int p = nsel + __popc(cb & lt); pos[p] = e; val[p] = v; }
+        nsel += __popc(cb);
+        __syncwarp();
+      }
+      int begin = 0;
+      if (lane == 0) {
+        if (nsel) begin = (int)t.seg_kbase[seg] + (int)atomicAdd(s + S_CURA, (uint32_t)nsel);
+        TK_PEERS(r) TK_HDR(out, r, psh)[xoff + tile] = make_int2(begin, nsel);
+      }
+      begin = __shfl_sync(0xffffffffu, begin, 0);
+      for (int i = lane; i < nsel; i += 32) {
+        const int e = pos[i];
+        const float v = val[i];
+        TK_PEERS(r) { TK_VALS(out, r, psh)[begin + i] = v; TK_IDX(out, r, psh)[begin + i] = local0 + e; }
+        if (ZERO) work[base + e] = 0.f;
+      }
     } else {
-      int inc = neq;
+      // crowded tile (many values share the threshold bin): walk the mask lane by lane.  Lanes own 128 consecutive
+      // elements, so lane order x bit order = index order.
+      uint32_t gt[4] = {0, 0, 0, 0}, eq[4] = {0, 0, 0, 0};
+      int neq = 0;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint32_t w = mw[i];
+        while (w) {
+          const int bit = __ffs(w) - 1;
+          w &= w - 1;
+          const uint32_t key = tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit));
+          if (takeall || key > thr) gt[i] |= 1u << bit;
+          else if (key == thr) { eq[i] |= 1u << bit; ++neq; }
+        }
+      }
+      uint32_t ch[4] = {gt[0], gt[1], gt[2], gt[3]};
+      if (!ambig) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ch[i] |= eq[i];
+      } else {
+        int inc = neq;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int n = __shfl_up_sync(0xffffffffu, inc, o);
+          if (lane >= o) inc += n;
+        }
+        int rank = d.tiecnt[tile] + inc - neq;                 // ties before this lane's first element
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint32_t w = eq[i];
+          while (w) {
+            const int bit = __ffs(w) - 1;
+            w &= w - 1;
+            if (rank < take) ch[i] |= 1u << bit;
+            ++rank;
+          }
+        }
+      }
+      const int mine = __popc(ch[0]) + __popc(ch[1]) + __popc(ch[2]) + __popc(ch[3]);
+      int inc = mine;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         const int n = __shfl_up_sync(0xffffffffu, inc, o);
         if (lane >= o) inc += n;
       }
-      int rank = d.tiecnt[tile] + inc - neq;                   // ties before this lane's first element
+      const int total = __shfl_sync(0xffffffffu, inc, 31);
+      int begin = 0;
+      if (lane == 0) {
+        if (total) begin = (int)t.seg_kbase[seg] + (int)atomicAdd(s + S_CURA, (uint32_t)total);
+        TK_PEERS(r) TK_HDR(out, r, psh)[xoff + tile] = make_int2(begin, total);
+      }
+      begin = __shfl_sync(0xffffffffu, begin, 0);
+      int p = begin + inc - mine;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        uint32_t w = eq[i];
+        uint32_t w = ch[i];
         while (w) {
           const int bit = __ffs(w) - 1;
           w &= w - 1;
-          if (rank < take) ch[i] |= 1u << bit;
-          ++rank;
+          const int e = lane * 128 + i * 32 + bit;
+          const float v = __ldcg(work + base + e);
+          TK_PEERS(r) { TK_VALS(out, r, psh)[p] = v; TK_IDX(out, r, psh)[p] = local0 + e; }
+          if (ZERO) work[base + e] = 0.f;
+          ++p;
         }
-      }
-    }
-    const int mine = __popc(ch[0]) + __popc(ch[1]) + __popc(ch[2]) + __popc(ch[3]);
-    int inc = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int n = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += n;
-    }
-    const int total = __shfl_sync(0xffffffffu, inc, 31);
-    int begin = 0;
-    if (lane == 0) {
-      if (total) begin = (int)t.seg_kbase[seg] + (int)atomicAdd(s + S_CURA, (uint32_t)total);
-      const int xoff = t.ntiles + 1;
-      for (int r = 0; r < out.n; ++r) out.hdr[r][xoff + tile] = make_int2(begin, total);
-    }
-    begin = __shfl_sync(0xffffffffu, begin, 0);
-    int pos = begin + inc - mine;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      uint32_t w = ch[i];
-      while (w) {
-        const int bit = __ffs(w) - 1;
-        w &= w - 1;
-        const int e = lane * 128 + i * 32 + bit;
-        const float v = __ldcg(work + base + e);
-        for (int r = 0; r < out.n; ++r) { out.vals[r][pos] = v; out.idx[r][pos] = local0 + e; }
-        if (ZERO) work[base + e] = 0.f;
-        ++pos;
       }
     }
   }

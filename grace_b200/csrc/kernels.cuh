@@ -51,9 +51,11 @@ void gb_launch_tick(StepCtl* ctl, cudaStream_t st);       // plan.cu
 // Last-block-done flag release shared by the send kernels: every CTA calls this after its
 // final peer store; the CTA that arrives last publishes `epoch` to all peers.
 __device__ __forceinline__ void release_flags_last_block(uint32_t* done, PeerPtrs peers, int channel, uint32_t epoch) {
-  __threadfence_system();
+  // One thread fences for the CTA: the barrier orders every thread's payload stores before thread 0's
+  // system-scope fence (fences are cumulative), so 255 threads do not each wait for a membar.sys.
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence_system();
     uint32_t ticket = atomicAdd(done, 1u);
     if (ticket == gridDim.x - 1) {
       __threadfence_system();
