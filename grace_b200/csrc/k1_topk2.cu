@@ -52,7 +52,7 @@ __device__ __forceinline__ uint32_t ldcg_u32(const uint32_t* p) { return __ldcg(
 
 // Block-wide search of the bin that holds the krem-th largest element: bins are walked from NB-1 downwards.
 // Every thread must call it.  Zeroes the histogram.  Returns false when the histogram holds fewer than krem entries.
-template <int NB>
+template <int NB, bool GLOBAL>
 __device__ __forceinline__ bool cta_select(uint32_t* h, uint32_t krem, uint32_t& bin, uint32_t& rem, uint32_t& cnt) {
   constexpr int PER = NB / GB_THREADS;
   __shared__ uint32_t wsum[GB_THREADS / 32];
@@ -62,7 +62,7 @@ __device__ __forceinline__ bool cta_select(uint32_t* h, uint32_t krem, uint32_t&
   uint32_t c[PER];
   uint32_t mine = 0;
 #pragma unroll
-  for (int i = 0; i < PER; ++i) { c[i] = ldcg_u32(h + hi - i); mine += c[i]; }
+  for (int i = 0; i < PER; ++i) { c[i] = GLOBAL ? ldcg_u32(h + hi - i) : h[hi - i]; mine += c[i]; }
 #pragma unroll
   for (int i = 0; i < PER; ++i) if (c[i]) h[hi - i] = 0;
   uint32_t inc = mine;
@@ -87,6 +87,29 @@ __device__ __forceinline__ bool cta_select(uint32_t* h, uint32_t krem, uint32_t&
   const bool found = res[3] != 0;
   __syncthreads();
   return found;
+}
+
+// Tile descriptors of the CTA's next TK_DCACHE tiles in shared memory: the per-tile table look-up (a global load
+// at the head of every iteration, and again in the thread that issues the copies) leaves the critical path.
+#define TK_DCACHE 128
+struct TkTile { int64_t base; int seg, local0, len; };
+__device__ __forceinline__ void tk_fill_descs(const SegTable& t, int4* sdesc, int first, int t1) {
+  for (int i = threadIdx.x; i < TK_DCACHE && first + i < t1; i += GB_THREADS) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, first + i, seg, base, local0, len);
+    sdesc[i] = make_int4((int)(uint32_t)(base & 0xFFFFFFFFll), (int)(uint32_t)((uint64_t)base >> 32), seg,
+                         (int)((uint32_t)len | ((uint32_t)(local0 / GB_TILE) << 13)));
+  }
+}
+__device__ __forceinline__ TkTile tk_desc(const int4* sdesc, int i) {
+  const int4 d = sdesc[i];
+  TkTile r;
+  r.base = (int64_t)(((uint64_t)(uint32_t)d.y << 32) | (uint32_t)d.x);
+  r.seg = d.z;
+  r.len = d.w & 0x1FFF;
+  r.local0 = (int)((uint32_t)d.w >> 13) * GB_TILE;
+  return r;
 }
 
 // the same for one warp and 1024 bins (32 per lane)
@@ -121,30 +144,92 @@ __device__ __forceinline__ bool warp_select1024(uint32_t* h, uint32_t krem, uint
   return true;
 }
 
+// ---------------------------------------------------------------- bulk-copy (TMA) tile pipeline
+// Tiles are contiguous 16 KB runs, so the one-dimensional bulk copy (cp.async.bulk, SASS UBLKCP) moves them:
+// one thread issues a tile's loads TK_STAGES tiles ahead, completion is counted in bytes on an mbarrier, nobody
+// holds the data in registers while it is in flight.
+#define TK_STAGES 3
+__device__ __forceinline__ uint32_t tk_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void tk_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tk_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void tk_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tk_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tk_mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(tk_smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// this GPU's memory only (gradient / residual buffers are local); no multicast
+__device__ __forceinline__ void tk_bulk_load(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(tk_smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(tk_smem_u32(bar))
+               : "memory");
+}
+
 // ---------------------------------------------------------------- pass 1
 template <bool WRITE>
-__global__ void __launch_bounds__(GB_THREADS, 4) tk_pass1(SegTable t, const float* __restrict__ grad, float* work, float beta,
+__global__ void __launch_bounds__(GB_THREADS, 2) tk_pass1(SegTable t, const float* __restrict__ grad, float* work, float beta,
                                                        float gamma, TkDev d, StepCtl* ctl) {
+  extern __shared__ __align__(128) unsigned char tk_dyn[];
+  float* sg = reinterpret_cast<float*>(tk_dyn);                       // [TK_STAGES][GB_TILE] gradient tiles
+  float* sr = sg + TK_STAGES * GB_TILE;                               // [TK_STAGES][GB_TILE] residual tiles (WRITE)
   __shared__ uint32_t sh[2048];
+  __shared__ __align__(16) int4 sdesc[TK_DCACHE];
+  __shared__ __align__(8) uint64_t full[TK_STAGES];
   __shared__ int s_last;
   if (WRITE && ctl->next_step == 0) { beta = 0.f; gamma = 1.f; }   // empty memory: compensate() is the identity
   const int t0 = (int)((int64_t)blockIdx.x * t.ntiles / gridDim.x);          // even split: the grid is a multiple of the SM count
   const int t1 = (int)((int64_t)(blockIdx.x + 1) * t.ntiles / gridDim.x);
   for (int b = threadIdx.x; b < 2048; b += GB_THREADS) sh[b] = 0;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < TK_STAGES; ++s) tk_mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  int dbase = t0;                                                   // first tile held by the descriptor cache
+  tk_fill_descs(t, sdesc, dbase, t1);
   __syncthreads();
-  int cur = t0 < t1 ? t.tile_seg[t0] : -1;
+  auto issue = [&](int tile, int s) {                               // one thread
+    const TkTile x = tk_desc(sdesc, tile - dbase);
+    const uint32_t bytes = (uint32_t)((x.len + 3) & ~3) * 4u;       // the pad up to the next 128 elements belongs to the segment
+    tk_mbar_expect_tx(&full[s], WRITE ? 2 * bytes : bytes);
+    tk_bulk_load(sg + s * GB_TILE, grad + x.base, bytes, &full[s]);
+    if (WRITE) tk_bulk_load(sr + s * GB_TILE, work + x.base, bytes, &full[s]);
+  };
+  if (threadIdx.x == 0)
+    for (int s = 0; s < TK_STAGES && t0 + s < t1; ++s) issue(t0 + s, s);
+  int cur = t0 < t1 ? tk_desc(sdesc, 0).seg : -1;
   int mine = 0;                                   // tiles of `cur` done by this CTA
+  auto write_sel = [&](uint32_t bin, uint32_t rem) {
+    uint32_t* s = d.sel + cur * TK_SEL;
+    s[S_BIN] = bin; s[S_KREM] = rem; s[S_CURA] = 0; s[S_FLAGS] = 0; s[S_THR] = 0; s[S_TAKE] = 0;
+  };
   auto close_segment = [&]() {
     __syncthreads();
+    uint32_t bin, rem, cnt;
+    if (t.seg_tile0[cur] >= t0 && t.seg_tile0[cur + 1] <= t1) {
+      // the whole tensor was histogrammed by this CTA (all small tensors): select straight from shared memory
+      cta_select<2048, false>(sh, (uint32_t)t.seg_k[cur], bin, rem, cnt);
+      if (threadIdx.x == 0) write_sel(bin, rem);
+      mine = 0;
+      return;
+    }
     uint32_t* hg = d.hist0 + (size_t)cur * 2048;
     for (int b = threadIdx.x; b < 2048; b += GB_THREADS) {
       const uint32_t c = sh[b];
       if (c) atomicAdd(hg + b, c);
       sh[b] = 0;
     }
-    __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
+      __threadfence();                             // cumulative: orders the CTA's histogram atomics (seen through the barrier)
       const uint32_t total = (uint32_t)(t.seg_tile0[cur + 1] - t.seg_tile0[cur]);
       const uint32_t old = atomicAdd(d.segdone + cur * 4, (uint32_t)mine);
       s_last = (old + (uint32_t)mine == total);
@@ -152,66 +237,60 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass1(SegTable t, const floa
     __syncthreads();
     if (s_last) {                                  // this CTA finished the tensor: choose its threshold bin
       __threadfence();
-      uint32_t bin, rem, cnt;
-      cta_select<2048>(hg, (uint32_t)t.seg_k[cur], bin, rem, cnt);      // always found: the histogram holds numel >= k
-      if (threadIdx.x == 0) {
-        uint32_t* s = d.sel + cur * TK_SEL;
-        s[S_BIN] = bin; s[S_KREM] = rem; s[S_CURA] = 0; s[S_FLAGS] = 0; s[S_THR] = 0; s[S_TAKE] = 0;
-        d.segdone[cur * 4] = 0;
-      }
+      cta_select<2048, true>(hg, (uint32_t)t.seg_k[cur], bin, rem, cnt);      // always found: the histogram holds numel >= k
+      if (threadIdx.x == 0) { write_sel(bin, rem); d.segdone[cur * 4] = 0; }
     }
     mine = 0;
   };
-  for (int tile = t0; tile < t1; ++tile) {
-    int seg, local0, len;
-    int64_t base;
-    tile_bounds(t, tile, seg, base, local0, len);
+  for (int tile = t0, it = 0; tile < t1; ++tile, ++it) {
+    const int st = it % TK_STAGES;
+    const uint32_t par = (uint32_t)(it / TK_STAGES) & 1u;
+    if (tile + TK_STAGES >= dbase + TK_DCACHE && dbase + TK_DCACHE < t1) {      // refill the descriptor cache (rare)
+      __syncthreads();
+      dbase = tile;
+      tk_fill_descs(t, sdesc, dbase, t1);
+      __syncthreads();
+    }
+    const TkTile x = tk_desc(sdesc, tile - dbase);
+    const int seg = x.seg, len = x.len;
+    const int64_t base = x.base;
     if (seg != cur) { close_segment(); cur = seg; }
     ++mine;
-    float4 vv4[4];
-    if (len == GB_TILE) {
-      if (WRITE) {
-        float4 rr4[4];
+    tk_mbar_wait(&full[st], par);
+    const float4* g4 = reinterpret_cast<const float4*>(sg + st * GB_TILE);
+    const float4* r4 = reinterpret_cast<const float4*>(sr + st * GB_TILE);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
-          vv4[j] = ld_stream_f4(grad + base + e0);
-          rr4[j] = *reinterpret_cast<const float4*>(work + base + e0);
+    for (int j = 0; j < 4; ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 < len) {
+        float4 v = g4[j * GB_THREADS + threadIdx.x];
+        if (WRITE) {
+          const float4 r = r4[j * GB_THREADS + threadIdx.x];
+          v.x = tk_comp(beta, r.x, gamma, v.x);
+          v.y = tk_comp(beta, r.y, gamma, v.y);
+          v.z = tk_comp(beta, r.z, gamma, v.z);
+          v.w = tk_comp(beta, r.w, gamma, v.w);
         }
+        if (e0 + 4 <= len) {
+          if (WRITE) *reinterpret_cast<float4*>(work + base + e0) = v;
+          atomicAdd(&sh[tk_absbits(v.x) >> 20], 1u);
+          atomicAdd(&sh[tk_absbits(v.y) >> 20], 1u);
+          atomicAdd(&sh[tk_absbits(v.z) >> 20], 1u);
+          atomicAdd(&sh[tk_absbits(v.w) >> 20], 1u);
+        } else {
+          const float vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
-          vv4[j].x = tk_comp(beta, rr4[j].x, gamma, vv4[j].x);
-          vv4[j].y = tk_comp(beta, rr4[j].y, gamma, vv4[j].y);
-          vv4[j].z = tk_comp(beta, rr4[j].z, gamma, vv4[j].z);
-          vv4[j].w = tk_comp(beta, rr4[j].w, gamma, vv4[j].w);
-          *reinterpret_cast<float4*>(work + base + e0) = vv4[j];
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) vv4[j] = ld_stream_f4(grad + base + (j * GB_THREADS + threadIdx.x) * 4);
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        atomicAdd(&sh[tk_absbits(vv4[j].x) >> 20], 1u);
-        atomicAdd(&sh[tk_absbits(vv4[j].y) >> 20], 1u);
-        atomicAdd(&sh[tk_absbits(vv4[j].z) >> 20], 1u);
-        atomicAdd(&sh[tk_absbits(vv4[j].w) >> 20], 1u);
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          if (e0 + q < len) {
-            float v = grad[base + e0 + q];
-            if (WRITE) { v = tk_comp(beta, work[base + e0 + q], gamma, v); work[base + e0 + q] = v; }
-            atomicAdd(&sh[tk_absbits(v) >> 20], 1u);
+          for (int q = 0; q < 4; ++q) {
+            if (e0 + q < len) {
+              if (WRITE) work[base + e0 + q] = vv[q];
+              atomicAdd(&sh[tk_absbits(vv[q]) >> 20], 1u);
+            }
           }
         }
       }
     }
+    __syncthreads();                               // every thread has read stage st: refill it
+    if (threadIdx.x == 0 && tile + TK_STAGES < t1) issue(tile + TK_STAGES, st);
   }
   if (cur >= 0) close_segment();
   // grid-wide last block: advance the device-side step block (what gb_tick_kernel does for the other codecs)
@@ -240,36 +319,73 @@ struct TkOut {
 #define TK_IDX(o, r, sh) ((int32_t*)((char*)(o).idx[r] + (sh)))
 #define TK_HDR(o, r, sh) ((int2*)((char*)(o).hdr[r] + (sh)))
 
+#define TK_STAGE_CAP 1024        // certain picks of one tile staged in shared memory (more: the tile is re-read)
+
+// Mask layout: word 4 * g + q of a tile, bit l  <->  element 128 * g + 4 * l + q  (g = 0..31 groups of 128 elements,
+// one warp-wide ballot per q).  A lane of the tail kernels loads the uint4 of group `lane`, i.e. 128 consecutive elements.
 template <bool ZERO>
-__global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* work, TkDev d, TkOut out, const StepCtl* ctl,
+__global__ void __launch_bounds__(GB_THREADS, 2) tk_pass2(SegTable t, float* work, TkDev d, TkOut out, const StepCtl* ctl,
                                                        size_t par_stride) {
-  __shared__ float sval[GB_TILE];
-  __shared__ int32_t sidx[GB_TILE];
+  extern __shared__ __align__(128) unsigned char tk_dyn[];
+  float* sw = reinterpret_cast<float*>(tk_dyn);                                 // [TK_STAGES][GB_TILE] tiles of `work`
+  float* sval = sw + TK_STAGES * GB_TILE;                                       // [3][TK_STAGE_CAP]
+  int32_t* sidx = reinterpret_cast<int32_t*>(sval + 3 * TK_STAGE_CAP);          // [3][TK_STAGE_CAP]
   __shared__ uint32_t sh1[1024];
-  __shared__ int scount[2];
-  __shared__ int sbegin, s_last;
+  __shared__ __align__(16) int4 sdesc[TK_DCACHE];
+  __shared__ __align__(8) uint64_t full[TK_STAGES];
+  __shared__ int scnt[3], s_tc[3], s_begin[3], s_len[3], s_local0[3], s_ovcnt[3];
+  __shared__ uint32_t s_bin[3];
+  __shared__ long long s_base[3];
+  __shared__ int s_last;
   const size_t psh = (ctl->epoch & 1) ? par_stride : 0;       // parity of the device-side epoch selects the slot
   const int t0 = (int)((int64_t)blockIdx.x * t.ntiles / gridDim.x);
   const int t1 = (int)((int64_t)(blockIdx.x + 1) * t.ntiles / gridDim.x);
   if (t0 >= t1) return;
   for (int b = threadIdx.x; b < 1024; b += GB_THREADS) sh1[b] = 0;
-  if (threadIdx.x < 2) scount[threadIdx.x] = 0;
+  if (threadIdx.x < 3) scnt[threadIdx.x] = 0;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < TK_STAGES; ++s) tk_mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  int dbase = t0;
+  tk_fill_descs(t, sdesc, dbase, t1);
   __syncthreads();
-  const int lane = threadIdx.x & 31;
-  int cur = t.tile_seg[t0];
+  auto issue = [&](int tile, int s) {                               // one thread
+    const TkTile x = tk_desc(sdesc, tile - dbase);
+    const uint32_t bytes = (uint32_t)((x.len + 3) & ~3) * 4u;
+    tk_mbar_expect_tx(&full[s], bytes);
+    tk_bulk_load(sw + s * GB_TILE, work + x.base, bytes, &full[s]);
+  };
+  if (threadIdx.x == 0)
+    for (int s = 0; s < TK_STAGES && t0 + s < t1; ++s) issue(t0 + s, s);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int cur = tk_desc(sdesc, 0).seg;
   uint32_t bin = d.sel[cur * TK_SEL + S_BIN];
   int mine = 0;
+  auto extend = [&](bool found, uint32_t b1, uint32_t rem) {          // thread 0: threshold prefix 11 -> 21 bits
+    uint32_t* s = d.sel + cur * TK_SEL;
+    if (found) { s[S_BIN] = (bin << 10) | b1; s[S_KREM] = rem; }
+    else s[S_FLAGS] = TKF_TAKEALL;                 // only zeros are left in the bin: they would add nothing
+  };
   auto close_segment = [&]() {
     __syncthreads();
+    uint32_t b1, rem, cnt;
+    const uint32_t krem = d.sel[cur * TK_SEL + S_KREM];
+    if (t.seg_tile0[cur] >= t0 && t.seg_tile0[cur + 1] <= t1) {     // tensor local to this CTA: no global histogram
+      const bool found = cta_select<1024, false>(sh1, krem, b1, rem, cnt);
+      if (threadIdx.x == 0) extend(found, b1, rem);
+      mine = 0;
+      return;
+    }
     uint32_t* hg = d.hist1 + (size_t)cur * 1024;
     for (int b = threadIdx.x; b < 1024; b += GB_THREADS) {
       const uint32_t c = sh1[b];
       if (c) atomicAdd(hg + b, c);
       sh1[b] = 0;
     }
-    __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
+      __threadfence();
       const uint32_t total = (uint32_t)(t.seg_tile0[cur + 1] - t.seg_tile0[cur]);
       const uint32_t old = atomicAdd(d.segdone + cur * 4 + 1, (uint32_t)mine);
       s_last = (old + (uint32_t)mine == total);
@@ -277,101 +393,106 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
     __syncthreads();
     if (s_last) {                                  // tensor complete: extend the threshold prefix by 10 bits
       __threadfence();
-      uint32_t* s = d.sel + cur * TK_SEL;
-      uint32_t b1, rem, cnt;
-      const bool found = cta_select<1024>(hg, s[S_KREM], b1, rem, cnt);
-      if (threadIdx.x == 0) {
-        if (found) { s[S_BIN] = (s[S_BIN] << 10) | b1; s[S_KREM] = rem; }
-        else s[S_FLAGS] = TKF_TAKEALL;             // only zeros are left in the bin: they would add nothing
-        d.segdone[cur * 4 + 1] = 0;
-      }
+      const bool found = cta_select<1024, true>(hg, krem, b1, rem, cnt);
+      if (threadIdx.x == 0) { extend(found, b1, rem); d.segdone[cur * 4 + 1] = 0; }
     }
     mine = 0;
   };
-  for (int tile = t0; tile < t1; ++tile) {
-    int seg, local0, len;
-    int64_t base;
-    tile_bounds(t, tile, seg, base, local0, len);
-    if (seg != cur) { close_segment(); cur = seg; bin = d.sel[cur * TK_SEL + S_BIN]; }
-    ++mine;
-    const int par = (tile - t0) & 1;
-    float vv[4][4];
-    if (len == GB_TILE) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float4 v = *reinterpret_cast<const float4*>(work + base + (j * GB_THREADS + threadIdx.x) * 4);
-        vv[j][0] = v.x; vv[j][1] = v.y; vv[j][2] = v.z; vv[j][3] = v.w;
+  // stores the staged certain picks of the tile in buffer b into every peer's payload and zeroes them in place;
+  // its range was claimed by thread 0 one barrier earlier
+  auto copy_out = [&](int b) {
+    const int tc = s_tc[b], begin = s_begin[b];
+    if (tc == 0) return;
+    const int64_t tb = (int64_t)s_base[b];
+    const int l0 = s_local0[b];
+    if (tc <= TK_STAGE_CAP) {
+      const float* sv = sval + b * TK_STAGE_CAP;
+      const int32_t* si = sidx + b * TK_STAGE_CAP;
+      for (int i = threadIdx.x; i < tc; i += GB_THREADS) {
+        const float v = sv[i];
+        const int32_t ix = si[i];
+        TK_PEERS(r) { TK_VALS(out, r, psh)[begin + i] = v; TK_IDX(out, r, psh)[begin + i] = ix; }
+        if (ZERO) work[tb + (ix - l0)] = 0.f;
       }
     } else {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) vv[j][q] = (e0 + q < len) ? work[base + e0 + q] : 0.f;     // zero fill: never picked, never marked
+      // crowded tile: more certain picks than the staging buffer holds -> re-read the tile from memory
+      const int len = s_len[b];
+      const uint32_t tbin = s_bin[b];
+      for (int e = threadIdx.x; e < len; e += GB_THREADS) {
+        const float v = __ldcg(work + tb + e);
+        if ((tk_absbits(v) >> 20) > tbin) {
+          const int pos = begin + atomicAdd(&s_ovcnt[b], 1);
+          TK_PEERS(r) { TK_VALS(out, r, psh)[pos] = v; TK_IDX(out, r, psh)[pos] = l0 + e; }
+          if (ZERO) work[tb + e] = 0.f;
+        }
       }
     }
+  };
+  int it = 0;
+  for (int tile = t0; tile < t1; ++tile, ++it) {
+    const int st = it % TK_STAGES;
+    const uint32_t par = (uint32_t)(it / TK_STAGES) & 1u;
+    const int b = it % 3;
+    if (tile + TK_STAGES >= dbase + TK_DCACHE && dbase + TK_DCACHE < t1) {      // refill the descriptor cache (rare)
+      __syncthreads();
+      dbase = tile;
+      tk_fill_descs(t, sdesc, dbase, t1);
+      __syncthreads();
+    }
+    const TkTile x = tk_desc(sdesc, tile - dbase);
+    const int seg = x.seg, len = x.len, local0 = x.local0;
+    const int64_t base = x.base;
+    if (seg != cur) { close_segment(); cur = seg; bin = d.sel[cur * TK_SEL + S_BIN]; }
+    ++mine;
+    tk_mbar_wait(&full[st], par);
+    const float4* w4 = reinterpret_cast<const float4*>(sw + st * GB_TILE);
+    const uint32_t lo_def = (bin + 1u) << 20;                // |x| bits >= lo_def: a higher bin, certain pick
+    const uint32_t lo_cand = bin ? (bin << 20) : 1u;         // threshold bin; exact zeros never matter
     uint32_t* mrow = d.mask + (size_t)tile * 128;
+    float* sv = sval + b * TK_STAGE_CAP;
+    int32_t* si = sidx + b * TK_STAGE_CAP;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
-      uint32_t dm = 0, cm = 0;
+      uint32_t cm = 0;
+      if (e0 < len) {
+        const float4 v = w4[j * GB_THREADS + threadIdx.x];
+        const uint32_t b0 = tk_absbits(v.x), b1 = e0 + 1 < len ? tk_absbits(v.y) : 0u, b2 = e0 + 2 < len ? tk_absbits(v.z) : 0u,
+                       b3 = e0 + 3 < len ? tk_absbits(v.w) : 0u;
+        if (max(max(b0, b1), max(b2, b3)) >= lo_cand) {      // ~7 % of the float4s: the rest is neither picked nor marked
+          const uint32_t bb[4] = {b0, b1, b2, b3};
+          const float vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const uint32_t b = tk_absbits(vv[j][q]);
-        const uint32_t hi = b >> 20;
-        dm |= (hi > bin ? 1u : 0u) << q;
-        cm |= ((hi == bin && b != 0u) ? 1u : 0u) << q;
-      }
-      // mask word = 8 consecutive threads x 4 elements
-      uint32_t w = cm << ((lane & 7) * 4);
-      w |= __shfl_xor_sync(0xffffffffu, w, 1);
-      w |= __shfl_xor_sync(0xffffffffu, w, 2);
-      w |= __shfl_xor_sync(0xffffffffu, w, 4);
-      if ((lane & 7) == 0) mrow[(j * GB_THREADS + threadIdx.x) >> 3] = w;
-      if (cm) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-          if ((cm >> q) & 1u) atomicAdd(&sh1[(tk_absbits(vv[j][q]) >> 10) & 1023u], 1u);
-      }
-      if (dm) {                                    // rare (< k per tensor): one shared-memory atomic per pick
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          if ((dm >> q) & 1u) {
-            const int pos = atomicAdd(&scount[par], 1);
-            sval[pos] = vv[j][q];
-            sidx[pos] = local0 + e0 + q;
-            vv[j][q] = 0.f;
-          }
-        }
-        if (ZERO) {
-          if (len == GB_TILE) {
-            *reinterpret_cast<float4*>(work + base + e0) = make_float4(vv[j][0], vv[j][1], vv[j][2], vv[j][3]);
-          } else {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) if ((dm >> q) & 1u) work[base + e0 + q] = 0.f;
+          for (int q = 0; q < 4; ++q) {
+            if (bb[q] >= lo_def) {
+              const int pos = atomicAdd(&scnt[b], 1);
+              if (pos < TK_STAGE_CAP) { sv[pos] = vv[q]; si[pos] = local0 + e0 + q; }
+            } else if (bb[q] >= lo_cand) {
+              cm |= 1u << q;
+              atomicAdd(&sh1[(bb[q] >> 10) & 1023u], 1u);
+            }
           }
         }
       }
+      const uint32_t m0 = __ballot_sync(0xffffffffu, cm & 1u), m1 = __ballot_sync(0xffffffffu, cm & 2u),
+                     m2 = __ballot_sync(0xffffffffu, cm & 4u), m3 = __ballot_sync(0xffffffffu, cm & 8u);
+      if (lane == 0) *reinterpret_cast<uint4*>(mrow + (j * 8 + wid) * 4) = make_uint4(m0, m1, m2, m3);
     }
-    __syncthreads();
+    __syncthreads();      // tile staged, stage st consumed, and every thread has stored the previous tile's picks
     if (threadIdx.x == 0) {
-      const int tc = scount[par];
-      const int begin = (int)t.seg_kbase[seg] + (int)atomicAdd(d.sel + seg * TK_SEL + S_CURA, (uint32_t)tc);
-      sbegin = begin;
-      scount[par ^ 1] = 0;
+      if (tile + TK_STAGES < t1) issue(tile + TK_STAGES, st);
+      const int tc = scnt[b];
+      int begin = 0;
+      if (tc) begin = (int)t.seg_kbase[seg] + (int)atomicAdd(d.sel + seg * TK_SEL + S_CURA, (uint32_t)tc);
+      s_tc[b] = tc; s_begin[b] = begin; s_len[b] = len; s_local0[b] = local0; s_bin[b] = bin; s_base[b] = (long long)base;
+      scnt[(b + 2) % 3] = 0;                       // buffer of the tile after the next one (its last user is stored by now)
+      s_ovcnt[b] = 0;
       TK_PEERS(r) TK_HDR(out, r, psh)[tile] = make_int2(begin, tc);
     }
-    __syncthreads();
-    const int tc = scount[par], begin = sbegin;
-    if (tc) {
-      TK_PEERS(r) {
-        float* dv = TK_VALS(out, r, psh) + begin;
-        int32_t* di = TK_IDX(out, r, psh) + begin;
-        for (int i = threadIdx.x; i < tc; i += GB_THREADS) { dv[i] = sval[i]; di[i] = sidx[i]; }
-      }
-    }
-    __syncthreads();
+    if (it > 0) copy_out((it - 1) % 3);            // overlaps thread 0's claim for this tile
   }
+  __syncthreads();
+  copy_out((it - 1) % 3);
   close_segment();
 }
 
@@ -398,14 +519,13 @@ __device__ __forceinline__ int tk_build_list(const uint32_t mw[4], int lane, uin
   const int total = __shfl_sync(0xffffffffu, inc, 31);
   if (total <= TK_LIST) {
     int o = inc - mine;
+    uint32_t u = mw[0] | mw[1] | mw[2] | mw[3];
+    while (u) {                                   // index order: l ascending, then q
+      const int l = __ffs(u) - 1;
+      u &= u - 1;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      uint32_t w = mw[i];
-      while (w) {
-        const int bit = __ffs(w) - 1;
-        w &= w - 1;
-        pos[o++] = (uint16_t)(lane * 128 + i * 32 + bit);
-      }
+      for (int q = 0; q < 4; ++q)
+        if ((mw[q] >> l) & 1u) pos[o++] = (uint16_t)(lane * 128 + 4 * l + q);
     }
   }
   __syncwarp();
@@ -416,13 +536,17 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_refine(SegTable t, const float
   __shared__ uint16_t s_pos[TK_WPT][TK_LIST];
   int tile, seg, local0, len;
   int64_t base;
+  const int lane = threadIdx.x & 31;
+  // the mask row does not depend on the tile descriptor: both loads are in flight together, then one 16-byte load
+  // fetches the tensor's selection state (three dependent memory latencies per warp instead of six)
+  const int tile_guess = min(blockIdx.x * TK_WPT + (threadIdx.x >> 5), t.ntiles - 1);
+  const uint4 m = *reinterpret_cast<const uint4*>(d.mask + (size_t)tile_guess * 128 + lane * 4);
   if (!tk_tile(t, tile, seg, base, local0, len)) return;
   uint32_t* s = d.sel + seg * TK_SEL;
-  if (s[S_FLAGS] & TKF_TAKEALL) return;
-  const int lane = threadIdx.x & 31;
+  const uint4 s0 = *reinterpret_cast<const uint4*>(s);         // BIN, KREM, CURA, FLAGS
+  if (s0.w & TKF_TAKEALL) return;
   uint16_t* pos = s_pos[threadIdx.x >> 5];
-  const uint32_t prefix = s[S_BIN];                            // 21 bits
-  const uint4 m = *reinterpret_cast<const uint4*>(d.mask + (size_t)tile * 128 + lane * 4);
+  const uint32_t prefix = s0.x;                                // 21 bits
   const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
   uint32_t* h2 = d.hist2 + (size_t)seg * 1024;
   const int total = tk_build_list(mw, lane, pos);
@@ -445,23 +569,25 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_refine(SegTable t, const float
       while (w) {
         const int bit = __ffs(w) - 1;
         w &= w - 1;
-        const uint32_t key = tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit));
+        const uint32_t key = tk_absbits(__ldcg(work + base + lane * 128 + 4 * bit + i));
         if ((key >> 10) == prefix) atomicAdd(h2 + (key & 1023u), 1u);
       }
     }
   }
-  __threadfence();
-  __syncwarp();
-  int last = 0;
-  if (lane == 0) {
-    const uint32_t total_tiles = (uint32_t)(t.seg_tile0[seg + 1] - t.seg_tile0[seg]);
-    last = atomicAdd(d.segdone + seg * 4 + 2, 1u) == total_tiles - 1;
+  __syncwarp();                                                // orders the lanes' atomics before lane 0's (cumulative) fence
+  const uint32_t total_tiles = (uint32_t)(t.seg_tile0[seg + 1] - t.seg_tile0[seg]);
+  int last = total_tiles == 1;                                 // a one-tile tensor needs no counter
+  if (!last) {
+    if (lane == 0) {
+      __threadfence();
+      last = atomicAdd(d.segdone + seg * 4 + 2, 1u) == total_tiles - 1;
+    }
+    last = __shfl_sync(0xffffffffu, last, 0);
   }
-  last = __shfl_sync(0xffffffffu, last, 0);
   if (last) {                                                  // this warp finished the tensor: exact threshold
     __threadfence();
     uint32_t b2 = 0, take = 0, cnt = 0;
-    const bool found = warp_select1024(h2, s[S_KREM], b2, take, cnt);
+    const bool found = warp_select1024(h2, s0.y, b2, take, cnt);
     if (lane == 0) {
       if (found) {
         s[S_THR] = (prefix << 10) | b2;
@@ -470,7 +596,7 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_refine(SegTable t, const float
       } else {
         s[S_FLAGS] = TKF_TAKEALL;                              // cannot happen (the prefix bin holds >= KREM values); safe
       }
-      d.segdone[seg * 4 + 2] = 0;
+      if (total_tiles != 1) d.segdone[seg * 4 + 2] = 0;
     }
   }
 }
@@ -481,7 +607,8 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_ties(SegTable t, const float* 
   int64_t base;
   if (!tk_tile(t, tile, seg, base, local0, len)) return;
   const uint32_t* s = d.sel + seg * TK_SEL;
-  if (!(s[S_FLAGS] & TKF_AMBIG)) return;
+  const uint4 s0 = *reinterpret_cast<const uint4*>(s);
+  if (!(s0.w & TKF_AMBIG)) return;
   const int lane = threadIdx.x & 31;
   uint16_t* pos = s_pos[threadIdx.x >> 5];
   const uint32_t thr = s[S_THR];
@@ -507,7 +634,7 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_ties(SegTable t, const float* 
       while (w) {
         const int bit = __ffs(w) - 1;
         w &= w - 1;
-        c += tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit)) == thr;
+        c += tk_absbits(__ldcg(work + base + lane * 128 + 4 * bit + i)) == thr;
       }
     }
   }
@@ -548,15 +675,18 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work
   const size_t psh = (epoch & 1) ? par_stride : 0;
   int tile, seg, local0, len;
   int64_t base;
+  const int tile_guess = min(blockIdx.x * TK_WPT + (threadIdx.x >> 5), t.ntiles - 1);
+  const uint4 m = *reinterpret_cast<const uint4*>(d.mask + (size_t)tile_guess * 128 + (threadIdx.x & 31) * 4);
   if (tk_tile(t, tile, seg, base, local0, len)) {
     uint32_t* s = d.sel + seg * TK_SEL;
     const int lane = threadIdx.x & 31;
     uint16_t* pos = s_pos[threadIdx.x >> 5];
     float* val = s_val[threadIdx.x >> 5];
-    const uint32_t flags = s[S_FLAGS], thr = s[S_THR];
-    const int take = (int)s[S_TAKE];
+    const uint4 s0 = *reinterpret_cast<const uint4*>(s);       // BIN, KREM, CURA, FLAGS
+    const uint2 s1 = *reinterpret_cast<const uint2*>(s + 4);   // THR, TAKE
+    const uint32_t flags = s0.w, thr = s1.x;
+    const int take = (int)s1.y;
     const bool takeall = flags & TKF_TAKEALL, ambig = flags & TKF_AMBIG;
-    const uint4 m = *reinterpret_cast<const uint4*>(d.mask + (size_t)tile * 128 + lane * 4);
     const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
     const int xoff = t.ntiles + 1;
     const int nmarked = tk_build_list(mw, lane, pos);
@@ -613,25 +743,25 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work
         if (ZERO) work[base + e] = 0.f;
       }
     } else {
-      // crowded tile (many values share the threshold bin): walk the mask lane by lane.  Lanes own 128 consecutive
-      // elements, so lane order x bit order = index order.
+      // crowded tile (many values share the threshold bin): walk the mask lane by lane.  A lane owns 128 consecutive
+      // elements; word q, bit l is element 4 l + q, so index order is l ascending, then q.
       uint32_t gt[4] = {0, 0, 0, 0}, eq[4] = {0, 0, 0, 0};
       int neq = 0;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        uint32_t w = mw[i];
+      for (int q = 0; q < 4; ++q) {
+        uint32_t w = mw[q];
         while (w) {
-          const int bit = __ffs(w) - 1;
+          const int l = __ffs(w) - 1;
           w &= w - 1;
-          const uint32_t key = tk_absbits(__ldcg(work + base + lane * 128 + i * 32 + bit));
-          if (takeall || key > thr) gt[i] |= 1u << bit;
-          else if (key == thr) { eq[i] |= 1u << bit; ++neq; }
+          const uint32_t key = tk_absbits(__ldcg(work + base + lane * 128 + 4 * l + q));
+          if (takeall || key > thr) gt[q] |= 1u << l;
+          else if (key == thr) { eq[q] |= 1u << l; ++neq; }
         }
       }
       uint32_t ch[4] = {gt[0], gt[1], gt[2], gt[3]};
       if (!ambig) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) ch[i] |= eq[i];
+        for (int q = 0; q < 4; ++q) ch[q] |= eq[q];
       } else {
         int inc = neq;
 #pragma unroll
@@ -640,14 +770,16 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work
           if (lane >= o) inc += n;
         }
         int rank = d.tiecnt[tile] + inc - neq;                 // ties before this lane's first element
+        uint32_t u = eq[0] | eq[1] | eq[2] | eq[3];
+        while (u) {
+          const int l = __ffs(u) - 1;
+          u &= u - 1;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          uint32_t w = eq[i];
-          while (w) {
-            const int bit = __ffs(w) - 1;
-            w &= w - 1;
-            if (rank < take) ch[i] |= 1u << bit;
-            ++rank;
+          for (int q = 0; q < 4; ++q) {
+            if ((eq[q] >> l) & 1u) {
+              if (rank < take) ch[q] |= 1u << l;
+              ++rank;
+            }
           }
         }
       }
@@ -667,12 +799,12 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work
       begin = __shfl_sync(0xffffffffu, begin, 0);
       int p = begin + inc - mine;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        uint32_t w = ch[i];
+      for (int q = 0; q < 4; ++q) {
+        uint32_t w = ch[q];
         while (w) {
-          const int bit = __ffs(w) - 1;
+          const int l = __ffs(w) - 1;
           w &= w - 1;
-          const int e = lane * 128 + i * 32 + bit;
+          const int e = lane * 128 + 4 * l + q;
           const float v = __ldcg(work + base + e);
           TK_PEERS(r) { TK_VALS(out, r, psh)[p] = v; TK_IDX(out, r, psh)[p] = local0 + e; }
           if (ZERO) work[base + e] = 0.f;
@@ -687,7 +819,15 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work
 // ---------------------------------------------------------------- host side
 #define TK_LAUNCHED(p) do { (p)->launches++; GB_CUDA(cudaGetLastError()); } while (0)
 
+#define TK_SMEM_P1 (TK_STAGES * GB_TILE * 4)
+#define TK_SMEM_P1W (2 * TK_STAGES * GB_TILE * 4)
+#define TK_SMEM_P2 (TK_STAGES * GB_TILE * 4 + 3 * TK_STAGE_CAP * 8)
+
 int tk_init(gb_plan* p) {
+  GB_CUDA(cudaFuncSetAttribute(tk_pass1<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM_P1W));
+  GB_CUDA(cudaFuncSetAttribute(tk_pass1<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM_P1));
+  GB_CUDA(cudaFuncSetAttribute(tk_pass2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM_P2));
+  GB_CUDA(cudaFuncSetAttribute(tk_pass2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM_P2));
   TkHost* h = new TkHost();
   memset(h, 0, sizeof(*h));
   p->topk2 = h;
@@ -733,13 +873,13 @@ int tk_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
     out.idx[r] = (int32_t*)(s + p->hdr_bytes + per);
   }
   out.n = c->world;
-  const int grid = std::min(p->ntiles, 148 * 4);
+  const int grid = std::min(p->ntiles, 148 * 2);            // two resident CTAs per SM, each with a 3-stage tile pipeline
   const int wgrid = (p->ntiles + TK_WPT - 1) / TK_WPT;
-  if (mem) tk_pass1<true><<<grid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, p->prm.beta, p->prm.gamma, h->d, p->d_ctl);
-  else tk_pass1<false><<<grid, GB_THREADS, 0, st>>>(p->tab, d_grad, work, p->prm.beta, p->prm.gamma, h->d, p->d_ctl);
+  if (mem) tk_pass1<true><<<grid, GB_THREADS, TK_SMEM_P1W, st>>>(p->tab, d_grad, work, p->prm.beta, p->prm.gamma, h->d, p->d_ctl);
+  else tk_pass1<false><<<grid, GB_THREADS, TK_SMEM_P1, st>>>(p->tab, d_grad, work, p->prm.beta, p->prm.gamma, h->d, p->d_ctl);
   TK_LAUNCHED(p);
-  if (mem) tk_pass2<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, h->d, out, p->d_ctl, p->par_stride);
-  else tk_pass2<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, h->d, out, p->d_ctl, p->par_stride);
+  if (mem) tk_pass2<true><<<grid, GB_THREADS, TK_SMEM_P2, st>>>(p->tab, work, h->d, out, p->d_ctl, p->par_stride);
+  else tk_pass2<false><<<grid, GB_THREADS, TK_SMEM_P2, st>>>(p->tab, work, h->d, out, p->d_ctl, p->par_stride);
   TK_LAUNCHED(p);
   tk_refine<<<wgrid, TK_WPT * 32, 0, st>>>(p->tab, work, h->d);
   TK_LAUNCHED(p);
