@@ -543,10 +543,13 @@ template <bool EXTRAS, int NW>
 __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, float* out, float divisor, PeerPtrs peers,
                                                        int channel, const StepCtl* ctl, size_t par_stride, uint32_t* status,
                                                        uint64_t timeout_ns, int wait) {
-  __shared__ float acc[GB_TILE];
+  __shared__ __align__(16) float acc[GB_TILE];
   const uint32_t epoch = ctl->epoch;
   if (epoch & 1) shift(in, par_stride);
+  // the accumulator tile starts at zero and is put back to zero by the write-out below: two barriers per tile
+  for (int i = threadIdx.x; i < GB_TILE; i += GB_THREADS) acc[i] = 0.f;
   if (wait) wait_all_ranks(peers, channel, epoch, status, timeout_ns);
+  else __syncthreads();
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
@@ -572,8 +575,6 @@ __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, 
         pv[r] = in.vals[r][h[r].x + threadIdx.x];
       }
     }
-    for (int i = threadIdx.x; i < GB_TILE; i += GB_THREADS) acc[i] = 0.f;
-    __syncthreads();
 #pragma unroll
     for (int r = 0; r < NW; ++r) {
       if (r < in.n) {
@@ -599,8 +600,9 @@ __global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, 
 #pragma unroll
     for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
       const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      float4 v = *reinterpret_cast<const float4*>(acc + e0);
+      *reinterpret_cast<float4*>(acc + e0) = make_float4(0.f, 0.f, 0.f, 0.f);
       if (e0 >= len) continue;
-      float4 v = make_float4(acc[e0], acc[e0 + 1], acc[e0 + 2], acc[e0 + 3]);
       if (divisor != 1.f) {          // torch's CUDA tensor / python-scalar is a multiply by the reciprocal
         const float inv = __fdiv_rn(1.0f, divisor);
         v.x = __fmul_rn(v.x, inv); v.y = __fmul_rn(v.y, inv);

@@ -55,7 +55,8 @@ __device__ __forceinline__ void release_flags_last_block(uint32_t* done, PeerPtr
   // system-scope fence (fences are cumulative), so 255 threads do not each wait for a membar.sys.
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence_system();
+    if (peers.world == 1) __threadfence();         // nothing left this GPU: device scope is enough
+    else __threadfence_system();
     uint32_t ticket = atomicAdd(done, 1u);
     if (ticket == gridDim.x - 1) {
       __threadfence_system();
