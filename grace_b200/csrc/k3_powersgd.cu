@@ -806,6 +806,14 @@ extern "C" int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream) {
   return 0;
 }
 
+// one-warp wait for every rank's P tiles (which = 0) or Q tiles (which = 1) of the current exchange (see gb_plan_wait)
+extern "C" int gb_psgd_wait(gb_psgd* p, int which, void* stream) {
+  if (p->comm->world == 1) return 0;
+  gb_launch_wait(p->comm, which == 0 ? p->chan_p : p->chan_q, p->d_ctl, (cudaStream_t)stream);
+  LAUNCHED(p);
+  return 0;
+}
+
 // phase 2: reduce + orthogonalise P, Q_r = M^T P^, push Q tiles, release flags
 extern "C" int gb_psgd_mid(gb_psgd* p, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;

@@ -47,6 +47,7 @@ size_t k0_slot_bytes(int64_t padded, int world, int bits);
 // at the head of every send advances the block on the device.
 struct StepCtl { uint32_t epoch, step, next_step, pad; };
 void gb_launch_tick(StepCtl* ctl, cudaStream_t st);       // plan.cu
+void gb_launch_wait(gb_comm* c, int channel, const StepCtl* ctl, cudaStream_t st);   // plan.cu: one-warp flag wait
 
 // Last-block-done flag release shared by the send kernels: every CTA calls this after its
 // final peer store; the CTA that arrives last publishes `epoch` to all peers.

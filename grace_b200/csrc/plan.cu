@@ -290,6 +290,27 @@ extern "C" int gb_plan_recv(gb_plan* p, float* d_out, void* stream) {
   return gb_codec_is_sparse(p->prm.codec) ? k1_recv(p, d_out, st) : k2_recv(p, d_out, st);
 }
 
+// One warp polls the peers' flags of the current exchange.  Enqueued in front of the receive kernels, it keeps their
+// (large) grids from occupying SM slots while a slower rank is still sending -- the receive side can then be queued
+// right behind its send and overlap the rest of backward (the receive kernels' own waits pass immediately).
+__global__ void gb_wait_kernel(PeerPtrs peers, int channel, const StepCtl* ctl, uint32_t* status, uint64_t timeout_ns) {
+  const uint32_t epoch = ctl->epoch;
+  if (threadIdx.x < peers.world)
+    wait_flag(gb_flag(peers.base[peers.rank], channel, epoch & 1, threadIdx.x), epoch, status, timeout_ns);
+}
+void gb_launch_wait(gb_comm* c, int channel, const StepCtl* ctl, cudaStream_t st) {
+  gb_wait_kernel<<<1, 32, 0, st>>>(gb_comm_peers(c), channel, ctl, c->status_dev, c->timeout_ns);
+}
+
+extern "C" int gb_plan_wait(gb_plan* p, void* stream) {
+  if (p->comm->world == 1) return 0;
+  GB_CHECK(p->epoch > 0, "gb_plan_wait before any gb_plan_send");
+  gb_launch_wait(p->comm, p->channel, p->d_ctl, (cudaStream_t)stream);
+  p->launches++;
+  GB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // Optional middle phase (only the dense two-shot path has one): lets a caller enqueue every
 // bucket's reduce before any bucket's gather.  gb_plan_recv runs it itself when skipped.
 extern "C" int gb_plan_mid(gb_plan* p, void* stream) {

@@ -84,6 +84,8 @@ def _declare(L):
         "gb_plan_send": (i32, [vp, vp, vp]),
         "gb_plan_recv": (i32, [vp, vp, vp]),
         "gb_plan_mid": (i32, [vp, vp]),
+        "gb_plan_wait": (i32, [vp, vp]),
+        "gb_psgd_wait": (i32, [vp, i32, vp]),
         "gb_plan_state": (i32, [vp, i32, P(vp), P(sz)]),
         "gb_plan_state_read": (i32, [vp, i32, vp, vp]),
         "gb_plan_state_write": (i32, [vp, i32, vp, vp]),

@@ -167,6 +167,10 @@ class Plan:
     def mid(self, stream=None):
         check(native.lib().gb_plan_mid(self._h, _stream_ptr(stream)))
 
+    def wait(self, stream=None):
+        """One-warp wait for the peers' flags of the exchange in flight (keeps the receive grids off the SMs)."""
+        check(native.lib().gb_plan_wait(self._h, _stream_ptr(stream)))
+
     def recv(self, out: torch.Tensor, stream=None):
         assert out.is_cuda and out.dtype == torch.float32 and out.numel() >= self.padded
         check(native.lib().gb_plan_recv(self._h, C.c_void_p(out.data_ptr()), _stream_ptr(stream)))
@@ -250,6 +254,9 @@ class PowerSGDPlan:
     def mid(self, stream=None):
         check(native.lib().gb_psgd_mid(self._h, _stream_ptr(stream)))
 
+    def wait(self, which=0, stream=None):
+        check(native.lib().gb_psgd_wait(self._h, int(which), _stream_ptr(stream)))
+
     def recv(self, out, stream=None):
         assert out.is_cuda and out.dtype == torch.float32 and out.numel() >= self.padded
         check(native.lib().gb_psgd_recv(self._h, C.c_void_p(out.data_ptr()), _stream_ptr(stream)))
@@ -307,6 +314,9 @@ class NvlsPlan:
 
     def signal(self, stream=None):
         check(native.lib().gb_nvls_signal(self._h, _stream_ptr(stream)))
+
+    def wait(self, stream=None):
+        pass
 
     def reduce(self, stream=None):
         check(native.lib().gb_nvls_reduce(self._h, C.c_void_p(self.mc), 1 if self.average else 0, _stream_ptr(stream)))

@@ -214,6 +214,12 @@ class _Bucket:
     def recv(self, stream):
         self.plan.recv(self.flat, stream=stream)
 
+    def receive_all(self, stream):
+        """Whole receive side of this bucket on ``stream``: a one-warp flag wait, then the kernels."""
+        self.plan.wait(stream=stream)
+        self.mid(stream)
+        self.recv(stream)
+
 
 class _PowerSGDBucket(_Bucket):
     """>=2-D gradients go through the native PowerSGD plan (K3), 1-D ones through a dense plan."""
@@ -268,6 +274,19 @@ class _PowerSGDBucket(_Bucket):
         if self.dense is not None:
             self.dense.recv(self.flat_v, stream=stream)
 
+    def receive_all(self, stream):
+        if self.psgd is not None:
+            self.psgd.wait(0, stream=stream)
+            self.psgd.mid(stream=stream)
+        if self.dense is not None:
+            self.dense.wait(stream=stream)
+            self.dense.mid(stream=stream)
+        if self.psgd is not None:
+            self.psgd.wait(1, stream=stream)
+            self.psgd.recv(self.flat_m, stream=stream)
+        if self.dense is not None:
+            self.dense.recv(self.flat_v, stream=stream)
+
 
 class _NvlsBucket(_Bucket):
     """Dense (None codec) bucket whose flat gradient buffer is a symmetric allocation bound to an
@@ -308,6 +327,9 @@ class _NvlsBucket(_Bucket):
     def recv(self, stream):
         self.plan.reduce(stream=stream)
 
+    def receive_all(self, stream):
+        self.plan.reduce(stream=stream)
+
 
 def _all_ranks_agree(ok):
     import torch.distributed as dist
@@ -344,18 +366,28 @@ class FusedDP:
         numels = [p.numel() for _, p in named if p.requires_grad]
         self.engine = get_engine(estimate_arena_bytes(numels, params, powersgd, world))
         self.passes = optimizer.backward_passes_per_step
-        self.side = torch.cuda.Stream()
+        self.side = torch.cuda.Stream()                   # sends (compensate + compress + peer stores)
+        self.side_recv = torch.cuda.Stream()              # receives: queued behind their send, overlap the rest of backward
+        self.overlap_recv = os.environ.get("GRACE_B200_OVERLAP_RECV", "1") != "0"
         self.transport = "p2p-store"                      # or "nvls-multimem" for dense buckets on NVLS hosts
         self.nvls_error = None
         bucket_bytes = bucket_bytes or DEFAULT_BUCKET_BYTES
         trainable = [(n, p) for n, p in named if p.requires_grad]
         # gradients become ready roughly in reverse registration order
         order = list(reversed(trainable))
+        # the last bucket's exchange cannot overlap backward (its gradients are the last to arrive): keep it small
+        tail_bytes = int(os.environ.get("GRACE_B200_TAIL_BUCKET_MB", "4")) << 20
+        total_bytes = sum(p.numel() * 4 for _, p in order)
+        tail_start = total_bytes - tail_bytes if total_bytes > 2 * tail_bytes else total_bytes + 1
         self.buckets: List[_Bucket] = []
-        cur, cur_bytes = [], 0
+        cur, cur_bytes, seen = [], 0, 0
         for n, p in order:
+            if cur and seen < tail_start <= seen + p.numel() * 4 and cur_bytes >= tail_bytes:
+                self.buckets.append(self._make_bucket(cur, params, powersgd))
+                cur, cur_bytes = [], 0
             cur.append((n, p))
             cur_bytes += p.numel() * 4
+            seen += p.numel() * 4
             if cur_bytes >= bucket_bytes:
                 self.buckets.append(self._make_bucket(cur, params, powersgd))
                 cur, cur_bytes = [], 0
@@ -432,6 +464,14 @@ class FusedDP:
         self.side.wait_event(ready)
         b.send(self.side)
         b.sent = True
+        if self.overlap_recv:
+            # receive side right behind the send, on its own stream: a one-warp kernel waits for the peers' flags,
+            # then decode + aggregate land in the bucket while backward still runs for the other buckets
+            sent = torch.cuda.Event()
+            sent.record(self.side)
+            self.side_recv.wait_event(sent)
+            b.receive_all(self.side_recv)
+            b.received = True
 
     # ------------------------------------------------------------------ optimizer side
     def synchronize(self):
@@ -439,14 +479,21 @@ class FusedDP:
         for b in self.buckets:
             if not b.sent:
                 self._send(b)
+        late = [b for b in self.buckets if not getattr(b, "received", False)]
+        if late:
+            sent = torch.cuda.Event()
+            sent.record(self.side)
+            self.side_recv.wait_event(sent)
+            for b in late:
+                b.mid(self.side_recv)                   # PowerSGD / dense two-shot: middle phase of every bucket first
+            for b in late:
+                b.recv(self.side_recv)                  # aggregate lands in the same views the optimizer reads
         for b in self.buckets:
-            b.mid(self.side)                            # PowerSGD only: reduce P, second GEMM, push Q
-        for b in self.buckets:
-            b.recv(self.side)                           # aggregate lands in the same views the optimizer reads
             b.sent = False
+            b.received = False
             b.pending = len(b.tensors)
         done = torch.cuda.Event()
-        done.record(self.side)
+        done.record(self.side_recv)
         torch.cuda.current_stream().wait_event(done)
         if self._lowp:
             torch._foreach_copy_([p.grad for p in self._lowp], self._lowp_views)

@@ -116,6 +116,11 @@ int gb_plan_send(gb_plan* p, const float* d_grad, void* stream);
 /* optional middle phase: the dense two-shot all-reduce (None/FP16 codec, world > 1) reduces its shard
  * here; a no-op for every other codec; gb_plan_recv runs it itself if the caller did not */
 int gb_plan_mid(gb_plan* p, void* stream);
+/* one warp polls every rank's flag of the current exchange (no-op at world size 1).  Enqueued before gb_plan_mid /
+ * gb_plan_recv it lets a caller queue the receive side right behind the send, overlapping the rest of backward,
+ * without the receive kernels' grids occupying SMs while a slower rank is still sending.  The reference receives
+ * everything after backward (patch_files/horovod/torch/__init__.py:143-161). */
+int gb_plan_wait(gb_plan* p, void* stream);
 /* wait for all ranks' flags, decode, aggregate; writes every element of d_out exactly once */
 int gb_plan_recv(gb_plan* p, float* d_out, void* stream);
 /* state access for state_dict(): which = 0 residual / dgc v, 1 momentum / dgc u */
@@ -151,6 +156,7 @@ int gb_psgd_destroy(gb_psgd* p);
 int64_t gb_psgd_padded_numel(gb_psgd* p);
 int gb_psgd_offsets(gb_psgd* p, int64_t* out);
 int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream);
+int gb_psgd_wait(gb_psgd* p, int which /* 0: P tiles, 1: Q tiles */, void* stream);
 int gb_psgd_mid(gb_psgd* p, void* stream);
 int gb_psgd_recv(gb_psgd* p, float* d_out, void* stream);
 int gb_psgd_launches(gb_psgd* p, int64_t* out);

@@ -143,6 +143,73 @@ def main():
         if not same_on_all_ranks(got):
             failures.append("dense all-reduce (%s): ranks disagree" % transport)
 
+    # PowerSGD (K3): tile-wise peer pushes of P and Q from the GEMM epilogues -- fused DistributedOptimizer against the
+    # generic cuBLAS + NCCL path (tf32 tolerance), replicas bit-identical; and the bucketed dist API (step_all)
+    def train_psgd(fused):
+        torch.manual_seed(0)
+        model = MnistNet().cuda().eval()
+        opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.5)
+        hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+        grc = hvd.grace_from_params(dict(compressor="powersgd", memory="powersgd", communicator="allreduce", compress_rank=4))
+        opt = hvd.DistributedOptimizer(opt, grc, named_parameters=model.named_parameters(), fused=fused, bucket_bytes=40000)
+        gen = torch.Generator(device="cuda").manual_seed(5 + rank)
+        for _ in range(4):
+            x = torch.randn(16, 1, 28, 28, device="cuda", generator=gen)
+            y = torch.randint(0, 10, (16,), device="cuda", generator=gen)
+            opt.zero_grad()
+            F.nll_loss(model(x), y).backward()
+            opt.step()
+        return torch.cat([p.detach().flatten() for p in model.parameters()])
+
+    qf, qg = train_psgd(True), train_psgd(False)
+    if not same_on_all_ranks(qf):
+        failures.append("PowerSGD fused DistributedOptimizer: replicas diverged")
+    rel = float((qf - qg).norm() / qg.norm())
+    if rel > 3e-2:
+        failures.append("PowerSGD fused vs generic differ by %g (relative)" % rel)
+
+    for comp, mem, comm, tol in (("topk", "residual", "allgather", 0.0), ("qsgd", "none", "allgather", 5e-3),
+                                 ("powersgd", "powersgd", "allreduce", 5e-2), ("signsgd", "none", "allgather", 0.0)):
+        prm = dict(compressor=comp, memory=mem, communicator=comm, world_size=world, compress_ratio=0.02, quantum_num=64,
+                   compress_rank=4)
+        fast, slow = grace_from_params(prm), grace_from_params(prm)
+        slow.fused = False
+        gen = torch.Generator(device="cuda").manual_seed(31 + rank)
+        for step in range(2):
+            named = [(n, torch.randn(sh, device="cuda", generator=gen) * 0.05) for n, sh in shapes.items()]
+            outs = fast.step_all([(n, g.clone()) for n, g in named])
+            for (n, g), a in zip(named, outs):
+                b = slow.step(g.clone(), n)
+                err = float((a - b).norm()) / max(float(b.norm()), 1e-12)
+                if err > tol + 1e-6:
+                    failures.append("step_all %s step %d %s: relative error %g" % (comp, step, n, err))
+                if not same_on_all_ranks(a.contiguous()):
+                    failures.append("step_all %s step %d %s: ranks disagree" % (comp, step, n))
+        if not (fast._stepper is not None and fast._stepper.enabled):
+            failures.append("step_all %s did not take the native path" % comp)
+        fast.close()
+
+    # whole step as one CUDA graph (forward + backward + overlapped exchange + optimizer): replicas stay identical
+    def train_graphed():
+        torch.manual_seed(0)
+        model = MnistNet().cuda().eval()
+        opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.5)
+        hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+        grc = hvd.grace_from_params(dict(compressor="topk", memory="residual", communicator="allgather", compress_ratio=0.01))
+        opt = hvd.DistributedOptimizer(opt, grc, named_parameters=model.named_parameters(), fused=True, bucket_bytes=40000)
+        gen = torch.Generator(device="cuda").manual_seed(5 + rank)
+        xs = [torch.randn(16, 1, 28, 28, device="cuda", generator=gen) for _ in range(5)]
+        ys = [torch.randint(0, 10, (16,), device="cuda", generator=gen) for _ in range(5)]
+        step = hvd.GraphedStep(model, opt, lambda m, x, y: F.nll_loss(m(x), y), [xs[0], ys[0]], amp_dtype=None, warmup=2)
+        for x, y in zip(xs, ys):
+            step(x, y)
+        torch.cuda.synchronize()
+        return torch.cat([p.detach().flatten() for p in model.parameters()])
+
+    gp = train_graphed()
+    if not same_on_all_ranks(gp):
+        failures.append("GraphedStep: replicas diverged")
+
     pf, pg = train(True), train(False)
     if not same_on_all_ranks(pf):
         failures.append("fused DistributedOptimizer: replicas diverged")
