@@ -96,4 +96,6 @@ struct gb_plan {
   void* adaq;            // AdaQ buffers (k1_adaq.cu)
   void* topk2;           // two-pass TopK buffers (k1_topk2.cu)
   uint32_t* d_samp;      // DGC: sampled magnitudes (k1_sparse.cu)
+  size_t chan2_off, slot2_bytes;   // DGC gradient clipping: per-tensor sum(g^2) of every rank (channel2's slots)
+  bool presend_done;     // gb_plan_presend already ran for the exchange being sent
 };

@@ -806,6 +806,97 @@ __global__ void __launch_bounds__(GB_THREADS) k1_dgc_accumulate(SegTable t, cons
   }
 }
 
+// ---- DgcMemory gradient clipping (memory/dgc.py:17-20): clamp g to +-sqrt(sum_r sum(g_r^2) / W) per tensor.
+// k1_dgc_sqsum: per-tile partial sums in double; the last CTA adds each tensor's tiles in tile order (deterministic)
+// and stores the W-th part of the scalar all-reduce -- this rank's nseg floats -- into every peer, then releases the
+// flags of the plan's second channel.  k1_dgc_accumulate_clip waits for all ranks' scalars, sums them in rank order
+// (identical on every rank), clamps, and applies the momentum correction + accumulation in the same pass.
+struct ClipOut { float* slot[GB_MAX_WORLD]; int n; };
+struct ClipIn { const float* slot[GB_MAX_WORLD]; int n; };
+
+__global__ void __launch_bounds__(GB_THREADS) k1_dgc_sqsum(SegTable t, const float* __restrict__ grad, double* tilesum, ClipOut out,
+                                                          uint32_t* done, PeerPtrs peers, int channel2, const StepCtl* ctl,
+                                                          size_t par_stride2) {
+  __shared__ double sh[GB_THREADS / 32];
+  __shared__ int s_last;
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    double acc = 0.0;
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      const float4 g = load4(grad + base, e0, len);
+      acc += (double)g.x * g.x + (double)g.y * g.y + (double)g.z * g.z + (double)g.w * g.w;
+    }
+    acc = warp_sum_d(acc);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double s = 0.0;
+      for (int w = 0; w < GB_THREADS / 32; ++w) s += sh[w];
+      tilesum[tile] = s;
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    s_last = atomicAdd(done, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const uint32_t epoch = ctl->epoch;
+  const size_t sh2 = (epoch & 1) ? par_stride2 : 0;
+  for (int seg = threadIdx.x; seg < t.nseg; seg += GB_THREADS) {
+    double s = 0.0;
+    for (int tile = t.seg_tile0[seg]; tile < t.seg_tile0[seg + 1]; ++tile) s += __ldcg(tilesum + tile);
+    const float f = (float)s;
+    for (int r = 0; r < out.n; ++r) ((float*)((char*)out.slot[r] + sh2))[seg] = f;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (peers.world == 1) __threadfence(); else __threadfence_system();
+    for (int r = 0; r < peers.world; ++r) st_release_sys(gb_flag(peers.base[r], channel2, epoch & 1, peers.rank), epoch);
+    *done = 0;
+  }
+}
+
+__global__ void __launch_bounds__(GB_THREADS) k1_dgc_accumulate_clip(SegTable t, const float* __restrict__ grad, float* v, float* u,
+                                                                    float momentum, ClipIn in, float world_f, PeerPtrs peers,
+                                                                    int channel2, const StepCtl* ctl, size_t par_stride2,
+                                                                    uint32_t* status, uint64_t timeout_ns) {
+  const uint32_t epoch = ctl->epoch;
+  const size_t sh2 = (epoch & 1) ? par_stride2 : 0;
+  wait_all_ranks(peers, channel2, epoch, status, timeout_ns);
+  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    float sq = 0.f;
+    for (int r = 0; r < in.n; ++r) sq = __fadd_rn(sq, __ldcg((const float*)((const char*)in.slot[r] + sh2) + seg));   // rank order
+    const float clip = __fsqrt_rn(__fdiv_rn(sq, world_f));
+#pragma unroll
+    for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      if (e0 >= len) continue;
+      float4 g = load4(grad + base, e0, len);
+      g.x = fmaxf(fminf(g.x, clip), -clip); g.y = fmaxf(fminf(g.y, clip), -clip);
+      g.z = fmaxf(fminf(g.z, clip), -clip); g.w = fmaxf(fminf(g.w, clip), -clip);
+      float4 uu = load4(u + base, e0, len);
+      float4 vv = load4(v + base, e0, len);
+      uu.x = __fadd_rn(__fmul_rn(momentum, uu.x), g.x); uu.y = __fadd_rn(__fmul_rn(momentum, uu.y), g.y);
+      uu.z = __fadd_rn(__fmul_rn(momentum, uu.z), g.z); uu.w = __fadd_rn(__fmul_rn(momentum, uu.w), g.w);
+      vv.x = __fadd_rn(vv.x, uu.x); vv.y = __fadd_rn(vv.y, uu.y); vv.z = __fadd_rn(vv.z, uu.z); vv.w = __fadd_rn(vv.w, uu.w);
+      store4(u + base, e0, len, uu);
+      store4(v + base, e0, len, vv);
+    }
+  }
+}
+
 // Sampling with replacement (Philox stream 1), one thread per sample on a (chunk, tensor) grid: magnitudes of
 // max(1, int(0.01 n)) positions go to a scratch list (seg_k = samples per tensor, seg_kbase = their offsets).
 __global__ void __launch_bounds__(GB_THREADS) k1_dgc_gather(SegTable t, const float* __restrict__ v, uint32_t seed, const StepCtl* ctl,
@@ -923,6 +1014,17 @@ __global__ void __launch_bounds__(GB_THREADS) k1_dgc_count(SegTable t, const flo
 }
 
 
+int k1_dgc_presend(gb_plan* p, const float* d_grad, cudaStream_t st) {
+  gb_comm* c = p->comm;
+  ClipOut out;
+  for (int r = 0; r < c->world; ++r) out.slot[r] = (float*)gb_slot_of(c, r, p->chan2_off, p->slot2_bytes, 0, c->rank);
+  out.n = c->world;
+  k1_dgc_sqsum<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, (double*)p->d_tilestats, out, p->d_done + 6, gb_comm_peers(c),
+                                                          p->channel2, p->d_ctl, (size_t)c->world * p->slot2_bytes);
+  LAUNCHED(p);
+  return 0;
+}
+
 static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   gb_comm* c = p->comm;
   GB_CHECK(p->prm.memory == GB_MEM_DGC || p->prm.memory == GB_MEM_NONE || p->prm.memory == GB_MEM_RESIDUAL,
@@ -936,7 +1038,17 @@ static int k1_dgc_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   const int grid = grid_for(p->ntiles);
   float* work;
   float* work2 = nullptr;
-  if (p->prm.memory == GB_MEM_DGC) {
+  if (p->prm.memory == GB_MEM_DGC && p->slot2_bytes) {
+    ClipIn in;
+    for (int r = 0; r < c->world; ++r) in.slot[r] = (const float*)gb_slot_of(c, c->rank, p->chan2_off, p->slot2_bytes, 0, r);
+    in.n = c->world;
+    k1_dgc_accumulate_clip<<<grid, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, p->d_state1, p->prm.momentum, in,
+                                                       (float)c->world, peers, p->channel2, ctl,
+                                                       (size_t)c->world * p->slot2_bytes, c->status_dev, c->timeout_ns);
+    LAUNCHED(p);
+    work = p->d_state0;
+    work2 = p->d_state1;
+  } else if (p->prm.memory == GB_MEM_DGC) {
     k1_dgc_accumulate<<<148 * 4, GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, p->d_state1, p->prm.momentum); LAUNCHED(p);
     work = p->d_state0;
     work2 = p->d_state1;

@@ -191,6 +191,14 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
     size_t unused;
     if (gb_comm_alloc_channel(c, 0, &p->channel2, &unused)) return -1;
   }
+  p->presend_done = false;
+  p->chan2_off = 0;
+  p->slot2_bytes = 0;
+  if (params->memory == GB_MEM_DGC && params->clip) {
+    // every rank's per-tensor sum(g^2) travels through a small channel of its own
+    p->slot2_bytes = ((size_t)nseg * 4 + 255) & ~size_t(255);
+    if (gb_comm_alloc_channel(c, p->slot2_bytes, &p->channel2, &p->chan2_off)) return -1;
+  }
   p->slot_bytes = (p->slot_bytes + 255) & ~size_t(255);
   p->par_stride = (size_t)c->world * p->slot_bytes;
   if (params->codec == GB_CODEC_SKETCH && sk_init(p)) return -1;
@@ -268,12 +276,26 @@ __global__ void gb_tick_kernel(StepCtl* c) {
 }
 void gb_launch_tick(StepCtl* ctl, cudaStream_t st) { gb_tick_kernel<<<1, 1, 0, st>>>(ctl); }
 
+int k1_dgc_presend(gb_plan* p, const float* d_grad, cudaStream_t st);   // k1_sparse.cu
+
+extern "C" int gb_plan_presend(gb_plan* p, const float* d_grad, void* stream) {
+  if (!p->slot2_bytes || p->presend_done) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  gb_launch_tick(p->d_ctl, st);
+  p->launches++;
+  if (k1_dgc_presend(p, d_grad, st)) return -1;
+  p->presend_done = true;
+  return 0;
+}
+
 extern "C" int gb_plan_send(gb_plan* p, const float* d_grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  if (!p->topk2) {                       // the two-pass TopK advances the step block in its first kernel
+  if (p->slot2_bytes && !p->presend_done && gb_plan_presend(p, d_grad, stream)) return -1;
+  if (!p->topk2 && !p->presend_done) {   // the two-pass TopK advances the step block in its first kernel
     gb_launch_tick(p->d_ctl, st);
     p->launches++;
   }
+  p->presend_done = false;
   int rc = p->prm.codec == GB_CODEC_SKETCH ? sk_send(p, d_grad, st) : p->prm.codec == GB_CODEC_ADAQ ? aq_send(p, d_grad, st) : p->prm.codec == GB_CODEC_INCEPTIONN ? in_send(p, d_grad, st) : p->dense2 ? k0_send(p, d_grad, st) : gb_codec_is_sparse(p->prm.codec) ? k1_send(p, d_grad, st) : k2_send(p, d_grad, st);
   if (rc) return rc;
   p->step++;

@@ -28,7 +28,7 @@ class CodecParams(C.Structure):
     _fields_ = [("ratio", C.c_double), ("codec", C.c_int32), ("memory", C.c_int32), ("beta", C.c_float),
                 ("gamma", C.c_float), ("threshold", C.c_float), ("quantum_num", C.c_int32), ("momentum", C.c_float),
                 ("lr", C.c_float), ("seed", C.c_uint32), ("average", C.c_int32), ("capacity", C.c_float),
-                ("one_minus_momentum", C.c_float)]
+                ("one_minus_momentum", C.c_float), ("clip", C.c_int32)]
 
 
 _lib = None
@@ -82,6 +82,7 @@ def _declare(L):
         "gb_plan_offsets": (i32, [vp, P(i64)]),
         "gb_plan_wire_bytes": (i64, [vp]),
         "gb_plan_send": (i32, [vp, vp, vp]),
+        "gb_plan_presend": (i32, [vp, vp, vp]),
         "gb_plan_recv": (i32, [vp, vp, vp]),
         "gb_plan_mid": (i32, [vp, vp]),
         "gb_plan_wait": (i32, [vp, vp]),

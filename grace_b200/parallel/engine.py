@@ -164,6 +164,11 @@ class Plan:
         assert grad.is_cuda and grad.dtype == torch.float32 and grad.numel() >= self.padded
         check(native.lib().gb_plan_send(self._h, C.c_void_p(grad.data_ptr()), _stream_ptr(stream)))
 
+    def presend(self, grad: torch.Tensor, stream=None):
+        """First half of ``send`` for plans whose send waits for the peers (DGC gradient clipping); only needed when
+        several ranks are driven from one stream (``Engine.local``)."""
+        check(native.lib().gb_plan_presend(self._h, C.c_void_p(grad.data_ptr()), _stream_ptr(stream)))
+
     def mid(self, stream=None):
         check(native.lib().gb_plan_mid(self._h, _stream_ptr(stream)))
 

@@ -150,8 +150,9 @@ def codec_params(compressor, memory):
         p.memory, p.beta, p.gamma = MEMORY["residual"], memory.beta, memory.gamma
     elif m is M.EFSignSGDMemory:
         p.memory, p.beta, p.gamma = MEMORY["residual"], 1.0, memory.learning_rate
-    elif m is M.DgcMemory and t is C.DgcCompressor and not memory.gradient_clipping:
+    elif m is M.DgcMemory and t is C.DgcCompressor:
         p.memory, p.momentum = MEMORY["dgc"], memory.momentum
+        p.clip = 1 if memory.gradient_clipping else 0      # truthy, as in the reference (the dist helper passes 0.3)
     else:
         return None
     return p

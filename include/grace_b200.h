@@ -65,6 +65,8 @@ typedef struct gb_codec_params {
   int32_t average;         /* divide the aggregate by world size                       */
   float capacity;          /* variable-size codecs: slot capacity as a fraction of numel (0 -> 1.0) */
   float one_minus_momentum;/* signum: (float)(1.0 - momentum) evaluated in double like python; 0 -> 1.0f - momentum */
+  int32_t clip;            /* dgc memory: clamp the gradient to +-sqrt(sum over ranks of sum(g^2) / W) per tensor
+                              (memory/dgc.py:17-20, the dist helper's default) before the momentum correction      */
 } gb_codec_params;
 
 const char* gb_last_error(void);
@@ -113,6 +115,11 @@ int gb_plan_offsets(gb_plan* p, int64_t* out /* [nseg] element offsets into the 
 int64_t gb_plan_wire_bytes(gb_plan* p);        /* payload bytes one rank sends to one peer */
 /* compensate + compress + store into every peer's slot + release flags */
 int gb_plan_send(gb_plan* p, const float* d_grad, void* stream);
+/* Optional first half of gb_plan_send for plans whose send itself waits for the peers (DGC with gradient clipping:
+ * every rank needs all ranks' sum(g^2) before it can clamp).  It advances the step and pushes this rank's scalars;
+ * the following gb_plan_send then continues from there.  Only needed when several ranks are driven from one
+ * stream (single-GPU emulation): all ranks' presend first, then all ranks' send.  A no-op for every other plan. */
+int gb_plan_presend(gb_plan* p, const float* d_grad, void* stream);
 /* optional middle phase: the dense two-shot all-reduce (None/FP16 codec, world > 1) reduces its shard
  * here; a no-op for every other codec; gb_plan_recv runs it itself if the caller did not */
 int gb_plan_mid(gb_plan* p, void* stream);

@@ -168,6 +168,26 @@ def main():
     if rel > 3e-2:
         failures.append("PowerSGD fused vs generic differ by %g (relative)" % rel)
 
+    # the dist helper's default DGC memory clips (gradient_clipping = 0.3 -> truthy): native scalar all-reduce
+    prm = dict(compressor="dgc", memory="dgc", communicator="allgather", world_size=world, compress_ratio=0.05)
+    fast, slow = grace_from_params(prm), grace_from_params(prm)
+    slow.fused = False
+    assert fast.memory.gradient_clipping
+    gen = torch.Generator(device="cuda").manual_seed(19 + rank)
+    for step in range(3):
+        for name, shape in shapes.items():
+            g = torch.randn(shape, device="cuda", generator=gen)
+            a = fast.step(g.clone(), name)
+            b = slow.step(g.clone(), name)
+            bad = float(((a - b).abs() > 1e-6 + 1e-5 * b.abs()).float().mean())
+            if bad > 0.01:
+                failures.append("dgc+clip step %d %s: %.4f of the elements differ" % (step, name, bad))
+            if not same_on_all_ranks(a):
+                failures.append("dgc+clip step %d %s: ranks disagree" % (step, name))
+    if not (fast._stepper is not None and fast._stepper.enabled):
+        failures.append("dgc with clipping did not take the native path")
+    fast.close()
+
     for comp, mem, comm, tol in (("topk", "residual", "allgather", 0.0), ("qsgd", "none", "allgather", 5e-3),
                                  ("powersgd", "powersgd", "allreduce", 5e-2), ("signsgd", "none", "allgather", 0.0)):
         prm = dict(compressor=comp, memory=mem, communicator=comm, world_size=world, compress_ratio=0.02, quantum_num=64,

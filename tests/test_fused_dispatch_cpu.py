@@ -32,7 +32,8 @@ def test_memory_mapping_and_hyperparameters():
     assert p.memory == MEMORY["residual"] and p.beta == 1.0 and abs(p.gamma - 0.3) < 1e-7 and p.average == 0
     p = codec_params(C.DgcCompressor(0.01), M.DgcMemory(0.9, False, 4))
     assert p.memory == MEMORY["dgc"] and abs(p.momentum - 0.9) < 1e-7
-    assert codec_params(C.DgcCompressor(0.01), M.DgcMemory(0.9, True, 4)) is None      # clipping: generic path
+    clipped = codec_params(C.DgcCompressor(0.01), M.DgcMemory(0.9, 0.3, 4))            # the dist helper's default (truthy 0.3)
+    assert clipped is not None and clipped.clip == 1                                   # native: scalar all-reduce on the engine
     assert codec_params(C.TopKCompressor(0.01), M.DgcMemory(0.9, False, 4)) is None    # DGC memory needs DGC codec
 
 

@@ -54,6 +54,8 @@ def run_fused(world, params, grads_per_step, sizes=None, names=None, arena_bytes
         for grads in grads_per_step:
             bufs = [_flat(plans[r], grads[r]) for r in range(world)]
             for r in range(world):
+                plans[r].presend(bufs[r])           # only DGC with clipping has one (its send waits for the peers)
+            for r in range(world):
                 plans[r].send(bufs[r])
             for r in range(world):
                 plans[r].mid()
@@ -176,6 +178,50 @@ def test_dgc_with_dgc_memory(world):
         for i, name in enumerate(NAMES):
             assert torch.equal(states[r][0][i], mems[r].gradients[name].reshape(-1))
             assert torch.equal(states[r][1][i], mems[r].residuals[name].reshape(-1))
+
+
+@pytest.mark.parametrize("world", [1, 2, 3])
+def test_dgc_with_gradient_clipping(world):
+    """DgcMemory(gradient_clipping=True) -- the dist helper's default (helper.py:60-62) -- stays native: the per-tensor
+    sum(g^2) is all-reduced through the engine's flags (one float per tensor per rank), the clamp is fused into the
+    momentum pass.  The kernel sums g^2 in double, torch in float: clip values agree to an ulp, so values are compared
+    with a tolerance and a few threshold flips are allowed."""
+    grads = make_grads(world, 3)
+    prm = _params("dgc", "dgc", ratio=0.05, momentum=0.9)
+    prm.clip = 1
+    fused, states = run_fused(world, prm, grads)
+    # the oracle's all-reduce: sum the ranks' scalars in rank order
+    pending = {}
+
+    def make_mem():
+        mem = M.DgcMemory(0.9, True, world)
+        return mem
+    comps = [C.DgcCompressor(0.05, seed=SEED) for _ in range(world)]
+    mems = [make_mem() for _ in range(world)]
+    oracle = []
+    for step in grads:
+        out = [[None] * len(SIZES) for _ in range(world)]
+        for i, name in enumerate(NAMES):
+            total = sum(torch.sum(step[r][i] * step[r][i]) for r in range(world))
+            payloads, ctxs = [], []
+            for r in range(world):
+                mems[r]._allreduce_sum = lambda t, total=total: total
+                x = mems[r].compensate(step[r][i], name)
+                pl, ctx = comps[r].compress(x, name)
+                mems[r].update(x, name, comps[r], pl, ctx)
+                payloads.append(pl); ctxs.append(ctx)
+            for r in range(world):
+                dec = [comps[r].decompress(pl, ctxs[r]) for pl in payloads]
+                out[r][i] = comps[r].aggregate(dec) / world
+        oracle.append(out)
+    assert_same(fused, oracle, exact=False, frac=0.01, rtol=1e-5, atol=1e-6, what="dgc+clip")
+    for s in fused:
+        for r in range(1, world):
+            for a, b in zip(s[0], s[r]):
+                assert torch.equal(a, b)            # all ranks hold the same aggregate
+    if world > 1:                                   # the clamp is active: the 1-element tensor of the largest rank is cut
+        clip = torch.sqrt(sum(grads[0][r][4] ** 2 for r in range(world)) / world)
+        assert any(float(grads[0][r][4].abs()) > float(clip) for r in range(world))
 
 
 @pytest.mark.parametrize("world", [1, 2, 4])
