@@ -1,8 +1,10 @@
 #!/usr/bin/env python
 """CIFAR10 DAWNBench-style ResNet-9 with the torch.distributed-style manual loop (workload of the
 reference's ``examples/dist/CIFAR10-dawndist/{dawn,core}.py``): piecewise-linear LR, Nesterov SGD,
-batch 512, after ``backward()`` one ``grc.step(grad, name)`` per parameter.  Synthetic CIFAR-shaped
-data unless ``--data-dir`` holds the real set.
+batch 512, Crop/FlipLR/Cutout augmentation, TableLogger + ``logs.tsv``, DAWN timing (evaluation excluded).  After
+``backward()`` the gradients are exchanged through the torch.distributed-flavour API: ``grc.step_all(named_grads)``,
+the bucketed form of the reference's ``for name, p: grc.step(p.grad, name)`` loop (``core.py:202-208``;
+``--per-tensor`` runs that loop literally).  Synthetic CIFAR-shaped data unless ``--data-dir`` holds the real set.
 
   torchrun --standalone --nproc-per-node 2 examples/dist/cifar10_dawn.py --epochs 2
 """
@@ -18,7 +20,8 @@ import torch.nn.functional as F
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", ".."))
 from grace_b200.dist import grace_from_params  # noqa: E402
 from grace_b200.models import resnet9  # noqa: E402
-from grace_b200.utils.metrics import TableLogger  # noqa: E402
+from grace_b200.utils.augment import DawnAugment, normalise, pad_reflect  # noqa: E402
+from grace_b200.utils.metrics import TableLogger, Timer, TSVLogger  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--epochs", type=int, default=24)
@@ -33,6 +36,8 @@ ap.add_argument("--compress-ratio", "--compress_ratio", dest="compress_ratio", t
 # flags of the reference's dawn.py:8-22, accepted so its command lines keep working (the reference parses most of them
 # and then ignores them in favour of hard-coded params, dawn.py:125-127; here they are honoured)
 ap.add_argument("--log_dir", default=".")
+ap.add_argument("--per-tensor", action="store_true", help="exchange with one grc.step per parameter (the reference loop)")
+ap.add_argument("--no-augment", action="store_true")
 ap.add_argument("--master_address", "-m", default="127.0.0.1")
 ap.add_argument("--rank", "-r", type=int, default=None)
 ap.add_argument("--world_size", "-w", type=int, default=None)
@@ -56,26 +61,35 @@ torch.manual_seed(0)
 
 
 def load():
+    """uint8 NHWC images + labels: the real CIFAR10 when --data-dir has it, else a synthetic set of the same shape."""
     try:
         import torchvision
         tr = torchvision.datasets.CIFAR10(args.data_dir, train=True, download=False)
         te = torchvision.datasets.CIFAR10(args.data_dir, train=False, download=False)
-        f = lambda d: (torch.tensor(d.data).permute(0, 3, 1, 2).float() / 255, torch.tensor(d.targets))
+        f = lambda d: (torch.tensor(d.data), torch.tensor(d.targets))
         return f(tr), f(te)
     except Exception:
         g = torch.Generator().manual_seed(1)
         def fake(n):
             y = torch.randint(0, 10, (n,), generator=g)
-            x = torch.rand(n, 3, 32, 32, generator=g) * 0.5
+            x = torch.rand(n, 32, 32, 3, generator=g) * 0.5
             for c in range(10):
-                x[y == c, c % 3, 3 * c:3 * c + 5, :] += 0.5
-            return x, y
+                x[y == c, 3 * c:3 * c + 5, :, c % 3] += 0.5
+            return (x * 255).to(torch.uint8), y
         return fake(8192), fake(2048)
 
 
+timer = Timer(synch=torch.cuda.synchronize if device.type == "cuda" else None)
 (train_x, train_y), (test_x, test_y) = load()
-mean, std = train_x.mean((0, 2, 3), keepdim=True), train_x.std((0, 2, 3), keepdim=True)
-train_x, test_x = (train_x - mean) / std, (test_x - mean) / std
+# reference preprocessing (core.py:50-62, dawn.py:105-108): normalise with the CIFAR10 statistics, reflect-pad the
+# training images by 4, NCHW -- once, on the device; the augmentation then crops 32x32 windows out of the padded set
+train_x = pad_reflect(normalise(train_x.to(device)), 4)
+test_x = normalise(test_x.to(device))
+train_y, test_y = train_y.to(device), test_y.to(device)
+augment = DawnAugment(crop=(32, 32), cutout=(8, 8), flip=True,
+                      generator=torch.Generator(device=device).manual_seed(1000 + int(os.environ.get("RANK", 0))))
+if os.environ.get("RANK", "0") == "0":
+    print("Preprocessing finished in %.2f seconds" % timer())
 model = resnet9().to(device).to(memory_format=torch.channels_last)
 if world > 1:
     for p in model.parameters():
@@ -87,31 +101,44 @@ grc = grace_from_params({"compressor": args.compressor, "memory": args.memory, "
                          "compress_ratio": args.compress_ratio, "world_size": world, "threshold": args.threshold,
                          "quantum_num": args.qstates, "lr": args.efsgdlr, "momentum": args.momentum,
                          "gradient_clipping": args.clipping})
-table = TableLogger(rank=rank)
-t0 = time.time()
+table, tsv = TableLogger(rank=rank), TSVLogger()
+named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
 for epoch in range(args.epochs):
     model.train()
-    perm = torch.randperm(len(train_x), generator=torch.Generator().manual_seed(epoch))
-    loss_sum = 0.0
+    perm = torch.randperm(len(train_x), generator=torch.Generator().manual_seed(epoch)).to(device)
+    loss_sum = torch.zeros((), device=device)
     for s in range(steps_per_epoch):
         idx = perm[(s * world + rank) * args.batch_size:(s * world + rank + 1) * args.batch_size]
-        x = train_x[idx].to(device).contiguous(memory_format=torch.channels_last)
-        y = train_y[idx].to(device)
+        x = train_x[idx]
+        x = (x[:, :, 4:36, 4:36] if args.no_augment else augment(x)).contiguous(memory_format=torch.channels_last)
+        y = train_y[idx]
         for g in opt.param_groups:
             g["lr"] = lr_at(epoch + s / steps_per_epoch) / args.batch_size
         opt.zero_grad(set_to_none=False)
         with torch.autocast(device.type, dtype=torch.bfloat16, enabled=device.type == "cuda"):
             loss = F.cross_entropy(model(x), y, reduction="sum")
         loss.backward()
-        for name, p in model.named_parameters():               # the reference's sequential exchange loop
-            p.grad.copy_(grc.step(p.grad, name))
+        if args.per_tensor:
+            for name, p in named:                              # the reference's sequential exchange loop
+                p.grad.copy_(grc.step(p.grad, name))
+        else:
+            grc.step_all([(n, p.grad) for n, p in named], inplace=True)      # same exchange, O(#buckets) launches
         opt.step()
-        loss_sum += float(loss.detach())
+        loss_sum += loss.detach()
+    train_time = timer()                                       # DAWN timing: training counts ...
     model.eval()
-    with torch.no_grad():
-        correct = sum(int((model(test_x[i:i + 1000].to(device)).argmax(1) == test_y[i:i + 1000].to(device)).sum())
-                      for i in range(0, len(test_x), 1000))
-    table.append({"epoch": epoch + 1, "lr": lr_at(epoch + 1), "train_loss": loss_sum / (steps_per_epoch * args.batch_size),
-                  "test_acc": correct / len(test_x), "total_time": time.time() - t0})
+    with torch.no_grad(), torch.autocast(device.type, dtype=torch.bfloat16, enabled=device.type == "cuda"):
+        correct = sum(int((model(test_x[i:i + 1000].contiguous(memory_format=torch.channels_last)).argmax(1)
+                           == test_y[i:i + 1000]).sum()) for i in range(0, len(test_x), 1000))
+    test_time = timer(include_in_total=False)                  # ... evaluation does not (dawn.py:129 test_time_in_total=False)
+    row = {"epoch": epoch + 1, "lr": lr_at(epoch + 1), "train_time": train_time,
+           "train_loss": float(loss_sum) / (steps_per_epoch * args.batch_size), "test_time": test_time,
+           "test_acc": correct / len(test_x), "total_time": timer.total_time}
+    table.append(row)
+    tsv.append(row)
+if rank == 0:
+    tsv.write(os.path.join(os.path.expanduser(args.log_dir), "logs.tsv"))
+if hasattr(grc, "close"):
+    grc.close()
 if world > 1:
     dist.destroy_process_group()

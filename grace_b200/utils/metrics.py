@@ -123,3 +123,43 @@ class TableLogger:
         if self.path:
             with open(self.path, "a") as f:
                 f.write(json.dumps(row) + "\n")
+
+
+class TSVLogger:
+    """DAWNBench submission log: ``epoch<TAB>hours<TAB>top1Accuracy`` per epoch (reference ``dawn.py:72-81``; written to
+    ``logs.tsv`` at the end of training, ``dawn.py:132-133``)."""
+
+    def __init__(self):
+        self.log = ["epoch\thours\ttop1Accuracy"]
+
+    def append(self, row):
+        self.log.append("%d\t%.8f\t%.2f" % (row["epoch"], row["total_time"] / 3600.0, row["test_acc"] * 100.0))
+
+    def __str__(self):
+        return "\n".join(self.log)
+
+    def write(self, path):
+        with open(path, "w") as f:
+            f.write(str(self))
+
+
+class Timer:
+    """Wall-clock timer that synchronises the device before every reading (reference ``core.py:14-27``):
+    ``timer()`` returns the time since the previous call and adds it to ``total_time`` unless told otherwise --
+    DAWNBench excludes evaluation (``test_time_in_total=False``, ``dawn.py:129``)."""
+
+    def __init__(self, synch=None):
+        import time
+        self._time = time.time
+        self.synch = synch or (lambda: None)
+        self.synch()
+        self.times = [self._time()]
+        self.total_time = 0.0
+
+    def __call__(self, include_in_total=True):
+        self.synch()
+        self.times.append(self._time())
+        delta = self.times[-1] - self.times[-2]
+        if include_in_total:
+            self.total_time += delta
+        return delta

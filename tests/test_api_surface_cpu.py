@@ -71,3 +71,39 @@ def test_constructor_signatures_match_the_reference():
     DgcMemory(0.9, False, 2)
     c = PowerSGDCompressor()
     PowerSGDMemory(c.q_memory, 1)
+
+
+def test_dawn_augmentation_matches_the_reference_transforms():
+    """Crop(32, 32) + FlipLR + Cutout(8, 8) of examples/dist/CIFAR10-dawndist/core.py:69-110, batched on the device:
+    every output is a 32x32 window of its padded source (possibly mirrored) with one 8x8 hole of zeros."""
+    import torch
+    from grace_b200.utils.augment import DawnAugment, normalise, pad_reflect
+    g = torch.Generator().manual_seed(0)
+    raw = torch.randint(1, 255, (16, 32, 32, 3), dtype=torch.uint8, generator=g)
+    x = normalise(raw)
+    assert x.shape == (16, 3, 32, 32) and abs(float(x.mean())) < 1.0
+    padded = pad_reflect(x, 4)
+    assert padded.shape == (16, 3, 40, 40) and torch.equal(padded[:, :, 4:36, 4:36], x)
+    out = DawnAugment(generator=g)(padded)
+    assert out.shape == (16, 3, 32, 32)
+    for i in range(16):
+        hole = (out[i] == 0).all(0)
+        assert int(hole.sum()) == 64                               # one 8x8 cut-out
+        found = False
+        for flip in (False, True):
+            src = padded[i].flip(2) if flip else padded[i]
+            windows = src.unfold(1, 32, 1).unfold(2, 32, 1)        # [3, 9, 9, 32, 32]
+            match = ((windows == out[i].view(3, 1, 1, 32, 32)) | hole.view(1, 1, 1, 32, 32)).all(-1).all(-1).all(0)
+            found = found or bool(match.any())
+        assert found
+
+
+def test_tsv_logger_and_timer():
+    from grace_b200.utils.metrics import Timer, TSVLogger
+    t = Timer()
+    a = t()
+    b = t(include_in_total=False)
+    assert a >= 0 and b >= 0 and abs(t.total_time - a) < 1e-9
+    log = TSVLogger()
+    log.append({"epoch": 3, "total_time": 7200.0, "test_acc": 0.9412})
+    assert str(log).splitlines() == ["epoch\thours\ttop1Accuracy", "3\t2.00000000\t94.12"]
