@@ -6,7 +6,7 @@ OUT="$HERE/../lib"
 mkdir -p "$OUT"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -Wall -Xcompiler -Wno-unknown-pragmas ${GB_NVCC_EXTRA}"
-SRCS="engine.cu plan.cu k1_sparse.cu k1_topk2.cu k1_adaq.cu k2_quant.cu k2_sketch.cu k2_inceptionn.cu"
+SRCS="engine.cu plan.cu ops.cu k1_sparse.cu k1_topk2.cu k1_adaq.cu k2_quant.cu k2_sketch.cu k2_inceptionn.cu"
 [ -f "$HERE/k0_dense.cu" ] && SRCS="$SRCS k0_dense.cu"
 [ -f "$HERE/k3_powersgd.cu" ] && SRCS="$SRCS k3_powersgd.cu"
 [ -f "$HERE/k1_static.cu" ] && SRCS="$SRCS k1_static.cu"

@@ -76,6 +76,12 @@ def _declare(L):
         "gb_handle_wait": (i32, [i64]),
         "gb_handle_stream_wait": (i32, [i64, vp]),
         "gb_handle_release": (i32, [i64]),
+        "gb_ops_create": (i32, [vp, sz, P(vp)]),
+        "gb_ops_destroy": (i32, [vp]),
+        "gb_ops_capacity": (sz, [vp]),
+        "gb_ops_launches": (i64, [vp]),
+        "gb_ops_send": (i32, [vp, vp, sz, vp]),
+        "gb_ops_recv": (i32, [vp, sz, i32, i32, sz, i32, C.c_double, vp, vp]),
         "gb_plan_create": (i32, [vp, i32, P(i64), P(u32), P(CodecParams), P(vp)]),
         "gb_plan_destroy": (i32, [vp]),
         "gb_plan_padded_numel": (i64, [vp]),

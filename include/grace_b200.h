@@ -106,6 +106,21 @@ int gb_handle_wait(int64_t handle);            /* blocks the host; releases the 
 int gb_handle_stream_wait(int64_t handle, void* stream);  /* make `stream` wait; keeps the handle */
 int gb_handle_release(int64_t handle);
 
+/* ---- point collectives for everything that is not a gradient bucket (reference: patch_files/horovod/torch/mpi_ops.py
+ * :157 allreduce_async_, :216 allgather_async, :362 broadcast_async_ over Horovod's core).  One op = gb_ops_send
+ * (store this rank's bytes into every peer, release the op's flag; NULL source = flag only) + gb_ops_recv (wait for
+ * all ranks, then mode 0: copy `count` ranks' payloads starting at `first` into d_out, `stride` bytes apart;
+ * mode 1/2/3/4: sum all ranks' payloads as float / double / int64 / int32 in rank order, times `scale`).
+ * Sizes are multiples of 16 bytes up to the capacity given at creation.  Issue the ops of one gb_ops on ONE stream. */
+typedef struct gb_ops gb_ops;
+int gb_ops_create(gb_comm* c, size_t slot_bytes, gb_ops** out);
+int gb_ops_destroy(gb_ops* o);
+size_t gb_ops_capacity(gb_ops* o);
+int64_t gb_ops_launches(gb_ops* o);
+int gb_ops_send(gb_ops* o, const void* d_src, size_t nbytes, void* stream);
+int gb_ops_recv(gb_ops* o, size_t nbytes, int first, int count, size_t stride, int mode, double scale, void* d_out,
+                void* stream);
+
 /* ---- plans: one gradient bucket, one compressed exchange */
 int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const uint32_t* name_hash,
                    const gb_codec_params* params, gb_plan** out);

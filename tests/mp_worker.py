@@ -230,6 +230,35 @@ def main():
     if not same_on_all_ranks(gp):
         failures.append("GraphedStep: replicas diverged")
 
+    # Horovod-style ops on CUDA tensors run on the engine (csrc/ops.cu), not through NCCL
+    from grace_b200.torch import mpi_ops
+    n0 = mpi_ops.native_op_launches()
+    x = torch.arange(1000, device="cuda", dtype=torch.float32) * (rank + 1)
+    got = hvd.allreduce(x, average=True)
+    want = torch.arange(1000, device="cuda", dtype=torch.float32) * (sum(range(1, world + 1)) / world)
+    if not torch.allclose(got, want, rtol=1e-6):
+        failures.append("native hvd.allreduce differs by %g" % float((got - want).abs().max()))
+    big = torch.full((3 << 20,), float(rank + 1), device="cuda")                    # > 4 MB: dense two-shot plan
+    got = hvd.allreduce(big, average=False)
+    if not torch.equal(got, torch.full_like(big, float(sum(range(1, world + 1))))):
+        failures.append("native large hvd.allreduce wrong")
+    rows = torch.full((rank + 1, 3), float(rank), device="cuda", dtype=torch.bfloat16)
+    got = hvd.allgather(rows)
+    want = torch.cat([torch.full((r + 1, 3), float(r), device="cuda", dtype=torch.bfloat16) for r in range(world)])
+    if got.shape != want.shape or not torch.equal(got, want):
+        failures.append("native hvd.allgather wrong: %s" % (tuple(got.shape),))
+    z = torch.full((7,), float(rank), device="cuda", dtype=torch.float64)
+    hvd.broadcast_(z, root_rank=world - 1)
+    if not torch.equal(z, torch.full_like(z, float(world - 1))):
+        failures.append("native hvd.broadcast_ wrong")
+    h = hvd.allreduce_async_(torch.ones(5, device="cuda", dtype=torch.int64) * rank, average=False)
+    while not hvd.poll(h):
+        pass
+    if int(hvd.synchronize(h)[0]) != sum(range(world)):
+        failures.append("native int64 allreduce wrong")
+    if mpi_ops.native_op_launches() <= n0:
+        failures.append("hvd ops on CUDA tensors did not take the native path")
+
     pf, pg = train(True), train(False)
     if not same_on_all_ranks(pf):
         failures.append("fused DistributedOptimizer: replicas diverged")

@@ -562,3 +562,68 @@ def test_degenerate_gradients_stay_finite(codec, memory):
     for st in states[0]:
         if st is not None:
             assert all(torch.isfinite(s).all() for s in st), codec
+
+
+@pytest.mark.parametrize("world", [1, 3])
+def test_point_collectives_over_the_arena(world):
+    """csrc/ops.cu, the native half of hvd.allreduce / allgather / broadcast (reference: Horovod core behind
+    patch_files/horovod/torch/mpi_ops.py:157,216,362): gather, broadcast and rank-ordered sums for the four element
+    types, several ops back to back on the same double-buffered slots."""
+    import ctypes as ct
+    from grace_b200.ops import native
+    from grace_b200.parallel.engine import Engine
+    L = native.lib()
+    engines = Engine.local(world, arena_bytes=32 << 20)
+    st = ct.c_void_p(torch.cuda.current_stream().cuda_stream)
+    try:
+        ops = []
+        for e in engines:
+            h = ct.c_void_p()
+            native.check(L.gb_ops_create(e._h, 1 << 20, ct.byref(h)))
+            ops.append(h)
+        g = torch.Generator(device="cuda").manual_seed(3)
+
+        def run(srcs, nbytes, first, count, stride, mode, scale, outs):
+            for r in range(world):
+                native.check(L.gb_ops_send(ops[r], ct.c_void_p(srcs[r].data_ptr() if srcs[r] is not None else 0), nbytes, st))
+            for r in range(world):
+                native.check(L.gb_ops_recv(ops[r], nbytes, first, count, stride, mode, ct.c_double(scale),
+                                           ct.c_void_p(outs[r].data_ptr()), st))
+            torch.cuda.synchronize()
+            for e in engines:
+                e.check_status()
+
+        for it in range(3):
+            n = 4096 + 4 * it
+            xs = [torch.randn(n, device="cuda", generator=g) for _ in range(world)]
+            outs = [torch.empty(n * world, device="cuda") for _ in range(world)]
+            run(xs, n * 4, 0, world, n * 4, 0, 1.0, outs)                       # all-gather
+            for o in outs:
+                assert torch.equal(o, torch.cat(xs))
+            root = it % world
+            outs = [torch.empty(n, device="cuda") for _ in range(world)]
+            run([xs[r] if r == root else None for r in range(world)], n * 4, root, 1, n * 4, 0, 1.0, outs)    # broadcast
+            for o in outs:
+                assert torch.equal(o, xs[root])
+            outs = [torch.empty(n, device="cuda") for _ in range(world)]
+            run(xs, n * 4, 0, world, n * 4, 1, 1.0 / world, outs)                # all-reduce (mean), rank order
+            want = xs[0].clone()
+            for x in xs[1:]:
+                want = want + x
+            want = want * torch.tensor(1.0 / world, device="cuda")
+            for o in outs:
+                assert torch.equal(o, want)
+        for dtype, mode in ((torch.float64, 2), (torch.int64, 3), (torch.int32, 4)):
+            xs = [(torch.randn(64, device="cuda", generator=g) * 100).to(dtype) for _ in range(world)]
+            outs = [torch.empty(64, dtype=dtype, device="cuda") for _ in range(world)]
+            run(xs, 64 * xs[0].element_size(), 0, world, 64 * xs[0].element_size(), mode, 1.0, outs)
+            want = xs[0].clone()
+            for x in xs[1:]:
+                want = want + x
+            for o in outs:
+                assert torch.equal(o, want)
+        for h in ops:
+            L.gb_ops_destroy(h)
+    finally:
+        for e in engines:
+            e.destroy()
