@@ -1,4 +1,4 @@
-// K3 -- PowerSGD (rank <= 4) as tcgen05/TMEM GEMMs fed by TMA, with the low-rank exchange
+// K3 -- PowerSGD (rank <= 16) as tcgen05/TMEM GEMMs fed by TMA, with the low-rank exchange
 // issued tile by tile from the GEMM epilogue.
 //
 // Reference: grace_dl/dist/compressor/powersgd.py:7-65 + memory/powersgd.py:12-37: per matrix
@@ -34,7 +34,7 @@
 #include <algorithm>
 #include <vector>
 
-#define PS_R 4           // max rank handled natively (columns per stored row)
+#define PS_RMAX 16       // max rank handled natively = UMMA N; rows of P / Q are stored with a pitch RP of 4, 8 or 16 floats
 #define PS_N 16          // UMMA N (rank padded to the minimum N for M=128)
 #define PS_BM 128        // UMMA M / rows of a tile in the GEMM's M dimension
 #define PS_BK 32         // K elements per pipeline stage (= one 128-byte swizzle row of tf32)
@@ -60,6 +60,8 @@ struct PsItem {         // one CTA of a grouped GEMM launch
 struct gb_psgd {
   gb_comm* comm;
   int nmat, rank_r, has_mem, use_tc;
+  int rp;                   // row pitch of the stored P / Q rows in floats: 4, 8 or 16 (rank rounded up)
+  float* d_qprev;           // warm start: the previous exchange's averaged Q [qrows][rp] (null: fresh Q every step)
   uint32_t seed, step, epoch;
   int64_t padded, prows, qrows;
   std::vector<PsMat> h_mat;
@@ -157,7 +159,7 @@ __device__ int g_dbg[8];   // {enable, lbo, sbo, k_step, a_major, dump, layout}
 __device__ float g_dbg_dump[8192];
 #endif
 
-template <int MODE>
+template <int MODE, int RP>
 __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ items, const PsMat* __restrict__ mats,
                                                   const CUtensorMap* __restrict__ maps, float* acc, uint32_t* tile_cnt,
                                                   PsPeers peers, const StepCtl* ctl, size_t par_stride) {
@@ -250,17 +252,21 @@ __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ ite
     const int row = it.m0 + q * 32 + lane;
     const int nrows = MODE == 1 ? mt.n : mt.m;
     const int row0 = MODE == 1 ? mt.prow0 : mt.qrow0;
-    float* dst = acc + (size_t)(row0 + row) * PS_R;
+    float* dst = acc + (size_t)(row0 + row) * RP;
     const bool live = row < nrows;
     if (it.nchunks == 1) {
       if (live) {
-        const float4 o = make_float4(__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3]));
-        for (int r = 0; r < peers.n; ++r) *reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * PS_R) = o;
+#pragma unroll
+        for (int c4 = 0; c4 < RP / 4; ++c4) {
+          const float4 o = make_float4(__uint_as_float(v[c4 * 4]), __uint_as_float(v[c4 * 4 + 1]), __uint_as_float(v[c4 * 4 + 2]),
+                                       __uint_as_float(v[c4 * 4 + 3]));
+          for (int r = 0; r < peers.n; ++r) reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP)[c4] = o;
+        }
       }
     } else {
       if (live) {
 #pragma unroll
-        for (int c = 0; c < PS_R; ++c) atomicAdd(dst + c, __uint_as_float(v[c]));
+        for (int c = 0; c < RP; ++c) atomicAdd(dst + c, __uint_as_float(v[c]));
       }
       __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -268,8 +274,11 @@ __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ ite
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (*last_flag && live) {                 // this CTA completed the tile: ship it to every peer
         __threadfence();
-        const float4 o = __ldcg(reinterpret_cast<const float4*>(dst));
-        for (int r = 0; r < peers.n; ++r) *reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * PS_R) = o;
+#pragma unroll
+        for (int c4 = 0; c4 < RP / 4; ++c4) {
+          const float4 o = __ldcg(reinterpret_cast<const float4*>(dst) + c4);
+          for (int r = 0; r < peers.n; ++r) reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP)[c4] = o;
+        }
       }
     }
   }
@@ -282,6 +291,7 @@ __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ ite
 }
 
 // ---------------------------------------------------------------- CUDA-core fallbacks (shapes TMA cannot address)
+template <int RP>
 __global__ void __launch_bounds__(GB_THREADS) k3_gemm1_simt(const PsMat* __restrict__ mats, int nmat, const float* __restrict__ work,
                                                            const float* __restrict__ q0t, int64_t qpad, float* acc) {
   // one warp per row: P[i][c] = sum_j M[i][j] Q0[j][c]
@@ -293,21 +303,27 @@ __global__ void __launch_bounds__(GB_THREADS) k3_gemm1_simt(const PsMat* __restr
     if (gw >= base && gw < base + mt.n) {
       const int i = gw - base;
       const float* rowp = work + mt.off + (size_t)i * mt.m;
-      float s[PS_R] = {0.f, 0.f, 0.f, 0.f};
+      float s[RP];
+#pragma unroll
+      for (int c = 0; c < RP; ++c) s[c] = 0.f;
       for (int j = lane; j < mt.m; j += 32) {
         const float x = rowp[j];
 #pragma unroll
-        for (int c = 0; c < PS_R; ++c) s[c] += x * q0t[(size_t)c * qpad + mt.qrow0 + j];
+        for (int c = 0; c < RP; ++c) s[c] += x * q0t[(size_t)c * qpad + mt.qrow0 + j];
       }
 #pragma unroll
-      for (int c = 0; c < PS_R; ++c) s[c] = warp_sum(s[c]);
-      if (lane == 0) *reinterpret_cast<float4*>(acc + (size_t)(mt.prow0 + i) * PS_R) = make_float4(s[0], s[1], s[2], s[3]);
+      for (int c = 0; c < RP; ++c) s[c] = warp_sum(s[c]);
+      if (lane == 0) {
+#pragma unroll
+        for (int c = 0; c < RP; ++c) acc[(size_t)(mt.prow0 + i) * RP + c] = s[c];
+      }
       return;
     }
     base += mt.n;
   }
 }
 
+template <int RP>
 __global__ void __launch_bounds__(GB_THREADS) k3_gemm2_simt(const PsMat* __restrict__ mats, int nmat, const float* __restrict__ work,
                                                            const float* __restrict__ ph, float* acc) {
   // one thread per column: Q[j][c] = sum_i M[i][j] P^[i][c]
@@ -318,14 +334,18 @@ __global__ void __launch_bounds__(GB_THREADS) k3_gemm2_simt(const PsMat* __restr
     if (mt.tc) continue;
     if (gt >= base && gt < base + mt.m) {
       const int j = gt - base;
-      float s[PS_R] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 8
+      float s[RP];
+#pragma unroll
+      for (int c = 0; c < RP; ++c) s[c] = 0.f;
+#pragma unroll 4
       for (int i = 0; i < mt.n; ++i) {
         const float x = work[mt.off + (size_t)i * mt.m + j];
-        const float4 p = *reinterpret_cast<const float4*>(ph + (size_t)(mt.prow0 + i) * PS_R);
-        s[0] += x * p.x; s[1] += x * p.y; s[2] += x * p.z; s[3] += x * p.w;
+        const float* pr = ph + (size_t)(mt.prow0 + i) * RP;
+#pragma unroll
+        for (int c = 0; c < RP; ++c) s[c] += x * pr[c];
       }
-      *reinterpret_cast<float4*>(acc + (size_t)(mt.qrow0 + j) * PS_R) = make_float4(s[0], s[1], s[2], s[3]);
+#pragma unroll
+      for (int c = 0; c < RP; ++c) acc[(size_t)(mt.qrow0 + j) * RP + c] = s[c];
       return;
     }
     base += mt.m;
@@ -333,7 +353,7 @@ __global__ void __launch_bounds__(GB_THREADS) k3_gemm2_simt(const PsMat* __restr
 }
 
 // pushes the rows of fallback matrices to every peer, then the last CTA releases the epoch flags
-__global__ void __launch_bounds__(GB_THREADS) k3_flag(const PsMat* __restrict__ mats, int nmat, int which, const float* acc,
+__global__ void __launch_bounds__(GB_THREADS) k3_flag(const PsMat* __restrict__ mats, int nmat, int which, const float* acc, int rp,
                                                      PsPeers peers_slots, uint32_t* done, PeerPtrs peers, int channel,
                                                      const StepCtl* ctl, size_t par_stride) {
   const uint32_t epoch = ctl->epoch;
@@ -342,9 +362,10 @@ __global__ void __launch_bounds__(GB_THREADS) k3_flag(const PsMat* __restrict__ 
     const PsMat mt = mats[mi];
     if (mt.tc) continue;
     const int rows = which == 1 ? mt.n : mt.m, row0 = which == 1 ? mt.prow0 : mt.qrow0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += gridDim.x * blockDim.x) {
-      const float4 o = *reinterpret_cast<const float4*>(acc + (size_t)(row0 + i) * PS_R);
-      for (int r = 0; r < peers_slots.n; ++r) *reinterpret_cast<float4*>(peers_slots.slot[r] + (size_t)(row0 + i) * PS_R) = o;
+    const int q4 = rp / 4;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows * q4; i += gridDim.x * blockDim.x) {
+      const float4 o = reinterpret_cast<const float4*>(acc + (size_t)row0 * rp)[i];
+      for (int r = 0; r < peers_slots.n; ++r) reinterpret_cast<float4*>(peers_slots.slot[r] + (size_t)row0 * rp)[i] = o;
     }
   }
   release_flags_last_block(done, peers, channel, epoch);
@@ -449,32 +470,127 @@ __device__ void cholqr2_inplace(float* buf, int len, int r, float* sh) {
   }
 }
 
-// Q0 = orth(normal) per matrix; scratch rows live in qacc (zeroed again afterwards by k3_prep order: prep runs first,
-// so k3_q0 uses its own scratch `q0` [qrows][4]) ; writes Q0^T [16][qpad]
-__global__ void __launch_bounds__(512) k3_q0(const PsMat* __restrict__ mats, float* q0, float* q0t, int64_t qpad, uint32_t seed,
-                                             const StepCtl* ctl) {
-  const uint32_t step = ctl->step;
-  __shared__ float sh[512];
-  const PsMat mt = mats[blockIdx.x];
-  float* buf = q0 + (size_t)mt.qrow0 * 4;
-  for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
-    float v[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int c = 0; c < mt.r; ++c) {
-      // element (j, c) of the (m, r) row-major normal draw: one Box-Muller pair per element index
-      const uint32_t e = (uint32_t)(j * mt.r + c);
-      const Philox4 p = philox4x32(e, step, GB_STREAM_NORMAL, 0u, seed, mt.hash);
-      const float u1 = (float)((p.x >> 8) + 1u) * (1.0f / 16777216.0f);
-      const float u2 = (float)(p.y >> 8) * (1.0f / 16777216.0f);
-      v[c] = sqrtf(-2.0f * logf(u1)) * cosf(6.283185307179586f * u2);
+// CholeskyQR2 for row pitches 8 and 16 (ranks 5..16): the Gram matrix is accumulated by RP x RP threads over row chunks
+// staged in shared memory, one warp factorises it (same eps-guarded formulas as chol_inv4) and inverts the triangular
+// factor, every thread then applies R^-1 to its rows.  sh: at least 128 * RP + 2 * RP * RP floats.
+template <int RP>
+__device__ void cholqr2_wide(float* buf, int len, int r, float* sh) {
+  constexpr int CH = 128;
+  float* tile = sh;                 // [CH][RP]
+  float* G = sh + CH * RP;          // [RP][RP] Gram matrix, then the upper-triangular factor R in place
+  float* INV = G + RP * RP;         // [RP][RP] R^-1
+  const int a = threadIdx.x / RP, b = threadIdx.x % RP;
+  const bool owner = threadIdx.x < RP * RP;
+  for (int round = 0; round < 2; ++round) {
+    float accv = 0.f;
+    for (int c0 = 0; c0 < len; c0 += CH) {
+      const int n = min(CH, len - c0);
+      for (int i = threadIdx.x; i < n * RP; i += blockDim.x) tile[i] = buf[(size_t)c0 * RP + i];
+      __syncthreads();
+      if (owner && a <= b) {
+#pragma unroll 4
+        for (int i = 0; i < n; ++i) accv += tile[i * RP + a] * tile[i * RP + b];
+      }
+      __syncthreads();
     }
-    *reinterpret_cast<float4*>(buf + (size_t)j * 4) = make_float4(v[0], v[1], v[2], v[3]);
+    if (owner) G[a * RP + b] = accv;            // upper triangle valid
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      const int lane = threadIdx.x;
+      for (int i = 0; i < RP; ++i) {
+        if (i >= r) {
+          if (lane < RP) G[i * RP + lane] = lane == i ? 1.f : 0.f;
+          __syncwarp();
+          continue;
+        }
+        float d = G[i * RP + i];
+        for (int k = 0; k < i; ++k) d -= G[k * RP + i] * G[k * RP + i];
+        const float rii = sqrtf(fmaxf(d, 0.f)) + 1e-8f;
+        float sv = 0.f;
+        if (lane > i && lane < r) {
+          sv = G[i * RP + lane];
+          for (int k = 0; k < i; ++k) sv -= G[k * RP + i] * G[k * RP + lane];
+          sv /= rii;
+        }
+        __syncwarp();
+        if (lane == i) G[i * RP + i] = rii;
+        else if (lane > i && lane < RP) G[i * RP + lane] = lane < r ? sv : 0.f;
+        __syncwarp();
+      }
+      if (lane < RP) {                            // column `lane` of R^-1 by back substitution
+        for (int i = RP - 1; i >= 0; --i) {
+          float sv = i == lane ? 1.f : 0.f;
+          for (int k = i + 1; k < RP; ++k) sv -= G[i * RP + k] * INV[k * RP + lane];
+          INV[i * RP + lane] = sv / G[i * RP + i];
+        }
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < len; i += blockDim.x) {
+      float x[RP], o[RP];
+      float4* row = reinterpret_cast<float4*>(buf + (size_t)i * RP);
+#pragma unroll
+      for (int c4 = 0; c4 < RP / 4; ++c4) { const float4 v = row[c4]; x[c4 * 4] = v.x; x[c4 * 4 + 1] = v.y; x[c4 * 4 + 2] = v.z; x[c4 * 4 + 3] = v.w; }
+#pragma unroll
+      for (int j = 0; j < RP; ++j) {
+        float sv = 0.f;
+#pragma unroll
+        for (int k = 0; k <= j; ++k) sv += x[k] * INV[k * RP + j];
+        o[j] = j < r ? sv : 0.f;
+      }
+#pragma unroll
+      for (int c4 = 0; c4 < RP / 4; ++c4) row[c4] = make_float4(o[c4 * 4], o[c4 * 4 + 1], o[c4 * 4 + 2], o[c4 * 4 + 3]);
+    }
+    __syncthreads();
+  }
+}
+
+template <int RP>
+__device__ __forceinline__ void cholqr2_any(float* buf, int len, int r, float* sh) {
+  if (RP == 4) cholqr2_inplace(buf, len, r, sh);
+  else cholqr2_wide<RP>(buf, len, r, sh);
+}
+template <int RP>
+struct PsShared { static constexpr int floats = RP == 4 ? 512 : 128 * RP + 2 * RP * RP; };
+
+// Q0 per matrix: a fresh Philox normal draw -- or, with a warm start and from the second exchange on, the previous
+// exchange's Q (reference: compressor/powersgd.py:37-39 use_memory) -- orthogonalised; writes Q0^T [16][qpad]
+template <int RP>
+__global__ void __launch_bounds__(512) k3_q0(const PsMat* __restrict__ mats, float* q0, const float* __restrict__ qprev, float* q0t,
+                                             int64_t qpad, uint32_t seed, const StepCtl* ctl) {
+  const uint32_t step = ctl->step;
+  __shared__ float sh[PsShared<RP>::floats];
+  const PsMat mt = mats[blockIdx.x];
+  float* buf = q0 + (size_t)mt.qrow0 * RP;
+  const bool warm = qprev != nullptr && step > 0;
+  for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
+    float v[RP];
+#pragma unroll
+    for (int c = 0; c < RP; ++c) v[c] = 0.f;
+    if (warm) {
+#pragma unroll
+      for (int c = 0; c < RP; ++c) v[c] = c < mt.r ? qprev[(size_t)(mt.qrow0 + j) * RP + c] : 0.f;
+    } else {
+#pragma unroll
+      for (int c = 0; c < RP; ++c) {
+        if (c < mt.r) {
+          // element (j, c) of the (m, r) row-major normal draw: one Box-Muller pair per element index
+          const uint32_t e = (uint32_t)(j * mt.r + c);
+          const Philox4 p = philox4x32(e, step, GB_STREAM_NORMAL, 0u, seed, mt.hash);
+          const float u1 = (float)((p.x >> 8) + 1u) * (1.0f / 16777216.0f);
+          const float u2 = (float)(p.y >> 8) * (1.0f / 16777216.0f);
+          v[c] = sqrtf(-2.0f * logf(u1)) * cosf(6.283185307179586f * u2);
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < RP; ++c) buf[(size_t)j * RP + c] = v[c];
   }
   __syncthreads();
-  cholqr2_inplace(buf, mt.m, mt.r, sh);
+  cholqr2_any<RP>(buf, mt.m, mt.r, sh);
   for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
-    const float4 x = *reinterpret_cast<const float4*>(buf + (size_t)j * 4);
-    const float v[4] = {x.x, x.y, x.z, x.w};
-    for (int c = 0; c < 4; ++c) q0t[(size_t)c * qpad + mt.qrow0 + j] = c < mt.r ? v[c] : 0.f;
+#pragma unroll
+    for (int c = 0; c < RP; ++c) q0t[(size_t)c * qpad + mt.qrow0 + j] = c < mt.r ? buf[(size_t)j * RP + c] : 0.f;
   }
 }
 
@@ -483,70 +599,91 @@ __device__ __forceinline__ void shift(PsIn& o, size_t bytes) {
   for (int r = 0; r < o.n; ++r) o.slot[r] = (const float*)((const char*)o.slot[r] + bytes);
 }
 
-// wait flags; P = mean_r P_r; orthogonalise; write P^ [prows][4] and P^^T [16][ppad]
+// wait flags; P = mean_r P_r; orthogonalise; write P^ [prows][RP] and P^^T [16][ppad]
+template <int RP>
 __global__ void __launch_bounds__(512) k3_orth(const PsMat* __restrict__ mats, PsIn in, float inv_world, float* ph, float* pht,
                                                int64_t ppad, PeerPtrs peers, int channel, const StepCtl* ctl, size_t par_stride,
                                                uint32_t* status, uint64_t timeout_ns) {
   const uint32_t epoch = ctl->epoch;
   if (epoch & 1) shift(in, par_stride);
-  __shared__ float sh[512];
+  __shared__ float sh[PsShared<RP>::floats];
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   const PsMat mt = mats[blockIdx.x];
-  float* buf = ph + (size_t)mt.prow0 * 4;
-  for (int i = threadIdx.x; i < mt.n; i += blockDim.x) {
+  float* buf = ph + (size_t)mt.prow0 * RP;
+  for (int i = threadIdx.x; i < mt.n * (RP / 4); i += blockDim.x) {
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int r = 0; r < in.n; ++r) {
-      const float4 x = *reinterpret_cast<const float4*>(in.slot[r] + (size_t)(mt.prow0 + i) * 4);
+      const float4 x = reinterpret_cast<const float4*>(in.slot[r] + (size_t)mt.prow0 * RP)[i];
       s.x += x.x; s.y += x.y; s.z += x.z; s.w += x.w;
     }
     if (in.n > 1) { s.x *= inv_world; s.y *= inv_world; s.z *= inv_world; s.w *= inv_world; }
-    *reinterpret_cast<float4*>(buf + (size_t)i * 4) = s;
+    reinterpret_cast<float4*>(buf)[i] = s;
   }
   __syncthreads();
-  cholqr2_inplace(buf, mt.n, mt.r, sh);
+  cholqr2_any<RP>(buf, mt.n, mt.r, sh);
   for (int i = threadIdx.x; i < mt.n; i += blockDim.x) {
-    const float4 x = *reinterpret_cast<const float4*>(buf + (size_t)i * 4);
-    const float v[4] = {x.x, x.y, x.z, x.w};
-    for (int c = 0; c < 4; ++c) pht[(size_t)c * ppad + mt.prow0 + i] = c < mt.r ? v[c] : 0.f;
+#pragma unroll
+    for (int c = 0; c < RP; ++c) pht[(size_t)c * ppad + mt.prow0 + i] = c < mt.r ? buf[(size_t)i * RP + c] : 0.f;
   }
 }
 
 // wait flags; out = P^ (mean_r Q_r)^T; residual = work - out.  One CTA per (matrix, 32-row band).
-__device__ __forceinline__ float dot4(const float4 a, const float4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
-
-__device__ __forceinline__ float4 mean_q(const PsIn& in, size_t row, float inv_world) {
-  float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+template <int RP>
+__device__ __forceinline__ void mean_q(const PsIn& in, size_t row, float inv_world, float (&q)[RP]) {
+#pragma unroll
+  for (int c = 0; c < RP; ++c) q[c] = 0.f;
   for (int r = 0; r < in.n; ++r) {
-    const float4 x = *reinterpret_cast<const float4*>(in.slot[r] + row * 4);
-    q.x += x.x; q.y += x.y; q.z += x.z; q.w += x.w;
+#pragma unroll
+    for (int c4 = 0; c4 < RP / 4; ++c4) {
+      const float4 x = reinterpret_cast<const float4*>(in.slot[r] + row * RP)[c4];
+      q[c4 * 4] += x.x; q[c4 * 4 + 1] += x.y; q[c4 * 4 + 2] += x.z; q[c4 * 4 + 3] += x.w;
+    }
   }
-  if (in.n > 1) { q.x *= inv_world; q.y *= inv_world; q.z *= inv_world; q.w *= inv_world; }
-  return q;
+  if (in.n > 1) {
+#pragma unroll
+    for (int c = 0; c < RP; ++c) q[c] *= inv_world;
+  }
+}
+template <int RP>
+__device__ __forceinline__ float dot_r(const float* p, const float (&q)[RP]) {
+  float s = 0.f;
+#pragma unroll
+  for (int c = 0; c < RP; ++c) s += p[c] * q[c];
+  return s;
 }
 
 // One CTA per (matrix, 32-row band).  A thread owns four consecutive columns (16-byte accesses) and walks
 // the band eight rows at a time with all loads issued before the dependent stores (first version: scalar
 // accesses with load->store->store chains, 245 us for ResNet-50 under ncu = half of the whole exchange).
+// The band that starts at row 0 also keeps the averaged Q for a warm start of the next exchange.
+template <int RP>
 __global__ void __launch_bounds__(GB_THREADS) k3_final(const PsBand* __restrict__ bands, const PsMat* __restrict__ mats, PsIn in,
                                                       float inv_world, const float* __restrict__ ph, const float* __restrict__ work,
-                                                      float* __restrict__ res, int has_res, float* __restrict__ out, PeerPtrs peers,
-                                                      int channel, const StepCtl* ctl, size_t par_stride, uint32_t* status,
-                                                      uint64_t timeout_ns) {
+                                                      float* __restrict__ res, int has_res, float* __restrict__ out, float* qkeep,
+                                                      PeerPtrs peers, int channel, const StepCtl* ctl, size_t par_stride,
+                                                      uint32_t* status, uint64_t timeout_ns) {
   const uint32_t epoch = ctl->epoch;
   if (epoch & 1) shift(in, par_stride);
-  __shared__ float4 sp[32];
+  __shared__ __align__(16) float sp[32 * RP];
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   const PsBand b = bands[blockIdx.x];
   const PsMat mt = mats[b.mat];
   const int nrow = min(32, mt.n - b.i0);
-  if (threadIdx.x < nrow) sp[threadIdx.x] = *reinterpret_cast<const float4*>(ph + (size_t)(mt.prow0 + b.i0 + threadIdx.x) * 4);
+  for (int i = threadIdx.x; i < nrow * RP; i += blockDim.x) sp[i] = ph[(size_t)(mt.prow0 + b.i0) * RP + i];
   __syncthreads();
   const size_t band0 = mt.off + (size_t)b.i0 * mt.m;
+  const bool keep = qkeep != nullptr && b.i0 == 0;
   if ((mt.m & 3) == 0) {
     for (int j = threadIdx.x * 4; j < mt.m; j += blockDim.x * 4) {
-      float4 q[4];
+      float q[4][RP];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) q[c] = mean_q(in, (size_t)(mt.qrow0 + j + c), inv_world);
+      for (int c = 0; c < 4; ++c) {
+        mean_q<RP>(in, (size_t)(mt.qrow0 + j + c), inv_world, q[c]);
+        if (keep) {
+#pragma unroll
+          for (int e = 0; e < RP; ++e) qkeep[(size_t)(mt.qrow0 + j + c) * RP + e] = q[c][e];
+        }
+      }
       for (int i0 = 0; i0 < nrow; i0 += 8) {
         float4 w[8];
 #pragma unroll
@@ -555,8 +692,8 @@ __global__ void __launch_bounds__(GB_THREADS) k3_final(const PsBand* __restrict_
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           if (i0 + u < nrow) {
-            const float4 pr = sp[i0 + u];
-            const float4 o = make_float4(dot4(pr, q[0]), dot4(pr, q[1]), dot4(pr, q[2]), dot4(pr, q[3]));
+            const float* pr = sp + (i0 + u) * RP;
+            const float4 o = make_float4(dot_r<RP>(pr, q[0]), dot_r<RP>(pr, q[1]), dot_r<RP>(pr, q[2]), dot_r<RP>(pr, q[3]));
             const size_t e = band0 + (size_t)(i0 + u) * mt.m + j;
             if (has_res) *reinterpret_cast<float4*>(res + e) = make_float4(w[u].x - o.x, w[u].y - o.y, w[u].z - o.z, w[u].w - o.w);
             *reinterpret_cast<float4*>(out + e) = o;
@@ -566,10 +703,15 @@ __global__ void __launch_bounds__(GB_THREADS) k3_final(const PsBand* __restrict_
     }
   } else {
     for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
-      const float4 q = mean_q(in, (size_t)(mt.qrow0 + j), inv_world);
+      float q[RP];
+      mean_q<RP>(in, (size_t)(mt.qrow0 + j), inv_world, q);
+      if (keep) {
+#pragma unroll
+        for (int e = 0; e < RP; ++e) qkeep[(size_t)(mt.qrow0 + j) * RP + e] = q[e];
+      }
       for (int i = 0; i < nrow; ++i) {
         const size_t e = band0 + (size_t)i * mt.m + j;
-        const float o = dot4(sp[i], q);
+        const float o = dot_r<RP>(sp + i * RP, q);
         if (has_res) res[e] = work[e] - o;
         out[e] = o;
       }
@@ -637,11 +779,30 @@ static void build_items(const std::vector<PsMat>& mats, int mode, std::vector<Ps
 
 extern "C" int gb_psgd_destroy(gb_psgd* p);
 
+static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, const int64_t* cols, const uint32_t* name_hash,
+                      int rank_r, uint32_t seed, int has_memory, int use_tcgen05, int warm_start);
+
+extern "C" int gb_psgd_create2(gb_comm* c, int nmat, const int64_t* rows, const int64_t* cols, const uint32_t* name_hash, int rank_r,
+                               uint32_t seed, int has_memory, int use_tcgen05, int warm_start, gb_psgd** out) {
+  GB_CHECK(nmat >= 1, "need at least one matrix");
+  GB_CHECK(rank_r >= 1 && rank_r <= PS_RMAX, "native PowerSGD supports rank 1..%d (got %d)", PS_RMAX, rank_r);
+  gb_psgd* p = new gb_psgd();            // value-initialised: every pointer starts as nullptr
+  if (psgd_build(p, c, nmat, rows, cols, name_hash, rank_r, seed, has_memory, use_tcgen05, warm_start)) {
+    gb_psgd_destroy(p);                  // one failure exit: releases whatever the builder had allocated
+    return -1;
+  }
+  *out = p;
+  return 0;
+}
 extern "C" int gb_psgd_create(gb_comm* c, int nmat, const int64_t* rows, const int64_t* cols, const uint32_t* name_hash, int rank_r,
                               uint32_t seed, int has_memory, int use_tcgen05, gb_psgd** out) {
-  GB_CHECK(nmat >= 1, "need at least one matrix");
-  GB_CHECK(rank_r >= 1 && rank_r <= PS_R, "native PowerSGD supports rank 1..%d (got %d)", PS_R, rank_r);
-  gb_psgd* p = new gb_psgd();
+  return gb_psgd_create2(c, nmat, rows, cols, name_hash, rank_r, seed, has_memory, use_tcgen05, 0, out);
+}
+
+static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, const int64_t* cols, const uint32_t* name_hash,
+                      int rank_r, uint32_t seed, int has_memory, int use_tcgen05, int warm_start) {
+  p->rp = rank_r <= 4 ? 4 : rank_r <= 8 ? 8 : 16;
+  p->d_qprev = nullptr;
   p->comm = c; p->nmat = nmat; p->rank_r = rank_r; p->has_mem = has_memory; p->use_tc = use_tcgen05;
   p->seed = seed; p->step = 0; p->epoch = 0; p->launches = 0;
   int64_t off = 0, prow = 0, qrow = 0;
@@ -680,9 +841,14 @@ extern "C" int gb_psgd_create(gb_comm* c, int nmat, const int64_t* rows, const i
   if (has_memory) { GB_CUDA(cudaMalloc((void**)&p->d_res, p->padded * 4)); GB_CUDA(cudaMemset(p->d_res, 0, p->padded * 4)); }
   GB_CUDA(cudaMalloc((void**)&p->d_q0t, PS_N * p->qpad * 4)); GB_CUDA(cudaMemset(p->d_q0t, 0, PS_N * p->qpad * 4));
   GB_CUDA(cudaMalloc((void**)&p->d_pht, PS_N * p->ppad * 4)); GB_CUDA(cudaMemset(p->d_pht, 0, PS_N * p->ppad * 4));
-  GB_CUDA(cudaMalloc((void**)&p->d_pacc, (p->prows + 8) * PS_R * 4));
-  GB_CUDA(cudaMalloc((void**)&p->d_qacc, (p->qrows + 8) * PS_R * 4 * 2));   // second half: Q0 scratch for k3_q0
-  GB_CUDA(cudaMalloc((void**)&p->d_ph, (p->prows + 8) * PS_R * 4));
+  const size_t RP = (size_t)p->rp;
+  GB_CUDA(cudaMalloc((void**)&p->d_pacc, (p->prows + 8) * RP * 4));
+  GB_CUDA(cudaMalloc((void**)&p->d_qacc, (p->qrows + 8) * RP * 4 * 2));   // second half: Q0 scratch for k3_q0
+  GB_CUDA(cudaMalloc((void**)&p->d_ph, (p->prows + 8) * RP * 4));
+  if (warm_start) {
+    GB_CUDA(cudaMalloc((void**)&p->d_qprev, (p->qrows + 8) * RP * 4));
+    GB_CUDA(cudaMemset(p->d_qprev, 0, (p->qrows + 8) * RP * 4));
+  }
   GB_CUDA(cudaMalloc((void**)&p->d_cnt1, (p->ntiles1 + p->ntiles2 + 64) * 4));
   p->d_cnt2 = p->d_cnt1 + p->ntiles1;
   p->d_done = p->d_cnt1 + p->ntiles1 + p->ntiles2;
@@ -706,14 +872,25 @@ extern "C" int gb_psgd_create(gb_comm* c, int nmat, const int64_t* rows, const i
   }
   GB_CUDA(cudaMalloc((void**)&p->d_maps, sizeof(CUtensorMap) * nmat * 4));
   GB_CUDA(cudaMemcpy(p->d_maps, maps.data(), sizeof(CUtensorMap) * nmat * 4, cudaMemcpyHostToDevice));
-  GB_CUDA(cudaFuncSetAttribute(k3_gemm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
-  GB_CUDA(cudaFuncSetAttribute(k3_gemm<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
-  p->slot_p = ((size_t)(p->prows + 8) * PS_R * 4 + 255) & ~size_t(255);
-  p->slot_q = ((size_t)(p->qrows + 8) * PS_R * 4 + 255) & ~size_t(255);
+  GB_CUDA(cudaFuncSetAttribute(k3_gemm<1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
+  GB_CUDA(cudaFuncSetAttribute(k3_gemm<2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
+  GB_CUDA(cudaFuncSetAttribute(k3_gemm<1, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
+  GB_CUDA(cudaFuncSetAttribute(k3_gemm<2, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
+  GB_CUDA(cudaFuncSetAttribute(k3_gemm<1, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
+  GB_CUDA(cudaFuncSetAttribute(k3_gemm<2, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
+  p->slot_p = ((size_t)(p->prows + 8) * RP * 4 + 255) & ~size_t(255);
+  p->slot_q = ((size_t)(p->qrows + 8) * RP * 4 + 255) & ~size_t(255);
+  // both channels in one request, so that a retry after the arena has grown does not leave a half-allocated pair behind
+  {
+    size_t need2 = (p->slot_p + p->slot_q) * 2 * (size_t)c->world;
+    if (gb_comm_arena_free(c) < need2) {
+      int dummy; size_t off;
+      return gb_comm_alloc_channel(c, p->slot_p + p->slot_q, &dummy, &off);     // fails and reports the bytes needed for both
+    }
+  }
   if (gb_comm_alloc_channel(c, p->slot_p, &p->chan_p, &p->off_p)) return -1;
   if (gb_comm_alloc_channel(c, p->slot_q, &p->chan_q, &p->off_q)) return -1;
   GB_CUDA(cudaDeviceSynchronize());
-  *out = p;
   return 0;
 }
 
@@ -724,6 +901,7 @@ extern "C" int gb_psgd_destroy(gb_psgd* p) {
   cudaFree(p->d_q0t); cudaFree(p->d_pht); cudaFree(p->d_pacc); cudaFree(p->d_qacc); cudaFree(p->d_ph); cudaFree(p->d_cnt1);
   cudaFree(p->d_maps);
   cudaFree(p->d_bands);
+  cudaFree(p->d_qprev);
   delete p;
   return 0;
 }
@@ -759,6 +937,19 @@ extern "C" int gb_psgd_state_write(gb_psgd* p, const void* d_src, void* stream) 
   GB_CUDA(cudaMemcpyAsync(p->d_res, d_src, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return 0;
 }
+// warm-start Q (state index 1 of the Python plan): copy out / in, [qrows + 8][rp] floats
+extern "C" int gb_psgd_qprev(gb_psgd* p, void** ptr, size_t* bytes) {
+  *ptr = p->d_qprev;
+  *bytes = p->d_qprev ? (size_t)(p->qrows + 8) * p->rp * 4 : 0;
+  return 0;
+}
+extern "C" int gb_psgd_qprev_copy(gb_psgd* p, void* d_buf, int to_plan, void* stream) {
+  GB_CHECK(p->d_qprev, "this PowerSGD plan has no warm-start memory");
+  const size_t bytes = (size_t)(p->qrows + 8) * p->rp * 4;
+  GB_CUDA(cudaMemcpyAsync(to_plan ? (void*)p->d_qprev : d_buf, to_plan ? d_buf : (void*)p->d_qprev, bytes, cudaMemcpyDeviceToDevice,
+                          (cudaStream_t)stream));
+  return 0;
+}
 #ifdef GB_K3_DEBUG
 extern "C" int gb_psgd_debug_set(const int* v8) {
   GB_CUDA(cudaMemcpyToSymbol(g_dbg, v8, 32));
@@ -769,7 +960,7 @@ extern "C" int gb_psgd_debug_dump(float* h_dst) {
   return 0;
 }
 #endif
-extern "C" int64_t gb_psgd_wire_bytes(gb_psgd* p) { return (int64_t)(p->prows + p->qrows) * PS_R * 4; }
+extern "C" int64_t gb_psgd_wire_bytes(gb_psgd* p) { return (int64_t)(p->prows + p->qrows) * p->rp * 4; }
 
 static PsPeers peer_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch = 0) {   // parity 0
   PsPeers s; gb_comm* c = p->comm; s.n = c->world;
@@ -782,6 +973,13 @@ static PsIn my_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t ep
   return s;
 }
 
+#define PS_DISPATCH(rp, CALL)                    \
+  do {                                           \
+    if ((rp) == 4) { constexpr int RP = 4; CALL; }        \
+    else if ((rp) == 8) { constexpr int RP = 8; CALL; }   \
+    else { constexpr int RP = 16; CALL; }                 \
+  } while (0)
+
 // phase 1: compensate, Q0, P_r = M Q0, push P tiles, release flags
 extern "C" int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
@@ -792,16 +990,23 @@ extern "C" int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream) {
   const size_t psp = (size_t)c->world * p->slot_p, psq = (size_t)c->world * p->slot_q;
   (void)psq;
   k3_prep<<<148 * 4, GB_THREADS, 0, st>>>(p->padded, d_grad, p->d_res, p->d_work, p->has_mem, p->d_pacc,
-                                         p->prows * PS_R, p->d_qacc, p->qrows * PS_R, p->d_cnt1, p->ntiles1 + p->ntiles2, p->d_ctl);
+                                         p->prows * p->rp, p->d_qacc, p->qrows * p->rp, p->d_cnt1, p->ntiles1 + p->ntiles2, p->d_ctl);
   LAUNCHED(p);
-  k3_q0<<<p->nmat, 512, 0, st>>>(p->d_mat, p->d_qacc + (size_t)(p->qrows + 8) * PS_R, p->d_q0t, p->qpad, p->seed, p->d_ctl);
+  PS_DISPATCH(p->rp, (k3_q0<RP><<<p->nmat, 512, 0, st>>>(p->d_mat, p->d_qacc + (size_t)(p->qrows + 8) * RP, p->d_qprev, p->d_q0t,
+                                                       p->qpad, p->seed, p->d_ctl)));
   LAUNCHED(p);
   const PsPeers ps = peer_slots(p, p->off_p, p->slot_p);
-  if (p->nitems1) { k3_gemm<1><<<p->nitems1, 192, PS_SMEM, st>>>(p->d_items1, p->d_mat, p->d_maps, p->d_pacc, p->d_cnt1, ps, p->d_ctl, psp); LAUNCHED(p); }
+  if (p->nitems1) {
+    PS_DISPATCH(p->rp, (k3_gemm<1, RP><<<p->nitems1, 192, PS_SMEM, st>>>(p->d_items1, p->d_mat, p->d_maps, p->d_pacc, p->d_cnt1, ps, p->d_ctl, psp)));
+    LAUNCHED(p);
+  }
   int simt_rows = 0;
   for (auto& m : p->h_mat) if (!m.tc) simt_rows += m.n;
-  if (simt_rows) { k3_gemm1_simt<<<(simt_rows * 32 + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, p->d_work, p->d_q0t, p->qpad, p->d_pacc); LAUNCHED(p); }
-  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 1, p->d_pacc, ps, p->d_done, gb_comm_peers(c), p->chan_p, p->d_ctl, psp);
+  if (simt_rows) {
+    PS_DISPATCH(p->rp, (k3_gemm1_simt<RP><<<(simt_rows * 32 + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, p->d_work, p->d_q0t, p->qpad, p->d_pacc)));
+    LAUNCHED(p);
+  }
+  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 1, p->d_pacc, p->rp, ps, p->d_done, gb_comm_peers(c), p->chan_p, p->d_ctl, psp);
   LAUNCHED(p);
   return 0;
 }
@@ -819,15 +1024,22 @@ extern "C" int gb_psgd_mid(gb_psgd* p, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   gb_comm* c = p->comm;
   const size_t psp = (size_t)c->world * p->slot_p, psq = (size_t)c->world * p->slot_q;
-  k3_orth<<<p->nmat, 512, 0, st>>>(p->d_mat, my_slots(p, p->off_p, p->slot_p), 1.0f / (float)c->world, p->d_ph, p->d_pht,
-                                  p->ppad, gb_comm_peers(c), p->chan_p, p->d_ctl, psp, c->status_dev, c->timeout_ns);
+  PS_DISPATCH(p->rp, (k3_orth<RP><<<p->nmat, 512, 0, st>>>(p->d_mat, my_slots(p, p->off_p, p->slot_p), 1.0f / (float)c->world, p->d_ph,
+                                                         p->d_pht, p->ppad, gb_comm_peers(c), p->chan_p, p->d_ctl, psp,
+                                                         c->status_dev, c->timeout_ns)));
   LAUNCHED(p);
   const PsPeers qs = peer_slots(p, p->off_q, p->slot_q);
-  if (p->nitems2) { k3_gemm<2><<<p->nitems2, 192, PS_SMEM, st>>>(p->d_items2, p->d_mat, p->d_maps, p->d_qacc, p->d_cnt2, qs, p->d_ctl, psq); LAUNCHED(p); }
+  if (p->nitems2) {
+    PS_DISPATCH(p->rp, (k3_gemm<2, RP><<<p->nitems2, 192, PS_SMEM, st>>>(p->d_items2, p->d_mat, p->d_maps, p->d_qacc, p->d_cnt2, qs, p->d_ctl, psq)));
+    LAUNCHED(p);
+  }
   int simt_cols = 0;
   for (auto& m : p->h_mat) if (!m.tc) simt_cols += m.m;
-  if (simt_cols) { k3_gemm2_simt<<<(simt_cols + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, p->d_work, p->d_ph, p->d_qacc); LAUNCHED(p); }
-  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 2, p->d_qacc, qs, p->d_done, gb_comm_peers(c), p->chan_q, p->d_ctl, psq);
+  if (simt_cols) {
+    PS_DISPATCH(p->rp, (k3_gemm2_simt<RP><<<(simt_cols + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, p->d_work, p->d_ph, p->d_qacc)));
+    LAUNCHED(p);
+  }
+  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 2, p->d_qacc, p->rp, qs, p->d_done, gb_comm_peers(c), p->chan_q, p->d_ctl, psq);
   LAUNCHED(p);
   return 0;
 }
@@ -836,10 +1048,10 @@ extern "C" int gb_psgd_mid(gb_psgd* p, void* stream) {
 extern "C" int gb_psgd_recv(gb_psgd* p, float* d_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   gb_comm* c = p->comm;
-  k3_final<<<p->nbands, GB_THREADS, 0, st>>>(p->d_bands, p->d_mat, my_slots(p, p->off_q, p->slot_q), 1.0f / (float)c->world, p->d_ph,
-                                     p->d_work, p->d_res, p->has_mem, d_out, gb_comm_peers(c), p->chan_q, p->d_ctl,
-                                     (size_t)c->world * p->slot_q,
-                                     c->status_dev, c->timeout_ns);
+  PS_DISPATCH(p->rp, (k3_final<RP><<<p->nbands, GB_THREADS, 0, st>>>(p->d_bands, p->d_mat, my_slots(p, p->off_q, p->slot_q),
+                                                                   1.0f / (float)c->world, p->d_ph, p->d_work, p->d_res, p->has_mem,
+                                                                   d_out, p->d_qprev, gb_comm_peers(c), p->chan_q, p->d_ctl,
+                                                                   (size_t)c->world * p->slot_q, c->status_dev, c->timeout_ns)));
   LAUNCHED(p);
   p->step++;
   return 0;

@@ -105,6 +105,9 @@ def _declare(L):
         "gb_nvls_reduce": (i32, [vp, vp, i32, vp]),
         "gb_nvls_launches": (i32, [vp, P(i64)]),
         "gb_psgd_create": (i32, [vp, i32, P(i64), P(i64), P(u32), i32, u32, i32, i32, P(vp)]),
+        "gb_psgd_create2": (i32, [vp, i32, P(i64), P(i64), P(u32), i32, u32, i32, i32, i32, P(vp)]),
+        "gb_psgd_qprev": (i32, [vp, P(vp), P(sz)]),
+        "gb_psgd_qprev_copy": (i32, [vp, vp, i32, vp]),
         "gb_psgd_destroy": (i32, [vp]),
         "gb_psgd_padded_numel": (i64, [vp]),
         "gb_psgd_offsets": (i32, [vp, P(i64)]),

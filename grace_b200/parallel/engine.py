@@ -230,7 +230,7 @@ class Plan:
 class PowerSGDPlan:
     """All >=2-D gradients of one bucket through the native PowerSGD pipeline (``gb_psgd``)."""
 
-    def __init__(self, engine: Engine, shapes, names, rank, seed, has_memory, use_tcgen05=True):
+    def __init__(self, engine: Engine, shapes, names, rank, seed, has_memory, use_tcgen05=True, warm_start=False):
         L = native.lib()
         self.engine = engine
         self.nmat = len(shapes)
@@ -241,8 +241,10 @@ class PowerSGDPlan:
         cols = (C.c_int64 * self.nmat)(*[c for _, c in self.shapes])
         hs = (C.c_uint32 * self.nmat)(*[fnv1a(n) for n in names])
         h = C.c_void_p()
-        engine.create_with_growth(lambda: L.gb_psgd_create(engine._h, self.nmat, rows, cols, hs, int(rank), int(seed) & 0xFFFFFFFF,
-                                                           1 if has_memory else 0, 1 if use_tcgen05 else 0, C.byref(h)))
+        engine.create_with_growth(lambda: L.gb_psgd_create2(engine._h, self.nmat, rows, cols, hs, int(rank), int(seed) & 0xFFFFFFFF,
+                                                            1 if has_memory else 0, 1 if use_tcgen05 else 0,
+                                                            1 if warm_start else 0, C.byref(h)))
+        self.warm_start = bool(warm_start)
         self._h = h
         self.padded = L.gb_psgd_padded_numel(h)
         off = (C.c_int64 * self.nmat)()
@@ -272,7 +274,15 @@ class PowerSGDPlan:
         return out.value
 
     def get_state(self, which=0):
+        """0: residual (error feedback), 1: the previous exchange's Q of a warm-started plan."""
         ptr, size = C.c_void_p(), C.c_size_t()
+        if which == 1:
+            check(native.lib().gb_psgd_qprev(self._h, C.byref(ptr), C.byref(size)))
+            if not ptr.value:
+                return None
+            out = torch.empty(size.value // 4, dtype=torch.float32, device="cuda")
+            check(native.lib().gb_psgd_qprev_copy(self._h, C.c_void_p(out.data_ptr()), 0, _stream_ptr()))
+            return out
         check(native.lib().gb_psgd_residual(self._h, C.byref(ptr), C.byref(size)))
         if which != 0 or not ptr.value:
             return None
@@ -281,6 +291,11 @@ class PowerSGDPlan:
         return out
 
     def set_state(self, which, tensor):
+        if which == 1 and tensor is not None and self.warm_start:
+            src = tensor.to(device="cuda", dtype=torch.float32).reshape(-1).contiguous()
+            check(native.lib().gb_psgd_qprev_copy(self._h, C.c_void_p(src.data_ptr()), 1, _stream_ptr()))
+            torch.cuda.current_stream().synchronize()
+            return
         if which != 0 or tensor is None:
             return
         src = tensor.to(device="cuda", dtype=torch.float32).reshape(-1).contiguous()

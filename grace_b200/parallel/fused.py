@@ -225,7 +225,7 @@ class _Bucket:
 class _PowerSGDBucket(_Bucket):
     """>=2-D gradients go through the native PowerSGD plan (K3), 1-D ones through a dense plan."""
 
-    def __init__(self, engine, named_params, rank, seed, has_memory, use_tc=True):
+    def __init__(self, engine, named_params, rank, seed, has_memory, use_tc=True, warm=False):
         from grace_b200.ops.native import CodecParams, CODEC, MEMORY
         from grace_b200.parallel.engine import PowerSGDPlan
         self.names = [n for n, _ in named_params]
@@ -238,7 +238,7 @@ class _PowerSGDBucket(_Bucket):
         self.psgd = self.dense = None
         if mats:
             shapes = [(p.shape[0], p.numel() // p.shape[0]) for _, p in mats]
-            self.psgd = PowerSGDPlan(engine, shapes, [n for n, _ in mats], rank, seed, has_memory, use_tc)
+            self.psgd = PowerSGDPlan(engine, shapes, [n for n, _ in mats], rank, seed, has_memory, use_tc, warm)
             self.flat_m = torch.zeros(self.psgd.padded, dtype=torch.float32, device=dev)
             for off, (n, p) in zip(self.psgd.offsets, mats):
                 view_of[p] = _grad_view(self.flat_m[off:off + p.numel()], p)
@@ -342,19 +342,21 @@ def _all_ranks_agree(ok):
 
 
 def powersgd_spec(grace):
-    """(rank, seed, has_memory) when ``grace`` is a natively supported PowerSGD triple, else None."""
+    """(rank, seed, has_memory, warm_start) when ``grace`` is a natively supported PowerSGD triple, else None."""
     from grace_b200.compressor.lowrank import RANK_KEY
     c, m = grace.compressor, grace.memory
     if type(c) is not C.PowerSGDCompressor or type(grace).__name__ != "Allreduce":
         return None
     if not type(grace).__module__.startswith("grace_b200."):
         return None
-    if c.use_memory or c.warm_start or type(m) not in (M.PowerSGDMemory, M.NoneMemory):
+    if type(m) not in (M.PowerSGDMemory, M.NoneMemory):
         return None
     rank = c.q_memory.get(RANK_KEY, c.rank)
-    if not 1 <= rank <= 4:
+    if not 1 <= rank <= 16:
         return None
-    return rank, c.seed, type(m) is M.PowerSGDMemory
+    # the previous Q survives to the next step only if the memory does not drop it (memory/powersgd.py:26-28 redraws it)
+    warm = bool(c.use_memory) and (type(m) is M.NoneMemory or bool(getattr(m, "warm_start", False)))
+    return rank, c.seed, type(m) is M.PowerSGDMemory, warm
 
 
 class FusedDP:
@@ -433,9 +435,9 @@ class FusedDP:
             self._nvls_failed = True
             self.nvls_error = repr(err)
         if powersgd is not None:
-            rank, seed, has_memory = powersgd
+            rank, seed, has_memory, warm = powersgd
             return _PowerSGDBucket(self.engine, named_params, rank, seed, has_memory,
-                                   use_tc=os.environ.get("GRACE_B200_PSGD_TCGEN05", "1") != "0")
+                                   use_tc=os.environ.get("GRACE_B200_PSGD_TCGEN05", "1") != "0", warm=warm)
         return _Bucket(self.engine, named_params, params)
 
     # ------------------------------------------------------------------ autograd side
@@ -605,9 +607,9 @@ class _StepAllSet:
 
     def _make(self, named_tensors, params, powersgd):
         if powersgd is not None:
-            rank, seed, has_memory = powersgd
+            rank, seed, has_memory, warm = powersgd
             return _PowerSGDBucket(self.engine, named_tensors, rank, seed, has_memory,
-                                   use_tc=os.environ.get("GRACE_B200_PSGD_TCGEN05", "1") != "0")
+                                   use_tc=os.environ.get("GRACE_B200_PSGD_TCGEN05", "1") != "0", warm=warm)
         return _Bucket(self.engine, named_tensors, params)
 
     def exchange(self, grads):
@@ -794,6 +796,8 @@ def _restore_buckets(buckets, saved):
         for pl, ps in zip(b.plans, s["plans"]):
             for which in (0, 1):
                 t = ps["state%d" % which]
+                if which == 1 and not hasattr(pl, "params"):
+                    continue                              # PowerSGD's warm-start Q has its own size; the plan checks it
                 if t is not None and t.numel() != pl.padded:
                     raise ValueError("state buffer of bucket %s... has %d elements, the plan expects %d"
                                      % (b.names[0], t.numel(), pl.padded))

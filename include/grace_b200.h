@@ -165,7 +165,9 @@ int gb_nvls_signal(gb_nvls* p, void* stream);                 /* this rank's cop
 int gb_nvls_reduce(gb_nvls* p, void* d_multicast, int average, void* stream);
 int gb_nvls_launches(gb_nvls* p, int64_t* out);
 
-/* ---- PowerSGD plans (reference: compressor/powersgd.py:7-65, memory/powersgd.py:6-37), rank <= 4.
+/* ---- PowerSGD plans (reference: compressor/powersgd.py:7-65, memory/powersgd.py:6-37), rank <= 16 (rows of P and Q
+ * travel with a pitch of 4, 8 or 16 floats).  gb_psgd_create2 adds warm_start: the averaged Q of one exchange seeds the
+ * next one instead of a fresh normal draw (compressor/powersgd.py:37-39 use_memory); gb_psgd_qprev* expose that state.
  * All >=2-D gradients of a bucket, flattened like a plan (128-element aligned).  One exchange is
  *   gb_psgd_send  (M += e; Q0; P_r = M Q0 on tcgen05/TMEM via TMA; P tiles stored into every peer)
  *   gb_psgd_mid   (wait; P = mean; orthogonalise; Q_r = M^T P^ on tcgen05; Q tiles to every peer)
@@ -174,6 +176,10 @@ int gb_nvls_launches(gb_nvls* p, int64_t* out);
 typedef struct gb_psgd gb_psgd;
 int gb_psgd_create(gb_comm* c, int nmat, const int64_t* rows, const int64_t* cols, const uint32_t* name_hash,
                    int rank, uint32_t seed, int has_memory, int use_tcgen05, gb_psgd** out);
+int gb_psgd_create2(gb_comm* c, int nmat, const int64_t* rows, const int64_t* cols, const uint32_t* name_hash,
+                    int rank, uint32_t seed, int has_memory, int use_tcgen05, int warm_start, gb_psgd** out);
+int gb_psgd_qprev(gb_psgd* p, void** d_ptr, size_t* bytes);
+int gb_psgd_qprev_copy(gb_psgd* p, void* d_buf, int to_plan, void* stream);
 int gb_psgd_destroy(gb_psgd* p);
 int64_t gb_psgd_padded_numel(gb_psgd* p);
 int gb_psgd_offsets(gb_psgd* p, int64_t* out);

@@ -12,9 +12,10 @@ SHAPES = [(512, 4608), (256, 1152), (64, 147), (1000, 2048), (128, 64), (40, 36)
 NAMES = ["m%d.weight" % i for i in range(len(SHAPES))]
 
 
-def oracle(world, rank_r, grads_per_step, memory):
+def oracle(world, rank_r, grads_per_step, memory, warm=False):
     """grads_per_step[step][rank][i] -> outs[step][i] (identical on every rank)."""
     residual = [[torch.zeros(s, device="cuda") for s in SHAPES] for _ in range(world)]
+    qprev = {}
     outs = []
     for step, grads in enumerate(grads_per_step):
         res = []
@@ -22,11 +23,15 @@ def oracle(world, rank_r, grads_per_step, memory):
             n, m = shape
             r = min(n, m, rank_r)
             mats = [grads[w][i] + (residual[w][i] if (memory and step > 0) else 0) for w in range(world)]
-            q0 = philox_normal(m * r, SEED, fnv1a(name), step, STREAM_NORMAL, device="cuda").view(m, r)
+            if warm and name in qprev:
+                q0 = qprev[name]
+            else:
+                q0 = philox_normal(m * r, SEED, fnv1a(name), step, STREAM_NORMAL, device="cuda").view(m, r)
             q0 = orthogonalize(q0.clone())
             p = sum(mt @ q0 for mt in mats) / world
             p = orthogonalize(p)
             q = sum(mt.t() @ p for mt in mats) / world
+            qprev[name] = q
             out = p @ q.t()
             for w in range(world):
                 residual[w][i] = mats[w] - out
@@ -35,10 +40,10 @@ def oracle(world, rank_r, grads_per_step, memory):
     return outs, residual
 
 
-def run_native(world, rank_r, grads_per_step, memory, use_tc):
+def run_native(world, rank_r, grads_per_step, memory, use_tc, warm=False):
     from grace_b200.parallel.engine import Engine, PowerSGDPlan
     engines = Engine.local(world)
-    plans = [PowerSGDPlan(e, SHAPES, NAMES, rank_r, SEED, memory, use_tc) for e in engines]
+    plans = [PowerSGDPlan(e, SHAPES, NAMES, rank_r, SEED, memory, use_tc, warm) for e in engines]
     outs = []
     try:
         for grads in grads_per_step:
@@ -68,7 +73,7 @@ def run_native(world, rank_r, grads_per_step, memory, use_tc):
     return outs, info
 
 
-def make(world, steps, lowrank=False):
+def make(world, steps, lowrank=False, true_rank=2):
     g = torch.Generator(device="cuda").manual_seed(5)
     out = []
     for _ in range(steps):
@@ -77,7 +82,9 @@ def make(world, steps, lowrank=False):
             ts = []
             for (n, m) in SHAPES:
                 if lowrank:
-                    a = torch.randn(n, 2, device="cuda", generator=g) @ torch.randn(2, m, device="cuda", generator=g)
+                    k = min(true_rank, n, m)
+                    scale = torch.logspace(0, -1, k, device="cuda")                 # separated singular values
+                    a = (torch.randn(n, k, device="cuda", generator=g) * scale) @ torch.randn(k, m, device="cuda", generator=g)
                     ts.append(a + 0.01 * torch.randn(n, m, device="cuda", generator=g))
                 else:
                     ts.append(torch.randn(n, m, device="cuda", generator=g))
@@ -112,3 +119,28 @@ def test_tcgen05_gemm_agrees_with_cuda_core_gemm_on_full_rank_noise():
     a, _ = run_native(1, 4, grads, False, True)
     b, _ = run_native(1, 4, grads, False, False)
     compare(a, b[0:1] and [b[0][0]], 2e-2, "tc-vs-simt")
+
+
+@pytest.mark.parametrize("use_tc", [False, True])
+@pytest.mark.parametrize("world,rank_r,memory", [(1, 8, True), (2, 16, True), (2, 6, False)])
+def test_powersgd_ranks_up_to_16(use_tc, world, rank_r, memory):
+    """Reference ranks are free (compressor/powersgd.py:23 ``rank``; the older single-file compressor defaults to 2 with
+    memory): rows of P and Q are stored with a pitch of 8 or 16 floats, CholeskyQR2 runs on a shared-memory Gram matrix.
+    tf32 tolerance for the tensor-core path, fp32 for the CUDA-core path."""
+    grads = make(world, 3, lowrank=True, true_rank=min(rank_r, 8))
+    native, (tc_mats, launches) = run_native(world, rank_r, grads, memory, use_tc)
+    want, _ = oracle(world, rank_r, grads, memory)
+    compare(native, want, 3e-2 if use_tc else 1e-3, "rank%d-%s" % (rank_r, "tc" if use_tc else "simt"))
+
+
+@pytest.mark.parametrize("rank_r", [2, 8])
+def test_powersgd_warm_start(rank_r):
+    """use_memory / warm start (compressor/powersgd.py:37-39): from the second exchange on, Q starts from the previous
+    exchange's averaged Q instead of a fresh normal draw; the state survives a get_state / set_state round trip."""
+    grads = make(2, 4, lowrank=True, true_rank=rank_r)
+    native, _ = run_native(2, rank_r, grads, True, False, warm=True)
+    want, _ = oracle(2, rank_r, grads, True, warm=True)
+    compare(native, want, 2e-3, "warm")
+    fresh, _ = oracle(2, rank_r, grads, True, warm=False)
+    differs = any(float((a - b).norm() / b.norm()) > 1e-3 for a, b in zip(want[2], fresh[2]))
+    assert differs                                            # the warm start is observable in the oracle itself
