@@ -59,10 +59,16 @@ def test_powersgd_spec():
     from grace_b200.dist import grace_from_params
     g = grace_from_params(dict(compressor="powersgd", memory="powersgd", communicator="allreduce", world_size=2,
                                compress_rank=4))
-    assert powersgd_spec(g) == (4, g.compressor.seed, True)
+    assert powersgd_spec(g) == (4, g.compressor.seed, True, False)
     g = grace_from_params(dict(compressor="powersgd", memory="none", communicator="allreduce", world_size=2,
                                compress_rank=8))
-    assert powersgd_spec(g) is None                                                    # rank > 4: generic path
+    assert powersgd_spec(g) == (8, g.compressor.seed, False, False)                    # ranks up to 16 are native
+    g = grace_from_params(dict(compressor="powersgd", memory="powersgd", communicator="allreduce", world_size=2,
+                               compress_rank=2, warm_start=True))
+    assert powersgd_spec(g) == (2, g.compressor.seed, True, True)                      # warm start: native as well
+    g = grace_from_params(dict(compressor="powersgd", memory="none", communicator="allreduce", world_size=2,
+                               compress_rank=17))
+    assert powersgd_spec(g) is None                                                    # beyond UMMA N = 16: generic path
     g = grace_from_params(dict(compressor="topk", memory="none", communicator="allgather", world_size=2))
     assert powersgd_spec(g) is None
 
