@@ -11,8 +11,9 @@
 //   phase 1 (gb_psgd_send):  k3_prep   work = grad + residual; zero accumulators
 //                            k3_q0     Philox normal Q0, CholeskyQR2 orthogonalisation, Q0^T (K-major B operand)
 //                            k3_gemm<1> P_r = M Q0 : TMA -> smem (128B swizzle) -> tcgen05.mma kind::tf32 ->
-//                                      TMEM -> tcgen05.ld epilogue.  Split-K partials are red.add'ed into a local
-//                                      accumulator; the CTA that completes a 128-row tile stores that tile straight
+//                                      TMEM -> tcgen05.ld epilogue.  Split-K slices store their partial tiles; the
+//                                      CTA that completes a 128-row tile adds them in slice order (no floating-point
+//                                      atomics: the same bits on every run) and stores that tile straight
 //                                      into EVERY peer's slot (P2P st.global over NVLink) -- the all-reduce is an
 //                                      all-gather of tiny P_r tiles + rank-ordered sum on the receiver.
 //                            k3_flag   releases the epoch flags (and pushes tiles of matrices that took the
@@ -54,13 +55,14 @@ struct PsMat {          // one matrix of the bucket (device copy)
 struct PsBand { int32_t mat, i0; };   // one CTA of k3_final: 32 rows of one matrix
 
 struct PsItem {         // one CTA of a grouped GEMM launch
-  int32_t mat, tile, m0, k0, k1, nchunks;
+  int32_t mat, tile, m0, k0, k1, nchunks, chunk;   // chunk: index of this K slice inside its tile (items of a tile are consecutive)
 };
 
 struct gb_psgd {
   gb_comm* comm;
   int nmat, rank_r, has_mem, use_tc;
   int rp;                   // row pitch of the stored P / Q rows in floats: 4, 8 or 16 (rank rounded up)
+  float *d_part1, *d_part2; // split-K partial tiles of the two grouped GEMMs [items][128][rp]
   float* d_qprev;           // warm start: the previous exchange's averaged Q [qrows][rp] (null: fresh Q every step)
   uint32_t seed, step, epoch;
   int64_t padded, prows, qrows;
@@ -161,7 +163,7 @@ __device__ float g_dbg_dump[8192];
 
 template <int MODE, int RP>
 __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ items, const PsMat* __restrict__ mats,
-                                                  const CUtensorMap* __restrict__ maps, float* acc, uint32_t* tile_cnt,
+                                                  const CUtensorMap* __restrict__ maps, float* part, uint32_t* tile_cnt,
                                                   PsPeers peers, const StepCtl* ctl, size_t par_stride) {
   extern __shared__ uint8_t smem_raw[];
   if (ctl->epoch & 1) shift(peers, par_stride);
@@ -252,7 +254,6 @@ __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ ite
     const int row = it.m0 + q * 32 + lane;
     const int nrows = MODE == 1 ? mt.n : mt.m;
     const int row0 = MODE == 1 ? mt.prow0 : mt.qrow0;
-    float* dst = acc + (size_t)(row0 + row) * RP;
     const bool live = row < nrows;
     if (it.nchunks == 1) {
       if (live) {
@@ -264,19 +265,28 @@ __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ ite
         }
       }
     } else {
-      if (live) {
+      // split-K without floating-point atomics: every K slice stores its partial tile, the CTA that completes the
+      // tile adds the slices in slice order (same bits on every run and every rank) and ships the sum
+      const int rl = q * 32 + lane;                                 // row inside the 128-row tile
+      float4* mine = reinterpret_cast<float4*>(part + ((size_t)blockIdx.x * PS_BM + rl) * RP);
 #pragma unroll
-        for (int c = 0; c < RP; ++c) atomicAdd(dst + c, __uint_as_float(v[c]));
-      }
+      for (int c4 = 0; c4 < RP / 4; ++c4)
+        mine[c4] = make_float4(__uint_as_float(v[c4 * 4]), __uint_as_float(v[c4 * 4 + 1]), __uint_as_float(v[c4 * 4 + 2]),
+                               __uint_as_float(v[c4 * 4 + 3]));
       __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (threadIdx.x == 64) *last_flag = (atomicAdd(tile_cnt + it.tile, 1u) == (uint32_t)it.nchunks - 1) ? 1u : 0u;
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (*last_flag && live) {                 // this CTA completed the tile: ship it to every peer
         __threadfence();
+        const size_t item0 = (size_t)blockIdx.x - it.chunk;
 #pragma unroll
         for (int c4 = 0; c4 < RP / 4; ++c4) {
-          const float4 o = __ldcg(reinterpret_cast<const float4*>(dst) + c4);
+          float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int ch = 0; ch < it.nchunks; ++ch) {
+            const float4 x = __ldcg(reinterpret_cast<const float4*>(part + ((item0 + ch) * PS_BM + rl) * RP) + c4);
+            o.x += x.x; o.y += x.y; o.z += x.z; o.w += x.w;
+          }
           for (int r = 0; r < peers.n; ++r) reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP)[c4] = o;
         }
       }
@@ -771,7 +781,7 @@ static void build_items(const std::vector<PsMat>& mats, int mode, std::vector<Ps
     const int nch = (kdim + chunk - 1) / chunk;
     for (int t = 0; t < mtiles; ++t) {
       for (int c = 0; c < nch; ++c)
-        items.push_back(PsItem{mi, ntiles, t * PS_BM, c * chunk, std::min(kdim, (c + 1) * chunk), nch});
+        items.push_back(PsItem{mi, ntiles, t * PS_BM, c * chunk, std::min(kdim, (c + 1) * chunk), nch, c});
       ++ntiles;
     }
   }
@@ -845,6 +855,8 @@ static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, con
   GB_CUDA(cudaMalloc((void**)&p->d_pacc, (p->prows + 8) * RP * 4));
   GB_CUDA(cudaMalloc((void**)&p->d_qacc, (p->qrows + 8) * RP * 4 * 2));   // second half: Q0 scratch for k3_q0
   GB_CUDA(cudaMalloc((void**)&p->d_ph, (p->prows + 8) * RP * 4));
+  GB_CUDA(cudaMalloc((void**)&p->d_part1, (it1.size() + 1) * PS_BM * RP * 4));
+  GB_CUDA(cudaMalloc((void**)&p->d_part2, (it2.size() + 1) * PS_BM * RP * 4));
   if (warm_start) {
     GB_CUDA(cudaMalloc((void**)&p->d_qprev, (p->qrows + 8) * RP * 4));
     GB_CUDA(cudaMemset(p->d_qprev, 0, (p->qrows + 8) * RP * 4));
@@ -902,6 +914,8 @@ extern "C" int gb_psgd_destroy(gb_psgd* p) {
   cudaFree(p->d_maps);
   cudaFree(p->d_bands);
   cudaFree(p->d_qprev);
+  cudaFree(p->d_part1);
+  cudaFree(p->d_part2);
   delete p;
   return 0;
 }
@@ -997,7 +1011,7 @@ extern "C" int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream) {
   LAUNCHED(p);
   const PsPeers ps = peer_slots(p, p->off_p, p->slot_p);
   if (p->nitems1) {
-    PS_DISPATCH(p->rp, (k3_gemm<1, RP><<<p->nitems1, 192, PS_SMEM, st>>>(p->d_items1, p->d_mat, p->d_maps, p->d_pacc, p->d_cnt1, ps, p->d_ctl, psp)));
+    PS_DISPATCH(p->rp, (k3_gemm<1, RP><<<p->nitems1, 192, PS_SMEM, st>>>(p->d_items1, p->d_mat, p->d_maps, p->d_part1, p->d_cnt1, ps, p->d_ctl, psp)));
     LAUNCHED(p);
   }
   int simt_rows = 0;
@@ -1030,7 +1044,7 @@ extern "C" int gb_psgd_mid(gb_psgd* p, void* stream) {
   LAUNCHED(p);
   const PsPeers qs = peer_slots(p, p->off_q, p->slot_q);
   if (p->nitems2) {
-    PS_DISPATCH(p->rp, (k3_gemm<2, RP><<<p->nitems2, 192, PS_SMEM, st>>>(p->d_items2, p->d_mat, p->d_maps, p->d_qacc, p->d_cnt2, qs, p->d_ctl, psq)));
+    PS_DISPATCH(p->rp, (k3_gemm<2, RP><<<p->nitems2, 192, PS_SMEM, st>>>(p->d_items2, p->d_mat, p->d_maps, p->d_part2, p->d_cnt2, qs, p->d_ctl, psq)));
     LAUNCHED(p);
   }
   int simt_cols = 0;

@@ -144,3 +144,15 @@ def test_powersgd_warm_start(rank_r):
     fresh, _ = oracle(2, rank_r, grads, True, warm=False)
     differs = any(float((a - b).norm() / b.norm()) > 1e-3 for a, b in zip(want[2], fresh[2]))
     assert differs                                            # the warm start is observable in the oracle itself
+
+
+def test_powersgd_is_bit_reproducible():
+    """Split-K slices are added in slice order by the CTA that completes a tile (no floating-point atomics): two runs
+    of the same exchange give the same bits."""
+    grads = make(2, 2, lowrank=False)
+    a, _ = run_native(2, 4, grads, True, True)
+    b, _ = run_native(2, 4, grads, True, True)
+    for sa, sb in zip(a, b):
+        for ra, rb in zip(sa, sb):
+            for x, y in zip(ra, rb):
+                assert torch.equal(x, y)
