@@ -39,6 +39,19 @@ void gb_set_error(const char* fmt, ...);
 // status word bits written by kernels (host-visible, see engine.cu)
 #define GB_STATUS_TIMEOUT 1u
 #define GB_STATUS_OVERFLOW 2u
+#define GB_STATUS_GUARD 4u      // a guard band behind a wire slot was overwritten (GRACE_B200_GUARD=1)
+#define GB_STATUS_ASSERT 8u     // a bounds assertion of a -DGB_DEBUG build failed (the store was skipped)
+#define GB_GUARD_BYTES 256
+#define GB_GUARD_WORD 0x7FC0DEADu   // a NaN pattern no codec produces
+
+// Bounds assertions of the debug build (bash csrc/build.sh with GB_NVCC_EXTRA=-DGB_DEBUG): a failed check raises a
+// status bit that Engine.check_status() turns into an exception, and skips the offending store.  compute-sanitizer
+// is not available on the GPU pool, so this and the guard bands are what watches the peer stores.
+#ifdef GB_DEBUG
+#define GB_ASSERT_STORE(cond, status) ((cond) ? true : (atomicOr((status), GB_STATUS_ASSERT), false))
+#else
+#define GB_ASSERT_STORE(cond, status) (true)
+#endif
 
 // ---------------------------------------------------------------- memory-model helpers
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {

@@ -51,6 +51,7 @@ static int comm_init_common(gb_comm* c, size_t arena_bytes) {
   }
   c->need_bytes = 0;
   c->siblings = nullptr;
+  c->guard = getenv("GRACE_B200_GUARD") && atoi(getenv("GRACE_B200_GUARD")) != 0;
   c->barrier_epoch = 0;
   for (int i = 0; i < GB_MAX_WORLD; ++i) { c->peer[i] = nullptr; c->opened[i] = false; }
   c->peer[c->rank] = c->base;
@@ -163,6 +164,45 @@ int gb_comm_alloc_channel(gb_comm* c, size_t slot_bytes, int* channel, size_t* o
   *channel = c->next_channel++;
   *offset = cursor | ((size_t)c->extra.size() << GB_REGION_SHIFT);
   cursor += need;
+  if (c->guard && slot_bytes > GB_GUARD_BYTES) {
+    // poison the last GB_GUARD_BYTES of each of the 2 * W slots of this channel in MY arena (peers write here)
+    const size_t sb = (slot_bytes + 255) & ~size_t(255);
+    char* first = gb_slot_of(c, c->rank, *offset, sb, 0, 0) + sb - GB_GUARD_BYTES;
+    std::vector<uint32_t> pat(GB_GUARD_BYTES / 4, GB_GUARD_WORD);
+    for (int s = 0; s < 2 * c->world; ++s)
+      GB_CUDA(cudaMemcpy(first + (size_t)s * sb, pat.data(), GB_GUARD_BYTES, cudaMemcpyHostToDevice));
+    c->guarded.push_back(gb_comm::GuardRec{*offset, sb});
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------- guard bands
+__global__ void guard_check_kernel(const uint32_t* band, size_t stride_words, int nslots, uint32_t* status) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nslots * (GB_GUARD_BYTES / 4); i += gridDim.x * blockDim.x) {
+    const int s = i / (GB_GUARD_BYTES / 4), w = i % (GB_GUARD_BYTES / 4);
+    if (band[(size_t)s * stride_words + w] != GB_GUARD_WORD) atomicOr(status, GB_STATUS_GUARD);
+  }
+}
+
+// test hook: overwrite one word of the first guard band, as a stray peer store would
+extern "C" int gb_comm_guard_poke(gb_comm* c) {
+  GB_CHECK(!c->guarded.empty(), "no guarded channel");
+  const gb_comm::GuardRec& g = c->guarded.front();
+  char* first = gb_slot_of(c, c->rank, g.chan_off, g.slot_bytes, 0, 0) + g.slot_bytes - GB_GUARD_BYTES;
+  GB_CUDA(cudaMemset(first + 8, 0, 4));
+  return 0;
+}
+
+// Scans the guard band behind every wire slot of this rank's arena (GRACE_B200_GUARD=1); an overwritten band raises
+// GB_STATUS_GUARD.  Synchronises the device; meant for tests and debugging runs.
+extern "C" int gb_comm_check_guards(gb_comm* c, int* nchannels) {
+  if (nchannels) *nchannels = (int)c->guarded.size();
+  for (const gb_comm::GuardRec& g : c->guarded) {
+    const char* first = gb_slot_of(c, c->rank, g.chan_off, g.slot_bytes, 0, 0) + g.slot_bytes - GB_GUARD_BYTES;
+    guard_check_kernel<<<2, 256>>>((const uint32_t*)first, g.slot_bytes / 4, 2 * c->world, c->status_dev);
+    GB_CUDA(cudaGetLastError());
+  }
+  GB_CUDA(cudaDeviceSynchronize());
   return 0;
 }
 

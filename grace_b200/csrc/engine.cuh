@@ -39,7 +39,15 @@ struct gb_comm {
   std::vector<gb_region> extra;   // regions 1.. (same order and sizes on every rank)
   size_t need_bytes;              // bytes the last failed channel allocation asked for (0 = none pending)
   gb_comm** siblings;             // local (single-process) groups: all virtual ranks, for collective growth
+  bool guard;                     // GRACE_B200_GUARD=1: every wire slot ends in a poisoned guard band
+  struct GuardRec { size_t chan_off, slot_bytes; };
+  std::vector<GuardRec> guarded;  // channels whose slots carry a guard band
 };
+
+// slot size as allocated: rounded to 256 bytes, plus the guard band when the communicator has guards on
+static inline size_t gb_guarded(const gb_comm* c, size_t bytes) {
+  return bytes ? ((bytes + 255) & ~size_t(255)) + (c->guard ? GB_GUARD_BYTES : 0) : 0;
+}
 
 int gb_comm_alloc_channel(gb_comm* c, size_t slot_bytes, int* channel, size_t* offset);
 PeerPtrs gb_comm_peers(const gb_comm* c);

@@ -37,6 +37,7 @@ struct TkDev {
   uint32_t* mask;     // [ntiles][128]  bit e of a tile = element e lies in the tensor's threshold bin
   int32_t* tiecnt;    // [ntiles]
   uint32_t* done;     // [16] grid-wide last-block counters
+  uint32_t* status;   // engine status word (debug-build bounds assertions)
 };
 
 struct TkHost {
@@ -460,7 +461,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
     if (lane == 0) *reinterpret_cast<uint4*>(mrow + (j * 8 + wid) * 4) = make_uint4(m0, m1, m2, m3);               \
   }
   int it = 0, b = 0;                               // b = it % 3: staging buffer of this tile
-  int pend_tc = 0, pend_b = -1;                    // thread 0: claim of the previous tile, not yet published
+  int pend_tc = 0, pend_b = -1, pend_k = 0;        // thread 0: claim of the previous tile, not yet published
   uint32_t pend_raw = 0;
   for (int tile = t0; tile < t1; ++tile, ++it) {
     const int st = it & 1;
@@ -509,6 +510,8 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
     // consumed here, so its round trip to L2 overlapped this tile's classification instead of holding up the barrier
     if (threadIdx.x == 0 && pend_b >= 0) {
       const int pb = *(volatile int*)&s_kb[pend_b] + (int)pend_raw;      // first use of the atomic's return value
+      // debug build: a tile's certain picks must stay inside its tensor's k payload entries
+      if (!GB_ASSERT_STORE(pend_raw + (uint32_t)pend_tc <= (uint32_t)pend_k, d.status)) s_tc[pend_b] = 0;
       s_begin[pend_b] = pb;
       TK_PEERS(r) TK_HDR(out, r, psh)[tile - 1] = make_int2(pb, pend_tc);
     }
@@ -520,6 +523,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
       s_kb[b] = (int)t.seg_kbase[seg];
       pend_raw = tc ? atomicAdd(d.sel + seg * TK_SEL + S_CURA, (uint32_t)tc) : 0u;
       pend_tc = tc;
+      pend_k = t.seg_k[seg];
       pend_b = b;
       s_tc[b] = tc; s_len[b] = len; s_local0[b] = local0; s_bin[b] = bin; s_base[b] = (long long)base;
       scnt[bprev] = 0;                             // buffer of the tile after the next one (its last user is stored by now)
@@ -530,6 +534,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
   }
   if (threadIdx.x == 0 && pend_b >= 0) {
     const int pb = s_kb[pend_b] + (int)pend_raw;
+    if (!GB_ASSERT_STORE(pend_raw + (uint32_t)pend_tc <= (uint32_t)pend_k, d.status)) s_tc[pend_b] = 0;
     s_begin[pend_b] = pb;
     TK_PEERS(r) TK_HDR(out, r, psh)[t1 - 1] = make_int2(pb, pend_tc);
   }
@@ -775,10 +780,17 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work
       }
       int begin = 0;
       if (lane == 0) {
-        if (nsel) begin = (int)t.seg_kbase[seg] + (int)atomicAdd(s + S_CURA, (uint32_t)nsel);
+        if (nsel) {
+          const uint32_t at = atomicAdd(s + S_CURA, (uint32_t)nsel);
+          begin = (int)t.seg_kbase[seg] + (int)at;
+          if (!GB_ASSERT_STORE(at + (uint32_t)nsel <= (uint32_t)t.seg_k[seg], d.status)) nsel = 0;     // debug build
+        }
         TK_PEERS(r) TK_HDR(out, r, psh)[xoff + tile] = make_int2(begin, nsel);
       }
       begin = __shfl_sync(0xffffffffu, begin, 0);
+#ifdef GB_DEBUG
+      nsel = __shfl_sync(0xffffffffu, nsel, 0);
+#endif
       for (int i = lane; i < nsel; i += 32) {
         const int e = pos[i];
         const float v = val[i];
@@ -890,6 +902,7 @@ int tk_init(gb_plan* p) {
   h->d.mask = (uint32_t*)(b + o_mask);
   h->d.tiecnt = (int32_t*)(b + o_tc);
   h->d.done = (uint32_t*)(b + o_done);
+  h->d.status = p->comm->status_dev;
   return 0;
 }
 

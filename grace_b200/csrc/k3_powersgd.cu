@@ -890,8 +890,8 @@ static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, con
   GB_CUDA(cudaFuncSetAttribute(k3_gemm<2, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
   GB_CUDA(cudaFuncSetAttribute(k3_gemm<1, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
   GB_CUDA(cudaFuncSetAttribute(k3_gemm<2, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM));
-  p->slot_p = ((size_t)(p->prows + 8) * RP * 4 + 255) & ~size_t(255);
-  p->slot_q = ((size_t)(p->qrows + 8) * RP * 4 + 255) & ~size_t(255);
+  p->slot_p = gb_guarded(c, (size_t)(p->prows + 8) * RP * 4);
+  p->slot_q = gb_guarded(c, (size_t)(p->qrows + 8) * RP * 4);
   // both channels in one request, so that a retry after the arena has grown does not leave a half-allocated pair behind
   {
     size_t need2 = (p->slot_p + p->slot_q) * 2 * (size_t)c->world;

@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(GB_THREADS) gb_ops_collect(OpsPeers src, size_
 extern "C" int gb_ops_create(gb_comm* c, size_t slot_bytes, gb_ops** out) {
   gb_ops* o = new gb_ops();
   o->comm = c;
-  o->slot_bytes = (slot_bytes + 255) & ~size_t(255);
+  o->slot_bytes = gb_guarded(c, slot_bytes);
   o->epoch = 0;
   o->launches = 0;
   o->d_done = nullptr;
@@ -111,7 +111,7 @@ extern "C" int gb_ops_destroy(gb_ops* o) {
   return 0;
 }
 
-extern "C" size_t gb_ops_capacity(gb_ops* o) { return o->slot_bytes; }
+extern "C" size_t gb_ops_capacity(gb_ops* o) { return o->slot_bytes - (o->comm->guard ? GB_GUARD_BYTES : 0); }
 extern "C" int64_t gb_ops_launches(gb_ops* o) { return o->launches; }
 
 static int ops_grid(size_t n16) { return (int)std::min<size_t>((n16 + GB_THREADS - 1) / GB_THREADS + 1, 148 * 4); }
@@ -131,7 +131,7 @@ static void ops_slots(gb_ops* o, uint32_t epoch, OpsPeers* dst, OpsPeers* src) {
 
 extern "C" int gb_ops_send(gb_ops* o, const void* d_src, size_t nbytes, void* stream) {
   gb_comm* c = o->comm;
-  GB_CHECK(nbytes % 16 == 0 && nbytes <= o->slot_bytes, "gb_ops_send: %zu bytes (slot capacity %zu, multiple of 16 required)",
+  GB_CHECK(nbytes % 16 == 0 && nbytes <= gb_ops_capacity(o), "gb_ops_send: %zu bytes (slot capacity %zu, multiple of 16 required)",
            nbytes, o->slot_bytes);
   GB_CHECK(((uintptr_t)d_src & 15) == 0, "gb_ops_send: 16-byte alignment");
   const uint32_t epoch = ++o->epoch;
@@ -149,7 +149,7 @@ extern "C" int gb_ops_recv(gb_ops* o, size_t nbytes, int first, int count, size_
                            void* stream) {
   gb_comm* c = o->comm;
   GB_CHECK(o->epoch > 0, "gb_ops_recv before gb_ops_send");
-  GB_CHECK(nbytes % 16 == 0 && nbytes <= o->slot_bytes && stride % 16 == 0 && ((uintptr_t)d_out & 15) == 0,
+  GB_CHECK(nbytes % 16 == 0 && nbytes <= gb_ops_capacity(o) && stride % 16 == 0 && ((uintptr_t)d_out & 15) == 0,
            "gb_ops_recv: sizes must be multiples of 16 within the slot capacity");
   GB_CHECK(first >= 0 && count >= 1 && first + count <= c->world, "gb_ops_recv: rank range");
   OpsPeers dst, src;

@@ -185,6 +185,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->dense2 = (params->codec == GB_CODEC_NONE || params->codec == GB_CODEC_FP16) && params->memory == GB_MEM_NONE &&
               c->world > 1 && !getenv("GRACE_B200_NO_K0");   // with a residual memory the K2 path keeps the state
   if (p->dense2) p->slot_bytes = k0_slot_bytes(p->padded, c->world, p->bits);
+  p->slot_bytes = gb_guarded(c, p->slot_bytes);
   if (gb_comm_alloc_channel(c, p->slot_bytes, &p->channel, &p->chan_off)) return -1;
   if (p->dense2) {
     // second flag channel for the gather phase (no payload of its own)
@@ -196,7 +197,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   p->slot2_bytes = 0;
   if (params->memory == GB_MEM_DGC && params->clip) {
     // every rank's per-tensor sum(g^2) travels through a small channel of its own
-    p->slot2_bytes = ((size_t)nseg * 4 + 255) & ~size_t(255);
+    p->slot2_bytes = gb_guarded(c, (size_t)nseg * 4);
     if (gb_comm_alloc_channel(c, p->slot2_bytes, &p->channel2, &p->chan2_off)) return -1;
   }
   p->slot_bytes = (p->slot_bytes + 255) & ~size_t(255);

@@ -61,6 +61,8 @@ def _declare(L):
         "gb_comm_destroy": (i32, [vp]),
         "gb_comm_status": (i32, [vp, P(u32)]),
         "gb_comm_clear_status": (i32, [vp]),
+        "gb_comm_check_guards": (i32, [vp, P(i32)]),
+        "gb_comm_guard_poke": (i32, [vp]),
         "gb_comm_set_timeout_ms": (i32, [vp, C.c_uint64]),
         "gb_comm_rank": (i32, [vp]),
         "gb_comm_world": (i32, [vp]),

@@ -79,12 +79,24 @@ class Engine:
         return out.value
 
     def check_status(self):
+        if os.environ.get("GRACE_B200_GUARD", "0") not in ("", "0") and not torch.cuda.is_current_stream_capturing():
+            check(native.lib().gb_comm_check_guards(self._h, None))      # debugging runs: scan the guard bands first
         s = self.status()
         if s:
             native.lib().gb_comm_clear_status(self._h)
             what = [n for b, n in ((1, "peer flag wait timed out (a rank is missing or hung)"),
-                                   (2, "variable-size payload exceeded the slot capacity")) if s & b]
+                                   (2, "variable-size payload exceeded the slot capacity"),
+                                   (4, "a guard band behind a wire slot was overwritten"),
+                                   (8, "a bounds assertion of the debug build failed")) if s & b]
             raise native.NativeError("engine status 0x%x: %s" % (s, "; ".join(what)))
+
+    def check_guards(self):
+        """Scan the poisoned guard bands behind this rank's wire slots (``GRACE_B200_GUARD=1``); raises through
+        ``check_status`` when a peer store ran past its slot.  Returns the number of guarded channels."""
+        n = C.c_int()
+        check(native.lib().gb_comm_check_guards(self._h, C.byref(n)))
+        self.check_status()
+        return n.value
 
     def set_timeout_ms(self, ms):
         check(native.lib().gb_comm_set_timeout_ms(self._h, int(ms)))

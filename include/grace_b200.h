@@ -81,7 +81,11 @@ int gb_comm_open_peers(gb_comm* c, const void* handles);         /* world * 64 b
 /* `world` virtual ranks on the current device (tests, single-GPU emulation of the protocol) */
 int gb_comm_create_local(int world, size_t arena_bytes, gb_comm** out /* [world] */);
 int gb_comm_destroy(gb_comm* c);
-int gb_comm_status(gb_comm* c, uint32_t* out);                   /* 0 ok; bit0 timeout; bit1 overflow */
+int gb_comm_status(gb_comm* c, uint32_t* out);                   /* 0 ok; bit0 timeout; bit1 overflow; bit2 guard band
+                                                                    overwritten; bit3 debug-build bounds assertion */
+/* With GRACE_B200_GUARD=1 (set before the communicator is created, on every rank) each wire slot ends in a 256-byte
+ * poisoned band that no kernel may touch; this scans them (device synchronisation) and raises status bit 2. */
+int gb_comm_check_guards(gb_comm* c, int* nchannels);
 int gb_comm_clear_status(gb_comm* c);
 int gb_comm_set_timeout_ms(gb_comm* c, uint64_t ms);
 int gb_comm_rank(gb_comm* c);

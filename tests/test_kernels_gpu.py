@@ -627,3 +627,44 @@ def test_point_collectives_over_the_arena(world):
     finally:
         for e in engines:
             e.destroy()
+
+
+def test_guard_bands_catch_a_stray_peer_store(monkeypatch):
+    """compute-sanitizer is closed on the GPU pool; the substitute: with GRACE_B200_GUARD=1 every wire slot ends in a
+    poisoned 256-byte band that no kernel may touch.  A full exchange of several codec families leaves all bands intact;
+    one overwritten word is reported through the status word."""
+    from grace_b200.ops import native
+    from grace_b200.ops.native import NativeError
+    from grace_b200.parallel.engine import Engine, PowerSGDPlan
+    monkeypatch.setenv("GRACE_B200_GUARD", "1")
+    engines = Engine.local(2, arena_bytes=64 << 20)
+    try:
+        grads = make_grads(2, 1)[0]
+        for codec, memory in (("topk", "residual"), ("qsgd", "none"), ("signsgd", "none"), ("threshold", "none"), ("fp16", "none")):
+            plans = [e.plan(SIZES, NAMES, _params(codec, memory)) for e in engines]
+            bufs = [_flat(plans[r], grads[r]) for r in range(2)]
+            for r in range(2):
+                plans[r].send(bufs[r])
+            for r in range(2):
+                plans[r].mid()
+            for r in range(2):
+                plans[r].recv(torch.empty(plans[r].padded, device="cuda"))
+        pp = [PowerSGDPlan(e, [(64, 96), (40, 36)], ["a.weight", "b.weight"], 4, 7, True, True) for e in engines]
+        bufs = [torch.randn(pp[0].padded, device="cuda") for _ in range(2)]
+        for r in range(2):
+            pp[r].send(bufs[r])
+        for r in range(2):
+            pp[r].mid()
+        for r in range(2):
+            pp[r].recv(torch.empty(pp[r].padded, device="cuda"))
+        torch.cuda.synchronize()
+        for e in engines:
+            assert e.check_guards() >= 6                      # every plan's channel is guarded, none was touched
+        native.check(native.lib().gb_comm_guard_poke(engines[1]._h))
+        with pytest.raises(NativeError, match="guard band"):
+            engines[1].check_guards()
+        engines[0].check_guards()                             # the other rank's arena is intact
+    finally:
+        monkeypatch.delenv("GRACE_B200_GUARD")
+        for e in engines:
+            e.destroy()
