@@ -21,6 +21,9 @@ sys.path.insert(0, ROOT)
 import torch
 import torch.distributed as dist
 
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from clocks import ClockSampler  # noqa: E402
+
 CODECS = [("none", "none"), ("fp16", "none"), ("topk", "residual"), ("randomk", "residual"), ("threshold", "residual"),
           ("dgc", "dgc"), ("qsgd", "none"), ("terngrad", "residual"), ("natural", "residual"), ("u8bit", "none"),
           ("signsgd", "none"), ("signum", "residual"), ("efsignsgd", "efsignsgd"), ("onebit", "residual"),
@@ -80,6 +83,7 @@ def main():
                 flush_r.sum()              # evicts the dirty lines of the write before the timed region starts
     flush = _Flush()
     rows = []
+    sampler = ClockSampler(torch.cuda.current_device()) if rank == 0 else None
     want = [c for c in args.codecs.split(",") if c]
     for comp, mem in CODECS:
         if want and comp not in want:
@@ -89,8 +93,10 @@ def main():
         c = build_compressor(prm, "dist", world)
         m = build_memory(prm, "dist", world, c)
         cp = codec_params(c, m)
-        if comp in ("threshold", "dgc", "adaq"):
+        if comp in ("dgc", "adaq"):
             cp.capacity = 0.1              # variable-size payload: slots hold up to 10 % of the bucket
+        if comp == "threshold":
+            cp.capacity = 0.25             # |x| > 2.5 sigma selects ~1.2 % of fresh noise; the residual raises that
         try:
             plan = eng.plan([n for _, n in named], [k for k, _ in named], cp)
         except Exception as exc:
@@ -100,6 +106,7 @@ def main():
         grad = torch.randn(plan.padded, device="cuda")
         out = torch.empty(plan.padded, device="cuda")
         times = []
+        t_begin = time.time()
         graph = None
         if args.graph:
             # epochs and codec steps live in device memory, so one captured exchange can be replayed
@@ -145,7 +152,8 @@ def main():
         roof = max(t_hbm, t_link)
         rows.append(dict(codec=comp, memory=mem, world=world, elements=numel, ms=ms, launches_per_exchange=None,
                          wire_bytes_per_peer=wire, roofline_ms=roof, fraction_of_roofline=roof / ms,
-                         grad_gbs=numel * 4 / ms / 1e6, peaks=how))
+                         grad_gbs=numel * 4 / ms / 1e6, peaks=how,
+                         clocks=sampler.window(t_begin, time.time()) if sampler else None))
         n0 = plan.launches()
         plan.send(grad); plan.recv(out)
         rows[-1]["launches_per_exchange"] = plan.launches() - n0
@@ -173,6 +181,7 @@ def main():
             plan = NvlsPlan(eng, padded, hd.multicast_ptr + (buf.data_ptr() - hd.buffer_ptrs[rank]), True)
             buf.normal_()
             times = []
+            t_nv = time.time()
             for it in range(args.warmup + args.iters):
                 flush.zero_()
                 dist.barrier()
@@ -191,7 +200,7 @@ def main():
             eng.check_status()
             busbw = 2 * (world - 1) / world * numel * 4 / ms / 1e6
             rows.append(dict(codec="none-nvls", memory="none", world=world, elements=numel, ms=ms, launches_per_exchange=2,
-                             bus_bandwidth_gbs=busbw, peaks=how))
+                             bus_bandwidth_gbs=busbw, peaks=how, clocks=sampler.window(t_nv, time.time()) if sampler else None))
             if rank == 0:
                 print("%-10s %-9s W=%d  %8.3f ms  all-reduce bus bandwidth %.0f GB/s (NCCL reference on this pool: 725 GB/s at 1 GiB)"
                       % ("none-nvls", "none", world, ms, busbw), flush=True)
@@ -202,6 +211,7 @@ def main():
         # library baseline: one NCCL all-reduce (+ 1/W scale) of the same 102 MB buffer, timed the same way
         buf = torch.randn((numel + 127) // 128 * 128, device="cuda")
         times = []
+        t_nc = time.time()
         for it in range(args.warmup + args.iters):
             flush.zero_()
             dist.barrier()
@@ -220,7 +230,7 @@ def main():
         ms = float(t)
         busbw = 2 * (world - 1) / world * numel * 4 / ms / 1e6
         rows.append(dict(codec="nccl-allreduce", memory="none", world=world, elements=numel, ms=ms, launches_per_exchange=2,
-                         bus_bandwidth_gbs=busbw, peaks=how))
+                         bus_bandwidth_gbs=busbw, peaks=how, clocks=sampler.window(t_nc, time.time()) if sampler else None))
         if rank == 0:
             print("%-10s %-9s W=%d  %8.3f ms  all-reduce bus bandwidth %.0f GB/s (library baseline: dist.all_reduce + div_)"
                   % ("nccl", "none", world, ms, busbw), flush=True)
@@ -236,6 +246,7 @@ def main():
             grad = torch.randn(plan.padded, device="cuda")
             out = torch.empty(plan.padded, device="cuda")
             times = []
+            t_ps = time.time()
             for it in range(args.warmup + args.iters):
                 flush.zero_()
                 if world > 1:
@@ -262,13 +273,16 @@ def main():
             rows.append(dict(codec="powersgd-r4" + ("-tcgen05" if use_tc else "-simt"), memory="powersgd", world=world,
                              elements=n_el, ms=ms, launches_per_exchange=plan.launches() - n0,
                              wire_bytes_per_peer=plan.wire_bytes, roofline_ms=roof, fraction_of_roofline=roof / ms,
-                             grad_gbs=n_el * 4 / ms / 1e6, peaks=how, tc_matrices=plan.tc_matrices))
+                             grad_gbs=n_el * 4 / ms / 1e6, peaks=how, tc_matrices=plan.tc_matrices,
+                             clocks=sampler.window(t_ps, time.time()) if sampler else None))
             if rank == 0:
                 r = rows[-1]
                 print("%-22s W=%d  %8.3f ms  %7.1f GB/s of gradient  wire %9d B/peer  roofline %6.3f ms (%.2f of %s)  launches %d  tcgen05 matrices %d/%d"
                       % (r["codec"], world, ms, r["grad_gbs"], plan.wire_bytes, roof, r["fraction_of_roofline"], how,
                          r["launches_per_exchange"], plan.tc_matrices, len(shapes)), flush=True)
             plan.destroy()
+    if sampler:
+        sampler.close()
     if rank == 0 and args.out:
         with open(args.out, "w") as f:
             json.dump(rows, f, indent=1)

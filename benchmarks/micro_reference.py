@@ -19,8 +19,13 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "baseline", "_ref"))      # the reference's grace_dl, not this repo's shim
 
+import time
+
 import torch
 import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from clocks import ClockSampler  # noqa: E402
 
 CODECS = [("none", "none", "allreduce"), ("fp16", "none", "allreduce"), ("topk", "residual", "allgather"),
           ("randomk", "residual", "allreduce"), ("threshold", "residual", "allgather"), ("dgc", "dgc", "allgather"),
@@ -48,8 +53,13 @@ def main():
     import grace_dl
     assert "baseline/_ref" in os.path.realpath(grace_dl.__file__), grace_dl.__file__
     from grace_dl.dist.helper import grace_from_params
-    import torchvision
-    named = [(n, tuple(p.shape)) for n, p in getattr(torchvision.models, args.shape)().named_parameters()]
+    if args.shape.startswith("flat:"):           # one tensor of N elements (BASELINE config 5 sizes); 2-D so that PowerSGD applies
+        n_el = int(args.shape.split(":")[1])
+        named = [("flat", (n_el // 4096, 4096) if n_el % 4096 == 0 else (n_el,))]
+    else:
+        import torchvision
+        named = [(n, tuple(p.shape)) for n, p in getattr(torchvision.models, args.shape)().named_parameters()]
+    sampler = ClockSampler(torch.cuda.current_device()) if rank == 0 else None
     numel = sum(int(torch.tensor(s).prod()) for _, s in named)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     want = [c for c in args.codecs.split(",") if c]
@@ -73,8 +83,10 @@ def main():
         return float(t)
 
     flat = torch.randn(numel, device="cuda")
+    t_b = time.time()
     ms = timed(lambda: dist.all_reduce(flat))
-    rows.append(dict(codec="nccl-allreduce-flat", world=world, ms=ms, elements=numel))
+    rows.append(dict(codec="nccl-allreduce-flat", world=world, ms=ms, elements=numel,
+                     clocks=sampler.window(t_b, time.time()) if sampler else None))
     if rank == 0:
         print("%-22s W=%d %9.3f ms  (one NCCL all-reduce of the %d MB flat gradient)" % ("nccl-allreduce-flat", world, ms, numel * 4 >> 20), flush=True)
 
@@ -92,13 +104,19 @@ def main():
             def exchange():
                 for n, g in grads:
                     grc.step(g, n)
+            t_b = time.time()
             ms = timed(exchange)
-            rows.append(dict(codec=comp, memory=mem, communicator=comm, world=world, ms=ms, elements=numel))
+            rows.append(dict(codec=comp, memory=mem, communicator=comm, world=world, ms=ms, elements=numel,
+                             clocks=sampler.window(t_b, time.time()) if sampler else None))
+            del grads, grc
+            torch.cuda.empty_cache()
             if rank == 0:
                 print("%-10s %-9s %-9s W=%d %9.3f ms" % (comp, mem, comm, world, ms), flush=True)
         except Exception as exc:           # several reference paths are broken
             if rank == 0:
                 print("%-10s %-9s %-9s W=%d  fails in the reference: %s" % (comp, mem, comm, world, str(exc)[:90]), flush=True)
+    if sampler:
+        sampler.close()
     if rank == 0 and args.out:
         with open(args.out, "w") as f:
             json.dump(rows, f, indent=1)

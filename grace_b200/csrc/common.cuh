@@ -84,6 +84,31 @@ __device__ __forceinline__ void st_stream_u4(void* p, uint4 v) {
                : "memory");
 }
 
+// Wire stores.  `mc` != 0: the pointer is an NVLS multicast address of a symmetric allocation -- ONE multimem.st reaches the
+// slot in every rank's arena (the NVSwitch replicates it: one egress copy instead of W - 1 P2P stores); else a plain
+// (peer-mapped) global store.  multimem.st moves bits, the .f32 type is only a width.
+__device__ __forceinline__ void wire_st_u4(void* p, uint4 v, int mc) {
+  if (mc) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(__uint_as_float(v.x)),
+                 "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+                 : "memory");
+  } else {
+    st_stream_u4(p, v);
+  }
+}
+__device__ __forceinline__ void wire_st_u2(void* p, uint2 v, int mc) {
+  if (mc) {
+    asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1,%2};" ::"l"(p), "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y))
+                 : "memory");
+  } else {
+    *reinterpret_cast<uint2*>(p) = v;
+  }
+}
+__device__ __forceinline__ void wire_st_u32(void* p, uint32_t v, int mc) {
+  if (mc) asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(__uint_as_float(v)) : "memory");
+  else *reinterpret_cast<uint32_t*>(p) = v;
+}
+
 // Wait until *flag has reached `epoch` (wrap-safe).  Bounded: a missing peer sets the
 // TIMEOUT status bit instead of hanging the GPU (SURVEY §5 failure-detection row).
 __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t epoch, uint32_t* status, uint64_t timeout_ns) {

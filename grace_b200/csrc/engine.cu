@@ -118,7 +118,7 @@ extern "C" int gb_comm_destroy(gb_comm* c) {
   for (gb_region& g : c->extra) {
     for (int r = 0; r < c->world; ++r)
       if (g.opened[r]) cudaIpcCloseMemHandle(g.peer[r]);
-    cudaFree(g.base);
+    if (!g.adopted) cudaFree(g.base);
   }
   if (c->siblings && c->rank == 0) delete[] c->siblings;
   cudaFree(c->base);
@@ -231,6 +231,25 @@ extern "C" int gb_comm_region_add(gb_comm* c, size_t bytes, int* index) {
   if (index) *index = (int)c->extra.size();
   return 0;
 }
+
+// Adopt a symmetric allocation made by the caller (torch.distributed._symmetric_memory): `peers` are this process'
+// mappings of every rank's copy (rank order, peers[rank] = the local one), `mc` its NVLS multicast address (0: none).
+// The memory stays owned by the caller and must outlive the communicator.  Collective like gb_comm_region_add.
+extern "C" int gb_comm_region_adopt(gb_comm* c, const uint64_t* peers, uint64_t mc, size_t bytes, int* index) {
+  gb_region g;
+  memset(&g, 0, sizeof(g));
+  g.bytes = bytes & ~size_t(255);
+  for (int r = 0; r < c->world; ++r) g.peer[r] = (char*)(uintptr_t)peers[r];
+  g.base = g.peer[c->rank];
+  g.mc = (char*)(uintptr_t)mc;
+  g.adopted = true;
+  GB_CHECK(g.base != nullptr && g.bytes > 0, "gb_comm_region_adopt: empty region");
+  c->extra.push_back(g);
+  c->need_bytes = 0;
+  if (index) *index = (int)c->extra.size();
+  return 0;
+}
+extern "C" int gb_comm_has_multicast(gb_comm* c) { return !c->extra.empty() && c->extra.back().mc != nullptr; }
 
 extern "C" int gb_comm_region_ipc_handle(gb_comm* c, int index, void* out64) {
   GB_CHECK(index >= 1 && index <= (int)c->extra.size(), "no region %d", index);

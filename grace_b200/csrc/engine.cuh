@@ -20,6 +20,8 @@ struct gb_region {
   size_t bytes, cursor;
   char* peer[GB_MAX_WORLD];
   bool opened[GB_MAX_WORLD];
+  char* mc;                  // NVLS multicast address of the same allocation on all ranks (adopted symmetric memory), or null
+  bool adopted;              // memory owned by the caller (torch symmetric memory): not freed here
 };
 #define GB_REGION_SHIFT 48   // a channel offset carries its region index in the bits above this
 
@@ -57,6 +59,14 @@ static inline char* gb_slot_of(const gb_comm* c, int arena_rank, size_t chan_off
   const size_t reg = chan_off >> GB_REGION_SHIFT, off = chan_off & ((size_t(1) << GB_REGION_SHIFT) - 1);
   char* base = reg == 0 ? c->peer[arena_rank] : c->extra[reg - 1].peer[arena_rank];
   return base + off + ((size_t)parity * c->world + src) * slot_bytes;
+}
+
+// The same slot through the region's multicast window (one multimem.st reaches this slot in EVERY rank's arena), or
+// null when the channel's region has no multicast mapping.
+static inline char* gb_slot_mc(const gb_comm* c, size_t chan_off, size_t slot_bytes, int parity, int src) {
+  const size_t reg = chan_off >> GB_REGION_SHIFT, off = chan_off & ((size_t(1) << GB_REGION_SHIFT) - 1);
+  if (reg == 0 || !c->extra[reg - 1].mc) return nullptr;
+  return c->extra[reg - 1].mc + off + ((size_t)parity * c->world + src) * slot_bytes;
 }
 
 // Slot r of parity q of a channel inside one arena.

@@ -325,7 +325,15 @@ struct TkOut {
   int32_t* idx[GB_MAX_WORLD];
   int2* hdr[GB_MAX_WORLD];      // [ntiles + 1] certain picks, then [ntiles + 1] threshold-bin picks
   int n;
+  int mc;                       // entry 0 is the NVLS multicast view of my slot (n == 1): one multimem.st serves all ranks
 };
+__device__ __forceinline__ void tk_put(const TkOut& out, int r, size_t psh, int pos, float v, int32_t ix) {
+  wire_st_u32((char*)out.vals[r] + psh + (size_t)pos * 4, __float_as_uint(v), out.mc);
+  wire_st_u32((char*)out.idx[r] + psh + (size_t)pos * 4, (uint32_t)ix, out.mc);
+}
+__device__ __forceinline__ void tk_put_hdr(const TkOut& out, int r, size_t psh, int slot, int begin, int count) {
+  wire_st_u2((char*)out.hdr[r] + psh + (size_t)slot * 8, make_uint2((uint32_t)begin, (uint32_t)count), out.mc);
+}
 // peers are addressed with compile-time indices (the kernel parameter stays in the constant bank, no local copy)
 #define TK_PEERS(r) _Pragma("unroll") for (int r = 0; r < GB_MAX_WORLD; ++r) if (r < out.n)
 #define TK_VALS(o, r, sh) ((float*)((char*)(o).vals[r] + (sh)))
@@ -425,7 +433,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
       for (int i = threadIdx.x; i < tc; i += GB_THREADS) {
         const float v = sv[i];
         const int32_t ix = si[i];
-        TK_PEERS(r) { TK_VALS(out, r, psh)[begin + i] = v; TK_IDX(out, r, psh)[begin + i] = ix; }
+        TK_PEERS(r) tk_put(out, r, psh, begin + i, v, ix);
         if (ZERO) work[tb + (ix - l0)] = 0.f;
       }
     } else {
@@ -436,7 +444,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
         const float v = __ldcg(work + tb + e);
         if ((tk_absbits(v) >> 20) > tbin) {
           const int pos = begin + atomicAdd(&s_ovcnt[b], 1);
-          TK_PEERS(r) { TK_VALS(out, r, psh)[pos] = v; TK_IDX(out, r, psh)[pos] = l0 + e; }
+          TK_PEERS(r) tk_put(out, r, psh, pos, v, l0 + e);
           if (ZERO) work[tb + e] = 0.f;
         }
       }
@@ -513,7 +521,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
       // debug build: a tile's certain picks must stay inside its tensor's k payload entries
       if (!GB_ASSERT_STORE(pend_raw + (uint32_t)pend_tc <= (uint32_t)pend_k, d.status)) s_tc[pend_b] = 0;
       s_begin[pend_b] = pb;
-      TK_PEERS(r) TK_HDR(out, r, psh)[tile - 1] = make_int2(pb, pend_tc);
+      TK_PEERS(r) tk_put_hdr(out, r, psh, tile - 1, pb, pend_tc);
     }
     __syncthreads();      // tile staged, stage st consumed, and every thread has stored the tile before the previous one
     const int bprev = b == 0 ? 2 : b - 1;          // (it - 1) % 3 == (it + 2) % 3
@@ -536,7 +544,7 @@ __global__ void __launch_bounds__(GB_THREADS, 4) tk_pass2(SegTable t, float* wor
     const int pb = s_kb[pend_b] + (int)pend_raw;
     if (!GB_ASSERT_STORE(pend_raw + (uint32_t)pend_tc <= (uint32_t)pend_k, d.status)) s_tc[pend_b] = 0;
     s_begin[pend_b] = pb;
-    TK_PEERS(r) TK_HDR(out, r, psh)[t1 - 1] = make_int2(pb, pend_tc);
+    TK_PEERS(r) tk_put_hdr(out, r, psh, t1 - 1, pb, pend_tc);
   }
   __syncthreads();
   copy_out(b == 0 ? 2 : b - 1);
@@ -785,7 +793,7 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work
           begin = (int)t.seg_kbase[seg] + (int)at;
           if (!GB_ASSERT_STORE(at + (uint32_t)nsel <= (uint32_t)t.seg_k[seg], d.status)) nsel = 0;     // debug build
         }
-        TK_PEERS(r) TK_HDR(out, r, psh)[xoff + tile] = make_int2(begin, nsel);
+        TK_PEERS(r) tk_put_hdr(out, r, psh, xoff + tile, begin, nsel);
       }
       begin = __shfl_sync(0xffffffffu, begin, 0);
 #ifdef GB_DEBUG
@@ -794,7 +802,7 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work
       for (int i = lane; i < nsel; i += 32) {
         const int e = pos[i];
         const float v = val[i];
-        TK_PEERS(r) { TK_VALS(out, r, psh)[begin + i] = v; TK_IDX(out, r, psh)[begin + i] = local0 + e; }
+        TK_PEERS(r) tk_put(out, r, psh, begin + i, v, local0 + e);
         if (ZERO) work[base + e] = 0.f;
       }
     } else {
@@ -849,7 +857,7 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work
       int begin = 0;
       if (lane == 0) {
         if (total) begin = (int)t.seg_kbase[seg] + (int)atomicAdd(s + S_CURA, (uint32_t)total);
-        TK_PEERS(r) TK_HDR(out, r, psh)[xoff + tile] = make_int2(begin, total);
+        TK_PEERS(r) tk_put_hdr(out, r, psh, xoff + tile, begin, total);
       }
       begin = __shfl_sync(0xffffffffu, begin, 0);
       int p = begin + inc - mine;
@@ -861,7 +869,7 @@ __global__ void __launch_bounds__(TK_WPT * 32) tk_finish(SegTable t, float* work
           w &= w - 1;
           const int e = lane * 128 + 4 * l + q;
           const float v = __ldcg(work + base + e);
-          TK_PEERS(r) { TK_VALS(out, r, psh)[p] = v; TK_IDX(out, r, psh)[p] = local0 + e; }
+          TK_PEERS(r) tk_put(out, r, psh, p, v, local0 + e);
           if (ZERO) work[base + e] = 0.f;
           ++p;
         }
@@ -929,6 +937,13 @@ int tk_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
     out.idx[r] = (int32_t*)(s + p->hdr_bytes + per);
   }
   out.n = c->world;
+  out.mc = 0;
+  if (char* mc = gb_slot_mc(c, p->chan_off, p->slot_bytes, 0, c->rank)) {   // NVLS: the switch replicates every store
+    out.n = 1; out.mc = 1;
+    out.hdr[0] = (int2*)mc;
+    out.vals[0] = (float*)(mc + p->hdr_bytes);
+    out.idx[0] = (int32_t*)(mc + p->hdr_bytes + per);
+  }
   const int grid = std::min(p->ntiles, 148 * 2);            // pass 1: two resident CTAs per SM, each with a 3-stage tile pipeline
   const int grid2 = std::min(p->ntiles, 148 * 4);
   const int wgrid = (p->ntiles + TK_WPT - 1) / TK_WPT;

@@ -50,7 +50,7 @@ struct QuantArgs {
   uint32_t seed, step;
 };
 
-struct WireOut { char* slot[GB_MAX_WORLD]; int n; };   // my slot inside every peer
+struct WireOut { char* slot[GB_MAX_WORLD]; int n; int mc; };   // my slot inside every peer; mc: slot[0] is the NVLS multicast view, n == 1
 struct WireIn { const char* slot[GB_MAX_WORLD]; int n; };  // every rank's slot inside my arena
 
 // first-call rules (empty memory: compensate() is the identity; Signum: m = x) and the Philox step
@@ -215,7 +215,9 @@ __global__ void k2_finalize(SegTable t, const float* __restrict__ tilestats, int
     }
     const float4 v = make_float4(o[0], o[1], o[2], o[3]);
     reinterpret_cast<float4*>(segstats)[seg] = v;
-    for (int r = 0; r < out.n; ++r) reinterpret_cast<float4*>(out.slot[r] + poff)[seg] = v;
+    for (int r = 0; r < out.n; ++r)
+      wire_st_u4(reinterpret_cast<float4*>(out.slot[r] + poff) + seg,
+                 make_uint4(__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w)), out.mc);
   }
 }
 
@@ -405,8 +407,8 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
         if (e0 < len) {
           for (int r = 0; r < out.n; ++r) {
             uint32_t* dst = reinterpret_cast<uint32_t*>(out.slot[r] + poff + hdr_bytes) + flat * BITS / 32;
-            if (WORDS == 4) st_stream_u4(dst, make_uint4(w[0], w[1 % WORDS], w[2 % WORDS], w[3 % WORDS]));
-            else *reinterpret_cast<uint2*>(dst) = make_uint2(w[0], w[1 % WORDS]);
+            if (WORDS == 4) wire_st_u4(dst, make_uint4(w[0], w[1 % WORDS], w[2 % WORDS], w[3 % WORDS]), out.mc);
+            else wire_st_u2(dst, make_uint2(w[0], w[1 % WORDS]), out.mc);
           }
         }
       } else {
@@ -428,8 +430,8 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
       for (int r = 0; r < out.n; ++r) {
         uint32_t* dst = reinterpret_cast<uint32_t*>(out.slot[r] + poff + hdr_bytes) + w0;
         for (int i = threadIdx.x; i < n4; i += GB_THREADS)
-          st_stream_u4(dst + 4 * i, *reinterpret_cast<const uint4*>(s_words + 4 * i));
-        if (threadIdx.x < (nwords & 3)) dst[4 * n4 + threadIdx.x] = s_words[4 * n4 + threadIdx.x];
+          wire_st_u4(dst + 4 * i, *reinterpret_cast<const uint4*>(s_words + 4 * i), out.mc);
+        if (threadIdx.x < (nwords & 3)) wire_st_u32(dst + 4 * n4 + threadIdx.x, s_words[4 * n4 + threadIdx.x], out.mc);
       }
       __syncthreads();
     }
@@ -652,7 +654,11 @@ int k2_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   ++p->epoch;                           // host mirror of the device-side epoch
   WireOut out;
   out.n = c->world;
+  out.mc = 0;
   for (int r = 0; r < c->world; ++r) out.slot[r] = gb_slot_of(c, r, p->chan_off, p->slot_bytes, 0, c->rank);
+  if (char* mc = gb_slot_mc(c, p->chan_off, p->slot_bytes, 0, c->rank)) {   // one multimem.st instead of W peer stores
+    out.n = 1; out.mc = 1; out.slot[0] = mc;
+  }
   const PeerPtrs peers = gb_comm_peers(c);
   if (needs_stats(a.codec)) {
     const int g = grid_for(p->ntiles);

@@ -151,7 +151,7 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int a_mn_major) {
 // MODE 1:  D[128 x 16] = M[m0:m0+128, k0:k1] * Q0[k0:k1, :]         (A K-major,  K = columns of M)
 // MODE 2:  D[128 x 16] = M[k0:k1, m0:m0+128]^T * P^[k0:k1, :]       (A MN-major, K = rows of M)
 // warp 0: TMA producer; warp 1: TMEM alloc + MMA issuer; warps 2-5: epilogue (TMEM lane quarter = warp % 4)
-struct PsPeers { float* slot[GB_MAX_WORLD]; int n; };
+struct PsPeers { float* slot[GB_MAX_WORLD]; int n; int mc; };   // mc: slot[0] is the NVLS multicast view, n == 1
 __device__ __forceinline__ void shift(PsPeers& o, size_t bytes) {
   for (int r = 0; r < o.n; ++r) o.slot[r] = (float*)((char*)o.slot[r] + bytes);
 }
@@ -261,7 +261,9 @@ __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ ite
         for (int c4 = 0; c4 < RP / 4; ++c4) {
           const float4 o = make_float4(__uint_as_float(v[c4 * 4]), __uint_as_float(v[c4 * 4 + 1]), __uint_as_float(v[c4 * 4 + 2]),
                                        __uint_as_float(v[c4 * 4 + 3]));
-          for (int r = 0; r < peers.n; ++r) reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP)[c4] = o;
+          for (int r = 0; r < peers.n; ++r)
+            wire_st_u4(reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP) + c4,
+                       make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), __float_as_uint(o.w)), peers.mc);
         }
       }
     } else {
@@ -287,7 +289,9 @@ __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ ite
             const float4 x = __ldcg(reinterpret_cast<const float4*>(part + ((item0 + ch) * PS_BM + rl) * RP) + c4);
             o.x += x.x; o.y += x.y; o.z += x.z; o.w += x.w;
           }
-          for (int r = 0; r < peers.n; ++r) reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP)[c4] = o;
+          for (int r = 0; r < peers.n; ++r)
+            wire_st_u4(reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP) + c4,
+                       make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), __float_as_uint(o.w)), peers.mc);
         }
       }
     }
@@ -375,7 +379,9 @@ __global__ void __launch_bounds__(GB_THREADS) k3_flag(const PsMat* __restrict__ 
     const int q4 = rp / 4;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows * q4; i += gridDim.x * blockDim.x) {
       const float4 o = reinterpret_cast<const float4*>(acc + (size_t)row0 * rp)[i];
-      for (int r = 0; r < peers_slots.n; ++r) reinterpret_cast<float4*>(peers_slots.slot[r] + (size_t)row0 * rp)[i] = o;
+      for (int r = 0; r < peers_slots.n; ++r)
+        wire_st_u4(reinterpret_cast<float4*>(peers_slots.slot[r] + (size_t)row0 * rp) + i,
+                   make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), __float_as_uint(o.w)), peers_slots.mc);
     }
   }
   release_flags_last_block(done, peers, channel, epoch);
@@ -977,8 +983,9 @@ extern "C" int gb_psgd_debug_dump(float* h_dst) {
 extern "C" int64_t gb_psgd_wire_bytes(gb_psgd* p) { return (int64_t)(p->prows + p->qrows) * p->rp * 4; }
 
 static PsPeers peer_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch = 0) {   // parity 0
-  PsPeers s; gb_comm* c = p->comm; s.n = c->world;
+  PsPeers s; gb_comm* c = p->comm; s.n = c->world; s.mc = 0;
   for (int r = 0; r < c->world; ++r) s.slot[r] = (float*)gb_slot_of(c, r, chan_off, slot_bytes, epoch & 1, c->rank);
+  if (char* mc = gb_slot_mc(c, chan_off, slot_bytes, epoch & 1, c->rank)) { s.n = 1; s.mc = 1; s.slot[0] = (float*)mc; }
   return s;
 }
 static PsIn my_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch = 0) {        // parity 0

@@ -24,13 +24,13 @@ struct gb_ops {
   int64_t launches;
 };
 
-struct OpsPeers { char* slot[GB_MAX_WORLD]; int n; };
+struct OpsPeers { char* slot[GB_MAX_WORLD]; int n; int mc; };
 
 __global__ void __launch_bounds__(GB_THREADS) gb_ops_post(const uint4* __restrict__ src, size_t n16, OpsPeers dst, uint32_t* done,
                                                          PeerPtrs peers, int channel, uint32_t epoch) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) {
     const uint4 v = src[i];
-    for (int r = 0; r < dst.n; ++r) st_stream_u4(reinterpret_cast<uint4*>(dst.slot[r]) + i, v);
+    for (int r = 0; r < dst.n; ++r) wire_st_u4(reinterpret_cast<uint4*>(dst.slot[r]) + i, v, dst.mc);
   }
   release_flags_last_block(done, peers, channel, epoch);
 }
@@ -127,6 +127,8 @@ static void ops_slots(gb_ops* o, uint32_t epoch, OpsPeers* dst, OpsPeers* src) {
     src->slot[r] = gb_slot_of(c, c->rank, o->chan_off, o->slot_bytes, epoch & 1, r);
   }
   dst->n = src->n = c->world;
+  dst->mc = src->mc = 0;
+  if (char* mc = gb_slot_mc(c, o->chan_off, o->slot_bytes, epoch & 1, c->rank)) { dst->n = 1; dst->mc = 1; dst->slot[0] = mc; }
 }
 
 extern "C" int gb_ops_send(gb_ops* o, const void* d_src, size_t nbytes, void* stream) {

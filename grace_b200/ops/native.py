@@ -71,6 +71,8 @@ def _declare(L):
         "gb_comm_arena_need": (sz, [vp]),
         "gb_comm_regions": (i32, [vp]),
         "gb_comm_region_add": (i32, [vp, sz, P(i32)]),
+        "gb_comm_region_adopt": (i32, [vp, P(C.c_uint64), C.c_uint64, sz, P(i32)]),
+        "gb_comm_has_multicast": (i32, [vp]),
         "gb_comm_region_ipc_handle": (i32, [vp, i32, vp]),
         "gb_comm_region_open_peers": (i32, [vp, i32, vp]),
         "gb_handle_record": (i32, [vp, P(i64)]),

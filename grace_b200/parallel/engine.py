@@ -33,6 +33,9 @@ class Engine:
         self._h = C.c_void_p(handle)
         self.rank, self.world, self.group = rank, world, group
         self._local = False
+        self._symmetric = []
+        self.multicast = False
+        self.nvls_error = None
         self.plans: List["Plan"] = []
 
     # ------------------------------------------------------------------ construction
@@ -59,6 +62,8 @@ class Engine:
             dist.all_gather_object(gathered, bytes(buf.raw), group=group)
             check(L.gb_comm_open_peers(eng._h, b"".join(gathered)))
             dist.barrier(group=group)
+            if os.environ.get("GRACE_B200_NVLS_PAYLOAD", "1") != "0" and group is None:
+                eng._adopt_symmetric(arena_bytes or cls.default_arena_bytes())
         return eng
 
     @classmethod
@@ -104,12 +109,47 @@ class Engine:
     def arena_free(self):
         return native.lib().gb_comm_arena_free(self._h)
 
+    def _adopt_symmetric(self, nbytes):
+        """Make the next arena region a symmetric allocation bound to an NVLS multicast address (when the host has
+        NVLink SHARP): wire slots carved from it are written with ONE multimem.st per 16 bytes for all ranks -- the
+        switch replicates the store -- instead of W - 1 peer stores.  Collective; all ranks agree or nobody adopts
+        (agreed fallback: the CUDA IPC arena with P2P store loops)."""
+        import torch.distributed._symmetric_memory as symm
+        L = native.lib()
+        buf = handle = None
+        ok = 1
+        try:
+            buf = symm.empty(int(nbytes), dtype=torch.uint8, device=torch.device("cuda", torch.cuda.current_device()))
+            handle = symm.rendezvous(buf, dist.group.WORLD)
+            mc = int(handle.multicast_ptr or 0)
+            ptrs = [int(x) for x in handle.buffer_ptrs]
+            if not mc or len(ptrs) != self.world:
+                ok = 0
+        except Exception as exc:                              # no multicast on this host / torch without symmetric memory
+            self.nvls_error = repr(exc)
+            ok = 0
+        t = torch.tensor([ok], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        if int(t) == 0:
+            return False
+        buf.zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        arr = (C.c_uint64 * self.world)(*ptrs)
+        idx = C.c_int()
+        check(L.gb_comm_region_adopt(self._h, arr, C.c_uint64(mc), int(nbytes), C.byref(idx)))
+        self._symmetric.append((buf, handle))                 # the memory must outlive the communicator
+        self.multicast = True
+        return True
+
     def grow(self, nbytes):
         """Collective: every rank adds an arena region of at least ``nbytes`` (same size everywhere), exports it
         with CUDA IPC and maps the peers' regions.  Called automatically when a plan's wire slot does not fit,
         so the arena is not limited to what the first model needed."""
         L = native.lib()
         nbytes = max(int(nbytes) + (1 << 20), int(os.environ.get("GRACE_B200_ARENA_GROW_MB", "256")) << 20)
+        if self.multicast and self._adopt_symmetric(nbytes):
+            return native.lib().gb_comm_regions(self._h) - 1
         idx = C.c_int()
         check(L.gb_comm_region_add(self._h, nbytes, C.byref(idx)))
         if self.world > 1 and not self._local:

@@ -372,7 +372,9 @@ class FusedDP:
         self.side = torch.cuda.Stream()                   # sends (compensate + compress + peer stores)
         self.side_recv = torch.cuda.Stream()              # receives: queued behind their send, overlap the rest of backward
         self.overlap_recv = os.environ.get("GRACE_B200_OVERLAP_RECV", "1") != "0"
-        self.transport = "p2p-store"                      # or "nvls-multimem" for dense buckets on NVLS hosts
+        # "p2p-store": W - 1 peer stores per payload; "nvls-multimem-store": one multicast store through the switch;
+        # "nvls-multimem": dense buckets reduced in the switch (multimem.ld_reduce)
+        self.transport = "nvls-multimem-store" if getattr(self.engine, "multicast", False) else "p2p-store"
         self.nvls_error = None
         bucket_bytes = bucket_bytes or DEFAULT_BUCKET_BYTES
         trainable = [(n, p) for n, p in named if p.requires_grad]

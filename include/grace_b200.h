@@ -98,6 +98,10 @@ size_t gb_comm_arena_free(gb_comm* c);
 size_t gb_comm_arena_need(gb_comm* c);
 int gb_comm_regions(gb_comm* c);
 int gb_comm_region_add(gb_comm* c, size_t bytes, int* index);
+/* adopt caller-owned symmetric memory (all ranks' mappings + its NVLS multicast address) as the next region: wire slots
+ * carved from it are written with ONE multimem.st per 16 bytes for all ranks instead of W - 1 peer stores */
+int gb_comm_region_adopt(gb_comm* c, const uint64_t* peers, uint64_t multicast, size_t bytes, int* index);
+int gb_comm_has_multicast(gb_comm* c);
 int gb_comm_region_ipc_handle(gb_comm* c, int index, void* out64);
 int gb_comm_region_open_peers(gb_comm* c, int index, const void* handles);
 /* all ranks reach this point (flag barrier over peer memory; used by tests and K0) */
