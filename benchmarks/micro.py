@@ -83,6 +83,8 @@ def main():
                 flush_r.sum()              # evicts the dirty lines of the write before the timed region starts
     flush = _Flush()
     rows = []
+    if rank == 0:
+        print("engine: world %d, payload transport %s" % (world, "nvls-multimem-store" if eng.multicast else "p2p-store"), flush=True)
     sampler = ClockSampler(torch.cuda.current_device()) if rank == 0 else None
     want = [c for c in args.codecs.split(",") if c]
     for comp, mem in CODECS:
