@@ -106,6 +106,9 @@ def triple(args, comp):
     mem = args.memory or {"topk": "residual", "qsgd": "none", "powersgd": "powersgd", "efsignsgd": "efsignsgd",
                           "dgc": "dgc", "none": "none"}.get(comp, "residual")
     comm = args.communicator or ("allreduce" if comp in ("powersgd", "none", "fp16") else "allgather")
+    if args.impl == "reference" and mem == "efsignsgd":
+        mem = "residual"      # the reference's dist helper has no 'efsignsgd' memory branch (helper.py:57-74); its own
+                              # older EFSignSGD wires ResidualMemory(beta=1, gamma=lr) (compression.py:255-257)
     return comp, mem, comm
 
 
