@@ -4,20 +4,23 @@
 // Reference op chain per tensor: tfp.stats.quantiles (a full sort), find_bins, unsorted_segment_mean,
 // cast; receive: gather means[bins] per rank + adds.  Here, per bucket:
 //   sk_prep    x = compensate(grad, residual) -> keys                      (one pass)
-//   cub::DeviceRadixSort::SortKeys on 64-bit keys (tensor id << 32 | order-preserving float bits): ONE sort
-//              for all tensors of the bucket; only 32 + log2(#tensors) key bits are sorted
+//   rs_hist / rs_scan / rs_scatter: a hand-written stable LSD radix sort (8-bit digits) of 64-bit keys
+//              (tensor id << 32 | order-preserving float bits): ONE sort for all tensors of the bucket; only the
+//              32 + log2(#tensors) key bits that differ are sorted (5 passes for ResNet-50's 161 tensors).  No
+//              library kernel is on this path (round 1 called cub::DeviceRadixSort here).
 //   sk_edges   q+1 cut points per tensor, linear interpolation between order statistics
 //   sk_means   one CTA per (bucket, tensor): the elements of a bucket are a contiguous range of the sorted
 //              tensor, so the mean is a fixed-order range sum (deterministic, no float atomics);
 //              means go straight into every peer's slot header
-//   sk_encode  bin = largest b with edges[b] <= x (7-step search in shared memory), 4 codes per 32-bit
-//              word, stores into every peer, residual = x - means[bin]; last CTA releases the flags
+//   sk_encode  bin = largest b with edges[b] <= x (binary search in shared memory), 8-bit codes (q < 256) or
+//              16-bit codes (q <= 1023; reference: uint16 bins, tensorflow/compressor/sketch.py:26) packed into
+//              32-bit words, stores into every peer, residual = x - means[bin]; last CTA releases the flags
 //   sk_decode  wait flags; sum_r means_r[code_r] in rank order, x 1/W
 #include "kernels.cuh"
 
-#include <cub/device/device_radix_sort.cuh>
+#include <utility>
 
-#define SK_MAXQ 255
+#define SK_MAXQ 1023
 
 struct SkSlots { char* slot[GB_MAX_WORLD]; int n; };
 struct SkIn { const char* slot[GB_MAX_WORLD]; int n; };
@@ -32,6 +35,91 @@ __device__ __forceinline__ float unflip_f(uint32_t k) {
   return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
 }
 __device__ __forceinline__ float sorted_at(const uint64_t* s, int64_t i) { return unflip_f((uint32_t)s[i]); }
+
+// ---------------------------------------------------------------- stable LSD radix sort, 8 bits per pass
+// A block owns RS_KEYS consecutive keys.  rs_hist counts its digits; rs_scan turns counts[digit][block] into exclusive
+// prefixes over the blocks (one CTA per digit) and digit totals; rs_scatter ranks every key among the equal digits
+// that precede it (warp match + per-warp counts, rounds of 256 keys in index order => stable) and stores it at
+// base[digit] + prefix[digit][block] + rank.
+#define RS_KEYS 4096
+__global__ void __launch_bounds__(GB_THREADS) rs_hist(const uint64_t* __restrict__ keys, int64_t n, int shift, uint32_t* counts, int nblocks) {
+  __shared__ uint32_t sh[256];
+  sh[threadIdx.x] = 0;
+  __syncthreads();
+  const int64_t k0 = (int64_t)blockIdx.x * RS_KEYS;
+  for (int i = threadIdx.x; i < RS_KEYS; i += GB_THREADS)
+    if (k0 + i < n) atomicAdd(&sh[(uint32_t)(keys[k0 + i] >> shift) & 255u], 1u);
+  __syncthreads();
+  counts[(size_t)threadIdx.x * nblocks + blockIdx.x] = sh[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(GB_THREADS) rs_scan(uint32_t* counts, int nblocks, uint32_t* totals) {
+  __shared__ uint32_t sh[GB_THREADS];
+  uint32_t* row = counts + (size_t)blockIdx.x * nblocks;
+  uint32_t carry = 0;
+  for (int c0 = 0; c0 < nblocks; c0 += GB_THREADS) {
+    const int i = c0 + threadIdx.x;
+    const uint32_t v = i < nblocks ? row[i] : 0u;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < GB_THREADS; o <<= 1) {
+      const uint32_t a = threadIdx.x >= o ? sh[threadIdx.x - o] : 0u;
+      __syncthreads();
+      sh[threadIdx.x] += a;
+      __syncthreads();
+    }
+    if (i < nblocks) row[i] = carry + sh[threadIdx.x] - v;
+    carry += sh[GB_THREADS - 1];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) totals[blockIdx.x] = carry;
+}
+
+__global__ void __launch_bounds__(GB_THREADS) rs_scatter(const uint64_t* __restrict__ keys, uint64_t* __restrict__ out, int64_t n, int shift,
+                                                        const uint32_t* __restrict__ prefix, int nblocks, const uint32_t* __restrict__ totals) {
+  __shared__ uint32_t s_base[256];               // where this block's first key with digit d goes
+  __shared__ uint32_t s_run[256];                // keys with digit d already placed by this block
+  __shared__ uint32_t s_cnt[GB_THREADS / 32][256];
+  {
+    // exclusive scan of the 256 digit totals (every block redoes it: 256 values)
+    uint32_t v = totals[threadIdx.x];
+    s_run[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < 256; o <<= 1) {
+      const uint32_t a = threadIdx.x >= o ? s_run[threadIdx.x - o] : 0u;
+      __syncthreads();
+      s_run[threadIdx.x] += a;
+      __syncthreads();
+    }
+    s_base[threadIdx.x] = s_run[threadIdx.x] - v + prefix[(size_t)threadIdx.x * nblocks + blockIdx.x];
+    __syncthreads();
+    s_run[threadIdx.x] = 0;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t k0 = (int64_t)blockIdx.x * RS_KEYS;
+  for (int r = 0; r < RS_KEYS / GB_THREADS; ++r) {
+    for (int w = 0; w < GB_THREADS / 32; ++w) s_cnt[w][threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t i = k0 + r * GB_THREADS + threadIdx.x;
+    const bool live = i < n;
+    const uint64_t key = live ? keys[i] : 0ull;
+    const uint32_t dg = live ? ((uint32_t)(key >> shift) & 255u) : 256u + (uint32_t)lane;     // dead lanes match nobody
+    const uint32_t same = __match_any_sync(0xffffffffu, dg);
+    const int rank = __popc(same & ((1u << lane) - 1u));
+    if (live && rank == 0) s_cnt[warp][dg] = (uint32_t)__popc(same);
+    __syncthreads();
+    if (live) {
+      uint32_t before = 0;
+      for (int w = 0; w < warp; ++w) before += s_cnt[w][dg];
+      out[(size_t)s_base[dg] + s_run[dg] + before + (uint32_t)rank] = key;
+    }
+    __syncthreads();
+    uint32_t tot = 0;
+    for (int w = 0; w < GB_THREADS / 32; ++w) tot += s_cnt[w][threadIdx.x];
+    s_run[threadIdx.x] += tot;
+    __syncthreads();
+  }
+}
 
 // x = compensate(grad, residual) -> vals (kept for the encode pass) and 64-bit sort keys; pad elements of a
 // tensor sort behind its real elements
@@ -130,6 +218,7 @@ __device__ __forceinline__ int sk_bin(const float* e, int q, float x) {
   return min(max(lo - 1, 0), q - 1);
 }
 
+template <int CB>   // code bits: 8 (q < 256) or 16
 __global__ void __launch_bounds__(GB_THREADS) sk_encode(SegTable t, const float* __restrict__ keys, float* res, int has_mem,
                                                        const float* __restrict__ edges, const float* __restrict__ means, int q,
                                                        SkSlots out, size_t hdr_bytes, uint32_t* done, PeerPtrs peers, int channel,
@@ -157,27 +246,35 @@ __global__ void __launch_bounds__(GB_THREADS) sk_encode(SegTable t, const float*
       if (e0 >= len) continue;
       const float4 v = *reinterpret_cast<const float4*>(keys + base + e0);
       const float x[4] = {v.x, v.y, v.z, v.w};
-      uint32_t word = 0;
+      uint32_t word[2] = {0u, 0u};
       float nres[4];
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const bool live = e0 + k < len;
         const int b = live ? sk_bin(se, q, x[k]) : 0;
-        word |= (uint32_t)b << (8 * k);
+        if (CB == 8) word[0] |= (uint32_t)b << (8 * k);
+        else word[k >> 1] |= (uint32_t)b << (16 * (k & 1));
         nres[k] = live ? __fsub_rn(x[k], sm[b]) : 0.f;
       }
       if (has_mem) *reinterpret_cast<float4*>(res + base + e0) = make_float4(nres[0], nres[1], nres[2], nres[3]);
-      const int64_t w = (base + e0) >> 2;
-      for (int r = 0; r < out.n; ++r) reinterpret_cast<uint32_t*>(out.slot[r] + hdr_bytes)[w] = word;
+      if (CB == 8) {
+        const int64_t w = (base + e0) >> 2;
+        for (int r = 0; r < out.n; ++r) reinterpret_cast<uint32_t*>(out.slot[r] + hdr_bytes)[w] = word[0];
+      } else {
+        const int64_t w = (base + e0) >> 1;
+        for (int r = 0; r < out.n; ++r) *reinterpret_cast<uint2*>(reinterpret_cast<uint32_t*>(out.slot[r] + hdr_bytes) + w) = make_uint2(word[0], word[1]);
+      }
     }
   }
   release_flags_last_block(done, peers, channel, epoch);
 }
 
+template <int CB>
 __global__ void __launch_bounds__(GB_THREADS) sk_decode(SegTable t, SkIn in, size_t hdr_bytes, int q, float* outp, float divisor,
                                                        PeerPtrs peers, int channel, const StepCtl* ctl, size_t par_stride,
                                                        uint32_t* status, uint64_t timeout_ns) {
-  __shared__ float sm[GB_MAX_WORLD][SK_MAXQ + 1];
+  constexpr int QCAP = CB == 8 ? 256 : SK_MAXQ + 1;
+  __shared__ float sm[GB_MAX_WORLD][QCAP];
   const uint32_t epoch = ctl->epoch;
   if (epoch & 1) shift(in, par_stride);
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
@@ -198,12 +295,17 @@ __global__ void __launch_bounds__(GB_THREADS) sk_decode(SegTable t, SkIn in, siz
     for (int j = 0; j < GB_TILE / (GB_THREADS * 4); ++j) {
       const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
       if (e0 >= len) continue;
-      const int64_t w = (base + e0) >> 2;
       float acc[4] = {0.f, 0.f, 0.f, 0.f};
       for (int r = 0; r < in.n; ++r) {
-        const uint32_t word = reinterpret_cast<const uint32_t*>(in.slot[r] + hdr_bytes)[w];
+        if (CB == 8) {
+          const uint32_t word = reinterpret_cast<const uint32_t*>(in.slot[r] + hdr_bytes)[(base + e0) >> 2];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) acc[k] += sm[r][(word >> (8 * k)) & 0xFFu];
+          for (int k = 0; k < 4; ++k) acc[k] += sm[r][(word >> (8 * k)) & 0xFFu];
+        } else {
+          const uint2 word = *reinterpret_cast<const uint2*>(reinterpret_cast<const uint32_t*>(in.slot[r] + hdr_bytes) + ((base + e0) >> 1));
+          acc[0] += sm[r][word.x & 0xFFFFu]; acc[1] += sm[r][word.x >> 16];
+          acc[2] += sm[r][word.y & 0xFFFFu]; acc[3] += sm[r][word.y >> 16];
+        }
       }
       float o[4];
 #pragma unroll
@@ -219,8 +321,8 @@ __global__ void __launch_bounds__(GB_THREADS) sk_decode(SegTable t, SkIn in, siz
 struct SketchBufs {          // lives in gb_plan::sketch (allocated by sk_init)
   float *vals, *edges, *means;
   uint64_t *keys, *sorted;
-  void* temp;
-  size_t temp_bytes;
+  uint32_t *counts, *totals;   // radix sort: [256][nblocks] digit counts -> prefixes, [256] digit totals
+  int nblocks;
   int end_bit;
 };
 
@@ -238,17 +340,16 @@ int sk_init(gb_plan* p) {
   GB_CUDA(cudaMalloc((void**)&b->means, (size_t)p->nseg * (SK_MAXQ + 1) * 4));
   b->end_bit = 32;
   while ((1ll << (b->end_bit - 32)) < p->nseg) ++b->end_bit;
-  b->temp = nullptr;
-  b->temp_bytes = 0;
-  GB_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, b->temp_bytes, (const uint64_t*)b->keys, b->sorted, (int)p->padded, 0, b->end_bit));
-  GB_CUDA(cudaMalloc(&b->temp, b->temp_bytes + 256));
+  b->nblocks = (int)((p->padded + RS_KEYS - 1) / RS_KEYS);
+  GB_CUDA(cudaMalloc((void**)&b->counts, (size_t)256 * b->nblocks * 4));
+  GB_CUDA(cudaMalloc((void**)&b->totals, 256 * 4));
   return 0;
 }
 
 void sk_free(gb_plan* p) {
   SketchBufs* b = (SketchBufs*)p->sketch;
   if (!b) return;
-  cudaFree(b->vals); cudaFree(b->keys); cudaFree(b->sorted); cudaFree(b->edges); cudaFree(b->means); cudaFree(b->temp);
+  cudaFree(b->vals); cudaFree(b->keys); cudaFree(b->sorted); cudaFree(b->edges); cudaFree(b->means); cudaFree(b->counts); cudaFree(b->totals);
   delete b;
   p->sketch = nullptr;
 }
@@ -267,13 +368,24 @@ int sk_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   sk_prep<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, b->vals, b->keys, has_mem, p->prm.beta, p->prm.gamma,
                                                      p->d_ctl);
   LAUNCHED(p);
-  size_t tb = b->temp_bytes;
-  GB_CUDA(cub::DeviceRadixSort::SortKeys(b->temp, tb, (const uint64_t*)b->keys, b->sorted, (int)p->padded, 0, b->end_bit, st));
-  p->launches += (b->end_bit + 7) / 8 + 2;          // histogram + one onesweep pass per 8 key bits
-  sk_edges<<<p->nseg, 128, 0, st>>>(p->tab, b->sorted, q, b->edges); LAUNCHED(p);
-  sk_means<<<dim3(q, p->nseg), 128, 0, st>>>(p->tab, b->sorted, b->edges, q, b->means, out, p->d_ctl, p->par_stride); LAUNCHED(p);
-  sk_encode<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, b->vals, p->d_state0, has_mem, b->edges, b->means, q, out, p->hdr_bytes,
-                                                       p->d_done, gb_comm_peers(c), p->channel, p->d_ctl, p->par_stride);
+  // stable LSD radix sort of the 64-bit keys, 8 bits per pass, ping-pong between keys and sorted
+  uint64_t* src = b->keys;
+  uint64_t* dst = b->sorted;
+  for (int shift = 0; shift < b->end_bit; shift += 8) {
+    rs_hist<<<b->nblocks, GB_THREADS, 0, st>>>(src, p->padded, shift, b->counts, b->nblocks); LAUNCHED(p);
+    rs_scan<<<256, GB_THREADS, 0, st>>>(b->counts, b->nblocks, b->totals); LAUNCHED(p);
+    rs_scatter<<<b->nblocks, GB_THREADS, 0, st>>>(src, dst, p->padded, shift, b->counts, b->nblocks, b->totals); LAUNCHED(p);
+    std::swap(src, dst);
+  }
+  const uint64_t* sorted = src;                       // after the last swap `src` holds the sorted keys
+  sk_edges<<<p->nseg, 128, 0, st>>>(p->tab, sorted, q, b->edges); LAUNCHED(p);
+  sk_means<<<dim3(q, p->nseg), 128, 0, st>>>(p->tab, sorted, b->edges, q, b->means, out, p->d_ctl, p->par_stride); LAUNCHED(p);
+  if (q < 256)
+    sk_encode<8><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, b->vals, p->d_state0, has_mem, b->edges, b->means, q, out, p->hdr_bytes,
+                                                            p->d_done, gb_comm_peers(c), p->channel, p->d_ctl, p->par_stride);
+  else
+    sk_encode<16><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, b->vals, p->d_state0, has_mem, b->edges, b->means, q, out, p->hdr_bytes,
+                                                             p->d_done, gb_comm_peers(c), p->channel, p->d_ctl, p->par_stride);
   LAUNCHED(p);
   return 0;
 }
@@ -283,9 +395,14 @@ int sk_recv(gb_plan* p, float* d_out, cudaStream_t st) {
   SkIn in;
   in.n = c->world;
   for (int r = 0; r < c->world; ++r) in.slot[r] = gb_slot_of(c, c->rank, p->chan_off, p->slot_bytes, 0, r);
-  sk_decode<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, p->hdr_bytes, p->prm.quantum_num, d_out,
-                                                       p->prm.average ? (float)c->world : 1.f, gb_comm_peers(c), p->channel, p->d_ctl,
-                                                       p->par_stride, c->status_dev, c->timeout_ns);
+  if (p->prm.quantum_num < 256)
+    sk_decode<8><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, p->hdr_bytes, p->prm.quantum_num, d_out,
+                                                            p->prm.average ? (float)c->world : 1.f, gb_comm_peers(c), p->channel, p->d_ctl,
+                                                            p->par_stride, c->status_dev, c->timeout_ns);
+  else
+    sk_decode<16><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, p->hdr_bytes, p->prm.quantum_num, d_out,
+                                                             p->prm.average ? (float)c->world : 1.f, gb_comm_peers(c), p->channel, p->d_ctl,
+                                                             p->par_stride, c->status_dev, c->timeout_ns);
   LAUNCHED(p);
   return 0;
 }

@@ -18,8 +18,8 @@ static int quant_bits(const gb_codec_params& p) {
     case GB_CODEC_FP16: return 16;
     case GB_CODEC_QSGD: return p.quantum_num <= 7 ? 4 : (p.quantum_num <= 127 ? 8 : 16);
     case GB_CODEC_TERNGRAD: return 2;
+    case GB_CODEC_SKETCH: return p.quantum_num < 256 ? 8 : 16;     // uint16 bins for >= 256 quantiles (sketch.py:26)
     case GB_CODEC_NATURAL:
-    case GB_CODEC_SKETCH:
     case GB_CODEC_U8BIT: return 8;
     case GB_CODEC_SIGNSGD:
     case GB_CODEC_SIGNUM:

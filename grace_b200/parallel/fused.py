@@ -139,7 +139,7 @@ def codec_params(compressor, memory):
         p.codec, p.ratio = CODEC["adaq"], compressor.compress_ratio
     elif t is C.INCEPTIONNCompressor and 0 < compressor.low_exp <= compressor.mid_exp <= 127:
         p.codec, p.quantum_num = CODEC["inceptionn"], int(compressor.low_exp) | (int(compressor.mid_exp) << 8)
-    elif t is C.SketchCompressor and 2 <= int(compressor.quantiles) <= 255:
+    elif t is C.SketchCompressor and 2 <= int(compressor.quantiles) <= 1023:
         p.codec, p.quantum_num = CODEC["sketch"], int(compressor.quantiles)
     else:
         return None

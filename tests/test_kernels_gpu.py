@@ -312,6 +312,16 @@ def test_sketch(world, memory):
                 assert float((a - b).norm()) <= 0.05 * float(b.norm()) + 1e-6
 
 
+@pytest.mark.parametrize("q", [256, 300, 1000])
+def test_sketch_with_16_bit_bins(q):
+    """>= 256 quantiles travel as uint16 bins (reference: tensorflow/compressor/sketch.py:26); the hand-written radix
+    sort orders all tensors of the bucket in one go (no library sort on the path)."""
+    grads = make_grads(2, 2, scale=0.02)
+    fused, _ = run_fused(2, _params("sketch", "none", quantum_num=q), grads)
+    oracle, _, _ = run_oracle(2, lambda: C.SketchCompressor(q), M.NoneMemory, grads)
+    assert_same(fused, oracle, exact=False, frac=0.002, rtol=2e-5, atol=1e-7, what="sketch%d" % q)
+
+
 @pytest.mark.parametrize("q,bits", [(4, 4), (64, 8), (256, 16)])
 def test_qsgd_bit_widths(q, bits):
     grads = make_grads(2, 1, scale=0.5)
