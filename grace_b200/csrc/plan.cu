@@ -16,7 +16,8 @@ static int quant_bits(const gb_codec_params& p) {
   switch (p.codec) {
     case GB_CODEC_NONE: return 32;
     case GB_CODEC_FP16: return 16;
-    case GB_CODEC_QSGD: return p.quantum_num <= 7 ? 4 : (p.quantum_num <= 127 ? 8 : 16);
+    // signed levels -q..q: 4 bits hold q <= 7, 5 bits q <= 15 ("QSGD 8 levels" of BASELINE config 4), 8 bits q <= 127
+    case GB_CODEC_QSGD: return p.quantum_num <= 7 ? 4 : (p.quantum_num <= 15 ? 5 : (p.quantum_num <= 127 ? 8 : 16));
     case GB_CODEC_TERNGRAD: return 2;
     case GB_CODEC_SKETCH: return p.quantum_num < 256 ? 8 : 16;     // uint16 bins for >= 256 quantiles (sketch.py:26)
     case GB_CODEC_NATURAL:
@@ -178,7 +179,7 @@ extern "C" int gb_plan_create(gb_comm* c, int nseg, const int64_t* numels, const
   } else {
     p->hdr_bytes = params->codec == GB_CODEC_SKETCH ? sk_header_bytes(nseg, params->quantum_num)
                                                     : (((size_t)nseg * 4 * 4 + 255) & ~size_t(255));
-    p->slot_bytes = p->hdr_bytes + (((size_t)p->padded * p->bits / 8 + 255) & ~size_t(255));
+    p->slot_bytes = p->hdr_bytes + (((size_t)p->padded * p->bits / 8 + 16 + 255) & ~size_t(255));   // + 16: the 5-bit decoder reads one word ahead
   }
   p->channel2 = 0;
   p->mid_epoch = 0;

@@ -322,10 +322,17 @@ def test_sketch_with_16_bit_bins(q):
     assert_same(fused, oracle, exact=False, frac=0.002, rtol=2e-5, atol=1e-7, what="sketch%d" % q)
 
 
-@pytest.mark.parametrize("q,bits", [(4, 4), (64, 8), (256, 16)])
+@pytest.mark.parametrize("q,bits", [(4, 4), (7, 4), (8, 5), (15, 5), (16, 8), (64, 8), (256, 16)])
 def test_qsgd_bit_widths(q, bits):
     grads = make_grads(2, 1, scale=0.5)
     fused, _ = run_fused(2, _params("qsgd", quantum_num=q), grads)
+    from grace_b200.parallel.engine import Engine
+    (e,) = Engine.local(1)
+    try:
+        pl = e.plan(SIZES, NAMES, _params("qsgd", quantum_num=q))
+        assert pl.padded * bits // 8 <= pl.wire_bytes <= pl.padded * bits // 8 + 4096, (pl.wire_bytes, pl.padded, bits)
+    finally:
+        e.destroy()
     oracle, _, _ = run_oracle(2, lambda: C.QSGDCompressor(q, seed=SEED), M.NoneMemory, grads)
     assert_same(fused, oracle, exact=False, frac=0.002, rtol=2e-5, atol=1e-7, what="qsgd%d" % q)
 
