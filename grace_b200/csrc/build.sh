@@ -3,6 +3,9 @@
 set -e
 HERE="$(cd "$(dirname "$0")" && pwd)"
 OUT="$HERE/../lib"
+# GB_DEBUG=1: the checking build (device-side bounds asserts -> GB_STATUS_ASSERT), kept next to the release one;
+# select it at run time with GRACE_B200_LIB=grace_b200/lib/debug/libgrace_b200.so
+if [ -n "$GB_DEBUG" ]; then OUT="$OUT/debug"; GB_NVCC_EXTRA="$GB_NVCC_EXTRA -DGB_DEBUG"; fi
 mkdir -p "$OUT"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -Wall -Xcompiler -Wno-unknown-pragmas ${GB_NVCC_EXTRA}"

@@ -11,7 +11,9 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libgrace_b200.so")
+# GRACE_B200_LIB picks another build of the same library, e.g. the -DGB_DEBUG one (bounds asserts in every
+# emit / merge / decode store) that ``GB_DEBUG=1 bash grace_b200/csrc/build.sh`` writes to lib/debug/
+LIB_PATH = os.environ.get("GRACE_B200_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libgrace_b200.so")
 BUILD_SH = os.path.join(os.path.dirname(_HERE), "csrc", "build.sh")
 
 CODEC = dict(none=0, fp16=1, topk=2, randomk=3, threshold=4, dgc=5, qsgd=6, terngrad=7, natural=8, u8bit=9,

@@ -88,21 +88,48 @@ def main():
     # back-to-back exchanges on the same double-buffered slots (SURVEY §5 race-detection row)
     import random
     rnd = random.Random(1234 + rank)
-    params = dict(compressor="topk", memory="residual", communicator="allgather", world_size=world, compress_ratio=0.02)
-    fast = grace_from_params(params)
-    gen = torch.Generator(device="cuda").manual_seed(77 + rank)
-    for it in range(40):
-        if rnd.random() < 0.5:
-            torch.cuda._sleep(int(rnd.random() * 3e6))          # up to ~1.5 ms of skew on this rank
-        g = torch.randn(50000, device="cuda", generator=gen)
-        a = fast.step(g, "stress").clone()
-        if not same_on_all_ranks(a):
-            failures.append("stress iteration %d: ranks disagree" % it)
-            break
-        k = max(1, int(50000 * 0.02))
-        if int((a != 0).sum()) > world * k:
-            failures.append("stress iteration %d: %d non-zeros > W*k" % (it, int((a != 0).sum())))
-            break
+    stress = [
+        ("topk", dict(compressor="topk", memory="residual", communicator="allgather", compress_ratio=0.02), (50000,)),
+        ("qsgd", dict(compressor="qsgd", memory="none", communicator="allgather", quantum_num=64), (50000,)),
+        ("signsgd", dict(compressor="signsgd", memory="none", communicator="allgather"), (50000,)),
+        ("none", dict(compressor="none", memory="none", communicator="allreduce"), (50000,)),
+        ("powersgd", dict(compressor="powersgd", memory="powersgd", communicator="allreduce", compress_rank=4), (200, 250)),
+    ]
+    for label, params, shape in stress:
+        fast = grace_from_params(dict(params, world_size=world))
+        gen = torch.Generator(device="cuda").manual_seed(77 + rank)
+        n = 1
+        for d in shape:
+            n *= d
+        for it in range(40):
+            if rnd.random() < 0.5:
+                torch.cuda._sleep(int(rnd.random() * 3e6))          # up to ~1.5 ms of skew on this rank
+            g = torch.randn(shape, device="cuda", generator=gen)
+            want = None
+            if label == "none":
+                want = g.clone()
+                dist.all_reduce(want)
+                want /= world
+            if label == "powersgd":            # K3's native path is the bucketed entry
+                a = torch.cat([o.flatten() for o in fast.step_all([("stress_a", g), ("stress_b", g[:64] * 2.0)])]).clone()
+            else:
+                a = fast.step(g, "stress_" + label).clone()
+            if not same_on_all_ranks(a):
+                failures.append("stress %s iteration %d: ranks disagree" % (label, it))
+                break
+            if not bool(torch.isfinite(a).all()):
+                failures.append("stress %s iteration %d: non-finite output" % (label, it))
+                break
+            if label == "topk" and int((a != 0).sum()) > world * max(1, int(n * 0.02)):
+                failures.append("stress iteration %d: %d non-zeros > W*k" % (it, int((a != 0).sum())))
+                break
+            if want is not None and not torch.allclose(a, want, rtol=1e-5, atol=1e-6):
+                failures.append("stress none iteration %d: differs from all_reduce by %g" % (it, float((a - want).abs().max())))
+                break
+        assert fast._stepper is not None and (fast._stepper.enabled or label == "powersgd"), label
+        if label == "powersgd":
+            assert fast._stepper.launches() > 0, "PowerSGD stress ran on the generic path"
+        fast.close()
 
     # dense buckets: NVLS multimem when the host has it, else the P2P two-shot plan -- same API
     def train_dense():
