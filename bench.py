@@ -268,8 +268,15 @@ def run_codec(args, comp_name, env):
     graphed, graph_note = None, "eager"
     if args.impl == "ours" and opt is not None and not args.no_graph:
         try:
+            from grace_b200.utils.capture import unmasked_attention_when_capturing
+
             def loss_fn(m, x, y):
-                return m(input_ids=x, labels=x, next_sentence_label=y).loss if is_bert else F.cross_entropy(m(x), y)
+                if not is_bert:
+                    return F.cross_entropy(m(x), y)
+                # no attention_mask is passed: keep transformers from materialising an all-ones mask while the
+                # stream captures (that mask sends SDPA to the fp32 math path; see grace_b200/utils/capture.py)
+                with unmasked_attention_when_capturing():
+                    return m(input_ids=x, labels=x, next_sentence_label=y).loss
             graphed = hvd.GraphedStep(model, opt, loss_fn, [dev_x, dev_y], amp_dtype=torch.bfloat16, warmup=3)
             dev_x, dev_y = graphed.static_inputs
             graph_note = "cuda-graph (whole step)"

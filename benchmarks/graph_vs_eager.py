@@ -78,6 +78,7 @@ def main():
     ap.add_argument("--compressor", default="qsgd")
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--keep-mask", action="store_true", help="capture without grace_b200.utils.capture's mask hint")
     a = ap.parse_args()
 
     import torch
@@ -107,8 +108,15 @@ def main():
         x = torch.randn(bs, 3, 224, 224, device=device).contiguous(memory_format=mf)
         y = torch.randint(0, 1000, (bs,), device=device)
 
+    import contextlib
+    from grace_b200.utils.capture import unmasked_attention_when_capturing
+    hint = contextlib.nullcontext if a.keep_mask else unmasked_attention_when_capturing
+
     def loss_fn(m, x, y):
-        return m(input_ids=x, labels=x, next_sentence_label=y).loss if is_bert else F.cross_entropy(m(x), y)
+        if not is_bert:
+            return F.cross_entropy(m(x), y)
+        with hint():
+            return m(input_ids=x, labels=x, next_sentence_label=y).loss
 
     def eager(x, y):
         opt.zero_grad()
@@ -133,7 +141,7 @@ def main():
         torch.cuda.synchronize()
         return e0.elapsed_time(e1) / n
 
-    out = {"model": a.model, "compressor": a.compressor,
+    out = {"model": a.model, "compressor": a.compressor, "mask_hint": not a.keep_mask,
            "unprofiled_ms_per_step": {"graph": timed(graphed), "eager": timed(eager)}}
     tmp = tempfile.mkdtemp()
     traces = {}

@@ -63,7 +63,10 @@ struct gb_psgd {
   int nmat, rank_r, has_mem, use_tc;
   int rp;                   // row pitch of the stored P / Q rows in floats: 4, 8 or 16 (rank rounded up)
   float *d_part1, *d_part2; // split-K partial tiles of the two grouped GEMMs [items][128][rp]
-  float* d_qprev;           // warm start: the previous exchange's averaged Q [qrows][rp] (null: fresh Q every step)
+  float* d_qprev;           // the previous exchange's averaged Q [qrows][rp]: implicit residual, and Q0 of a warm start
+  int warm;                 // 1: Q0 = previous Q (compressor/powersgd.py:37-39), 0: fresh normal draw every step
+  int* d_simt;              // indices of the matrices on the CUDA-core fallback
+  int nsimt, simt_rows, simt_cblocks;
   uint32_t seed, step, epoch;
   int64_t padded, prows, qrows;
   std::vector<PsMat> h_mat;
@@ -72,7 +75,7 @@ struct gb_psgd {
   PsItem *d_items1, *d_items2;
   int nitems1, nitems2, ntiles1, ntiles2;
   CUtensorMap* d_maps;      // [nmat][4]: A1 (M, box 32x128), B1 (Q0^T), A2 (M, box 32x32), B2 (P^^T)
-  float *d_work, *d_res;    // compensated gradient / residual (padded floats)
+  float* d_work;            // compensated gradient M of the last exchange (padded floats); residual = M - P^ Q^T is implicit
   float *d_q0t, *d_pht;     // Q0^T [16][qrows_pad], P^^T [16][prows_pad]  (per-matrix column windows)
   float *d_pacc, *d_qacc;   // local accumulators [prows][4], [qrows][4]
   float *d_ph;              // P^ [prows][4]
@@ -164,7 +167,8 @@ __device__ float g_dbg_dump[8192];
 template <int MODE, int RP>
 __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ items, const PsMat* __restrict__ mats,
                                                   const CUtensorMap* __restrict__ maps, float* part, uint32_t* tile_cnt,
-                                                  PsPeers peers, const StepCtl* ctl, size_t par_stride) {
+                                                  PsPeers peers, const StepCtl* ctl, size_t par_stride, uint32_t* done,
+                                                  PeerPtrs flag_peers, int channel, int release) {
   extern __shared__ uint8_t smem_raw[];
   if (ctl->epoch & 1) shift(peers, par_stride);
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -302,18 +306,37 @@ __global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ ite
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(32u) : "memory");
   }
+  // every matrix of the bucket went through this launch: the CTA that finishes last publishes the epoch (no separate
+  // flag kernel); with CUDA-core fallback matrices in the bucket their launch, which follows on the stream, does it
+  if (release) release_flags_last_block(done, flag_peers, channel, ctl->epoch);
 }
 
 // ---------------------------------------------------------------- CUDA-core fallbacks (shapes TMA cannot address)
+// Matrices whose row pitch is not a multiple of 16 bytes (ResNet-50: the 64 x 147 stem convolution) or that are
+// smaller than one MMA tile.  `simt` lists their indices, so nobody walks the whole matrix table.  Both kernels store
+// their rows straight into every peer's slot and -- running last on the stream in their phase -- release the flags.
 template <int RP>
-__global__ void __launch_bounds__(GB_THREADS) k3_gemm1_simt(const PsMat* __restrict__ mats, int nmat, const float* __restrict__ work,
-                                                           const float* __restrict__ q0t, int64_t qpad, float* acc) {
-  // one warp per row: P[i][c] = sum_j M[i][j] Q0[j][c]
+__device__ __forceinline__ void push_row(const PsPeers& peers, size_t row, const float (&s)[RP]) {
+#pragma unroll
+  for (int c4 = 0; c4 < RP / 4; ++c4)
+    for (int r = 0; r < peers.n; ++r)
+      wire_st_u4(reinterpret_cast<float4*>(peers.slot[r] + row * RP) + c4,
+                 make_uint4(__float_as_uint(s[c4 * 4]), __float_as_uint(s[c4 * 4 + 1]), __float_as_uint(s[c4 * 4 + 2]),
+                            __float_as_uint(s[c4 * 4 + 3])), peers.mc);
+}
+
+// one warp per row: P[i][c] = sum_j M[i][j] Q0[j][c]
+template <int RP>
+__global__ void __launch_bounds__(GB_THREADS) k3_gemm1_simt(const PsMat* __restrict__ mats, const int* __restrict__ simt, int nsimt,
+                                                           const float* __restrict__ work, const float* __restrict__ q0t,
+                                                           int64_t qpad, PsPeers out, uint32_t* done, PeerPtrs peers, int channel,
+                                                           const StepCtl* ctl, size_t par_stride) {
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(out, par_stride);
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   int base = 0;
-  for (int mi = 0; mi < nmat; ++mi) {
-    const PsMat mt = mats[mi];
-    if (mt.tc) continue;
+  for (int si = 0; si < nsimt; ++si) {
+    const PsMat mt = mats[simt[si]];
     if (gw >= base && gw < base + mt.n) {
       const int i = gw - base;
       const float* rowp = work + mt.off + (size_t)i * mt.m;
@@ -327,83 +350,60 @@ __global__ void __launch_bounds__(GB_THREADS) k3_gemm1_simt(const PsMat* __restr
       }
 #pragma unroll
       for (int c = 0; c < RP; ++c) s[c] = warp_sum(s[c]);
-      if (lane == 0) {
-#pragma unroll
-        for (int c = 0; c < RP; ++c) acc[(size_t)(mt.prow0 + i) * RP + c] = s[c];
-      }
-      return;
+      if (lane == 0) push_row<RP>(out, (size_t)(mt.prow0 + i), s);
+      break;
     }
     base += mt.n;
-  }
-}
-
-template <int RP>
-__global__ void __launch_bounds__(GB_THREADS) k3_gemm2_simt(const PsMat* __restrict__ mats, int nmat, const float* __restrict__ work,
-                                                           const float* __restrict__ ph, float* acc) {
-  // one thread per column: Q[j][c] = sum_i M[i][j] P^[i][c]
-  const int gt = blockIdx.x * blockDim.x + threadIdx.x;
-  int base = 0;
-  for (int mi = 0; mi < nmat; ++mi) {
-    const PsMat mt = mats[mi];
-    if (mt.tc) continue;
-    if (gt >= base && gt < base + mt.m) {
-      const int j = gt - base;
-      float s[RP];
-#pragma unroll
-      for (int c = 0; c < RP; ++c) s[c] = 0.f;
-#pragma unroll 4
-      for (int i = 0; i < mt.n; ++i) {
-        const float x = work[mt.off + (size_t)i * mt.m + j];
-        const float* pr = ph + (size_t)(mt.prow0 + i) * RP;
-#pragma unroll
-        for (int c = 0; c < RP; ++c) s[c] += x * pr[c];
-      }
-#pragma unroll
-      for (int c = 0; c < RP; ++c) acc[(size_t)(mt.qrow0 + j) * RP + c] = s[c];
-      return;
-    }
-    base += mt.m;
-  }
-}
-
-// pushes the rows of fallback matrices to every peer, then the last CTA releases the epoch flags
-__global__ void __launch_bounds__(GB_THREADS) k3_flag(const PsMat* __restrict__ mats, int nmat, int which, const float* acc, int rp,
-                                                     PsPeers peers_slots, uint32_t* done, PeerPtrs peers, int channel,
-                                                     const StepCtl* ctl, size_t par_stride) {
-  const uint32_t epoch = ctl->epoch;
-  if (epoch & 1) shift(peers_slots, par_stride);
-  for (int mi = 0; mi < nmat; ++mi) {
-    const PsMat mt = mats[mi];
-    if (mt.tc) continue;
-    const int rows = which == 1 ? mt.n : mt.m, row0 = which == 1 ? mt.prow0 : mt.qrow0;
-    const int q4 = rp / 4;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows * q4; i += gridDim.x * blockDim.x) {
-      const float4 o = reinterpret_cast<const float4*>(acc + (size_t)row0 * rp)[i];
-      for (int r = 0; r < peers_slots.n; ++r)
-        wire_st_u4(reinterpret_cast<float4*>(peers_slots.slot[r] + (size_t)row0 * rp) + i,
-                   make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), __float_as_uint(o.w)), peers_slots.mc);
-    }
   }
   release_flags_last_block(done, peers, channel, epoch);
 }
 
-// ---------------------------------------------------------------- element-wise prep
-__global__ void __launch_bounds__(GB_THREADS) k3_prep(int64_t padded, const float* __restrict__ grad, const float* __restrict__ res,
-                                                     float* work, int has_mem, float* pacc, int64_t np, float* qacc, int64_t nq,
-                                                     uint32_t* cnt, int ncnt, const StepCtl* ctl) {
-  const int has_res = has_mem && ctl->step > 0;      // first call: the memory is empty
-  const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = tid; i < padded / 4; i += nth) {
-    float4 g = reinterpret_cast<const float4*>(grad)[i];
-    if (has_res) {
-      const float4 r = reinterpret_cast<const float4*>(res)[i];
-      g.x = __fadd_rn(g.x, r.x); g.y = __fadd_rn(g.y, r.y); g.z = __fadd_rn(g.z, r.z); g.w = __fadd_rn(g.w, r.w);
+// Q[j][c] = sum_i M[i][j] P^[i][c]: a CTA owns 32 columns, its 8 warps take every 8th row, the slices are added in
+// slice order (first version: one thread per column walking all rows, 27 us for the 64 x 147 matrix alone)
+template <int RP>
+__global__ void __launch_bounds__(GB_THREADS) k3_gemm2_simt(const PsMat* __restrict__ mats, const int* __restrict__ simt, int nsimt,
+                                                           const float* __restrict__ work, const float* __restrict__ ph, PsPeers out,
+                                                           uint32_t* done, PeerPtrs peers, int channel, const StepCtl* ctl,
+                                                           size_t par_stride) {
+  const uint32_t epoch = ctl->epoch;
+  if (epoch & 1) shift(out, par_stride);
+  __shared__ float part[8][32][RP + 1];
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  int base = 0;
+  for (int si = 0; si < nsimt; ++si) {
+    const PsMat mt = mats[simt[si]];
+    const int nb = (mt.m + 31) / 32;
+    if ((int)blockIdx.x >= base && (int)blockIdx.x < base + nb) {
+      const int j = ((int)blockIdx.x - base) * 32 + lane;
+      float s[RP];
+#pragma unroll
+      for (int c = 0; c < RP; ++c) s[c] = 0.f;
+      if (j < mt.m) {
+#pragma unroll 4
+        for (int i = slice; i < mt.n; i += 8) {
+          const float x = work[mt.off + (size_t)i * mt.m + j];
+          const float* pr = ph + (size_t)(mt.prow0 + i) * RP;
+#pragma unroll
+          for (int c = 0; c < RP; ++c) s[c] += x * pr[c];
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < RP; ++c) part[slice][lane][c] = s[c];
+      __syncthreads();
+      if (slice == 0 && j < mt.m) {
+#pragma unroll
+        for (int c = 0; c < RP; ++c) {
+          float t = part[0][lane][c];
+          for (int k = 1; k < 8; ++k) t += part[k][lane][c];
+          s[c] = t;
+        }
+        push_row<RP>(out, (size_t)(mt.qrow0 + j), s);
+      }
+      break;
     }
-    reinterpret_cast<float4*>(work)[i] = g;
+    base += nb;
   }
-  for (int64_t i = tid; i < np; i += nth) pacc[i] = 0.f;
-  for (int64_t i = tid; i < nq; i += nth) qacc[i] = 0.f;
-  for (int64_t i = tid; i < ncnt; i += nth) cnt[i] = 0u;
+  release_flags_last_block(done, peers, channel, epoch);
 }
 
 // ---------------------------------------------------------------- Cholesky-QR on a tall [len][4] matrix
@@ -569,14 +569,11 @@ __device__ __forceinline__ void cholqr2_any(float* buf, int len, int r, float* s
 template <int RP>
 struct PsShared { static constexpr int floats = RP == 4 ? 512 : 128 * RP + 2 * RP * RP; };
 
-// Q0 per matrix: a fresh Philox normal draw -- or, with a warm start and from the second exchange on, the previous
-// exchange's Q (reference: compressor/powersgd.py:37-39 use_memory) -- orthogonalised; writes Q0^T [16][qpad]
+// Q0 per matrix (one CTA of k3_prep): a fresh Philox normal draw -- or, with a warm start and from the second exchange
+// on, the previous exchange's Q (reference: compressor/powersgd.py:37-39 use_memory) -- orthogonalised; writes Q0^T [16][qpad]
 template <int RP>
-__global__ void __launch_bounds__(512) k3_q0(const PsMat* __restrict__ mats, float* q0, const float* __restrict__ qprev, float* q0t,
-                                             int64_t qpad, uint32_t seed, const StepCtl* ctl) {
-  const uint32_t step = ctl->step;
-  __shared__ float sh[PsShared<RP>::floats];
-  const PsMat mt = mats[blockIdx.x];
+__device__ __forceinline__ void q0_body(const PsMat& mt, float* q0, const float* __restrict__ qprev, float* q0t, int64_t qpad,
+                                        uint32_t seed, uint32_t step, float* sh) {
   float* buf = q0 + (size_t)mt.qrow0 * RP;
   const bool warm = qprev != nullptr && step > 0;
   for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
@@ -668,71 +665,174 @@ __device__ __forceinline__ float dot_r(const float* p, const float (&q)[RP]) {
   return s;
 }
 
-// One CTA per (matrix, 32-row band).  A thread owns four consecutive columns (16-byte accesses) and walks
-// the band eight rows at a time with all loads issued before the dependent stores (first version: scalar
-// accesses with load->store->store chains, 245 us for ResNet-50 under ncu = half of the whole exchange).
-// The band that starts at row 0 also keeps the averaged Q for a warm start of the next exchange.
+// ---------------------------------------------------------------- band kernels: prep, final, residual read-out
+// One CTA per (matrix, 32-row band).  A thread owns four consecutive columns (16-byte accesses) and every `rl`-th row
+// of the band, eight rows at a time with all loads issued before the dependent stores; narrow matrices spread their
+// 32 rows over the threads the columns leave idle.
+//
+// The error-feedback memory is IMPLICIT: `work` keeps the compensated gradient M of the last exchange, `ph` and
+// `qkeep` its P^ and averaged Q, and the residual  e = M - P^ Q^T  (memory/powersgd.py:24-37) is recomputed where it
+// is consumed -- in the next exchange's prep:  M' = grad + (M - P^ Q^T)  -- by the same dot product that produced the
+// output, so the bits are those a stored residual would have had.  A write-only k3_final (102 MB instead of reading
+// 102 MB and writing 204 MB for ResNet-50; streaming writes run at about half the read bandwidth here) and no
+// residual buffer at all are what that buys.
+//   MODE 0 (prep)   work = grad [+ work - P^ Q^T]          Q from qkeep
+//   MODE 1 (final)  out  = P^ Q^T, qkeep = Q               Q = mean over the ranks' slots
+//   MODE 2 (resid)  out  = work - P^ Q^T                   Q from qkeep (state read-out)
+template <int RP, int MODE>
+__device__ __forceinline__ void band_body(const PsMat& mt, const PsBand& b, const float* __restrict__ ph, const float* qsrc,
+                                          const PsIn& in, float inv_world, const float* __restrict__ grad, float* work,
+                                          float* out, float* qkeep, bool use_prev, float* sp) {
+  const int nrow = min(32, mt.n - b.i0);
+  const bool need_pq = MODE != 0 || use_prev;
+  if (need_pq)
+    for (int i = threadIdx.x; i < nrow * RP; i += blockDim.x) sp[i] = ph[(size_t)(mt.prow0 + b.i0) * RP + i];
+  __syncthreads();
+  const size_t band0 = mt.off + (size_t)b.i0 * mt.m;
+  const bool vec = (mt.m & 3) == 0;
+  const int ncg = vec ? mt.m >> 2 : mt.m;                       // column groups: 4 columns (or 1 on the scalar path)
+  const int cgs = min(ncg, (int)blockDim.x), rl = (int)blockDim.x / cgs;
+  const int my_cg = threadIdx.x % cgs, my_r = threadIdx.x / cgs;
+  if (my_r >= rl) return;
+  const bool keep = MODE == 1 && qkeep != nullptr && b.i0 == 0 && my_r == 0;
+  if (vec) {
+    for (int cg = my_cg; cg < ncg; cg += cgs) {
+      const int j = cg * 4;
+      float q[4][RP];
+      if (need_pq) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (MODE == 1) {
+            mean_q<RP>(in, (size_t)(mt.qrow0 + j + c), inv_world, q[c]);
+          } else {
+#pragma unroll
+            for (int c4 = 0; c4 < RP / 4; ++c4) {
+              const float4 x = reinterpret_cast<const float4*>(qsrc + (size_t)(mt.qrow0 + j + c) * RP)[c4];
+              q[c][c4 * 4] = x.x; q[c][c4 * 4 + 1] = x.y; q[c][c4 * 4 + 2] = x.z; q[c][c4 * 4 + 3] = x.w;
+            }
+          }
+          if (keep) {
+#pragma unroll
+            for (int c4 = 0; c4 < RP / 4; ++c4)
+              reinterpret_cast<float4*>(qkeep + (size_t)(mt.qrow0 + j + c) * RP)[c4] =
+                  make_float4(q[c][c4 * 4], q[c][c4 * 4 + 1], q[c][c4 * 4 + 2], q[c][c4 * 4 + 3]);
+          }
+        }
+      }
+      constexpr int U = MODE == 0 ? 4 : 8;       // rows in flight per thread (prep loads two streams: same bytes in flight)
+      for (int i0 = my_r; i0 < nrow; i0 += U * rl) {
+        float4 w[U], g[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int i = i0 + u * rl;
+          if (i < nrow) {
+            const size_t e = band0 + (size_t)i * mt.m + j;
+            if (MODE == 0) g[u] = *reinterpret_cast<const float4*>(grad + e);
+            if (MODE == 2 || (MODE == 0 && use_prev)) w[u] = *reinterpret_cast<const float4*>(work + e);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int i = i0 + u * rl;
+          if (i < nrow) {
+            const size_t e = band0 + (size_t)i * mt.m + j;
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (need_pq) {
+              const float* pr = sp + i * RP;
+              o = make_float4(dot_r<RP>(pr, q[0]), dot_r<RP>(pr, q[1]), dot_r<RP>(pr, q[2]), dot_r<RP>(pr, q[3]));
+            }
+            if (MODE == 1) {
+              *reinterpret_cast<float4*>(out + e) = o;
+            } else if (MODE == 2) {
+              *reinterpret_cast<float4*>(out + e) = make_float4(w[u].x - o.x, w[u].y - o.y, w[u].z - o.z, w[u].w - o.w);
+            } else if (use_prev) {
+              *reinterpret_cast<float4*>(work + e) =
+                  make_float4(__fadd_rn(g[u].x, w[u].x - o.x), __fadd_rn(g[u].y, w[u].y - o.y), __fadd_rn(g[u].z, w[u].z - o.z),
+                              __fadd_rn(g[u].w, w[u].w - o.w));
+            } else {
+              *reinterpret_cast<float4*>(work + e) = g[u];
+            }
+          }
+        }
+      }
+    }
+  } else {
+    for (int j = my_cg; j < ncg; j += cgs) {
+      float q[RP];
+#pragma unroll
+      for (int c = 0; c < RP; ++c) q[c] = 0.f;
+      if (need_pq) {
+        if (MODE == 1) {
+          mean_q<RP>(in, (size_t)(mt.qrow0 + j), inv_world, q);
+        } else {
+#pragma unroll
+          for (int c = 0; c < RP; ++c) q[c] = qsrc[(size_t)(mt.qrow0 + j) * RP + c];
+        }
+        if (keep) {
+#pragma unroll
+          for (int c = 0; c < RP; ++c) qkeep[(size_t)(mt.qrow0 + j) * RP + c] = q[c];
+        }
+      }
+      for (int i = my_r; i < nrow; i += rl) {
+        const size_t e = band0 + (size_t)i * mt.m + j;
+        const float o = need_pq ? dot_r<RP>(sp + i * RP, q) : 0.f;
+        if (MODE == 1) out[e] = o;
+        else if (MODE == 2) out[e] = work[e] - o;
+        else if (use_prev) work[e] = __fadd_rn(grad[e], work[e] - o);
+        else work[e] = grad[e];
+      }
+    }
+  }
+}
+
+#define PS_BAND_THREADS 512
+
+// phase 1 prologue, one launch: CTAs [0, nmat) draw and orthogonalise Q0 (latency-bound, one matrix each), the band
+// CTAs behind them stream  work = grad + residual  and clear the split-K tile counters
 template <int RP>
-__global__ void __launch_bounds__(GB_THREADS) k3_final(const PsBand* __restrict__ bands, const PsMat* __restrict__ mats, PsIn in,
-                                                      float inv_world, const float* __restrict__ ph, const float* __restrict__ work,
-                                                      float* __restrict__ res, int has_res, float* __restrict__ out, float* qkeep,
-                                                      PeerPtrs peers, int channel, const StepCtl* ctl, size_t par_stride,
-                                                      uint32_t* status, uint64_t timeout_ns) {
+__global__ void __launch_bounds__(PS_BAND_THREADS, RP == 16 ? 1 : 2) k3_prep(const PsBand* __restrict__ bands, const PsMat* __restrict__ mats, int nmat,
+                                                           const float* __restrict__ grad, float* work, const float* __restrict__ ph,
+                                                           float* qkeep, int has_mem, int warm, float* q0, float* q0t, int64_t qpad,
+                                                           uint32_t seed, uint32_t* cnt, int ncnt, const StepCtl* ctl) {
+  __shared__ __align__(16) float sh[PsShared<RP>::floats > 32 * RP ? PsShared<RP>::floats : 32 * RP];
+  const uint32_t step = ctl->step;
+  if ((int)blockIdx.x < nmat) {
+    q0_body<RP>(mats[blockIdx.x], q0, warm ? qkeep : nullptr, q0t, qpad, seed, step, sh);
+    return;
+  }
+  const int bi = (int)blockIdx.x - nmat;
+  for (int i = bi * (int)blockDim.x + (int)threadIdx.x; i < ncnt; i += ((int)gridDim.x - nmat) * (int)blockDim.x) cnt[i] = 0u;
+  const PsBand b = bands[bi];
+  const PsMat mt = mats[b.mat];
+  PsIn none; none.n = 0;
+  band_body<RP, 0>(mt, b, ph, qkeep, none, 1.f, grad, work, nullptr, nullptr, has_mem && step > 0, sh);
+}
+
+// phase 3: wait flags; Q = mean_r Q_r; out = P^ Q^T (write only; the band that starts at row 0 keeps Q)
+template <int RP>
+__global__ void __launch_bounds__(PS_BAND_THREADS) k3_final(const PsBand* __restrict__ bands, const PsMat* __restrict__ mats, PsIn in,
+                                                            float inv_world, const float* __restrict__ ph, float* __restrict__ out,
+                                                            float* qkeep, PeerPtrs peers, int channel, const StepCtl* ctl,
+                                                            size_t par_stride, uint32_t* status, uint64_t timeout_ns) {
   const uint32_t epoch = ctl->epoch;
   if (epoch & 1) shift(in, par_stride);
   __shared__ __align__(16) float sp[32 * RP];
   wait_all_ranks(peers, channel, epoch, status, timeout_ns);
   const PsBand b = bands[blockIdx.x];
   const PsMat mt = mats[b.mat];
-  const int nrow = min(32, mt.n - b.i0);
-  for (int i = threadIdx.x; i < nrow * RP; i += blockDim.x) sp[i] = ph[(size_t)(mt.prow0 + b.i0) * RP + i];
-  __syncthreads();
-  const size_t band0 = mt.off + (size_t)b.i0 * mt.m;
-  const bool keep = qkeep != nullptr && b.i0 == 0;
-  if ((mt.m & 3) == 0) {
-    for (int j = threadIdx.x * 4; j < mt.m; j += blockDim.x * 4) {
-      float q[4][RP];
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        mean_q<RP>(in, (size_t)(mt.qrow0 + j + c), inv_world, q[c]);
-        if (keep) {
-#pragma unroll
-          for (int e = 0; e < RP; ++e) qkeep[(size_t)(mt.qrow0 + j + c) * RP + e] = q[c][e];
-        }
-      }
-      for (int i0 = 0; i0 < nrow; i0 += 8) {
-        float4 w[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-          if (has_res && i0 + u < nrow) w[u] = *reinterpret_cast<const float4*>(work + band0 + (size_t)(i0 + u) * mt.m + j);
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          if (i0 + u < nrow) {
-            const float* pr = sp + (i0 + u) * RP;
-            const float4 o = make_float4(dot_r<RP>(pr, q[0]), dot_r<RP>(pr, q[1]), dot_r<RP>(pr, q[2]), dot_r<RP>(pr, q[3]));
-            const size_t e = band0 + (size_t)(i0 + u) * mt.m + j;
-            if (has_res) *reinterpret_cast<float4*>(res + e) = make_float4(w[u].x - o.x, w[u].y - o.y, w[u].z - o.z, w[u].w - o.w);
-            *reinterpret_cast<float4*>(out + e) = o;
-          }
-        }
-      }
-    }
-  } else {
-    for (int j = threadIdx.x; j < mt.m; j += blockDim.x) {
-      float q[RP];
-      mean_q<RP>(in, (size_t)(mt.qrow0 + j), inv_world, q);
-      if (keep) {
-#pragma unroll
-        for (int e = 0; e < RP; ++e) qkeep[(size_t)(mt.qrow0 + j) * RP + e] = q[e];
-      }
-      for (int i = 0; i < nrow; ++i) {
-        const size_t e = band0 + (size_t)i * mt.m + j;
-        const float o = dot_r<RP>(sp + i * RP, q);
-        if (has_res) res[e] = work[e] - o;
-        out[e] = o;
-      }
-    }
-  }
+  band_body<RP, 1>(mt, b, ph, nullptr, in, inv_world, nullptr, nullptr, out, qkeep, true, sp);
+}
+
+// state read-out: dst = work - P^ Q^T, the residual a PowerSGDMemory would hold after the last exchange
+template <int RP>
+__global__ void __launch_bounds__(PS_BAND_THREADS) k3_resid(const PsBand* __restrict__ bands, const PsMat* __restrict__ mats,
+                                                            const float* __restrict__ ph, const float* __restrict__ qkeep,
+                                                            float* work, float* dst) {
+  __shared__ __align__(16) float sp[32 * RP];
+  const PsBand b = bands[blockIdx.x];
+  const PsMat mt = mats[b.mat];
+  PsIn none; none.n = 0;
+  band_body<RP, 2>(mt, b, ph, qkeep, none, 1.f, nullptr, work, dst, nullptr, true, sp);
 }
 
 // ---------------------------------------------------------------- host side
@@ -818,7 +918,7 @@ extern "C" int gb_psgd_create(gb_comm* c, int nmat, const int64_t* rows, const i
 static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, const int64_t* cols, const uint32_t* name_hash,
                       int rank_r, uint32_t seed, int has_memory, int use_tcgen05, int warm_start) {
   p->rp = rank_r <= 4 ? 4 : rank_r <= 8 ? 8 : 16;
-  p->d_qprev = nullptr;
+  p->d_qprev = nullptr; p->d_simt = nullptr; p->warm = warm_start ? 1 : 0;
   p->comm = c; p->nmat = nmat; p->rank_r = rank_r; p->has_mem = has_memory; p->use_tc = use_tcgen05;
   p->seed = seed; p->step = 0; p->epoch = 0; p->launches = 0;
   int64_t off = 0, prow = 0, qrow = 0;
@@ -853,19 +953,25 @@ static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, con
   if (!it2.empty()) GB_CUDA(cudaMemcpy(p->d_items2, it2.data(), sizeof(PsItem) * it2.size(), cudaMemcpyHostToDevice));
   GB_CUDA(cudaMalloc((void**)&p->d_work, p->padded * 4));
   GB_CUDA(cudaMemset(p->d_work, 0, p->padded * 4));
-  p->d_res = nullptr;
-  if (has_memory) { GB_CUDA(cudaMalloc((void**)&p->d_res, p->padded * 4)); GB_CUDA(cudaMemset(p->d_res, 0, p->padded * 4)); }
   GB_CUDA(cudaMalloc((void**)&p->d_q0t, PS_N * p->qpad * 4)); GB_CUDA(cudaMemset(p->d_q0t, 0, PS_N * p->qpad * 4));
   GB_CUDA(cudaMalloc((void**)&p->d_pht, PS_N * p->ppad * 4)); GB_CUDA(cudaMemset(p->d_pht, 0, PS_N * p->ppad * 4));
   const size_t RP = (size_t)p->rp;
   GB_CUDA(cudaMalloc((void**)&p->d_pacc, (p->prows + 8) * RP * 4));
   GB_CUDA(cudaMalloc((void**)&p->d_qacc, (p->qrows + 8) * RP * 4 * 2));   // second half: Q0 scratch for k3_q0
   GB_CUDA(cudaMalloc((void**)&p->d_ph, (p->prows + 8) * RP * 4));
+  GB_CUDA(cudaMemset(p->d_ph, 0, (p->prows + 8) * RP * 4));          // P^ = 0: no residual before the first exchange
   GB_CUDA(cudaMalloc((void**)&p->d_part1, (it1.size() + 1) * PS_BM * RP * 4));
   GB_CUDA(cudaMalloc((void**)&p->d_part2, (it2.size() + 1) * PS_BM * RP * 4));
-  if (warm_start) {
-    GB_CUDA(cudaMalloc((void**)&p->d_qprev, (p->qrows + 8) * RP * 4));
-    GB_CUDA(cudaMemset(p->d_qprev, 0, (p->qrows + 8) * RP * 4));
+  GB_CUDA(cudaMalloc((void**)&p->d_qprev, (p->qrows + 8) * RP * 4));
+  GB_CUDA(cudaMemset(p->d_qprev, 0, (p->qrows + 8) * RP * 4));
+  {
+    std::vector<int> simt;
+    p->simt_rows = p->simt_cblocks = 0;
+    for (int i = 0; i < nmat; ++i)
+      if (!p->h_mat[i].tc) { simt.push_back(i); p->simt_rows += p->h_mat[i].n; p->simt_cblocks += (p->h_mat[i].m + 31) / 32; }
+    p->nsimt = (int)simt.size();
+    GB_CUDA(cudaMalloc((void**)&p->d_simt, sizeof(int) * (simt.size() + 1)));
+    if (!simt.empty()) GB_CUDA(cudaMemcpy(p->d_simt, simt.data(), sizeof(int) * simt.size(), cudaMemcpyHostToDevice));
   }
   GB_CUDA(cudaMalloc((void**)&p->d_cnt1, (p->ntiles1 + p->ntiles2 + 64) * 4));
   p->d_cnt2 = p->d_cnt1 + p->ntiles1;
@@ -915,7 +1021,7 @@ static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, con
 extern "C" int gb_psgd_destroy(gb_psgd* p) {
   if (!p) return 0;
   cudaDeviceSynchronize();
-  cudaFree(p->d_mat); cudaFree(p->d_items1); cudaFree(p->d_items2); cudaFree(p->d_work); cudaFree(p->d_res);
+  cudaFree(p->d_mat); cudaFree(p->d_items1); cudaFree(p->d_items2); cudaFree(p->d_work); cudaFree(p->d_simt);
   cudaFree(p->d_q0t); cudaFree(p->d_pht); cudaFree(p->d_pacc); cudaFree(p->d_qacc); cudaFree(p->d_ph); cudaFree(p->d_cnt1);
   cudaFree(p->d_maps);
   cudaFree(p->d_bands);
@@ -940,32 +1046,58 @@ extern "C" int gb_psgd_set_step(gb_psgd* p, uint32_t s) {
   GB_CUDA(cudaMemcpy(&p->d_ctl->next_step, &s, 4, cudaMemcpyHostToDevice));
   return 0;
 }
-extern "C" int gb_psgd_residual(gb_psgd* p, void** ptr, size_t* bytes) { *ptr = p->d_res; *bytes = p->d_res ? (size_t)p->padded * 4 : 0; return 0; }
+// non-NULL when the plan keeps error-feedback state.  The residual itself is implicit (work - P^ Q^T, see the band
+// kernels): read it with gb_psgd_state_read, which materialises it into the caller's buffer.
+extern "C" int gb_psgd_residual(gb_psgd* p, void** ptr, size_t* bytes) {
+  *ptr = p->has_mem ? p->d_work : nullptr;
+  *bytes = p->has_mem ? (size_t)p->padded * 4 : 0;
+  return 0;
+}
 // debugging / tests: copy an internal buffer out.  what: 0 P accumulator, 1 Q accumulator, 2 Q0^T, 3 P^^T, 4 P^, 5 work
 extern "C" int gb_psgd_peek(gb_psgd* p, int what, float* d_dst, int64_t nfloats, void* stream) {
   const float* src = what == 0 ? p->d_pacc : what == 1 ? p->d_qacc : what == 2 ? p->d_q0t : what == 3 ? p->d_pht : what == 4 ? p->d_ph : p->d_work;
   GB_CUDA(cudaMemcpyAsync(d_dst, src, (size_t)nfloats * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return 0;
 }
+#define PS_DISPATCH(rp, CALL)                    \
+  do {                                           \
+    if ((rp) == 4) { constexpr int RP = 4; CALL; }        \
+    else if ((rp) == 8) { constexpr int RP = 8; CALL; }   \
+    else { constexpr int RP = 16; CALL; }                 \
+  } while (0)
+
 extern "C" int gb_psgd_state_read(gb_psgd* p, void* d_dst, void* stream) {
-  GB_CHECK(p->d_res, "this PowerSGD plan has no residual memory");
-  GB_CUDA(cudaMemcpyAsync(d_dst, p->d_res, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  GB_CHECK(p->has_mem, "this PowerSGD plan has no residual memory");
+  cudaStream_t st = (cudaStream_t)stream;
+  GB_CUDA(cudaMemsetAsync(d_dst, 0, (size_t)p->padded * 4, st));          // alignment gaps between the matrices
+  PS_DISPATCH(p->rp, (k3_resid<RP><<<p->nbands, PS_BAND_THREADS, 0, st>>>(p->d_bands, p->d_mat, p->d_ph, p->d_qprev, p->d_work, (float*)d_dst)));
+  GB_CUDA(cudaGetLastError());
+  return 0;
+}
+// makes the implicit residual explicit in `work` (work -= P^ Q^T, P^ = 0) so that Q may be replaced underneath it
+static int psgd_fold_residual(gb_psgd* p, cudaStream_t st) {
+  PS_DISPATCH(p->rp, (k3_resid<RP><<<p->nbands, PS_BAND_THREADS, 0, st>>>(p->d_bands, p->d_mat, p->d_ph, p->d_qprev, p->d_work, p->d_work)));
+  GB_CUDA(cudaGetLastError());
+  GB_CUDA(cudaMemsetAsync(p->d_ph, 0, (size_t)(p->prows + 8) * p->rp * 4, st));
   return 0;
 }
 extern "C" int gb_psgd_state_write(gb_psgd* p, const void* d_src, void* stream) {
-  GB_CHECK(p->d_res, "this PowerSGD plan has no residual memory");
-  GB_CUDA(cudaMemcpyAsync(p->d_res, d_src, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  GB_CHECK(p->has_mem, "this PowerSGD plan has no residual memory");
+  cudaStream_t st = (cudaStream_t)stream;
+  GB_CUDA(cudaMemcpyAsync(p->d_work, d_src, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, st));
+  GB_CUDA(cudaMemsetAsync(p->d_ph, 0, (size_t)(p->prows + 8) * p->rp * 4, st));      // residual = work - 0
   return 0;
 }
 // warm-start Q (state index 1 of the Python plan): copy out / in, [qrows + 8][rp] floats
 extern "C" int gb_psgd_qprev(gb_psgd* p, void** ptr, size_t* bytes) {
-  *ptr = p->d_qprev;
-  *bytes = p->d_qprev ? (size_t)(p->qrows + 8) * p->rp * 4 : 0;
+  *ptr = p->warm ? p->d_qprev : nullptr;
+  *bytes = p->warm ? (size_t)(p->qrows + 8) * p->rp * 4 : 0;
   return 0;
 }
 extern "C" int gb_psgd_qprev_copy(gb_psgd* p, void* d_buf, int to_plan, void* stream) {
-  GB_CHECK(p->d_qprev, "this PowerSGD plan has no warm-start memory");
+  GB_CHECK(p->warm, "this PowerSGD plan has no warm-start memory");
   const size_t bytes = (size_t)(p->qrows + 8) * p->rp * 4;
+  if (to_plan && p->has_mem && psgd_fold_residual(p, (cudaStream_t)stream)) return -1;   // the residual refers to the old Q
   GB_CUDA(cudaMemcpyAsync(to_plan ? (void*)p->d_qprev : d_buf, to_plan ? d_buf : (void*)p->d_qprev, bytes, cudaMemcpyDeviceToDevice,
                           (cudaStream_t)stream));
   return 0;
@@ -994,41 +1126,33 @@ static PsIn my_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t ep
   return s;
 }
 
-#define PS_DISPATCH(rp, CALL)                    \
-  do {                                           \
-    if ((rp) == 4) { constexpr int RP = 4; CALL; }        \
-    else if ((rp) == 8) { constexpr int RP = 8; CALL; }   \
-    else { constexpr int RP = 16; CALL; }                 \
-  } while (0)
-
-// phase 1: compensate, Q0, P_r = M Q0, push P tiles, release flags
+// phase 1: compensate + Q0 (one launch), P_r = M Q0 with the P tiles pushed from the epilogue; the last CTA of the
+// last launch releases the flags
 extern "C" int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   gb_comm* c = p->comm;
   GB_CHECK(((uintptr_t)d_grad & 15) == 0, "gradient buffer must be 16-byte aligned");
   ++p->epoch;
   gb_launch_tick(p->d_ctl, st);
-  const size_t psp = (size_t)c->world * p->slot_p, psq = (size_t)c->world * p->slot_q;
-  (void)psq;
-  k3_prep<<<148 * 4, GB_THREADS, 0, st>>>(p->padded, d_grad, p->d_res, p->d_work, p->has_mem, p->d_pacc,
-                                         p->prows * p->rp, p->d_qacc, p->qrows * p->rp, p->d_cnt1, p->ntiles1 + p->ntiles2, p->d_ctl);
-  LAUNCHED(p);
-  PS_DISPATCH(p->rp, (k3_q0<RP><<<p->nmat, 512, 0, st>>>(p->d_mat, p->d_qacc + (size_t)(p->qrows + 8) * RP, p->d_qprev, p->d_q0t,
-                                                       p->qpad, p->seed, p->d_ctl)));
+  const size_t psp = (size_t)c->world * p->slot_p;
+  PS_DISPATCH(p->rp, (k3_prep<RP><<<p->nmat + p->nbands, PS_BAND_THREADS, 0, st>>>(
+                         p->d_bands, p->d_mat, p->nmat, d_grad, p->d_work, p->d_ph, p->d_qprev, p->has_mem, p->warm,
+                         p->d_qacc + (size_t)(p->qrows + 8) * RP, p->d_q0t, p->qpad, p->seed, p->d_cnt1, p->ntiles1 + p->ntiles2,
+                         p->d_ctl)));
   LAUNCHED(p);
   const PsPeers ps = peer_slots(p, p->off_p, p->slot_p);
   if (p->nitems1) {
-    PS_DISPATCH(p->rp, (k3_gemm<1, RP><<<p->nitems1, 192, PS_SMEM, st>>>(p->d_items1, p->d_mat, p->d_maps, p->d_part1, p->d_cnt1, ps, p->d_ctl, psp)));
+    PS_DISPATCH(p->rp, (k3_gemm<1, RP><<<p->nitems1, 192, PS_SMEM, st>>>(p->d_items1, p->d_mat, p->d_maps, p->d_part1, p->d_cnt1, ps,
+                                                                        p->d_ctl, psp, p->d_done, gb_comm_peers(c), p->chan_p,
+                                                                        p->nsimt == 0)));
     LAUNCHED(p);
   }
-  int simt_rows = 0;
-  for (auto& m : p->h_mat) if (!m.tc) simt_rows += m.n;
-  if (simt_rows) {
-    PS_DISPATCH(p->rp, (k3_gemm1_simt<RP><<<(simt_rows * 32 + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, p->d_work, p->d_q0t, p->qpad, p->d_pacc)));
+  if (p->nsimt) {
+    PS_DISPATCH(p->rp, (k3_gemm1_simt<RP><<<(p->simt_rows * 32 + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(
+                           p->d_mat, p->d_simt, p->nsimt, p->d_work, p->d_q0t, p->qpad, ps, p->d_done, gb_comm_peers(c), p->chan_p,
+                           p->d_ctl, psp)));
     LAUNCHED(p);
   }
-  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 1, p->d_pacc, p->rp, ps, p->d_done, gb_comm_peers(c), p->chan_p, p->d_ctl, psp);
-  LAUNCHED(p);
   return 0;
 }
 
@@ -1051,28 +1175,28 @@ extern "C" int gb_psgd_mid(gb_psgd* p, void* stream) {
   LAUNCHED(p);
   const PsPeers qs = peer_slots(p, p->off_q, p->slot_q);
   if (p->nitems2) {
-    PS_DISPATCH(p->rp, (k3_gemm<2, RP><<<p->nitems2, 192, PS_SMEM, st>>>(p->d_items2, p->d_mat, p->d_maps, p->d_part2, p->d_cnt2, qs, p->d_ctl, psq)));
+    PS_DISPATCH(p->rp, (k3_gemm<2, RP><<<p->nitems2, 192, PS_SMEM, st>>>(p->d_items2, p->d_mat, p->d_maps, p->d_part2, p->d_cnt2, qs,
+                                                                        p->d_ctl, psq, p->d_done, gb_comm_peers(c), p->chan_q,
+                                                                        p->nsimt == 0)));
     LAUNCHED(p);
   }
-  int simt_cols = 0;
-  for (auto& m : p->h_mat) if (!m.tc) simt_cols += m.m;
-  if (simt_cols) {
-    PS_DISPATCH(p->rp, (k3_gemm2_simt<RP><<<(simt_cols + GB_THREADS - 1) / GB_THREADS, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, p->d_work, p->d_ph, p->d_qacc)));
+  if (p->nsimt) {
+    PS_DISPATCH(p->rp, (k3_gemm2_simt<RP><<<p->simt_cblocks, GB_THREADS, 0, st>>>(p->d_mat, p->d_simt, p->nsimt, p->d_work, p->d_ph, qs,
+                                                                                 p->d_done, gb_comm_peers(c), p->chan_q, p->d_ctl,
+                                                                                 psq)));
     LAUNCHED(p);
   }
-  k3_flag<<<64, GB_THREADS, 0, st>>>(p->d_mat, p->nmat, 2, p->d_qacc, p->rp, qs, p->d_done, gb_comm_peers(c), p->chan_q, p->d_ctl, psq);
-  LAUNCHED(p);
   return 0;
 }
 
-// phase 3: reduce Q, out = P^ Q^T, residual update
+// phase 3: reduce Q, out = P^ Q^T (the residual stays implicit: see the band kernels)
 extern "C" int gb_psgd_recv(gb_psgd* p, float* d_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   gb_comm* c = p->comm;
-  PS_DISPATCH(p->rp, (k3_final<RP><<<p->nbands, GB_THREADS, 0, st>>>(p->d_bands, p->d_mat, my_slots(p, p->off_q, p->slot_q),
-                                                                   1.0f / (float)c->world, p->d_ph, p->d_work, p->d_res, p->has_mem,
-                                                                   d_out, p->d_qprev, gb_comm_peers(c), p->chan_q, p->d_ctl,
-                                                                   (size_t)c->world * p->slot_q, c->status_dev, c->timeout_ns)));
+  PS_DISPATCH(p->rp, (k3_final<RP><<<p->nbands, PS_BAND_THREADS, 0, st>>>(p->d_bands, p->d_mat, my_slots(p, p->off_q, p->slot_q),
+                                                                         1.0f / (float)c->world, p->d_ph, d_out, p->d_qprev,
+                                                                         gb_comm_peers(c), p->chan_q, p->d_ctl,
+                                                                         (size_t)c->world * p->slot_q, c->status_dev, c->timeout_ns)));
   LAUNCHED(p);
   p->step++;
   return 0;
