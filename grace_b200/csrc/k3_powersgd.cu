@@ -52,7 +52,7 @@ struct PsMat {          // one matrix of the bucket (device copy)
   int32_t tc;           // 1: tcgen05 path, 0: CUDA-core fallback (TMA constraints not met)
 };
 
-struct PsBand { int32_t mat, i0; };   // one CTA of k3_final: 32 rows of one matrix
+struct PsBand { int32_t mat, i0, j0, j1; };   // one CTA of the band kernels: rows [i0, i0 + 32) x columns [j0, j1) of one matrix
 
 struct PsItem {         // one CTA of a grouped GEMM launch
   int32_t mat, tile, m0, k0, k1, nchunks, chunk;   // chunk: index of this K slice inside its tile (items of a tile are consecutive)
@@ -165,7 +165,7 @@ __device__ float g_dbg_dump[8192];
 #endif
 
 template <int MODE, int RP>
-__global__ void __launch_bounds__(192, 1) k3_gemm(const PsItem* __restrict__ items, const PsMat* __restrict__ mats,
+__global__ void __launch_bounds__(192, 2) k3_gemm(const PsItem* __restrict__ items, const PsMat* __restrict__ mats,
                                                   const CUtensorMap* __restrict__ maps, float* part, uint32_t* tile_cnt,
                                                   PsPeers peers, const StepCtl* ctl, size_t par_stride, uint32_t* done,
                                                   PeerPtrs flag_peers, int channel, int release) {
@@ -689,15 +689,15 @@ __device__ __forceinline__ void band_body(const PsMat& mt, const PsBand& b, cons
     for (int i = threadIdx.x; i < nrow * RP; i += blockDim.x) sp[i] = ph[(size_t)(mt.prow0 + b.i0) * RP + i];
   __syncthreads();
   const size_t band0 = mt.off + (size_t)b.i0 * mt.m;
-  const bool vec = (mt.m & 3) == 0;
-  const int ncg = vec ? mt.m >> 2 : mt.m;                       // column groups: 4 columns (or 1 on the scalar path)
+  const bool vec = (mt.m & 3) == 0;                             // (then j0 and j1 are multiples of 4 as well)
+  const int ncg = vec ? (b.j1 - b.j0) >> 2 : b.j1 - b.j0;       // column groups: 4 columns (or 1 on the scalar path)
   const int cgs = min(ncg, (int)blockDim.x), rl = (int)blockDim.x / cgs;
   const int my_cg = threadIdx.x % cgs, my_r = threadIdx.x / cgs;
   if (my_r >= rl) return;
   const bool keep = MODE == 1 && qkeep != nullptr && b.i0 == 0 && my_r == 0;
   if (vec) {
     for (int cg = my_cg; cg < ncg; cg += cgs) {
-      const int j = cg * 4;
+      const int j = b.j0 + cg * 4;
       float q[4][RP];
       if (need_pq) {
 #pragma unroll
@@ -757,7 +757,8 @@ __device__ __forceinline__ void band_body(const PsMat& mt, const PsBand& b, cons
       }
     }
   } else {
-    for (int j = my_cg; j < ncg; j += cgs) {
+    for (int jj = my_cg; jj < ncg; jj += cgs) {
+      const int j = b.j0 + jj;
       float q[RP];
 #pragma unroll
       for (int c = 0; c < RP; ++c) q[c] = 0.f;
@@ -874,7 +875,11 @@ static void build_items(const std::vector<PsMat>& mats, int mode, std::vector<Ps
   // aim for >= ~3 CTAs per SM overall; never split K finer than 8 pipeline stages
   int64_t total = 0;
   for (auto& m : mats) if (m.tc) total += (int64_t)m.n * m.m;
-  int64_t per_item = std::max<int64_t>((int64_t)PS_BM * PS_BK * 8, total / (148 * 3) + 1);
+  // two CTAs are resident per SM (2 x 110 KB of pipeline stages): one streams while the other is in its prologue or
+  // epilogue; four items per SM = two full waves
+  const char* ips = getenv("GB_PSGD_ITEMS_PER_SM");
+  const int items_per_sm = ips ? std::max(1, atoi(ips)) : 4;
+  int64_t per_item = std::max<int64_t>((int64_t)PS_BM * PS_BK * 8, total / (148 * items_per_sm) + 1);
   if (getenv("GB_PSGD_NOSPLIT")) per_item = int64_t(1) << 40;      // debugging: one K chunk per tile
   ntiles = 0;
   for (int mi = 0; mi < (int)mats.size(); ++mi) {
@@ -941,9 +946,21 @@ static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, con
   build_items(p->h_mat, 1, it1, p->ntiles1);
   build_items(p->h_mat, 2, it2, p->ntiles2);
   p->nitems1 = (int)it1.size(); p->nitems2 = (int)it2.size();
+  // band items: 32 rows x at most 2048 columns (one 4-column group per thread), largest first so that the tail of the
+  // launch is made of small CTAs (the matrices arrive in network order: the widest ones last)
   std::vector<PsBand> bands;
-  for (int i = 0; i < nmat; ++i)
-    for (int r0 = 0; r0 < p->h_mat[i].n; r0 += 32) bands.push_back(PsBand{i, r0});
+  for (int i = 0; i < nmat; ++i) {
+    const int m = p->h_mat[i].m;
+    const int nchunk = (m + 4 * PS_BAND_THREADS - 1) / (4 * PS_BAND_THREADS);
+    const int chunk = ((m + nchunk - 1) / nchunk + 3) / 4 * 4;
+    for (int r0 = 0; r0 < p->h_mat[i].n; r0 += 32)
+      for (int j0 = 0; j0 < m; j0 += chunk) bands.push_back(PsBand{i, r0, j0, std::min(m, j0 + chunk)});
+  }
+  std::stable_sort(bands.begin(), bands.end(), [&](const PsBand& a, const PsBand& b) {
+    const int64_t sa = (int64_t)std::min(32, p->h_mat[a.mat].n - a.i0) * (a.j1 - a.j0);
+    const int64_t sb = (int64_t)std::min(32, p->h_mat[b.mat].n - b.i0) * (b.j1 - b.j0);
+    return sa > sb;
+  });
 
   GB_CUDA(cudaMalloc((void**)&p->d_mat, sizeof(PsMat) * nmat));
   GB_CUDA(cudaMemcpy(p->d_mat, p->h_mat.data(), sizeof(PsMat) * nmat, cudaMemcpyHostToDevice));
