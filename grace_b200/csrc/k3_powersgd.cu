@@ -45,8 +45,10 @@
 #define PS_SMEM (PS_STAGES * (PS_A_BYTES + PS_B_BYTES) + 1024 + 256)
 
 struct PsMat {          // one matrix of the bucket (device copy)
-  int64_t off;          // element offset of M in the flat buffers
+  int64_t off;          // element offset of M in the flat gradient / output buffers (row pitch m)
+  int64_t woff;         // element offset of M in `work`, whose rows have a pitch of ldw floats
   int32_t n, m, r;      // rows, cols, effective rank
+  int32_t ldw;          // m rounded up to 4: every row of `work` starts on 16 bytes, so TMA can address any matrix
   int32_t prow0, qrow0; // first row of this matrix in the P / Q row spaces
   uint32_t hash;
   int32_t tc;           // 1: tcgen05 path, 0: CUDA-core fallback (TMA constraints not met)
@@ -68,7 +70,7 @@ struct gb_psgd {
   int* d_simt;              // indices of the matrices on the CUDA-core fallback
   int nsimt, simt_rows, simt_cblocks;
   uint32_t seed, step, epoch;
-  int64_t padded, prows, qrows;
+  int64_t padded, wpadded, prows, qrows;   // wpadded: floats of `work` (rows padded to 16 bytes)
   std::vector<PsMat> h_mat;
   std::vector<int64_t> h_off;
   PsMat* d_mat;
@@ -339,7 +341,7 @@ __global__ void __launch_bounds__(GB_THREADS) k3_gemm1_simt(const PsMat* __restr
     const PsMat mt = mats[simt[si]];
     if (gw >= base && gw < base + mt.n) {
       const int i = gw - base;
-      const float* rowp = work + mt.off + (size_t)i * mt.m;
+      const float* rowp = work + mt.woff + (size_t)i * mt.ldw;
       float s[RP];
 #pragma unroll
       for (int c = 0; c < RP; ++c) s[c] = 0.f;
@@ -381,7 +383,7 @@ __global__ void __launch_bounds__(GB_THREADS) k3_gemm2_simt(const PsMat* __restr
       if (j < mt.m) {
 #pragma unroll 4
         for (int i = slice; i < mt.n; i += 8) {
-          const float x = work[mt.off + (size_t)i * mt.m + j];
+          const float x = work[mt.woff + (size_t)i * mt.ldw + j];
           const float* pr = ph + (size_t)(mt.prow0 + i) * RP;
 #pragma unroll
           for (int c = 0; c < RP; ++c) s[c] += x * pr[c];
@@ -679,6 +681,8 @@ __device__ __forceinline__ float dot_r(const float* p, const float (&q)[RP]) {
 //   MODE 0 (prep)   work = grad [+ work - P^ Q^T]          Q from qkeep
 //   MODE 1 (final)  out  = P^ Q^T, qkeep = Q               Q = mean over the ranks' slots
 //   MODE 2 (resid)  out  = work - P^ Q^T                   Q from qkeep (state read-out)
+//   MODE 3 (fold)   work = work - P^ Q^T                   the residual made explicit in place
+// grad / out are flat (row pitch m); `work` is private to the plan and pads its rows to 16 bytes (PsMat::ldw).
 template <int RP, int MODE>
 __device__ __forceinline__ void band_body(const PsMat& mt, const PsBand& b, const float* __restrict__ ph, const float* qsrc,
                                           const PsIn& in, float inv_world, const float* __restrict__ grad, float* work,
@@ -688,7 +692,8 @@ __device__ __forceinline__ void band_body(const PsMat& mt, const PsBand& b, cons
   if (need_pq)
     for (int i = threadIdx.x; i < nrow * RP; i += blockDim.x) sp[i] = ph[(size_t)(mt.prow0 + b.i0) * RP + i];
   __syncthreads();
-  const size_t band0 = mt.off + (size_t)b.i0 * mt.m;
+  const size_t band0 = mt.off + (size_t)b.i0 * mt.m;            // in grad / out
+  const size_t wband0 = mt.woff + (size_t)b.i0 * mt.ldw;        // in work
   const bool vec = (mt.m & 3) == 0;                             // (then j0 and j1 are multiples of 4 as well)
   const int ncg = vec ? (b.j1 - b.j0) >> 2 : b.j1 - b.j0;       // column groups: 4 columns (or 1 on the scalar path)
   const int cgs = min(ncg, (int)blockDim.x), rl = (int)blockDim.x / cgs;
@@ -726,16 +731,16 @@ __device__ __forceinline__ void band_body(const PsMat& mt, const PsBand& b, cons
         for (int u = 0; u < U; ++u) {
           const int i = i0 + u * rl;
           if (i < nrow) {
-            const size_t e = band0 + (size_t)i * mt.m + j;
+            const size_t e = band0 + (size_t)i * mt.m + j, ew = wband0 + (size_t)i * mt.ldw + j;
             if (MODE == 0) g[u] = *reinterpret_cast<const float4*>(grad + e);
-            if (MODE == 2 || (MODE == 0 && use_prev)) w[u] = *reinterpret_cast<const float4*>(work + e);
+            if (MODE >= 2 || (MODE == 0 && use_prev)) w[u] = *reinterpret_cast<const float4*>(work + ew);
           }
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const int i = i0 + u * rl;
           if (i < nrow) {
-            const size_t e = band0 + (size_t)i * mt.m + j;
+            const size_t e = band0 + (size_t)i * mt.m + j, ew = wband0 + (size_t)i * mt.ldw + j;
             float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
             if (need_pq) {
               const float* pr = sp + i * RP;
@@ -745,12 +750,14 @@ __device__ __forceinline__ void band_body(const PsMat& mt, const PsBand& b, cons
               *reinterpret_cast<float4*>(out + e) = o;
             } else if (MODE == 2) {
               *reinterpret_cast<float4*>(out + e) = make_float4(w[u].x - o.x, w[u].y - o.y, w[u].z - o.z, w[u].w - o.w);
+            } else if (MODE == 3) {
+              *reinterpret_cast<float4*>(work + ew) = make_float4(w[u].x - o.x, w[u].y - o.y, w[u].z - o.z, w[u].w - o.w);
             } else if (use_prev) {
-              *reinterpret_cast<float4*>(work + e) =
+              *reinterpret_cast<float4*>(work + ew) =
                   make_float4(__fadd_rn(g[u].x, w[u].x - o.x), __fadd_rn(g[u].y, w[u].y - o.y), __fadd_rn(g[u].z, w[u].z - o.z),
                               __fadd_rn(g[u].w, w[u].w - o.w));
             } else {
-              *reinterpret_cast<float4*>(work + e) = g[u];
+              *reinterpret_cast<float4*>(work + ew) = g[u];
             }
           }
         }
@@ -775,12 +782,13 @@ __device__ __forceinline__ void band_body(const PsMat& mt, const PsBand& b, cons
         }
       }
       for (int i = my_r; i < nrow; i += rl) {
-        const size_t e = band0 + (size_t)i * mt.m + j;
+        const size_t e = band0 + (size_t)i * mt.m + j, ew = wband0 + (size_t)i * mt.ldw + j;
         const float o = need_pq ? dot_r<RP>(sp + i * RP, q) : 0.f;
         if (MODE == 1) out[e] = o;
-        else if (MODE == 2) out[e] = work[e] - o;
-        else if (use_prev) work[e] = __fadd_rn(grad[e], work[e] - o);
-        else work[e] = grad[e];
+        else if (MODE == 2) out[e] = work[ew] - o;
+        else if (MODE == 3) work[ew] = work[ew] - o;
+        else if (use_prev) work[ew] = __fadd_rn(grad[e], work[ew] - o);
+        else work[ew] = grad[e];
       }
     }
   }
@@ -824,8 +832,8 @@ __global__ void __launch_bounds__(PS_BAND_THREADS) k3_final(const PsBand* __rest
   band_body<RP, 1>(mt, b, ph, nullptr, in, inv_world, nullptr, nullptr, out, qkeep, true, sp);
 }
 
-// state read-out: dst = work - P^ Q^T, the residual a PowerSGDMemory would hold after the last exchange
-template <int RP>
+// state read-out: dst = work - P^ Q^T, the residual a PowerSGDMemory would hold after the last exchange (FOLD: in place)
+template <int RP, int FOLD>
 __global__ void __launch_bounds__(PS_BAND_THREADS) k3_resid(const PsBand* __restrict__ bands, const PsMat* __restrict__ mats,
                                                             const float* __restrict__ ph, const float* __restrict__ qkeep,
                                                             float* work, float* dst) {
@@ -833,7 +841,17 @@ __global__ void __launch_bounds__(PS_BAND_THREADS) k3_resid(const PsBand* __rest
   const PsBand b = bands[blockIdx.x];
   const PsMat mt = mats[b.mat];
   PsIn none; none.n = 0;
-  band_body<RP, 2>(mt, b, ph, qkeep, none, 1.f, nullptr, work, dst, nullptr, true, sp);
+  band_body<RP, FOLD ? 3 : 2>(mt, b, ph, qkeep, none, 1.f, nullptr, work, dst, nullptr, true, sp);
+}
+
+// state write: work = src (flat layout -> padded rows)
+__global__ void __launch_bounds__(PS_BAND_THREADS) k3_load(const PsBand* __restrict__ bands, const PsMat* __restrict__ mats,
+                                                           const float* __restrict__ src, float* work) {
+  __shared__ __align__(16) float sp[32 * 4];
+  const PsBand b = bands[blockIdx.x];
+  const PsMat mt = mats[b.mat];
+  PsIn none; none.n = 0;
+  band_body<4, 0>(mt, b, nullptr, nullptr, none, 1.f, src, work, nullptr, nullptr, false, sp);
 }
 
 // ---------------------------------------------------------------- host side
@@ -926,21 +944,23 @@ static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, con
   p->d_qprev = nullptr; p->d_simt = nullptr; p->warm = warm_start ? 1 : 0;
   p->comm = c; p->nmat = nmat; p->rank_r = rank_r; p->has_mem = has_memory; p->use_tc = use_tcgen05;
   p->seed = seed; p->step = 0; p->epoch = 0; p->launches = 0;
-  int64_t off = 0, prow = 0, qrow = 0;
+  int64_t off = 0, woff = 0, prow = 0, qrow = 0;
   for (int i = 0; i < nmat; ++i) {
     GB_CHECK(rows[i] >= 1 && cols[i] >= 1 && rows[i] * cols[i] < (int64_t(1) << 31), "matrix %d has a bad shape", i);
     PsMat m;
     m.off = off; m.n = (int)rows[i]; m.m = (int)cols[i];
+    m.ldw = (m.m + 3) / 4 * 4; m.woff = woff;
     m.r = (int)std::min<int64_t>(rank_r, std::min(rows[i], cols[i]));
     m.prow0 = (int)prow; m.qrow0 = (int)qrow; m.hash = name_hash[i];
-    m.tc = use_tcgen05 && (m.m % 4 == 0) && m.n >= 8 && m.m >= 32;
+    m.tc = use_tcgen05 && m.n >= 8 && m.m >= 32;      // smaller than a pipeline stage: CUDA-core fallback
     p->h_mat.push_back(m);
     p->h_off.push_back(off);
     off += (rows[i] * cols[i] + GB_ALIGN - 1) / GB_ALIGN * GB_ALIGN;
+    woff += (rows[i] * m.ldw + GB_ALIGN - 1) / GB_ALIGN * GB_ALIGN;
     prow += (rows[i] + 3) / 4 * 4;        // keep every matrix's row window 16-byte aligned in the transposed buffers
     qrow += (cols[i] + 3) / 4 * 4;
   }
-  p->padded = off; p->prows = prow; p->qrows = qrow;
+  p->padded = off; p->wpadded = woff; p->prows = prow; p->qrows = qrow;
   p->ppad = (prow + 31) / 32 * 32; p->qpad = (qrow + 31) / 32 * 32;
   std::vector<PsItem> it1, it2;
   build_items(p->h_mat, 1, it1, p->ntiles1);
@@ -968,8 +988,8 @@ static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, con
   GB_CUDA(cudaMalloc((void**)&p->d_items2, sizeof(PsItem) * (it2.size() + 1)));
   if (!it1.empty()) GB_CUDA(cudaMemcpy(p->d_items1, it1.data(), sizeof(PsItem) * it1.size(), cudaMemcpyHostToDevice));
   if (!it2.empty()) GB_CUDA(cudaMemcpy(p->d_items2, it2.data(), sizeof(PsItem) * it2.size(), cudaMemcpyHostToDevice));
-  GB_CUDA(cudaMalloc((void**)&p->d_work, p->padded * 4));
-  GB_CUDA(cudaMemset(p->d_work, 0, p->padded * 4));
+  GB_CUDA(cudaMalloc((void**)&p->d_work, p->wpadded * 4));
+  GB_CUDA(cudaMemset(p->d_work, 0, p->wpadded * 4));
   GB_CUDA(cudaMalloc((void**)&p->d_q0t, PS_N * p->qpad * 4)); GB_CUDA(cudaMemset(p->d_q0t, 0, PS_N * p->qpad * 4));
   GB_CUDA(cudaMalloc((void**)&p->d_pht, PS_N * p->ppad * 4)); GB_CUDA(cudaMemset(p->d_pht, 0, PS_N * p->ppad * 4));
   const size_t RP = (size_t)p->rp;
@@ -1004,10 +1024,10 @@ static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, con
   for (int i = 0; i < nmat; ++i) {
     const PsMat& m = p->h_mat[i];
     if (!m.tc) continue;
-    const float* M = p->d_work + m.off;
-    if (make_map(&maps[i * 4 + 0], M, m.m, m.n, m.m, PS_BK, PS_BM)) return -1;
+    const float* M = p->d_work + m.woff;
+    if (make_map(&maps[i * 4 + 0], M, m.m, m.n, m.ldw, PS_BK, PS_BM)) return -1;
     if (make_map(&maps[i * 4 + 1], p->d_q0t + m.qrow0, m.m, PS_N, p->qpad, PS_BK, PS_N)) return -1;
-    if (make_map(&maps[i * 4 + 2], M, m.m, m.n, m.m, 32, PS_BK,
+    if (make_map(&maps[i * 4 + 2], M, m.m, m.n, m.ldw, 32, PS_BK,
                  getenv("GB_PSGD_SWZ128") ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return -1;
     if (make_map(&maps[i * 4 + 3], p->d_pht + m.prow0, m.n, PS_N, p->ppad, PS_BK, PS_N)) return -1;
   }
@@ -1087,13 +1107,13 @@ extern "C" int gb_psgd_state_read(gb_psgd* p, void* d_dst, void* stream) {
   GB_CHECK(p->has_mem, "this PowerSGD plan has no residual memory");
   cudaStream_t st = (cudaStream_t)stream;
   GB_CUDA(cudaMemsetAsync(d_dst, 0, (size_t)p->padded * 4, st));          // alignment gaps between the matrices
-  PS_DISPATCH(p->rp, (k3_resid<RP><<<p->nbands, PS_BAND_THREADS, 0, st>>>(p->d_bands, p->d_mat, p->d_ph, p->d_qprev, p->d_work, (float*)d_dst)));
+  PS_DISPATCH(p->rp, (k3_resid<RP, 0><<<p->nbands, PS_BAND_THREADS, 0, st>>>(p->d_bands, p->d_mat, p->d_ph, p->d_qprev, p->d_work, (float*)d_dst)));
   GB_CUDA(cudaGetLastError());
   return 0;
 }
 // makes the implicit residual explicit in `work` (work -= P^ Q^T, P^ = 0) so that Q may be replaced underneath it
 static int psgd_fold_residual(gb_psgd* p, cudaStream_t st) {
-  PS_DISPATCH(p->rp, (k3_resid<RP><<<p->nbands, PS_BAND_THREADS, 0, st>>>(p->d_bands, p->d_mat, p->d_ph, p->d_qprev, p->d_work, p->d_work)));
+  PS_DISPATCH(p->rp, (k3_resid<RP, 1><<<p->nbands, PS_BAND_THREADS, 0, st>>>(p->d_bands, p->d_mat, p->d_ph, p->d_qprev, p->d_work, nullptr)));
   GB_CUDA(cudaGetLastError());
   GB_CUDA(cudaMemsetAsync(p->d_ph, 0, (size_t)(p->prows + 8) * p->rp * 4, st));
   return 0;
@@ -1101,7 +1121,8 @@ static int psgd_fold_residual(gb_psgd* p, cudaStream_t st) {
 extern "C" int gb_psgd_state_write(gb_psgd* p, const void* d_src, void* stream) {
   GB_CHECK(p->has_mem, "this PowerSGD plan has no residual memory");
   cudaStream_t st = (cudaStream_t)stream;
-  GB_CUDA(cudaMemcpyAsync(p->d_work, d_src, (size_t)p->padded * 4, cudaMemcpyDeviceToDevice, st));
+  k3_load<<<p->nbands, PS_BAND_THREADS, 0, st>>>(p->d_bands, p->d_mat, (const float*)d_src, p->d_work);
+  GB_CUDA(cudaGetLastError());
   GB_CUDA(cudaMemsetAsync(p->d_ph, 0, (size_t)(p->prows + 8) * p->rp * 4, st));      // residual = work - 0
   return 0;
 }
