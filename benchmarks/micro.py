@@ -268,8 +268,9 @@ def main():
                 ms = float(t)
             eng.check_status()
             n_el = sum(r * c for r, c in shapes)
-            # M is read by prep (+residual r/w), GEMM 1, GEMM 2 and the final pass (+ out and residual writes)
-            hbm_bytes = n_el * 4 * 8
+            # prep reads grad and M and writes M (the residual is implicit), GEMM 1 and GEMM 2 read M, the final pass
+            # writes the output: 6 passes over the bucket (8 before the residual buffer was dropped)
+            hbm_bytes = n_el * 4 * 6
             roof = max(hbm_bytes / (hbm * 1e9) * 1e3, plan.wire_bytes * max(world - 1, 0) / (nvlink * 1e9) * 1e3)
             n0 = plan.launches(); plan.send(grad); plan.mid(); plan.recv(out); torch.cuda.synchronize()
             rows.append(dict(codec="powersgd-r4" + ("-tcgen05" if use_tc else "-simt"), memory="powersgd", world=world,
