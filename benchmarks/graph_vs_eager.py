@@ -168,6 +168,9 @@ def main():
                                   for d, n, ce, te, cg, tg in diff[:12]]
     out["faster_in_graph_top"] = [dict(name=n, eager_count=ce, eager_ms=te, graph_count=cg, graph_ms=tg, delta_ms=d / 1e3)
                                   for d, n, ce, te, cg, tg in diff[-6:]]
+    for mode, names in (("eager", ne), ("graph", ng)):
+        top = sorted(names.items(), key=lambda kv: -kv[1][1])[:18]
+        out["top_kernels_" + mode] = [dict(name=k[:110], count=c, ms=t / 1e3) for k, (c, t) in top]
     text = json.dumps(out, indent=1)
     print(text)
     if a.out:
