@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* wo
 
 // NW: compile-time bound of the number of ranks (1, 2, 4, 8): keeps the per-rank prefetch registers to what is needed
 template <bool EXTRAS, int NW>
-__global__ void __launch_bounds__(GB_THREADS) k1_merge(SegTable t, SparseIn in, float* out, float divisor, PeerPtrs peers,
+__global__ void __launch_bounds__(GB_THREADS, 5) k1_merge(SegTable t, SparseIn in, float* out, float divisor, PeerPtrs peers,
                                                        int channel, const StepCtl* ctl, size_t par_stride, uint32_t* status,
                                                        uint64_t timeout_ns, int wait) {
   __shared__ __align__(16) float acc[GB_TILE];
@@ -784,7 +784,9 @@ int k1_recv(gb_plan* p, float* d_out, cudaStream_t st) {
     LAUNCHED(p);
     return 0;
   }
-#define MERGE(EX, NW) k1_merge<EX, NW><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns, 1)
+  // 48 registers, 16.6 KB of shared memory: five CTAs are resident per SM; the tile loop is persistent
+  const int mgrid = p->ntiles < 148 * 5 ? p->ntiles : 148 * 5;
+#define MERGE(EX, NW) k1_merge<EX, NW><<<mgrid, GB_THREADS, 0, st>>>(p->tab, in, d_out, divisor, peers, p->channel, p->d_ctl, p->par_stride, c->status_dev, c->timeout_ns, 1)
   const bool ex = p->prm.codec == GB_CODEC_TOPK;
   if (c->world == 1) { if (ex) MERGE(true, 1); else MERGE(false, 1); }
   else if (c->world == 2) { if (ex) MERGE(true, 2); else MERGE(false, 2); }
