@@ -21,7 +21,8 @@ def test_every_builtin_codec_maps_to_a_native_codec_or_is_declared_generic():
     for comp, name in native.items():
         p = codec_params(comp, M.NoneMemory())
         assert p is not None and p.codec == CODEC[name], name
-    for comp in (C.SketchCompressor(1000), C.INCEPTIONNCompressor(error_bound=1e300), C.PowerSGDCompressor()):
+    assert codec_params(C.SketchCompressor(1000), M.NoneMemory()).quantum_num == 1000      # 16-bit bins: native up to 1023
+    for comp in (C.SketchCompressor(2000), C.INCEPTIONNCompressor(error_bound=1e300), C.PowerSGDCompressor()):
         assert codec_params(comp, M.NoneMemory()) is None
 
 
