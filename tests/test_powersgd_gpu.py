@@ -156,3 +156,50 @@ def test_powersgd_is_bit_reproducible():
         for ra, rb in zip(sa, sb):
             for x, y in zip(ra, rb):
                 assert torch.equal(x, y)
+
+
+@pytest.mark.parametrize("warm", [False, True])
+def test_implicit_residual_reads_out_and_survives_a_checkpoint(warm):
+    """The plan stores no residual: get_state(0) materialises M - P^ Q^T (memory/powersgd.py:24-37), set_state loads it
+    back.  A plan restored from another plan's state after two exchanges must produce the same third exchange, bit for
+    bit -- including the 64 x 147 matrix whose rows are padded inside the plan and, with a warm start, the kept Q."""
+    from grace_b200.parallel.engine import Engine, PowerSGDPlan
+    grads = make(1, 3, lowrank=True)
+    want, want_res = oracle(1, 4, grads[:2], True, warm=warm)
+
+    def flat(plan, ts):
+        buf = torch.zeros(plan.padded, device="cuda")
+        for off, g in zip(plan.offsets, ts):
+            buf[off:off + g.numel()] = g.reshape(-1)
+        return buf
+
+    def exchange(plan, ts):
+        out = torch.full((plan.padded,), float("nan"), device="cuda")
+        plan.send(flat(plan, ts)); plan.mid(); plan.recv(out)
+        torch.cuda.synchronize()
+        return out
+
+    (e1,) = Engine.local(1)
+    (e2,) = Engine.local(1)
+    try:
+        a = PowerSGDPlan(e1, SHAPES, NAMES, 4, SEED, True, False, warm)
+        b = PowerSGDPlan(e2, SHAPES, NAMES, 4, SEED, True, False, warm)
+        assert float(a.get_state(0).abs().max()) == 0.0                  # nothing exchanged yet
+        for s in range(2):
+            exchange(a, grads[s][0])
+        res = a.get_state(0)
+        for off, (n, m), w in zip(a.offsets, SHAPES, want_res[0]):
+            got = res[off:off + n * m].view(n, m)
+            assert float((got - w).norm() / (w.norm() + 1e-12)) < 2e-4, (n, m)
+        assert torch.equal(res, a.get_state(0))                          # reading the state does not disturb it
+        b.set_state(0, res)
+        if warm:
+            b.set_state(1, a.get_state(1))
+        b.step = a.step
+        oa, ob = exchange(a, grads[2][0]), exchange(b, grads[2][0])
+        for off, (n, m) in zip(a.offsets, SHAPES):
+            assert torch.equal(oa[off:off + n * m], ob[off:off + n * m]), (n, m)
+        assert torch.equal(a.get_state(0), b.get_state(0))
+    finally:
+        e1.destroy()
+        e2.destroy()
