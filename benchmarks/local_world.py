@@ -34,8 +34,9 @@ def main():
         engines = Engine.local(a.world, arena_bytes=(1 << 30))
         prm = CodecParams()
         prm.codec = CODEC[codec]
-        prm.memory = MEMORY["residual" if codec in ("topk", "natural") else "none"]
+        prm.memory = MEMORY["dgc" if codec == "dgc" else "none" if codec in ("qsgd", "signsgd", "u8bit", "none", "fp16") else "residual"]
         prm.ratio, prm.beta, prm.gamma, prm.quantum_num, prm.seed, prm.average, prm.capacity = a.ratio, 1.0, 1.0, 64, 1234, 1, 1.0
+        prm.threshold, prm.momentum, prm.lr = 2.5, 0.9, 0.1           # threshold: ~1.2 % of N(0,1) gradients pass
         plans = [e.plan(sizes, names, prm) for e in engines]
         grads = [torch.randn(plans[0].padded, device="cuda") for _ in range(a.world)]
         out = torch.empty(plans[0].padded, device="cuda")

@@ -332,21 +332,81 @@ __device__ __forceinline__ void aq_adjust_one(uint32_t* q, int count, double rat
   q[0] = __float_as_uint(thr);
 }
 
+// One round of the threshold adjustment (FINAL = false) or the final selection pass (FINAL = true: per-tile counts and
+// sums of the selected values).  Adjustment rounds: round 0 counts every tile; the CTA that finishes last applies the
+// rule to every (tensor, sign) and lists the tensors with an open sign (OpenDir); later rounds walk only those
+// tensors' tiles and return at once when none is open (first version: 21 launches that each walked every tile,
+// 14-24 us apiece; one persistent kernel with a grid barrier measured slower than the launches, see k1_dgc_count).
+#define AQ_PREF_CACHE 1024
 template <bool FINAL>
 __global__ void __launch_bounds__(GB_THREADS) aq_select(SegTable t, const float* __restrict__ work, uint32_t* sel, double* tsum,
                                                         int32_t* tsel, const int32_t* __restrict__ segcnt, double ratio,
-                                                        uint32_t* done) {
+                                                        uint32_t* done, uint32_t* dir_scratch, int round) {
   __shared__ double shd[GB_THREADS / 32];
   __shared__ int shc[2];
   __shared__ int s_last;
-  for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
+  __shared__ int s_pref[FINAL ? 1 : AQ_PREF_CACHE];
+  const OpenDir dir = open_dir(dir_scratch, t.nseg);
+  auto do_tile = [&](int tile) {
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
     const uint32_t* q0 = sel + (seg * 2) * 4;
     const uint32_t* q1 = q0 + 4;
     const bool d0 = q0[1] != 0, d1 = q1[1] != 0;
-    if (!FINAL && d0 && d1) continue;
+    if (!FINAL && d0 && d1) return;
+    if (!FINAL && round == 0 && t.seg_tile0[seg + 1] - t.seg_tile0[seg] == 1) {
+      // A tensor of one tile belongs to this CTA alone: all rounds of both signs run here on the values in registers
+      // (these small tensors are the ones that keep adjusting; a global round costs ~12 us however little it counts)
+      constexpr int NJ = GB_TILE / (GB_THREADS * 4);
+      float vals[NJ * 4];
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (e0 < len) v = ld4(work + base, e0, len);
+        vals[j * 4] = v.x; vals[j * 4 + 1] = v.y; vals[j * 4 + 2] = v.z; vals[j * 4 + 3] = v.w;
+      }
+      uint32_t qa[4] = {q0[0], q0[1], q0[2], q0[3]}, qb[4] = {q1[0], q1[1], q1[2], q1[3]};
+      for (int it = 0; it <= 20 && !(qa[1] && qb[1]); ++it) {
+        const float ta = __uint_as_float(qa[0]), tb = __uint_as_float(qb[0]);
+        const bool ga = qa[3] != 0, gb = qb[3] != 0, da = qa[1] != 0, db = qb[1] != 0;
+        int c0 = 0, c1 = 0;
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) {
+          const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (e0 + q >= len) continue;
+            const float x = vals[j * 4 + q];
+            const float mp = x > 0.f ? x : 0.f;
+            const float mn = x < 0.f ? -x : 0.f;
+            c0 += !da && (ga ? mp >= ta : mp > ta);
+            c1 += !db && (gb ? mn >= tb : mn > tb);
+          }
+        }
+        c0 = warp_sum_i(c0);
+        c1 = warp_sum_i(c1);
+        if (threadIdx.x < 2) shc[threadIdx.x] = 0;
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) {
+          if (c0) atomicAdd(&shc[0], c0);
+          if (c1) atomicAdd(&shc[1], c1);
+        }
+        __syncthreads();
+        qa[2] += (uint32_t)shc[0];
+        qb[2] += (uint32_t)shc[1];
+        __syncthreads();
+        aq_adjust_one(qa, segcnt[seg * 2], ratio);
+        aq_adjust_one(qb, segcnt[seg * 2 + 1], ratio);
+      }
+      if (threadIdx.x == 0) {
+        uint32_t* w0 = sel + (seg * 2) * 4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { w0[i] = qa[i]; w0[4 + i] = qb[i]; }
+      }
+      return;
+    }
     const float thr0 = __uint_as_float(q0[0]), thr1 = __uint_as_float(q1[0]);
     const bool ge0 = q0[3] != 0, ge1 = q1[3] != 0;
     if (threadIdx.x < 2) shc[threadIdx.x] = 0;
@@ -391,16 +451,33 @@ __global__ void __launch_bounds__(GB_THREADS) aq_select(SegTable t, const float*
       else if (c) atomicAdd(&sel[(seg * 2 + threadIdx.x) * 4 + 2], (uint32_t)c);
     }
     __syncthreads();
+  };
+  if (FINAL || round == 0) {
+    for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) do_tile(tile);
+  } else {
+    const int nopen = __ldcg(dir.hdr), total = __ldcg(dir.hdr + 1);
+    if (nopen == 0) return;                            // every threshold is final: nothing left to do in this round
+    const int cached = min(nopen, AQ_PREF_CACHE);
+    for (int i = threadIdx.x; i < cached; i += GB_THREADS) s_pref[i] = __ldcg(dir.pref + i);
+    __syncthreads();
+    for (int vt = blockIdx.x; vt < total; vt += gridDim.x) do_tile(open_dir_tile(t, dir, s_pref, cached, nopen, vt));
   }
   if (!FINAL) {
-    // the CTA that finishes last applies the refinement rule to every (tensor, sign): one launch per iteration
+    // the CTA that finishes last applies the refinement rule to every (tensor, sign) and rebuilds the directory
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) s_last = atomicAdd(done, 1u) == gridDim.x - 1;
     __syncthreads();
     if (s_last) {
       __threadfence();
-      for (int i = threadIdx.x; i < t.nseg * 2; i += GB_THREADS) aq_adjust_one(sel + i * 4, segcnt[i], ratio);
+      for (int i = threadIdx.x; i < t.nseg * 2; i += GB_THREADS) {
+        const uint4 qv = __ldcg(reinterpret_cast<const uint4*>(sel + i * 4));
+        uint32_t q[4] = {qv.x, qv.y, qv.z, qv.w};
+        aq_adjust_one(q, segcnt[i], ratio);
+        __stcg(reinterpret_cast<uint4*>(sel + i * 4), make_uint4(q[0], q[1], q[2], q[3]));
+      }
+      __syncthreads();
+      open_dir_build(t, dir, [&](int seg) { return __ldcg(sel + (seg * 2) * 4 + 1) == 0u || __ldcg(sel + (seg * 2 + 1) * 4 + 1) == 0u; });
       if (threadIdx.x == 0) *done = 0;
     }
   }
@@ -666,10 +743,10 @@ int aq_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   AQ_LAUNCHED(p);
   uint32_t* adj_done = p->d_done + 4;
   for (int it = 0; it <= 20; ++it) {
-    aq_select<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel, b->segcnt, p->prm.ratio, adj_done);
+    aq_select<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel, b->segcnt, p->prm.ratio, adj_done, p->d_hist, it);
     AQ_LAUNCHED(p);
   }
-  aq_select<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel, b->segcnt, p->prm.ratio, adj_done);
+  aq_select<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel, b->segcnt, p->prm.ratio, adj_done, p->d_hist, 0);
   AQ_LAUNCHED(p);
   aq_mean<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, b->tsum, b->tsel, b->means, out, ctl, p->par_stride); AQ_LAUNCHED(p);
   uint32_t* cursor = p->d_done + 2;

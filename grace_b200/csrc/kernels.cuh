@@ -67,6 +67,67 @@ __device__ __forceinline__ void release_flags_last_block(uint32_t* done, PeerPtr
   }
 }
 
+// Directory of the tiles that still have work in a multi-round refinement (DGC / AdaQ thresholds): the CTA that
+// finishes a round last lists the open tensors with a running tile count; the next round's launch walks
+// 0 .. #open tiles  instead of every tile of the bucket and returns at once when nothing is open.  Lives in global
+// scratch (4 + 2 nseg ints); L2 accesses (__ldcg / __stcg) so the scheme also holds inside one persistent kernel.
+struct OpenDir { int* hdr; int* seg; int* pref; };      // hdr[0] = open tensors, hdr[1] = their tiles
+__device__ __forceinline__ OpenDir open_dir(uint32_t* scratch, int nseg) {
+  OpenDir d;
+  d.hdr = reinterpret_cast<int*>(scratch);
+  d.seg = d.hdr + 4;
+  d.pref = d.seg + nseg;
+  return d;
+}
+template <typename F>
+__device__ __forceinline__ void open_dir_build(const SegTable& t, const OpenDir& d, F is_open) {      // whole CTA
+  __shared__ unsigned long long s_w[GB_THREADS / 32];
+  __shared__ unsigned long long s_base;
+  constexpr unsigned long long LOW = (1ull << 40) - 1ull;
+  if (threadIdx.x == 0) s_base = 0ull;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int b0 = 0; b0 < t.nseg; b0 += GB_THREADS) {
+    const int seg = b0 + (int)threadIdx.x;
+    const bool open = seg < t.nseg && is_open(seg);
+    const unsigned long long val = open ? ((1ull << 40) | (unsigned long long)(t.seg_tile0[seg + 1] - t.seg_tile0[seg])) : 0ull;
+    unsigned long long inc = val;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned long long nb = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += nb;
+    }
+    if (lane == 31) s_w[wid] = inc;
+    __syncthreads();
+    unsigned long long wbase = s_base;
+    for (int w = 0; w < wid; ++w) wbase += s_w[w];
+    const unsigned long long ex = wbase + inc - val;
+    if (open) {
+      const int k = (int)(ex >> 40);
+      __stcg(d.seg + k, seg);
+      __stcg(d.pref + k, (int)(ex & LOW));
+    }
+    __syncthreads();
+    if (threadIdx.x == GB_THREADS - 1) s_base = wbase + inc;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    __stcg(d.hdr, (int)(s_base >> 40));
+    __stcg(d.hdr + 1, (int)(s_base & LOW));
+  }
+}
+// the vt-th open tile; s_pref caches the first `cached` running tile counts in shared memory
+__device__ __forceinline__ int open_dir_tile(const SegTable& t, const OpenDir& d, const int* s_pref, int cached, int nopen, int vt) {
+  int lo = 0, hi = nopen;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    const int pm = mid < cached ? s_pref[mid] : __ldcg(d.pref + mid);
+    if (pm <= vt) lo = mid; else hi = mid;
+  }
+  const int pl = lo < cached ? s_pref[lo] : __ldcg(d.pref + lo);
+  return t.seg_tile0[__ldcg(d.seg + lo)] + vt - pl;
+}
+
 // All threads of the CTA return once every rank's flag for `epoch` has arrived.
 __device__ __forceinline__ void wait_all_ranks(PeerPtrs peers, int channel, uint32_t epoch, uint32_t* status,
                                                uint64_t timeout_ns) {
