@@ -413,11 +413,14 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit(SegTable t, float* work, f
 }
 
 // Unordered, single-pass compaction (the common case: no ambiguity among equal magnitudes).
-// Per tile: ballot-compact the picked (value, index) pairs into shared memory, claim a range of the
-// payload with one atomicAdd (per-segment cursor for TopK, one global cursor for the variable-size
-// codecs), then copy the staged pairs to every peer with coalesced stores.  The receiver only needs
-// the per-tile {begin, count} header, so neither the order of tiles in the payload nor the order
-// inside a tile matters for the (deterministic) dense result.
+// Per tile: ballot-compact the picked (value, index) pairs into shared memory; a range of the payload is claimed with
+// one atomicAdd (per-segment cursor for TopK, one global cursor for the variable-size codecs) and the staged pairs go
+// to every peer with coalesced stores.  The receiver only needs the per-tile {begin, count} header, so neither the
+// order of tiles in the payload nor the order inside a tile matters for the (deterministic) dense result.
+// With the global cursor a CTA keeps staging tile after tile and claims once per BATCH (when the 4096-entry staging
+// buffer would overflow, or at its last tile): 25 000 tiles claiming one address one by one were the bound of the
+// first version -- same-address atomics serialise in L2, 105 us for the 102 MB DGC bucket whatever else overlapped.
+#define EF_BATCH 32
 template <bool ZERO>
 __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* work, float* work2, uint32_t* sel, uint32_t fixed_thr,
                                                            int use_fixed, int per_segment, uint32_t* cursor, SparseOut out,
@@ -428,17 +431,49 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* wo
   if (epoch & 1) shift(out, par_stride);
   __shared__ int32_t sidx[GB_TILE];
   __shared__ int scount, sbegin;
-  const int lane = threadIdx.x & 31;
+  __shared__ int b_tile[EF_BATCH], b_off[EF_BATCH], b_cnt[EF_BATCH], b_n;   // tiles staged in the current batch
+  __shared__ int s_warp[GB_THREADS / 32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) { scount = 0; b_n = 0; }
+  __syncthreads();
+  // claim the staged range, write the tiles' headers, copy the pairs out
+  auto flush = [&](int seg_for_cursor) {
+    if (threadIdx.x == 0) {
+      int tc = scount;
+      int64_t begin;
+      if (per_segment) begin = t.seg_kbase[seg_for_cursor] + atomicAdd(&sel[seg_for_cursor * 4 + 2], (uint32_t)tc);
+      else begin = atomicAdd(cursor, (uint32_t)tc);
+      int keep = tc;
+      if (begin + tc > capacity) {
+        atomicOr(status, GB_STATUS_OVERFLOW);
+        keep = (int)max((int64_t)0, capacity - begin);
+      }
+      for (int i = 0; i < b_n; ++i) {
+        const int c = max(0, min(b_cnt[i], keep - b_off[i]));
+        for (int r = 0; r < out.n; ++r) out.hdr[r][b_tile[i]] = make_int2((int)begin + b_off[i], c);
+      }
+      scount = keep;
+      sbegin = (int)begin;
+    }
+    __syncthreads();
+    const int tcnt = scount, begin = sbegin;
+    for (int r = 0; r < out.n; ++r) {
+      float* dv = out.vals[r] + begin;
+      int32_t* di = out.idx[r] + begin;
+      for (int i = threadIdx.x; i < tcnt; i += GB_THREADS) { dv[i] = sval[i]; di[i] = sidx[i]; }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { scount = 0; b_n = 0; }
+    __syncthreads();
+  };
+  int last_seg = -1;
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
     if (per_segment && sel[seg * 4 + 3] != 0) continue;          // ambiguous ties: ordered kernels do this segment
     const uint32_t thr = use_fixed ? fixed_thr : sel[seg * 4];
-    if (threadIdx.x == 0) scount = 0;
-    __syncthreads();
-    // all 16 values of this thread stay in registers; one warp prefix sum and one shared-memory
-    // atomic per warp and tile place the picked pairs in the staging buffers
+    // all 16 values of this thread stay in registers; one warp prefix sum per tile places the picked pairs
     float vv[4][4];
     uint32_t picks = 0;
     int cnt = 0;
@@ -475,14 +510,24 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* wo
       const int n = __shfl_up_sync(0xffffffffu, incl, o);
       if (lane >= o) incl += n;
     }
-    const int wtotal = __shfl_sync(0xffffffffu, incl, 31);
-    int wbase = 0;
-    if (wtotal) {
-      if (lane == 0) wbase = atomicAdd(&scount, wtotal);
-      wbase = __shfl_sync(0xffffffffu, wbase, 0);
+    if (lane == 31) s_warp[wid] = incl;
+    __syncthreads();
+    int wbase = 0, tile_total = 0;
+#pragma unroll
+    for (int w = 0; w < GB_THREADS / 32; ++w) {
+      const int c = s_warp[w];
+      if (w < wid) wbase += c;
+      tile_total += c;
     }
+    // the batch is flushed first when this tile would not fit, when the batch table is full, or (per-segment cursors)
+    // when the tile belongs to another tensor than the batch
+    const bool must_flush = b_n > 0 && (scount + tile_total > GB_TILE || b_n == EF_BATCH || (per_segment && seg != last_seg));
+    __syncthreads();
+    if (must_flush) flush(last_seg);
+    const int off0 = scount;
+    __syncthreads();
     if (picks) {
-      int pos = wbase + incl - cnt;
+      int pos = off0 + wbase + incl - cnt;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
@@ -510,29 +555,15 @@ __global__ void __launch_bounds__(GB_THREADS) k1_emit_fast(SegTable t, float* wo
         }
       }
     }
-    __syncthreads();
     if (threadIdx.x == 0) {
-      int tc = scount;
-      int64_t begin;
-      if (per_segment) begin = t.seg_kbase[seg] + atomicAdd(&sel[seg * 4 + 2], (uint32_t)tc);
-      else begin = atomicAdd(cursor, (uint32_t)tc);
-      if (begin + tc > capacity) {
-        atomicOr(status, GB_STATUS_OVERFLOW);
-        tc = (int)max((int64_t)0, capacity - begin);
-        scount = tc;
-      }
-      sbegin = (int)begin;
-      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = make_int2((int)begin, tc);
+      b_tile[b_n] = tile; b_off[b_n] = off0; b_cnt[b_n] = tile_total;
+      b_n = b_n + 1;
+      scount = off0 + tile_total;
     }
-    __syncthreads();
-    const int tcnt = scount, begin = sbegin;
-    for (int r = 0; r < out.n; ++r) {
-      float* dv = out.vals[r] + begin;
-      int32_t* di = out.idx[r] + begin;
-      for (int i = threadIdx.x; i < tcnt; i += GB_THREADS) { dv[i] = sval[i]; di[i] = sidx[i]; }
-    }
+    last_seg = seg;
     __syncthreads();
   }
+  if (b_n > 0) flush(last_seg);
   if (release) release_flags_last_block(done, peers, channel, epoch);
 }
 
