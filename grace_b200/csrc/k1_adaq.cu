@@ -518,17 +518,48 @@ __global__ void __launch_bounds__(GB_THREADS) aq_emit(SegTable t, float* work, c
                                                       const StepCtl* ctl, size_t par_stride) {
   __shared__ int32_t sidx[GB_TILE];
   __shared__ int scount, sbegin;
+  // a CTA stages tile after tile and claims the payload cursor once per batch: same-address atomics serialise in L2
+  // (see k1_emit_fast)
+  constexpr int BATCH = 32;
+  __shared__ int b_tile[BATCH], b_off[BATCH], b_cnt[BATCH], b_n;
+  __shared__ int s_warp[GB_THREADS / 32];
   const uint32_t epoch = ctl->epoch;
   if (epoch & 1) shift(out, par_stride);
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) { scount = 0; b_n = 0; }
+  __syncthreads();
+  auto flush = [&]() {
+    if (threadIdx.x == 0) {
+      const int tc = scount;
+      const int64_t begin = atomicAdd(cursor, (uint32_t)tc);
+      int keep = tc;
+      if (begin + tc > capacity) {
+        atomicOr(status, GB_STATUS_OVERFLOW);
+        keep = (int)max((int64_t)0, capacity - begin);
+      }
+      sbegin = (int)min(begin, capacity);
+      for (int i = 0; i < b_n; ++i) {
+        const int c = max(0, min(b_cnt[i], keep - b_off[i]));
+        for (int r = 0; r < out.n; ++r) out.hdr[r][b_tile[i]] = make_int2(sbegin + (c ? b_off[i] : 0), c);
+      }
+      scount = keep;
+    }
+    __syncthreads();
+    const int tcnt = scount, begin = sbegin;
+    for (int r = 0; r < out.n; ++r) {
+      int32_t* di = out.idx[r] + begin;
+      for (int i = threadIdx.x; i < tcnt; i += GB_THREADS) di[i] = sidx[i];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { scount = 0; b_n = 0; }
+    __syncthreads();
+  };
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
     int seg, local0, len;
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
     const float thr0 = __uint_as_float(sel[(seg * 2) * 4]), thr1 = __uint_as_float(sel[(seg * 2 + 1) * 4]);
     const float m0 = means[seg * 2], m1 = means[seg * 2 + 1];
-    if (threadIdx.x == 0) scount = 0;
-    __syncthreads();
     float vv[4][4];
     uint32_t picks = 0, negs = 0;
     int cnt = 0;
@@ -550,14 +581,22 @@ __global__ void __launch_bounds__(GB_THREADS) aq_emit(SegTable t, float* work, c
       }
     }
     const int incl = warp_incl_scan(cnt, lane);
-    const int wtotal = __shfl_sync(0xffffffffu, incl, 31);
-    int wbase = 0;
-    if (wtotal) {
-      if (lane == 0) wbase = atomicAdd(&scount, wtotal);
-      wbase = __shfl_sync(0xffffffffu, wbase, 0);
+    if (lane == 31) s_warp[wid] = incl;
+    __syncthreads();
+    int wbase = 0, tile_total = 0;
+#pragma unroll
+    for (int w = 0; w < GB_THREADS / 32; ++w) {
+      const int c = s_warp[w];
+      if (w < wid) wbase += c;
+      tile_total += c;
     }
+    const bool must_flush = b_n > 0 && (scount + tile_total > GB_TILE || b_n == BATCH);
+    __syncthreads();
+    if (must_flush) flush();
+    const int off0 = scount;
+    __syncthreads();
     if (picks) {
-      int pos = wbase + incl - cnt;
+      int pos = off0 + wbase + incl - cnt;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
@@ -574,26 +613,14 @@ __global__ void __launch_bounds__(GB_THREADS) aq_emit(SegTable t, float* work, c
         }
       }
     }
-    __syncthreads();
     if (threadIdx.x == 0) {
-      int tc = scount;
-      const int64_t begin = atomicAdd(cursor, (uint32_t)tc);
-      if (begin + tc > capacity) {
-        atomicOr(status, GB_STATUS_OVERFLOW);
-        tc = (int)max((int64_t)0, capacity - begin);
-        scount = tc;
-      }
-      sbegin = (int)min(begin, capacity);
-      for (int r = 0; r < out.n; ++r) out.hdr[r][tile] = make_int2(sbegin, tc);
-    }
-    __syncthreads();
-    const int tcnt = scount, begin = sbegin;
-    for (int r = 0; r < out.n; ++r) {
-      int32_t* di = out.idx[r] + begin;
-      for (int i = threadIdx.x; i < tcnt; i += GB_THREADS) di[i] = sidx[i];
+      b_tile[b_n] = tile; b_off[b_n] = off0; b_cnt[b_n] = tile_total;
+      b_n = b_n + 1;
+      scount = off0 + tile_total;
     }
     __syncthreads();
   }
+  if (b_n > 0) flush();
   release_flags_last_block(done, peers, channel, epoch);
 }
 
