@@ -107,3 +107,19 @@ def test_tsv_logger_and_timer():
     log = TSVLogger()
     log.append({"epoch": 3, "total_time": 7200.0, "test_acc": 0.9412})
     assert str(log).splitlines() == ["epoch\thours\ttop1Accuracy", "3\t2.00000000\t94.12"]
+
+
+def test_capture_hint_lifts_the_mask_guard_only_for_maskless_calls():
+    """grace_b200.utils.capture: inside the context transformers' `is_tracing` guard answers False for a call without a
+    padding mask (so no all-ones mask is materialised while a stream captures) and is untouched for calls with one;
+    the original function is restored on exit."""
+    import torch
+    mu = pytest.importorskip("transformers.masking_utils")
+    from grace_b200.utils.capture import unmasked_attention_when_capturing
+    orig = mu.is_tracing
+    sentinel = torch.ones(2, 4)
+    with unmasked_attention_when_capturing():
+        assert mu.is_tracing is not orig
+        assert mu.is_tracing(None) is False and mu.is_tracing() is False
+        assert mu.is_tracing(sentinel) == orig(sentinel)
+    assert mu.is_tracing is orig
