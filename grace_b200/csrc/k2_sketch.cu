@@ -4,10 +4,12 @@
 // Reference op chain per tensor: tfp.stats.quantiles (a full sort), find_bins, unsorted_segment_mean,
 // cast; receive: gather means[bins] per rank + adds.  Here, per bucket:
 //   sk_prep    x = compensate(grad, residual) -> keys                      (one pass)
-//   rs_hist / rs_scan / rs_scatter: a hand-written stable LSD radix sort (8-bit digits) of 64-bit keys
-//              (tensor id << 32 | order-preserving float bits): ONE sort for all tensors of the bucket; only the
-//              32 + log2(#tensors) key bits that differ are sorted (5 passes for ResNet-50's 161 tensors).  No
-//              library kernel is on this path (round 1 called cub::DeviceRadixSort here).
+//   rs_hist / rs_scan / rs_scatter: a hand-written stable LSD radix sort (8-bit digits, 4 passes) of the
+//              order-preserving 32-bit float keys, SEGMENTED: every tensor of the bucket is sorted in place inside its
+//              own range of the flat buffer -- a sort block is a plan tile, which never straddles two tensors, so the
+//              digit prefixes are taken over the tiles of one tensor and no tensor id has to travel in the key (the
+//              first version sorted 64-bit (tensor id, key) words of the whole bucket in 5 passes: twice the bytes).
+//              No library kernel is on this path (round 1 called cub::DeviceRadixSort here).
 //   sk_edges   q+1 cut points per tensor, linear interpolation between order statistics
 //   sk_means   one CTA per (bucket, tensor): the elements of a bucket are a contiguous range of the sorted
 //              tensor, so the mean is a fixed-order range sum (deterministic, no float atomics);
@@ -34,76 +36,87 @@ __device__ __forceinline__ uint32_t flip_f(float x) {            // order-preser
 __device__ __forceinline__ float unflip_f(uint32_t k) {
   return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
 }
-__device__ __forceinline__ float sorted_at(const uint64_t* s, int64_t i) { return unflip_f((uint32_t)s[i]); }
+__device__ __forceinline__ float sorted_at(const uint32_t* s, int64_t i) { return unflip_f(s[i]); }
 
-// ---------------------------------------------------------------- stable LSD radix sort, 8 bits per pass
-// A block owns RS_KEYS consecutive keys.  rs_hist counts its digits; rs_scan turns counts[digit][block] into exclusive
-// prefixes over the blocks (one CTA per digit) and digit totals; rs_scatter ranks every key among the equal digits
-// that precede it (warp match + per-warp counts, rounds of 256 keys in index order => stable) and stores it at
-// base[digit] + prefix[digit][block] + rank.
-#define RS_KEYS 4096
-__global__ void __launch_bounds__(GB_THREADS) rs_hist(const uint64_t* __restrict__ keys, int64_t n, int shift, uint32_t* counts, int nblocks) {
+// ---------------------------------------------------------------- stable segmented LSD radix sort, 8 bits per pass
+// A sort block is a plan tile (<= 4096 keys of ONE tensor, the tensor's tail padding included in its last tile).
+// rs_hist counts the block's digits into counts[tile][digit]; rs_scan (one CTA per tensor, one thread per digit) turns
+// them into exclusive prefixes over the tensor's tiles and the tensor's exclusive digit offsets; rs_scatter ranks
+// every key among the equal digits that precede it (warp match + per-warp counts, rounds of 256 keys in index order
+// => stable) and stores it at  tensor offset + digit offset + prefix[tile][digit] + rank.
+__device__ __forceinline__ int sk_tile_keys(const SegTable& t, int tile, int64_t& base) {
+  int seg, local0, len;
+  tile_bounds(t, tile, seg, base, local0, len);
+  return min(GB_TILE, (int)(t.seg_off[seg + 1] - base));
+}
+
+__global__ void __launch_bounds__(GB_THREADS) rs_hist(SegTable t, const uint32_t* __restrict__ keys, int shift, uint32_t* counts) {
   __shared__ uint32_t sh[256];
   sh[threadIdx.x] = 0;
   __syncthreads();
-  const int64_t k0 = (int64_t)blockIdx.x * RS_KEYS;
-  for (int i = threadIdx.x; i < RS_KEYS; i += GB_THREADS)
-    if (k0 + i < n) atomicAdd(&sh[(uint32_t)(keys[k0 + i] >> shift) & 255u], 1u);
+  int64_t base;
+  const int n = sk_tile_keys(t, blockIdx.x, base);
+  for (int i = threadIdx.x * 4; i < n; i += GB_THREADS * 4) {            // tile bases and lengths are multiples of 4
+    const uint4 k = *reinterpret_cast<const uint4*>(keys + base + i);
+    atomicAdd(&sh[(k.x >> shift) & 255u], 1u);
+    atomicAdd(&sh[(k.y >> shift) & 255u], 1u);
+    atomicAdd(&sh[(k.z >> shift) & 255u], 1u);
+    atomicAdd(&sh[(k.w >> shift) & 255u], 1u);
+  }
   __syncthreads();
-  counts[(size_t)threadIdx.x * nblocks + blockIdx.x] = sh[threadIdx.x];
+  counts[(size_t)blockIdx.x * 256 + threadIdx.x] = sh[threadIdx.x];
 }
 
-__global__ void __launch_bounds__(GB_THREADS) rs_scan(uint32_t* counts, int nblocks, uint32_t* totals) {
+// grid: one CTA per tensor; thread d owns digit d.  digit_base[seg][d] = keys of the tensor with a smaller digit.
+__global__ void __launch_bounds__(GB_THREADS) rs_scan(SegTable t, uint32_t* counts, uint32_t* digit_base) {
   __shared__ uint32_t sh[GB_THREADS];
-  uint32_t* row = counts + (size_t)blockIdx.x * nblocks;
-  uint32_t carry = 0;
-  for (int c0 = 0; c0 < nblocks; c0 += GB_THREADS) {
-    const int i = c0 + threadIdx.x;
-    const uint32_t v = i < nblocks ? row[i] : 0u;
-    sh[threadIdx.x] = v;
+  const int seg = blockIdx.x, d = threadIdx.x;
+  const int t0 = t.seg_tile0[seg], t1 = t.seg_tile0[seg + 1];
+  uint32_t run = 0;
+  int tile = t0;
+  for (; tile + 8 <= t1; tile += 8) {                                   // eight independent loads in flight
+    uint32_t v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = counts[(size_t)(tile + u) * 256 + d];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { counts[(size_t)(tile + u) * 256 + d] = run; run += v[u]; }
+  }
+  for (; tile < t1; ++tile) {
+    const uint32_t v = counts[(size_t)tile * 256 + d];
+    counts[(size_t)tile * 256 + d] = run;
+    run += v;
+  }
+  sh[d] = run;
+  __syncthreads();
+  for (int o = 1; o < GB_THREADS; o <<= 1) {
+    const uint32_t a = d >= o ? sh[d - o] : 0u;
     __syncthreads();
-    for (int o = 1; o < GB_THREADS; o <<= 1) {
-      const uint32_t a = threadIdx.x >= o ? sh[threadIdx.x - o] : 0u;
-      __syncthreads();
-      sh[threadIdx.x] += a;
-      __syncthreads();
-    }
-    if (i < nblocks) row[i] = carry + sh[threadIdx.x] - v;
-    carry += sh[GB_THREADS - 1];
+    sh[d] += a;
     __syncthreads();
   }
-  if (threadIdx.x == 0) totals[blockIdx.x] = carry;
+  digit_base[(size_t)seg * 256 + d] = sh[d] - run;
 }
 
-__global__ void __launch_bounds__(GB_THREADS) rs_scatter(const uint64_t* __restrict__ keys, uint64_t* __restrict__ out, int64_t n, int shift,
-                                                        const uint32_t* __restrict__ prefix, int nblocks, const uint32_t* __restrict__ totals) {
-  __shared__ uint32_t s_base[256];               // where this block's first key with digit d goes
+__global__ void __launch_bounds__(GB_THREADS) rs_scatter(SegTable t, const uint32_t* __restrict__ keys, uint32_t* __restrict__ out, int shift,
+                                                        const uint32_t* __restrict__ prefix, const uint32_t* __restrict__ digit_base) {
+  __shared__ uint32_t s_base[256];               // where this block's first key with digit d goes (relative to the tensor)
   __shared__ uint32_t s_run[256];                // keys with digit d already placed by this block
   __shared__ uint32_t s_cnt[GB_THREADS / 32][256];
-  {
-    // exclusive scan of the 256 digit totals (every block redoes it: 256 values)
-    uint32_t v = totals[threadIdx.x];
-    s_run[threadIdx.x] = v;
-    __syncthreads();
-    for (int o = 1; o < 256; o <<= 1) {
-      const uint32_t a = threadIdx.x >= o ? s_run[threadIdx.x - o] : 0u;
-      __syncthreads();
-      s_run[threadIdx.x] += a;
-      __syncthreads();
-    }
-    s_base[threadIdx.x] = s_run[threadIdx.x] - v + prefix[(size_t)threadIdx.x * nblocks + blockIdx.x];
-    __syncthreads();
-    s_run[threadIdx.x] = 0;
-  }
+  int seg, local0, len;
+  int64_t base;
+  tile_bounds(t, blockIdx.x, seg, base, local0, len);
+  const int n = min(GB_TILE, (int)(t.seg_off[seg + 1] - base));
+  uint32_t* dst = out + t.seg_off[seg];
+  s_base[threadIdx.x] = digit_base[(size_t)seg * 256 + threadIdx.x] + prefix[(size_t)blockIdx.x * 256 + threadIdx.x];
+  s_run[threadIdx.x] = 0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t k0 = (int64_t)blockIdx.x * RS_KEYS;
-  for (int r = 0; r < RS_KEYS / GB_THREADS; ++r) {
+  for (int r = 0; r * GB_THREADS < n; ++r) {
     for (int w = 0; w < GB_THREADS / 32; ++w) s_cnt[w][threadIdx.x] = 0;
     __syncthreads();
-    const int64_t i = k0 + r * GB_THREADS + threadIdx.x;
+    const int i = r * GB_THREADS + threadIdx.x;
     const bool live = i < n;
-    const uint64_t key = live ? keys[i] : 0ull;
-    const uint32_t dg = live ? ((uint32_t)(key >> shift) & 255u) : 256u + (uint32_t)lane;     // dead lanes match nobody
+    const uint32_t key = live ? keys[base + i] : 0u;
+    const uint32_t dg = live ? ((key >> shift) & 255u) : 256u + (uint32_t)lane;     // dead lanes match nobody
     const uint32_t same = __match_any_sync(0xffffffffu, dg);
     const int rank = __popc(same & ((1u << lane) - 1u));
     if (live && rank == 0) s_cnt[warp][dg] = (uint32_t)__popc(same);
@@ -111,7 +124,7 @@ __global__ void __launch_bounds__(GB_THREADS) rs_scatter(const uint64_t* __restr
     if (live) {
       uint32_t before = 0;
       for (int w = 0; w < warp; ++w) before += s_cnt[w][dg];
-      out[(size_t)s_base[dg] + s_run[dg] + before + (uint32_t)rank] = key;
+      dst[(size_t)s_base[dg] + s_run[dg] + before + (uint32_t)rank] = key;
     }
     __syncthreads();
     uint32_t tot = 0;
@@ -121,10 +134,10 @@ __global__ void __launch_bounds__(GB_THREADS) rs_scatter(const uint64_t* __restr
   }
 }
 
-// x = compensate(grad, residual) -> vals (kept for the encode pass) and 64-bit sort keys; pad elements of a
+// x = compensate(grad, residual) -> vals (kept for the encode pass) and 32-bit sort keys; pad elements of a
 // tensor sort behind its real elements
 __global__ void __launch_bounds__(GB_THREADS) sk_prep(SegTable t, const float* __restrict__ grad, const float* __restrict__ res,
-                                                     float* __restrict__ vals, uint64_t* __restrict__ keys, int has_mem, float beta,
+                                                     float* __restrict__ vals, uint32_t* __restrict__ keys, int has_mem, float beta,
                                                      float gamma, const StepCtl* ctl) {
   if (ctl->step == 0) { beta = 0.f; gamma = 1.f; }
   for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) {
@@ -132,7 +145,6 @@ __global__ void __launch_bounds__(GB_THREADS) sk_prep(SegTable t, const float* _
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
     const int padded_len = min(GB_TILE, (int)(t.seg_off[seg + 1] - base));      // tile incl. the tensor's tail padding
-    const uint64_t hi = (uint64_t)seg << 32;
     for (int e = threadIdx.x; e < padded_len; e += blockDim.x) {
       float x = 0.f;
       uint32_t k = 0xFFFFFFFFu;
@@ -142,16 +154,16 @@ __global__ void __launch_bounds__(GB_THREADS) sk_prep(SegTable t, const float* _
         k = flip_f(x);
       }
       vals[base + e] = x;
-      keys[base + e] = hi | k;
+      keys[base + e] = k;
     }
   }
 }
 
 // edges[seg][0..q]: srt[lo] + (srt[hi] - srt[lo]) * frac with pos = j * ((n-1)/q)  (quant.py: linear_quantile_edges)
-__global__ void sk_edges(SegTable t, const uint64_t* __restrict__ sorted, int q, float* edges) {
+__global__ void sk_edges(SegTable t, const uint32_t* __restrict__ sorted, int q, float* edges) {
   const int seg = blockIdx.x;
   const int n = t.seg_numel[seg];
-  const uint64_t* s = sorted + t.seg_off[seg];
+  const uint32_t* s = sorted + t.seg_off[seg];
   const double step = (double)(n - 1) / (double)q;
   for (int j = threadIdx.x; j <= q; j += blockDim.x) {
     const double pos = (double)j * step;
@@ -164,7 +176,7 @@ __global__ void sk_edges(SegTable t, const uint64_t* __restrict__ sorted, int q,
   }
 }
 
-__device__ __forceinline__ int lower_bound_f(const uint64_t* s, int n, float v) {   // first i with s[i] >= v
+__device__ __forceinline__ int lower_bound_f(const uint32_t* s, int n, float v) {   // first i with s[i] >= v
   int lo = 0, hi = n;
   while (lo < hi) {
     const int mid = (lo + hi) >> 1;
@@ -174,14 +186,14 @@ __device__ __forceinline__ int lower_bound_f(const uint64_t* s, int n, float v) 
 }
 
 // grid (q, nseg): mean of bucket b of tensor seg; written to means[seg][b] and every peer's header
-__global__ void __launch_bounds__(128) sk_means(SegTable t, const uint64_t* __restrict__ sorted, const float* __restrict__ edges, int q,
+__global__ void __launch_bounds__(128) sk_means(SegTable t, const uint32_t* __restrict__ sorted, const float* __restrict__ edges, int q,
                                                 float* means, SkSlots out, const StepCtl* ctl, size_t par_stride) {
   __shared__ double sh[4];
   __shared__ int s_lo, s_hi;
   if (ctl->epoch & 1) shift(out, par_stride);
   const int b = blockIdx.x, seg = blockIdx.y;
   const int n = t.seg_numel[seg];
-  const uint64_t* s = sorted + t.seg_off[seg];
+  const uint32_t* s = sorted + t.seg_off[seg];
   const float* e = edges + (size_t)seg * (SK_MAXQ + 1);
   if (threadIdx.x == 0) {
     // bucket b = { x : b is the largest index (< q) with e[b] <= x }
@@ -320,10 +332,8 @@ __global__ void __launch_bounds__(GB_THREADS) sk_decode(SegTable t, SkIn in, siz
 
 struct SketchBufs {          // lives in gb_plan::sketch (allocated by sk_init)
   float *vals, *edges, *means;
-  uint64_t *keys, *sorted;
-  uint32_t *counts, *totals;   // radix sort: [256][nblocks] digit counts -> prefixes, [256] digit totals
-  int nblocks;
-  int end_bit;
+  uint32_t *keys, *sorted;
+  uint32_t *counts, *totals;   // radix sort: [ntiles][256] digit counts -> prefixes over a tensor's tiles, [nseg][256] digit offsets
 };
 
 size_t sk_header_bytes(int nseg, int q) { return ((size_t)nseg * q * 4 + 255) & ~size_t(255); }
@@ -334,15 +344,12 @@ int sk_init(gb_plan* p) {
   SketchBufs* b = new SketchBufs();
   p->sketch = b;
   GB_CUDA(cudaMalloc((void**)&b->vals, p->padded * 4));
-  GB_CUDA(cudaMalloc((void**)&b->keys, p->padded * 8));
-  GB_CUDA(cudaMalloc((void**)&b->sorted, p->padded * 8));
+  GB_CUDA(cudaMalloc((void**)&b->keys, p->padded * 4));
+  GB_CUDA(cudaMalloc((void**)&b->sorted, p->padded * 4));
   GB_CUDA(cudaMalloc((void**)&b->edges, (size_t)p->nseg * (SK_MAXQ + 1) * 4));
   GB_CUDA(cudaMalloc((void**)&b->means, (size_t)p->nseg * (SK_MAXQ + 1) * 4));
-  b->end_bit = 32;
-  while ((1ll << (b->end_bit - 32)) < p->nseg) ++b->end_bit;
-  b->nblocks = (int)((p->padded + RS_KEYS - 1) / RS_KEYS);
-  GB_CUDA(cudaMalloc((void**)&b->counts, (size_t)256 * b->nblocks * 4));
-  GB_CUDA(cudaMalloc((void**)&b->totals, 256 * 4));
+  GB_CUDA(cudaMalloc((void**)&b->counts, (size_t)256 * p->ntiles * 4));
+  GB_CUDA(cudaMalloc((void**)&b->totals, (size_t)256 * p->nseg * 4));
   return 0;
 }
 
@@ -368,16 +375,16 @@ int sk_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   sk_prep<<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, d_grad, p->d_state0, b->vals, b->keys, has_mem, p->prm.beta, p->prm.gamma,
                                                      p->d_ctl);
   LAUNCHED(p);
-  // stable LSD radix sort of the 64-bit keys, 8 bits per pass, ping-pong between keys and sorted
-  uint64_t* src = b->keys;
-  uint64_t* dst = b->sorted;
-  for (int shift = 0; shift < b->end_bit; shift += 8) {
-    rs_hist<<<b->nblocks, GB_THREADS, 0, st>>>(src, p->padded, shift, b->counts, b->nblocks); LAUNCHED(p);
-    rs_scan<<<256, GB_THREADS, 0, st>>>(b->counts, b->nblocks, b->totals); LAUNCHED(p);
-    rs_scatter<<<b->nblocks, GB_THREADS, 0, st>>>(src, dst, p->padded, shift, b->counts, b->nblocks, b->totals); LAUNCHED(p);
+  // stable segmented LSD radix sort of the 32-bit keys, 8 bits per pass, ping-pong between keys and sorted
+  uint32_t* src = b->keys;
+  uint32_t* dst = b->sorted;
+  for (int shift = 0; shift < 32; shift += 8) {
+    rs_hist<<<p->ntiles, GB_THREADS, 0, st>>>(p->tab, src, shift, b->counts); LAUNCHED(p);
+    rs_scan<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, b->counts, b->totals); LAUNCHED(p);
+    rs_scatter<<<p->ntiles, GB_THREADS, 0, st>>>(p->tab, src, dst, shift, b->counts, b->totals); LAUNCHED(p);
     std::swap(src, dst);
   }
-  const uint64_t* sorted = src;                       // after the last swap `src` holds the sorted keys
+  const uint32_t* sorted = src;                       // after the last swap `src` holds the sorted keys
   sk_edges<<<p->nseg, 128, 0, st>>>(p->tab, sorted, q, b->edges); LAUNCHED(p);
   sk_means<<<dim3(q, p->nseg), 128, 0, st>>>(p->tab, sorted, b->edges, q, b->means, out, p->d_ctl, p->par_stride); LAUNCHED(p);
   if (q < 256)
