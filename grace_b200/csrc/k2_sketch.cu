@@ -97,40 +97,82 @@ __global__ void __launch_bounds__(GB_THREADS) rs_scan(SegTable t, uint32_t* coun
   digit_base[(size_t)seg * 256 + d] = sh[d] - run;
 }
 
+// Ranking without block barriers: warp w owns keys [512 w, 512 w + 512) of the block and walks them 32 at a time;
+// a key's rank among the warp's earlier equal digits is the warp's running counter for that digit plus its position in
+// the match mask.  One block-wide step then turns the 8 x 256 counters into exclusive offsets in (digit, warp) order,
+// the keys are placed in shared memory in that order (= stable), and every thread copies keys i, i + 256, ... to their
+// final places: the keys of one digit are consecutive in both, so a warp stores contiguous runs.
+// (First version: 16 block-wide rounds of 256 keys with four barriers each and 4-byte stores straight from the round:
+// 240 us per pass for 102 MB.)
 __global__ void __launch_bounds__(GB_THREADS) rs_scatter(SegTable t, const uint32_t* __restrict__ keys, uint32_t* __restrict__ out, int shift,
                                                         const uint32_t* __restrict__ prefix, const uint32_t* __restrict__ digit_base) {
-  __shared__ uint32_t s_base[256];               // where this block's first key with digit d goes (relative to the tensor)
-  __shared__ uint32_t s_run[256];                // keys with digit d already placed by this block
+  __shared__ uint32_t s_key[GB_TILE];            // the block's keys ordered by digit (stable)
+  __shared__ uint32_t s_dst[256];                // final position of the block's first key with digit d, minus its offset in s_key
+  __shared__ uint32_t s_scan[256];
   __shared__ uint32_t s_cnt[GB_THREADS / 32][256];
   int seg, local0, len;
   int64_t base;
   tile_bounds(t, blockIdx.x, seg, base, local0, len);
   const int n = min(GB_TILE, (int)(t.seg_off[seg + 1] - base));
   uint32_t* dst = out + t.seg_off[seg];
-  s_base[threadIdx.x] = digit_base[(size_t)seg * 256 + threadIdx.x] + prefix[(size_t)blockIdx.x * 256 + threadIdx.x];
-  s_run[threadIdx.x] = 0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int r = 0; r * GB_THREADS < n; ++r) {
-    for (int w = 0; w < GB_THREADS / 32; ++w) s_cnt[w][threadIdx.x] = 0;
-    __syncthreads();
-    const int i = r * GB_THREADS + threadIdx.x;
-    const bool live = i < n;
-    const uint32_t key = live ? keys[base + i] : 0u;
-    const uint32_t dg = live ? ((key >> shift) & 255u) : 256u + (uint32_t)lane;     // dead lanes match nobody
-    const uint32_t same = __match_any_sync(0xffffffffu, dg);
-    const int rank = __popc(same & ((1u << lane) - 1u));
-    if (live && rank == 0) s_cnt[warp][dg] = (uint32_t)__popc(same);
-    __syncthreads();
-    if (live) {
-      uint32_t before = 0;
-      for (int w = 0; w < warp; ++w) before += s_cnt[w][dg];
-      dst[(size_t)s_base[dg] + s_run[dg] + before + (uint32_t)rank] = key;
+  constexpr int R = GB_TILE / GB_THREADS;            // 16 keys per thread
+  constexpr int WK = GB_TILE / (GB_THREADS / 32);    // 512 keys per warp
+  for (int w = 0; w < GB_THREADS / 32; ++w) s_cnt[w][threadIdx.x] = 0;
+  uint32_t key[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int i = warp * WK + r * 32 + lane;
+    key[r] = i < n ? keys[base + i] : 0u;
+  }
+  __syncthreads();
+  uint32_t rank[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const bool live = warp * WK + r * 32 + lane < n;
+    const uint32_t dg = (key[r] >> shift) & 255u;
+    // lanes with the same digit: eight ballots, one per digit bit (MATCH.ANY occupies the SM's ADU pipe for ~64 cycles
+    // per warp instruction -- ncu: that pipe 73 % busy, 250 us per pass; a ballot is a few cycles)
+    uint32_t same = __ballot_sync(0xffffffffu, live);
+#pragma unroll
+    for (int bit = 0; bit < 8; ++bit) {
+      const uint32_t bal = __ballot_sync(0xffffffffu, (dg >> bit) & 1u);
+      same &= ((dg >> bit) & 1u) ? bal : ~bal;
     }
+    const uint32_t before = live ? s_cnt[warp][dg] : 0u;
+    rank[r] = before + (uint32_t)__popc(same & ((1u << lane) - 1u));
+    __syncwarp();
+    if (live && (same & ((1u << lane) - 1u)) == 0u) s_cnt[warp][dg] = before + (uint32_t)__popc(same);
+    __syncwarp();
+  }
+  __syncthreads();
+  {
+    // thread d: counters of digit d over the warps -> exclusive offsets in (digit, warp) order
+    uint32_t c[GB_THREADS / 32], tot = 0;
+#pragma unroll
+    for (int w = 0; w < GB_THREADS / 32; ++w) { c[w] = s_cnt[w][threadIdx.x]; tot += c[w]; }
+    s_scan[threadIdx.x] = tot;
     __syncthreads();
-    uint32_t tot = 0;
-    for (int w = 0; w < GB_THREADS / 32; ++w) tot += s_cnt[w][threadIdx.x];
-    s_run[threadIdx.x] += tot;
-    __syncthreads();
+    for (int o = 1; o < 256; o <<= 1) {
+      const uint32_t a = threadIdx.x >= o ? s_scan[threadIdx.x - o] : 0u;
+      __syncthreads();
+      s_scan[threadIdx.x] += a;
+      __syncthreads();
+    }
+    uint32_t run = s_scan[threadIdx.x] - tot;
+    s_dst[threadIdx.x] = digit_base[(size_t)seg * 256 + threadIdx.x] + prefix[(size_t)blockIdx.x * 256 + threadIdx.x] - run;
+#pragma unroll
+    for (int w = 0; w < GB_THREADS / 32; ++w) { s_cnt[w][threadIdx.x] = run; run += c[w]; }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    if (warp * WK + r * 32 + lane < n) s_key[s_cnt[warp][(key[r] >> shift) & 255u] + rank[r]] = key[r];
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += GB_THREADS) {
+    const uint32_t k = s_key[i];
+    dst[s_dst[(k >> shift) & 255u] + (uint32_t)i] = k;
   }
 }
 
