@@ -37,6 +37,15 @@ __device__ __forceinline__ float unflip_f(uint32_t k) {
   return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
 }
 __device__ __forceinline__ float sorted_at(const uint32_t* s, int64_t i) { return unflip_f(s[i]); }
+__device__ __forceinline__ float4 sk_ld4(const float* p, int e0, int len) {      // p + e0 is 16-byte aligned
+  if (e0 + 4 <= len) return *reinterpret_cast<const float4*>(p + e0);
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (e0 < len) v.x = p[e0];
+  if (e0 + 1 < len) v.y = p[e0 + 1];
+  if (e0 + 2 < len) v.z = p[e0 + 2];
+  if (e0 + 3 < len) v.w = p[e0 + 3];
+  return v;
+}
 
 // ---------------------------------------------------------------- stable segmented LSD radix sort, 8 bits per pass
 // A sort block is a plan tile (<= 4096 keys of ONE tensor, the tensor's tail padding included in its last tile).
@@ -67,34 +76,59 @@ __global__ void __launch_bounds__(GB_THREADS) rs_hist(SegTable t, const uint32_t
   counts[(size_t)blockIdx.x * 256 + threadIdx.x] = sh[threadIdx.x];
 }
 
-// grid: one CTA per tensor; thread d owns digit d.  digit_base[seg][d] = keys of the tensor with a smaller digit.
-__global__ void __launch_bounds__(GB_THREADS) rs_scan(SegTable t, uint32_t* counts, uint32_t* digit_base) {
-  __shared__ uint32_t sh[GB_THREADS];
-  const int seg = blockIdx.x, d = threadIdx.x;
+// grid: one CTA per tensor, RS_GROUPS x 256 threads; thread (g, d) owns digit d over the g-th quarter of the tensor's
+// tiles: first the quarter's digit totals, then -- started from the totals of the quarters before it -- the exclusive
+// prefixes (a tensor of 576 tiles walked by one group kept the launch at 65 us).
+// digit_base[seg][d] = keys of the tensor with a smaller digit.
+#define RS_GROUPS 4
+__global__ void __launch_bounds__(RS_GROUPS * 256) rs_scan(SegTable t, uint32_t* counts, uint32_t* digit_base) {
+  __shared__ uint32_t s_tot[RS_GROUPS][256];
+  __shared__ uint32_t sh[256];
+  const int seg = blockIdx.x, d = threadIdx.x & 255, g = threadIdx.x >> 8;
   const int t0 = t.seg_tile0[seg], t1 = t.seg_tile0[seg + 1];
-  uint32_t run = 0;
-  int tile = t0;
-  for (; tile + 8 <= t1; tile += 8) {                                   // eight independent loads in flight
+  const int per = (t1 - t0 + RS_GROUPS - 1) / RS_GROUPS;
+  const int a0 = min(t1, t0 + g * per), a1 = min(t1, a0 + per);
+  uint32_t sum = 0;
+  int tile = a0;
+  for (; tile + 8 <= a1; tile += 8) {                                   // eight independent loads in flight
+    uint32_t v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = counts[(size_t)(tile + u) * 256 + d];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) sum += v[u];
+  }
+  for (; tile < a1; ++tile) sum += counts[(size_t)tile * 256 + d];
+  s_tot[g][d] = sum;
+  __syncthreads();
+  uint32_t run = 0, total = 0;
+#pragma unroll
+  for (int k = 0; k < RS_GROUPS; ++k) {
+    const uint32_t v = s_tot[k][d];
+    if (k < g) run += v;
+    total += v;
+  }
+  tile = a0;
+  for (; tile + 8 <= a1; tile += 8) {
     uint32_t v[8];
 #pragma unroll
     for (int u = 0; u < 8; ++u) v[u] = counts[(size_t)(tile + u) * 256 + d];
 #pragma unroll
     for (int u = 0; u < 8; ++u) { counts[(size_t)(tile + u) * 256 + d] = run; run += v[u]; }
   }
-  for (; tile < t1; ++tile) {
+  for (; tile < a1; ++tile) {
     const uint32_t v = counts[(size_t)tile * 256 + d];
     counts[(size_t)tile * 256 + d] = run;
     run += v;
   }
-  sh[d] = run;
+  if (g == 0) sh[d] = total;
   __syncthreads();
-  for (int o = 1; o < GB_THREADS; o <<= 1) {
-    const uint32_t a = d >= o ? sh[d - o] : 0u;
+  for (int o = 1; o < 256; o <<= 1) {
+    const uint32_t a = (g == 0 && d >= o) ? sh[d - o] : 0u;
     __syncthreads();
-    sh[d] += a;
+    if (g == 0) sh[d] += a;
     __syncthreads();
   }
-  digit_base[(size_t)seg * 256 + d] = sh[d] - run;
+  if (g == 0) digit_base[(size_t)seg * 256 + d] = sh[d] - total;
 }
 
 // Ranking without block barriers: warp w owns keys [512 w, 512 w + 512) of the block and walks them 32 at a time;
@@ -187,34 +221,24 @@ __global__ void __launch_bounds__(GB_THREADS) sk_prep(SegTable t, const float* _
     int64_t base;
     tile_bounds(t, tile, seg, base, local0, len);
     const int padded_len = min(GB_TILE, (int)(t.seg_off[seg + 1] - base));      // tile incl. the tensor's tail padding
-    for (int e = threadIdx.x; e < padded_len; e += blockDim.x) {
-      float x = 0.f;
-      uint32_t k = 0xFFFFFFFFu;
+    for (int e = threadIdx.x * 4; e < padded_len; e += GB_THREADS * 4) {        // bases and padded lengths: multiples of 4
+      float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
       if (e < len) {
-        x = grad[base + e];
-        if (has_mem) x = __fadd_rn(__fmul_rn(beta, res[base + e]), __fmul_rn(gamma, x));
-        k = flip_f(x);
+        x = sk_ld4(grad + base, e, len);
+        if (has_mem) {
+          const float4 r = sk_ld4(res + base, e, len);
+          x.x = __fadd_rn(__fmul_rn(beta, r.x), __fmul_rn(gamma, x.x)); x.y = __fadd_rn(__fmul_rn(beta, r.y), __fmul_rn(gamma, x.y));
+          x.z = __fadd_rn(__fmul_rn(beta, r.z), __fmul_rn(gamma, x.z)); x.w = __fadd_rn(__fmul_rn(beta, r.w), __fmul_rn(gamma, x.w));
+        }
       }
-      vals[base + e] = x;
-      keys[base + e] = k;
+      const uint4 k = make_uint4(e < len ? flip_f(x.x) : 0xFFFFFFFFu, e + 1 < len ? flip_f(x.y) : 0xFFFFFFFFu,
+                                 e + 2 < len ? flip_f(x.z) : 0xFFFFFFFFu, e + 3 < len ? flip_f(x.w) : 0xFFFFFFFFu);
+      if (e + 1 >= len) x.y = 0.f;
+      if (e + 2 >= len) x.z = 0.f;
+      if (e + 3 >= len) x.w = 0.f;
+      *reinterpret_cast<float4*>(vals + base + e) = x;
+      *reinterpret_cast<uint4*>(keys + base + e) = k;
     }
-  }
-}
-
-// edges[seg][0..q]: srt[lo] + (srt[hi] - srt[lo]) * frac with pos = j * ((n-1)/q)  (quant.py: linear_quantile_edges)
-__global__ void sk_edges(SegTable t, const uint32_t* __restrict__ sorted, int q, float* edges) {
-  const int seg = blockIdx.x;
-  const int n = t.seg_numel[seg];
-  const uint32_t* s = sorted + t.seg_off[seg];
-  const double step = (double)(n - 1) / (double)q;
-  for (int j = threadIdx.x; j <= q; j += blockDim.x) {
-    const double pos = (double)j * step;
-    const double lo = floor(pos);
-    int hi = (int)ceil(pos);
-    if (hi > n - 1) hi = n - 1;
-    const float frac = (float)(pos - lo);
-    const float a = sorted_at(s, (int)lo), b = sorted_at(s, hi);
-    edges[(size_t)seg * (SK_MAXQ + 1) + j] = __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), frac));
   }
 }
 
@@ -227,29 +251,45 @@ __device__ __forceinline__ int lower_bound_f(const uint32_t* s, int n, float v) 
   return lo;
 }
 
+// edges[seg][0..q]: srt[lo] + (srt[hi] - srt[lo]) * frac with pos = j * ((n-1)/q)  (quant.py: linear_quantile_edges),
+// and bound[seg][j] = first sorted position with a value >= edges[j]: thread j does both, so the q + 1 binary searches
+// of a tensor run side by side (they used to be done one after the other by thread 0 of every sk_means CTA: two
+// 21-step chains of dependent loads in front of every bucket sum, 188 us for the launch)
+__global__ void sk_edges(SegTable t, const uint32_t* __restrict__ sorted, int q, float* edges, int* bound) {
+  const int seg = blockIdx.x;
+  const int n = t.seg_numel[seg];
+  const uint32_t* s = sorted + t.seg_off[seg];
+  const double step = (double)(n - 1) / (double)q;
+  for (int j = threadIdx.x; j <= q; j += blockDim.x) {
+    const double pos = (double)j * step;
+    const double lo = floor(pos);
+    int hi = (int)ceil(pos);
+    if (hi > n - 1) hi = n - 1;
+    const float frac = (float)(pos - lo);
+    const float a = sorted_at(s, (int)lo), b = sorted_at(s, hi);
+    const float e = __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), frac));
+    edges[(size_t)seg * (SK_MAXQ + 1) + j] = e;
+    bound[(size_t)seg * (SK_MAXQ + 1) + j] = j == 0 ? 0 : lower_bound_f(s, n, e);
+  }
+}
+
 // grid (q, nseg): mean of bucket b of tensor seg; written to means[seg][b] and every peer's header
-__global__ void __launch_bounds__(128) sk_means(SegTable t, const uint32_t* __restrict__ sorted, const float* __restrict__ edges, int q,
-                                                float* means, SkSlots out, const StepCtl* ctl, size_t par_stride) {
+__global__ void __launch_bounds__(128) sk_means(SegTable t, const uint32_t* __restrict__ sorted, const float* __restrict__ edges,
+                                                const int* __restrict__ bound, int q, float* means, SkSlots out, const StepCtl* ctl,
+                                                size_t par_stride) {
   __shared__ double sh[4];
-  __shared__ int s_lo, s_hi;
   if (ctl->epoch & 1) shift(out, par_stride);
   const int b = blockIdx.x, seg = blockIdx.y;
   const int n = t.seg_numel[seg];
   const uint32_t* s = sorted + t.seg_off[seg];
   const float* e = edges + (size_t)seg * (SK_MAXQ + 1);
-  if (threadIdx.x == 0) {
-    // bucket b = { x : b is the largest index (< q) with e[b] <= x }
-    int bb = b;
-    while (bb + 1 < q && e[bb + 1] == e[b]) ++bb;          // equal cut points: the highest index owns the values
-    if (bb != b) { s_lo = 0; s_hi = 0; }
-    else {
-      s_lo = b == 0 ? 0 : lower_bound_f(s, n, e[b]);
-      s_hi = b == q - 1 ? n : lower_bound_f(s, n, e[b + 1]);
-      // cut points equal to e[b] at lower indices were skipped above; values equal to e[b+1] belong to b+1
-    }
+  const int* bd = bound + (size_t)seg * (SK_MAXQ + 1);
+  // bucket b = { x : b is the largest index (< q) with e[b] <= x }; equal cut points: the highest index owns the values
+  int lo = 0, hi = 0;
+  if (!(b + 1 < q && e[b + 1] == e[b])) {
+    lo = bd[b];                          // cut points equal to e[b] at lower indices own nothing: lower_bound covers them
+    hi = b == q - 1 ? n : bd[b + 1];     // values equal to e[b+1] belong to b+1
   }
-  __syncthreads();
-  const int lo = s_lo, hi = s_hi;
   double acc = 0;
   for (int i = lo + threadIdx.x; i < hi; i += blockDim.x) acc += (double)sorted_at(s, i);
   acc = warp_sum_d(acc);
@@ -374,6 +414,7 @@ __global__ void __launch_bounds__(GB_THREADS) sk_decode(SegTable t, SkIn in, siz
 
 struct SketchBufs {          // lives in gb_plan::sketch (allocated by sk_init)
   float *vals, *edges, *means;
+  int* bound;                  // [nseg][SK_MAXQ + 1] first sorted position >= edge
   uint32_t *keys, *sorted;
   uint32_t *counts, *totals;   // radix sort: [ntiles][256] digit counts -> prefixes over a tensor's tiles, [nseg][256] digit offsets
 };
@@ -390,6 +431,7 @@ int sk_init(gb_plan* p) {
   GB_CUDA(cudaMalloc((void**)&b->sorted, p->padded * 4));
   GB_CUDA(cudaMalloc((void**)&b->edges, (size_t)p->nseg * (SK_MAXQ + 1) * 4));
   GB_CUDA(cudaMalloc((void**)&b->means, (size_t)p->nseg * (SK_MAXQ + 1) * 4));
+  GB_CUDA(cudaMalloc((void**)&b->bound, (size_t)p->nseg * (SK_MAXQ + 1) * 4));
   GB_CUDA(cudaMalloc((void**)&b->counts, (size_t)256 * p->ntiles * 4));
   GB_CUDA(cudaMalloc((void**)&b->totals, (size_t)256 * p->nseg * 4));
   return 0;
@@ -398,7 +440,7 @@ int sk_init(gb_plan* p) {
 void sk_free(gb_plan* p) {
   SketchBufs* b = (SketchBufs*)p->sketch;
   if (!b) return;
-  cudaFree(b->vals); cudaFree(b->keys); cudaFree(b->sorted); cudaFree(b->edges); cudaFree(b->means); cudaFree(b->counts); cudaFree(b->totals);
+  cudaFree(b->vals); cudaFree(b->keys); cudaFree(b->sorted); cudaFree(b->edges); cudaFree(b->means); cudaFree(b->bound); cudaFree(b->counts); cudaFree(b->totals);
   delete b;
   p->sketch = nullptr;
 }
@@ -422,13 +464,13 @@ int sk_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   uint32_t* dst = b->sorted;
   for (int shift = 0; shift < 32; shift += 8) {
     rs_hist<<<p->ntiles, GB_THREADS, 0, st>>>(p->tab, src, shift, b->counts); LAUNCHED(p);
-    rs_scan<<<p->nseg, GB_THREADS, 0, st>>>(p->tab, b->counts, b->totals); LAUNCHED(p);
+    rs_scan<<<p->nseg, RS_GROUPS * 256, 0, st>>>(p->tab, b->counts, b->totals); LAUNCHED(p);
     rs_scatter<<<p->ntiles, GB_THREADS, 0, st>>>(p->tab, src, dst, shift, b->counts, b->totals); LAUNCHED(p);
     std::swap(src, dst);
   }
   const uint32_t* sorted = src;                       // after the last swap `src` holds the sorted keys
-  sk_edges<<<p->nseg, 128, 0, st>>>(p->tab, sorted, q, b->edges); LAUNCHED(p);
-  sk_means<<<dim3(q, p->nseg), 128, 0, st>>>(p->tab, sorted, b->edges, q, b->means, out, p->d_ctl, p->par_stride); LAUNCHED(p);
+  sk_edges<<<p->nseg, 128, 0, st>>>(p->tab, sorted, q, b->edges, b->bound); LAUNCHED(p);
+  sk_means<<<dim3(q, p->nseg), 128, 0, st>>>(p->tab, sorted, b->edges, b->bound, q, b->means, out, p->d_ctl, p->par_stride); LAUNCHED(p);
   if (q < 256)
     sk_encode<8><<<grid_for(p->ntiles), GB_THREADS, 0, st>>>(p->tab, b->vals, p->d_state0, has_mem, b->edges, b->means, q, out, p->hdr_bytes,
                                                             p->d_done, gb_comm_peers(c), p->channel, p->d_ctl, p->par_stride);
