@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(RS_GROUPS * 256) rs_scan(SegTable t, uint32_t*
 // final places: the keys of one digit are consecutive in both, so a warp stores contiguous runs.
 // (First version: 16 block-wide rounds of 256 keys with four barriers each and 4-byte stores straight from the round:
 // 240 us per pass for 102 MB.)
-__global__ void __launch_bounds__(GB_THREADS) rs_scatter(SegTable t, const uint32_t* __restrict__ keys, uint32_t* __restrict__ out, int shift,
+__global__ void __launch_bounds__(GB_THREADS, 4) rs_scatter(SegTable t, const uint32_t* __restrict__ keys, uint32_t* __restrict__ out, int shift,
                                                         const uint32_t* __restrict__ prefix, const uint32_t* __restrict__ digit_base) {
   __shared__ uint32_t s_key[GB_TILE];            // the block's keys ordered by digit (stable)
   __shared__ uint32_t s_dst[256];                // final position of the block's first key with digit d, minus its offset in s_key
@@ -290,8 +290,28 @@ __global__ void __launch_bounds__(128) sk_means(SegTable t, const uint32_t* __re
     lo = bd[b];                          // cut points equal to e[b] at lower indices own nothing: lower_bound covers them
     hi = b == q - 1 ? n : bd[b + 1];     // values equal to e[b+1] belong to b+1
   }
+  // 16-byte loads over the aligned middle of [lo, hi) (the tensor's range starts on a 512-byte boundary), four of
+  // them in flight per thread; a big tensor's bucket is 150 KB and one 4-byte load per thread and trip kept the
+  // launch at 158 us
   double acc = 0;
-  for (int i = lo + threadIdx.x; i < hi; i += blockDim.x) acc += (double)sorted_at(s, i);
+  const int a0 = min(hi, (lo + 3) & ~3), a1 = max(a0, hi & ~3);
+  for (int i = lo + threadIdx.x; i < a0; i += blockDim.x) acc += (double)sorted_at(s, i);
+  for (int i = a1 + threadIdx.x; i < hi; i += blockDim.x) acc += (double)sorted_at(s, i);
+  const uint4* s4 = reinterpret_cast<const uint4*>(s + a0);
+  const int n4 = (a1 - a0) >> 2;
+  int i = threadIdx.x;
+  for (; i + 3 * (int)blockDim.x < n4; i += 4 * blockDim.x) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = s4[i + u * blockDim.x];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      acc += ((double)unflip_f(v[u].x) + (double)unflip_f(v[u].y)) + ((double)unflip_f(v[u].z) + (double)unflip_f(v[u].w));
+  }
+  for (; i < n4; i += blockDim.x) {
+    const uint4 v = s4[i];
+    acc += ((double)unflip_f(v.x) + (double)unflip_f(v.y)) + ((double)unflip_f(v.z) + (double)unflip_f(v.w));
+  }
   acc = warp_sum_d(acc);
   if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
   __syncthreads();
