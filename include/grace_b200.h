@@ -177,10 +177,13 @@ int gb_nvls_launches(gb_nvls* p, int64_t* out);
  * travel with a pitch of 4, 8 or 16 floats).  gb_psgd_create2 adds warm_start: the averaged Q of one exchange seeds the
  * next one instead of a fresh normal draw (compressor/powersgd.py:37-39 use_memory); gb_psgd_qprev* expose that state.
  * All >=2-D gradients of a bucket, flattened like a plan (128-element aligned).  One exchange is
- *   gb_psgd_send  (M += e; Q0; P_r = M Q0 on tcgen05/TMEM via TMA; P tiles stored into every peer)
+ *   gb_psgd_send  (M = grad + e; Q0; P_r = M Q0 on tcgen05/TMEM via TMA; P tiles stored into every peer)
  *   gb_psgd_mid   (wait; P = mean; orthogonalise; Q_r = M^T P^ on tcgen05; Q tiles to every peer)
- *   gb_psgd_recv  (wait; Q = mean; out = P^ Q^T; e = M - out)
- * use_tcgen05 = 0 forces the CUDA-core GEMMs (also taken per matrix when cols % 4 != 0). */
+ *   gb_psgd_recv  (wait; Q = mean; out = P^ Q^T)
+ * The error-feedback memory e = M - P^ Q^T is implicit: the plan keeps M, P^ and Q of the last exchange and the next
+ * gb_psgd_send recomputes e where it is consumed (same bits as a stored residual); gb_psgd_state_read materialises it
+ * into a caller buffer of gb_psgd_padded_numel floats, gb_psgd_state_write loads one (checkpoint / resume).
+ * use_tcgen05 = 0 forces the CUDA-core GEMMs (also taken per matrix smaller than 8 x 32). */
 typedef struct gb_psgd gb_psgd;
 int gb_psgd_create(gb_comm* c, int nmat, const int64_t* rows, const int64_t* cols, const uint32_t* name_hash,
                    int rank, uint32_t seed, int has_memory, int use_tcgen05, gb_psgd** out);
@@ -199,8 +202,8 @@ int gb_psgd_launches(gb_psgd* p, int64_t* out);
 int gb_psgd_tc_matrices(gb_psgd* p);          /* how many matrices take the tcgen05 path */
 int gb_psgd_get_step(gb_psgd* p, uint32_t* step);
 int gb_psgd_set_step(gb_psgd* p, uint32_t step);
-int gb_psgd_residual(gb_psgd* p, void** d_ptr, size_t* bytes);
-int gb_psgd_state_read(gb_psgd* p, void* d_dst, void* stream);    /* residual buffer, padded floats */
+int gb_psgd_residual(gb_psgd* p, void** d_ptr, size_t* bytes);    /* non-NULL iff the plan keeps error-feedback state */
+int gb_psgd_state_read(gb_psgd* p, void* d_dst, void* stream);    /* residual, padded floats (computed on demand) */
 int gb_psgd_state_write(gb_psgd* p, const void* d_src, void* stream);
 int64_t gb_psgd_wire_bytes(gb_psgd* p);
 
