@@ -483,6 +483,166 @@ __global__ void __launch_bounds__(GB_THREADS) aq_select(SegTable t, const float*
   }
 }
 
+// The threshold adjustment with FOUR decisions per launch: a launch counts every element against the current threshold
+// of its sign AND the 14 thresholds the next three decisions can lead to (binary tree: child 2i+1 = 1.25f * T[i] after
+// "too many", child 2i+2 = 0.9f * T[i] after "too few" -- the products aq_adjust_one would form), and the CTA that
+// finishes last walks the tree with the rule of aq_adjust_one.  21 evaluations = 6 launches instead of 21; single-tile
+// tensors are refined to the end by their CTA in launch 0; later launches walk the open tensors' tiles only (OpenDir).
+// cnt[(seg * 2 + sign) * 16 + node]: values of that sign that pass node's threshold.
+#define AQ_TREE 15
+#define AQ_TREE_LAUNCHES 6
+__device__ __forceinline__ void aq_tree(float thr, float (&T)[AQ_TREE]) {
+  T[0] = thr;
+#pragma unroll
+  for (int i = 0; 2 * i + 2 < AQ_TREE; ++i) { T[2 * i + 1] = __fmul_rn(1.25f, T[i]); T[2 * i + 2] = __fmul_rn(0.9f, T[i]); }
+}
+__global__ void __launch_bounds__(GB_THREADS) aq_refine_tree(SegTable t, const float* __restrict__ work, uint32_t* sel,
+                                                            const int32_t* __restrict__ segcnt, double ratio, uint32_t* done,
+                                                            uint32_t* dir_scratch, int round) {
+  __shared__ int shc[2];
+  __shared__ int s_cnt[2][16];
+  __shared__ int s_last;
+  __shared__ int s_pref[AQ_PREF_CACHE];
+  const OpenDir dir = open_dir(dir_scratch, t.nseg);
+  uint32_t* cnt = dir_scratch + ((4 + 2 * t.nseg + 15) & ~15);          // [nseg * 2][16]
+  auto do_tile = [&](int tile) {
+    int seg, local0, len;
+    int64_t base;
+    tile_bounds(t, tile, seg, base, local0, len);
+    const uint32_t* q0 = sel + (seg * 2) * 4;
+    const uint32_t* q1 = q0 + 4;
+    const bool d0 = q0[1] != 0, d1 = q1[1] != 0;
+    if (d0 && d1) return;
+    constexpr int NJ = GB_TILE / (GB_THREADS * 4);
+    float vals[NJ * 4];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (e0 < len) v = ld4(work + base, e0, len);
+      vals[j * 4] = v.x; vals[j * 4 + 1] = v.y; vals[j * 4 + 2] = v.z; vals[j * 4 + 3] = v.w;
+    }
+    if (round == 0 && t.seg_tile0[seg + 1] - t.seg_tile0[seg] == 1) {
+      // a tensor of one tile belongs to this CTA alone: all evaluations of both signs here, values in registers
+      uint32_t qa[4] = {q0[0], q0[1], q0[2], q0[3]}, qb[4] = {q1[0], q1[1], q1[2], q1[3]};
+      for (int it = 0; it <= 20 && !(qa[1] && qb[1]); ++it) {
+        const float ta = __uint_as_float(qa[0]), tb = __uint_as_float(qb[0]);
+        const bool ga = qa[3] != 0, gb = qb[3] != 0, da = qa[1] != 0, db = qb[1] != 0;
+        int c0 = 0, c1 = 0;
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) {
+          const int e0 = (j * GB_THREADS + threadIdx.x) * 4;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (e0 + q >= len) continue;
+            const float x = vals[j * 4 + q];
+            const float mp = x > 0.f ? x : 0.f;
+            const float mn = x < 0.f ? -x : 0.f;
+            c0 += !da && (ga ? mp >= ta : mp > ta);
+            c1 += !db && (gb ? mn >= tb : mn > tb);
+          }
+        }
+        c0 = warp_sum_i(c0);
+        c1 = warp_sum_i(c1);
+        if (threadIdx.x < 2) shc[threadIdx.x] = 0;
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) {
+          if (c0) atomicAdd(&shc[0], c0);
+          if (c1) atomicAdd(&shc[1], c1);
+        }
+        __syncthreads();
+        qa[2] += (uint32_t)shc[0];
+        qb[2] += (uint32_t)shc[1];
+        __syncthreads();
+        aq_adjust_one(qa, segcnt[seg * 2], ratio);
+        aq_adjust_one(qb, segcnt[seg * 2 + 1], ratio);
+      }
+      if (threadIdx.x == 0) {
+        uint32_t* w0 = sel + (seg * 2) * 4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { w0[i] = qa[i]; w0[4 + i] = qb[i]; }
+      }
+      return;
+    }
+    if (threadIdx.x < 32) s_cnt[threadIdx.x >> 4][threadIdx.x & 15] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int sgn = 0; sgn < 2; ++sgn) {
+      const uint32_t* q = sgn ? q1 : q0;
+      if (q[1] != 0) continue;                         // this sign is final (uniform over the CTA)
+      float T[AQ_TREE];
+      aq_tree(__uint_as_float(q[0]), T);
+      const bool ge_root = q[3] != 0;                  // the root compares like aq_select: > before the first adjustment
+#pragma unroll
+      for (int i = 0; i < AQ_TREE; ++i) {
+        int c = 0;
+#pragma unroll
+        for (int e = 0; e < NJ * 4; ++e) {
+          const int e0 = ((e >> 2) * GB_THREADS + threadIdx.x) * 4 + (e & 3);
+          const float x = vals[e];
+          const float m = sgn ? (x < 0.f ? -x : 0.f) : (x > 0.f ? x : 0.f);
+          c += (e0 < len) && ((i == 0 && !ge_root) ? m > T[i] : m >= T[i]);
+        }
+        c = warp_sum_i(c);
+        if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_cnt[sgn][i], c);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      const int c = s_cnt[threadIdx.x >> 4][threadIdx.x & 15];
+      if (c) atomicAdd(&cnt[(size_t)(seg * 2 + (threadIdx.x >> 4)) * 16 + (threadIdx.x & 15)], (uint32_t)c);
+    }
+    __syncthreads();
+  };
+  if (round == 0) {
+    for (int tile = blockIdx.x; tile < t.ntiles; tile += gridDim.x) do_tile(tile);
+  } else {
+    const int nopen = __ldcg(dir.hdr), total = __ldcg(dir.hdr + 1);
+    if (nopen == 0) return;                            // every threshold is final: nothing left to do
+    const int cached = min(nopen, AQ_PREF_CACHE);
+    for (int i = threadIdx.x; i < cached; i += GB_THREADS) s_pref[i] = __ldcg(dir.pref + i);
+    __syncthreads();
+    for (int vt = blockIdx.x; vt < total; vt += gridDim.x) do_tile(open_dir_tile(t, dir, s_pref, cached, nopen, vt));
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(done, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (s_last) {
+    __threadfence();
+    for (int i = threadIdx.x; i < t.nseg * 2; i += GB_THREADS) {
+      const uint4 qv = __ldcg(reinterpret_cast<const uint4*>(sel + i * 4));
+      if (qv.y) continue;                              // final already (or refined by its own CTA)
+      float T[AQ_TREE];
+      aq_tree(__uint_as_float(qv.x), T);
+      const double target = ceil((double)segcnt[i] * ratio);
+      uint32_t adj = qv.w, fin = 0;
+      float thr = T[0];
+      int node = 0;
+      while (node < AQ_TREE) {
+        const double selected = (double)__ldcg(cnt + (size_t)i * 16 + node);
+        thr = T[node];
+        const bool over = selected > 1.25 * target, under = selected < 0.8 * target;
+        if (adj < 20u && (over || under)) {
+          thr = over ? __fmul_rn(1.25f, thr) : __fmul_rn(0.9f, thr);
+          node = over ? 2 * node + 1 : 2 * node + 2;
+          ++adj;
+        } else {
+          if (selected < 1.0) thr = __fmul_rn(0.8f, thr);
+          fin = 1u;
+          break;
+        }
+      }
+      __stcg(reinterpret_cast<uint4*>(sel + i * 4), make_uint4(__float_as_uint(thr), fin, 0u, adj));
+#pragma unroll
+      for (int k = 0; k < 16; ++k) __stcg(cnt + (size_t)i * 16 + k, 0u);
+    }
+    __syncthreads();
+    open_dir_build(t, dir, [&](int seg) { return __ldcg(sel + (seg * 2) * 4 + 1) == 0u || __ldcg(sel + (seg * 2 + 1) * 4 + 1) == 0u; });
+    if (threadIdx.x == 0) *done = 0;
+  }
+}
+
 // One CTA per tensor: fixed-order sum of the tile partials -> mean per sign, stored locally and to every peer.
 __global__ void __launch_bounds__(GB_THREADS) aq_mean(SegTable t, const double* __restrict__ tsum, const int32_t* __restrict__ tsel,
                                                       float* means, AdaqOut out, const StepCtl* ctl, size_t par_stride) {
@@ -769,9 +929,16 @@ int aq_send(gb_plan* p, const float* d_grad, cudaStream_t st) {
   aq_kth<<<p->nseg * 2, GB_THREADS, 0, st>>>(p->tab, b->segcnt, b->samp_off, b->samp, b->samp_total, p->prm.ratio, b->sel);
   AQ_LAUNCHED(p);
   uint32_t* adj_done = p->d_done + 4;
-  for (int it = 0; it <= 20; ++it) {
-    aq_select<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel, b->segcnt, p->prm.ratio, adj_done, p->d_hist, it);
-    AQ_LAUNCHED(p);
+  if (getenv("GRACE_B200_ADAQ_ROUND_PER_LAUNCH")) {      // the earlier shape (one evaluation per launch), kept for A/B timing
+    for (int it = 0; it <= 20; ++it) {
+      aq_select<false><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel, b->segcnt, p->prm.ratio, adj_done, p->d_hist, it);
+      AQ_LAUNCHED(p);
+    }
+  } else {
+    for (int it = 0; it < AQ_TREE_LAUNCHES; ++it) {       // four evaluations per launch: 6 x 4 >= 21
+      aq_refine_tree<<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->segcnt, p->prm.ratio, adj_done, p->d_hist, it);
+      AQ_LAUNCHED(p);
+    }
   }
   aq_select<true><<<grid, GB_THREADS, 0, st>>>(p->tab, work, b->sel, b->tsum, b->tsel, b->segcnt, p->prm.ratio, adj_done, p->d_hist, 0);
   AQ_LAUNCHED(p);
