@@ -43,6 +43,7 @@
 #define PS_A_BYTES (PS_BM * PS_BK * 4)   // 16 KiB
 #define PS_B_BYTES (PS_N * PS_BK * 4)    //  2 KiB
 #define PS_SMEM (PS_STAGES * (PS_A_BYTES + PS_B_BYTES) + 1024 + 256)
+#define PS_GRID (148 * 2)   // persistent GEMM: two resident CTAs per SM
 
 struct PsMat {          // one matrix of the bucket (device copy)
   int64_t off;          // element offset of M in the flat gradient / output buffers (row pitch m)
@@ -166,8 +167,13 @@ __device__ int g_dbg[8];   // {enable, lbo, sbo, k_step, a_major, dump, layout}
 __device__ float g_dbg_dump[8192];
 #endif
 
+// PERSISTENT: the grid is two CTAs per SM and CTA b walks work items b, b + grid, b + 2 grid, ...  The barriers, the
+// TMEM allocation and the pipeline live across items: the producer runs ahead into the next item's tiles while the
+// epilogue of the previous one drains, and the two 16-column TMEM accumulators alternate so the MMA of item i+1
+// starts before item i has been read back.  (First version: one CTA per item -- ncu showed the SMs active 68 % of the
+// launch: 2.24 waves of ~10-stage items, each paying its own barrier init, TMEM alloc, pipeline fill and epilogue.)
 template <int MODE, int RP>
-__global__ void __launch_bounds__(192, 2) k3_gemm(const PsItem* __restrict__ items, const PsMat* __restrict__ mats,
+__global__ void __launch_bounds__(192, 2) k3_gemm(const PsItem* __restrict__ items, int nitems, const PsMat* __restrict__ mats,
                                                   const CUtensorMap* __restrict__ maps, float* part, uint32_t* tile_cnt,
                                                   PsPeers peers, const StepCtl* ctl, size_t par_stride, uint32_t* done,
                                                   PeerPtrs flag_peers, int channel, int release) {
@@ -178,20 +184,15 @@ __global__ void __launch_bounds__(192, 2) k3_gemm(const PsItem* __restrict__ ite
   uint8_t* sB = smem + PS_STAGES * PS_A_BYTES;
   uint64_t* full = (uint64_t*)(smem + PS_STAGES * (PS_A_BYTES + PS_B_BYTES));
   uint64_t* empty = full + PS_STAGES;
-  uint64_t* accum_ready = empty + PS_STAGES;
-  uint32_t* tmem_slot = (uint32_t*)(accum_ready + 1);
+  uint64_t* accum_full = empty + PS_STAGES;       // [2] MMAs of an item have landed in accumulator b
+  uint64_t* accum_free = accum_full + 2;          // [2] the epilogue has read accumulator b back
+  uint32_t* tmem_slot = (uint32_t*)(accum_free + 2);
   uint32_t* last_flag = tmem_slot + 1;
-
-  const PsItem it = items[blockIdx.x];
-  const PsMat mt = mats[it.mat];
-  const CUtensorMap* mapA = maps + it.mat * 4 + (MODE == 1 ? 0 : 2);
-  const CUtensorMap* mapB = maps + it.mat * 4 + (MODE == 1 ? 1 : 3);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nkb = (it.k1 - it.k0 + PS_BK - 1) / PS_BK;
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < PS_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    mbar_init(accum_ready, 1);
+    for (int b = 0; b < 2; ++b) { mbar_init(&accum_full[b], 1); mbar_init(&accum_free[b], 128); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -201,103 +202,121 @@ __global__ void __launch_bounds__(192, 2) k3_gemm(const PsItem* __restrict__ ite
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem_d = *tmem_slot;
+  const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0 && lane == 0) {
-    // ---- TMA producer
-    for (int kb = 0; kb < nkb; ++kb) {
-      const int s = kb % PS_STAGES;
-      if (kb >= PS_STAGES) mbar_wait(&empty[s], ((kb / PS_STAGES) - 1) & 1);
-      mbar_expect_tx(&full[s], PS_A_BYTES + PS_B_BYTES);
-      const int k = it.k0 + kb * PS_BK;
-      if (MODE == 1) {
-        tma_load_2d(sA + s * PS_A_BYTES, mapA, &full[s], k, it.m0);               // box 32 (K) x 128 (rows)
-      } else {
+    // ---- TMA producer: one running stage counter over all items of this CTA
+    uint32_t g = 0;
+    for (int ii = blockIdx.x; ii < nitems; ii += gridDim.x) {
+      const PsItem it = items[ii];
+      const CUtensorMap* mapA = maps + it.mat * 4 + (MODE == 1 ? 0 : 2);
+      const CUtensorMap* mapB = maps + it.mat * 4 + (MODE == 1 ? 1 : 3);
+      const int nkb = (it.k1 - it.k0 + PS_BK - 1) / PS_BK;
+      for (int kb = 0; kb < nkb; ++kb, ++g) {
+        const int s = g % PS_STAGES;
+        if (g >= PS_STAGES) mbar_wait(&empty[s], ((g / PS_STAGES) - 1) & 1);
+        mbar_expect_tx(&full[s], PS_A_BYTES + PS_B_BYTES);
+        const int k = it.k0 + kb * PS_BK;
+        if (MODE == 1) {
+          tma_load_2d(sA + s * PS_A_BYTES, mapA, &full[s], k, it.m0);               // box 32 (K) x 128 (rows)
+        } else {
 #pragma unroll
-        for (int b = 0; b < 4; ++b)                                                // 4 boxes 32 (cols) x 32 (K rows)
-          tma_load_2d(sA + s * PS_A_BYTES + b * 4096, mapA, &full[s], it.m0 + b * 32, k);
+          for (int b = 0; b < 4; ++b)                                                // 4 boxes 32 (cols) x 32 (K rows)
+            tma_load_2d(sA + s * PS_A_BYTES + b * 4096, mapA, &full[s], it.m0 + b * 32, k);
+        }
+        tma_load_2d(sB + s * PS_B_BYTES, mapB, &full[s], k, 0);                      // box 32 (K) x 16
       }
-      tma_load_2d(sB + s * PS_B_BYTES, mapB, &full[s], k, 0);                      // box 32 (K) x 16
     }
   } else if (warp == 1 && lane == 0) {
     // ---- MMA issuer (one thread)
     constexpr uint32_t idesc = idesc_tf32(MODE == 2);
-    for (int kb = 0; kb < nkb; ++kb) {
-      const int s = kb % PS_STAGES;
-      mbar_wait(&full[s], (kb / PS_STAGES) & 1);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t a0 = smem_u32(sA + s * PS_A_BYTES), b0 = smem_u32(sB + s * PS_B_BYTES);
-#pragma unroll
-      for (int j = 0; j < PS_BK / 8; ++j) {                                        // UMMA_K = 8 for tf32
-        uint64_t ad, bd;
-        if (MODE == 1) ad = smem_desc_sw128(a0 + j * 32, 16, 1024);               // K-major: +32 B per K step
-#ifdef GB_K3_DEBUG
-        else if (g_dbg[0]) ad = smem_desc_sw128(a0 + j * g_dbg[3], g_dbg[1], g_dbg[2], g_dbg[6]);
-#endif
-        // MN-major tf32 must use the 128B swizzle with 32-byte atoms (atom = 32 MN x 4 K): blocks of 32
-        // columns are 4096 B apart (LBO), groups of 4 K rows 512 B apart (SBO), 8 K rows per MMA
-        else ad = smem_desc_sw128(a0 + j * 1024, 4096, 512, 1);
-        bd = smem_desc_sw128(b0 + j * 32, 16, 1024);
-        uint32_t id = idesc;
-#ifdef GB_K3_DEBUG
-        if (MODE == 2 && g_dbg[0]) id = (idesc & ~(1u << 15)) | ((uint32_t)g_dbg[4] << 15);
-        if (MODE == 2 && g_dbg[5] && kb == 0 && j == 0 && blockIdx.x == 0) {
-          for (int i = 0; i < 4096 + 512; ++i) g_dbg_dump[i] = i < 4096 ? ((float*)(sA))[i] : ((float*)(sB))[i - 4096];
-        }
-#endif
-        umma_tf32(tmem_d, ad, bd, id, (kb | j) != 0);
+    uint32_t g = 0, n = 0;
+    for (int ii = blockIdx.x; ii < nitems; ii += gridDim.x, ++n) {
+      const PsItem it = items[ii];
+      const int nkb = (it.k1 - it.k0 + PS_BK - 1) / PS_BK;
+      const uint32_t buf = n & 1u, use = n >> 1;
+      if (use > 0) {                                      // accumulator `buf` was used by item n - 2: wait for its read-back
+        mbar_wait(&accum_free[buf], (use - 1) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       }
-      umma_commit(&empty[s]);                 // frees the smem stage once these MMAs have read it
+      const uint32_t tmem_d = tmem_base + buf * PS_N;
+      for (int kb = 0; kb < nkb; ++kb, ++g) {
+        const int s = g % PS_STAGES;
+        mbar_wait(&full[s], (g / PS_STAGES) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t a0 = smem_u32(sA + s * PS_A_BYTES), b0 = smem_u32(sB + s * PS_B_BYTES);
+#pragma unroll
+        for (int j = 0; j < PS_BK / 8; ++j) {                                        // UMMA_K = 8 for tf32
+          uint64_t ad, bd;
+          if (MODE == 1) ad = smem_desc_sw128(a0 + j * 32, 16, 1024);               // K-major: +32 B per K step
+          // MN-major tf32 must use the 128B swizzle with 32-byte atoms (atom = 32 MN x 4 K): blocks of 32
+          // columns are 4096 B apart (LBO), groups of 4 K rows 512 B apart (SBO), 8 K rows per MMA
+          else ad = smem_desc_sw128(a0 + j * 1024, 4096, 512, 1);
+          bd = smem_desc_sw128(b0 + j * 32, 16, 1024);
+          umma_tf32(tmem_d, ad, bd, idesc, (kb | j) != 0);
+        }
+        umma_commit(&empty[s]);                 // frees the smem stage once these MMAs have read it
+      }
+      umma_commit(&accum_full[buf]);
     }
-    umma_commit(accum_ready);
   } else if (warp >= 2) {
     // ---- epilogue: TMEM -> registers -> accumulate / push
-    mbar_wait(accum_ready, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const int q = warp & 3;
-    uint32_t v[16];
-    tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16), v);
-    const int row = it.m0 + q * 32 + lane;
-    const int nrows = MODE == 1 ? mt.n : mt.m;
-    const int row0 = MODE == 1 ? mt.prow0 : mt.qrow0;
-    const bool live = row < nrows;
-    if (it.nchunks == 1) {
-      if (live) {
+    uint32_t n = 0;
+    for (int ii = blockIdx.x; ii < nitems; ii += gridDim.x, ++n) {
+      const PsItem it = items[ii];
+      const PsMat mt = mats[it.mat];
+      const uint32_t buf = n & 1u, use = n >> 1;
+      mbar_wait(&accum_full[buf], use & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const int q = warp & 3;
+      uint32_t v[16];
+      tmem_ld16(tmem_base + buf * PS_N + ((uint32_t)(q * 32) << 16), v);
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&accum_free[buf])) : "memory");
+      const int row = it.m0 + q * 32 + lane;
+      const int nrows = MODE == 1 ? mt.n : mt.m;
+      const int row0 = MODE == 1 ? mt.prow0 : mt.qrow0;
+      const bool live = row < nrows;
+      if (it.nchunks == 1) {
+        if (live) {
 #pragma unroll
-        for (int c4 = 0; c4 < RP / 4; ++c4) {
-          const float4 o = make_float4(__uint_as_float(v[c4 * 4]), __uint_as_float(v[c4 * 4 + 1]), __uint_as_float(v[c4 * 4 + 2]),
-                                       __uint_as_float(v[c4 * 4 + 3]));
-          for (int r = 0; r < peers.n; ++r)
-            wire_st_u4(reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP) + c4,
-                       make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), __float_as_uint(o.w)), peers.mc);
-        }
-      }
-    } else {
-      // split-K without floating-point atomics: every K slice stores its partial tile, the CTA that completes the
-      // tile adds the slices in slice order (same bits on every run and every rank) and ships the sum
-      const int rl = q * 32 + lane;                                 // row inside the 128-row tile
-      float4* mine = reinterpret_cast<float4*>(part + ((size_t)blockIdx.x * PS_BM + rl) * RP);
-#pragma unroll
-      for (int c4 = 0; c4 < RP / 4; ++c4)
-        mine[c4] = make_float4(__uint_as_float(v[c4 * 4]), __uint_as_float(v[c4 * 4 + 1]), __uint_as_float(v[c4 * 4 + 2]),
-                               __uint_as_float(v[c4 * 4 + 3]));
-      __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (threadIdx.x == 64) *last_flag = (atomicAdd(tile_cnt + it.tile, 1u) == (uint32_t)it.nchunks - 1) ? 1u : 0u;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (*last_flag && live) {                 // this CTA completed the tile: ship it to every peer
-        __threadfence();
-        const size_t item0 = (size_t)blockIdx.x - it.chunk;
-#pragma unroll
-        for (int c4 = 0; c4 < RP / 4; ++c4) {
-          float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-          for (int ch = 0; ch < it.nchunks; ++ch) {
-            const float4 x = __ldcg(reinterpret_cast<const float4*>(part + ((item0 + ch) * PS_BM + rl) * RP) + c4);
-            o.x += x.x; o.y += x.y; o.z += x.z; o.w += x.w;
+          for (int c4 = 0; c4 < RP / 4; ++c4) {
+            const float4 o = make_float4(__uint_as_float(v[c4 * 4]), __uint_as_float(v[c4 * 4 + 1]), __uint_as_float(v[c4 * 4 + 2]),
+                                         __uint_as_float(v[c4 * 4 + 3]));
+            for (int r = 0; r < peers.n; ++r)
+              wire_st_u4(reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP) + c4,
+                         make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), __float_as_uint(o.w)), peers.mc);
           }
-          for (int r = 0; r < peers.n; ++r)
-            wire_st_u4(reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP) + c4,
-                       make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), __float_as_uint(o.w)), peers.mc);
+        }
+      } else {
+        // split-K without floating-point atomics: every K slice stores its partial tile, the CTA that completes the
+        // tile adds the slices in slice order (same bits on every run and every rank) and ships the sum
+        const int rl = q * 32 + lane;                                 // row inside the 128-row tile
+        float4* mine = reinterpret_cast<float4*>(part + ((size_t)ii * PS_BM + rl) * RP);
+#pragma unroll
+        for (int c4 = 0; c4 < RP / 4; ++c4)
+          mine[c4] = make_float4(__uint_as_float(v[c4 * 4]), __uint_as_float(v[c4 * 4 + 1]), __uint_as_float(v[c4 * 4 + 2]),
+                                 __uint_as_float(v[c4 * 4 + 3]));
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == 64) *last_flag = (atomicAdd(tile_cnt + it.tile, 1u) == (uint32_t)it.nchunks - 1) ? 1u : 0u;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const bool last = *last_flag != 0u;
+        asm volatile("bar.sync 1, 128;" ::: "memory");               // last_flag is reused by the next item
+        if (last && live) {                       // this CTA completed the tile: ship it to every peer
+          __threadfence();
+          const size_t item0 = (size_t)ii - it.chunk;
+#pragma unroll
+          for (int c4 = 0; c4 < RP / 4; ++c4) {
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int ch = 0; ch < it.nchunks; ++ch) {
+              const float4 x = __ldcg(reinterpret_cast<const float4*>(part + ((item0 + ch) * PS_BM + rl) * RP) + c4);
+              o.x += x.x; o.y += x.y; o.z += x.z; o.w += x.w;
+            }
+            for (int r = 0; r < peers.n; ++r)
+              wire_st_u4(reinterpret_cast<float4*>(peers.slot[r] + (size_t)(row0 + row) * RP) + c4,
+                         make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), __float_as_uint(o.w)), peers.mc);
+          }
         }
       }
     }
@@ -306,7 +325,7 @@ __global__ void __launch_bounds__(192, 2) k3_gemm(const PsItem* __restrict__ ite
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(32u) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(32u) : "memory");
   }
   // every matrix of the bucket went through this launch: the CTA that finishes last publishes the epoch (no separate
   // flag kernel); with CUDA-core fallback matrices in the bucket their launch, which follows on the stream, does it
@@ -1180,7 +1199,7 @@ extern "C" int gb_psgd_send(gb_psgd* p, const float* d_grad, void* stream) {
   LAUNCHED(p);
   const PsPeers ps = peer_slots(p, p->off_p, p->slot_p);
   if (p->nitems1) {
-    PS_DISPATCH(p->rp, (k3_gemm<1, RP><<<p->nitems1, 192, PS_SMEM, st>>>(p->d_items1, p->d_mat, p->d_maps, p->d_part1, p->d_cnt1, ps,
+    PS_DISPATCH(p->rp, (k3_gemm<1, RP><<<std::min(p->nitems1, PS_GRID), 192, PS_SMEM, st>>>(p->d_items1, p->nitems1, p->d_mat, p->d_maps, p->d_part1, p->d_cnt1, ps,
                                                                         p->d_ctl, psp, p->d_done, gb_comm_peers(c), p->chan_p,
                                                                         p->nsimt == 0)));
     LAUNCHED(p);
@@ -1213,7 +1232,7 @@ extern "C" int gb_psgd_mid(gb_psgd* p, void* stream) {
   LAUNCHED(p);
   const PsPeers qs = peer_slots(p, p->off_q, p->slot_q);
   if (p->nitems2) {
-    PS_DISPATCH(p->rp, (k3_gemm<2, RP><<<p->nitems2, 192, PS_SMEM, st>>>(p->d_items2, p->d_mat, p->d_maps, p->d_part2, p->d_cnt2, qs,
+    PS_DISPATCH(p->rp, (k3_gemm<2, RP><<<std::min(p->nitems2, PS_GRID), 192, PS_SMEM, st>>>(p->d_items2, p->nitems2, p->d_mat, p->d_maps, p->d_part2, p->d_cnt2, qs,
                                                                         p->d_ctl, psq, p->d_done, gb_comm_peers(c), p->chan_q,
                                                                         p->nsimt == 0)));
     LAUNCHED(p);
