@@ -200,7 +200,13 @@ __global__ void __launch_bounds__(GB_THREADS) in_send_k(SegTable t, const float*
     const int words = n32 + (2 * n16 + n8 + 3) / 4;
     __syncthreads();
     if (threadIdx.x == 0) {
-      int64_t begin = words ? (int64_t)atomicAdd(cursor, (uint32_t)words) : 0;
+      // A tile never needs more stream words than it has elements, so with a slot sized for the whole bucket (the
+      // default capacity of 1.0) the tile's own element offset is a free place for its words: no claim at all.  The
+      // shared cursor compacts the stream only when the slot is smaller -- one same-address atomic per tile, which
+      // serialises in L2 (~100 us for the 25 000 tiles of ResNet-50).
+      int64_t begin = 0;
+      if (cap_words >= t.padded) begin = base;
+      else if (words) begin = (int64_t)atomicAdd(cursor, (uint32_t)words);
       int4 h = make_int4((int)begin, n32, n16, n8);
       if (begin + words > cap_words) {
         atomicOr(status, GB_STATUS_OVERFLOW);
