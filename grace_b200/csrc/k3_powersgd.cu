@@ -38,10 +38,14 @@
 #define PS_RMAX 16       // max rank handled natively = UMMA N; rows of P / Q are stored with a pitch RP of 4, 8 or 16 floats
 #define PS_N 16          // UMMA N (rank padded to the minimum N for M=128)
 #define PS_BM 128        // UMMA M / rows of a tile in the GEMM's M dimension
-#define PS_BK 32         // K elements per pipeline stage (= one 128-byte swizzle row of tf32)
-#define PS_STAGES 6
-#define PS_A_BYTES (PS_BM * PS_BK * 4)   // 16 KiB
-#define PS_B_BYTES (PS_N * PS_BK * 4)    //  2 KiB
+#define PS_BOXK 32       // K elements of one TMA box (= one 128-byte swizzle row of tf32)
+#define PS_HALVES 2      // boxes along K per pipeline stage: the two 128-byte pieces of a row are requested together
+#define PS_BK (PS_BOXK * PS_HALVES)      // K elements per pipeline stage
+#define PS_STAGES 3
+#define PS_A_HALF (PS_BM * PS_BOXK * 4)  // 16 KiB
+#define PS_B_HALF (PS_N * PS_BOXK * 4)   //  2 KiB
+#define PS_A_BYTES (PS_A_HALF * PS_HALVES)
+#define PS_B_BYTES (PS_B_HALF * PS_HALVES)
 #define PS_SMEM (PS_STAGES * (PS_A_BYTES + PS_B_BYTES) + 1024 + 256)
 #define PS_GRID (148 * 2)   // persistent GEMM: two resident CTAs per SM
 
@@ -217,14 +221,18 @@ __global__ void __launch_bounds__(192, 2) k3_gemm(const PsItem* __restrict__ ite
         if (g >= PS_STAGES) mbar_wait(&empty[s], ((g / PS_STAGES) - 1) & 1);
         mbar_expect_tx(&full[s], PS_A_BYTES + PS_B_BYTES);
         const int k = it.k0 + kb * PS_BK;
-        if (MODE == 1) {
-          tma_load_2d(sA + s * PS_A_BYTES, mapA, &full[s], k, it.m0);               // box 32 (K) x 128 (rows)
-        } else {
 #pragma unroll
-          for (int b = 0; b < 4; ++b)                                                // 4 boxes 32 (cols) x 32 (K rows)
-            tma_load_2d(sA + s * PS_A_BYTES + b * 4096, mapA, &full[s], it.m0 + b * 32, k);
+        for (int h = 0; h < PS_HALVES; ++h) {
+          const int kh = k + h * PS_BOXK;
+          if (MODE == 1) {
+            tma_load_2d(sA + s * PS_A_BYTES + h * PS_A_HALF, mapA, &full[s], kh, it.m0);   // box 32 (K) x 128 (rows)
+          } else {
+#pragma unroll
+            for (int b = 0; b < 4; ++b)                                              // 4 boxes 32 (cols) x 32 (K rows)
+              tma_load_2d(sA + s * PS_A_BYTES + h * PS_A_HALF + b * 4096, mapA, &full[s], it.m0 + b * 32, kh);
+          }
+          tma_load_2d(sB + s * PS_B_BYTES + h * PS_B_HALF, mapB, &full[s], kh, 0);   // box 32 (K) x 16
         }
-        tma_load_2d(sB + s * PS_B_BYTES, mapB, &full[s], k, 0);                      // box 32 (K) x 16
       }
     }
   } else if (warp == 1 && lane == 0) {
@@ -247,12 +255,14 @@ __global__ void __launch_bounds__(192, 2) k3_gemm(const PsItem* __restrict__ ite
         const uint32_t a0 = smem_u32(sA + s * PS_A_BYTES), b0 = smem_u32(sB + s * PS_B_BYTES);
 #pragma unroll
         for (int j = 0; j < PS_BK / 8; ++j) {                                        // UMMA_K = 8 for tf32
+          const uint32_t ah = a0 + (j / 4) * PS_A_HALF, bh = b0 + (j / 4) * PS_B_HALF;  // which 32-wide box of the stage
+          const int jj = j & 3;
           uint64_t ad, bd;
-          if (MODE == 1) ad = smem_desc_sw128(a0 + j * 32, 16, 1024);               // K-major: +32 B per K step
+          if (MODE == 1) ad = smem_desc_sw128(ah + jj * 32, 16, 1024);              // K-major: +32 B per K step
           // MN-major tf32 must use the 128B swizzle with 32-byte atoms (atom = 32 MN x 4 K): blocks of 32
           // columns are 4096 B apart (LBO), groups of 4 K rows 512 B apart (SBO), 8 K rows per MMA
-          else ad = smem_desc_sw128(a0 + j * 1024, 4096, 512, 1);
-          bd = smem_desc_sw128(b0 + j * 32, 16, 1024);
+          else ad = smem_desc_sw128(ah + jj * 1024, 4096, 512, 1);
+          bd = smem_desc_sw128(bh + jj * 32, 16, 1024);
           umma_tf32(tmem_d, ad, bd, idesc, (kb | j) != 0);
         }
         umma_commit(&empty[s]);                 // frees the smem stage once these MMAs have read it
@@ -1044,11 +1054,11 @@ static int psgd_build(gb_psgd* p, gb_comm* c, int nmat, const int64_t* rows, con
     const PsMat& m = p->h_mat[i];
     if (!m.tc) continue;
     const float* M = p->d_work + m.woff;
-    if (make_map(&maps[i * 4 + 0], M, m.m, m.n, m.ldw, PS_BK, PS_BM)) return -1;
-    if (make_map(&maps[i * 4 + 1], p->d_q0t + m.qrow0, m.m, PS_N, p->qpad, PS_BK, PS_N)) return -1;
-    if (make_map(&maps[i * 4 + 2], M, m.m, m.n, m.ldw, 32, PS_BK,
+    if (make_map(&maps[i * 4 + 0], M, m.m, m.n, m.ldw, PS_BOXK, PS_BM)) return -1;
+    if (make_map(&maps[i * 4 + 1], p->d_q0t + m.qrow0, m.m, PS_N, p->qpad, PS_BOXK, PS_N)) return -1;
+    if (make_map(&maps[i * 4 + 2], M, m.m, m.n, m.ldw, 32, PS_BOXK,
                  getenv("GB_PSGD_SWZ128") ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return -1;
-    if (make_map(&maps[i * 4 + 3], p->d_pht + m.prow0, m.n, PS_N, p->ppad, PS_BK, PS_N)) return -1;
+    if (make_map(&maps[i * 4 + 3], p->d_pht + m.prow0, m.n, PS_N, p->ppad, PS_BOXK, PS_N)) return -1;
   }
   GB_CUDA(cudaMalloc((void**)&p->d_maps, sizeof(CUtensorMap) * nmat * 4));
   GB_CUDA(cudaMemcpy(p->d_maps, maps.data(), sizeof(CUtensorMap) * nmat * 4, cudaMemcpyHostToDevice));
