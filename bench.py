@@ -266,7 +266,7 @@ def run_codec(args, comp_name, env):
     step = eager_step
     # ours: the whole step (forward, backward, fused exchange, optimizer) as ONE CUDA graph
     graphed, graph_note = None, "eager"
-    if args.impl == "ours" and opt is not None and not args.no_graph:
+    if args.impl == "ours" and (opt is not None or dist_grc is not None) and not args.no_graph:
         try:
             from grace_b200.utils.capture import unmasked_attention_when_capturing
 
@@ -277,7 +277,11 @@ def run_codec(args, comp_name, env):
                 # stream captures (that mask sends SDPA to the fp32 math path; see grace_b200/utils/capture.py)
                 with unmasked_attention_when_capturing():
                     return m(input_ids=x, labels=x, next_sentence_label=y).loss
-            graphed = hvd.GraphedStep(model, opt, loss_fn, [dev_x, dev_y], amp_dtype=torch.bfloat16, warmup=3)
+            if opt is not None:
+                graphed = hvd.GraphedStep(model, opt, loss_fn, [dev_x, dev_y], amp_dtype=torch.bfloat16, warmup=3)
+            else:        # dist flavour: the manual loop, bucketed (step_all), captured with the plain optimizer
+                graphed = hvd.GraphedStep(model, base_opt, loss_fn, [dev_x, dev_y], amp_dtype=torch.bfloat16, warmup=3,
+                                          communicator=dist_grc)
             dev_x, dev_y = graphed.static_inputs
             graph_note = "cuda-graph (whole step)"
         except Exception as exc:                      # capture refused: fall back to the eager loop

@@ -106,11 +106,18 @@ def read_back(scalar, host=None, check=None):
 
 
 class GraphedStep:
-    def __init__(self, model, optimizer, loss_fn, example_inputs, amp_dtype=torch.bfloat16, warmup=3):
+    """``optimizer`` is an ``hvd.DistributedOptimizer`` (its hooks exchange the gradients), or -- for the
+    ``torch.distributed`` flavour, whose integration is a manual loop over the parameters
+    (examples/dist/CIFAR10-dawndist/core.py:202-208) -- a plain torch optimizer plus ``communicator=``: the captured
+    step then runs ``communicator.step_all((name, grad) ...)`` between backward and the optimizer update."""
+
+    def __init__(self, model, optimizer, loss_fn, example_inputs, amp_dtype=torch.bfloat16, warmup=3, communicator=None):
         if not torch.cuda.is_available():
             raise RuntimeError("GraphedStep needs CUDA")
         self.model, self.optimizer, self.loss_fn = model, optimizer, loss_fn
         self.amp_dtype = amp_dtype
+        self.communicator = communicator
+        self._named = [(n, p) for n, p in model.named_parameters() if p.requires_grad] if communicator is not None else None
         self.static_inputs = [t.clone() for t in example_inputs]
         fused = getattr(optimizer, "_fused", None)
         # eager warm-up on a side stream (cuDNN autotuning, lazy optimizer state, first-call codec rules)
@@ -121,23 +128,35 @@ class GraphedStep:
                 self._step_body()
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
-        n0 = fused.launches() if fused is not None else 0
+        stepper = getattr(communicator, "_stepper", None) if communicator is not None else None
+        counter = fused.launches if fused is not None else (stepper.launches if stepper is not None else (lambda: 0))
+        n0 = counter()
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self.static_loss = self._step_body()
-        self.native_launches_per_step = (fused.launches() - n0) if fused is not None else 0
+        self.native_launches_per_step = counter() - n0
         # Python (and with it FusedDP.synchronize's status check) does not run during a replay: the pinned status
         # word is read around every replay instead -- a plain host load, no device synchronisation
-        self._check = fused.engine.check_status if fused is not None else None
+        self._check = None
+        if fused is not None:
+            self._check = fused.engine.check_status
+        elif stepper is not None and stepper.enabled:
+            from grace_b200.parallel.fused import get_engine
+            self._check = get_engine().check_status
         self.replays = 0
         self._feeder = None
         self._loss_host = None
 
     def _step_body(self):
-        self.optimizer.zero_grad()
+        if self.communicator is not None:
+            self.optimizer.zero_grad(set_to_none=False)
+        else:
+            self.optimizer.zero_grad()
         with torch.autocast("cuda", dtype=self.amp_dtype, enabled=self.amp_dtype is not None):
             loss = self.loss_fn(self.model, *self.static_inputs)
         loss.backward()
+        if self.communicator is not None:
+            self.communicator.step_all([(n, p.grad) for n, p in self._named], inplace=True)
         self.optimizer.step()
         return loss.detach()
 
