@@ -38,6 +38,9 @@ ap.add_argument("--compress-ratio", "--compress_ratio", dest="compress_ratio", t
 ap.add_argument("--log_dir", default=".")
 ap.add_argument("--per-tensor", action="store_true", help="exchange with one grc.step per parameter (the reference loop)")
 ap.add_argument("--no-augment", action="store_true")
+ap.add_argument("--graph", action="store_true",
+                help="CUDA only: capture forward, backward, grc.step_all and the optimizer update as ONE CUDA graph "
+                     "(grace_b200.dist.GraphedStep); the learning rate lives in a device tensor updated in place")
 ap.add_argument("--master_address", "-m", default="127.0.0.1")
 ap.add_argument("--rank", "-r", type=int, default=None)
 ap.add_argument("--world_size", "-w", type=int, default=None)
@@ -96,13 +99,30 @@ if world > 1:
         dist.broadcast(p.data, 0)
 steps_per_epoch = len(train_x) // (args.batch_size * world)
 lr_at = lambda e: max(0.0, (e / 5 if e < 5 else (args.epochs - e) / max(args.epochs - 5, 1))) * 0.4   # piecewise linear
-opt = torch.optim.SGD(model.parameters(), lr=0.0, momentum=0.9, nesterov=True, weight_decay=5e-4 * args.batch_size)
+use_graph = args.graph and device.type == "cuda" and not args.per_tensor
+lr_t = torch.zeros((), device=device) if use_graph else None     # a Python float would be frozen into the graph
+# (torch's foreach SGD reads a tensor learning rate back with .item(), which a capturing stream forbids; fused=True
+#  takes the tensor as is)
+opt = torch.optim.SGD(model.parameters(), lr=lr_t if use_graph else 0.0, momentum=0.9, nesterov=True,
+                      weight_decay=5e-4 * args.batch_size, fused=True if use_graph else None)
 grc = grace_from_params({"compressor": args.compressor, "memory": args.memory, "communicator": args.communicator,
                          "compress_ratio": args.compress_ratio, "world_size": world, "threshold": args.threshold,
                          "quantum_num": args.qstates, "lr": args.efsgdlr, "momentum": args.momentum,
                          "gradient_clipping": args.clipping})
 table, tsv = TableLogger(rank=rank), TSVLogger()
 named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+gstep = None
+if use_graph:
+    from grace_b200.dist import GraphedStep
+    model.train()
+    ex = train_x[:args.batch_size]
+    ex = (ex[:, :, 4:36, 4:36] if args.no_augment else augment(ex)).contiguous(memory_format=torch.channels_last)
+    # three warm-up steps at lr = 0 (parameters do not move), then the capture; every later step is one graph replay
+    gstep = GraphedStep(model, opt, lambda m, x, y: F.cross_entropy(m(x), y, reduction="sum"), [ex, train_y[:args.batch_size]],
+                        amp_dtype=torch.bfloat16, warmup=3, communicator=grc)
+    for st in opt.state.values():                              # the warm-up gradients must not seed the momentum
+        if "momentum_buffer" in st and st["momentum_buffer"] is not None:
+            st["momentum_buffer"].zero_()
 for epoch in range(args.epochs):
     model.train()
     perm = torch.randperm(len(train_x), generator=torch.Generator().manual_seed(epoch)).to(device)
@@ -112,6 +132,10 @@ for epoch in range(args.epochs):
         x = train_x[idx]
         x = (x[:, :, 4:36, 4:36] if args.no_augment else augment(x)).contiguous(memory_format=torch.channels_last)
         y = train_y[idx]
+        if gstep is not None:
+            lr_t.fill_(lr_at(epoch + s / steps_per_epoch) / args.batch_size)
+            loss_sum += gstep(x, y)
+            continue
         for g in opt.param_groups:
             g["lr"] = lr_at(epoch + s / steps_per_epoch) / args.batch_size
         opt.zero_grad(set_to_none=False)
