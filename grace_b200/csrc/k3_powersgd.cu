@@ -166,10 +166,6 @@ __device__ __forceinline__ void shift(PsPeers& o, size_t bytes) {
   for (int r = 0; r < o.n; ++r) o.slot[r] = (float*)((char*)o.slot[r] + bytes);
 }
 
-#ifdef GB_K3_DEBUG   // descriptor experiments of benchmarks/dbg_k3.py (build with GB_NVCC_EXTRA=-DGB_K3_DEBUG)
-__device__ int g_dbg[8];   // {enable, lbo, sbo, k_step, a_major, dump, layout}
-__device__ float g_dbg_dump[8192];
-#endif
 
 // PERSISTENT: the grid is two CTAs per SM and CTA b walks work items b, b + grid, b + 2 grid, ...  The barriers, the
 // TMEM allocation and the pipeline live across items: the producer runs ahead into the next item's tiles while the
@@ -1169,16 +1165,6 @@ extern "C" int gb_psgd_qprev_copy(gb_psgd* p, void* d_buf, int to_plan, void* st
                           (cudaStream_t)stream));
   return 0;
 }
-#ifdef GB_K3_DEBUG
-extern "C" int gb_psgd_debug_set(const int* v8) {
-  GB_CUDA(cudaMemcpyToSymbol(g_dbg, v8, 32));
-  return 0;
-}
-extern "C" int gb_psgd_debug_dump(float* h_dst) {
-  GB_CUDA(cudaMemcpyFromSymbol(h_dst, g_dbg_dump, 8192 * 4));
-  return 0;
-}
-#endif
 extern "C" int64_t gb_psgd_wire_bytes(gb_psgd* p) { return (int64_t)(p->prows + p->qrows) * p->rp * 4; }
 
 static PsPeers peer_slots(gb_psgd* p, size_t chan_off, size_t slot_bytes, uint32_t epoch = 0) {   // parity 0
