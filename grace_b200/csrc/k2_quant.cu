@@ -327,11 +327,12 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
   // Sub-word codes (1/2/4/8 bit): the tile's packed words are staged in shared memory and go to every peer
   // as 16-byte stores of one contiguous run (512 B .. 4 KB per tile and peer).  Storing each word straight
   // from the lane that finished it produced 16-byte NVLink writes for the 1-bit codecs.
-  constexpr int STAGE_WORDS = WORDS == 1 ? GB_TILE * BITS / 32 + (BITS == 5 ? 4 : 0) : 4;
+  constexpr bool ODD = BITS == 5 || BITS == 6 || BITS == 7;     // widths that do not divide 32
+  constexpr int STAGE_WORDS = WORDS == 1 ? GB_TILE * BITS / 32 + (ODD ? 4 : 0) : 4;
   __shared__ __align__(16) uint32_t s_words[STAGE_WORDS];
-  // 5-bit lane (QSGD with 8..15 levels): 20 bits per thread do not tile a word, so the codes are OR-ed into the
-  // zeroed staging words at their bit position (a tile starts on a word boundary: 128 elements = 20 words)
-  if (BITS == 5) {
+  // 5/6/7-bit lanes (QSGD with 8..63 levels): 20/24/28 bits per thread do not tile a word, so the codes are OR-ed into
+  // the zeroed staging words at their bit position (a tile starts on a word boundary: 128 elements = 4 BITS words)
+  if (ODD) {
     for (int i = threadIdx.x; i < STAGE_WORDS; i += GB_THREADS) s_words[i] = 0u;
     __syncthreads();
   }
@@ -421,11 +422,11 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
         uint32_t sub = 0;
 #pragma unroll
         for (int q = 0; q < 4; ++q) sub |= code[q] << (q * BITS);
-        if (BITS == 5) {
+        if (ODD) {
           if (e0 < len && sub) {
-            const int bit = e0 * 5, wi = bit >> 5, sh = bit & 31;
+            const int bit = e0 * BITS, wi = bit >> 5, sh = bit & 31;
             atomicOr(&s_words[wi], sub << sh);
-            if (sh > 12) atomicOr(&s_words[wi + 1], sub >> (32 - sh));
+            if (sh > 32 - SUB) atomicOr(&s_words[wi + 1], sub >> (32 - sh));
           }
         } else {
           const int lane = threadIdx.x & 31;
@@ -448,7 +449,7 @@ __global__ void __launch_bounds__(GB_THREADS) k2_encode(SegTable t, const float*
         if (threadIdx.x < (nwords & 3)) wire_st_u32(dst + 4 * n4 + threadIdx.x, s_words[4 * n4 + threadIdx.x], out.mc);
       }
       __syncthreads();
-      if (BITS == 5) {
+      if (ODD) {
         for (int i = threadIdx.x; i < STAGE_WORDS; i += GB_THREADS) s_words[i] = 0u;
         __syncthreads();
       }
@@ -495,8 +496,9 @@ __global__ void __launch_bounds__(GB_THREADS, 4) k2_decode(SegTable t, WireIn in
     // rank loop through a `break`, which serialised W x 4 four-byte loads per thread and tile and capped the
     // kernel at ~1 TB/s at W = 8.
     constexpr int NJ = GB_TILE / (GB_THREADS * 4);
-    constexpr int WPT = BITS == 32 ? 4 : ((BITS == 16 || BITS == 5) ? 2 : 1);      // 32-bit words per thread, rank and group
-    constexpr int JCH = BITS == 32 ? 1 : ((BITS == 16 || BITS == 5) ? 2 : 4);      // groups whose loads are in flight together
+    constexpr bool ODD = BITS == 5 || BITS == 6 || BITS == 7;                       // widths that do not divide 32
+    constexpr int WPT = BITS == 32 ? 4 : ((BITS == 16 || ODD) ? 2 : 1);            // 32-bit words per thread, rank and group
+    constexpr int JCH = BITS == 32 ? 1 : ((BITS == 16 || ODD) ? 2 : 4);            // groups whose loads are in flight together
 #pragma unroll
     for (int j0 = 0; j0 < NJ; j0 += JCH) {
       uint32_t raw[JCH][GB_MAX_WORLD][WPT];
@@ -513,9 +515,9 @@ __global__ void __launch_bounds__(GB_THREADS, 4) k2_decode(SegTable t, WireIn in
           } else if (BITS == 16) {
             const uint2 w = *reinterpret_cast<const uint2*>(words + flat / 2);
             raw[jj][r][0] = w.x; raw[jj][r][1 % WPT] = w.y;
-          } else if (BITS == 5) {
-            raw[jj][r][0] = words[(flat * 5) >> 5];                      // 20 bits from bit (5 flat) & 31: may straddle
-            raw[jj][r][1 % WPT] = words[((flat * 5) >> 5) + 1];
+          } else if (ODD) {
+            raw[jj][r][0] = words[(flat * BITS) >> 5];                   // 4 BITS bits from bit (BITS flat) & 31: may straddle
+            raw[jj][r][1 % WPT] = words[((flat * BITS) >> 5) + 1];
           } else {
             raw[jj][r][0] = words[flat * BITS / 32];
           }
@@ -534,11 +536,11 @@ __global__ void __launch_bounds__(GB_THREADS, 4) k2_decode(SegTable t, WireIn in
           } else if (BITS == 16) {
             code[0] = raw[jj][r][0] & 0xFFFFu; code[1] = raw[jj][r][0] >> 16;
             code[2] = raw[jj][r][1 % WPT] & 0xFFFFu; code[3] = raw[jj][r][1 % WPT] >> 16;
-          } else if (BITS == 5) {
+          } else if (ODD) {
             const uint64_t v = ((uint64_t)raw[jj][r][1 % WPT] << 32) | raw[jj][r][0];
-            const int sh = (int)((flat * 5) & 31);
+            const int sh = (int)((flat * BITS) & 31);
 #pragma unroll
-            for (int q = 0; q < 4; ++q) code[q] = (uint32_t)(v >> (sh + q * 5)) & 31u;
+            for (int q = 0; q < 4; ++q) code[q] = (uint32_t)(v >> (sh + q * BITS)) & (0xFFFFFFFFu >> (32 - BITS));
           } else {
             const int sh = (int)((flat * BITS) & 31);
 #pragma unroll
@@ -653,6 +655,8 @@ static int launch_decode(gb_plan* p, float* o, const WireIn& in, const PeerPtrs&
     case GB_CODEC_QSGD:                                                                           \
       if (p->bits == 4) return FN<GB_CODEC_QSGD, 4>(__VA_ARGS__);                                 \
       if (p->bits == 5) return FN<GB_CODEC_QSGD, 5>(__VA_ARGS__);                                 \
+      if (p->bits == 6) return FN<GB_CODEC_QSGD, 6>(__VA_ARGS__);                                 \
+      if (p->bits == 7) return FN<GB_CODEC_QSGD, 7>(__VA_ARGS__);                                 \
       if (p->bits == 8) return FN<GB_CODEC_QSGD, 8>(__VA_ARGS__);                                 \
       return FN<GB_CODEC_QSGD, 16>(__VA_ARGS__);                                                  \
     case GB_CODEC_TERNGRAD: return FN<GB_CODEC_TERNGRAD, 2>(__VA_ARGS__);                         \

@@ -16,8 +16,11 @@ static int quant_bits(const gb_codec_params& p) {
   switch (p.codec) {
     case GB_CODEC_NONE: return 32;
     case GB_CODEC_FP16: return 16;
-    // signed levels -q..q: 4 bits hold q <= 7, 5 bits q <= 15 ("QSGD 8 levels" of BASELINE config 4), 8 bits q <= 127
-    case GB_CODEC_QSGD: return p.quantum_num <= 7 ? 4 : (p.quantum_num <= 15 ? 5 : (p.quantum_num <= 127 ? 8 : 16));
+    // signed levels -q..q in two's complement: b bits hold q <= 2^(b-1) - 1 ("QSGD 8 levels" of BASELINE config 4: 5 bits)
+    case GB_CODEC_QSGD: {
+      const int q = p.quantum_num;
+      return q <= 7 ? 4 : q <= 15 ? 5 : q <= 31 ? 6 : q <= 63 ? 7 : q <= 127 ? 8 : 16;
+    }
     case GB_CODEC_TERNGRAD: return 2;
     case GB_CODEC_SKETCH: return p.quantum_num < 256 ? 8 : 16;     // uint16 bins for >= 256 quantiles (sketch.py:26)
     case GB_CODEC_NATURAL:

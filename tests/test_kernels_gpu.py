@@ -322,7 +322,7 @@ def test_sketch_with_16_bit_bins(q):
     assert_same(fused, oracle, exact=False, frac=0.002, rtol=2e-5, atol=1e-7, what="sketch%d" % q)
 
 
-@pytest.mark.parametrize("q,bits", [(4, 4), (7, 4), (8, 5), (15, 5), (16, 8), (64, 8), (256, 16)])
+@pytest.mark.parametrize("q,bits", [(4, 4), (7, 4), (8, 5), (15, 5), (16, 6), (31, 6), (32, 7), (63, 7), (64, 8), (256, 16)])
 def test_qsgd_bit_widths(q, bits):
     grads = make_grads(2, 1, scale=0.5)
     fused, _ = run_fused(2, _params("qsgd", quantum_num=q), grads)
