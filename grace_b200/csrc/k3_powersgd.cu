@@ -7,21 +7,23 @@
 // i.e. ~20 + 12r library launches, three cuBLAS SGEMMs and two blocking NCCL all-reduces per
 // matrix, x 54 matrices for ResNet-50 (SURVEY §2.9-B PowerSGD row, §3.4).
 //
-// Here, for ALL matrices of a bucket at once (grouped through a work-item table):
-//   phase 1 (gb_psgd_send):  k3_prep   work = grad + residual; zero accumulators
-//                            k3_q0     Philox normal Q0, CholeskyQR2 orthogonalisation, Q0^T (K-major B operand)
-//                            k3_gemm<1> P_r = M Q0 : TMA -> smem (128B swizzle) -> tcgen05.mma kind::tf32 ->
-//                                      TMEM -> tcgen05.ld epilogue.  Split-K slices store their partial tiles; the
-//                                      CTA that completes a 128-row tile adds them in slice order (no floating-point
-//                                      atomics: the same bits on every run) and stores that tile straight
-//                                      into EVERY peer's slot (P2P st.global over NVLink) -- the all-reduce is an
-//                                      all-gather of tiny P_r tiles + rank-ordered sum on the receiver.
-//                            k3_flag   releases the epoch flags (and pushes tiles of matrices that took the
-//                                      CUDA-core fallback)
+// Here, for ALL matrices of a bucket at once (grouped through a work-item table), five launches after the tick:
+//   phase 1 (gb_psgd_send):  k3_prep   CTAs [0, nmat): Philox normal Q0 (or the previous Q on a warm start),
+//                                      CholeskyQR2, Q0^T (K-major B operand); band CTAs: M = grad + (M - P^ Q^T) -- the
+//                                      error-feedback memory is implicit, see the band kernels -- and clear the
+//                                      split-K tile counters
+//                            k3_gemm<1> P_r = M Q0 : persistent CTAs walk the work items; TMA -> smem (128B swizzle)
+//                                      -> tcgen05.mma kind::tf32 -> TMEM (two alternating accumulators) ->
+//                                      tcgen05.ld epilogue.  Split-K slices store their partial tiles; the CTA that
+//                                      completes a 128-row tile adds them in slice order (no floating-point atomics:
+//                                      the same bits on every run) and stores that tile straight into EVERY peer's
+//                                      slot (P2P st.global over NVLink, or one multimem.st) -- the all-reduce is an
+//                                      all-gather of tiny P_r tiles + rank-ordered sum on the receiver.  The CTA that
+//                                      finishes last releases the epoch flags.
+//                            (k3_gemm1_simt: matrices smaller than 8 x 32 on CUDA cores, pushes + releases itself)
 //   phase 2 (gb_psgd_mid):   k3_orth   wait flags; P = mean_r P_r (rank order); CholeskyQR2; P^ and P^^T
 //                            k3_gemm<2> Q_r = M^T P^ : A operand is MN-major straight from the row-major M tile
-//                            k3_flag
-//   phase 3 (gb_psgd_recv):  k3_final  wait flags; Q = mean_r Q_r; out = P^ Q^T; residual = work - out
+//   phase 3 (gb_psgd_recv):  k3_final  wait flags; Q = mean_r Q_r (kept for the next prep); out = P^ Q^T (write only)
 // Results are bit-identical on all ranks (every rank sums the same W tiles in the same order).
 // Orthogonalisation: two rounds of Cholesky-QR (Gram matrix, Cholesky, triangular solve) -- the
 // same Q factor Gram-Schmidt produces, with the reference formula's missing epsilon added
