@@ -11,8 +11,10 @@
 //                tile prefix, the 32 sub-block counts of that tile and a scan of one 128-element sub-block -- the
 //                reference's boolean_mask + gather without ever materialising the masked tensor
 //   aq_kth       k-th largest sampled magnitude (3 histogram rounds, one CTA per tensor and sign)
-//   21 x aq_select   the refinement loop, device-resident: count above the current thresholds; the CTA that
-//                finishes last applies the x1.25 / x0.9 rule to every (tensor, sign) -- no host round trips
+//   6 x aq_refine_tree   the refinement loop (<= 21 evaluations), device-resident: a launch counts against the current
+//                thresholds AND the 14 thresholds the next three decisions can lead to, the CTA that finishes last
+//                walks that tree with the x1.25 / x0.9 rule for every (tensor, sign): four evaluations per launch,
+//                no host round trips; single-tile tensors are refined to the end by their own CTA
 //   aq_select<final> + aq_mean    fixed-order sums -> one mean per tensor and sign, stored to every peer
 //   aq_emit      unordered compaction of the picked indices (sign in bit 31) straight into every peer's
 //                slot; residual = x - mean at the picked positions; the last CTA releases the flags

@@ -4,7 +4,9 @@
 //   memory/residual.py:10-20 (compensate / update), compressor/topk.py:6-18 (abs, topk,
 //   gather, zeros + scatter_), compressor/threshold.py:17-18 (where), compressor/randomk.py:6-12
 //   (randperm, index), communicator/allgather.py:8-45 (all_gather, W x scatter, sum, div)
-// by (SURVEY §2.9-B, rows TopK/Threshold/RandomK):
+// by (SURVEY §2.9-B, rows TopK/Threshold/RandomK) -- TopK itself now runs the two-pass kernels of k1_topk2.cu; the
+// four-pass kernels here stay behind GRACE_B200_TOPK_V1 and serve the stand-alone gb_topk_compress; Threshold, DGC
+// and the receive kernel k1_merge (all sparse codecs) live here:
 //   send:  pass1  compensate (written in place into the residual buffer) + radix histogram
 //          select exact per-segment threshold by 3 histogram rounds (11+10+10 bits of |x|)
 //          count / scan / emit: index-ORDERED compaction; (value, index32) pairs are stored

@@ -15,7 +15,7 @@
 //                       releases the flags
 //   recv:  k2_decode    acquire W flags; unpack the W ranks' codes, decode with the sender's
 //                       scalars, add in rank order (majority vote for sign codecs), write once
-// Wire formats are true bit-packs (1 bit sign codecs, 2-bit TernGrad, 4/8/16-bit QSGD) instead
+// Wire formats are true bit-packs (1 bit sign codecs, 2-bit TernGrad, 4/5/6/7/8/16-bit QSGD) instead
 // of the reference's one byte per element.
 #include "kernels.cuh"
 #include <cuda_fp16.h>

@@ -10,7 +10,8 @@
 //              digit prefixes are taken over the tiles of one tensor and no tensor id has to travel in the key (the
 //              first version sorted 64-bit (tensor id, key) words of the whole bucket in 5 passes: twice the bytes).
 //              No library kernel is on this path (round 1 called cub::DeviceRadixSort here).
-//   sk_edges   q+1 cut points per tensor, linear interpolation between order statistics
+//   sk_edges   q+1 cut points per tensor, linear interpolation between order statistics, and the first sorted position
+//              at or above every cut point (q+1 binary searches side by side)
 //   sk_means   one CTA per (bucket, tensor): the elements of a bucket are a contiguous range of the sorted
 //              tensor, so the mean is a fixed-order range sum (deterministic, no float atomics);
 //              means go straight into every peer's slot header
